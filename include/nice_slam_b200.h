@@ -1,0 +1,210 @@
+/*
+ * nice_slam_b200.h -- C ABI of the B200 (sm_100a) render hot path of NICE-SLAM.
+ *
+ * The reference (WohimLee/NICE-SLAM-annotation, pure Python/PyTorch) has no FFI: its hot
+ * path is the Python API Renderer.render_batch_ray / eval_points + the conv_onet decoders
+ * (SURVEY.md section 8b).  This header is what a native binding for that path binds: every
+ * entry point names the reference code it replaces (paths relative to the reference root).
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every pointer is a DEVICE pointer unless the name ends
+ *    in _host; nothing is allocated, retained or freed by the library; all work is queued
+ *    on `stream` (a cudaStream_t passed as void*) and the call returns without syncing.
+ *  - every function returns 0 on success, a negative NSB_E* code for a bad argument, or a
+ *    positive cudaError_t; nsb_last_error() returns a thread-local description.
+ *  - feature grids are fp32, logical shape [1, 32, Z, Y, X] as in the reference
+ *    (src/NICE_SLAM.py:243-320) but CHANNELS-LAST in memory: element (c, z, y, x) lives at
+ *    ((z*Y + y)*X + x)*32 + c, i.e. one 128-byte line per voxel
+ *    (torch.channels_last_3d).  Gradients use the same layout.
+ *  - points are addressed either as rays (p = rays_o + rays_d * z, evaluated in fp64 like
+ *    src/utils/Renderer.py:227-231) or as an explicit [P,3] array (fp64 or fp32).
+ */
+#ifndef NICE_SLAM_B200_H
+#define NICE_SLAM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NSB_VERSION 1
+
+/* error codes (negative); positive values are cudaError_t */
+#define NSB_EINVAL (-22)
+#define NSB_ENOSYS (-38)
+
+/* decoder kinds: src/conv_onet/models/decoder.py:316-334 (NICE sub-decoders) */
+#define NSB_DEC_COARSE 0 /* MLP_no_xyz, c_dim 32, 1 output  (decoder.py:222-297) */
+#define NSB_DEC_MIDDLE 1 /* MLP, fourier 93, c_dim 32, 1 output (decoder.py:93-219) */
+#define NSB_DEC_FINE 2   /* MLP, fourier 93, c_dim 64 (fine ++ middle feature), 1 output */
+#define NSB_DEC_COLOR 3  /* MLP, fourier 93, c_dim 32, 4 outputs */
+#define NSB_NUM_DEC 4
+
+/* stages of NICE.forward (decoder.py:336-370) */
+#define NSB_STAGE_COARSE 0
+#define NSB_STAGE_MIDDLE 1
+#define NSB_STAGE_FINE 2
+#define NSB_STAGE_COLOR 3
+/* NSB_STAGE_SINGLE + NSB_DEC_x: run decoder x alone (MLP.forward / MLP_no_xyz.forward,
+ * decoder.py:190-219,285-297); its plane is out_occ0 (coarse, middle), out_occ1 (fine) or
+ * out_rgb (color).  Accepted by nsb_decoders_forward / nsb_decoders_backward only. */
+#define NSB_STAGE_SINGLE 16
+
+/* backward selection flags */
+#define NSB_GRAD_GRID 1u   /* scatter-add d(grid) for the levels that carry gradient */
+#define NSB_GRAD_POINT 2u  /* d(point) -> per-ray d(rays_o), d(rays_d) */
+#define NSB_GRAD_WEIGHT 4u /* d(decoder parameters), bitmask of decoders in dweight_mask */
+
+typedef struct NsbGrid {
+    const float* data; /* channels-last fp32, may be NULL when the stage does not use it */
+    float* grad;       /* same layout, accumulated into (caller zeroes), may be NULL */
+    int32_t X, Y, Z;   /* grid_sample convention: X <-> p[:,0] <-> LAST logical dim */
+} NsbGrid;
+
+/* Point set of one call.  Ray mode: rays_o/rays_d [N,3] fp32 (row strides in floats, so a
+ * stride-0 rays_o as produced by src/common.py:88 is accepted) and z [N,S] fp64.
+ * Explicit mode (rays_o == NULL): p32 or p64 [P,3]. */
+typedef struct NsbPoints {
+    const float* rays_o;
+    const float* rays_d;
+    int64_t rays_o_stride; /* floats between consecutive rays (0 or 3) */
+    int64_t rays_d_stride;
+    const double* z;       /* [N,S] */
+    int64_t N;
+    int32_t S;
+    const double* p64;     /* [P,3] explicit points (fp64), or NULL */
+    const float* p32;      /* [P,3] explicit points (fp32), or NULL */
+    int64_t P;             /* number of points (N*S in ray mode) */
+} NsbPoints;
+
+/* Scene of one call: bound (src/NICE_SLAM.py:188-208), grids, packed decoders. */
+typedef struct NsbScene {
+    double bound[3][2];        /* lo/hi per axis, the Renderer's (non-enlarged) bound */
+    double coarse_bound[3][2]; /* bound * coarse_bound_enlarge (NICE_SLAM.py:208) */
+    NsbGrid grid[4];           /* indexed by NSB_DEC_* : coarse, middle, fine, color */
+    const float* packed[4];    /* nsb_pack_weights output per decoder, or NULL */
+} NsbScene;
+
+int nsb_version(void);
+const char* nsb_last_error(void);
+
+/* ---- decoder parameter packing ------------------------------------------------------
+ * Canonical parameter order of one decoder (reference state_dict names, decoder.py):
+ *   pts_linears.{0..4}.weight, pts_linears.{0..4}.bias, fc_c.{0..4}.weight,
+ *   fc_c.{0..4}.bias (absent for COARSE), output_linear.weight, output_linear.bias,
+ *   embedder._B (absent for COARSE).
+ * nsb_param_count / nsb_param_numel describe it; nsb_packed_numel is the size of the
+ * packed blob; nsb_pack_table_host fills a host int32 table (one entry per packed float:
+ * (param_index << 20) | element_offset, or -1 for a zero pad).  nsb_pack_weights gathers the
+ * blob on the device from the live parameter storages (dev array of pointers).
+ * nsb_unpack_weight_grads is not needed: weight gradients are produced in canonical flat
+ * order (concatenation of the parameters above). */
+int nsb_param_count(int kind);
+int64_t nsb_param_numel(int kind, int index);
+int64_t nsb_flat_numel(int kind);   /* sum of nsb_param_numel */
+int64_t nsb_packed_numel(int kind);
+int nsb_pack_table_host(int kind, int32_t* table_host);
+int nsb_pack_weights(int kind, const float* const* param_ptrs, const int32_t* table,
+                     float* packed, void* stream);
+
+/* ---- K1: rays and sample depths -------------------------------------------------------
+ * nsb_sample_rays: get_samples / get_rays_from_uv (src/common.py:74-134).  indices are flat
+ * indices into the crop [H0:H1, W0:W1] (row-major), as drawn by torch.randint
+ * (common.py:99).  c2w is 12 floats (3x4 row-major).  color may be fp32 or fp64
+ * (color_is_f64), the sampled colour is written as fp32.  prefilter (optional, may be
+ * NULL): keep[n] = (bbox exit >= gt depth), src/Tracker.py:100-107, src/Mapper.py:580-591. */
+int nsb_sample_rays(const int64_t* indices, int64_t n, int H0, int H1, int W0, int W1,
+                    int W_img, float fx, float fy, float cx, float cy, const float* c2w,
+                    const float* depth_img, const void* color_img, int color_is_f64,
+                    const double* bound6_host, float* rays_o, float* rays_d, float* gt_depth,
+                    float* gt_color, uint8_t* keep, void* stream);
+
+/* all-pixel rays, get_rays (src/common.py:259-277) */
+int nsb_all_rays(int H, int W, float fx, float fy, float cx, float cy, const float* c2w,
+                 float* rays_o, float* rays_d, void* stream);
+
+/* max over the batch of gt_depth (Renderer.py:157,194): out[0] = max(gt), fp32. */
+int nsb_depth_max(const float* gt_depth, int64_t N, float* out, void* stream);
+
+/* sorted sample depths z[N, N_samples + N_surface] in fp64 (Renderer.py:116-224).
+ * gt_depth NULL => near 0.01, far = box exit + 0.01, no surface samples.
+ * t_uniform [N_samples] fp32 and t_surface [N_surface] fp64 are torch.linspace(0,1,.)
+ * values supplied by the host; u (optional) [N,N_samples] fp32 uniforms for perturb > 0. */
+int nsb_sample_z(const NsbPoints* rays, const float* gt_depth, const double* bound6_host,
+                 int N_samples, int N_surface, int lindisp, const float* t_uniform,
+                 const double* t_surface, const float* u, const float* depth_max,
+                 double* z_out, void* stream);
+
+/* importance resampling: sample_pdf (src/common.py:19-63) + sort-merge with the old depths
+ * (Renderer.py:244-249).  weights [N,S] fp32 of the first pass, u [N,N_imp] fp32
+ * (torch.linspace for the deterministic case, uniforms otherwise). */
+int nsb_importance_z(const double* z, const float* weights, int64_t N, int S, int N_imp,
+                     const float* u, int64_t u_row_stride, double* z_samples, double* z_out,
+                     void* stream);
+
+/* ---- K2 + K3: grid gather + decoders --------------------------------------------------
+ * Forward of NICE.forward at `stage` (decoder.py:336-370) for all points.  Outputs are
+ * the raw decoder outputs per point, one plane per decoder that the stage runs:
+ *   out_occ0 [P]   coarse (stage coarse) or middle decoder output
+ *   out_occ1 [P]   fine decoder output (stages fine, color)
+ *   out_rgb  [P,4] colour decoder output (stage color)
+ * Planes a stage does not run may be NULL. */
+int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene, int stage,
+                         float* out_occ0, float* out_occ1, float* out_rgb, void* stream);
+
+/* raw [P,4] as returned by Renderer.eval_points (Renderer.py:36-93): rgb from out_rgb (or 0),
+ * occupancy = occ1 + occ0 (decoder.py:369), 100 for points outside the bound
+ * (Renderer.py:63-66,87).  inbound (optional) receives the mask. */
+int nsb_assemble_raw(const NsbPoints* pts, const double* bound6_host, int stage,
+                     const float* out_occ0, const float* out_occ1, const float* out_rgb,
+                     float* raw, uint8_t* inbound, void* stream);
+
+/* Backward of the above.  d_raw [P,4] is dL/d(raw) as produced by nsb_composite_backward
+ * (channel 3 already zero for out-of-bound points).  Selected by `flags`:
+ *   NSB_GRAD_GRID   -> scene->grid[k].grad accumulated (levels with gradient at this stage)
+ *   NSB_GRAD_POINT  -> d_point [ndec, P, 3] fp32, one plane per decoder that ran
+ *   NSB_GRAD_WEIGHT -> d_weight[k] (flat canonical order, accumulated) for k in dweight_mask;
+ *                      scratch must hold nsb_dweight_scratch_bytes(P) bytes
+ * Points whose incoming gradient is exactly zero are skipped. */
+int64_t nsb_dweight_scratch_bytes(int kind, int64_t P);
+int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene, int stage,
+                          const float* d_raw, unsigned flags, unsigned dweight_mask,
+                          float* const* d_weight_host, float* d_point, void* scratch,
+                          int64_t scratch_bytes, void* stream);
+
+/* ---- K4: volume rendering -------------------------------------------------------------
+ * raw2outputs_nerf_color (src/common.py:215-256) on the decoder planes of a stage, with the
+ * out-of-bound rule of eval_points folded in.  occupancy != 0: alpha = sigmoid(10 raw3);
+ * else alpha = 1 - exp(-relu(raw3) * dz * |rays_d|).  Outputs depth/var fp64, rgb fp32,
+ * weights [N,S] fp32 (optional). */
+int nsb_composite_forward(const NsbPoints* rays, const double* bound6_host, int stage,
+                          int occupancy, const float* out_occ0, const float* out_occ1,
+                          const float* out_rgb, double* depth, double* var, float* rgb,
+                          float* weights, void* stream);
+
+/* adjoint: (g_depth, g_var fp64; g_rgb fp32) -> d_raw [P,4]; in density mode also
+ * d_rays_d_norm [N,3] (gradient through |rays_d|), may be NULL otherwise. */
+int nsb_composite_backward(const NsbPoints* rays, const double* bound6_host, int stage,
+                           int occupancy, const float* out_occ0, const float* out_occ1,
+                           const float* out_rgb, const double* depth, const double* g_depth,
+                           const double* g_var, const float* g_rgb, float* d_raw,
+                           float* d_rays_d_norm, void* stream);
+
+/* per-ray reduction of point gradients: g_o[n] = sum_s dp, g_d[n] = sum_s z dp
+ * (+ d_rays_d_norm).  d_point [ndec, P, 3]. */
+int nsb_ray_grad_reduce(const NsbPoints* rays, const float* d_point, int ndec,
+                        const float* d_rays_d_norm, float* g_rays_o, float* g_rays_d,
+                        void* stream);
+
+/* camera gradient (src/common.py:137-176 adjoint): from per-ray
+ * gradients and pixel directions to d(camera_tensor[7]) = [dquat(4), dt(3)].
+ * dirs are recomputed from the pixel indices of nsb_sample_rays. */
+int nsb_pose_grad(const float* g_rays_o, const float* g_rays_d, const int64_t* indices,
+                  const uint8_t* keep, int64_t n, int H0, int W0, int Wc, float fx, float fy,
+                  float cx, float cy, const float* cam7, float* d_cam7, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NICE_SLAM_B200_H */

@@ -1,0 +1,100 @@
+"""ctypes binding of the C-ABI library ``csrc/libnsb200.so`` (include/nice_slam_b200.h).
+
+The library is loaded lazily, once per process, the first time a kernel is needed: the
+reference pickles Renderer / decoders into three spawned worker processes
+(src/NICE_SLAM.py:357-376), so no handle may be created at construction time.  There is no
+CPU fallback: a missing library is a hard error.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "csrc", "libnsb200.so")
+
+NSB_EINVAL, NSB_ENOSYS = -22, -38
+DEC_COARSE, DEC_MIDDLE, DEC_FINE, DEC_COLOR = 0, 1, 2, 3
+STAGES = {"coarse": 0, "middle": 1, "fine": 2, "color": 3}
+GRAD_GRID, GRAD_POINT, GRAD_WEIGHT = 1, 2, 4
+
+c_f32p = C.c_void_p      # device pointers travel as integers
+c_ptr = C.c_void_p
+
+
+class NsbGrid(C.Structure):
+    _fields_ = [("data", c_ptr), ("grad", c_ptr), ("X", C.c_int32), ("Y", C.c_int32), ("Z", C.c_int32)]
+
+
+class NsbPoints(C.Structure):
+    _fields_ = [("rays_o", c_ptr), ("rays_d", c_ptr), ("rays_o_stride", C.c_int64),
+                ("rays_d_stride", C.c_int64), ("z", c_ptr), ("N", C.c_int64), ("S", C.c_int32),
+                ("p64", c_ptr), ("p32", c_ptr), ("P", C.c_int64)]
+
+
+class NsbScene(C.Structure):
+    _fields_ = [("bound", (C.c_double * 2) * 3), ("coarse_bound", (C.c_double * 2) * 3),
+                ("grid", NsbGrid * 4), ("packed", c_ptr * 4)]
+
+
+_SIGS = {
+    "nsb_version": (C.c_int, []),
+    "nsb_last_error": (C.c_char_p, []),
+    "nsb_param_count": (C.c_int, [C.c_int]),
+    "nsb_param_numel": (C.c_int64, [C.c_int, C.c_int]),
+    "nsb_flat_numel": (C.c_int64, [C.c_int]),
+    "nsb_packed_numel": (C.c_int64, [C.c_int]),
+    "nsb_pack_table_host": (C.c_int, [C.c_int, c_ptr]),
+    "nsb_pack_weights": (C.c_int, [C.c_int, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "nsb_sample_rays": (C.c_int, [c_ptr, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                  C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, c_ptr, c_ptr,
+                                  C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "nsb_all_rays": (C.c_int, [C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, c_ptr,
+                               c_ptr, c_ptr, c_ptr]),
+    "nsb_depth_max": (C.c_int, [c_ptr, C.c_int64, c_ptr, c_ptr]),
+    "nsb_sample_z": (C.c_int, [C.POINTER(NsbPoints), c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, c_ptr,
+                               c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "nsb_importance_z": (C.c_int, [c_ptr, c_ptr, C.c_int64, C.c_int, C.c_int, c_ptr, C.c_int64, c_ptr,
+                                   c_ptr, c_ptr]),
+    "nsb_decoders_forward": (C.c_int, [C.POINTER(NsbPoints), C.POINTER(NsbScene), C.c_int, c_ptr, c_ptr,
+                                       c_ptr, c_ptr]),
+    "nsb_assemble_raw": (C.c_int, [C.POINTER(NsbPoints), c_ptr, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr,
+                                   c_ptr, c_ptr]),
+    "nsb_dweight_scratch_bytes": (C.c_int64, [C.c_int, C.c_int64]),
+    "nsb_decoders_backward": (C.c_int, [C.POINTER(NsbPoints), C.POINTER(NsbScene), C.c_int, c_ptr,
+                                        C.c_uint, C.c_uint, c_ptr, c_ptr, c_ptr, C.c_int64, c_ptr]),
+    "nsb_composite_forward": (C.c_int, [C.POINTER(NsbPoints), c_ptr, C.c_int, C.c_int, c_ptr, c_ptr,
+                                        c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "nsb_composite_backward": (C.c_int, [C.POINTER(NsbPoints), c_ptr, C.c_int, C.c_int, c_ptr, c_ptr,
+                                         c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "nsb_ray_grad_reduce": (C.c_int, [C.POINTER(NsbPoints), c_ptr, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "nsb_pose_grad": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_int, C.c_int, C.c_int,
+                                C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, c_ptr, c_ptr]),
+}
+
+EXPORTS = tuple(_SIGS)
+_lib = None
+
+
+def lib():
+    """The loaded library (raises if it has not been built: there is no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build the CUDA extension first "
+                "(python -m nice_slam_annotation_b200.build); there is no CPU fallback")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(handle, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = handle
+    return _lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = lib().nsb_last_error().decode(errors="replace")
+        raise RuntimeError(f"nice_slam_b200 {what} failed (code {rc}): {msg}")
+
+
+def __getstate__():      # pragma: no cover - module objects are not pickled
+    return {}

@@ -1,0 +1,208 @@
+// C-ABI plumbing: error reporting, decoder parameter description, pack tables, pack kernel.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "nsb_common.cuh"
+
+namespace nsb {
+
+static thread_local char g_err[512] = "";
+
+int set_error(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error((int)e, "%s: %s", what, cudaGetErrorString(e));
+    return 0;
+}
+
+// ---- canonical parameters ----------------------------------------------------------------------
+template <int KIND>
+static int64_t param_numel(int idx) {
+    using C = DecCfg<KIND>;
+    if (idx < 0 || idx >= C::N_PARAM) return -1;
+    if (idx < 5) return (int64_t)HID * C::in_dim(idx);           // pts_linears.i.weight [32, in]
+    if (idx < 10) return HID;                                    // pts_linears.i.bias
+    if (C::EMBED) {
+        if (idx < 15) return (int64_t)HID * C::C_IN;             // fc_c.i.weight [32, c_dim]
+        if (idx < 20) return HID;
+        if (idx == 20) return (int64_t)C::NOUT * HID;            // output_linear.weight [NOUT, 32]
+        if (idx == 21) return C::NOUT;
+        return 3 * EMB;                                          // embedder._B [3, 93]
+    }
+    if (idx == 10) return HID;
+    return 1;
+}
+
+static inline int32_t enc(int param, int off) { return (int32_t)((param << 20) | off); }
+
+// Fill one packed GEMM block.  slot(j,tau) -> k index of the source matrix or -1;
+// col(n,gamma) -> n index of the source matrix or -1; src(k, n) -> table entry.
+template <typename SlotF, typename ColF, typename SrcF>
+static void put_block(int32_t* tab, int off, int J, int NT, SlotF slot, ColF col, SrcF src) {
+    for (int j = 0; j < J; ++j)
+        for (int n = 0; n < NT; ++n)
+            for (int lane = 0; lane < 32; ++lane) {
+                const int g = lane >> 2, t = lane & 3;
+                int base;
+                if (NT == 1) base = off + (j * 32 + lane) * 2;
+                else base = off + ((j * (NT / 2) + n / 2) * 32 + lane) * 4 + 2 * (n & 1);
+                for (int q = 0; q < 2; ++q) {
+                    const int k = slot(j, t + 4 * q), c = col(n, g);
+                    tab[base + q] = (k < 0 || c < 0) ? -1 : src(k, c);
+                }
+            }
+}
+
+template <int KIND>
+static void build_table(int32_t* tab) {
+    using C = DecCfg<KIND>;
+    for (int i = 0; i < C::TOTAL; ++i) tab[i] = -1;
+    if (C::EMBED)
+        for (int a = 0; a < 3; ++a)
+            for (int f = 0; f < EMB; ++f) tab[C::OFF_B + a * EMB_PAD + f] = enc(C::P_EMB, a * EMB + f);
+    for (int i = 0; i < 5; ++i)
+        for (int k = 0; k < HID; ++k) {
+            tab[C::OFF_BIAS + i * HID + k] = enc(C::P_B + i, k);
+            if (C::EMBED) tab[C::OFF_BC + i * HID + k] = enc(C::P_BC + i, k);
+        }
+    for (int k = 0; k < C::NOUT; ++k) tab[C::OFF_BO + k] = enc(C::P_BO, k);
+
+    auto nat_out = [](int n, int g) { return 8 * n + g; };
+    // W_i as forward operand: B[k = input feature][n = output feature] = W[n][k]
+    auto fwdW = [](int i) {
+        const int in = C::in_dim(i);
+        return [i, in](int k, int n) { return enc(C::P_W + i, n * in + k); };
+    };
+    // W_i as backward operand: B[k = output feature][n = input feature] = W[k][n]
+    auto bwdW = [](int i) {
+        const int in = C::in_dim(i);
+        return [i, in](int k, int n) { return enc(C::P_W + i, k * in + n); };
+    };
+    auto chain_slot = [](int j, int tau) { return slot_chain(j, tau); };
+    auto gather_slot = [](int j, int tau) { return slot_gather(j, tau); };
+    auto gather_col = [](int n, int g) { return col_gather(n, g); };
+
+    const int offL[5] = {C::OFF_L0, C::OFF_L1, C::OFF_L2, C::OFF_L3, C::OFF_L4};
+    const int offC[5] = {C::OFF_C0, C::OFF_C1, C::OFF_C2, C::OFF_C3, C::OFF_C4};
+    const int offTL[5] = {C::OFF_TL0, C::OFF_TL1, C::OFF_TL2, C::OFF_TL3, C::OFF_TL4};
+    const int offTC[5] = {C::OFF_TC0, C::OFF_TC1, C::OFF_TC2, C::OFF_TC3, C::OFF_TC4};
+
+    if (C::EMBED) {
+        auto emb_slot = [](int j, int tau) { int f = slot_natural(j, tau); return f < EMB ? f : -1; };
+        auto emb_col = [](int n, int g) { int f = 8 * n + g; return f < EMB ? f : -1; };
+        // forward
+        put_block(tab, C::OFF_L0, E_SLABS, 4, emb_slot, nat_out, fwdW(0));
+        put_block(tab, C::OFF_L1, 4, 4, chain_slot, nat_out, fwdW(1));
+        put_block(tab, C::OFF_L2, 4, 4, chain_slot, nat_out, fwdW(2));
+        put_block(tab, C::OFF_L3, E_SLABS, 4, emb_slot, nat_out, fwdW(3));
+        put_block(tab, C::OFF_L3 + E_SLABS * C::SZ_SLAB, 4, 4,
+                  [](int j, int tau) { return EMB + slot_chain(j, tau); }, nat_out, fwdW(3));
+        put_block(tab, C::OFF_L4, 4, 4, chain_slot, nat_out, fwdW(4));
+        for (int i = 0; i < 5; ++i)
+            put_block(tab, offC[i], C::CS, 4, gather_slot, nat_out,
+                      [i](int k, int n) { return enc(C::P_WC + i, n * C::C_IN + k); });
+        // backward
+        put_block(tab, C::OFF_TL0, 4, E_SLABS, chain_slot, emb_col, bwdW(0));
+        put_block(tab, C::OFF_TL1, 4, 4, chain_slot, nat_out, bwdW(1));
+        put_block(tab, C::OFF_TL2, 4, 4, chain_slot, nat_out, bwdW(2));
+        put_block(tab, C::OFF_TL3X, 4, E_SLABS, chain_slot, emb_col, bwdW(3));
+        put_block(tab, C::OFF_TL3, 4, 4, chain_slot, [](int n, int g) { return EMB + 8 * n + g; }, bwdW(3));
+        put_block(tab, C::OFF_TL4, 4, 4, chain_slot, nat_out, bwdW(4));
+        for (int i = 0; i < 5; ++i)
+            put_block(tab, offTC[i], 4, 4, chain_slot, gather_col,
+                      [i](int k, int n) { return enc(C::P_WC + i, k * C::C_IN + n); });
+    } else {
+        put_block(tab, C::OFF_L0, 4, 4, gather_slot, nat_out, fwdW(0));
+        put_block(tab, C::OFF_L1, 4, 4, chain_slot, nat_out, fwdW(1));
+        put_block(tab, C::OFF_L2, 4, 4, chain_slot, nat_out, fwdW(2));
+        put_block(tab, C::OFF_L3, 4, 4, gather_slot, nat_out, fwdW(3));
+        put_block(tab, C::OFF_L3 + 4 * C::SZ_SLAB, 4, 4,
+                  [](int j, int tau) { return CDIM + slot_chain(j, tau); }, nat_out, fwdW(3));
+        put_block(tab, C::OFF_L4, 4, 4, chain_slot, nat_out, fwdW(4));
+        put_block(tab, C::OFF_TL0, 4, 4, chain_slot, gather_col, bwdW(0));
+        put_block(tab, C::OFF_TL1, 4, 4, chain_slot, nat_out, bwdW(1));
+        put_block(tab, C::OFF_TL2, 4, 4, chain_slot, nat_out, bwdW(2));
+        put_block(tab, C::OFF_TL3X, 4, 4, chain_slot, gather_col, bwdW(3));
+        put_block(tab, C::OFF_TL3, 4, 4, chain_slot, [](int n, int g) { return CDIM + 8 * n + g; }, bwdW(3));
+        put_block(tab, C::OFF_TL4, 4, 4, chain_slot, nat_out, bwdW(4));
+    }
+    (void)offL; (void)offTL;
+    // output layer: forward B[k = hidden][n = output] = Wo[n][k] (one n-tile);
+    // backward B[k = output (natural slot)][n = hidden] = Wo[k][n]
+    put_block(tab, C::OFF_OUT, 4, 1, chain_slot,
+              [](int n, int g) { (void)n; return g < C::NOUT ? g : -1; },
+              [](int k, int n) { return enc(C::P_WO, n * HID + k); });
+    put_block(tab, C::OFF_TOUT, 1, 4,
+              [](int j, int tau) { (void)j; return tau < C::NOUT ? tau : -1; }, nat_out,
+              [](int k, int n) { return enc(C::P_WO, k * HID + n); });
+}
+
+__global__ void k_pack(const float* const* __restrict__ ptrs, const int32_t* __restrict__ table,
+                       float* __restrict__ out, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int32_t e = table[i];
+    out[i] = e < 0 ? 0.f : ptrs[e >> 20][e & 0xfffff];
+}
+
+}  // namespace nsb
+
+using namespace nsb;
+
+#define KIND_SWITCH(kind, EXPR)                                            \
+    switch (kind) {                                                        \
+        case KIND_COARSE: { constexpr int K = KIND_COARSE; EXPR; } break;  \
+        case KIND_MIDDLE: { constexpr int K = KIND_MIDDLE; EXPR; } break;  \
+        case KIND_FINE: { constexpr int K = KIND_FINE; EXPR; } break;      \
+        case KIND_COLOR: { constexpr int K = KIND_COLOR; EXPR; } break;    \
+        default: return set_error(NSB_EINVAL, "bad decoder kind %d", kind); \
+    }
+
+extern "C" int nsb_version(void) { return NSB_VERSION; }
+extern "C" const char* nsb_last_error(void) { return g_err; }
+
+extern "C" int nsb_param_count(int kind) {
+    KIND_SWITCH(kind, return DecCfg<K>::N_PARAM);
+    return 0;
+}
+
+extern "C" int64_t nsb_param_numel(int kind, int index) {
+    KIND_SWITCH(kind, return param_numel<K>(index));
+    return 0;
+}
+
+extern "C" int64_t nsb_flat_numel(int kind) {
+    int n = nsb_param_count(kind);
+    if (n < 0) return n;
+    int64_t s = 0;
+    for (int i = 0; i < n; ++i) s += nsb_param_numel(kind, i);
+    return s;
+}
+
+extern "C" int64_t nsb_packed_numel(int kind) {
+    KIND_SWITCH(kind, return DecCfg<K>::TOTAL);
+    return 0;
+}
+
+extern "C" int nsb_pack_table_host(int kind, int32_t* table_host) {
+    if (!table_host) return set_error(NSB_EINVAL, "null table");
+    KIND_SWITCH(kind, build_table<K>(table_host));
+    return 0;
+}
+
+extern "C" int nsb_pack_weights(int kind, const float* const* param_ptrs, const int32_t* table,
+                                float* packed, void* stream) {
+    if (!param_ptrs || !table || !packed) return set_error(NSB_EINVAL, "null argument");
+    int64_t n = nsb_packed_numel(kind);
+    if (n < 0) return (int)n;
+    k_pack<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(param_ptrs, table, packed, (int)n);
+    return check_launch("k_pack");
+}

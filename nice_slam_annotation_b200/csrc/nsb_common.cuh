@@ -1,0 +1,172 @@
+// Device-side helpers shared by the kernels of the render hot path (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/nice_slam_b200.h"
+#include "nsb_layout.h"
+
+namespace nsb {
+
+constexpr int WARPS = 8;                 // warps per CTA of the decoder kernels
+constexpr int THREADS = WARPS * 32;
+constexpr unsigned FULL = 0xffffffffu;
+
+// ---- host-side error plumbing (nsb_api.cu) -------------------------------------------
+int set_error(int code, const char* fmt, ...);
+int check_launch(const char* what);
+
+// ---- points -------------------------------------------------------------------------
+struct PointsDev {
+    const float* ro;
+    const float* rd;
+    long long so, sd;
+    const double* z;
+    long long N;
+    int S;
+    const double* p64;
+    const float* p32;
+    long long P;
+};
+
+inline PointsDev to_dev(const NsbPoints& p) {
+    PointsDev d;
+    d.ro = p.rays_o; d.rd = p.rays_d; d.so = p.rays_o_stride; d.sd = p.rays_d_stride;
+    d.z = p.z; d.N = p.N; d.S = p.S; d.p64 = p.p64; d.p32 = p.p32;
+    d.P = p.rays_o ? p.N * (long long)p.S : p.P;
+    return d;
+}
+
+struct BoundDev {
+    double lo[3], hi[3];
+};
+
+inline BoundDev to_bound(const double* b6) {
+    BoundDev b;
+    for (int a = 0; a < 3; ++a) { b.lo[a] = b6[2 * a]; b.hi[a] = b6[2 * a + 1]; }
+    return b;
+}
+
+// p = rays_o + rays_d * z in fp64, un-fused, as torch evaluates
+// src/utils/Renderer.py:227-228 (fp32 rays promoted to fp64 by the fp64 z).
+__device__ __forceinline__ void ray_point(const PointsDev& q, long long i, double (&p)[3]) {
+    long long r = i / q.S;
+    double z = q.z[i];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+        p[a] = __dadd_rn((double)q.ro[r * q.so + a], __dmul_rn((double)q.rd[r * q.sd + a], z));
+}
+
+// strict in-bound test of Renderer.eval_points (Renderer.py:63-66)
+__device__ __forceinline__ bool inbound64(const double (&p)[3], const BoundDev& b) {
+    return p[0] < b.hi[0] && p[0] > b.lo[0] && p[1] < b.hi[1] && p[1] > b.lo[1] &&
+           p[2] < b.hi[2] && p[2] > b.lo[2];
+}
+__device__ __forceinline__ bool inbound32(const float (&p)[3], const BoundDev& b) {
+    return p[0] < (float)b.hi[0] && p[0] > (float)b.lo[0] && p[1] < (float)b.hi[1] &&
+           p[1] > (float)b.lo[1] && p[2] < (float)b.hi[2] && p[2] > (float)b.lo[2];
+}
+
+__device__ __forceinline__ bool point_inbound(const PointsDev& q, long long i, const BoundDev& b) {
+    if (q.ro) {
+        double p[3];
+        ray_point(q, i, p);
+        return inbound64(p, b);
+    }
+    if (q.p64) {
+        double p[3] = {q.p64[3 * i], q.p64[3 * i + 1], q.p64[3 * i + 2]};
+        return inbound64(p, b);
+    }
+    float p[3] = {q.p32[3 * i], q.p32[3 * i + 1], q.p32[3 * i + 2]};
+    return inbound32(p, b);
+}
+
+// ---- tensor-core primitives ---------------------------------------------------------------
+// D += A(16x8, row) * B(8x8, col), tf32 inputs, fp32 accumulate.
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
+                                         uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, "
+        "{%8,%9}, {%0,%1,%2,%3};\n"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// Exact two-term split x = hi + lo with hi representable in tf32 (low 13 mantissa bits
+// cleared).  Three tf32 products hi*hi + lo*hi + hi*lo then carry ~2^-20 relative error
+// per term, i.e. fp32-class accuracy on the tensor cores ("3xTF32").
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+    hi = __float_as_uint(x) & 0xffffe000u;
+    lo = __float_as_uint(x - __uint_as_float(hi));
+}
+
+// acc[NT][4] += A[J slabs] * B, B in packed fragment order (nsb_layout.h), 3xTF32.
+// a[j] is the A fragment of slab j: (row g, slot t), (row g+8, slot t), (row g, slot t+4),
+// (row g+8, slot t+4).
+template <int J, int NT>
+__device__ __forceinline__ void gemm3(float (&acc)[NT][4], const float (&a)[J][4],
+                                      const float* __restrict__ Bs, int lane) {
+    static_assert(NT % 2 == 0, "n-tiles come in pairs");
+    const float4* B4 = reinterpret_cast<const float4*>(Bs);
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        uint32_t ah[4], al[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) split_tf32(a[j][i], ah[i], al[i]);
+#pragma unroll
+        for (int h = 0; h < NT / 2; ++h) {
+            float4 b = B4[(j * (NT / 2) + h) * 32 + lane];
+            uint32_t bh[4], bl[4];
+            split_tf32(b.x, bh[0], bl[0]);
+            split_tf32(b.y, bh[1], bl[1]);
+            split_tf32(b.z, bh[2], bl[2]);
+            split_tf32(b.w, bh[3], bl[3]);
+            mma_tf32(acc[2 * h], al, bh[0], bh[1]);
+            mma_tf32(acc[2 * h], ah, bl[0], bl[1]);
+            mma_tf32(acc[2 * h], ah, bh[0], bh[1]);
+            mma_tf32(acc[2 * h + 1], al, bh[2], bh[3]);
+            mma_tf32(acc[2 * h + 1], ah, bl[2], bl[3]);
+            mma_tf32(acc[2 * h + 1], ah, bh[2], bh[3]);
+        }
+    }
+}
+
+// single n-tile variant: B stored as float2 per lane per slab (output layer)
+template <int J>
+__device__ __forceinline__ void gemm3_n1(float (&acc)[4], const float (&a)[J][4],
+                                         const float* __restrict__ Bs, int lane) {
+    const float2* B2 = reinterpret_cast<const float2*>(Bs);
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        uint32_t ah[4], al[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) split_tf32(a[j][i], ah[i], al[i]);
+        float2 b = B2[j * 32 + lane];
+        uint32_t bh[2], bl[2];
+        split_tf32(b.x, bh[0], bl[0]);
+        split_tf32(b.y, bh[1], bl[1]);
+        mma_tf32(acc, al, bh[0], bh[1]);
+        mma_tf32(acc, ah, bl[0], bl[1]);
+        mma_tf32(acc, ah, bh[0], bh[1]);
+    }
+}
+
+// accumulator (C fragment) of n-tile j -> A fragment of k-slab j under the "chain" slot map
+template <int J>
+__device__ __forceinline__ void chain(float (&a)[J][4], const float (&c)[J][4]) {
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        a[j][0] = c[j][0];
+        a[j][1] = c[j][2];
+        a[j][2] = c[j][1];
+        a[j][3] = c[j][3];
+    }
+}
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};\n" ::"l"(addr), "f"(a), "f"(b),
+                 "f"(c), "f"(d)
+                 : "memory");
+}
+
+}  // namespace nsb

@@ -1,0 +1,746 @@
+// K2 + K3 (+ their part of K5): trilinear grid gather, Gaussian-Fourier embedding and the
+// NICE decoder MLPs, forward and backward, as ONE persistent kernel per stage.
+//
+// Replaces, per point: MLP.sample_grid_feature / F.grid_sample (decoder.py:179-188,273-283),
+// GaussianFourierFeatureTransform (decoder.py:26-30), MLP.forward / MLP_no_xyz.forward
+// (decoder.py:190-219,285-297) and the stage mixing of NICE.forward (decoder.py:336-370),
+// plus their autograd backward.
+//
+// Design (B200, sm_100a):
+//  * a CTA is bound to ONE decoder of the stage (the stage's decoders run side by side in one
+//    launch on disjoint CTA ranges); it stages that decoder's packed weights in shared memory
+//    once and then loops over 16-point tiles, one tile per warp per iteration;
+//  * a warp owns 16 consecutive points.  Lane (g,t) (g = lane/4, t = lane%4) owns points g
+//    and g+8 and, of each gathered 32-channel voxel line, channels 8t..8t+7: every corner
+//    fetch is two 128-bit loads per lane, four lanes cover the 128-byte line, and the result
+//    lands DIRECTLY in mma A-fragment registers (slot map "gather", nsb_layout.h);
+//  * all layers run on the tensor cores as mma.sync.m16n8k8 tf32 with the 3xTF32 error
+//    compensation (fp32-class accuracy: parity with the reference's fp32 SGEMM needs it,
+//    SURVEY.md 7.3-1); the accumulator of one layer is re-used as the A operand of the next
+//    by permuting the k index of the packed weights ("chain" slot map), so activations never
+//    leave registers;
+//  * the Fourier embedding is evaluated in plain fp32 FMA + sinf/cosf (tf32 would destroy
+//    the phase, |p.B| reaches hundreds of radians);
+//  * backward recomputes the forward per tile (keeping only the ReLU sign bits), runs the
+//    transposed chain, turns d(e) into d(p) on the fly, scatters d(c) to the grid gradient
+//    with 128-bit vector reductions (red.global.add.v4.f32) and re-gathers the corners for
+//    the coordinate gradient.  Tiles whose incoming gradient is exactly zero are skipped.
+#include "nsb_common.cuh"
+
+namespace nsb {
+
+struct GridDev {
+    const float* data;
+    float* grad;
+    int X, Y, Z;
+};
+
+struct DecTask {
+    int kind;
+    int cta_begin, cta_count;
+    const float* packed;
+    GridDev own;      // grid whose feature feeds the decoder (gradient flows)
+    GridDev aux;      // FINE: the middle grid, sampled without gradient (decoder.py:199-201)
+    double lo[3], ext[3];
+    float* out;       // forward: [P] (1 output) or [P,4]
+    float* d_point;   // backward: [P,3] plane or NULL
+    float* dw_scratch;
+};
+
+struct StageParams {
+    PointsDev pts;
+    DecTask task[3];
+    int ntask;
+    const float* d_raw;   // backward: [P,4]
+    unsigned flags;
+};
+
+// ---- per-thread view of its two points -------------------------------------------------------
+struct Rows {
+    float p[2][3];   // world point, fp32 (embedding input: decoder.py:204 p.float())
+    float u[2][3];   // normalised to [-1,1] (common.py:280-295), fp32 as grid_sample sees it
+    bool valid[2];
+    long long idx[2];
+};
+
+template <int KIND>
+__device__ __forceinline__ void load_rows(const PointsDev& q, const DecTask& T, long long tile,
+                                          int lane, Rows& R) {
+    long long i = tile * 16 + (lane & 15);
+    bool ok = i < q.P;
+    long long ii = ok ? i : q.P - 1;
+    float p32[3], u[3];
+    if (q.ro == nullptr && q.p32 != nullptr) {
+        // fp32 points (Mesher / regulation callers): normalised in fp32
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            p32[a] = q.p32[3 * ii + a];
+            u[a] = __fsub_rn(__fmul_rn(__fdiv_rn(__fsub_rn(p32[a], (float)T.lo[a]), (float)T.ext[a]), 2.f), 1.0f);
+        }
+    } else {
+        double p[3];
+        if (q.ro) {
+            ray_point(q, ii, p);
+        } else {
+            p[0] = q.p64[3 * ii]; p[1] = q.p64[3 * ii + 1]; p[2] = q.p64[3 * ii + 2];
+        }
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            p32[a] = (float)p[a];
+            u[a] = (float)__dsub_rn(__dmul_rn(__ddiv_rn(__dsub_rn(p[a], T.lo[a]), T.ext[a]), 2.0), 1.0);
+        }
+    }
+    const int g = lane >> 2;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const int src = g + 8 * r;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            R.p[r][a] = __shfl_sync(FULL, p32[a], src);
+            R.u[r][a] = __shfl_sync(FULL, u[a], src);
+        }
+        R.valid[r] = __shfl_sync(FULL, (int)ok, src) != 0;
+        R.idx[r] = tile * 16 + src;
+    }
+}
+
+// ---- trilinear, ATen grid_sampler_3d semantics (bilinear, border, align_corners=True) ----------
+struct Tri {
+    float ix, iy, iz;      // clipped un-normalised coordinate
+    float x0, y0, z0;      // floor
+    int base, sx, sy, sz;  // voxel index of the (x0,y0,z0) corner and +1 steps (0 at the border)
+    float mx, my, mz;      // d(ix)/d(u) with the border rule (0 when clipped)
+};
+
+__device__ __forceinline__ void tri_axis(float u, int S, float& ic, float& f0, float& mult) {
+    float v = ((u + 1.f) / 2) * (float)(S - 1);
+    mult = (v <= 0.f || v >= (float)(S - 1)) ? 0.f : (float)(S - 1) / 2;
+    ic = fminf((float)(S - 1), fmaxf(v, 0.f));
+    f0 = floorf(ic);
+}
+
+__device__ __forceinline__ Tri tri_setup(const float (&u)[3], const GridDev& G) {
+    Tri t;
+    tri_axis(u[0], G.X, t.ix, t.x0, t.mx);
+    tri_axis(u[1], G.Y, t.iy, t.y0, t.my);
+    tri_axis(u[2], G.Z, t.iz, t.z0, t.mz);
+    int x0 = (int)t.x0, y0 = (int)t.y0, z0 = (int)t.z0;
+    t.base = (z0 * G.Y + y0) * G.X + x0;
+    t.sx = (x0 + 1 <= G.X - 1) ? 1 : 0;
+    t.sy = (y0 + 1 <= G.Y - 1) ? G.X : 0;
+    t.sz = (z0 + 1 <= G.Z - 1) ? G.X * G.Y : 0;
+    return t;
+}
+
+__device__ __forceinline__ float tri_weight(const Tri& T, int k) {
+    float wx = (k & 1) ? (T.ix - T.x0) : ((T.x0 + 1.f) - T.ix);
+    float wy = (k & 2) ? (T.iy - T.y0) : ((T.y0 + 1.f) - T.iy);
+    float wz = (k & 4) ? (T.iz - T.z0) : ((T.z0 + 1.f) - T.iz);
+    return (wx * wy) * wz;
+}
+
+__device__ __forceinline__ int tri_offset(const Tri& T, int k) {
+    return T.base + ((k & 1) ? T.sx : 0) + ((k & 2) ? T.sy : 0) + ((k & 4) ? T.sz : 0);
+}
+
+// 8 channels (8t .. 8t+7) of the trilinear feature of one point
+__device__ __forceinline__ void gather8(const float* __restrict__ grid, const Tri& T, int t,
+                                        float (&f)[8]) {
+    float4 v[8][2];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const float4* p = reinterpret_cast<const float4*>(grid + (size_t)tri_offset(T, k) * CDIM + 8 * t);
+        v[k][0] = __ldg(p);
+        v[k][1] = __ldg(p + 1);
+    }
+#pragma unroll
+    for (int c = 0; c < 8; ++c) f[c] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        float w = tri_weight(T, k);
+        f[0] = fmaf(v[k][0].x, w, f[0]); f[1] = fmaf(v[k][0].y, w, f[1]);
+        f[2] = fmaf(v[k][0].z, w, f[2]); f[3] = fmaf(v[k][0].w, w, f[3]);
+        f[4] = fmaf(v[k][1].x, w, f[4]); f[5] = fmaf(v[k][1].y, w, f[5]);
+        f[6] = fmaf(v[k][1].z, w, f[6]); f[7] = fmaf(v[k][1].w, w, f[7]);
+    }
+}
+
+// features of the thread's two points -> 4 A-fragment slabs ("gather" slot map)
+__device__ __forceinline__ void gather_level(const GridDev& G, const Rows& R, int t,
+                                             float (*c)[4]) {
+    float f0[8], f1[8];
+    Tri t0 = tri_setup(R.u[0], G), t1 = tri_setup(R.u[1], G);
+    gather8(G.data, t0, t, f0);
+    gather8(G.data, t1, t, f1);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        c[j][0] = f0[2 * j];
+        c[j][1] = f1[2 * j];
+        c[j][2] = f0[2 * j + 1];
+        c[j][3] = f1[2 * j + 1];
+    }
+}
+
+// e = sin(p @ B) (decoder.py:26-30) as 12 A-fragment slabs, "natural" slot map
+__device__ __forceinline__ float phase(const float (&p)[3], const float* Bs, int f) {
+    return fmaf(p[2], Bs[2 * EMB_PAD + f], fmaf(p[1], Bs[EMB_PAD + f], p[0] * Bs[f]));
+}
+
+__device__ __forceinline__ void embed(const Rows& R, const float* Bs, int t, float (&e)[E_SLABS][4]) {
+#pragma unroll
+    for (int j = 0; j < E_SLABS; ++j) {
+        const int f0 = 8 * j + t, f1 = f0 + 4;
+        e[j][0] = sinf(phase(R.p[0], Bs, f0));
+        e[j][1] = sinf(phase(R.p[1], Bs, f0));
+        e[j][2] = sinf(phase(R.p[0], Bs, f1));
+        e[j][3] = sinf(phase(R.p[1], Bs, f1));
+    }
+}
+
+// ---- MLP pieces ------------------------------------------------------------------------------
+__device__ __forceinline__ void bias_init(float (&acc)[4][4], const float* b, int t) {
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+        float2 v = *reinterpret_cast<const float2*>(b + 8 * n + 2 * t);
+        acc[n][0] = v.x; acc[n][1] = v.y; acc[n][2] = v.x; acc[n][3] = v.y;
+    }
+}
+__device__ __forceinline__ void bias_add(float (&acc)[4][4], const float* b, int t) {
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+        float2 v = *reinterpret_cast<const float2*>(b + 8 * n + 2 * t);
+        acc[n][0] += v.x; acc[n][1] += v.y; acc[n][2] += v.x; acc[n][3] += v.y;
+    }
+}
+template <bool MASK>
+__device__ __forceinline__ void relu_(float (&acc)[4][4], uint32_t& m) {
+    uint32_t bits = 0;
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            bool pos = acc[n][q] > 0.f;
+            if (MASK) bits |= (pos ? 1u : 0u) << (n * 4 + q);
+            acc[n][q] = pos ? acc[n][q] : 0.f;
+        }
+    if (MASK) m = bits;
+}
+__device__ __forceinline__ void mask_(float (&acc)[4][4], uint32_t m) {
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            if (!((m >> (n * 4 + q)) & 1u)) acc[n][q] = 0.f;
+}
+__device__ __forceinline__ void zero_(float (&acc)[4][4]) {
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[n][q] = 0.f;
+}
+
+// MLP.forward (EMBED) / MLP_no_xyz.forward (COARSE) for one 16-point tile.  e: embedding
+// slabs (unused for COARSE), c: feature slabs.  out: C fragment of the padded 8-column output
+// tile (columns 2t, 2t+1 for rows g, g+8).  mask[i]: sign bits of the i-th ReLU input.
+template <int KIND, bool MASK>
+__device__ __forceinline__ void mlp_forward(const float* sm, int lane,
+                                            const float (&e)[E_SLABS][4],
+                                            const float (&c)[DecCfg<KIND>::CS][4], float (&out)[4],
+                                            uint32_t (&mask)[5]) {
+    using C = DecCfg<KIND>;
+    const int t = lane & 3;
+    float acc[4][4], h[4][4];
+    const float* b = sm + C::OFF_BIAS;
+    const float* bc = sm + C::OFF_BC;
+    if constexpr (C::EMBED) {
+        bias_init(acc, b, t);
+        gemm3<E_SLABS, 4>(acc, e, sm + C::OFF_L0, lane);
+        relu_<MASK>(acc, mask[0]);
+        bias_add(acc, bc, t);
+        gemm3<C::CS, 4>(acc, c, sm + C::OFF_C0, lane);
+        chain<4>(h, acc);
+
+        bias_init(acc, b + 32, t);
+        gemm3<4, 4>(acc, h, sm + C::OFF_L1, lane);
+        relu_<MASK>(acc, mask[1]);
+        bias_add(acc, bc + 32, t);
+        gemm3<C::CS, 4>(acc, c, sm + C::OFF_C1, lane);
+        chain<4>(h, acc);
+
+        bias_init(acc, b + 64, t);
+        gemm3<4, 4>(acc, h, sm + C::OFF_L2, lane);
+        relu_<MASK>(acc, mask[2]);
+        bias_add(acc, bc + 64, t);
+        gemm3<C::CS, 4>(acc, c, sm + C::OFF_C2, lane);
+        chain<4>(h, acc);
+
+        bias_init(acc, b + 96, t);                                   // skip: [e, h] (decoder.py:214-215)
+        gemm3<E_SLABS, 4>(acc, e, sm + C::OFF_L3, lane);
+        gemm3<4, 4>(acc, h, sm + C::OFF_L3 + E_SLABS * C::SZ_SLAB, lane);
+        relu_<MASK>(acc, mask[3]);
+        bias_add(acc, bc + 96, t);
+        gemm3<C::CS, 4>(acc, c, sm + C::OFF_C3, lane);
+        chain<4>(h, acc);
+
+        bias_init(acc, b + 128, t);
+        gemm3<4, 4>(acc, h, sm + C::OFF_L4, lane);
+        relu_<MASK>(acc, mask[4]);
+        bias_add(acc, bc + 128, t);
+        gemm3<C::CS, 4>(acc, c, sm + C::OFF_C4, lane);
+        chain<4>(h, acc);
+    } else {
+        bias_init(acc, b, t);
+        gemm3<4, 4>(acc, c, sm + C::OFF_L0, lane);
+        relu_<MASK>(acc, mask[0]);
+        chain<4>(h, acc);
+        bias_init(acc, b + 32, t);
+        gemm3<4, 4>(acc, h, sm + C::OFF_L1, lane);
+        relu_<MASK>(acc, mask[1]);
+        chain<4>(h, acc);
+        bias_init(acc, b + 64, t);
+        gemm3<4, 4>(acc, h, sm + C::OFF_L2, lane);
+        relu_<MASK>(acc, mask[2]);
+        chain<4>(h, acc);
+        bias_init(acc, b + 96, t);                                   // skip: [c, h] (decoder.py:293-294)
+        gemm3<4, 4>(acc, c, sm + C::OFF_L3, lane);
+        gemm3<4, 4>(acc, h, sm + C::OFF_L3 + 4 * C::SZ_SLAB, lane);
+        relu_<MASK>(acc, mask[3]);
+        chain<4>(h, acc);
+        bias_init(acc, b + 128, t);
+        gemm3<4, 4>(acc, h, sm + C::OFF_L4, lane);
+        relu_<MASK>(acc, mask[4]);
+        chain<4>(h, acc);
+    }
+    float2 bo = *reinterpret_cast<const float2*>(sm + C::OFF_BO + 2 * t);
+    out[0] = bo.x; out[1] = bo.y; out[2] = bo.x; out[3] = bo.y;
+    gemm3_n1<4>(out, h, sm + C::OFF_OUT, lane);
+}
+
+__device__ __forceinline__ void stage_weights(float* sm, const float* __restrict__ packed, int n) {
+    const float4* src = reinterpret_cast<const float4*>(packed);
+    float4* dst = reinterpret_cast<float4*>(sm);
+    for (int i = threadIdx.x; i < n / 4; i += blockDim.x) dst[i] = __ldg(src + i);
+    __syncthreads();
+}
+
+// inputs of a tile: rows, embedding, features
+template <int KIND>
+__device__ __forceinline__ void tile_inputs(const PointsDev& q, const DecTask& T, const float* sm,
+                                            long long tile, int lane, Rows& R,
+                                            float (&e)[E_SLABS][4],
+                                            float (&c)[DecCfg<KIND>::CS][4]) {
+    using C = DecCfg<KIND>;
+    const int t = lane & 3;
+    load_rows<KIND>(q, T, tile, lane, R);
+    gather_level(T.own, R, t, c);
+    if constexpr (KIND == KIND_FINE) gather_level(T.aux, R, t, c + 4);
+    if constexpr (C::EMBED) embed(R, sm + C::OFF_B, t, e);
+}
+
+template <int KIND>
+__device__ void decoder_forward_cta(const StageParams& P, const DecTask& T, float* sm) {
+    using C = DecCfg<KIND>;
+    stage_weights(sm, T.packed, C::FWD_END);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const long long ntiles = (P.pts.P + 15) / 16;
+    for (long long tile = (long long)(blockIdx.x - T.cta_begin) * WARPS + warp; tile < ntiles;
+         tile += (long long)T.cta_count * WARPS) {
+        Rows R;
+        float e[E_SLABS][4];
+        float c[C::CS][4];
+        tile_inputs<KIND>(P.pts, T, sm, tile, lane, R, e, c);
+        float out[4];
+        uint32_t mask[5];
+        mlp_forward<KIND, false>(sm, lane, e, c, out, mask);
+        if constexpr (C::NOUT == 1) {
+            if (t == 0) {
+                if (R.valid[0]) T.out[R.idx[0]] = out[0];
+                if (R.valid[1]) T.out[R.idx[1]] = out[2];
+            }
+        } else {
+            if (t < 2) {
+                if (R.valid[0]) *reinterpret_cast<float2*>(T.out + 4 * R.idx[0] + 2 * t) = make_float2(out[0], out[1]);
+                if (R.valid[1]) *reinterpret_cast<float2*>(T.out + 4 * R.idx[1] + 2 * t) = make_float2(out[2], out[3]);
+            }
+        }
+        (void)g;
+    }
+}
+
+__global__ void __launch_bounds__(THREADS, 1)
+k_decoders_forward(const __grid_constant__ StageParams P) {
+    extern __shared__ __align__(16) float sm[];
+    int k = 0;
+    while (k + 1 < P.ntask && (int)blockIdx.x >= P.task[k + 1].cta_begin) ++k;
+    const DecTask& T = P.task[k];
+    switch (T.kind) {
+        case KIND_COARSE: decoder_forward_cta<KIND_COARSE>(P, T, sm); break;
+        case KIND_MIDDLE: decoder_forward_cta<KIND_MIDDLE>(P, T, sm); break;
+        case KIND_FINE: decoder_forward_cta<KIND_FINE>(P, T, sm); break;
+        default: decoder_forward_cta<KIND_COLOR>(P, T, sm); break;
+    }
+}
+
+// ---- backward -------------------------------------------------------------------------------
+// d(e) (C fragments, natural column map, 12 n-tiles) -> d(p): e = sin(p.B) so
+// d(p_a) += d(e_f) cos(p.B_f) B[a][f].
+__device__ __forceinline__ void embed_grad(const float (&dE)[E_SLABS][4], const Rows& R,
+                                           const float* Bs, int t, float (&dp)[2][3]) {
+#pragma unroll
+    for (int n = 0; n < E_SLABS; ++n)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int r = q >> 1, f = 8 * n + 2 * t + (q & 1);
+            float v = dE[n][q] * cosf(phase(R.p[r], Bs, f));
+            dp[r][0] = fmaf(v, Bs[f], dp[r][0]);
+            dp[r][1] = fmaf(v, Bs[EMB_PAD + f], dp[r][1]);
+            dp[r][2] = fmaf(v, Bs[2 * EMB_PAD + f], dp[r][2]);
+        }
+}
+
+// scatter-add d(c) (8 channels of one point) to the 8 corners; optionally the coordinate
+// gradient (ATen grid_sampler_3d_backward: d(ix) = sum_corners +-(other two weights) <g, v>)
+template <bool SCATTER, bool COORD>
+__device__ __forceinline__ void grid_backward(const GridDev& G, const float (&u)[3],
+                                              const double* ext, int t, const float (&dc)[8],
+                                              float (&dp)[3]) {
+    Tri T = tri_setup(u, G);
+    float gx = 0.f, gy = 0.f, gz = 0.f;
+    const float wx[2] = {(T.x0 + 1.f) - T.ix, T.ix - T.x0};
+    const float wy[2] = {(T.y0 + 1.f) - T.iy, T.iy - T.y0};
+    const float wz[2] = {(T.z0 + 1.f) - T.iz, T.iz - T.z0};
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const size_t off = (size_t)tri_offset(T, k) * CDIM + 8 * t;
+        if (SCATTER) {
+            float w = tri_weight(T, k);
+            red_add_v4(G.grad + off, w * dc[0], w * dc[1], w * dc[2], w * dc[3]);
+            red_add_v4(G.grad + off + 4, w * dc[4], w * dc[5], w * dc[6], w * dc[7]);
+        }
+        if (COORD) {
+            const float4* p = reinterpret_cast<const float4*>(G.data + off);
+            float4 a = __ldg(p), b = __ldg(p + 1);
+            float s = a.x * dc[0] + a.y * dc[1] + a.z * dc[2] + a.w * dc[3] + b.x * dc[4] +
+                      b.y * dc[5] + b.z * dc[6] + b.w * dc[7];
+            const int dx = k & 1, dy = (k >> 1) & 1, dz = k >> 2;
+            gx += (dx ? s : -s) * wy[dy] * wz[dz];
+            gy += (dy ? s : -s) * wx[dx] * wz[dz];
+            gz += (dz ? s : -s) * wx[dx] * wy[dy];
+        }
+    }
+    if (COORD) {
+        dp[0] += gx * T.mx * (float)(2.0 / ext[0]);
+        dp[1] += gy * T.my * (float)(2.0 / ext[1]);
+        dp[2] += gz * T.mz * (float)(2.0 / ext[2]);
+    }
+}
+
+template <int KIND>
+__device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, float* sm) {
+    using C = DecCfg<KIND>;
+    stage_weights(sm, T.packed, C::TOTAL);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, t = lane & 3;
+    const long long ntiles = (P.pts.P + 15) / 16;
+    const bool want_grid = (P.flags & NSB_GRAD_GRID) && T.own.grad != nullptr;
+    const bool want_point = (P.flags & NSB_GRAD_POINT) && T.d_point != nullptr;
+    for (long long tile = (long long)(blockIdx.x - T.cta_begin) * WARPS + warp; tile < ntiles;
+         tile += (long long)T.cta_count * WARPS) {
+        // incoming gradient first: most tiles behind the surface carry exact zeros
+        float dA[1][4];
+        {
+            const long long i0 = tile * 16 + (lane >> 2), i1 = i0 + 8;
+            float v0 = 0.f, v1 = 0.f;
+            if (C::NOUT == 1) {
+                if (t == 0) {
+                    if (i0 < P.pts.P) v0 = P.d_raw[4 * i0 + 3];
+                    if (i1 < P.pts.P) v1 = P.d_raw[4 * i1 + 3];
+                }
+            } else {
+                if (t < 3) {
+                    if (i0 < P.pts.P) v0 = P.d_raw[4 * i0 + t];
+                    if (i1 < P.pts.P) v1 = P.d_raw[4 * i1 + t];
+                }
+            }
+            dA[0][0] = v0; dA[0][1] = v1; dA[0][2] = 0.f; dA[0][3] = 0.f;
+            if (!__any_sync(FULL, v0 != 0.f || v1 != 0.f)) {
+                if (want_point && t == 0) {
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        if (i0 < P.pts.P) T.d_point[3 * i0 + a] = 0.f;
+                        if (i1 < P.pts.P) T.d_point[3 * i1 + a] = 0.f;
+                    }
+                }
+                continue;
+            }
+        }
+        Rows R;
+        uint32_t mask[5];
+        {
+            float e[E_SLABS][4];
+            float c[C::CS][4];
+            float out[4];
+            tile_inputs<KIND>(P.pts, T, sm, tile, lane, R, e, c);
+            mlp_forward<KIND, true>(sm, lane, e, c, out, mask);
+        }
+        float dp[2][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
+        float dh[4][4], a[4][4], dc[4][4];
+        zero_(dh);
+        zero_(dc);
+        gemm3<1, 4>(dh, dA, sm + C::OFF_TOUT, lane);                  // d(h5)
+        // layer 4
+        chain<4>(a, dh);
+        if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + C::OFF_TC4, lane);
+        mask_(dh, mask[4]); chain<4>(a, dh); zero_(dh);
+        gemm3<4, 4>(dh, a, sm + C::OFF_TL4, lane);                    // d(h4)
+        // layer 3 (skip input)
+        chain<4>(a, dh);
+        if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + C::OFF_TC3, lane);
+        mask_(dh, mask[3]); chain<4>(a, dh); zero_(dh);
+        if constexpr (C::EMBED) {
+            if (want_point) {
+                float dE[E_SLABS][4];
+#pragma unroll
+                for (int n = 0; n < E_SLABS; ++n)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) dE[n][q] = 0.f;
+                gemm3<4, E_SLABS>(dE, a, sm + C::OFF_TL3X, lane);
+                embed_grad(dE, R, sm + C::OFF_B, t, dp);
+            }
+        } else {
+            gemm3<4, 4>(dc, a, sm + C::OFF_TL3X, lane);
+        }
+        gemm3<4, 4>(dh, a, sm + C::OFF_TL3, lane);                    // d(h3)
+        // layer 2
+        chain<4>(a, dh);
+        if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + C::OFF_TC2, lane);
+        mask_(dh, mask[2]); chain<4>(a, dh); zero_(dh);
+        gemm3<4, 4>(dh, a, sm + C::OFF_TL2, lane);
+        // layer 1
+        chain<4>(a, dh);
+        if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + C::OFF_TC1, lane);
+        mask_(dh, mask[1]); chain<4>(a, dh); zero_(dh);
+        gemm3<4, 4>(dh, a, sm + C::OFF_TL1, lane);
+        // layer 0
+        chain<4>(a, dh);
+        if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + C::OFF_TC0, lane);
+        mask_(dh, mask[0]); chain<4>(a, dh);
+        if constexpr (C::EMBED) {
+            if (want_point) {
+                float dE[E_SLABS][4];
+#pragma unroll
+                for (int n = 0; n < E_SLABS; ++n)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) dE[n][q] = 0.f;
+                gemm3<4, E_SLABS>(dE, a, sm + C::OFF_TL0, lane);
+                embed_grad(dE, R, sm + C::OFF_B, t, dp);
+            }
+        } else {
+            gemm3<4, 4>(dc, a, sm + C::OFF_TL0, lane);
+        }
+        // d(c): gather column map -> lane holds channels 8t..8t+7 of rows g, g+8
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            float d8[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) d8[k] = dc[k >> 1][2 * r + (k & 1)];
+            if (R.valid[r]) {
+                if (want_grid && want_point) grid_backward<true, true>(T.own, R.u[r], T.ext, t, d8, dp[r]);
+                else if (want_grid) grid_backward<true, false>(T.own, R.u[r], T.ext, t, d8, dp[r]);
+                else if (want_point) grid_backward<false, true>(T.own, R.u[r], T.ext, t, d8, dp[r]);
+            }
+        }
+        if (want_point) {
+#pragma unroll
+            for (int r = 0; r < 2; ++r)
+#pragma unroll
+                for (int ax = 0; ax < 3; ++ax) {
+                    float v = dp[r][ax];
+                    v += __shfl_xor_sync(FULL, v, 1);
+                    v += __shfl_xor_sync(FULL, v, 2);
+                    if (t == 0 && R.valid[r]) T.d_point[3 * R.idx[r] + ax] = v;
+                }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(THREADS, 1)
+k_decoders_backward(const __grid_constant__ StageParams P) {
+    extern __shared__ __align__(16) float sm[];
+    int k = 0;
+    while (k + 1 < P.ntask && (int)blockIdx.x >= P.task[k + 1].cta_begin) ++k;
+    const DecTask& T = P.task[k];
+    switch (T.kind) {
+        case KIND_COARSE: decoder_backward_cta<KIND_COARSE>(P, T, sm); break;
+        case KIND_MIDDLE: decoder_backward_cta<KIND_MIDDLE>(P, T, sm); break;
+        case KIND_FINE: decoder_backward_cta<KIND_FINE>(P, T, sm); break;
+        default: decoder_backward_cta<KIND_COLOR>(P, T, sm); break;
+    }
+}
+
+// ---- host side -------------------------------------------------------------------------------
+static int g_num_sms = 0;
+static bool g_attr_done = false;
+
+static int blob_floats(int kind, bool bwd) {
+    switch (kind) {
+        case KIND_COARSE: return bwd ? DecCfg<KIND_COARSE>::TOTAL : DecCfg<KIND_COARSE>::FWD_END;
+        case KIND_MIDDLE: return bwd ? DecCfg<KIND_MIDDLE>::TOTAL : DecCfg<KIND_MIDDLE>::FWD_END;
+        case KIND_FINE: return bwd ? DecCfg<KIND_FINE>::TOTAL : DecCfg<KIND_FINE>::FWD_END;
+        default: return bwd ? DecCfg<KIND_COLOR>::TOTAL : DecCfg<KIND_COLOR>::FWD_END;
+    }
+}
+
+static int init_device() {
+    if (g_attr_done) return 0;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return set_error((int)e, "cudaGetDevice: %s", cudaGetErrorString(e));
+    int sms = 0;
+    e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return set_error((int)e, "device attribute: %s", cudaGetErrorString(e));
+    g_num_sms = sms;
+    const int max_smem = DecCfg<KIND_FINE>::TOTAL * 4;
+    e = cudaFuncSetAttribute(k_decoders_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_decoders_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+    if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    g_attr_done = true;
+    return 0;
+}
+
+// decoders of a stage (decoder.py:336-370) and their relative cost per point
+static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp, float* out_occ0,
+                       float* out_occ1, float* out_rgb, float* d_point, long long P) {
+    int kinds[3], n = 0;
+    float cost[3];
+    switch (stage) {
+        case NSB_STAGE_COARSE: kinds[n] = KIND_COARSE; cost[n++] = 12.f; break;
+        case NSB_STAGE_MIDDLE: kinds[n] = KIND_MIDDLE; cost[n++] = 30.f; break;
+        case NSB_STAGE_FINE:
+            kinds[n] = KIND_MIDDLE; cost[n++] = 30.f;
+            kinds[n] = KIND_FINE; cost[n++] = 41.f;
+            break;
+        case NSB_STAGE_COLOR:
+            kinds[n] = KIND_MIDDLE; cost[n++] = 30.f;
+            kinds[n] = KIND_FINE; cost[n++] = 41.f;
+            kinds[n] = KIND_COLOR; cost[n++] = 31.f;
+            break;
+        default:
+            if (stage >= NSB_STAGE_SINGLE && stage < NSB_STAGE_SINGLE + NSB_NUM_DEC) {
+                kinds[n] = stage - NSB_STAGE_SINGLE; cost[n++] = 1.f;     // one decoder on its own
+                break;
+            }
+            return set_error(NSB_EINVAL, "bad stage %d", stage);
+    }
+    const long long tiles = (P + 15) / 16;
+    const long long want_ll = (tiles + WARPS - 1) / WARPS;   // CTAs that give every warp one tile
+    const int want = want_ll > (1 << 20) ? (1 << 20) : (int)want_ll;
+    float total = 0.f;
+    for (int i = 0; i < n; ++i) total += cost[i];
+    // one persistent CTA per SM, split between the decoders in proportion to their cost
+    int share_of[3], used = 0;
+    float frac[3];
+    for (int i = 0; i < n; ++i) {
+        float s = g_num_sms * cost[i] / total;
+        share_of[i] = (int)s;
+        frac[i] = s - share_of[i];
+        if (share_of[i] < 1) { share_of[i] = 1; frac[i] = 0.f; }
+        used += share_of[i];
+    }
+    while (used < g_num_sms) {
+        int best = 0;
+        for (int i = 1; i < n; ++i) if (frac[i] > frac[best]) best = i;
+        share_of[best]++; frac[best] = -1.f; used++;
+    }
+    int begin = 0;
+    for (int i = 0; i < n; ++i) {
+        DecTask& T = sp.task[i];
+        const int k = kinds[i];
+        T.kind = k;
+        if (!sc.packed[k]) return set_error(NSB_EINVAL, "stage %d needs packed decoder %d", stage, k);
+        T.packed = sc.packed[k];
+        const NsbGrid& G = sc.grid[k];
+        if (!G.data) return set_error(NSB_EINVAL, "stage %d needs grid %d", stage, k);
+        T.own = GridDev{G.data, G.grad, G.X, G.Y, G.Z};
+        T.aux = GridDev{nullptr, nullptr, 1, 1, 1};
+        if (k == KIND_FINE) {
+            const NsbGrid& M = sc.grid[KIND_MIDDLE];
+            if (!M.data) return set_error(NSB_EINVAL, "fine decoder needs the middle grid");
+            T.aux = GridDev{M.data, nullptr, M.X, M.Y, M.Z};
+        }
+        for (int a = 0; a < 3; ++a) {
+            const double lo = k == KIND_COARSE ? sc.coarse_bound[a][0] : sc.bound[a][0];
+            const double hi = k == KIND_COARSE ? sc.coarse_bound[a][1] : sc.bound[a][1];
+            T.lo[a] = lo;
+            T.ext[a] = hi - lo;
+        }
+        T.out = (k == KIND_COLOR) ? out_rgb : (k == KIND_FINE ? out_occ1 : out_occ0);
+        if (!bwd && !T.out) return set_error(NSB_EINVAL, "missing output plane for decoder %d", k);
+        T.d_point = d_point ? d_point + (size_t)i * P * 3 : nullptr;
+        T.dw_scratch = nullptr;
+        int share = share_of[i];
+        if (share > want) share = want;
+        T.cta_begin = begin;
+        T.cta_count = share;
+        begin += share;
+    }
+    sp.ntask = n;
+    return begin;
+}
+
+static int max_blob(const StageParams& sp, bool bwd) {
+    int m = 0;
+    for (int i = 0; i < sp.ntask; ++i) {
+        int b = blob_floats(sp.task[i].kind, bwd);
+        if (b > m) m = b;
+    }
+    return m;
+}
+
+}  // namespace nsb
+
+using namespace nsb;
+
+extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene, int stage,
+                                    float* out_occ0, float* out_occ1, float* out_rgb,
+                                    void* stream) {
+    if (!pts || !scene) return set_error(NSB_EINVAL, "null argument");
+    if (int rc = init_device()) return rc;
+    StageParams sp{};
+    sp.pts = to_dev(*pts);
+    if (sp.pts.P <= 0) return 0;
+    if (!sp.pts.ro && !sp.pts.p64 && !sp.pts.p32) return set_error(NSB_EINVAL, "no points given");
+    int ctas = stage_tasks(*scene, stage, false, sp, out_occ0, out_occ1, out_rgb, nullptr, sp.pts.P);
+    if (ctas < 0) return ctas;
+    sp.d_raw = nullptr;
+    sp.flags = 0;
+    k_decoders_forward<<<ctas, THREADS, max_blob(sp, false) * 4, (cudaStream_t)stream>>>(sp);
+    return check_launch("k_decoders_forward");
+}
+
+extern "C" int64_t nsb_dweight_scratch_bytes(int kind, int64_t P) {
+    (void)kind; (void)P;
+    return 0;
+}
+
+extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene, int stage,
+                                     const float* d_raw, unsigned flags, unsigned dweight_mask,
+                                     float* const* d_weight_host, float* d_point, void* scratch,
+                                     int64_t scratch_bytes, void* stream) {
+    if (!pts || !scene || !d_raw) return set_error(NSB_EINVAL, "null argument");
+    if (int rc = init_device()) return rc;
+    if ((flags & NSB_GRAD_WEIGHT) && dweight_mask)
+        return set_error(NSB_ENOSYS, "decoder weight gradients are not available in this build");
+    (void)d_weight_host; (void)scratch; (void)scratch_bytes;
+    StageParams sp{};
+    sp.pts = to_dev(*pts);
+    if (sp.pts.P <= 0) return 0;
+    if ((flags & NSB_GRAD_POINT) && !d_point) return set_error(NSB_EINVAL, "d_point is NULL");
+    int ctas = stage_tasks(*scene, stage, true, sp, nullptr, nullptr, nullptr,
+                           (flags & NSB_GRAD_POINT) ? d_point : nullptr, sp.pts.P);
+    if (ctas < 0) return ctas;
+    sp.d_raw = d_raw;
+    sp.flags = flags;
+    k_decoders_backward<<<ctas, THREADS, max_blob(sp, true) * 4, (cudaStream_t)stream>>>(sp);
+    return check_launch("k_decoders_backward");
+}

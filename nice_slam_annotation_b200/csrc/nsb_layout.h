@@ -1,0 +1,114 @@
+// Packed decoder blob layout, shared by the host table generator (nsb_api.cu) and the
+// device kernels (nsb_decoder.cu).  One blob per decoder:
+//
+//   [ B 3x96 ][ biases ][ FWD fragments ][ BWD fragments ]
+//
+// All GEMM operands are stored in mma.sync.m16n8k8 B-fragment order so a warp reads them
+// with conflict-free 128-bit shared loads: for a GEMM with J k-slabs and NT n-tiles the
+// float4 at ((j*(NT/2) + h)*32 + lane) holds (b0,b1) of n-tile 2h and (b0,b1) of n-tile
+// 2h+1 for lane = 4*g + t, where b0/b1 are the k-slots t and t+4 of slab j, column g of
+// the n-tile.  Which input feature a k-slot means ("slot map") and which output feature
+// an accumulator column means ("column map") is chosen per GEMM so that activations never
+// leave registers between layers (see nsb_decoder.cu).
+#pragma once
+#include <stdint.h>
+
+#ifndef NSB_HD
+#ifdef __CUDACC__
+#define NSB_HD __host__ __device__
+#else
+#define NSB_HD
+#endif
+#endif
+
+namespace nsb {
+
+constexpr int HID = 32;        // hidden width (decoder.py:318)
+constexpr int EMB = 93;        // fourier features (decoder.py:127-130)
+constexpr int EMB_PAD = 96;
+constexpr int E_SLABS = 12;
+constexpr int CDIM = 32;       // feature channels per grid
+
+constexpr int KIND_COARSE = 0, KIND_MIDDLE = 1, KIND_FINE = 2, KIND_COLOR = 3;
+
+template <int KIND>
+struct DecCfg {
+    static constexpr bool EMBED = KIND != KIND_COARSE;
+    static constexpr int CS = KIND == KIND_FINE ? 8 : 4;      // k-slabs of the feature input
+    static constexpr int NOUT = KIND == KIND_COLOR ? 4 : 1;
+    // ---- blob offsets in floats
+    static constexpr int OFF_B = 0;
+    static constexpr int SZ_B = EMBED ? 3 * EMB_PAD : 0;
+    static constexpr int OFF_BIAS = OFF_B + SZ_B;
+    // biases: b[5][32], (bc[5][32] if EMBED), bo[8]
+    static constexpr int OFF_BC = OFF_BIAS + 5 * HID;
+    static constexpr int OFF_BO = OFF_BC + (EMBED ? 5 * HID : 0);
+    static constexpr int OFF_FWD = OFF_BO + 8;
+    // forward GEMMs.  EMBED: L0 (12 slabs) C0 L1 C1 L2 C2 L3 (12+4 slabs) C3 L4 C4 OUT
+    //                 COARSE: L0 (4, gather map) L1 L2 L3 (4 gather + 4 chain) L4 OUT
+    static constexpr int SZ_SLAB = 256;                        // floats per k-slab with 4 n-tiles
+    static constexpr int L0_SLABS = EMBED ? E_SLABS : 4;
+    static constexpr int L3_SLABS = EMBED ? E_SLABS + 4 : 8;
+    static constexpr int SZ_C = EMBED ? CS * SZ_SLAB : 0;
+    static constexpr int OFF_L0 = OFF_FWD;
+    static constexpr int OFF_C0 = OFF_L0 + L0_SLABS * SZ_SLAB;
+    static constexpr int OFF_L1 = OFF_C0 + SZ_C;
+    static constexpr int OFF_C1 = OFF_L1 + 4 * SZ_SLAB;
+    static constexpr int OFF_L2 = OFF_C1 + SZ_C;
+    static constexpr int OFF_C2 = OFF_L2 + 4 * SZ_SLAB;
+    static constexpr int OFF_L3 = OFF_C2 + SZ_C;
+    static constexpr int OFF_C3 = OFF_L3 + L3_SLABS * SZ_SLAB;
+    static constexpr int OFF_L4 = OFF_C3 + SZ_C;
+    static constexpr int OFF_C4 = OFF_L4 + 4 * SZ_SLAB;
+    static constexpr int OFF_OUT = OFF_C4 + SZ_C;              // 4 slabs x 32 lanes x float2
+    static constexpr int OFF_BWD = OFF_OUT + 4 * 64;
+    static constexpr int FWD_END = OFF_BWD;
+    // backward (transposed) GEMMs, K = 32 (4 slabs) except TOUT (1 slab, K = 8 padded).
+    //   TOUT : N = 32                       d(out) -> d(h5)
+    //   TLi  : N = 32                       d(a_i) -> d(h_i)      natural column map
+    //   TCi  : N = 32                       d(h_{i+1}) -> d(c)    gather column map
+    //   TL3X / TL0 : the input-side part of layers 3 / 0:  EMBED d(a) -> d(e), N = 96,
+    //   natural map; COARSE d(a) -> d(c), N = 32, gather map.  TL3 is the h part of layer 3.
+    static constexpr int X_NT = EMBED ? 12 : 4;                // n-tiles of the TL3X / TL0 blocks
+    static constexpr int SZ_TC = EMBED ? 4 * SZ_SLAB : 0;
+    static constexpr int OFF_TOUT = OFF_BWD;                   // 1 slab x 4 n-tiles
+    static constexpr int OFF_TL4 = OFF_TOUT + SZ_SLAB;
+    static constexpr int OFF_TC4 = OFF_TL4 + 4 * SZ_SLAB;
+    static constexpr int OFF_TL3 = OFF_TC4 + SZ_TC;
+    static constexpr int OFF_TL3X = OFF_TL3 + 4 * SZ_SLAB;
+    static constexpr int OFF_TC3 = OFF_TL3X + 4 * X_NT * 64;
+    static constexpr int OFF_TL2 = OFF_TC3 + SZ_TC;
+    static constexpr int OFF_TC2 = OFF_TL2 + 4 * SZ_SLAB;
+    static constexpr int OFF_TL1 = OFF_TC2 + SZ_TC;
+    static constexpr int OFF_TC1 = OFF_TL1 + 4 * SZ_SLAB;
+    static constexpr int OFF_TL0 = OFF_TC1 + SZ_TC;
+    static constexpr int OFF_TC0 = OFF_TL0 + 4 * X_NT * 64;
+    static constexpr int TOTAL = OFF_TC0 + SZ_TC;
+    // ---- canonical parameters
+    static constexpr int N_PARAM = EMBED ? 23 : 12;
+    static constexpr int P_W = 0;                              // pts_linears.i.weight
+    static constexpr int P_B = 5;                              // pts_linears.i.bias
+    static constexpr int P_WC = 10;                            // fc_c.i.weight (EMBED)
+    static constexpr int P_BC = 15;
+    static constexpr int P_WO = EMBED ? 20 : 10;
+    static constexpr int P_BO = EMBED ? 21 : 11;
+    static constexpr int P_EMB = 22;
+    static constexpr int C_IN = KIND == KIND_FINE ? 64 : 32;   // fc_c input width
+    NSB_HD static constexpr int in_dim(int i) {
+        return EMBED ? (i == 0 ? EMB : (i == 3 ? EMB + HID : HID)) : (i == 3 ? 2 * HID : HID);
+    }
+};
+
+// slot maps: feature index of k-slot tau (0..7) of slab j
+NSB_HD inline int slot_natural(int j, int tau) { return 8 * j + tau; }
+NSB_HD inline int slot_chain(int j, int tau) { return 8 * j + 2 * (tau & 3) + (tau >> 2); }
+// gather map: lane t holds channels 8t..8t+7 of its rows; slab j (mod 4) uses 8t+2j, 8t+2j+1;
+// slabs 4..7 (fine decoder) are the concatenated middle-grid feature (channels 32..63)
+NSB_HD inline int slot_gather(int j, int tau) {
+    return 32 * (j >> 2) + 8 * (tau & 3) + 2 * (j & 3) + (tau >> 2);
+}
+// column maps: output feature of accumulator column gamma (0..7) of n-tile n
+NSB_HD inline int col_natural(int n, int gamma) { return 8 * n + gamma; }
+NSB_HD inline int col_gather(int n, int gamma) { return 8 * (gamma >> 1) + 2 * n + (gamma & 1); }
+
+}  // namespace nsb

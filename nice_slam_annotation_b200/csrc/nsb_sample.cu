@@ -1,0 +1,336 @@
+// K1: pixel -> ray, bound pre-filter, batch depth max, sample depths along the rays and the
+// iMAP importance resampling.  Replaces get_samples / get_rays (src/common.py:74-134,
+// 259-277), the sampling half of Renderer.render_batch_ray (src/utils/Renderer.py:116-224)
+// and sample_pdf (src/common.py:19-63).  Depths are fp64 like the reference (its scene bound
+// is an fp64 tensor, NICE_SLAM.py:196, which promotes everything downstream).
+#include "nsb_common.cuh"
+
+namespace nsb {
+
+constexpr int MAX_LIST = 128;   // per-ray limit of N_samples, N_surface, N_importance each
+
+struct CamDev {
+    float fx, fy, cx, cy;
+};
+
+// dirs = [(i-cx)/fx, -(j-cy)/fy, -1]; rays_d = sum(dirs * R, -1) evaluated without fusing, in
+// the order torch evaluates common.py:82-87
+__device__ __forceinline__ void pixel_ray(float i, float j, const CamDev& cam,
+                                          const float* __restrict__ c2w, float (&d)[3]) {
+    const float x = __fdiv_rn(__fsub_rn(i, cam.cx), cam.fx);
+    const float y = -__fdiv_rn(__fsub_rn(j, cam.cy), cam.fy);
+    const float z = -1.f;
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+        d[a] = __fadd_rn(__fadd_rn(__fmul_rn(x, c2w[4 * a]), __fmul_rn(y, c2w[4 * a + 1])),
+                         __fmul_rn(z, c2w[4 * a + 2]));
+}
+
+// NaN-propagating max/min like torch.max / torch.min
+__device__ __forceinline__ double tmax(double a, double b) { return (a > b || a != a) ? a : b; }
+__device__ __forceinline__ double tmin(double a, double b) { return (a < b || a != a) ? a : b; }
+
+// slab exit of the scene box: min_axis max(lo,hi)((bound - o)/d), fp64 (Renderer.py:139-150)
+__device__ __forceinline__ double box_exit(const float (&o)[3], const float (&d)[3], const BoundDev& b) {
+    double far = 0.0;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        double tl = __ddiv_rn(__dsub_rn(b.lo[a], (double)o[a]), (double)d[a]);
+        double th = __ddiv_rn(__dsub_rn(b.hi[a], (double)o[a]), (double)d[a]);
+        double m = tmax(tl, th);
+        far = a == 0 ? m : tmin(far, m);
+    }
+    return far;
+}
+
+__global__ void k_sample_rays(const int64_t* __restrict__ indices, long long n, int H0, int W0,
+                              int hc, int wc, int W_img, CamDev cam, const float* __restrict__ c2w,
+                              const float* __restrict__ depth_img, const void* __restrict__ color_img,
+                              int color_is_f64, BoundDev bound, int have_bound,
+                              float* __restrict__ rays_o, float* __restrict__ rays_d,
+                              float* __restrict__ gt_depth, float* __restrict__ gt_color,
+                              uint8_t* __restrict__ keep) {
+    long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    long long idx = indices[r];
+    const long long total = (long long)hc * wc;
+    idx = idx < 0 ? 0 : (idx >= total ? total - 1 : idx);
+    const int pi = W0 + (int)(idx % wc), pj = H0 + (int)(idx / wc);
+    float d[3], o[3];
+    pixel_ray((float)pi, (float)pj, cam, c2w, d);
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        o[a] = c2w[4 * a + 3];
+        rays_o[3 * r + a] = o[a];
+        rays_d[3 * r + a] = d[a];
+    }
+    const long long pix = (long long)pj * W_img + pi;
+    const float gd = depth_img[pix];
+    if (gt_depth) gt_depth[r] = gd;
+    if (gt_color) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+            gt_color[3 * r + c] = color_is_f64 ? (float)reinterpret_cast<const double*>(color_img)[3 * pix + c]
+                                               : reinterpret_cast<const float*>(color_img)[3 * pix + c];
+    }
+    if (keep) keep[r] = have_bound ? (box_exit(o, d, bound) >= (double)gd ? 1 : 0) : 1;
+}
+
+__global__ void k_all_rays(int H, int W, CamDev cam, const float* __restrict__ c2w,
+                           float* __restrict__ rays_o, float* __restrict__ rays_d) {
+    long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (r >= (long long)H * W) return;
+    float d[3];
+    pixel_ray((float)(r % W), (float)(r / W), cam, c2w, d);
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        rays_o[3 * r + a] = c2w[4 * a + 3];
+        rays_d[3 * r + a] = d[a];
+    }
+}
+
+__global__ void k_depth_max(const float* __restrict__ gt, long long n, float* __restrict__ out) {
+    __shared__ float part[32];
+    float m = -INFINITY;
+    bool nan = false;
+    for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+        float v = gt[i];
+        nan |= (v != v);
+        m = fmaxf(m, v);
+    }
+    if (nan) m = NAN;
+    for (int s = 16; s > 0; s >>= 1) {
+        float o = __shfl_xor_sync(FULL, m, s);
+        m = (o > m || o != o) ? o : m;
+    }
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        m = threadIdx.x < (blockDim.x >> 5) ? part[threadIdx.x] : -INFINITY;
+        for (int s = 16; s > 0; s >>= 1) {
+            float o = __shfl_xor_sync(FULL, m, s);
+            m = (o > m || o != o) ? o : m;
+        }
+        if (threadIdx.x == 0) out[0] = m;
+    }
+}
+
+__device__ __forceinline__ bool is_sorted(const double* v, int n) {
+    bool ok = true;
+    for (int i = 1; i < n; ++i) ok &= (v[i - 1] <= v[i]);
+    return ok;
+}
+
+__device__ __forceinline__ void insertion_sort(double* v, int n) {
+    for (int i = 1; i < n; ++i) {
+        double x = v[i];
+        int j = i - 1;
+        // NaNs sort last, as torch.sort does
+        while (j >= 0 && (v[j] > x || (v[j] != v[j] && x == x))) { v[j + 1] = v[j]; --j; }
+        v[j + 1] = x;
+    }
+}
+
+// ascending merge of two ascending lists (what torch.sort(torch.cat(...)) returns for them)
+__device__ __forceinline__ void merge_sorted(const double* a, int na, const double* b, int nb,
+                                             double* __restrict__ out) {
+    int i = 0, j = 0, k = 0;
+    while (i < na && j < nb) out[k++] = (b[j] < a[i]) ? b[j++] : a[i++];
+    while (i < na) out[k++] = a[i++];
+    while (j < nb) out[k++] = b[j++];
+}
+
+__global__ void k_sample_z(PointsDev q, const float* __restrict__ gt_depth, BoundDev bound,
+                           int Ns, int Nf, int lindisp, const float* __restrict__ t_uniform,
+                           const double* __restrict__ t_surface, const float* __restrict__ u,
+                           const float* __restrict__ depth_max, double* __restrict__ z_out) {
+    long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (r >= q.N) return;
+    float o[3], d[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { o[a] = q.ro[r * q.so + a]; d[a] = q.rd[r * q.sd + a]; }
+    const double far_bb = __dadd_rn(box_exit(o, d, bound), 0.01);
+    double zu[MAX_LIST], zs[MAX_LIST];
+    float near;
+    double far;
+    float g = 0.f;
+    if (gt_depth) {
+        g = gt_depth[r];
+        near = __fmul_rn(g, 0.01f);
+        const double cap = (double)__fmul_rn(depth_max[0], 1.2f);     // max(gt_depth * 1.2)
+        far = tmin(tmax(far_bb, 0.0), cap);                            // torch.clamp(far_bb, 0, cap)
+        if (far_bb != far_bb) far = far_bb;
+    } else {
+        near = 0.01f;
+        far = far_bb;
+    }
+    for (int k = 0; k < Ns; ++k) {
+        const float t = t_uniform[k];
+        const float omt = __fsub_rn(1.f, t);
+        if (!lindisp) {
+            zu[k] = __dadd_rn((double)__fmul_rn(near, omt), __dmul_rn(far, (double)t));
+        } else {
+            const float inv_near = gt_depth ? __fdiv_rn(1.f, near) : 100.f;
+            const double s = __dadd_rn((double)__fmul_rn(inv_near, omt),
+                                       __dmul_rn(__ddiv_rn(1.0, far), (double)t));
+            zu[k] = __ddiv_rn(1.0, s);
+        }
+    }
+    if (u) {   // stratified jitter (Renderer.py:212-219)
+        double prev = zu[0], lower = zu[0];
+        for (int k = 0; k < Ns; ++k) {
+            const double cur = zu[k];
+            const double upper = (k + 1 < Ns) ? __dmul_rn(0.5, __dadd_rn(zu[k + 1], cur)) : cur;
+            if (k > 0) lower = __dmul_rn(0.5, __dadd_rn(cur, prev));
+            prev = cur;
+            zu[k] = __dadd_rn(lower, __dmul_rn(__dsub_rn(upper, lower), (double)u[r * Ns + k]));
+        }
+    }
+    double* out = z_out + r * (long long)(Ns + Nf);
+    if (Nf > 0 && gt_depth) {
+        if (g > 0.f) {       // 0.95 d .. 1.05 d (Renderer.py:177-185)
+            const double a = (double)__fmul_rn(0.95f, g), b = (double)__fmul_rn(1.05f, g);
+            for (int k = 0; k < Nf; ++k) {
+                const double ts = t_surface[k];
+                zs[k] = __dadd_rn(__dmul_rn(a, __dsub_rn(1.0, ts)), __dmul_rn(b, ts));
+            }
+        } else {             // no sensor depth: 0.001 .. max depth of the batch (Renderer.py:191-200)
+            const double fs = (double)depth_max[0];
+            for (int k = 0; k < Nf; ++k) {
+                const double ts = t_surface[k];
+                zs[k] = __dadd_rn(__dmul_rn(0.001, __dsub_rn(1.0, ts)), __dmul_rn(fs, ts));
+            }
+        }
+        if (is_sorted(zu, Ns) && is_sorted(zs, Nf)) {
+            merge_sorted(zu, Ns, zs, Nf, out);
+        } else {
+            for (int k = 0; k < Ns; ++k) out[k] = zu[k];
+            for (int k = 0; k < Nf; ++k) out[Ns + k] = zs[k];
+            insertion_sort(out, Ns + Nf);
+        }
+    } else {
+        for (int k = 0; k < Ns; ++k) out[k] = zu[k];
+    }
+}
+
+// sample_pdf (common.py:19-63) on bins = mid(z), weights = w[1:-1]; then the sort-merge of
+// Renderer.py:249
+__global__ void k_importance_z(const double* __restrict__ z, const float* __restrict__ w,
+                               long long N, int S, int Ni, const float* __restrict__ u,
+                               long long u_stride, double* __restrict__ z_samples,
+                               double* __restrict__ z_out) {
+    long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (r >= N) return;
+    const double* zr = z + r * (long long)S;
+    const float* wr = w + r * (long long)S;
+    const int M = S - 1;          // bins
+    const int K = S - 2;          // weights
+    float cdf[MAX_LIST];
+    double zs[MAX_LIST];
+    float sum = 0.f;
+    for (int k = 0; k < K; ++k) sum = __fadd_rn(sum, __fadd_rn(wr[k + 1], 1e-5f));
+    cdf[0] = 0.f;
+    float run = 0.f;
+    for (int k = 0; k < K; ++k) {
+        run = __fadd_rn(run, __fdiv_rn(__fadd_rn(wr[k + 1], 1e-5f), sum));
+        cdf[k + 1] = run;
+    }
+    const int L = K + 1;          // cdf length == number of bins
+    for (int k = 0; k < Ni; ++k) {
+        const float uu = u[r * u_stride + k];
+        int lo = 0, hi = L;       // searchsorted(right=True): first index with cdf > u
+        while (lo < hi) {
+            int mid = (lo + hi) >> 1;
+            if (cdf[mid] > uu) hi = mid; else lo = mid + 1;
+        }
+        const int below = lo - 1 > 0 ? lo - 1 : 0;
+        const int above = lo < L - 1 ? lo : L - 1;
+        float denom = __fsub_rn(cdf[above], cdf[below]);
+        if (denom < 1e-5f) denom = 1.f;
+        const float t = __fdiv_rn(__fsub_rn(uu, cdf[below]), denom);
+        const double bb = __dmul_rn(0.5, __dadd_rn(zr[below + 1], zr[below]));
+        const double ba = __dmul_rn(0.5, __dadd_rn(zr[above + 1], zr[above]));
+        zs[k] = __dadd_rn(bb, __dmul_rn((double)t, __dsub_rn(ba, bb)));
+        if (z_samples) z_samples[r * (long long)Ni + k] = zs[k];
+    }
+    (void)M;
+    if (!is_sorted(zs, Ni)) insertion_sort(zs, Ni);
+    double* out = z_out + r * (long long)(S + Ni);
+    if (is_sorted(zr, S)) {
+        merge_sorted(zr, S, zs, Ni, out);
+    } else {
+        for (int k = 0; k < S; ++k) out[k] = zr[k];
+        for (int k = 0; k < Ni; ++k) out[S + k] = zs[k];
+        insertion_sort(out, S + Ni);
+    }
+}
+
+}  // namespace nsb
+
+using namespace nsb;
+
+static inline unsigned blocks_for(long long n, int bs) { return (unsigned)((n + bs - 1) / bs); }
+
+extern "C" int nsb_sample_rays(const int64_t* indices, int64_t n, int H0, int H1, int W0, int W1,
+                               int W_img, float fx, float fy, float cx, float cy, const float* c2w,
+                               const float* depth_img, const void* color_img, int color_is_f64,
+                               const double* bound6_host, float* rays_o, float* rays_d,
+                               float* gt_depth, float* gt_color, uint8_t* keep, void* stream) {
+    if (!indices || !c2w || !depth_img || !rays_o || !rays_d) return set_error(NSB_EINVAL, "null argument");
+    if (gt_color && !color_img) return set_error(NSB_EINVAL, "gt_color requested without an image");
+    if (H1 <= H0 || W1 <= W0) return set_error(NSB_EINVAL, "empty crop");
+    if (n <= 0) return 0;
+    BoundDev b{};
+    if (bound6_host) b = to_bound(bound6_host);
+    CamDev cam{fx, fy, cx, cy};
+    k_sample_rays<<<blocks_for(n, 128), 128, 0, (cudaStream_t)stream>>>(
+        indices, n, H0, W0, H1 - H0, W1 - W0, W_img, cam, c2w, depth_img, color_img, color_is_f64, b,
+        bound6_host != nullptr, rays_o, rays_d, gt_depth, gt_color, keep);
+    return check_launch("k_sample_rays");
+}
+
+extern "C" int nsb_all_rays(int H, int W, float fx, float fy, float cx, float cy, const float* c2w,
+                            float* rays_o, float* rays_d, void* stream) {
+    if (!c2w || !rays_o || !rays_d) return set_error(NSB_EINVAL, "null argument");
+    if (H <= 0 || W <= 0) return 0;
+    CamDev cam{fx, fy, cx, cy};
+    k_all_rays<<<blocks_for((long long)H * W, 256), 256, 0, (cudaStream_t)stream>>>(H, W, cam, c2w, rays_o, rays_d);
+    return check_launch("k_all_rays");
+}
+
+extern "C" int nsb_depth_max(const float* gt_depth, int64_t N, float* out, void* stream) {
+    if (!gt_depth || !out) return set_error(NSB_EINVAL, "null argument");
+    k_depth_max<<<1, 1024, 0, (cudaStream_t)stream>>>(gt_depth, N, out);
+    return check_launch("k_depth_max");
+}
+
+extern "C" int nsb_sample_z(const NsbPoints* rays, const float* gt_depth, const double* bound6_host,
+                            int N_samples, int N_surface, int lindisp, const float* t_uniform,
+                            const double* t_surface, const float* u, const float* depth_max,
+                            double* z_out, void* stream) {
+    if (!rays || !rays->rays_o || !rays->rays_d || !bound6_host || !t_uniform || !z_out)
+        return set_error(NSB_EINVAL, "null argument");
+    if (N_samples < 1 || N_samples > MAX_LIST || N_surface < 0 || N_surface > MAX_LIST)
+        return set_error(NSB_EINVAL, "N_samples / N_surface out of range (1..%d)", MAX_LIST);
+    if (!gt_depth) N_surface = 0;
+    if (gt_depth && !depth_max) return set_error(NSB_EINVAL, "depth_max is required with gt_depth");
+    if (N_surface > 0 && !t_surface) return set_error(NSB_EINVAL, "t_surface is NULL");
+    if (rays->N <= 0) return 0;
+    PointsDev q = to_dev(*rays);
+    k_sample_z<<<blocks_for(q.N, 64), 64, 0, (cudaStream_t)stream>>>(
+        q, gt_depth, to_bound(bound6_host), N_samples, N_surface, lindisp, t_uniform, t_surface, u,
+        depth_max, z_out);
+    return check_launch("k_sample_z");
+}
+
+extern "C" int nsb_importance_z(const double* z, const float* weights, int64_t N, int S, int N_imp,
+                                const float* u, int64_t u_row_stride, double* z_samples,
+                                double* z_out, void* stream) {
+    if (!z || !weights || !u || !z_out) return set_error(NSB_EINVAL, "null argument");
+    if (S < 3 || S > MAX_LIST || N_imp < 1 || N_imp > MAX_LIST)
+        return set_error(NSB_EINVAL, "S / N_importance out of range");
+    if (N <= 0) return 0;
+    k_importance_z<<<blocks_for(N, 64), 64, 0, (cudaStream_t)stream>>>(z, weights, N, S, N_imp, u,
+                                                                      u_row_stride, z_samples, z_out);
+    return check_launch("k_importance_z");
+}
