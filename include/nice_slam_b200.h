@@ -105,6 +105,9 @@ int64_t nsb_param_numel(int kind, int index);
 int64_t nsb_flat_numel(int kind);   /* sum of nsb_param_numel */
 int64_t nsb_packed_numel(int kind);
 int nsb_pack_table_host(int kind, int32_t* table_host);
+/* test hook: 32 ints describing the blob layout (offsets of B, biases and every packed GEMM
+ * block, in the order listed in csrc/nsb_api.cu:layout_offsets) */
+int nsb_layout_offsets(int kind, int32_t* out32_host);
 int nsb_pack_weights(int kind, const float* const* param_ptrs, const int32_t* table,
                      float* packed, void* stream);
 

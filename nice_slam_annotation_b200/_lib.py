@@ -43,6 +43,7 @@ _SIGS = {
     "nsb_flat_numel": (C.c_int64, [C.c_int]),
     "nsb_packed_numel": (C.c_int64, [C.c_int]),
     "nsb_pack_table_host": (C.c_int, [C.c_int, c_ptr]),
+    "nsb_layout_offsets": (C.c_int, [C.c_int, c_ptr]),
     "nsb_pack_weights": (C.c_int, [C.c_int, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_sample_rays": (C.c_int, [c_ptr, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                   C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, c_ptr, c_ptr,

@@ -198,6 +198,24 @@ extern "C" int nsb_pack_table_host(int kind, int32_t* table_host) {
     return 0;
 }
 
+template <int KIND>
+static void layout_offsets(int32_t* o) {
+    using C = DecCfg<KIND>;
+    const int v[] = {C::OFF_B, C::OFF_BIAS, C::OFF_BC, C::OFF_BO,
+                     C::OFF_L0, C::OFF_L1, C::OFF_L2, C::OFF_L3, C::OFF_L4,
+                     C::OFF_C0, C::OFF_C1, C::OFF_C2, C::OFF_C3, C::OFF_C4, C::OFF_OUT, C::OFF_TOUT,
+                     C::OFF_TL0, C::OFF_TL1, C::OFF_TL2, C::OFF_TL3, C::OFF_TL4, C::OFF_TL3X,
+                     C::OFF_TC0, C::OFF_TC1, C::OFF_TC2, C::OFF_TC3, C::OFF_TC4, C::FWD_END, C::TOTAL,
+                     C::CS, C::NOUT, C::EMBED ? 1 : 0};
+    for (int i = 0; i < 32; ++i) o[i] = v[i];
+}
+
+extern "C" int nsb_layout_offsets(int kind, int32_t* out32_host) {
+    if (!out32_host) return set_error(NSB_EINVAL, "null argument");
+    KIND_SWITCH(kind, layout_offsets<K>(out32_host));
+    return 0;
+}
+
 extern "C" int nsb_pack_weights(int kind, const float* const* param_ptrs, const int32_t* table,
                                 float* packed, void* stream) {
     if (!param_ptrs || !table || !packed) return set_error(NSB_EINVAL, "null argument");
