@@ -8,7 +8,7 @@
 
 namespace nsb {
 
-constexpr int WARPS = 8;                 // warps per CTA of the decoder kernels
+constexpr int WARPS = 12;                // warps per CTA of the decoder kernels
 constexpr int THREADS = WARPS * 32;
 constexpr unsigned FULL = 0xffffffffu;
 

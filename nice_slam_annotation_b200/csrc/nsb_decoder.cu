@@ -165,35 +165,80 @@ __device__ __forceinline__ void gather8(const float* __restrict__ grid, const Tr
     }
 }
 
-// features of the thread's two points -> 4 A-fragment slabs ("gather" slot map)
+// features of the thread's two points -> 4 A-fragment slabs ("gather" slot map).  The row
+// loop is rolled (one copy of the 16-load body in the instruction stream).
 __device__ __forceinline__ void gather_level(const GridDev& G, const Rows& R, int t,
                                              float (*c)[4]) {
-    float f0[8], f1[8];
-    Tri t0 = tri_setup(R.u[0], G), t1 = tri_setup(R.u[1], G);
-    gather8(G.data, t0, t, f0);
-    gather8(G.data, t1, t, f1);
+#pragma unroll 1
+    for (int r = 0; r < 2; ++r) {
+        float f[8];
+        const float u[3] = {r ? R.u[1][0] : R.u[0][0], r ? R.u[1][1] : R.u[0][1], r ? R.u[1][2] : R.u[0][2]};
+        Tri tr = tri_setup(u, G);
+        gather8(G.data, tr, t, f);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        c[j][0] = f0[2 * j];
-        c[j][1] = f1[2 * j];
-        c[j][2] = f0[2 * j + 1];
-        c[j][3] = f1[2 * j + 1];
+        for (int j = 0; j < 4; ++j) {
+            if (r == 0) { c[j][0] = f[2 * j]; c[j][2] = f[2 * j + 1]; }
+            else { c[j][1] = f[2 * j]; c[j][3] = f[2 * j + 1]; }
+        }
     }
 }
 
-// e = sin(p @ B) (decoder.py:26-30) as 12 A-fragment slabs, "natural" slot map
+// ---- Fourier embedding -------------------------------------------------------------------------
+// e = sin(p @ B) (decoder.py:26-30).  The 16 x 96 tile of a warp lives in a per-warp shared
+// buffer, each lane writing exactly the A-fragment elements it later reads (slot map
+// "natural": rows g / g+8, features 8j+t / 8j+t+4), XOR-swizzled so that both the stores and
+// the fragment loads are bank-conflict free.  Keeping e out of registers lets the 12-slab
+// GEMMs of layers 0 and 3 be ROLLED loops: the kernel body stays small enough for the
+// instruction cache (the fully unrolled first version stalled 3-5 cycles per issue on
+// instruction fetch) and 48 registers per thread are freed for a third warp per scheduler.
+constexpr int E_BUF = 16 * EMB_PAD;      // floats per warp
+
+__device__ __forceinline__ int esw(int row, int col) { return row * EMB_PAD + (col ^ ((row & 7) << 2)); }
+
 __device__ __forceinline__ float phase(const float (&p)[3], const float* Bs, int f) {
     return fmaf(p[2], Bs[2 * EMB_PAD + f], fmaf(p[1], Bs[EMB_PAD + f], p[0] * Bs[f]));
 }
 
-__device__ __forceinline__ void embed(const Rows& R, const float* Bs, int t, float (&e)[E_SLABS][4]) {
-#pragma unroll
+__device__ __forceinline__ void embed_to_smem(const Rows& R, const float* Bs, int lane, float* es) {
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll 1
     for (int j = 0; j < E_SLABS; ++j) {
         const int f0 = 8 * j + t, f1 = f0 + 4;
-        e[j][0] = sinf(phase(R.p[0], Bs, f0));
-        e[j][1] = sinf(phase(R.p[1], Bs, f0));
-        e[j][2] = sinf(phase(R.p[0], Bs, f1));
-        e[j][3] = sinf(phase(R.p[1], Bs, f1));
+        es[esw(g, f0)] = sinf(phase(R.p[0], Bs, f0));
+        es[esw(g + 8, f0)] = sinf(phase(R.p[1], Bs, f0));
+        es[esw(g, f1)] = sinf(phase(R.p[0], Bs, f1));
+        es[esw(g + 8, f1)] = sinf(phase(R.p[1], Bs, f1));
+    }
+}
+
+// acc[4][4] += e(16 x 96) * B, A fragments streamed from the warp's e buffer (rolled)
+__device__ __forceinline__ void egemm(float (&acc)[4][4], const float* es,
+                                      const float* __restrict__ Bs, int lane) {
+    const int g = lane >> 2, t = lane & 3;
+    const float4* B4 = reinterpret_cast<const float4*>(Bs);
+#pragma unroll 2
+    for (int j = 0; j < E_SLABS; ++j) {
+        const int f0 = 8 * j + t, f1 = f0 + 4;
+        uint32_t ah[4], al[4];
+        split_tf32(es[esw(g, f0)], ah[0], al[0]);
+        split_tf32(es[esw(g + 8, f0)], ah[1], al[1]);
+        split_tf32(es[esw(g, f1)], ah[2], al[2]);
+        split_tf32(es[esw(g + 8, f1)], ah[3], al[3]);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            float4 b = B4[(j * 2 + h) * 32 + lane];
+            uint32_t bh[4], bl[4];
+            split_tf32(b.x, bh[0], bl[0]);
+            split_tf32(b.y, bh[1], bl[1]);
+            split_tf32(b.z, bh[2], bl[2]);
+            split_tf32(b.w, bh[3], bl[3]);
+            mma_tf32(acc[2 * h], al, bh[0], bh[1]);
+            mma_tf32(acc[2 * h], ah, bl[0], bl[1]);
+            mma_tf32(acc[2 * h], ah, bh[0], bh[1]);
+            mma_tf32(acc[2 * h + 1], al, bh[2], bh[3]);
+            mma_tf32(acc[2 * h + 1], ah, bl[2], bl[3]);
+            mma_tf32(acc[2 * h + 1], ah, bh[2], bh[3]);
+        }
     }
 }
 
@@ -212,18 +257,18 @@ __device__ __forceinline__ void bias_add(float (&acc)[4][4], const float* b, int
         acc[n][0] += v.x; acc[n][1] += v.y; acc[n][2] += v.x; acc[n][3] += v.y;
     }
 }
-template <bool MASK>
-__device__ __forceinline__ void relu_(float (&acc)[4][4], uint32_t& m) {
+// ReLU in place; returns the 16 sign bits (bit n*4+q)
+__device__ __forceinline__ uint32_t relu_(float (&acc)[4][4]) {
     uint32_t bits = 0;
 #pragma unroll
     for (int n = 0; n < 4; ++n)
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             bool pos = acc[n][q] > 0.f;
-            if (MASK) bits |= (pos ? 1u : 0u) << (n * 4 + q);
+            bits |= (pos ? 1u : 0u) << (n * 4 + q);
             acc[n][q] = pos ? acc[n][q] : 0.f;
         }
-    if (MASK) m = bits;
+    return bits;
 }
 __device__ __forceinline__ void mask_(float (&acc)[4][4], uint32_t m) {
 #pragma unroll
@@ -239,76 +284,67 @@ __device__ __forceinline__ void zero_(float (&acc)[4][4]) {
         for (int q = 0; q < 4; ++q) acc[n][q] = 0.f;
 }
 
-// MLP.forward (EMBED) / MLP_no_xyz.forward (COARSE) for one 16-point tile.  e: embedding
-// slabs (unused for COARSE), c: feature slabs.  out: C fragment of the padded 8-column output
-// tile (columns 2t, 2t+1 for rows g, g+8).  mask[i]: sign bits of the i-th ReLU input.
-template <int KIND, bool MASK>
-__device__ __forceinline__ void mlp_forward(const float* sm, int lane,
-                                            const float (&e)[E_SLABS][4],
-                                            const float (&c)[DecCfg<KIND>::CS][4], float (&out)[4],
-                                            uint32_t (&mask)[5]) {
+// ReLU sign bits of the five layers, 16 bits each, in three registers
+struct Masks {
+    uint32_t m01, m23, m4;
+    __device__ __forceinline__ void set(int i, uint32_t bits) {
+        if (i == 0) m01 = bits;
+        else if (i == 1) m01 |= bits << 16;
+        else if (i == 2) m23 = bits;
+        else if (i == 3) m23 |= bits << 16;
+        else m4 = bits;
+    }
+    __device__ __forceinline__ uint32_t get(int i) const {
+        const uint32_t w = i < 2 ? m01 : (i < 4 ? m23 : m4);
+        return (i & 1) ? (w >> 16) : (w & 0xffffu);
+    }
+};
+
+// blob offsets of layer i as functions (runtime i: the layer loops are rolled)
+template <int KIND>
+struct Off {
     using C = DecCfg<KIND>;
+    static constexpr int XS = C::EMBED ? E_SLABS : 4;      // slabs of the input-side part of layers 0 / 3
+    __device__ __forceinline__ static int X(int i) { return i == 0 ? C::OFF_L0 : C::OFF_L3; }
+    __device__ __forceinline__ static int H(int i) {
+        return i == 1 ? C::OFF_L1 : (i == 2 ? C::OFF_L2 : (i == 3 ? C::OFF_L3 + XS * C::SZ_SLAB : C::OFF_L4));
+    }
+    __device__ __forceinline__ static int Cc(int i) {
+        return i == 0 ? C::OFF_C0 : (i == 1 ? C::OFF_C1 : (i == 2 ? C::OFF_C2 : (i == 3 ? C::OFF_C3 : C::OFF_C4)));
+    }
+    __device__ __forceinline__ static int TL(int i) {
+        return i == 1 ? C::OFF_TL1 : (i == 2 ? C::OFF_TL2 : (i == 3 ? C::OFF_TL3 : C::OFF_TL4));
+    }
+    __device__ __forceinline__ static int TX(int i) { return i == 0 ? C::OFF_TL0 : C::OFF_TL3X; }
+    __device__ __forceinline__ static int TC(int i) {
+        return i == 0 ? C::OFF_TC0 : (i == 1 ? C::OFF_TC1 : (i == 2 ? C::OFF_TC2 : (i == 3 ? C::OFF_TC3 : C::OFF_TC4)));
+    }
+};
+
+// MLP.forward (EMBED) / MLP_no_xyz.forward (COARSE) for one 16-point tile.  es: the warp's
+// embedding buffer (unused for COARSE), c: feature slabs.  out: C fragment of the padded
+// 8-column output tile (columns 2t, 2t+1 for rows g, g+8).
+template <int KIND>
+__device__ __forceinline__ void mlp_forward(const float* sm, const float* es, int lane,
+                                            const float (&c)[DecCfg<KIND>::CS][4], float (&out)[4],
+                                            Masks& mk) {
+    using C = DecCfg<KIND>;
+    using O = Off<KIND>;
     const int t = lane & 3;
     float acc[4][4], h[4][4];
-    const float* b = sm + C::OFF_BIAS;
-    const float* bc = sm + C::OFF_BC;
-    if constexpr (C::EMBED) {
-        bias_init(acc, b, t);
-        gemm3<E_SLABS, 4>(acc, e, sm + C::OFF_L0, lane);
-        relu_<MASK>(acc, mask[0]);
-        bias_add(acc, bc, t);
-        gemm3<C::CS, 4>(acc, c, sm + C::OFF_C0, lane);
-        chain<4>(h, acc);
-
-        bias_init(acc, b + 32, t);
-        gemm3<4, 4>(acc, h, sm + C::OFF_L1, lane);
-        relu_<MASK>(acc, mask[1]);
-        bias_add(acc, bc + 32, t);
-        gemm3<C::CS, 4>(acc, c, sm + C::OFF_C1, lane);
-        chain<4>(h, acc);
-
-        bias_init(acc, b + 64, t);
-        gemm3<4, 4>(acc, h, sm + C::OFF_L2, lane);
-        relu_<MASK>(acc, mask[2]);
-        bias_add(acc, bc + 64, t);
-        gemm3<C::CS, 4>(acc, c, sm + C::OFF_C2, lane);
-        chain<4>(h, acc);
-
-        bias_init(acc, b + 96, t);                                   // skip: [e, h] (decoder.py:214-215)
-        gemm3<E_SLABS, 4>(acc, e, sm + C::OFF_L3, lane);
-        gemm3<4, 4>(acc, h, sm + C::OFF_L3 + E_SLABS * C::SZ_SLAB, lane);
-        relu_<MASK>(acc, mask[3]);
-        bias_add(acc, bc + 96, t);
-        gemm3<C::CS, 4>(acc, c, sm + C::OFF_C3, lane);
-        chain<4>(h, acc);
-
-        bias_init(acc, b + 128, t);
-        gemm3<4, 4>(acc, h, sm + C::OFF_L4, lane);
-        relu_<MASK>(acc, mask[4]);
-        bias_add(acc, bc + 128, t);
-        gemm3<C::CS, 4>(acc, c, sm + C::OFF_C4, lane);
-        chain<4>(h, acc);
-    } else {
-        bias_init(acc, b, t);
-        gemm3<4, 4>(acc, c, sm + C::OFF_L0, lane);
-        relu_<MASK>(acc, mask[0]);
-        chain<4>(h, acc);
-        bias_init(acc, b + 32, t);
-        gemm3<4, 4>(acc, h, sm + C::OFF_L1, lane);
-        relu_<MASK>(acc, mask[1]);
-        chain<4>(h, acc);
-        bias_init(acc, b + 64, t);
-        gemm3<4, 4>(acc, h, sm + C::OFF_L2, lane);
-        relu_<MASK>(acc, mask[2]);
-        chain<4>(h, acc);
-        bias_init(acc, b + 96, t);                                   // skip: [c, h] (decoder.py:293-294)
-        gemm3<4, 4>(acc, c, sm + C::OFF_L3, lane);
-        gemm3<4, 4>(acc, h, sm + C::OFF_L3 + 4 * C::SZ_SLAB, lane);
-        relu_<MASK>(acc, mask[3]);
-        chain<4>(h, acc);
-        bias_init(acc, b + 128, t);
-        gemm3<4, 4>(acc, h, sm + C::OFF_L4, lane);
-        relu_<MASK>(acc, mask[4]);
+#pragma unroll 1
+    for (int i = 0; i < 5; ++i) {
+        bias_init(acc, sm + C::OFF_BIAS + 32 * i, t);
+        if (i == 0 || i == 3) {                     // input-side part; layer 3 is the skip [x, h]
+            if constexpr (C::EMBED) egemm(acc, es, sm + O::X(i), lane);
+            else gemm3<4, 4>(acc, c, sm + O::X(i), lane);
+        }
+        if (i > 0) gemm3<4, 4>(acc, h, sm + O::H(i), lane);
+        mk.set(i, relu_(acc));
+        if constexpr (C::EMBED) {
+            bias_add(acc, sm + C::OFF_BC + 32 * i, t);
+            gemm3<C::CS, 4>(acc, c, sm + O::Cc(i), lane);
+        }
         chain<4>(h, acc);
     }
     float2 bo = *reinterpret_cast<const float2*>(sm + C::OFF_BO + 2 * t);
@@ -323,35 +359,34 @@ __device__ __forceinline__ void stage_weights(float* sm, const float* __restrict
     __syncthreads();
 }
 
-// inputs of a tile: rows, embedding, features
+// inputs of a tile: rows, embedding (to shared), features (to registers)
 template <int KIND>
 __device__ __forceinline__ void tile_inputs(const PointsDev& q, const DecTask& T, const float* sm,
-                                            long long tile, int lane, Rows& R,
-                                            float (&e)[E_SLABS][4],
+                                            float* es, long long tile, int lane, Rows& R,
                                             float (&c)[DecCfg<KIND>::CS][4]) {
     using C = DecCfg<KIND>;
     const int t = lane & 3;
     load_rows<KIND>(q, T, tile, lane, R);
     gather_level(T.own, R, t, c);
     if constexpr (KIND == KIND_FINE) gather_level(T.aux, R, t, c + 4);
-    if constexpr (C::EMBED) embed(R, sm + C::OFF_B, t, e);
+    if constexpr (C::EMBED) embed_to_smem(R, sm + C::OFF_B, lane, es);
 }
 
 template <int KIND>
 __device__ void decoder_forward_cta(const StageParams& P, const DecTask& T, float* sm) {
     using C = DecCfg<KIND>;
     stage_weights(sm, T.packed, C::FWD_END);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, t = lane & 3;
+    float* es = sm + C::FWD_END + warp * E_BUF;
     const long long ntiles = (P.pts.P + 15) / 16;
     for (long long tile = (long long)(blockIdx.x - T.cta_begin) * WARPS + warp; tile < ntiles;
          tile += (long long)T.cta_count * WARPS) {
         Rows R;
-        float e[E_SLABS][4];
         float c[C::CS][4];
-        tile_inputs<KIND>(P.pts, T, sm, tile, lane, R, e, c);
+        tile_inputs<KIND>(P.pts, T, sm, es, tile, lane, R, c);
         float out[4];
-        uint32_t mask[5];
-        mlp_forward<KIND, false>(sm, lane, e, c, out, mask);
+        Masks mk;
+        mlp_forward<KIND>(sm, es, lane, c, out, mk);
         if constexpr (C::NOUT == 1) {
             if (t == 0) {
                 if (R.valid[0]) T.out[R.idx[0]] = out[0];
@@ -363,7 +398,6 @@ __device__ void decoder_forward_cta(const StageParams& P, const DecTask& T, floa
                 if (R.valid[1]) *reinterpret_cast<float2*>(T.out + 4 * R.idx[1] + 2 * t) = make_float2(out[2], out[3]);
             }
         }
-        (void)g;
     }
 }
 
@@ -382,53 +416,78 @@ k_decoders_forward(const __grid_constant__ StageParams P) {
 }
 
 // ---- backward -------------------------------------------------------------------------------
-// d(e) (C fragments, natural column map, 12 n-tiles) -> d(p): e = sin(p.B) so
-// d(p_a) += d(e_f) cos(p.B_f) B[a][f].
-__device__ __forceinline__ void embed_grad(const float (&dE)[E_SLABS][4], const Rows& R,
-                                           const float* Bs, int t, float (&dp)[2][3]) {
+// d(a) (A fragments, chain map) -> d(e) = d(a) W^T two n-tiles at a time (rolled over the 6
+// n-tile pairs), consumed on the fly: e = sin(p.B) so d(p_a) += d(e_f) cos(p.B_f) B[a][f].
+__device__ __forceinline__ void embed_grad(const float (&a)[4][4], const float* __restrict__ Ws,
+                                           const Rows& R, const float* Bs, int lane, float (&dp)[2][3]) {
+    const int t = lane & 3;
+    uint32_t ah[4][4], al[4][4];
 #pragma unroll
-    for (int n = 0; n < E_SLABS; ++n)
+    for (int j = 0; j < 4; ++j)
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int r = q >> 1, f = 8 * n + 2 * t + (q & 1);
-            float v = dE[n][q] * cosf(phase(R.p[r], Bs, f));
-            dp[r][0] = fmaf(v, Bs[f], dp[r][0]);
-            dp[r][1] = fmaf(v, Bs[EMB_PAD + f], dp[r][1]);
-            dp[r][2] = fmaf(v, Bs[2 * EMB_PAD + f], dp[r][2]);
+        for (int i = 0; i < 4; ++i) split_tf32(a[j][i], ah[j][i], al[j][i]);
+    const float4* B4 = reinterpret_cast<const float4*>(Ws);
+#pragma unroll 1
+    for (int h = 0; h < E_SLABS / 2; ++h) {
+        float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float4 b = B4[(j * (E_SLABS / 2) + h) * 32 + lane];
+            uint32_t bh[4], bl[4];
+            split_tf32(b.x, bh[0], bl[0]);
+            split_tf32(b.y, bh[1], bl[1]);
+            split_tf32(b.z, bh[2], bl[2]);
+            split_tf32(b.w, bh[3], bl[3]);
+            mma_tf32(d0, al[j], bh[0], bh[1]);
+            mma_tf32(d0, ah[j], bl[0], bl[1]);
+            mma_tf32(d0, ah[j], bh[0], bh[1]);
+            mma_tf32(d1, al[j], bh[2], bh[3]);
+            mma_tf32(d1, ah[j], bl[2], bl[3]);
+            mma_tf32(d1, ah[j], bh[2], bh[3]);
         }
+#pragma unroll
+        for (int nn = 0; nn < 2; ++nn)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int r = q >> 1, f = 8 * (2 * h + nn) + 2 * t + (q & 1);
+                const float v = (nn ? d1[q] : d0[q]) * cosf(phase(R.p[r], Bs, f));
+                dp[r][0] = fmaf(v, Bs[f], dp[r][0]);
+                dp[r][1] = fmaf(v, Bs[EMB_PAD + f], dp[r][1]);
+                dp[r][2] = fmaf(v, Bs[2 * EMB_PAD + f], dp[r][2]);
+            }
+    }
 }
 
 // scatter-add d(c) (8 channels of one point) to the 8 corners; optionally the coordinate
 // gradient (ATen grid_sampler_3d_backward: d(ix) = sum_corners +-(other two weights) <g, v>)
-template <bool SCATTER, bool COORD>
-__device__ __forceinline__ void grid_backward(const GridDev& G, const float (&u)[3],
-                                              const double* ext, int t, const float (&dc)[8],
-                                              float (&dp)[3]) {
+__device__ __forceinline__ void grid_backward(bool scatter, bool coord, const GridDev& G,
+                                              const float (&u)[3], const double* ext, int t,
+                                              const float (&dc)[8], float (&dp)[3]) {
     Tri T = tri_setup(u, G);
     float gx = 0.f, gy = 0.f, gz = 0.f;
-    const float wx[2] = {(T.x0 + 1.f) - T.ix, T.ix - T.x0};
-    const float wy[2] = {(T.y0 + 1.f) - T.iy, T.iy - T.y0};
-    const float wz[2] = {(T.z0 + 1.f) - T.iz, T.iz - T.z0};
-#pragma unroll
+#pragma unroll 1
     for (int k = 0; k < 8; ++k) {
+        const int dx = k & 1, dy = (k >> 1) & 1, dz = k >> 2;
+        const float wx = dx ? (T.ix - T.x0) : ((T.x0 + 1.f) - T.ix);
+        const float wy = dy ? (T.iy - T.y0) : ((T.y0 + 1.f) - T.iy);
+        const float wz = dz ? (T.iz - T.z0) : ((T.z0 + 1.f) - T.iz);
         const size_t off = (size_t)tri_offset(T, k) * CDIM + 8 * t;
-        if (SCATTER) {
-            float w = tri_weight(T, k);
+        if (scatter) {
+            const float w = (wx * wy) * wz;
             red_add_v4(G.grad + off, w * dc[0], w * dc[1], w * dc[2], w * dc[3]);
             red_add_v4(G.grad + off + 4, w * dc[4], w * dc[5], w * dc[6], w * dc[7]);
         }
-        if (COORD) {
+        if (coord) {
             const float4* p = reinterpret_cast<const float4*>(G.data + off);
             float4 a = __ldg(p), b = __ldg(p + 1);
             float s = a.x * dc[0] + a.y * dc[1] + a.z * dc[2] + a.w * dc[3] + b.x * dc[4] +
                       b.y * dc[5] + b.z * dc[6] + b.w * dc[7];
-            const int dx = k & 1, dy = (k >> 1) & 1, dz = k >> 2;
-            gx += (dx ? s : -s) * wy[dy] * wz[dz];
-            gy += (dy ? s : -s) * wx[dx] * wz[dz];
-            gz += (dz ? s : -s) * wx[dx] * wy[dy];
+            gx += (dx ? s : -s) * wy * wz;
+            gy += (dy ? s : -s) * wx * wz;
+            gz += (dz ? s : -s) * wx * wy;
         }
     }
-    if (COORD) {
+    if (coord) {
         dp[0] += gx * T.mx * (float)(2.0 / ext[0]);
         dp[1] += gy * T.my * (float)(2.0 / ext[1]);
         dp[2] += gz * T.mz * (float)(2.0 / ext[2]);
@@ -438,8 +497,10 @@ __device__ __forceinline__ void grid_backward(const GridDev& G, const float (&u)
 template <int KIND>
 __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, float* sm) {
     using C = DecCfg<KIND>;
+    using O = Off<KIND>;
     stage_weights(sm, T.packed, C::TOTAL);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, t = lane & 3;
+    float* es = sm + C::TOTAL + warp * E_BUF;
     const long long ntiles = (P.pts.P + 15) / 16;
     const bool want_grid = (P.flags & NSB_GRAD_GRID) && T.own.grad != nullptr;
     const bool want_point = (P.flags & NSB_GRAD_POINT) && T.d_point != nullptr;
@@ -474,79 +535,48 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, flo
             }
         }
         Rows R;
-        uint32_t mask[5];
+        Masks mk;
         {
-            float e[E_SLABS][4];
             float c[C::CS][4];
             float out[4];
-            tile_inputs<KIND>(P.pts, T, sm, tile, lane, R, e, c);
-            mlp_forward<KIND, true>(sm, lane, e, c, out, mask);
+            tile_inputs<KIND>(P.pts, T, sm, es, tile, lane, R, c);
+            mlp_forward<KIND>(sm, es, lane, c, out, mk);
         }
         float dp[2][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
         float dh[4][4], a[4][4], dc[4][4];
         zero_(dh);
         zero_(dc);
         gemm3<1, 4>(dh, dA, sm + C::OFF_TOUT, lane);                  // d(h5)
-        // layer 4
-        chain<4>(a, dh);
-        if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + C::OFF_TC4, lane);
-        mask_(dh, mask[4]); chain<4>(a, dh); zero_(dh);
-        gemm3<4, 4>(dh, a, sm + C::OFF_TL4, lane);                    // d(h4)
-        // layer 3 (skip input)
-        chain<4>(a, dh);
-        if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + C::OFF_TC3, lane);
-        mask_(dh, mask[3]); chain<4>(a, dh); zero_(dh);
-        if constexpr (C::EMBED) {
-            if (want_point) {
-                float dE[E_SLABS][4];
-#pragma unroll
-                for (int n = 0; n < E_SLABS; ++n)
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) dE[n][q] = 0.f;
-                gemm3<4, E_SLABS>(dE, a, sm + C::OFF_TL3X, lane);
-                embed_grad(dE, R, sm + C::OFF_B, t, dp);
+#pragma unroll 1
+        for (int i = 4; i >= 0; --i) {
+            chain<4>(a, dh);                                           // d(h_{i+1})
+            if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + O::TC(i), lane);
+            mask_(dh, mk.get(i));                                      // through the ReLU
+            chain<4>(a, dh);
+            if (i == 3 || i == 0) {                                    // input-side part of the layer
+                if constexpr (C::EMBED) {
+                    if (want_point) embed_grad(a, sm + O::TX(i), R, sm + C::OFF_B, lane, dp);
+                } else {
+                    gemm3<4, 4>(dc, a, sm + O::TX(i), lane);
+                }
             }
-        } else {
-            gemm3<4, 4>(dc, a, sm + C::OFF_TL3X, lane);
-        }
-        gemm3<4, 4>(dh, a, sm + C::OFF_TL3, lane);                    // d(h3)
-        // layer 2
-        chain<4>(a, dh);
-        if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + C::OFF_TC2, lane);
-        mask_(dh, mask[2]); chain<4>(a, dh); zero_(dh);
-        gemm3<4, 4>(dh, a, sm + C::OFF_TL2, lane);
-        // layer 1
-        chain<4>(a, dh);
-        if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + C::OFF_TC1, lane);
-        mask_(dh, mask[1]); chain<4>(a, dh); zero_(dh);
-        gemm3<4, 4>(dh, a, sm + C::OFF_TL1, lane);
-        // layer 0
-        chain<4>(a, dh);
-        if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + C::OFF_TC0, lane);
-        mask_(dh, mask[0]); chain<4>(a, dh);
-        if constexpr (C::EMBED) {
-            if (want_point) {
-                float dE[E_SLABS][4];
-#pragma unroll
-                for (int n = 0; n < E_SLABS; ++n)
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) dE[n][q] = 0.f;
-                gemm3<4, E_SLABS>(dE, a, sm + C::OFF_TL0, lane);
-                embed_grad(dE, R, sm + C::OFF_B, t, dp);
+            if (i > 0) {
+                zero_(dh);
+                gemm3<4, 4>(dh, a, sm + O::TL(i), lane);               // d(h_i)
             }
-        } else {
-            gemm3<4, 4>(dc, a, sm + C::OFF_TL0, lane);
         }
         // d(c): gather column map -> lane holds channels 8t..8t+7 of rows g, g+8
-#pragma unroll
+#pragma unroll 1
         for (int r = 0; r < 2; ++r) {
-            float d8[8];
+            float d8[8], g3[3] = {0.f, 0.f, 0.f};
 #pragma unroll
-            for (int k = 0; k < 8; ++k) d8[k] = dc[k >> 1][2 * r + (k & 1)];
-            if (R.valid[r]) {
-                if (want_grid && want_point) grid_backward<true, true>(T.own, R.u[r], T.ext, t, d8, dp[r]);
-                else if (want_grid) grid_backward<true, false>(T.own, R.u[r], T.ext, t, d8, dp[r]);
-                else if (want_point) grid_backward<false, true>(T.own, R.u[r], T.ext, t, d8, dp[r]);
+            for (int k = 0; k < 8; ++k) d8[k] = r ? dc[k >> 1][2 + (k & 1)] : dc[k >> 1][k & 1];
+            const float u[3] = {r ? R.u[1][0] : R.u[0][0], r ? R.u[1][1] : R.u[0][1], r ? R.u[1][2] : R.u[0][2]};
+            if ((r ? R.valid[1] : R.valid[0]) && (want_grid || want_point))
+                grid_backward(want_grid, want_point, T.own, u, T.ext, t, d8, g3);
+#pragma unroll
+            for (int ax = 0; ax < 3; ++ax) {
+                if (r == 0) dp[0][ax] += g3[ax]; else dp[1][ax] += g3[ax];
             }
         }
         if (want_point) {
@@ -599,7 +629,7 @@ static int init_device() {
     e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return set_error((int)e, "device attribute: %s", cudaGetErrorString(e));
     g_num_sms = sms;
-    const int max_smem = DecCfg<KIND_FINE>::TOTAL * 4;
+    const int max_smem = (DecCfg<KIND_FINE>::TOTAL + WARPS * E_BUF) * 4;
     e = cudaFuncSetAttribute(k_decoders_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(k_decoders_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
@@ -688,13 +718,14 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
     return begin;
 }
 
+// dynamic shared memory of a launch in floats: the largest blob + one e buffer per warp
 static int max_blob(const StageParams& sp, bool bwd) {
     int m = 0;
     for (int i = 0; i < sp.ntask; ++i) {
         int b = blob_floats(sp.task[i].kind, bwd);
         if (b > m) m = b;
     }
-    return m;
+    return m + WARPS * E_BUF;
 }
 
 }  // namespace nsb
