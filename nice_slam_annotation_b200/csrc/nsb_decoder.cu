@@ -25,6 +25,8 @@
 //    transposed chain, turns d(e) into d(p) on the fly, scatters d(c) to the grid gradient
 //    with 128-bit vector reductions (red.global.add.v4.f32) and re-gathers the corners for
 //    the coordinate gradient.  Tiles whose incoming gradient is exactly zero are skipped.
+#include <cstring>
+
 #include "nsb_common.cuh"
 
 namespace nsb {
@@ -44,7 +46,8 @@ struct DecTask {
     double lo[3], ext[3];
     float* out;       // forward: [P] (1 output) or [P,4]
     float* d_point;   // backward: [P,3] plane or NULL
-    float* dw_scratch;
+    float* dw_scratch;         // backward: weight-gradient records of this launch's tiles, or NULL
+    unsigned char* dw_flags;   // one byte per tile: record written
 };
 
 struct StageParams {
@@ -53,6 +56,7 @@ struct StageParams {
     int ntask;
     const float* d_raw;   // backward: [P,4]
     unsigned flags;
+    long long tile_begin, tile_end;   // tiles of this launch (backward is chunked for d(W))
 };
 
 // ---- per-thread view of its two points -------------------------------------------------------
@@ -321,13 +325,23 @@ struct Off {
     }
 };
 
+// C fragments [4 n-tiles] of a 16 x 32 tile -> dense [16][32] (record section)
+__device__ __forceinline__ void store_c32(float* dst, const float (&acc)[4][4], int lane) {
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+        *reinterpret_cast<float2*>(dst + g * HID + 8 * n + 2 * t) = make_float2(acc[n][0], acc[n][1]);
+        *reinterpret_cast<float2*>(dst + (g + 8) * HID + 8 * n + 2 * t) = make_float2(acc[n][2], acc[n][3]);
+    }
+}
+
 // MLP.forward (EMBED) / MLP_no_xyz.forward (COARSE) for one 16-point tile.  es: the warp's
 // embedding buffer (unused for COARSE), c: feature slabs.  out: C fragment of the padded
 // 8-column output tile (columns 2t, 2t+1 for rows g, g+8).
 template <int KIND>
 __device__ __forceinline__ void mlp_forward(const float* sm, const float* es, int lane,
                                             const float (&c)[DecCfg<KIND>::CS][4], float (&out)[4],
-                                            Masks& mk) {
+                                            Masks& mk, float* rec = nullptr) {
     using C = DecCfg<KIND>;
     using O = Off<KIND>;
     const int t = lane & 3;
@@ -346,6 +360,7 @@ __device__ __forceinline__ void mlp_forward(const float* sm, const float* es, in
             gemm3<C::CS, 4>(acc, c, sm + O::Cc(i), lane);
         }
         chain<4>(h, acc);
+        if (rec) store_c32(rec + RecCfg<KIND>::R_H + i * 16 * HID, acc, lane);     // h_{i+1}
     }
     float2 bo = *reinterpret_cast<const float2*>(sm + C::OFF_BO + 2 * t);
     out[0] = bo.x; out[1] = bo.y; out[2] = bo.x; out[3] = bo.y;
@@ -419,8 +434,9 @@ k_decoders_forward(const __grid_constant__ StageParams P) {
 // d(a) (A fragments, chain map) -> d(e) = d(a) W^T two n-tiles at a time (rolled over the 6
 // n-tile pairs), consumed on the fly: e = sin(p.B) so d(p_a) += d(e_f) cos(p.B_f) B[a][f].
 __device__ __forceinline__ void embed_grad(const float (&a)[4][4], const float* __restrict__ Ws,
-                                           const Rows& R, const float* Bs, int lane, float (&dp)[2][3]) {
-    const int t = lane & 3;
+                                           const Rows& R, const float* Bs, int lane, float (&dp)[2][3],
+                                           float* des = nullptr, bool des_add = false) {
+    const int t = lane & 3, g = lane >> 2;
     uint32_t ah[4][4], al[4][4];
 #pragma unroll
     for (int j = 0; j < 4; ++j)
@@ -451,6 +467,10 @@ __device__ __forceinline__ void embed_grad(const float (&a)[4][4], const float* 
             for (int q = 0; q < 4; ++q) {
                 const int r = q >> 1, f = 8 * (2 * h + nn) + 2 * t + (q & 1);
                 const float v = (nn ? d1[q] : d0[q]) * cosf(phase(R.p[r], Bs, f));
+                if (des) {                      // d(B)[a][f] = sum_points p_a * v  (k_dweight)
+                    float* q_ = des + (g + 8 * r) * EMB_PAD + f;
+                    *q_ = des_add ? *q_ + v : v;
+                }
                 dp[r][0] = fmaf(v, Bs[f], dp[r][0]);
                 dp[r][1] = fmaf(v, Bs[EMB_PAD + f], dp[r][1]);
                 dp[r][2] = fmaf(v, Bs[2 * EMB_PAD + f], dp[r][2]);
@@ -504,8 +524,11 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, flo
     const long long ntiles = (P.pts.P + 15) / 16;
     const bool want_grid = (P.flags & NSB_GRAD_GRID) && T.own.grad != nullptr;
     const bool want_point = (P.flags & NSB_GRAD_POINT) && T.d_point != nullptr;
-    for (long long tile = (long long)(blockIdx.x - T.cta_begin) * WARPS + warp; tile < ntiles;
+    using RC = RecCfg<KIND>;
+    (void)ntiles;
+    for (long long tile = P.tile_begin + (long long)(blockIdx.x - T.cta_begin) * WARPS + warp; tile < P.tile_end;
          tile += (long long)T.cta_count * WARPS) {
+        float* rec = T.dw_scratch ? T.dw_scratch + (size_t)(tile - P.tile_begin) * RC::REC : nullptr;
         // incoming gradient first: most tiles behind the surface carry exact zeros
         float dA[1][4];
         {
@@ -524,6 +547,7 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, flo
             }
             dA[0][0] = v0; dA[0][1] = v1; dA[0][2] = 0.f; dA[0][3] = 0.f;
             if (!__any_sync(FULL, v0 != 0.f || v1 != 0.f)) {
+                if (rec && lane == 0) T.dw_flags[tile - P.tile_begin] = 0;
                 if (want_point && t == 0) {
 #pragma unroll
                     for (int a = 0; a < 3; ++a) {
@@ -540,7 +564,55 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, flo
             float c[C::CS][4];
             float out[4];
             tile_inputs<KIND>(P.pts, T, sm, es, tile, lane, R, c);
-            mlp_forward<KIND>(sm, es, lane, c, out, mk);
+            mlp_forward<KIND>(sm, es, lane, c, out, mk, rec);
+            if (rec) {      // layer inputs that live outside the MLP loop: e, c, p; and d(out)
+                const int g = lane >> 2;
+                if (lane == 0) T.dw_flags[tile - P.tile_begin] = 1;
+                if constexpr (C::EMBED) {
+#pragma unroll 1
+                    for (int j = 0; j < E_SLABS; ++j) {
+                        const int f0 = 8 * j + t, f1 = f0 + 4;
+                        rec[RC::R_E + g * EMB_PAD + f0] = es[esw(g, f0)];
+                        rec[RC::R_E + (g + 8) * EMB_PAD + f0] = es[esw(g + 8, f0)];
+                        rec[RC::R_E + g * EMB_PAD + f1] = es[esw(g, f1)];
+                        rec[RC::R_E + (g + 8) * EMB_PAD + f1] = es[esw(g + 8, f1)];
+                    }
+                }
+#pragma unroll
+                for (int L = 0; L < C::CS / 4; ++L) {       // channels 8t..8t+7 of grid level L
+                    float* c0 = rec + RC::R_C + g * C::C_IN + 32 * L + 8 * t;
+                    float* c1 = rec + RC::R_C + (g + 8) * C::C_IN + 32 * L + 8 * t;
+                    const int j0 = 4 * L;
+                    *reinterpret_cast<float4*>(c0) = make_float4(c[j0][0], c[j0][2], c[j0 + 1][0], c[j0 + 1][2]);
+                    *reinterpret_cast<float4*>(c0 + 4) = make_float4(c[j0 + 2][0], c[j0 + 2][2], c[j0 + 3][0], c[j0 + 3][2]);
+                    *reinterpret_cast<float4*>(c1) = make_float4(c[j0][1], c[j0][3], c[j0 + 1][1], c[j0 + 1][3]);
+                    *reinterpret_cast<float4*>(c1 + 4) = make_float4(c[j0 + 2][1], c[j0 + 2][3], c[j0 + 3][1], c[j0 + 3][3]);
+                }
+                // p: [16][8] (cols 0..2), d(out): [16][32] (cols < NOUT, rest zero)
+                {
+                    float* p0 = rec + RC::R_P + g * 8, * p1 = rec + RC::R_P + (g + 8) * 8;
+                    if (t == 0) {
+                        *reinterpret_cast<float4*>(p0) = make_float4(R.p[0][0], R.p[0][1], R.p[0][2], 0.f);
+                        *reinterpret_cast<float4*>(p1) = make_float4(R.p[1][0], R.p[1][1], R.p[1][2], 0.f);
+                    } else if (t == 1) {
+                        *reinterpret_cast<float4*>(p0 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+                        *reinterpret_cast<float4*>(p1 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                    // gather the (up to 4) output gradients of the row from lanes t = 0..3
+                    float d0[4], d1[4];
+#pragma unroll
+                    for (int o = 0; o < 4; ++o) {
+                        d0[o] = __shfl_sync(FULL, dA[0][0], (lane & ~3) | o);
+                        d1[o] = __shfl_sync(FULL, dA[0][1], (lane & ~3) | o);
+                    }
+                    float* o0 = rec + RC::R_DO + g * HID + 8 * t, * o1 = rec + RC::R_DO + (g + 8) * HID + 8 * t;
+                    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    *reinterpret_cast<float4*>(o0) = t == 0 ? make_float4(d0[0], d0[1], d0[2], d0[3]) : z4;
+                    *reinterpret_cast<float4*>(o1) = t == 0 ? make_float4(d1[0], d1[1], d1[2], d1[3]) : z4;
+                    *reinterpret_cast<float4*>(o0 + 4) = z4;
+                    *reinterpret_cast<float4*>(o1 + 4) = z4;
+                }
+            }
         }
         float dp[2][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
         float dh[4][4], a[4][4], dc[4][4];
@@ -550,12 +622,18 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, flo
 #pragma unroll 1
         for (int i = 4; i >= 0; --i) {
             chain<4>(a, dh);                                           // d(h_{i+1})
-            if constexpr (C::EMBED) gemm3<4, 4>(dc, a, sm + O::TC(i), lane);
+            if constexpr (C::EMBED) {
+                gemm3<4, 4>(dc, a, sm + O::TC(i), lane);
+                if (rec) store_c32(rec + RC::R_DH + i * 16 * HID, dh, lane);
+            }
             mask_(dh, mk.get(i));                                      // through the ReLU
+            if (rec) store_c32(rec + RC::R_DA + i * 16 * HID, dh, lane);
             chain<4>(a, dh);
             if (i == 3 || i == 0) {                                    // input-side part of the layer
                 if constexpr (C::EMBED) {
-                    if (want_point) embed_grad(a, sm + O::TX(i), R, sm + C::OFF_B, lane, dp);
+                    if (want_point || rec)
+                        embed_grad(a, sm + O::TX(i), R, sm + C::OFF_B, lane, dp,
+                                   rec ? rec + RC::R_DE : nullptr, i == 0);
                 } else {
                     gemm3<4, 4>(dc, a, sm + O::TX(i), lane);
                 }
@@ -607,9 +685,211 @@ k_decoders_backward(const __grid_constant__ StageParams P) {
     }
 }
 
+// ---- weight gradients ------------------------------------------------------------------------
+// d(W) = G^T X summed over points, for every linear layer of one decoder, from the records
+// the backward kernel wrote (nsb_layout.h RecCfg).  A CTA walks its share of the tiles; per
+// tile the record is copied to shared memory (rows padded to a stride of 8 mod 32) and each
+// warp runs its "units" -- a unit is one 32 x 8 block of some d(W) (two m-tiles, one n-tile),
+// 3xTF32, accumulators in registers for the whole kernel -- then adds them to the flat
+// gradient with one atomic per element per CTA.  Bias gradients are column sums of G.
+constexpr int DW_UNIT_INTS = 12;
+constexpr int DW_UPW = 8;          // max units per warp
+constexpr int DW_MAX_UNITS = DW_UPW * WARPS;
+constexpr int DW_MAX_SEC = 24;
+constexpr int DW_MAX_BIAS = THREADS;
+
+struct DwUnit {       // all offsets in floats of the PADDED shared-memory record
+    int a_off, a_w, a_col0;      // G section, padded row stride, first row (f') of the 32-row block
+    int b_off, b_w, b_col0;      // X section, padded row stride, first column of the n-tile
+    int out_off, ld_row, ld_col; // flat gradient index = out_off + row*ld_row + col*ld_col
+    int rows_valid, cols_valid, pad_;
+};
+struct DwSec { int g_off, width, s_off; };
+struct DwBias { int s_off, s_w, col, out_idx; };
+
+struct DwTables {
+    DwUnit unit[DW_MAX_UNITS];
+    DwSec sec[DW_MAX_SEC];
+    DwBias bias[DW_MAX_BIAS];
+    int nunit, nsec, nbias, rec, rec_padded;
+};
+
+struct DwParams {
+    const float* scratch;
+    const unsigned char* flags;
+    long long ntiles;
+    const DwTables* tab;     // device copy
+    float* dflat;
+};
+
+__global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
+    extern __shared__ __align__(16) float sm[];
+    const DwTables& TB = *P.tab;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    float acc[DW_UPW][2][4];
+#pragma unroll
+    for (int k = 0; k < DW_UPW; ++k)
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[k][m][q] = 0.f;
+    float bias_acc = 0.f;
+    const int nunit = TB.nunit, nsec = TB.nsec, nbias = TB.nbias, rec = TB.rec;
+    for (long long tile = blockIdx.x; tile < P.ntiles; tile += gridDim.x) {
+        if (!P.flags[tile]) continue;                       // uniform over the CTA
+        const float* src = P.scratch + (size_t)tile * rec;
+        __syncthreads();                                     // previous tile fully consumed
+        for (int s = 0; s < nsec; ++s) {
+            const DwSec sc = TB.sec[s];
+            const int w4 = sc.width >> 2;
+            for (int i = threadIdx.x; i < 16 * w4; i += THREADS) {
+                const int row = i / w4, c4 = i - row * w4;
+                const float4 v = __ldg(reinterpret_cast<const float4*>(src + sc.g_off + row * sc.width) + c4);
+                *reinterpret_cast<float4*>(sm + sc.s_off + row * (sc.width + REC_PAD) + 4 * c4) = v;
+            }
+        }
+        __syncthreads();
+        if ((int)threadIdx.x < nbias) {
+            const DwBias b = TB.bias[threadIdx.x];
+            float s = 0.f;
+#pragma unroll
+            for (int pt = 0; pt < 16; ++pt) s += sm[b.s_off + pt * b.s_w + b.col];
+            bias_acc += s;
+        }
+#pragma unroll
+        for (int k = 0; k < DW_UPW; ++k) {
+            const int u = warp + WARPS * k;
+            if (u < nunit) {
+                const DwUnit U = TB.unit[u];
+#pragma unroll
+                for (int ks = 0; ks < 2; ++ks) {
+                    const float* Ap = sm + U.a_off + (8 * ks + t) * U.a_w + U.a_col0 + g;
+                    const float* Bp = sm + U.b_off + (8 * ks + t) * U.b_w + U.b_col0 + g;
+                    uint32_t bh[2], bl[2];
+                    split_tf32(Bp[0], bh[0], bl[0]);
+                    split_tf32(Bp[4 * U.b_w], bh[1], bl[1]);
+#pragma unroll
+                    for (int m = 0; m < 2; ++m) {
+                        uint32_t ah[4], al[4];
+                        split_tf32(Ap[16 * m], ah[0], al[0]);
+                        split_tf32(Ap[16 * m + 8], ah[1], al[1]);
+                        split_tf32(Ap[4 * U.a_w + 16 * m], ah[2], al[2]);
+                        split_tf32(Ap[4 * U.a_w + 16 * m + 8], ah[3], al[3]);
+                        mma_tf32(acc[k][m], al, bh[0], bh[1]);
+                        mma_tf32(acc[k][m], ah, bl[0], bl[1]);
+                        mma_tf32(acc[k][m], ah, bh[0], bh[1]);
+                    }
+                }
+            }
+        }
+    }
+    // flush: C fragment (row 16m + g (+8), col 2t (+1)) of unit u
+#pragma unroll
+    for (int k = 0; k < DW_UPW; ++k) {
+        const int u = warp + WARPS * k;
+        if (u < nunit) {
+            const DwUnit U = TB.unit[u];
+#pragma unroll
+            for (int m = 0; m < 2; ++m)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int row = 16 * m + g + 8 * (q >> 1), col = 2 * t + (q & 1);
+                    if (row < U.rows_valid && col < U.cols_valid && acc[k][m][q] != 0.f)
+                        atomicAdd(P.dflat + U.out_off + row * U.ld_row + col * U.ld_col, acc[k][m][q]);
+                }
+        }
+    }
+    if ((int)threadIdx.x < nbias && bias_acc != 0.f) atomicAdd(P.dflat + TB.bias[threadIdx.x].out_idx, bias_acc);
+}
+
+// host: tables of one decoder kind
+template <int KIND>
+static void build_dw_tables(DwTables& T) {
+    using C = DecCfg<KIND>;
+    using RC = RecCfg<KIND>;
+    memset(&T, 0, sizeof(T));
+    // flat offsets of the canonical parameters
+    int off[32], acc_off = 0;
+    for (int i = 0; i < C::N_PARAM; ++i) {
+        off[i] = acc_off;
+        int numel;
+        if (i < 5) numel = HID * C::in_dim(i);
+        else if (i < 10) numel = HID;
+        else if (C::EMBED) numel = i < 15 ? HID * C::C_IN : (i < 20 ? HID : (i == 20 ? C::NOUT * HID : (i == 21 ? C::NOUT : 3 * EMB)));
+        else numel = i == 10 ? HID : 1;
+        acc_off += numel;
+    }
+    // sections and their padded shared offsets
+    int s_off = 0;
+    auto add_sec = [&](int g_off, int width) {
+        DwSec& s = T.sec[T.nsec++];
+        s.g_off = g_off; s.width = width; s.s_off = s_off;
+        const int r = s_off;
+        s_off += 16 * (width + REC_PAD);
+        return r;
+    };
+    int sE = -1, sH[5], sC, sP = -1, sDA[5], sDH[5], sDO, sDE = -1;
+    if (C::EMBED) sE = add_sec(RC::R_E, EMB_PAD);
+    for (int i = 0; i < 5; ++i) sH[i] = add_sec(RC::R_H + i * 16 * HID, HID);
+    sC = add_sec(RC::R_C, C::C_IN);
+    if (C::EMBED) sP = add_sec(RC::R_P, 8);
+    for (int i = 0; i < 5; ++i) sDA[i] = add_sec(RC::R_DA + i * 16 * HID, HID);
+    if (C::EMBED) for (int i = 0; i < 5; ++i) sDH[i] = add_sec(RC::R_DH + i * 16 * HID, HID);
+    sDO = add_sec(RC::R_DO, HID);
+    if (C::EMBED) sDE = add_sec(RC::R_DE, EMB_PAD);
+    T.rec = RC::REC;
+    T.rec_padded = s_off;
+    auto add_unit = [&](int a_off, int a_width, int a_col0, int b_off, int b_width, int b_col0, int out_off,
+                        int ld_row, int ld_col, int rows_valid, int cols_valid) {
+        DwUnit& u = T.unit[T.nunit++];
+        u.a_off = a_off; u.a_w = a_width + REC_PAD; u.a_col0 = a_col0;
+        u.b_off = b_off; u.b_w = b_width + REC_PAD; u.b_col0 = b_col0;
+        u.out_off = out_off; u.ld_row = ld_row; u.ld_col = ld_col;
+        u.rows_valid = rows_valid; u.cols_valid = cols_valid;
+    };
+    // X parts of layer i: (section, width, number of n-tiles, valid features, first input column)
+    for (int i = 0; i < 5; ++i) {
+        const int in = C::in_dim(i);
+        auto part = [&](int sec, int width, int feats, int col_base) {
+            for (int n = 0; n * 8 < feats; ++n) {
+                const int valid = feats - 8 * n < 8 ? feats - 8 * n : 8;
+                add_unit(sDA[i], HID, 0, sec, width, 8 * n, off[C::P_W + i] + col_base + 8 * n, in, 1, HID, valid);
+            }
+        };
+        if (C::EMBED) {
+            if (i == 0) part(sE, EMB_PAD, EMB, 0);
+            else if (i == 3) { part(sE, EMB_PAD, EMB, 0); part(sH[2], HID, HID, EMB); }
+            else part(sH[i - 1], HID, HID, 0);
+            for (int n = 0; n * 8 < C::C_IN; ++n)
+                add_unit(sDH[i], HID, 0, sC, C::C_IN, 8 * n, off[C::P_WC + i] + 8 * n, C::C_IN, 1, HID, 8);
+        } else {
+            if (i == 0) part(sC, CDIM, CDIM, 0);
+            else if (i == 3) { part(sC, CDIM, CDIM, 0); part(sH[2], HID, HID, CDIM); }
+            else part(sH[i - 1], HID, HID, 0);
+        }
+    }
+    for (int n = 0; n < 4; ++n)       // output layer: rows = outputs
+        add_unit(sDO, HID, 0, sH[4], HID, 8 * n, off[C::P_WO] + 8 * n, HID, 1, C::NOUT, 8);
+    if (C::EMBED)
+        for (int m0 = 0; m0 < EMB_PAD; m0 += 32)   // d(B)[a][f]: rows = features f, cols = axes a
+            add_unit(sDE, EMB_PAD, m0, sP, 8, 0, off[C::P_EMB] + m0, 1, EMB, (EMB - m0 < 32 ? EMB - m0 : 32), 3);
+    auto add_bias = [&](int sec, int width, int col, int out_idx) {
+        DwBias& b = T.bias[T.nbias++];
+        b.s_off = sec; b.s_w = width + REC_PAD; b.col = col; b.out_idx = out_idx;
+    };
+    for (int i = 0; i < 5; ++i)
+        for (int f = 0; f < HID; ++f) {
+            add_bias(sDA[i], HID, f, off[C::P_B + i] + f);
+            if (C::EMBED) add_bias(sDH[i], HID, f, off[C::P_BC + i] + f);
+        }
+    for (int o = 0; o < C::NOUT; ++o) add_bias(sDO, HID, o, off[C::P_BO] + o);
+}
+
 // ---- host side -------------------------------------------------------------------------------
 static int g_num_sms = 0;
 static bool g_attr_done = false;
+__device__ DwTables g_dw_tables[4];
+static DwTables g_dw_host[4];
 
 static int blob_floats(int kind, bool bwd) {
     switch (kind) {
@@ -634,6 +914,14 @@ static int init_device() {
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(k_decoders_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    build_dw_tables<KIND_COARSE>(g_dw_host[0]);
+    build_dw_tables<KIND_MIDDLE>(g_dw_host[1]);
+    build_dw_tables<KIND_FINE>(g_dw_host[2]);
+    build_dw_tables<KIND_COLOR>(g_dw_host[3]);
+    e = cudaMemcpyToSymbol(g_dw_tables, g_dw_host, sizeof(g_dw_host));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_dweight, cudaFuncAttributeMaxDynamicSharedMemorySize, g_dw_host[2].rec_padded * 4);
+    if (e != cudaSuccess) return set_error((int)e, "d(W) tables: %s", cudaGetErrorString(e));
     g_attr_done = true;
     return 0;
 }
@@ -708,6 +996,7 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
         if (!bwd && !T.out) return set_error(NSB_EINVAL, "missing output plane for decoder %d", k);
         T.d_point = d_point ? d_point + (size_t)i * P * 3 : nullptr;
         T.dw_scratch = nullptr;
+        T.dw_flags = nullptr;
         int share = share_of[i];
         if (share > want) share = want;
         T.cta_begin = begin;
@@ -745,13 +1034,22 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
     if (ctas < 0) return ctas;
     sp.d_raw = nullptr;
     sp.flags = 0;
+    sp.tile_begin = 0;
+    sp.tile_end = (sp.pts.P + 15) / 16;
     k_decoders_forward<<<ctas, THREADS, max_blob(sp, false) * 4, (cudaStream_t)stream>>>(sp);
     return check_launch("k_decoders_forward");
 }
 
+// bytes of one tile's record + flag, sized for the largest decoder
+static const int64_t kDwTileBytes = (int64_t)REC_MAX * 4 + 1;
+static const int64_t kDwMaxTiles = 4096;     // 64 Ki points per chunk
+
 extern "C" int64_t nsb_dweight_scratch_bytes(int kind, int64_t P) {
-    (void)kind; (void)P;
-    return 0;
+    (void)kind;
+    int64_t tiles = (P + 15) / 16;
+    if (tiles > kDwMaxTiles) tiles = kDwMaxTiles;
+    if (tiles < 1) tiles = 1;
+    return tiles * kDwTileBytes + 256;
 }
 
 extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene, int stage,
@@ -760,9 +1058,6 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
                                      int64_t scratch_bytes, void* stream) {
     if (!pts || !scene || !d_raw) return set_error(NSB_EINVAL, "null argument");
     if (int rc = init_device()) return rc;
-    if ((flags & NSB_GRAD_WEIGHT) && dweight_mask)
-        return set_error(NSB_ENOSYS, "decoder weight gradients are not available in this build");
-    (void)d_weight_host; (void)scratch; (void)scratch_bytes;
     StageParams sp{};
     sp.pts = to_dev(*pts);
     if (sp.pts.P <= 0) return 0;
@@ -772,6 +1067,56 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
     if (ctas < 0) return ctas;
     sp.d_raw = d_raw;
     sp.flags = flags;
-    k_decoders_backward<<<ctas, THREADS, max_blob(sp, true) * 4, (cudaStream_t)stream>>>(sp);
-    return check_launch("k_decoders_backward");
+    const long long ntiles = (sp.pts.P + 15) / 16;
+    // decoders whose parameters want a gradient
+    int ndw = 0;
+    if (flags & NSB_GRAD_WEIGHT)
+        for (int i = 0; i < sp.ntask; ++i)
+            if (dweight_mask & (1u << sp.task[i].kind)) {
+                if (!d_weight_host || !d_weight_host[sp.task[i].kind])
+                    return set_error(NSB_EINVAL, "d_weight[%d] is NULL", sp.task[i].kind);
+                ++ndw;
+            }
+    long long chunk = ntiles;
+    if (ndw) {
+        if (!scratch) return set_error(NSB_EINVAL, "weight gradients need a scratch buffer");
+        const int64_t share = (scratch_bytes - 256) / ndw;
+        chunk = share / kDwTileBytes;
+        if (chunk < 1) return set_error(NSB_EINVAL, "scratch too small: %lld bytes for %d decoders",
+                                        (long long)scratch_bytes, ndw);
+        if (chunk > ntiles) chunk = ntiles;
+        // carve: [records of decoder 0 | records of decoder 1 | ... | flags ...]
+        char* base = (char*)(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
+        int k = 0;
+        for (int i = 0; i < sp.ntask; ++i)
+            if (dweight_mask & (1u << sp.task[i].kind)) {
+                sp.task[i].dw_scratch = (float*)(base + (size_t)k * chunk * REC_MAX * 4);
+                sp.task[i].dw_flags = (unsigned char*)(base + (size_t)ndw * chunk * REC_MAX * 4 + (size_t)k * chunk);
+                ++k;
+            }
+    }
+    const int smem = max_blob(sp, true) * 4;
+    for (long long t0 = 0; t0 < ntiles; t0 += chunk) {
+        sp.tile_begin = t0;
+        sp.tile_end = t0 + chunk < ntiles ? t0 + chunk : ntiles;
+        k_decoders_backward<<<ctas, THREADS, smem, (cudaStream_t)stream>>>(sp);
+        if (int rc = check_launch("k_decoders_backward")) return rc;
+        for (int i = 0; i < sp.ntask && ndw; ++i) {
+            const DecTask& T = sp.task[i];
+            if (!T.dw_scratch) continue;
+            DwParams dp;
+            dp.scratch = T.dw_scratch;
+            dp.flags = T.dw_flags;
+            dp.ntiles = sp.tile_end - sp.tile_begin;
+            DwTables* dev_tab = nullptr;
+            cudaError_t e = cudaGetSymbolAddress((void**)&dev_tab, g_dw_tables);
+            if (e != cudaSuccess) return set_error((int)e, "cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            dp.tab = dev_tab + T.kind;
+            dp.dflat = d_weight_host[T.kind];
+            int grid = (int)(dp.ntiles < g_num_sms ? dp.ntiles : g_num_sms);
+            k_dweight<<<grid, THREADS, g_dw_host[T.kind].rec_padded * 4, (cudaStream_t)stream>>>(dp);
+            if (int rc = check_launch("k_dweight")) return rc;
+        }
+    }
+    return 0;
 }

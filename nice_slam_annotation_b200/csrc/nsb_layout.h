@@ -112,3 +112,28 @@ NSB_HD inline int col_natural(int n, int gamma) { return 8 * n + gamma; }
 NSB_HD inline int col_gather(int n, int gamma) { return 8 * (gamma >> 1) + 2 * n + (gamma & 1); }
 
 }  // namespace nsb
+
+// ---- weight-gradient scratch record ---------------------------------------------------------
+// One record per 16-point tile, written by the backward kernel and consumed by k_dweight:
+// the layer inputs X and the output-side gradients G of every linear layer, each a dense
+// [16 points][width] fp32 matrix.  d(W) of a layer is G^T X summed over points.
+namespace nsb {
+template <int KIND>
+struct RecCfg {
+    using C = DecCfg<KIND>;
+    static constexpr int W_E = C::EMBED ? EMB_PAD : 0;
+    static constexpr int R_E = 0;                              // e = sin(pB)          [16][96]
+    static constexpr int R_H = R_E + 16 * W_E;                 // h1..h5               5 x [16][32]
+    static constexpr int R_C = R_H + 5 * 16 * HID;             // c                    [16][C_IN]
+    static constexpr int R_P = R_C + 16 * C::C_IN;             // p (cols 0..2)        [16][8]
+    static constexpr int R_DA = R_P + 16 * 8;                  // d(a1)..d(a5)         5 x [16][32]
+    static constexpr int R_DH = R_DA + 5 * 16 * HID;           // d(h1)..d(h5)         5 x [16][32]
+    static constexpr int R_DO = R_DH + 5 * 16 * HID;           // d(out) (cols < NOUT) [16][32]
+    static constexpr int R_DE = R_DO + 16 * HID;               // d(e) * cos(pB)       [16][96]
+    static constexpr int REC = R_DE + 16 * W_E;
+};
+constexpr int REC_MAX = RecCfg<KIND_FINE>::REC;
+// shared-memory copy of a record pads every row by 8 floats (stride = 8 mod 32: the
+// transposed fragment reads of k_dweight are then bank-conflict free)
+constexpr int REC_PAD = 8;
+}  // namespace nsb

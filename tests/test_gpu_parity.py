@@ -39,8 +39,6 @@ def test_small_scene_forward_backward_vs_reference(gpu, golden, stage):
     ro = torch.as_tensor(d["rays_o"]).to(gpu.DEV).requires_grad_(True)
     rd = torch.as_tensor(d["rays_d"]).to(gpu.DEV).requires_grad_(True)
     gd = torch.as_tensor(d["gt_depth"]).to(gpu.DEV)
-    for p in dec.parameters():
-        p.requires_grad_(False)
     depth, var, color = _render(gpu, d, stage, ro, rd, gd, grids, dec)
     ref = sub(d, stage + ".")
     assert depth.dtype == torch.float64 and var.dtype == torch.float64 and color.dtype == torch.float32
@@ -62,6 +60,21 @@ def test_small_scene_forward_backward_vs_reference(gpu, golden, stage):
             assert_close(g.grad.cpu(), ref["g_" + k], TOL_GRAD, "g_" + k)
         else:
             assert g.grad is None or float(g.grad.abs().max()) == 0.0, k
+    _check_param_grads(dec, ref)
+
+
+def _check_param_grads(dec, ref):
+    """decoder parameter gradients against the reference's (gp_<state_dict name>)"""
+    n = 0
+    for name, p in dec.named_parameters():
+        key = "gp_" + name
+        if key in ref:
+            assert p.grad is not None, name
+            assert_close(p.grad.cpu(), ref[key], TOL_GRAD, key)
+            n += 1
+        else:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, name
+    assert n > 0
 
 
 def test_no_gt_depth(gpu, golden):
@@ -136,8 +149,6 @@ def test_trained_scene_vs_reference(gpu, golden, stage):
     """F2 fixture: state produced by the reference's own mapping step (meaningful depths)."""
     d = golden("trained_nice")
     dec = gpu.nice_from_state(sub(d, "dec."), d["bound"])
-    for p in dec.parameters():
-        p.requires_grad_(False)
     grids = gpu.grids_from(d, requires_grad=True)
     ro = torch.as_tensor(d["r.rays_o"]).to(gpu.DEV).requires_grad_(True)
     rd = torch.as_tensor(d["r.rays_d"]).to(gpu.DEV).requires_grad_(True)
@@ -155,3 +166,4 @@ def test_trained_scene_vs_reference(gpu, golden, stage):
     for k, g in grids.items():
         if "g_" + k in ref:
             assert_close(g.grad.cpu(), ref["g_" + k], TOL_GRAD, "g_" + k)
+    _check_param_grads(dec, ref)
