@@ -114,12 +114,13 @@ int nsb_pack_weights(int kind, const float* const* param_ptrs, const int32_t* ta
 /* ---- K1: rays and sample depths -------------------------------------------------------
  * nsb_sample_rays: get_samples / get_rays_from_uv (src/common.py:74-134).  indices are flat
  * indices into the crop [H0:H1, W0:W1] (row-major), as drawn by torch.randint
- * (common.py:99).  c2w is 12 floats (3x4 row-major).  color may be fp32 or fp64
+ * (common.py:99).  c2w is 12 floats (3x4 row-major); alternatively cam7 = [quat(4), t(3)]
+ * (get_camera_from_tensor, common.py:163-176, evaluated in the kernel).  color may be fp32 or fp64
  * (color_is_f64), the sampled colour is written as fp32.  prefilter (optional, may be
  * NULL): keep[n] = (bbox exit >= gt depth), src/Tracker.py:100-107, src/Mapper.py:580-591. */
 int nsb_sample_rays(const int64_t* indices, int64_t n, int H0, int H1, int W0, int W1,
                     int W_img, float fx, float fy, float cx, float cy, const float* c2w,
-                    const float* depth_img, const void* color_img, int color_is_f64,
+                    const float* cam7, const float* depth_img, const void* color_img, int color_is_f64,
                     const double* bound6_host, float* rays_o, float* rays_d, float* gt_depth,
                     float* gt_color, uint8_t* keep, void* stream);
 
@@ -145,6 +146,11 @@ int nsb_sample_z(const NsbPoints* rays, const float* gt_depth, const double* bou
 int nsb_importance_z(const double* z, const float* weights, int64_t N, int S, int N_imp,
                      const float* u, int64_t u_row_stride, double* z_samples, double* z_out,
                      void* stream);
+
+/* sample_pdf itself (src/common.py:19-63): bins [N,M] fp64, weights [N,M-1] fp32 ->
+ * samples [N,N_samples] fp64 (unsorted, as the reference returns them). */
+int nsb_sample_pdf(const double* bins, const float* weights, int64_t N, int M, int N_samples,
+                   const float* u, int64_t u_row_stride, double* samples, void* stream);
 
 /* ---- K2 + K3: grid gather + decoders --------------------------------------------------
  * Forward of NICE.forward at `stage` (decoder.py:336-370) for all points.  Outputs are

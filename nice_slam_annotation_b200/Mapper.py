@@ -1,0 +1,350 @@
+"""Mapper step with the reference's interface (src/Mapper.py): ``optimize_map`` is the
+per-mapped-frame optimisation whose iteration body (Mapper.py:488-642) is the render hot path
+and runs on the fused sm_100a kernels.
+
+Grids are kept channels-last in memory (one 128-byte line per voxel, the kernels' layout)
+while keeping the reference's logical shape [1,32,Z,Y,X]; everything the reference does with
+them (boolean-mask indexing, Adam, checkpointing) works unchanged on such tensors.
+
+``get_mask_from_c2w`` and ``keyframe_selection_overlap`` (Mapper.py:100-293) are callers of
+the path that run once per mapped frame; they are restated here with torch ops on the
+device (SURVEY.md 8f-2 marks them "next"; they are not kernels yet).  The frame loop
+``run()`` stays with the reference.
+"""
+import numpy as np
+import torch
+
+from .common import get_camera_from_tensor, get_samples, get_tensor_from_camera, random_select
+
+
+class Mapper(object):
+    def __init__(self, cfg, args, slam, coarse_mapper=False):
+        # Mapper.py:23-98 without dataset reader / visualiser / logger plumbing
+        self.cfg = cfg
+        self.args = args
+        self.coarse_mapper = coarse_mapper
+        for name in ('idx', 'logger', 'mesher', 'output', 'verbose', 'low_gpu_mem', 'mapping_idx',
+                     'mapping_cnt', 'estimate_c2w_list', 'mapping_first_frame'):
+            setattr(self, name, getattr(slam, name, None))
+        self.nice = slam.nice
+        self.c = slam.shared_c
+        self.bound = slam.bound
+        self.renderer = slam.renderer
+        self.decoders = slam.shared_decoders
+        self.scale = cfg['scale']
+        self.coarse = cfg['coarse']
+        self.occupancy = cfg['occupancy']
+        self.sync_method = cfg.get('sync_method', 'strict')
+        m = cfg['mapping']
+        self.device = m['device']
+        self.fix_fine = m['fix_fine']
+        self.BA = False
+        self.BA_cam_lr = m['BA_cam_lr']
+        self.fix_color = m['fix_color']
+        self.mapping_pixels = m['pixels']
+        self.num_joint_iters = m['iters']
+        self.every_frame = m['every_frame']
+        self.color_refine = m['color_refine']
+        self.w_color_loss = m['w_color_loss']
+        self.keyframe_every = m['keyframe_every']
+        self.fine_iter_ratio = m['fine_iter_ratio']
+        self.middle_iter_ratio = m['middle_iter_ratio']
+        self.mapping_window_size = m['mapping_window_size']
+        self.no_vis_on_first_frame = m['no_vis_on_first_frame']
+        self.frustum_feature_selection = m['frustum_feature_selection']
+        self.keyframe_selection_method = m['keyframe_selection_method']
+        self.save_selected_keyframes_info = m['save_selected_keyframes_info']
+        if self.save_selected_keyframes_info:
+            self.selected_keyframes = {}
+        if self.nice and coarse_mapper:
+            self.keyframe_selection_method = 'global'
+        self.keyframe_dict = []
+        self.keyframe_list = []
+        # optional iterator of pixel-index tensors replacing the torch.randint draws of
+        # get_samples (common.py:99), one per frame per iteration: lets a test share the draws
+        self.index_source = None
+        self.H, self.W, self.fx, self.fy, self.cx, self.cy = slam.H, slam.W, slam.fx, slam.fy, slam.cx, slam.cy
+
+    # ---- callers of the hot path, once per mapped frame ------------------------------------
+    def _project(self, points, c2w):
+        """world points [P,3] -> pixel uv [P,2], camera z [P] (Mapper.py:129-146,256-271)."""
+        c2w = c2w.detach().to(points.device).double()
+        if c2w.shape[0] == 3:
+            c2w = torch.cat([c2w, torch.tensor([[0, 0, 0, 1.]], dtype=torch.float64, device=points.device)], 0)
+        w2c = torch.linalg.inv(c2w)
+        cam = points.double() @ w2c[:3, :3].T + w2c[:3, 3]
+        x, y, z = -cam[:, 0], cam[:, 1], cam[:, 2]
+        zz = z + 1e-5
+        u = (self.fx * x + self.cx * z) / zz
+        v = (self.fy * y + self.cy * z) / zz
+        return torch.stack([u, v], -1).float(), zz
+
+    def get_mask_from_c2w(self, c2w, key, val_shape, depth_np):
+        """Frustum feature selection (Mapper.py:100-187): boolean mask [X,Y,Z] of the voxels of
+        grid ``key`` seen by the current frame.  ``depth_np`` may be a numpy array or a tensor.
+        Depth is looked up bilinearly (the reference uses cv2.remap INTER_LINEAR, whose 5-bit
+        fixed-point weights differ in the last bits)."""
+        dev = self.device
+        if key == 'grid_coarse':
+            return np.ones(tuple(val_shape)[::-1]).astype(bool)
+        b = torch.as_tensor(self.bound, dtype=torch.float32)
+        X, Y, Z = torch.meshgrid(torch.linspace(float(b[0][0]), float(b[0][1]), val_shape[2]),
+                                 torch.linspace(float(b[1][0]), float(b[1][1]), val_shape[1]),
+                                 torch.linspace(float(b[2][0]), float(b[2][1]), val_shape[0]), indexing='ij')
+        points = torch.stack([X, Y, Z], dim=-1).reshape(-1, 3).to(dev)
+        depth = torch.as_tensor(depth_np, dtype=torch.float32, device=dev)
+        uv, z = self._project(points, c2w)
+        H, W = self.H, self.W
+        x0 = torch.floor(uv[:, 0])
+        y0 = torch.floor(uv[:, 1])
+        wx, wy = uv[:, 0] - x0, uv[:, 1] - y0
+
+        def tap(xi, yi):        # BORDER_CONSTANT 0 outside the image, as cv2.remap defaults to
+            ok = (xi >= 0) & (xi < W) & (yi >= 0) & (yi < H)
+            v = depth[yi.clamp(0, H - 1).long(), xi.clamp(0, W - 1).long()]
+            return torch.where(ok, v, torch.zeros_like(v))
+        depths = (tap(x0, y0) * (1 - wx) * (1 - wy) + tap(x0 + 1, y0) * wx * (1 - wy) +
+                  tap(x0, y0 + 1) * (1 - wx) * wy + tap(x0 + 1, y0 + 1) * wx * wy)
+        mask = (uv[:, 0] < W) & (uv[:, 0] > 0) & (uv[:, 1] < H) & (uv[:, 1] > 0)
+        depths = torch.where(depths == 0, depths.max(), depths)
+        mask = mask & (0 <= -z) & (-z <= depths.double() + 0.5)
+        ray_o = c2w[:3, 3].detach().to(dev).float()
+        mask = mask | (((points - ray_o) ** 2).sum(1) < 0.25)
+        return mask.reshape(val_shape[2], val_shape[1], val_shape[0]).cpu().numpy()
+
+    def keyframe_selection_overlap(self, gt_color, gt_depth, c2w, keyframe_dict, k, N_samples=16, pixels=100):
+        """Keyframes whose view overlaps the current frame (Mapper.py:189-293)."""
+        device = self.device
+        H, W, fx, fy, cx, cy = self.H, self.W, self.fx, self.fy, self.cx, self.cy
+        rays_o, rays_d, gt_depth, gt_color = get_samples(
+            0, H, 0, W, pixels, H, W, fx, fy, cx, cy, c2w, gt_depth.to(device), gt_color.to(device), device)
+        gt_depth = gt_depth.reshape(-1, 1).repeat(1, N_samples)
+        t_vals = torch.linspace(0., 1., steps=N_samples).to(device)
+        z_vals = gt_depth * 0.8 * (1. - t_vals) + (gt_depth + 0.5) * t_vals
+        pts = (rays_o[..., None, :] + rays_d[..., None, :] * z_vals[..., :, None]).reshape(-1, 3).detach()
+        list_keyframe = []
+        edge = 20
+        for keyframeid, keyframe in enumerate(keyframe_dict):
+            uv, z = self._project(pts, keyframe['est_c2w'])
+            mask = (uv[:, 0] < W - edge) & (uv[:, 0] > edge) & (uv[:, 1] < H - edge) & (uv[:, 1] > edge) & (z < 0)
+            list_keyframe.append({'id': keyframeid, 'percent_inside': float(mask.sum()) / uv.shape[0]})
+        list_keyframe = sorted(list_keyframe, key=lambda i: i['percent_inside'], reverse=True)
+        selected = [dic['id'] for dic in list_keyframe if dic['percent_inside'] > 0.00]
+        return list(np.random.permutation(np.array(selected))[:k])
+
+    # ---- the mapping optimisation ----------------------------------------------------------
+    def optimize_map(self, num_joint_iters, lr_factor, idx, cur_gt_color, cur_gt_depth, gt_cur_c2w,
+                     keyframe_dict, keyframe_list, cur_c2w):
+        """Mapping iterations: sample pixels from the selected keyframes, optimise the scene
+        representation (and the camera poses under local BA) (Mapper.py:295-669).
+        Returns the updated cur_c2w when BA ran, else None."""
+        H, W, fx, fy, cx, cy = self.H, self.W, self.fx, self.fy, self.cx, self.cy
+        c = self.c
+        cfg = self.cfg
+        device = self.device
+        bottom = torch.tensor([[0, 0, 0, 1.]], dtype=torch.float32, device=device)
+        if len(keyframe_dict) == 0:
+            optimize_frame = []
+        else:
+            num = self.mapping_window_size - 2
+            if self.keyframe_selection_method == 'global':
+                optimize_frame = random_select(len(self.keyframe_dict) - 1, num)
+            else:
+                optimize_frame = self.keyframe_selection_overlap(
+                    cur_gt_color, cur_gt_depth, cur_c2w, keyframe_dict[:-1], num)
+        oldest_frame = None
+        if len(keyframe_list) > 0:
+            optimize_frame = optimize_frame + [len(keyframe_list) - 1]
+            oldest_frame = min(optimize_frame)
+        optimize_frame += [-1]
+        if self.save_selected_keyframes_info:
+            info = []
+            for frame in optimize_frame:
+                if frame != -1:
+                    info.append({'idx': keyframe_list[frame], 'gt_c2w': keyframe_dict[frame]['gt_c2w'],
+                                 'est_c2w': keyframe_dict[frame]['est_c2w']})
+                else:
+                    info.append({'idx': idx, 'gt_c2w': gt_cur_c2w, 'est_c2w': cur_c2w})
+            self.selected_keyframes[idx] = info
+        pixs_per_image = self.mapping_pixels // len(optimize_frame)
+
+        decoders_para_list = []
+        grid_para = {'grid_coarse': [], 'grid_middle': [], 'grid_fine': [], 'grid_color': []}
+        if self.nice:
+            if self.frustum_feature_selection:
+                masked_c_grad = {}
+                mask_c2w = cur_c2w
+            for key, val in c.items():
+                val = val.to(device)
+                if val.dim() == 5:     # the kernels' layout; logical shape unchanged
+                    val = val.contiguous(memory_format=torch.channels_last_3d)
+                if not self.frustum_feature_selection:
+                    val = val.detach().requires_grad_(True)
+                    c[key] = val
+                    grid_para[key].append(val)
+                else:
+                    mask = self.get_mask_from_c2w(mask_c2w, key, val.shape[2:], cur_gt_depth)
+                    mask = torch.from_numpy(mask).permute(2, 1, 0).unsqueeze(0).unsqueeze(0).repeat(
+                        1, val.shape[1], 1, 1, 1).to(device)
+                    c[key] = val
+                    val_grad = val[mask].clone().detach().requires_grad_(True)
+                    masked_c_grad[key] = val_grad
+                    masked_c_grad[key + 'mask'] = mask
+                    grid_para[key].append(val_grad)
+            if not self.fix_fine:
+                decoders_para_list += list(self.decoders.fine_decoder.parameters())
+            if not self.fix_color:
+                decoders_para_list += list(self.decoders.color_decoder.parameters())
+        else:
+            decoders_para_list += list(self.decoders.parameters())
+        # only parameters an optimiser group owns need a gradient (the reference lets autograd
+        # compute the others and drops them)
+        wanted = {id(p) for p in decoders_para_list}
+        for p in self.decoders.parameters():
+            p.requires_grad_(id(p) in wanted)
+
+        camera_tensor_list, gt_camera_tensor_list = [], []
+        if self.BA:
+            for frame in optimize_frame:
+                if frame != oldest_frame:
+                    if frame != -1:
+                        c2w, gt_c2w = keyframe_dict[frame]['est_c2w'], keyframe_dict[frame]['gt_c2w']
+                    else:
+                        c2w, gt_c2w = cur_c2w, gt_cur_c2w
+                    camera_tensor = get_tensor_from_camera(c2w).to(device).requires_grad_(True)
+                    camera_tensor_list.append(camera_tensor)
+                    gt_camera_tensor_list.append(get_tensor_from_camera(gt_c2w))
+        if self.nice:
+            groups = [{'params': decoders_para_list, 'lr': 0},
+                      {'params': grid_para['grid_coarse'], 'lr': 0},
+                      {'params': grid_para['grid_middle'], 'lr': 0},
+                      {'params': grid_para['grid_fine'], 'lr': 0},
+                      {'params': grid_para['grid_color'], 'lr': 0}]
+            if self.BA:
+                groups.append({'params': camera_tensor_list, 'lr': 0})
+            optimizer = torch.optim.Adam(groups)
+        else:
+            groups = [{'params': decoders_para_list, 'lr': 0}]
+            if self.BA:
+                groups.append({'params': camera_tensor_list, 'lr': 0})
+            optimizer = torch.optim.Adam(groups)
+            from torch.optim.lr_scheduler import StepLR
+            scheduler = StepLR(optimizer, step_size=200, gamma=0.8)
+
+        for joint_iter in range(num_joint_iters):
+            if self.nice:
+                if self.frustum_feature_selection:
+                    for key, val in c.items():
+                        if (self.coarse_mapper and 'coarse' in key) or \
+                                ((not self.coarse_mapper) and ('coarse' not in key)):
+                            val_grad = masked_c_grad[key]
+                            mask = masked_c_grad[key + 'mask']
+                            val = val.to(device)
+                            val[mask] = val_grad
+                            c[key] = val
+                if self.coarse_mapper:
+                    self.stage = 'coarse'
+                elif joint_iter <= int(num_joint_iters * self.middle_iter_ratio):
+                    self.stage = 'middle'
+                elif joint_iter <= int(num_joint_iters * self.fine_iter_ratio):
+                    self.stage = 'fine'
+                else:
+                    self.stage = 'color'
+                st = cfg['mapping']['stage'][self.stage]
+                optimizer.param_groups[0]['lr'] = st['decoders_lr'] * lr_factor
+                optimizer.param_groups[1]['lr'] = st['coarse_lr'] * lr_factor
+                optimizer.param_groups[2]['lr'] = st['middle_lr'] * lr_factor
+                optimizer.param_groups[3]['lr'] = st['fine_lr'] * lr_factor
+                optimizer.param_groups[4]['lr'] = st['color_lr'] * lr_factor
+                if self.BA and self.stage == 'color':
+                    optimizer.param_groups[5]['lr'] = self.BA_cam_lr
+            else:
+                self.stage = 'color'
+                optimizer.param_groups[0]['lr'] = cfg['mapping']['imap_decoders_lr']
+                if self.BA:
+                    optimizer.param_groups[1]['lr'] = self.BA_cam_lr
+
+            optimizer.zero_grad()
+            ro_l, rd_l, gd_l, gc_l = [], [], [], []
+            camera_tensor_id = 0
+            for frame in optimize_frame:
+                if frame != -1:
+                    gt_depth = keyframe_dict[frame]['depth'].to(device)
+                    gt_color = keyframe_dict[frame]['color'].to(device)
+                    if self.BA and frame != oldest_frame:
+                        camera_tensor = camera_tensor_list[camera_tensor_id]
+                        camera_tensor_id += 1
+                        c2w = get_camera_from_tensor(camera_tensor)
+                    else:
+                        c2w = keyframe_dict[frame]['est_c2w']
+                else:
+                    gt_depth = cur_gt_depth.to(device)
+                    gt_color = cur_gt_color.to(device)
+                    if self.BA:
+                        camera_tensor = camera_tensor_list[camera_tensor_id]
+                        c2w = get_camera_from_tensor(camera_tensor)
+                    else:
+                        c2w = cur_c2w
+                ro, rd, gd, gc = get_samples(0, H, 0, W, pixs_per_image, H, W, fx, fy, cx, cy, c2w,
+                                             gt_depth, gt_color, self.device,
+                                             indices=None if self.index_source is None else next(self.index_source))
+                ro_l.append(ro.float()), rd_l.append(rd.float()), gd_l.append(gd.float()), gc_l.append(gc.float())
+            batch_rays_d, batch_rays_o = torch.cat(rd_l), torch.cat(ro_l)
+            batch_gt_depth, batch_gt_color = torch.cat(gd_l), torch.cat(gc_l)
+
+            if self.nice:                                     # Mapper.py:580-596
+                with torch.no_grad():
+                    b = torch.as_tensor(self.bound, dtype=torch.float64).to(device)
+                    t = (b.unsqueeze(0) - batch_rays_o.detach().unsqueeze(-1)) / batch_rays_d.detach().unsqueeze(-1)
+                    t, _ = torch.min(torch.max(t, dim=2)[0], dim=1)
+                    inside_mask = t >= batch_gt_depth
+                batch_rays_d = batch_rays_d[inside_mask]
+                batch_rays_o = batch_rays_o[inside_mask]
+                batch_gt_depth = batch_gt_depth[inside_mask]
+                batch_gt_color = batch_gt_color[inside_mask]
+            depth, uncertainty, color = self.renderer.render_batch_ray(
+                c, self.decoders, batch_rays_d, batch_rays_o, device, self.stage,
+                gt_depth=None if self.coarse_mapper else batch_gt_depth)
+            depth_mask = (batch_gt_depth > 0)
+            loss = torch.abs(batch_gt_depth[depth_mask] - depth[depth_mask]).sum()
+            if (not self.nice) or (self.stage == 'color'):
+                loss += self.w_color_loss * torch.abs(batch_gt_color - color).sum()
+            if not self.occupancy:                            # iMAP regulariser, Mapper.py:614-621
+                point_sigma = self.renderer.regulation(
+                    c, self.decoders, batch_rays_d, batch_rays_o, batch_gt_depth, device, self.stage)
+                loss += 0.0005 * torch.abs(point_sigma).sum()
+            loss.backward(retain_graph=False)
+            optimizer.step()
+            if not self.nice:
+                scheduler.step()
+            optimizer.zero_grad()
+
+            if self.nice and self.frustum_feature_selection:  # Mapper.py:633-642
+                for key, val in c.items():
+                    if (self.coarse_mapper and 'coarse' in key) or \
+                            ((not self.coarse_mapper) and ('coarse' not in key)):
+                        val_grad = masked_c_grad[key]
+                        mask = masked_c_grad[key + 'mask']
+                        val = val.detach()
+                        val[mask] = val_grad.clone().detach()
+                        c[key] = val
+
+        if self.BA:                                           # Mapper.py:644-667
+            camera_tensor_id = 0
+            for frame in optimize_frame:
+                if frame != -1:
+                    if frame != oldest_frame:
+                        c2w = get_camera_from_tensor(camera_tensor_list[camera_tensor_id].detach())
+                        c2w = torch.cat([c2w, bottom], dim=0)
+                        camera_tensor_id += 1
+                        keyframe_dict[frame]['est_c2w'] = c2w.clone()
+                else:
+                    c2w = get_camera_from_tensor(camera_tensor_list[-1].detach())
+                    cur_c2w = torch.cat([c2w, bottom], dim=0).clone()
+            return cur_c2w
+        return None
+
+    def run(self):
+        raise NotImplementedError(
+            "Mapper.run (dataset loop, tracker synchronisation, keyframe bookkeeping, meshing, logging: "
+            "src/Mapper.py:671-806) is outside the render hot path; drive optimize_map from the reference's loop")

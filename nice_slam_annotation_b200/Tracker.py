@@ -1,0 +1,155 @@
+"""Tracker step with the reference's interface (src/Tracker.py): ``optimize_cam_in_batch``
+is the per-iteration hot path (Tracker.py:78-135) and runs on the fused sm_100a kernels.
+
+The frame loop ``run()`` (Tracker.py:151-299: dataset reader, process synchronisation with
+the mapper, visualiser) is a caller of this path and stays with the reference; only the
+state it hands to the step is mirrored here (same attribute names, read from cfg / slam).
+"""
+import copy
+import ctypes as C
+
+import torch
+
+from . import fused
+from ._lib import check, lib
+from .fused import _bound6, _ptr, _stream
+
+
+class _CameraRaysFn(torch.autograd.Function):
+    """get_camera_from_tensor + get_samples + the box pre-filter (common.py:163-176,92-134,
+    Tracker.py:100-107) as ONE kernel; backward is the fused pose gradient
+    (d(rays_o), d(rays_d)) -> d(camera_tensor[7]) (csrc/nsb_composite.cu:k_pose_grad)."""
+
+    @staticmethod
+    def forward(ctx, cam7, indices, crop, intr, depth, color, bound):
+        H0, H1, W0, W1 = crop
+        fx, fy, cx, cy = intr
+        dev = depth.device
+        n = indices.shape[0]
+        cam = cam7.detach().float().contiguous()
+        ro = torch.empty(n, 3, dtype=torch.float32, device=dev)
+        rd = torch.empty(n, 3, dtype=torch.float32, device=dev)
+        gd = torch.empty(n, dtype=torch.float32, device=dev)
+        gc = torch.empty(n, 3, dtype=torch.float32, device=dev)
+        keep = torch.empty(n, dtype=torch.uint8, device=dev)
+        check(lib().nsb_sample_rays(_ptr(indices), n, H0, H1, W0, W1, depth.shape[1], fx, fy, cx, cy, None,
+                                    _ptr(cam), _ptr(depth), _ptr(color), int(color.dtype == torch.float64),
+                                    None if bound is None else _bound6(bound), _ptr(ro), _ptr(rd), _ptr(gd),
+                                    _ptr(gc), _ptr(keep), _stream()), "sample_rays")
+        ctx.save_for_backward(indices, cam)
+        ctx.geom = (crop, intr)
+        ctx.mark_non_differentiable(gd, gc, keep)
+        return ro, rd, gd, gc, keep
+
+    @staticmethod
+    def backward(ctx, g_o, g_d, _a, _b, _c):
+        indices, cam = ctx.saved_tensors
+        (H0, H1, W0, W1), (fx, fy, cx, cy) = ctx.geom
+        n = indices.shape[0]
+        dev = cam.device
+        g_o = torch.zeros(n, 3, device=dev) if g_o is None else g_o.float().contiguous()
+        g_d = torch.zeros(n, 3, device=dev) if g_d is None else g_d.float().contiguous()
+        d_cam = torch.empty(7, dtype=torch.float32, device=dev)
+        check(lib().nsb_pose_grad(_ptr(g_o), _ptr(g_d), _ptr(indices), None, n, H0, W0, W1 - W0, fx, fy, cx, cy,
+                                  _ptr(cam), _ptr(d_cam), _stream()), "pose_grad")
+        return d_cam, None, None, None, None, None, None
+
+
+class Tracker(object):
+    def __init__(self, cfg, args, slam):
+        # Tracker.py:19-76 without the dataset reader / visualiser (callers of the step)
+        self.cfg = cfg
+        self.args = args
+        self.scale = cfg['scale']
+        self.coarse = cfg['coarse']
+        self.occupancy = cfg['occupancy']
+        self.sync_method = cfg.get('sync_method', 'strict')
+        for name in ('idx', 'mesher', 'output', 'verbose', 'shared_c', 'gt_c2w_list', 'low_gpu_mem',
+                     'mapping_idx', 'mapping_cnt', 'shared_decoders', 'estimate_c2w_list'):
+            setattr(self, name, getattr(slam, name, None))
+        self.nice = slam.nice
+        self.bound = slam.bound
+        self.renderer = slam.renderer
+        t = cfg['tracking']
+        self.cam_lr = t['lr']
+        self.device = t['device']
+        self.num_cam_iters = t['iters']
+        self.gt_camera = t['gt_camera']
+        self.tracking_pixels = t['pixels']
+        self.seperate_LR = t['seperate_LR']
+        self.w_color_loss = t['w_color_loss']
+        self.ignore_edge_W = t['ignore_edge_W']
+        self.ignore_edge_H = t['ignore_edge_H']
+        self.handle_dynamic = t['handle_dynamic']
+        self.use_color_in_tracking = t['use_color_in_tracking']
+        self.const_speed_assumption = t['const_speed_assumption']
+        self.every_frame = cfg['mapping']['every_frame']
+        self.no_vis_on_first_frame = cfg['mapping']['no_vis_on_first_frame']
+        self.prev_mapping_idx = -1
+        self.c = {}
+        self.decoders = None
+        self.H, self.W, self.fx, self.fy, self.cx, self.cy = slam.H, slam.W, slam.fx, slam.fy, slam.cx, slam.cy
+
+    def optimize_cam_in_batch(self, camera_tensor, gt_color, gt_depth, batch_size, optimizer, indices=None):
+        """One camera iteration: sample pixels, render depth/colour, loss, backward to the 7-dof
+        camera tensor, optimiser step (Tracker.py:78-135).  Returns the loss value.
+
+        ``indices`` optionally replaces the torch.randint pixel draw (common.py:99)."""
+        device = self.device
+        H, W, fx, fy, cx, cy = self.H, self.W, self.fx, self.fy, self.cx, self.cy
+        optimizer.zero_grad()
+        Wedge, Hedge = self.ignore_edge_W, self.ignore_edge_H
+        H0, H1, W0, W1 = Hedge, H - Hedge, Wedge, W - Wedge
+        gt_depth = gt_depth.to(device)
+        gt_color = gt_color.to(device)
+        if gt_depth.dtype != torch.float32:
+            gt_depth = gt_depth.float()
+        if gt_color.dtype not in (torch.float32, torch.float64):
+            gt_color = gt_color.float()
+        gt_depth, gt_color = gt_depth.contiguous(), gt_color.contiguous()
+        if indices is None:
+            indices = torch.randint((H1 - H0) * (W1 - W0), (batch_size,), device=gt_depth.device)
+        indices = indices.to(gt_depth.device).contiguous()
+        rays_o, rays_d, batch_gt_depth, batch_gt_color, keep = _CameraRaysFn.apply(
+            camera_tensor, indices, (H0, H1, W0, W1), (float(fx), float(fy), float(cx), float(cy)),
+            gt_depth, gt_color, self.bound if self.nice else None)
+        if self.nice:                                        # Tracker.py:100-111
+            inside_mask = keep.bool()
+            rays_d = rays_d[inside_mask]
+            rays_o = rays_o[inside_mask]
+            batch_gt_depth = batch_gt_depth[inside_mask]
+            batch_gt_color = batch_gt_color[inside_mask]
+        depth, uncertainty, color = self.renderer.render_batch_ray(
+            self.c, self.decoders, rays_d, rays_o, self.device, stage='color', gt_depth=batch_gt_depth)
+        uncertainty = uncertainty.detach()
+        if self.handle_dynamic:
+            tmp = torch.abs(batch_gt_depth - depth) / torch.sqrt(uncertainty + 1e-10)
+            mask = (tmp < 10 * tmp.median()) & (batch_gt_depth > 0)
+        else:
+            mask = batch_gt_depth > 0
+        loss = (torch.abs(batch_gt_depth - depth) / torch.sqrt(uncertainty + 1e-10))[mask].sum()
+        if self.use_color_in_tracking:
+            color_loss = torch.abs(batch_gt_color - color)[mask].sum()
+            loss += self.w_color_loss * color_loss
+        loss.backward()
+        optimizer.step()
+        optimizer.zero_grad()
+        return loss.item()
+
+    def update_para_from_mapping(self):
+        """Copy decoders / grids from the mapper's shared state (Tracker.py:137-149).  The copies
+        are detached and parameter gradients are switched off: tracking only needs d(camera)
+        (the reference computes, and discards, the decoder gradients here)."""
+        if self.mapping_idx is None or self.mapping_idx[0] != self.prev_mapping_idx:
+            self.decoders = copy.deepcopy(self.shared_decoders).to(self.device)
+            for p in self.decoders.parameters():
+                p.requires_grad_(False)
+            for key, val in self.shared_c.items():
+                self.c[key] = val.detach().clone().to(self.device)
+            if self.mapping_idx is not None:
+                self.prev_mapping_idx = self.mapping_idx[0].clone()
+
+    def run(self):
+        raise NotImplementedError(
+            "Tracker.run (dataset loop, mapper synchronisation, visualiser: src/Tracker.py:151-299) is "
+            "outside the render hot path; drive optimize_cam_in_batch from the reference's loop")

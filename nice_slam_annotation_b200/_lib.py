@@ -46,7 +46,7 @@ _SIGS = {
     "nsb_layout_offsets": (C.c_int, [C.c_int, c_ptr]),
     "nsb_pack_weights": (C.c_int, [C.c_int, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_sample_rays": (C.c_int, [c_ptr, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
-                                  C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, c_ptr, c_ptr,
+                                  C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, c_ptr, c_ptr, c_ptr,
                                   C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_all_rays": (C.c_int, [C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, c_ptr,
                                c_ptr, c_ptr, c_ptr]),
@@ -55,6 +55,7 @@ _SIGS = {
                                c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_importance_z": (C.c_int, [c_ptr, c_ptr, C.c_int64, C.c_int, C.c_int, c_ptr, C.c_int64, c_ptr,
                                    c_ptr, c_ptr]),
+    "nsb_sample_pdf": (C.c_int, [c_ptr, c_ptr, C.c_int64, C.c_int, C.c_int, c_ptr, C.c_int64, c_ptr, c_ptr]),
     "nsb_decoders_forward": (C.c_int, [C.POINTER(NsbPoints), C.POINTER(NsbScene), C.c_int, c_ptr, c_ptr,
                                        c_ptr, c_ptr]),
     "nsb_assemble_raw": (C.c_int, [C.POINTER(NsbPoints), c_ptr, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr,

@@ -43,8 +43,28 @@ __device__ __forceinline__ double box_exit(const float (&o)[3], const float (&d)
     return far;
 }
 
+// [quat, t] -> 3x4 pose in fp32 with the operation order of quad2rotation (common.py:137-160)
+__device__ __forceinline__ void cam7_to_c2w(const float* __restrict__ q7, float (&m)[12]) {
+    const float qr = q7[0], qi = q7[1], qj = q7[2], qk = q7[3];
+    const float nn = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(qr, qr), __fmul_rn(qi, qi)), __fmul_rn(qj, qj)), __fmul_rn(qk, qk));
+    const float s = __fdiv_rn(2.0f, nn);
+    auto sq = [](float a) { return __fmul_rn(a, a); };
+    auto mm = [](float a, float b) { return __fmul_rn(a, b); };
+    m[0] = __fsub_rn(1.f, mm(s, __fadd_rn(sq(qj), sq(qk))));
+    m[1] = mm(s, __fsub_rn(mm(qi, qj), mm(qk, qr)));
+    m[2] = mm(s, __fadd_rn(mm(qi, qk), mm(qj, qr)));
+    m[4] = mm(s, __fadd_rn(mm(qi, qj), mm(qk, qr)));
+    m[5] = __fsub_rn(1.f, mm(s, __fadd_rn(sq(qi), sq(qk))));
+    m[6] = mm(s, __fsub_rn(mm(qj, qk), mm(qi, qr)));
+    m[8] = mm(s, __fsub_rn(mm(qi, qk), mm(qj, qr)));
+    m[9] = mm(s, __fadd_rn(mm(qj, qk), mm(qi, qr)));
+    m[10] = __fsub_rn(1.f, mm(s, __fadd_rn(sq(qi), sq(qj))));
+    m[3] = q7[4]; m[7] = q7[5]; m[11] = q7[6];
+}
+
 __global__ void k_sample_rays(const int64_t* __restrict__ indices, long long n, int H0, int W0,
-                              int hc, int wc, int W_img, CamDev cam, const float* __restrict__ c2w,
+                              int hc, int wc, int W_img, CamDev cam, const float* __restrict__ c2w_in,
+                              const float* __restrict__ cam7,
                               const float* __restrict__ depth_img, const void* __restrict__ color_img,
                               int color_is_f64, BoundDev bound, int have_bound,
                               float* __restrict__ rays_o, float* __restrict__ rays_d,
@@ -57,6 +77,13 @@ __global__ void k_sample_rays(const int64_t* __restrict__ indices, long long n, 
     idx = idx < 0 ? 0 : (idx >= total ? total - 1 : idx);
     const int pi = W0 + (int)(idx % wc), pj = H0 + (int)(idx / wc);
     float d[3], o[3];
+    float c2w[12];
+    if (cam7) {
+        cam7_to_c2w(cam7, c2w);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) c2w[k] = c2w_in[k];
+    }
     pixel_ray((float)pi, (float)pj, cam, c2w, d);
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
@@ -265,6 +292,41 @@ __global__ void k_importance_z(const double* __restrict__ z, const float* __rest
     }
 }
 
+// sample_pdf (common.py:19-63) as a function of explicit bins [N,M] and weights [N,M-1]
+__global__ void k_sample_pdf(const double* __restrict__ bins, const float* __restrict__ w, long long N,
+                             int M, int Ni, const float* __restrict__ u, long long u_stride,
+                             double* __restrict__ samples) {
+    long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (r >= N) return;
+    const double* br = bins + r * (long long)M;
+    const float* wr = w + r * (long long)(M - 1);
+    const int K = M - 1;
+    float cdf[MAX_LIST];
+    float sum = 0.f;
+    for (int k = 0; k < K; ++k) sum = __fadd_rn(sum, __fadd_rn(wr[k], 1e-5f));
+    cdf[0] = 0.f;
+    float run = 0.f;
+    for (int k = 0; k < K; ++k) {
+        run = __fadd_rn(run, __fdiv_rn(__fadd_rn(wr[k], 1e-5f), sum));
+        cdf[k + 1] = run;
+    }
+    const int L = K + 1;
+    for (int k = 0; k < Ni; ++k) {
+        const float uu = u[r * u_stride + k];
+        int lo = 0, hi = L;
+        while (lo < hi) {
+            int mid = (lo + hi) >> 1;
+            if (cdf[mid] > uu) hi = mid; else lo = mid + 1;
+        }
+        const int below = lo - 1 > 0 ? lo - 1 : 0;
+        const int above = lo < L - 1 ? lo : L - 1;
+        float denom = __fsub_rn(cdf[above], cdf[below]);
+        if (denom < 1e-5f) denom = 1.f;
+        const float t = __fdiv_rn(__fsub_rn(uu, cdf[below]), denom);
+        samples[r * (long long)Ni + k] = __dadd_rn(br[below], __dmul_rn((double)t, __dsub_rn(br[above], br[below])));
+    }
+}
+
 }  // namespace nsb
 
 using namespace nsb;
@@ -273,10 +335,10 @@ static inline unsigned blocks_for(long long n, int bs) { return (unsigned)((n + 
 
 extern "C" int nsb_sample_rays(const int64_t* indices, int64_t n, int H0, int H1, int W0, int W1,
                                int W_img, float fx, float fy, float cx, float cy, const float* c2w,
-                               const float* depth_img, const void* color_img, int color_is_f64,
-                               const double* bound6_host, float* rays_o, float* rays_d,
+                               const float* cam7, const float* depth_img, const void* color_img,
+                               int color_is_f64, const double* bound6_host, float* rays_o, float* rays_d,
                                float* gt_depth, float* gt_color, uint8_t* keep, void* stream) {
-    if (!indices || !c2w || !depth_img || !rays_o || !rays_d) return set_error(NSB_EINVAL, "null argument");
+    if (!indices || (!c2w && !cam7) || !depth_img || !rays_o || !rays_d) return set_error(NSB_EINVAL, "null argument");
     if (gt_color && !color_img) return set_error(NSB_EINVAL, "gt_color requested without an image");
     if (H1 <= H0 || W1 <= W0) return set_error(NSB_EINVAL, "empty crop");
     if (n <= 0) return 0;
@@ -284,7 +346,7 @@ extern "C" int nsb_sample_rays(const int64_t* indices, int64_t n, int H0, int H1
     if (bound6_host) b = to_bound(bound6_host);
     CamDev cam{fx, fy, cx, cy};
     k_sample_rays<<<blocks_for(n, 128), 128, 0, (cudaStream_t)stream>>>(
-        indices, n, H0, W0, H1 - H0, W1 - W0, W_img, cam, c2w, depth_img, color_img, color_is_f64, b,
+        indices, n, H0, W0, H1 - H0, W1 - W0, W_img, cam, c2w, cam7, depth_img, color_img, color_is_f64, b,
         bound6_host != nullptr, rays_o, rays_d, gt_depth, gt_color, keep);
     return check_launch("k_sample_rays");
 }
@@ -333,4 +395,14 @@ extern "C" int nsb_importance_z(const double* z, const float* weights, int64_t N
     k_importance_z<<<blocks_for(N, 64), 64, 0, (cudaStream_t)stream>>>(z, weights, N, S, N_imp, u,
                                                                       u_row_stride, z_samples, z_out);
     return check_launch("k_importance_z");
+}
+
+extern "C" int nsb_sample_pdf(const double* bins, const float* weights, int64_t N, int M, int N_samples,
+                              const float* u, int64_t u_row_stride, double* samples, void* stream) {
+    if (!bins || !weights || !u || !samples) return set_error(NSB_EINVAL, "null argument");
+    if (M < 2 || M > MAX_LIST || N_samples < 1) return set_error(NSB_EINVAL, "bins / N_samples out of range");
+    if (N <= 0) return 0;
+    k_sample_pdf<<<blocks_for(N, 64), 64, 0, (cudaStream_t)stream>>>(bins, weights, N, M, N_samples, u,
+                                                                    u_row_stride, samples);
+    return check_launch("k_sample_pdf");
 }

@@ -167,3 +167,97 @@ def test_trained_scene_vs_reference(gpu, golden, stage):
         if "g_" + k in ref:
             assert_close(g.grad.cpu(), ref["g_" + k], TOL_GRAD, "g_" + k)
     _check_param_grads(dec, ref)
+
+
+# ---- the two SLAM steps through the reference-facing classes -------------------------------------
+def _slam_ns(gpu, d, cfg_over=None):
+    """cfg + the SimpleNamespace NICE_SLAM hands to Renderer / Tracker / Mapper."""
+    import types
+    from nice_slam_annotation_b200.utils.Renderer import Renderer
+    H, W, fx, fy, cx, cy = [float(v) for v in d["cam"]]
+    cfg = {
+        "scale": 1, "coarse": True, "occupancy": True, "sync_method": "strict",
+        "rendering": {"N_samples": 32, "N_surface": 16, "N_importance": 0, "lindisp": False, "perturb": 0.0},
+        "model": {"coarse_bound_enlarge": 2},
+        "tracking": {"lr": 1e-3, "device": gpu.DEV, "iters": 10, "gt_camera": False, "pixels": 150,
+                     "seperate_LR": False, "w_color_loss": 0.5, "ignore_edge_W": 4, "ignore_edge_H": 4,
+                     "handle_dynamic": True, "use_color_in_tracking": True, "const_speed_assumption": True},
+        "mapping": {"device": gpu.DEV, "every_frame": 5, "no_vis_on_first_frame": True, "fix_fine": True,
+                    "BA_cam_lr": 0.001, "fix_color": False, "pixels": 400, "iters": 60, "color_refine": True,
+                    "w_color_loss": 0.2, "keyframe_every": 50, "fine_iter_ratio": 0.6, "middle_iter_ratio": 0.4,
+                    "mapping_window_size": 5, "frustum_feature_selection": False,
+                    "keyframe_selection_method": "overlap", "save_selected_keyframes_info": False,
+                    "stage": {"coarse": {"decoders_lr": 0.0, "coarse_lr": 0.001, "middle_lr": 0.0, "fine_lr": 0.0, "color_lr": 0.0},
+                              "middle": {"decoders_lr": 0.0, "coarse_lr": 0.0, "middle_lr": 0.1, "fine_lr": 0.0, "color_lr": 0.0},
+                              "fine": {"decoders_lr": 0.0, "coarse_lr": 0.0, "middle_lr": 0.005, "fine_lr": 0.005, "color_lr": 0.0},
+                              "color": {"decoders_lr": 0.005, "coarse_lr": 0.0, "middle_lr": 0.005, "fine_lr": 0.005, "color_lr": 0.005}}},
+    }
+    for k, v in (cfg_over or {}).items():
+        cfg[k].update(v)
+    ns = types.SimpleNamespace(nice=True, bound=torch.as_tensor(d["bound"]), H=int(H), W=int(W), fx=fx, fy=fy,
+                               cx=cx, cy=cy)
+    ns.renderer = Renderer(cfg, None, ns)
+    return cfg, ns
+
+
+def test_tracker_iteration_vs_reference(gpu, golden):
+    """Tracker.optimize_cam_in_batch: loss, camera gradient and Adam step against the
+    reference's own step on the same pixel draw (golden 't.*')."""
+    from nice_slam_annotation_b200.Tracker import Tracker
+    d = golden("trained_nice")
+    cfg, ns = _slam_ns(gpu, d)
+    ns.shared_decoders = gpu.nice_from_state(sub(d, "dec."), d["bound"])
+    ns.shared_c = gpu.grids_from(d)
+    tr = Tracker(cfg, None, ns)
+    tr.update_para_from_mapping()
+    cam = torch.as_tensor(d["t.cam0"]).to(gpu.DEV).requires_grad_(True)
+    opt = torch.optim.Adam([cam], lr=1e-3)
+    grads = {}
+    step0 = opt.step
+
+    def spy(*a, **k):
+        grads["g"] = cam.grad.detach().clone()
+        return step0(*a, **k)
+    opt.step = spy
+    depth = torch.as_tensor(d["depth_img"]).to(gpu.DEV)
+    color = torch.as_tensor(d["color_img"]).to(gpu.DEV)
+    loss = tr.optimize_cam_in_batch(cam, color, depth, 150, opt, indices=torch.as_tensor(d["t.indices"]))
+    assert abs(loss - float(d["t.loss"])) <= 1e-4 * abs(float(d["t.loss"])), (loss, float(d["t.loss"]))
+    assert_close(grads["g"].cpu(), d["t.grad"], TOL_GRAD, "camera gradient")
+    assert_close((cam.detach().cpu() - torch.as_tensor(d["t.cam0"])), d["t.cam1"] - d["t.cam0"], 1e-2, "Adam step")
+
+
+def test_mapper_iterations_vs_reference(gpu, golden):
+    """Three Mapper.optimize_map iterations (middle, middle, color schedule of a 3-iteration run)
+    from the trained state reproduce the reference's updated grids and decoders (golden 'm.*')."""
+    from nice_slam_annotation_b200.Mapper import Mapper
+    d = golden("trained_nice")
+    cfg, ns = _slam_ns(gpu, d)
+    ns.shared_decoders = gpu.nice_from_state(sub(d, "dec."), d["bound"])
+    ns.shared_c = gpu.grids_from(d)
+    mp = Mapper(cfg, None, ns)
+    mp.index_source = iter([torch.as_tensor(r) for r in d["m.indices"]])
+    depth = torch.as_tensor(d["depth_img"]).to(gpu.DEV)
+    color = torch.as_tensor(d["color_img"]).to(gpu.DEV)
+    c2w = torch.as_tensor(d["c2w"]).to(gpu.DEV)
+    before = {k: v.detach().clone() for k, v in ns.shared_c.items()}
+    mp.optimize_map(3, 1.0, 5, color, depth, c2w, [], [], c2w)
+    def mostly_close(actual, ref, what, tol=2e-3, frac=0.999):
+        # Adam's first steps are lr * sign(g): an element whose gradient is rounding noise may step
+        # the other way, so require all but a sliver of the elements to agree
+        ref = torch.as_tensor(ref).double()
+        err = (actual.double() - ref).abs()
+        ok = (err <= tol * ref.abs().max()).double().mean().item()
+        assert ok >= frac, f"{what}: only {ok:.5f} of the elements within {tol:g}"
+
+    for k, ref in sub(d, "m.c_after.").items():
+        delta_ref = ref - torch.as_tensor(d["c." + k])
+        delta = (mp.c[k].detach() - before[k]).cpu()
+        if float(delta_ref.abs().max()) == 0.0:
+            assert float(delta.abs().max()) == 0.0, k
+        else:
+            assert torch.equal(delta_ref != 0, delta != 0) or \
+                ((delta_ref != 0) != (delta != 0)).double().mean().item() < 1e-3, "touched voxels differ: " + k
+            mostly_close(mp.c[k].detach().cpu(), ref, "grid after 3 iterations: " + k)
+    for k, ref in sub(d, "m.dec_after.").items():
+        mostly_close(mp.decoders.state_dict()[k].cpu(), ref, "decoder after 3 iterations: " + k, frac=0.99)
