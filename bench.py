@@ -1,0 +1,349 @@
+#!/usr/bin/env python
+"""Benchmark of the render hot path: mapping rays/s, forward + backward, Replica room0 shape.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A *step* is one mapping iteration body (src/Mapper.py:598-624 without the optimiser): render a
+batch of rays at stage ``color`` (32 uniform + 16 surface samples, middle + fine + colour
+decoders), the mapping loss, and the backward pass to the three feature grids and the colour
+decoder.  ``value`` times it with inputs resident in HBM; ``e2e`` times the same step through
+``Renderer.render_batch_ray`` with the ray batch in pinned HOST memory (H2D copies and the D2H
+read of the loss inside the timed region).  ``--impl reference`` times the reference's CPU
+implementation of the same step (the oracle restatement: /root/reference is not on the GPU box)
+on the host cores.  One JSON line on stdout (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+SHAPE = "replica_room0"
+STAGE = "color"
+N_SAMPLES, N_SURFACE = 32, 16
+FRAMES = 5
+# algorithmic bytes (request level: 8 corners x 128 B per level per point)
+BYTES_PER_POINT_BWD = 3 * 1024 + 3 * 2048          # recompute gather of 3 levels + scatter RMW of 3 levels
+BYTES_PER_POINT_FWD = 3 * 1024
+L2_FLUSH_BYTES = 256 << 20
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm = sorted(float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def make_batches(ns, n_rays, n_batches, seed):
+    """Ray batches as Mapper.optimize_map builds them (Mapper.py:543-596): n_rays // FRAMES pixels
+    from each of FRAMES frames, concatenated, pre-filtered against the scene box."""
+    from nice_slam_annotation_b200.common import get_samples
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    out = []
+    b = ns.bound.to(ns.frames[0][1].device)
+    for _ in range(n_batches):
+        parts = []
+        for c2w, depth, color in ns.frames:
+            idx = torch.randint(ns.H * ns.W, (n_rays // len(ns.frames),), generator=g)
+            parts.append(get_samples(0, ns.H, 0, ns.W, idx.numel(), ns.H, ns.W, ns.fx, ns.fy, ns.cx, ns.cy, c2w,
+                                     depth, color, depth.device, indices=idx))
+        ro, rd, gd, gc = (torch.cat([p[i] for p in parts]) for i in range(4))
+        t = (b.unsqueeze(0) - ro.unsqueeze(-1)) / rd.unsqueeze(-1)
+        keep = torch.min(torch.max(t, dim=2)[0], dim=1)[0] >= gd
+        out.append(tuple(x[keep].contiguous() for x in (ro, rd, gd, gc)))
+    return out
+
+
+def make_batches_cpu(ns, n_rays, n_batches, seed):
+    """make_batches on the host through the oracle (reference arm: nothing of the product runs)."""
+    from oracle import nice_oracle as O
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    out = []
+    for _ in range(n_batches):
+        parts = []
+        for c2w, depth, color in ns.frames:
+            idx = torch.randint(ns.H * ns.W, (n_rays // len(ns.frames),), generator=g)
+            parts.append(O.get_samples(0, ns.H, 0, ns.W, idx.numel(), ns.fx, ns.fy, ns.cx, ns.cy, c2w, depth, color, idx))
+        ro, rd, gd, gc = (torch.cat([p[i] for p in parts]) for i in range(4))
+        keep = O.prefilter_mask(ro, rd, gd, ns.bound)
+        out.append(tuple(x[keep].contiguous() for x in (ro, rd, gd, gc)))
+    return out
+
+
+def mapping_loss(depth, color, gd, gc, w_color=0.2):
+    """src/Mapper.py:604-612 at stage color."""
+    m = gd > 0
+    return torch.abs(gd[m] - depth[m]).sum() + w_color * torch.abs(gc - color).sum()
+
+
+# ---------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch.distributed as dist
+    from nice_slam_annotation_b200 import _lib, fused
+    from nice_slam_annotation_b200.scene import build_scene
+    import ctypes as C
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+    L = _lib.lib()
+
+    ns = build_scene(SHAPE, dev, seed=0, n_frames=FRAMES)
+    dec, c = ns.shared_decoders, ns.shared_c
+    # what the mapper optimises at stage color: the three grids and the colour decoder
+    for p in dec.parameters():
+        p.requires_grad_(False)
+    for p in dec.color_decoder.parameters():
+        p.requires_grad_(True)
+    grids = {k: (v.requires_grad_(True) if k != "grid_coarse" else v) for k, v in c.items()}
+    leaves = [grids["grid_middle"], grids["grid_fine"], grids["grid_color"]] + list(dec.color_decoder.parameters())
+    batches = make_batches(ns, args.rays, 8, seed=100 + rank)       # weak scaling: every rank its own rays
+    n_rays = sum(b[0].shape[0] for b in batches) / len(batches)
+    flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.float32, device=dev)
+
+    def allreduce_grads():
+        if world == 1:
+            return
+        flat = torch._utils._flatten_dense_tensors([p.grad.contiguous() if p.grad.dim() != 5 else
+                                                    p.grad.permute(0, 2, 3, 4, 1).contiguous() for p in leaves])
+        dist.all_reduce(flat)      # SUM over ranks: the mapping loss is a sum over rays (Mapper.py:605-612)
+        return flat
+
+    def step_device(b):
+        ro, rd, gd, gc = b
+        depth, _, color = fused.render_batch_ray(grids, dec, rd, ro, STAGE, gd, ns.bound, N_samples=N_SAMPLES,
+                                                 N_surface=N_SURFACE)
+        loss = mapping_loss(depth, color, gd, gc)
+        loss.backward()
+        allreduce_grads()
+        for p in leaves:
+            p.grad = None
+        return loss
+
+    def step_e2e(hb):
+        ro, rd, gd, gc = (x.to(dev, non_blocking=True) for x in hb)
+        depth, _, color = ns.renderer.render_batch_ray(grids, dec, rd, ro, dev, STAGE, gt_depth=gd)
+        loss = mapping_loss(depth, color, gd, gc)
+        loss.backward()
+        allreduce_grads()
+        for p in leaves:
+            p.grad = None
+        return loss.item()                                          # device -> host read of the result
+
+    def timed(fn, items, steps, warmup, after_warmup=None):
+        for i in range(warmup):
+            fn(items[i % len(items)])
+        torch.cuda.synchronize()
+        if after_warmup:
+            after_warmup()
+        if world > 1:
+            dist.barrier()
+        evs = []
+        for i in range(steps):
+            flush.fill_(float(i))                                   # evict the grids from L2, untimed
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn(items[(warmup + i) % len(items)])
+            e1.record()
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms = sum(a.elapsed_time(b) for a, b in evs)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item() / steps
+
+    with ClockSampler(local) as clk:
+        def start_counters():
+            L.nsb_launch_count(1)
+            L.nsb_timing(1)
+        ms_dev = timed(step_device, batches, args.steps, args.warmup, start_counters)
+        launches = L.nsb_launch_count(0)
+        msf, nf, msb, nb = C.c_double(), C.c_int(), C.c_double(), C.c_int()
+        _lib.check(L.nsb_timing_read(C.byref(msf), C.byref(nf), C.byref(msb), C.byref(nb)))
+        L.nsb_timing(0)
+        host_batches = [tuple(x.cpu().pin_memory() for x in b) for b in batches]
+        ms_e2e = timed(step_e2e, host_batches, args.steps, args.warmup)
+    launches_timed = launches
+
+    peaks, peak_src = measured_peaks()
+    S = N_SAMPLES + N_SURFACE
+    pts = n_rays * S
+    bwd_ms = msb.value / max(nb.value, 1)
+    fwd_ms = msf.value / max(nf.value, 1)
+    achieved = BYTES_PER_POINT_BWD * pts / (bwd_ms * 1e-3) / 1e9
+    h2d = sum(x.numel() * x.element_size() for x in host_batches[0])
+    out = {
+        "metric": "mapping rays/s fwd+bwd at Replica shape", "value": world * n_rays / (ms_dev * 1e-3),
+        "unit": "rays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"Replica room0 shape (680x1200) mapping step: {args.rays} rays from {FRAMES} frames "
+                               f"(~{n_rays:.0f} after the box pre-filter) x ({N_SAMPLES} uniform + {N_SURFACE} surface) "
+                               f"samples, stage color (middle+fine+color decoders), fwd + loss + bwd to 3 grids and "
+                               f"the colour decoder; optimiser excluded",
+                   "shape": SHAPE, "rays_per_gpu": args.rays, "samples_per_ray": S, "stage": STAGE,
+                   "grids_mb": sum(v.numel() * 4 for v in c.values()) / 1e6,
+                   "l2": "256 MB buffer written between timed steps (outside the per-step CUDA events)",
+                   "parallelism": f"rays sharded over {world} GPU(s), grids+decoders replicated"
+                                  + (", NCCL all-reduce of grid and decoder gradients inside the step" if world > 1 else "")},
+        "e2e": {"value": world * n_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
+                "api": "Renderer.render_batch_ray + mapping loss + backward, ray batch in pinned host memory"},
+        "gpu_launches": int(launches_timed),
+        "roofline": {"bound": "hbm", "kernel": "k_decoders_backward", "achieved": achieved,
+                     "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
+                     "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)" if peak_src == "measured" else "fallback",
+                     "traffic": args.traffic, "kernel_ms": bwd_ms, "algorithmic_bytes_per_launch": BYTES_PER_POINT_BWD * pts,
+                     "forward_kernel_ms": fwd_ms,
+                     "forward_achieved_gbs": BYTES_PER_POINT_FWD * pts / (fwd_ms * 1e-3) / 1e9},
+        "clocks": clk.summary(),
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(ns, batches, budget_s=20.0)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------
+def oracle_step_fn(ns, batches):
+    """The same step on the CPU through the oracle restatement of the reference's torch code."""
+    from oracle import nice_oracle as O
+    dec = ns.shared_decoders
+    prm = {k: v.detach().cpu().clone() for k, v in dec.state_dict().items()}
+    for k, v in prm.items():
+        v.requires_grad_(k.startswith("color_decoder."))
+    grids = {k: v.detach().cpu().contiguous().clone().requires_grad_(k != "grid_coarse") for k, v in ns.shared_c.items()}
+    bound = ns.bound.cpu()
+    cpu_batches = [tuple(x.cpu() for x in b) for b in batches]
+
+    def step(i):
+        ro, rd, gd, gc = cpu_batches[i % len(cpu_batches)]
+        depth, _, color = O.render_batch_ray(prm, grids, rd, ro, STAGE, gd, bound, N_samples=N_SAMPLES,
+                                             N_surface=N_SURFACE)
+        loss = O.mapping_loss(depth, color, gd, gc)
+        loss.backward()
+        for t in list(prm.values()) + list(grids.values()):
+            t.grad = None
+        return float(loss), ro.shape[0]
+    return step
+
+
+def cpu_baseline(ns, batches, budget_s):
+    step = oracle_step_fn(ns, batches)
+    step(0)                                   # warm-up
+    t0, n, rays = time.perf_counter(), 0, 0
+    while True:
+        _, r = step(n)
+        n += 1
+        rays += r
+        if time.perf_counter() - t0 > budget_s or n >= 10:
+            break
+    dt = time.perf_counter() - t0
+    return {"value": rays / dt, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{n} steps of the same workload (oracle/nice_oracle.py, torch CPU fp32, {dt:.1f} s)"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port) on the host cores, rank 0 only."""
+    if int(os.environ.get("RANK", 0)) != 0:
+        return
+    from nice_slam_annotation_b200.scene import build_scene
+    ns = build_scene(SHAPE, "cpu", seed=0, n_frames=FRAMES)        # host only: no kernel of ours on this arm
+    batches = make_batches_cpu(ns, args.rays, 4, seed=100)
+    step = oracle_step_fn(ns, batches)
+    for i in range(args.warmup):
+        step(i)
+    t0, rays = time.perf_counter(), 0
+    for i in range(args.steps):
+        rays += step(args.warmup + i)[1]
+    dt = time.perf_counter() - t0
+    v = rays / dt
+    S = N_SAMPLES + N_SURFACE
+    out = {"impl": "reference", "metric": "mapping rays/s fwd+bwd at Replica shape", "value": v, "unit": "rays/s",
+           "n_gpus": int(os.environ.get("WORLD_SIZE", 1)), "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f32", "data": "synthetic",
+           "config": {"workload": f"Replica room0 shape (680x1200) mapping step: {args.rays} rays from {FRAMES} frames x "
+                                  f"({N_SAMPLES} uniform + {N_SURFACE} surface) samples, stage color, fwd + loss + bwd "
+                                  f"to 3 grids and the colour decoder; optimiser excluded",
+                      "shape": SHAPE, "rays_per_gpu": args.rays, "samples_per_ray": S, "stage": STAGE},
+           "cpu_baseline": {"value": v, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "port",
+                            "sample": f"{args.steps} full steps ({dt:.1f} s), oracle/nice_oracle.py on torch CPU"},
+           "e2e": {"value": v, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rays", type=int, default=1000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--traffic", type=float, default=None,
+                    help="ncu dram bytes per launch of the dominant kernel (profiles/), reported as roofline.traffic")
+    a = ap.parse_args()
+    a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -89,6 +89,14 @@ typedef struct NsbScene {
 int nsb_version(void);
 const char* nsb_last_error(void);
 
+/* ---- instrumentation (bench.py) -------------------------------------------------------
+ * nsb_launch_count: kernels launched by this library in this process (optionally reset).
+ * nsb_timing(1) brackets every decoder forward / backward kernel with CUDA events on the
+ * launching stream; nsb_timing_read sums their durations (ms) and counts since nsb_timing(). */
+int64_t nsb_launch_count(int reset);
+int nsb_timing(int enable);
+int nsb_timing_read(double* ms_forward, int* n_forward, double* ms_backward, int* n_backward);
+
 /* ---- decoder parameter packing ------------------------------------------------------
  * Canonical parameter order of one decoder (reference state_dict names, decoder.py):
  *   pts_linears.{0..4}.weight, pts_linears.{0..4}.bias, fc_c.{0..4}.weight,

@@ -38,6 +38,9 @@ class NsbScene(C.Structure):
 _SIGS = {
     "nsb_version": (C.c_int, []),
     "nsb_last_error": (C.c_char_p, []),
+    "nsb_launch_count": (C.c_int64, [C.c_int]),
+    "nsb_timing": (C.c_int, [C.c_int]),
+    "nsb_timing_read": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_param_count": (C.c_int, [C.c_int]),
     "nsb_param_numel": (C.c_int64, [C.c_int, C.c_int]),
     "nsb_flat_numel": (C.c_int64, [C.c_int]),

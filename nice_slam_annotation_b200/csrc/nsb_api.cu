@@ -17,10 +17,38 @@ int set_error(int code, const char* fmt, ...) {
     return code;
 }
 
+static long long g_launches = 0;
+
 int check_launch(const char* what) {
+    ++g_launches;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error((int)e, "%s: %s", what, cudaGetErrorString(e));
     return 0;
+}
+
+// ---- optional device-side timing of the two decoder kernels (bench.py roofline) ---------------
+constexpr int TIMING_MAX = 4096;
+static bool g_timing = false;
+static cudaEvent_t g_ev[2][TIMING_MAX][2];
+static int g_ev_created[2] = {0, 0};
+static int g_ev_used[2] = {0, 0};
+
+void timing_mark(int which, int phase, cudaStream_t s) {
+    if (!g_timing) return;
+    int& used = g_ev_used[which];
+    if (phase == 0) {
+        if (used >= TIMING_MAX) return;
+        if (used >= g_ev_created[which]) {
+            if (cudaEventCreate(&g_ev[which][used][0]) != cudaSuccess) return;
+            if (cudaEventCreate(&g_ev[which][used][1]) != cudaSuccess) return;
+            g_ev_created[which] = used + 1;
+        }
+        cudaEventRecord(g_ev[which][used][0], s);
+    } else {
+        if (used >= g_ev_created[which]) return;
+        cudaEventRecord(g_ev[which][used][1], s);
+        ++used;
+    }
 }
 
 // ---- canonical parameters ----------------------------------------------------------------------
@@ -167,6 +195,35 @@ using namespace nsb;
     }
 
 extern "C" int nsb_version(void) { return NSB_VERSION; }
+
+extern "C" int64_t nsb_launch_count(int reset) {
+    long long v = g_launches;
+    if (reset) g_launches = 0;
+    return v;
+}
+
+extern "C" int nsb_timing(int enable) {
+    g_timing = enable != 0;
+    g_ev_used[0] = g_ev_used[1] = 0;
+    return 0;
+}
+
+extern "C" int nsb_timing_read(double* ms_forward, int* n_forward, double* ms_backward, int* n_backward) {
+    double ms[2] = {0.0, 0.0};
+    for (int w = 0; w < 2; ++w)
+        for (int i = 0; i < g_ev_used[w]; ++i) {
+            cudaError_t e = cudaEventSynchronize(g_ev[w][i][1]);
+            float t = 0.f;
+            if (e == cudaSuccess) e = cudaEventElapsedTime(&t, g_ev[w][i][0], g_ev[w][i][1]);
+            if (e != cudaSuccess) return set_error((int)e, "timing: %s", cudaGetErrorString(e));
+            ms[w] += t;
+        }
+    if (ms_forward) *ms_forward = ms[0];
+    if (n_forward) *n_forward = g_ev_used[0];
+    if (ms_backward) *ms_backward = ms[1];
+    if (n_backward) *n_backward = g_ev_used[1];
+    return 0;
+}
 extern "C" const char* nsb_last_error(void) { return g_err; }
 
 extern "C" int nsb_param_count(int kind) {

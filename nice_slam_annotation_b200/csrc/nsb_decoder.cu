@@ -1036,7 +1036,9 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
     sp.flags = 0;
     sp.tile_begin = 0;
     sp.tile_end = (sp.pts.P + 15) / 16;
+    timing_mark(0, 0, (cudaStream_t)stream);
     k_decoders_forward<<<ctas, THREADS, max_blob(sp, false) * 4, (cudaStream_t)stream>>>(sp);
+    timing_mark(0, 1, (cudaStream_t)stream);
     return check_launch("k_decoders_forward");
 }
 
@@ -1099,7 +1101,9 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
     for (long long t0 = 0; t0 < ntiles; t0 += chunk) {
         sp.tile_begin = t0;
         sp.tile_end = t0 + chunk < ntiles ? t0 + chunk : ntiles;
+        timing_mark(1, 0, (cudaStream_t)stream);
         k_decoders_backward<<<ctas, THREADS, smem, (cudaStream_t)stream>>>(sp);
+        timing_mark(1, 1, (cudaStream_t)stream);
         if (int rc = check_launch("k_decoders_backward")) return rc;
         for (int i = 0; i < sp.ntask && ndw; ++i) {
             const DecTask& T = sp.task[i];
