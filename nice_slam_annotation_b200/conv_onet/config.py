@@ -1,22 +1,16 @@
-"""Mirror of src/conv_onet/config.py:4-33 (same keys, same constructor arguments)."""
-from . import models
+"""Decoder factory with the interface of the reference's ``src/conv_onet/config.py:4-33``:
+``get_model(cfg, nice)`` builds the NICE four-level decoder or the single iMAP* MLP from the
+same yaml keys, so ``NICE_SLAM.__init__`` can call it unchanged."""
+from .models import decoder_dict
+
+# iMAP* hyper-parameters are constants of the reference factory, not yaml keys (config.py:29-32)
+_IMAP_KW = dict(c_dim=0, color=True, hidden_size=256, skips=[], n_blocks=4)
 
 
 def get_model(cfg, nice=True):
-    dim = cfg['data']['dim']
-    coarse_grid_len = cfg['grid_len']['coarse']
-    middle_grid_len = cfg['grid_len']['middle']
-    fine_grid_len = cfg['grid_len']['fine']
-    color_grid_len = cfg['grid_len']['color']
-    c_dim = cfg['model']['c_dim']
-    pos_embedding_method = cfg['model']['pos_embedding_method']
-    if nice:
-        decoder = models.decoder_dict['nice'](
-            dim=dim, c_dim=c_dim, coarse=cfg['coarse'], coarse_grid_len=coarse_grid_len,
-            middle_grid_len=middle_grid_len, fine_grid_len=fine_grid_len,
-            color_grid_len=color_grid_len, pos_embedding_method=pos_embedding_method)
-    else:
-        decoder = models.decoder_dict['imap'](
-            dim=dim, c_dim=0, color=True,
-            hidden_size=256, skips=[], n_blocks=4, pos_embedding_method=pos_embedding_method)
-    return decoder
+    embed = cfg['model']['pos_embedding_method']
+    if not nice:
+        return decoder_dict['imap'](dim=cfg['data']['dim'], pos_embedding_method=embed, **_IMAP_KW)
+    lens = {f'{level}_grid_len': cfg['grid_len'][level] for level in ('coarse', 'middle', 'fine', 'color')}
+    return decoder_dict['nice'](dim=cfg['data']['dim'], c_dim=cfg['model']['c_dim'], coarse=cfg['coarse'],
+                                pos_embedding_method=embed, **lens)

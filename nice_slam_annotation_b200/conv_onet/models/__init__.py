@@ -1,7 +1,4 @@
-"""Mirror of src/conv_onet/models/__init__.py:4-7."""
-from . import decoder
+"""Decoder registry, keyed as in the reference (src/conv_onet/models/__init__.py:4-7)."""
+from .decoder import MLP, NICE
 
-decoder_dict = {
-    'nice': decoder.NICE,
-    'imap': decoder.MLP,
-}
+decoder_dict = dict(nice=NICE, imap=MLP)

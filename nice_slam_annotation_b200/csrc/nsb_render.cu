@@ -1,0 +1,265 @@
+// One-call forward / backward of Renderer.render_batch_ray (src/utils/Renderer.py:95-262) for
+// the common case without importance resampling, and the two fused losses of the SLAM steps
+// (src/Mapper.py:604-612, src/Tracker.py:117-130).  These only chain the kernels of the other
+// files on one stream with a caller-provided workspace, so that the host issues two calls per
+// iteration instead of a dozen.
+#include "nsb_common.cuh"
+
+namespace nsb {
+
+struct Carve {
+    char* p;
+    explicit Carve(void* base) : p((char*)(((uintptr_t)base + 255) & ~(uintptr_t)255)) {}
+    template <typename T>
+    T* take(int64_t n) {
+        T* r = (T*)p;
+        p += ((n * (int64_t)sizeof(T) + 255) / 256) * 256;
+        return r;
+    }
+};
+
+struct Ws {
+    float* depth_max;
+    double* z;
+    float *occ0, *occ1, *rgb, *d_raw, *d_point, *d_dnorm;
+};
+
+static Ws carve_ws(void* base, int64_t N, int S) {
+    Carve c(base);
+    Ws w;
+    const int64_t P = N * S;
+    w.depth_max = c.take<float>(64);
+    w.z = c.take<double>(P);
+    w.occ0 = c.take<float>(P);
+    w.occ1 = c.take<float>(P);
+    w.rgb = c.take<float>(4 * P);
+    w.d_raw = c.take<float>(4 * P);
+    w.d_point = c.take<float>(9 * P);
+    w.d_dnorm = c.take<float>(3 * N);
+    return w;
+}
+
+static NsbPoints ray_pts(const NsbRenderCall* r, const double* z, int S) {
+    NsbPoints p{};
+    p.rays_o = r->rays_o; p.rays_d = r->rays_d;
+    p.rays_o_stride = r->rays_o_stride; p.rays_d_stride = r->rays_d_stride;
+    p.z = z; p.N = r->N; p.S = S; p.P = r->N * S;
+    return p;
+}
+
+static void stage_planes(int stage, const Ws& w, float*& o0, float*& o1, float*& rgb) {
+    o0 = w.occ0;
+    o1 = (stage == NSB_STAGE_FINE || stage == NSB_STAGE_COLOR) ? w.occ1 : nullptr;
+    rgb = stage == NSB_STAGE_COLOR ? w.rgb : nullptr;
+}
+
+// ---- losses ----------------------------------------------------------------------------------
+// Mapping: sum_{gt>0} |gt - d| + w * sum |gt_c - c| (Mapper.py:604-612) and its gradient.
+__global__ void k_mapping_loss(const double* __restrict__ depth, const float* __restrict__ color,
+                               const float* __restrict__ gd, const float* __restrict__ gc,
+                               const uint8_t* __restrict__ keep, long long N, float w_color, int use_color,
+                               double* __restrict__ loss, double* __restrict__ g_depth,
+                               float* __restrict__ g_color) {
+    __shared__ double part[32];
+    double acc = 0.0;
+    for (long long i = threadIdx.x; i < N; i += blockDim.x) {
+        const bool live = !keep || keep[i];
+        double gdv = 0.0;
+        if (live && gd[i] > 0.f) {
+            const double diff = (double)gd[i] - depth[i];
+            acc += fabs(diff);
+            gdv = diff > 0 ? -1.0 : (diff < 0 ? 1.0 : 0.0);
+        }
+        g_depth[i] = gdv;
+        for (int c = 0; c < 3; ++c) {
+            float g = 0.f;
+            if (live && use_color) {
+                const float diff = gc[3 * i + c] - color[3 * i + c];
+                acc += (double)(w_color * fabsf(diff));
+                g = diff > 0 ? -w_color : (diff < 0 ? w_color : 0.f);
+            }
+            g_color[3 * i + c] = g;
+        }
+    }
+    for (int s = 16; s > 0; s >>= 1) {
+        int lo = __shfl_xor_sync(FULL, __double2loint(acc), s), hi = __shfl_xor_sync(FULL, __double2hiint(acc), s);
+        acc += __hiloint2double(hi, lo);
+    }
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += part[k];
+        loss[0] = t;
+    }
+}
+
+// Tracking (Tracker.py:117-130): tmp = |gt - d| / sqrt(var + 1e-10); mask = tmp < 10 median(tmp)
+// & gt > 0 (handle_dynamic) or gt > 0; loss = sum_mask tmp + w sum_mask |gt_c - c|.  The median
+// is torch's lower median of the live rays, found by a bitonic sort in shared memory.
+__global__ void k_tracking_loss(const double* __restrict__ depth, const double* __restrict__ var,
+                                const float* __restrict__ color, const float* __restrict__ gd,
+                                const float* __restrict__ gc, const uint8_t* __restrict__ keep, long long N,
+                                int npow2, float w_color, int use_color, int handle_dynamic,
+                                double* __restrict__ loss, double* __restrict__ g_depth,
+                                float* __restrict__ g_color) {
+    extern __shared__ double sh[];      // npow2 doubles
+    __shared__ double part[32];
+    __shared__ int s_live;
+    if (threadIdx.x == 0) s_live = 0;
+    __syncthreads();
+    int live_local = 0;
+    for (long long i = threadIdx.x; i < npow2; i += blockDim.x) {
+        double v = INFINITY;
+        if (i < N && (!keep || keep[i])) {
+            v = fabs((double)gd[i] - depth[i]) / sqrt(var[i] + 1e-10);
+            ++live_local;
+        }
+        sh[i] = v;
+    }
+    atomicAdd(&s_live, live_local);
+    __syncthreads();
+    double thr = INFINITY;
+    if (handle_dynamic) {
+        for (int k = 2; k <= npow2; k <<= 1)
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int i = threadIdx.x; i < npow2; i += blockDim.x) {
+                    const int ixj = i ^ j;
+                    if (ixj > i) {
+                        const bool up = (i & k) == 0;
+                        const double a = sh[i], b = sh[ixj];
+                        // NaN sorts last like torch
+                        const bool gt = (a > b) || (a != a && b == b);
+                        if (gt == up) { sh[i] = b; sh[ixj] = a; }
+                    }
+                }
+                __syncthreads();
+            }
+        const int n_live = s_live;
+        thr = n_live > 0 ? 10.0 * sh[(n_live - 1) / 2] : INFINITY;
+    }
+    __syncthreads();
+    double acc = 0.0;
+    for (long long i = threadIdx.x; i < N; i += blockDim.x) {
+        const bool live = !keep || keep[i];
+        double gdv = 0.0;
+        float gcv[3] = {0.f, 0.f, 0.f};
+        if (live) {
+            const double sd = sqrt(var[i] + 1e-10);
+            const double diff = (double)gd[i] - depth[i];
+            const double tmp = fabs(diff) / sd;
+            const bool m = (handle_dynamic ? tmp < thr : true) && gd[i] > 0.f;
+            if (m) {
+                acc += tmp;
+                gdv = (diff > 0 ? -1.0 : (diff < 0 ? 1.0 : 0.0)) / sd;
+                if (use_color)
+                    for (int c = 0; c < 3; ++c) {
+                        const float dc = gc[3 * i + c] - color[3 * i + c];
+                        acc += (double)w_color * (double)fabsf(dc);
+                        gcv[c] = dc > 0 ? -w_color : (dc < 0 ? w_color : 0.f);
+                    }
+            }
+        }
+        g_depth[i] = gdv;
+        for (int c = 0; c < 3; ++c) g_color[3 * i + c] = gcv[c];
+    }
+    for (int s = 16; s > 0; s >>= 1) {
+        int lo = __shfl_xor_sync(FULL, __double2loint(acc), s), hi = __shfl_xor_sync(FULL, __double2hiint(acc), s);
+        acc += __hiloint2double(hi, lo);
+    }
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += part[k];
+        loss[0] = t;
+    }
+}
+
+}  // namespace nsb
+
+using namespace nsb;
+
+extern "C" int64_t nsb_render_workspace_bytes(int64_t N, int S) {
+    const int64_t P = N * S;
+    // depth_max, z, occ0, occ1, rgb, d_raw, d_point (3 planes), d_dnorm, each rounded to 256 B
+    return 256 * 10 + 256 + P * 8 + P * 4 * 2 + P * 16 * 2 + P * 36 + N * 12;
+}
+
+extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
+    if (!r || !r->rays_o || !r->rays_d || !r->workspace || !r->depth || !r->var || !r->color)
+        return set_error(NSB_EINVAL, "null argument");
+    const int Nf = r->gt_depth ? r->N_surface : 0;
+    const int S = r->N_samples + Nf;
+    if (r->workspace_bytes < nsb_render_workspace_bytes(r->N, S)) return set_error(NSB_EINVAL, "workspace too small");
+    if (r->N <= 0) return 0;
+    Ws w = carve_ws(r->workspace, r->N, S);
+    const double* b6 = &r->scene.bound[0][0];
+    if (r->gt_depth)
+        if (int rc = nsb_depth_max(r->gt_depth, r->keep, r->N, w.depth_max, stream)) return rc;
+    NsbPoints rays = ray_pts(r, nullptr, 0);
+    if (int rc = nsb_sample_z(&rays, r->gt_depth, b6, r->N_samples, Nf, r->lindisp, r->t_uniform, r->t_surface,
+                              r->u, w.depth_max, w.z, stream)) return rc;
+    NsbPoints pts = ray_pts(r, w.z, S);
+    float *o0, *o1, *rgb;
+    stage_planes(r->stage, w, o0, o1, rgb);
+    if (int rc = nsb_decoders_forward(&pts, &r->scene, r->stage, o0, o1, rgb, stream)) return rc;
+    return nsb_composite_forward(&pts, b6, r->stage, r->occupancy, o0, o1, rgb, r->depth, r->var, r->color,
+                                 nullptr, stream);
+}
+
+extern "C" int nsb_render_backward(const NsbRenderCall* r, void* stream) {
+    if (!r || !r->rays_o || !r->rays_d || !r->workspace || !r->depth) return set_error(NSB_EINVAL, "null argument");
+    const int Nf = r->gt_depth ? r->N_surface : 0;
+    const int S = r->N_samples + Nf;
+    if (r->N <= 0) return 0;
+    Ws w = carve_ws(r->workspace, r->N, S);
+    const double* b6 = &r->scene.bound[0][0];
+    NsbPoints pts = ray_pts(r, w.z, S);
+    float *o0, *o1, *rgb;
+    stage_planes(r->stage, w, o0, o1, rgb);
+    const bool want_rays = (r->flags & NSB_GRAD_POINT) != 0;
+    float* dn = (!r->occupancy && want_rays) ? w.d_dnorm : nullptr;
+    if (int rc = nsb_composite_backward(&pts, b6, r->stage, r->occupancy, o0, o1, rgb, r->depth, r->g_depth,
+                                        r->g_var, r->g_color, w.d_raw, dn, stream)) return rc;
+    if (r->flags)
+        if (int rc = nsb_decoders_backward(&pts, &r->scene, r->stage, w.d_raw, r->flags, r->dweight_mask,
+                                           r->d_weight, w.d_point, r->scratch, r->scratch_bytes, stream)) return rc;
+    if (want_rays) {
+        if (!r->g_rays_o || !r->g_rays_d) return set_error(NSB_EINVAL, "ray gradient outputs are NULL");
+        const int ndec = r->stage == NSB_STAGE_COLOR ? 3 : (r->stage == NSB_STAGE_FINE ? 2 : 1);
+        return nsb_ray_grad_reduce(&pts, w.d_point, ndec, dn, r->g_rays_o, r->g_rays_d, stream);
+    }
+    return 0;
+}
+
+extern "C" int nsb_mapping_loss(const double* depth, const float* color, const float* gt_depth,
+                                const float* gt_color, const uint8_t* keep, int64_t N, float w_color,
+                                int use_color, double* loss, double* g_depth, float* g_color, void* stream) {
+    if (!depth || !color || !gt_depth || !gt_color || !loss || !g_depth || !g_color)
+        return set_error(NSB_EINVAL, "null argument");
+    k_mapping_loss<<<1, 1024, 0, (cudaStream_t)stream>>>(depth, color, gt_depth, gt_color, keep, N, w_color,
+                                                       use_color, loss, g_depth, g_color);
+    return check_launch("k_mapping_loss");
+}
+
+extern "C" int nsb_tracking_loss(const double* depth, const double* var, const float* color,
+                                 const float* gt_depth, const float* gt_color, const uint8_t* keep, int64_t N,
+                                 float w_color, int use_color, int handle_dynamic, double* loss,
+                                 double* g_depth, float* g_color, void* stream) {
+    if (!depth || !var || !color || !gt_depth || !gt_color || !loss || !g_depth || !g_color)
+        return set_error(NSB_EINVAL, "null argument");
+    int npow2 = 1;
+    while (npow2 < N) npow2 <<= 1;
+    if (npow2 > 16384) return set_error(NSB_EINVAL, "tracking loss supports up to 16384 rays per batch");
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(k_tracking_loss, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 * 8);
+        if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        attr = true;
+    }
+    k_tracking_loss<<<1, 1024, npow2 * 8, (cudaStream_t)stream>>>(depth, var, color, gt_depth, gt_color, keep, N,
+                                                                npow2, w_color, use_color, handle_dynamic, loss,
+                                                                g_depth, g_color);
+    return check_launch("k_tracking_loss");
+}
