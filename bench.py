@@ -120,18 +120,16 @@ def make_batches_cpu(ns, n_rays, n_batches, seed):
     return out
 
 
-def mapping_loss(depth, color, gd, gc, w_color=0.2):
-    """src/Mapper.py:604-612 at stage color."""
-    m = gd > 0
-    return torch.abs(gd[m] - depth[m]).sum() + w_color * torch.abs(gc - color).sum()
+W_COLOR = 0.2            # mapping w_color_loss (configs/nice_slam.yaml)
 
 
 # ---------------------------------------------------------------------------------------
 def run_ours(args):
+    import ctypes as C
     import torch.distributed as dist
     from nice_slam_annotation_b200 import _lib, fused
     from nice_slam_annotation_b200.scene import build_scene
-    import ctypes as C
+    from nice_slam_annotation_b200.step import FusedStep
 
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -155,34 +153,32 @@ def run_ours(args):
     n_rays = sum(b[0].shape[0] for b in batches) / len(batches)
     flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.float32, device=dev)
 
-    def allreduce_grads():
-        if world == 1:
-            return
-        flat = torch._utils._flatten_dense_tensors([p.grad.contiguous() if p.grad.dim() != 5 else
-                                                    p.grad.permute(0, 2, 3, 4, 1).contiguous() for p in leaves])
-        dist.all_reduce(flat)      # SUM over ranks: the mapping loss is a sum over rays (Mapper.py:605-612)
-        return flat
+    # ---- engine path (value): forward + loss + backward as 3 library calls, CUDA-graph replay,
+    #      gradients in one flat bucket, ONE NCCL all-reduce per step when sharded
+    step = FusedStep(ns.renderer, dec, grids, STAGE, args.rays, loss="mapping", w_color=W_COLOR, use_color=True,
+                     grid_grads=("grid_middle", "grid_fine", "grid_color"), decoder_grads=("color_decoder",))
 
     def step_device(b):
-        ro, rd, gd, gc = b
-        depth, _, color = fused.render_batch_ray(grids, dec, rd, ro, STAGE, gd, ns.bound, N_samples=N_SAMPLES,
-                                                 N_surface=N_SURFACE)
-        loss = mapping_loss(depth, color, gd, gc)
-        loss.backward()
-        allreduce_grads()
-        for p in leaves:
-            p.grad = None
-        return loss
+        step.load(*b)
+        return step.run()
 
+    # ---- API path (e2e): Renderer.render_batch_ray + loss + backward through autograd, host batches
     def step_e2e(hb):
         ro, rd, gd, gc = (x.to(dev, non_blocking=True) for x in hb)
         depth, _, color = ns.renderer.render_batch_ray(grids, dec, rd, ro, dev, STAGE, gt_depth=gd)
-        loss = mapping_loss(depth, color, gd, gc)
+        loss = fused.mapping_loss(depth, color, gd, gc, W_COLOR, use_color=True)
         loss.backward()
-        allreduce_grads()
+        if world > 1:
+            flat = torch.cat([p.grad.reshape(-1) if p.grad.dim() != 5 else p.grad.permute(0, 2, 3, 4, 1).reshape(-1)
+                              for p in leaves])
+            dist.all_reduce(flat)
         for p in leaves:
             p.grad = None
         return loss.item()                                          # device -> host read of the result
+
+    def step_engine_host(hb):
+        step.load(*hb)                                              # pinned host -> static device buffers
+        return step.run().item()
 
     def timed(fn, items, steps, warmup, after_warmup=None):
         for i in range(warmup):
@@ -209,24 +205,36 @@ def run_ours(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t.item() / steps
 
+    def kernel_ms(which):
+        ms, n = C.c_double(), C.c_int()
+        _lib.check(L.nsb_timing_read_kernel(which, C.byref(ms), C.byref(n)))
+        return ms.value / max(n.value, 1), n.value
+
     with ClockSampler(local) as clk:
-        def start_counters():
-            L.nsb_launch_count(1)
+        # (1) per-kernel durations: the same step, un-graphed, CUDA events around the decoder kernels
+        def start_timing():
             L.nsb_timing(1)
-        ms_dev = timed(step_device, batches, args.steps, args.warmup, start_counters)
-        launches = L.nsb_launch_count(0)
-        msf, nf, msb, nb = C.c_double(), C.c_int(), C.c_double(), C.c_int()
-        _lib.check(L.nsb_timing_read(C.byref(msf), C.byref(nf), C.byref(msb), C.byref(nb)))
+        timed(step_device, batches, max(args.steps // 2, 3), args.warmup, start_timing)
+        (fwd_ms, _), (bwd_ms, _), (dw_ms, _) = kernel_ms(0), kernel_ms(1), kernel_ms(2)
         L.nsb_timing(0)
+        # (2) value: graph replay
+        L.nsb_launch_count(1)
+        if not args.no_graph:
+            step.capture()
+        launches_per_step = L.nsb_launch_count(0) if not args.no_graph else None
+        L.nsb_launch_count(1)
+        ms_dev = timed(step_device, batches, args.steps, args.warmup)
+        if launches_per_step is not None:
+            launches = launches_per_step * args.steps               # kernels inside the replayed graph
+        else:
+            launches = int(L.nsb_launch_count(0) * args.steps / (args.steps + args.warmup))
         host_batches = [tuple(x.cpu().pin_memory() for x in b) for b in batches]
         ms_e2e = timed(step_e2e, host_batches, args.steps, args.warmup)
-    launches_timed = launches
+        ms_eng = timed(step_engine_host, host_batches, args.steps, args.warmup)
 
     peaks, peak_src = measured_peaks()
     S = N_SAMPLES + N_SURFACE
-    pts = n_rays * S
-    bwd_ms = msb.value / max(nb.value, 1)
-    fwd_ms = msf.value / max(nf.value, 1)
+    pts = args.rays * S
     achieved = BYTES_PER_POINT_BWD * pts / (bwd_ms * 1e-3) / 1e9
     h2d = sum(x.numel() * x.element_size() for x in host_batches[0])
     out = {
@@ -234,24 +242,30 @@ def run_ours(args):
         "unit": "rays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"Replica room0 shape (680x1200) mapping step: {args.rays} rays from {FRAMES} frames "
-                               f"(~{n_rays:.0f} after the box pre-filter) x ({N_SAMPLES} uniform + {N_SURFACE} surface) "
+                               f"(~{n_rays:.0f} kept by the box pre-filter) x ({N_SAMPLES} uniform + {N_SURFACE} surface) "
                                f"samples, stage color (middle+fine+color decoders), fwd + loss + bwd to 3 grids and "
                                f"the colour decoder; optimiser excluded",
                    "shape": SHAPE, "rays_per_gpu": args.rays, "samples_per_ray": S, "stage": STAGE,
                    "grids_mb": sum(v.numel() * 4 for v in c.values()) / 1e6,
                    "l2": "256 MB buffer written between timed steps (outside the per-step CUDA events)",
+                   "engine": "FusedStep: render forward + loss + render backward as 3 library calls"
+                             + ("" if args.no_graph else ", replayed as one CUDA graph"),
                    "parallelism": f"rays sharded over {world} GPU(s), grids+decoders replicated"
-                                  + (", NCCL all-reduce of grid and decoder gradients inside the step" if world > 1 else "")},
+                                  + (", one NCCL all-reduce of the flat gradient bucket per step" if world > 1 else "")},
         "e2e": {"value": world * n_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
-                "api": "Renderer.render_batch_ray + mapping loss + backward, ray batch in pinned host memory"},
-        "gpu_launches": int(launches_timed),
+                "api": "Renderer.render_batch_ray + mapping loss + backward (autograd), ray batch in pinned host memory"},
+        "e2e_engine": {"value": world * n_rays / (ms_eng * 1e-3), "unit": "rays/s", "ms_per_step": ms_eng,
+                       "api": "FusedStep.load(pinned host batch) + run() + loss.item()"},
+        "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "k_decoders_backward", "achieved": achieved,
                      "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                      "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)" if peak_src == "measured" else "fallback",
                      "traffic": args.traffic, "kernel_ms": bwd_ms, "algorithmic_bytes_per_launch": BYTES_PER_POINT_BWD * pts,
                      "forward_kernel_ms": fwd_ms,
-                     "forward_achieved_gbs": BYTES_PER_POINT_FWD * pts / (fwd_ms * 1e-3) / 1e9},
+                     "forward_achieved_gbs": BYTES_PER_POINT_FWD * pts / (fwd_ms * 1e-3) / 1e9,
+                     "dweight_kernel_ms": dw_ms,
+                     "how": "CUDA events around each launch on the launching stream, un-graphed pass of the same step"},
         "clocks": clk.summary(),
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -339,6 +353,7 @@ if __name__ == "__main__":
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rays", type=int, default=1000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch the engine step kernel by kernel")
     ap.add_argument("--traffic", type=float, default=None,
                     help="ncu dram bytes per launch of the dominant kernel (profiles/), reported as roofline.traffic")
     a = ap.parse_args()

@@ -96,6 +96,8 @@ const char* nsb_last_error(void);
 int64_t nsb_launch_count(int reset);
 int nsb_timing(int enable);
 int nsb_timing_read(double* ms_forward, int* n_forward, double* ms_backward, int* n_backward);
+/* which: 0 k_decoders_forward, 1 k_decoders_backward, 2 k_dweight */
+int nsb_timing_read_kernel(int which, double* ms, int* n);
 
 /* ---- decoder parameter packing ------------------------------------------------------
  * Canonical parameter order of one decoder (reference state_dict names, decoder.py):
@@ -136,8 +138,10 @@ int nsb_sample_rays(const int64_t* indices, int64_t n, int H0, int H1, int W0, i
 int nsb_all_rays(int H, int W, float fx, float fy, float cx, float cy, const float* c2w,
                  float* rays_o, float* rays_d, void* stream);
 
-/* max over the batch of gt_depth (Renderer.py:157,194): out[0] = max(gt), fp32. */
-int nsb_depth_max(const float* gt_depth, int64_t N, float* out, void* stream);
+/* max over the batch of gt_depth (Renderer.py:157,194): out[0] = max(gt), fp32.  keep (optional,
+ * [N] bytes) restricts the max to the rays the box pre-filter kept (the reference compacts the
+ * batch before rendering; a fixed-shape caller passes the mask instead). */
+int nsb_depth_max(const float* gt_depth, const uint8_t* keep, int64_t N, float* out, void* stream);
 
 /* sorted sample depths z[N, N_samples + N_surface] in fp64 (Renderer.py:116-224).
  * gt_depth NULL => near 0.01, far = box exit + 0.01, no surface samples.
@@ -220,6 +224,66 @@ int nsb_ray_grad_reduce(const NsbPoints* rays, const float* d_point, int ndec,
 int nsb_pose_grad(const float* g_rays_o, const float* g_rays_d, const int64_t* indices,
                   const uint8_t* keep, int64_t n, int H0, int W0, int Wc, float fx, float fy,
                   float cx, float cy, const float* cam7, float* d_cam7, void* stream);
+
+/* ---- whole render call ---------------------------------------------------------------------
+ * Renderer.render_batch_ray (src/utils/Renderer.py:95-262) without importance resampling, and
+ * its backward, as ONE host call each: depth max -> sample depths -> decoders -> compositing
+ * (forward), compositing adjoint -> decoders backward (+ weight gradients) -> per-ray reduction
+ * (backward), all queued on `stream`.  The forward keeps z and the decoder planes in
+ * `workspace` (nsb_render_workspace_bytes), which the backward of the same call reads, so the
+ * caller must leave it untouched in between.  `keep` (optional) marks the rays of a fixed-shape
+ * batch that survived the box pre-filter: dropped rays are excluded from the batch depth max;
+ * the caller gives them zero incoming gradient. */
+typedef struct NsbRenderCall {
+    const float* rays_o;
+    const float* rays_d;
+    int64_t rays_o_stride, rays_d_stride;
+    int64_t N;
+    const float* gt_depth;  /* [N] or NULL (coarse stage / no sensor depth) */
+    const uint8_t* keep;    /* [N] or NULL */
+    const float* depth_max; /* [1] or NULL: batch max of gt_depth computed by the caller (a rank that
+                             * renders a shard of the batch passes the max over the WHOLE batch) */
+    int32_t N_samples, N_surface, lindisp, stage, occupancy;
+    const float* t_uniform;  /* [N_samples] torch.linspace(0,1) fp32 */
+    const double* t_surface; /* [N_surface] fp64 */
+    const float* u;          /* [N,N_samples] jitter uniforms or NULL */
+    NsbScene scene;          /* grid[k].grad are the scatter targets of the backward */
+    void* workspace;
+    int64_t workspace_bytes;
+    /* forward outputs */
+    double* depth; /* [N] */
+    double* var;   /* [N] */
+    float* color;  /* [N,3] */
+    /* backward inputs (NULL = zero) and outputs */
+    const double* g_depth;
+    const double* g_var;
+    const float* g_color;
+    uint32_t flags, dweight_mask;
+    float* d_weight[4]; /* flat canonical gradients per decoder kind (accumulated) */
+    void* scratch;      /* weight-gradient records, nsb_dweight_scratch_bytes */
+    int64_t scratch_bytes;
+    float* g_rays_o; /* [N,3] with NSB_GRAD_POINT */
+    float* g_rays_d;
+} NsbRenderCall;
+
+int64_t nsb_render_workspace_bytes(int64_t N, int S);
+int nsb_render_forward(const NsbRenderCall* call, void* stream);
+int nsb_render_backward(const NsbRenderCall* call, void* stream);
+
+/* ---- losses of the two SLAM steps, value and gradient in one kernel --------------------------
+ * mapping (src/Mapper.py:604-612): loss = sum_{gt>0} |gt - depth| + w_color sum |gt_c - color|
+ * (colour term when use_color).  tracking (src/Tracker.py:113-130): tmp = |gt - depth| /
+ * sqrt(var + 1e-10); mask = gt > 0 (& tmp < 10 median(tmp) when handle_dynamic); loss =
+ * sum_mask tmp + w_color sum_mask |gt_c - color|.  Outputs: loss[0] fp64, g_depth [N] fp64,
+ * g_color [N,3] fp32 (d loss / d depth, d loss / d color; var is detached as in the reference).
+ * keep (optional) drops rays of a fixed-shape batch. */
+int nsb_mapping_loss(const double* depth, const float* color, const float* gt_depth,
+                     const float* gt_color, const uint8_t* keep, int64_t N, float w_color,
+                     int use_color, double* loss, double* g_depth, float* g_color, void* stream);
+int nsb_tracking_loss(const double* depth, const double* var, const float* color,
+                      const float* gt_depth, const float* gt_color, const uint8_t* keep, int64_t N,
+                      float w_color, int use_color, int handle_dynamic, double* loss,
+                      double* g_depth, float* g_color, void* stream);
 
 #ifdef __cplusplus
 }

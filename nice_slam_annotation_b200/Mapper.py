@@ -14,6 +14,7 @@ device (SURVEY.md 8f-2 marks them "next"; they are not kernels yet).  The frame 
 import numpy as np
 import torch
 
+from . import fused
 from .common import get_camera_from_tensor, get_samples, get_tensor_from_camera, random_select
 
 
@@ -292,23 +293,25 @@ class Mapper(object):
             batch_rays_d, batch_rays_o = torch.cat(rd_l), torch.cat(ro_l)
             batch_gt_depth, batch_gt_color = torch.cat(gd_l), torch.cat(gc_l)
 
+            keep = None
             if self.nice:                                     # Mapper.py:580-596
+                # the reference compacts the batch with boolean indexing (a host sync per
+                # iteration); the fused path keeps the shape and passes the mask to the kernels
                 with torch.no_grad():
                     b = torch.as_tensor(self.bound, dtype=torch.float64).to(device)
                     t = (b.unsqueeze(0) - batch_rays_o.detach().unsqueeze(-1)) / batch_rays_d.detach().unsqueeze(-1)
                     t, _ = torch.min(torch.max(t, dim=2)[0], dim=1)
-                    inside_mask = t >= batch_gt_depth
-                batch_rays_d = batch_rays_d[inside_mask]
-                batch_rays_o = batch_rays_o[inside_mask]
-                batch_gt_depth = batch_gt_depth[inside_mask]
-                batch_gt_color = batch_gt_color[inside_mask]
+                    keep = (t >= batch_gt_depth).to(torch.uint8)
+            if keep is not None and not self.renderer.fixed_shape_ok():
+                m = keep.bool()
+                batch_rays_d, batch_rays_o = batch_rays_d[m], batch_rays_o[m]
+                batch_gt_depth, batch_gt_color = batch_gt_depth[m], batch_gt_color[m]
+                keep = None
             depth, uncertainty, color = self.renderer.render_batch_ray(
                 c, self.decoders, batch_rays_d, batch_rays_o, device, self.stage,
-                gt_depth=None if self.coarse_mapper else batch_gt_depth)
-            depth_mask = (batch_gt_depth > 0)
-            loss = torch.abs(batch_gt_depth[depth_mask] - depth[depth_mask]).sum()
-            if (not self.nice) or (self.stage == 'color'):
-                loss += self.w_color_loss * torch.abs(batch_gt_color - color).sum()
+                gt_depth=None if self.coarse_mapper else batch_gt_depth, keep=keep)
+            loss = fused.mapping_loss(depth, color, batch_gt_depth, batch_gt_color, self.w_color_loss,
+                                      use_color=(not self.nice) or (self.stage == 'color'), keep=keep)
             if not self.occupancy:                            # iMAP regulariser, Mapper.py:614-621
                 point_sigma = self.renderer.regulation(
                     c, self.decoders, batch_rays_d, batch_rays_o, batch_gt_depth, device, self.stage)

@@ -113,24 +113,21 @@ class Tracker(object):
         rays_o, rays_d, batch_gt_depth, batch_gt_color, keep = _CameraRaysFn.apply(
             camera_tensor, indices, (H0, H1, W0, W1), (float(fx), float(fy), float(cx), float(cy)),
             gt_depth, gt_color, self.bound if self.nice else None)
-        if self.nice:                                        # Tracker.py:100-111
+        # Tracker.py:100-111 drops the rays that leave the scene box before their sensor depth by
+        # boolean indexing (a device->host sync per iteration); the fused path keeps the batch
+        # shape and hands the mask to the kernels instead: dropped rays are excluded from the
+        # batch depth max, the median and the loss, so every value is the same.
+        if not self.nice:
+            keep = None
+        elif not self.renderer.fixed_shape_ok():
             inside_mask = keep.bool()
-            rays_d = rays_d[inside_mask]
-            rays_o = rays_o[inside_mask]
-            batch_gt_depth = batch_gt_depth[inside_mask]
-            batch_gt_color = batch_gt_color[inside_mask]
+            rays_d, rays_o = rays_d[inside_mask], rays_o[inside_mask]
+            batch_gt_depth, batch_gt_color = batch_gt_depth[inside_mask], batch_gt_color[inside_mask]
+            keep = None
         depth, uncertainty, color = self.renderer.render_batch_ray(
-            self.c, self.decoders, rays_d, rays_o, self.device, stage='color', gt_depth=batch_gt_depth)
-        uncertainty = uncertainty.detach()
-        if self.handle_dynamic:
-            tmp = torch.abs(batch_gt_depth - depth) / torch.sqrt(uncertainty + 1e-10)
-            mask = (tmp < 10 * tmp.median()) & (batch_gt_depth > 0)
-        else:
-            mask = batch_gt_depth > 0
-        loss = (torch.abs(batch_gt_depth - depth) / torch.sqrt(uncertainty + 1e-10))[mask].sum()
-        if self.use_color_in_tracking:
-            color_loss = torch.abs(batch_gt_color - color)[mask].sum()
-            loss += self.w_color_loss * color_loss
+            self.c, self.decoders, rays_d, rays_o, self.device, stage='color', gt_depth=batch_gt_depth, keep=keep)
+        loss = fused.tracking_loss(depth, uncertainty, color, batch_gt_depth, batch_gt_color,
+                                   self.w_color_loss, self.use_color_in_tracking, self.handle_dynamic, keep=keep)
         loss.backward()
         optimizer.step()
         optimizer.zero_grad()

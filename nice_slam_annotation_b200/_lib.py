@@ -35,12 +35,26 @@ class NsbScene(C.Structure):
                 ("grid", NsbGrid * 4), ("packed", c_ptr * 4)]
 
 
+class NsbRenderCall(C.Structure):
+    _fields_ = [("rays_o", c_ptr), ("rays_d", c_ptr), ("rays_o_stride", C.c_int64), ("rays_d_stride", C.c_int64),
+                ("N", C.c_int64), ("gt_depth", c_ptr), ("keep", c_ptr), ("depth_max", c_ptr),
+                ("N_samples", C.c_int32), ("N_surface", C.c_int32), ("lindisp", C.c_int32), ("stage", C.c_int32),
+                ("occupancy", C.c_int32),
+                ("t_uniform", c_ptr), ("t_surface", c_ptr), ("u", c_ptr), ("scene", NsbScene),
+                ("workspace", c_ptr), ("workspace_bytes", C.c_int64),
+                ("depth", c_ptr), ("var", c_ptr), ("color", c_ptr),
+                ("g_depth", c_ptr), ("g_var", c_ptr), ("g_color", c_ptr),
+                ("flags", C.c_uint32), ("dweight_mask", C.c_uint32), ("d_weight", c_ptr * 4),
+                ("scratch", c_ptr), ("scratch_bytes", C.c_int64), ("g_rays_o", c_ptr), ("g_rays_d", c_ptr)]
+
+
 _SIGS = {
     "nsb_version": (C.c_int, []),
     "nsb_last_error": (C.c_char_p, []),
     "nsb_launch_count": (C.c_int64, [C.c_int]),
     "nsb_timing": (C.c_int, [C.c_int]),
     "nsb_timing_read": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr]),
+    "nsb_timing_read_kernel": (C.c_int, [C.c_int, c_ptr, c_ptr]),
     "nsb_param_count": (C.c_int, [C.c_int]),
     "nsb_param_numel": (C.c_int64, [C.c_int, C.c_int]),
     "nsb_flat_numel": (C.c_int64, [C.c_int]),
@@ -53,7 +67,7 @@ _SIGS = {
                                   C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_all_rays": (C.c_int, [C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, c_ptr,
                                c_ptr, c_ptr, c_ptr]),
-    "nsb_depth_max": (C.c_int, [c_ptr, C.c_int64, c_ptr, c_ptr]),
+    "nsb_depth_max": (C.c_int, [c_ptr, c_ptr, C.c_int64, c_ptr, c_ptr]),
     "nsb_sample_z": (C.c_int, [C.POINTER(NsbPoints), c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, c_ptr,
                                c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_importance_z": (C.c_int, [c_ptr, c_ptr, C.c_int64, C.c_int, C.c_int, c_ptr, C.c_int64, c_ptr,
@@ -73,6 +87,13 @@ _SIGS = {
     "nsb_ray_grad_reduce": (C.c_int, [C.POINTER(NsbPoints), c_ptr, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_pose_grad": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_int, C.c_int, C.c_int,
                                 C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, c_ptr, c_ptr]),
+    "nsb_render_workspace_bytes": (C.c_int64, [C.c_int64, C.c_int]),
+    "nsb_render_forward": (C.c_int, [C.POINTER(NsbRenderCall), c_ptr]),
+    "nsb_render_backward": (C.c_int, [C.POINTER(NsbRenderCall), c_ptr]),
+    "nsb_mapping_loss": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_float, C.c_int, c_ptr,
+                                   c_ptr, c_ptr, c_ptr]),
+    "nsb_tracking_loss": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_float, C.c_int,
+                                    C.c_int, c_ptr, c_ptr, c_ptr, c_ptr]),
 }
 
 EXPORTS = tuple(_SIGS)

@@ -29,9 +29,10 @@ int check_launch(const char* what) {
 // ---- optional device-side timing of the two decoder kernels (bench.py roofline) ---------------
 constexpr int TIMING_MAX = 4096;
 static bool g_timing = false;
-static cudaEvent_t g_ev[2][TIMING_MAX][2];
-static int g_ev_created[2] = {0, 0};
-static int g_ev_used[2] = {0, 0};
+constexpr int TIMING_SLOTS = 3;      // 0 decoder forward, 1 decoder backward, 2 weight gradients
+static cudaEvent_t g_ev[TIMING_SLOTS][TIMING_MAX][2];
+static int g_ev_created[TIMING_SLOTS] = {0, 0, 0};
+static int g_ev_used[TIMING_SLOTS] = {0, 0, 0};
 
 void timing_mark(int which, int phase, cudaStream_t s) {
     if (!g_timing) return;
@@ -204,7 +205,22 @@ extern "C" int64_t nsb_launch_count(int reset) {
 
 extern "C" int nsb_timing(int enable) {
     g_timing = enable != 0;
-    g_ev_used[0] = g_ev_used[1] = 0;
+    for (int w = 0; w < TIMING_SLOTS; ++w) g_ev_used[w] = 0;
+    return 0;
+}
+
+extern "C" int nsb_timing_read_kernel(int which, double* ms, int* n) {
+    if (which < 0 || which >= TIMING_SLOTS) return set_error(NSB_EINVAL, "bad timing slot %d", which);
+    double acc = 0.0;
+    for (int i = 0; i < g_ev_used[which]; ++i) {
+        cudaError_t e = cudaEventSynchronize(g_ev[which][i][1]);
+        float t = 0.f;
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&t, g_ev[which][i][0], g_ev[which][i][1]);
+        if (e != cudaSuccess) return set_error((int)e, "timing: %s", cudaGetErrorString(e));
+        acc += t;
+    }
+    if (ms) *ms = acc;
+    if (n) *n = g_ev_used[which];
     return 0;
 }
 

@@ -57,7 +57,30 @@ struct StageParams {
     const float* d_raw;   // backward: [P,4]
     unsigned flags;
     long long tile_begin, tile_end;   // tiles of this launch (backward is chunked for d(W))
+    unsigned* ctr;                    // [4]: next tile of task 0..2 (relative to tile_begin), CTAs done
 };
+
+// Tiles are handed out dynamically: a warp takes the next tile of its CTA's decoder with one
+// atomic (fetched one tile ahead, so the round trip is hidden).  Work per tile is uneven --
+// the backward skips tiles whose incoming gradient is zero -- and a static round-robin left
+// the slowest CTA running for 2x the average (ncu, profiles/r01b).
+__device__ __forceinline__ long long next_tile(unsigned* ctr, int lane) {
+    unsigned v = 0;
+    if (lane == 0) v = atomicAdd(ctr, 1u);
+    return (long long)__shfl_sync(FULL, v, 0);
+}
+// last CTA out re-arms the counters for the next launch that uses this slot
+__device__ __forceinline__ void release_counters(unsigned* ctr) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(ctr + 3, 1u) == gridDim.x - 1) {
+            ctr[0] = 0; ctr[1] = 0; ctr[2] = 0;
+            __threadfence();
+            ctr[3] = 0;
+        }
+    }
+}
 
 // ---- per-thread view of its two points -------------------------------------------------------
 struct Rows {
@@ -325,13 +348,14 @@ struct Off {
     }
 };
 
-// C fragments [4 n-tiles] of a 16 x 32 tile -> dense [16][32] (record section)
+// C fragments [4 n-tiles] of a 16 x 32 tile -> [16][32] record section (rec_sw columns)
 __device__ __forceinline__ void store_c32(float* dst, const float (&acc)[4][4], int lane) {
     const int g = lane >> 2, t = lane & 3;
 #pragma unroll
     for (int n = 0; n < 4; ++n) {
-        *reinterpret_cast<float2*>(dst + g * HID + 8 * n + 2 * t) = make_float2(acc[n][0], acc[n][1]);
-        *reinterpret_cast<float2*>(dst + (g + 8) * HID + 8 * n + 2 * t) = make_float2(acc[n][2], acc[n][3]);
+        const int col = rec_sw(g, 8 * n + 2 * t);          // (g + 8) & 3 == g & 3
+        *reinterpret_cast<float2*>(dst + g * HID + col) = make_float2(acc[n][0], acc[n][1]);
+        *reinterpret_cast<float2*>(dst + (g + 8) * HID + col) = make_float2(acc[n][2], acc[n][3]);
     }
 }
 
@@ -388,14 +412,15 @@ __device__ __forceinline__ void tile_inputs(const PointsDev& q, const DecTask& T
 }
 
 template <int KIND>
-__device__ void decoder_forward_cta(const StageParams& P, const DecTask& T, float* sm) {
+__device__ void decoder_forward_cta(const StageParams& P, const DecTask& T, int task, float* sm) {
     using C = DecCfg<KIND>;
     stage_weights(sm, T.packed, C::FWD_END);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, t = lane & 3;
     float* es = sm + C::FWD_END + warp * E_BUF;
     const long long ntiles = (P.pts.P + 15) / 16;
-    for (long long tile = (long long)(blockIdx.x - T.cta_begin) * WARPS + warp; tile < ntiles;
-         tile += (long long)T.cta_count * WARPS) {
+    unsigned* ctr = P.ctr + task;
+    for (long long tile = next_tile(ctr, lane), nxt; tile < ntiles; tile = nxt) {
+        nxt = next_tile(ctr, lane);
         Rows R;
         float c[C::CS][4];
         tile_inputs<KIND>(P.pts, T, sm, es, tile, lane, R, c);
@@ -423,11 +448,12 @@ k_decoders_forward(const __grid_constant__ StageParams P) {
     while (k + 1 < P.ntask && (int)blockIdx.x >= P.task[k + 1].cta_begin) ++k;
     const DecTask& T = P.task[k];
     switch (T.kind) {
-        case KIND_COARSE: decoder_forward_cta<KIND_COARSE>(P, T, sm); break;
-        case KIND_MIDDLE: decoder_forward_cta<KIND_MIDDLE>(P, T, sm); break;
-        case KIND_FINE: decoder_forward_cta<KIND_FINE>(P, T, sm); break;
-        default: decoder_forward_cta<KIND_COLOR>(P, T, sm); break;
+        case KIND_COARSE: decoder_forward_cta<KIND_COARSE>(P, T, k, sm); break;
+        case KIND_MIDDLE: decoder_forward_cta<KIND_MIDDLE>(P, T, k, sm); break;
+        case KIND_FINE: decoder_forward_cta<KIND_FINE>(P, T, k, sm); break;
+        default: decoder_forward_cta<KIND_COLOR>(P, T, k, sm); break;
     }
+    release_counters(P.ctr);
 }
 
 // ---- backward -------------------------------------------------------------------------------
@@ -435,7 +461,7 @@ k_decoders_forward(const __grid_constant__ StageParams P) {
 // n-tile pairs), consumed on the fly: e = sin(p.B) so d(p_a) += d(e_f) cos(p.B_f) B[a][f].
 __device__ __forceinline__ void embed_grad(const float (&a)[4][4], const float* __restrict__ Ws,
                                            const Rows& R, const float* Bs, int lane, float (&dp)[2][3],
-                                           float* des = nullptr, bool des_add = false) {
+                                           float* des = nullptr) {
     const int t = lane & 3, g = lane >> 2;
     uint32_t ah[4][4], al[4][4];
 #pragma unroll
@@ -467,10 +493,7 @@ __device__ __forceinline__ void embed_grad(const float (&a)[4][4], const float* 
             for (int q = 0; q < 4; ++q) {
                 const int r = q >> 1, f = 8 * (2 * h + nn) + 2 * t + (q & 1);
                 const float v = (nn ? d1[q] : d0[q]) * cosf(phase(R.p[r], Bs, f));
-                if (des) {                      // d(B)[a][f] = sum_points p_a * v  (k_dweight)
-                    float* q_ = des + (g + 8 * r) * EMB_PAD + f;
-                    *q_ = des_add ? *q_ + v : v;
-                }
+                if (des) des[(g + 8 * r) * EMB_PAD + rec_sw(g, f)] = v;   // d(B)[a][f] = sum_points p_a v
                 dp[r][0] = fmaf(v, Bs[f], dp[r][0]);
                 dp[r][1] = fmaf(v, Bs[EMB_PAD + f], dp[r][1]);
                 dp[r][2] = fmaf(v, Bs[2 * EMB_PAD + f], dp[r][2]);
@@ -515,7 +538,7 @@ __device__ __forceinline__ void grid_backward(bool scatter, bool coord, const Gr
 }
 
 template <int KIND>
-__device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, float* sm) {
+__device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, int task, float* sm) {
     using C = DecCfg<KIND>;
     using O = Off<KIND>;
     stage_weights(sm, T.packed, C::TOTAL);
@@ -526,8 +549,9 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, flo
     const bool want_point = (P.flags & NSB_GRAD_POINT) && T.d_point != nullptr;
     using RC = RecCfg<KIND>;
     (void)ntiles;
-    for (long long tile = P.tile_begin + (long long)(blockIdx.x - T.cta_begin) * WARPS + warp; tile < P.tile_end;
-         tile += (long long)T.cta_count * WARPS) {
+    unsigned* ctr = P.ctr + task;
+    for (long long tile = P.tile_begin + next_tile(ctr, lane), nxt; tile < P.tile_end; tile = nxt) {
+        nxt = P.tile_begin + next_tile(ctr, lane);
         float* rec = T.dw_scratch ? T.dw_scratch + (size_t)(tile - P.tile_begin) * RC::REC : nullptr;
         // incoming gradient first: most tiles behind the surface carry exact zeros
         float dA[1][4];
@@ -572,16 +596,16 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, flo
 #pragma unroll 1
                     for (int j = 0; j < E_SLABS; ++j) {
                         const int f0 = 8 * j + t, f1 = f0 + 4;
-                        rec[RC::R_E + g * EMB_PAD + f0] = es[esw(g, f0)];
-                        rec[RC::R_E + (g + 8) * EMB_PAD + f0] = es[esw(g + 8, f0)];
-                        rec[RC::R_E + g * EMB_PAD + f1] = es[esw(g, f1)];
-                        rec[RC::R_E + (g + 8) * EMB_PAD + f1] = es[esw(g + 8, f1)];
+                        rec[RC::R_E + g * EMB_PAD + rec_sw(g, f0)] = es[esw(g, f0)];
+                        rec[RC::R_E + (g + 8) * EMB_PAD + rec_sw(g, f0)] = es[esw(g + 8, f0)];
+                        rec[RC::R_E + g * EMB_PAD + rec_sw(g, f1)] = es[esw(g, f1)];
+                        rec[RC::R_E + (g + 8) * EMB_PAD + rec_sw(g, f1)] = es[esw(g + 8, f1)];
                     }
                 }
 #pragma unroll
                 for (int L = 0; L < C::CS / 4; ++L) {       // channels 8t..8t+7 of grid level L
-                    float* c0 = rec + RC::R_C + g * C::C_IN + 32 * L + 8 * t;
-                    float* c1 = rec + RC::R_C + (g + 8) * C::C_IN + 32 * L + 8 * t;
+                    float* c0 = rec + RC::R_C + g * C::C_IN + rec_sw(g, 32 * L + 8 * t);
+                    float* c1 = rec + RC::R_C + (g + 8) * C::C_IN + rec_sw(g, 32 * L + 8 * t);
                     const int j0 = 4 * L;
                     *reinterpret_cast<float4*>(c0) = make_float4(c[j0][0], c[j0][2], c[j0 + 1][0], c[j0 + 1][2]);
                     *reinterpret_cast<float4*>(c0 + 4) = make_float4(c[j0 + 2][0], c[j0 + 2][2], c[j0 + 3][0], c[j0 + 3][2]);
@@ -605,7 +629,9 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, flo
                         d0[o] = __shfl_sync(FULL, dA[0][0], (lane & ~3) | o);
                         d1[o] = __shfl_sync(FULL, dA[0][1], (lane & ~3) | o);
                     }
-                    float* o0 = rec + RC::R_DO + g * HID + 8 * t, * o1 = rec + RC::R_DO + (g + 8) * HID + 8 * t;
+                    // logical columns 8t..8t+7 of the row; the row's data (cols 0..3) is lane t == 0's
+                    float* o0 = rec + RC::R_DO + g * HID + rec_sw(g, 8 * t);
+                    float* o1 = rec + RC::R_DO + (g + 8) * HID + rec_sw(g, 8 * t);
                     const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
                     *reinterpret_cast<float4*>(o0) = t == 0 ? make_float4(d0[0], d0[1], d0[2], d0[3]) : z4;
                     *reinterpret_cast<float4*>(o1) = t == 0 ? make_float4(d1[0], d1[1], d1[2], d1[3]) : z4;
@@ -633,7 +659,7 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, flo
                 if constexpr (C::EMBED) {
                     if (want_point || rec)
                         embed_grad(a, sm + O::TX(i), R, sm + C::OFF_B, lane, dp,
-                                   rec ? rec + RC::R_DE : nullptr, i == 0);
+                                   rec ? rec + (i == 3 ? RC::R_DE : RC::R_DE0) : nullptr);
                 } else {
                     gemm3<4, 4>(dc, a, sm + O::TX(i), lane);
                 }
@@ -678,40 +704,45 @@ k_decoders_backward(const __grid_constant__ StageParams P) {
     while (k + 1 < P.ntask && (int)blockIdx.x >= P.task[k + 1].cta_begin) ++k;
     const DecTask& T = P.task[k];
     switch (T.kind) {
-        case KIND_COARSE: decoder_backward_cta<KIND_COARSE>(P, T, sm); break;
-        case KIND_MIDDLE: decoder_backward_cta<KIND_MIDDLE>(P, T, sm); break;
-        case KIND_FINE: decoder_backward_cta<KIND_FINE>(P, T, sm); break;
-        default: decoder_backward_cta<KIND_COLOR>(P, T, sm); break;
+        case KIND_COARSE: decoder_backward_cta<KIND_COARSE>(P, T, k, sm); break;
+        case KIND_MIDDLE: decoder_backward_cta<KIND_MIDDLE>(P, T, k, sm); break;
+        case KIND_FINE: decoder_backward_cta<KIND_FINE>(P, T, k, sm); break;
+        default: decoder_backward_cta<KIND_COLOR>(P, T, k, sm); break;
     }
+    release_counters(P.ctr);
 }
 
 // ---- weight gradients ------------------------------------------------------------------------
 // d(W) = G^T X summed over points, for every linear layer of one decoder, from the records
-// the backward kernel wrote (nsb_layout.h RecCfg).  A CTA walks its share of the tiles; per
-// tile the record is copied to shared memory (rows padded to a stride of 8 mod 32) and each
-// warp runs its "units" -- a unit is one 32 x 8 block of some d(W) (two m-tiles, one n-tile),
+// the backward kernel wrote (nsb_layout.h RecCfg).  A CTA owns a contiguous range of tiles,
+// compacts the live ones (flag set) and streams their records through a two-stage shared-
+// memory ring with 16-byte async copies (a record is one contiguous, pre-swizzled block, so
+// the copy is linear and the transposed fragment reads are bank-conflict free).  Each warp
+// runs its "units" -- a unit is one 32 x 8 block of some d(W) (two m-tiles, one n-tile),
 // 3xTF32, accumulators in registers for the whole kernel -- then adds them to the flat
 // gradient with one atomic per element per CTA.  Bias gradients are column sums of G.
 constexpr int DW_UNIT_INTS = 12;
 constexpr int DW_UPW = 8;          // max units per warp
 constexpr int DW_MAX_UNITS = DW_UPW * WARPS;
-constexpr int DW_MAX_SEC = 24;
+constexpr int DW_MAX_SEC = 26;
 constexpr int DW_MAX_BIAS = THREADS;
+constexpr int DW_LIVE_MAX = 64;    // tiles per CTA range
 
-struct DwUnit {       // all offsets in floats of the PADDED shared-memory record
-    int a_off, a_w, a_col0;      // G section, padded row stride, first row (f') of the 32-row block
-    int b_off, b_w, b_col0;      // X section, padded row stride, first column of the n-tile
+struct DwUnit {       // all offsets in floats of the record
+    int a_off, a_w, a_col0;      // G section, row stride, first row (f') of the 32-row block
+    int b_off, b_w, b_col0;      // X section, row stride, first column of the n-tile
     int out_off, ld_row, ld_col; // flat gradient index = out_off + row*ld_row + col*ld_col
-    int rows_valid, cols_valid, pad_;
+    int rows_valid, cols_valid;
+    int sw;                      // bit 0: G section columns are rec_sw-swizzled, bit 1: X section
 };
-struct DwSec { int g_off, width, s_off; };
+struct DwSec { int g_off, width; };
 struct DwBias { int s_off, s_w, col, out_idx; };
 
 struct DwTables {
     DwUnit unit[DW_MAX_UNITS];
     DwSec sec[DW_MAX_SEC];
     DwBias bias[DW_MAX_BIAS];
-    int nunit, nsec, nbias, rec, rec_padded;
+    int nunit, nsec, nbias, rec;
 };
 
 struct DwParams {
@@ -722,10 +753,42 @@ struct DwParams {
     float* dflat;
 };
 
+constexpr int DW_HEAD_FLOATS = DW_MAX_UNITS * DW_UNIT_INTS + DW_LIVE_MAX;   // unit table + live list
+
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gmem_src) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src) : "memory");
+}
+
 __global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
     extern __shared__ __align__(16) float sm[];
     const DwTables& TB = *P.tab;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    int* s_unit = reinterpret_cast<int*>(sm);
+    int* s_live = s_unit + DW_MAX_UNITS * DW_UNIT_INTS;
+    float* ring = sm + DW_HEAD_FLOATS;
+    __shared__ int s_nlive;
+    const int nunit = TB.nunit, nbias = TB.nbias, rec = TB.rec;
+    for (int i = threadIdx.x; i < nunit * DW_UNIT_INTS; i += THREADS)
+        s_unit[i] = reinterpret_cast<const int*>(TB.unit)[i];
+    DwBias mybias{0, 0, 0, 0};
+    if ((int)threadIdx.x < nbias) mybias = TB.bias[threadIdx.x];
+    // live tiles of this CTA's range, in order (deterministic summation order)
+    const long long per = (P.ntiles + gridDim.x - 1) / gridDim.x;
+    const long long t0 = (long long)blockIdx.x * per;
+    if (warp == 0) {
+        int n = 0;
+        for (int base = 0; base < (int)per; base += 32) {
+            const long long i = t0 + base + lane;
+            const bool live = (base + lane) < per && i < P.ntiles && P.flags[i] != 0;
+            const unsigned m = __ballot_sync(FULL, live);
+            if (live) s_live[n + __popc(m & ((1u << lane) - 1u))] = base + lane;
+            n += __popc(m);
+        }
+        if (lane == 0) s_nlive = n;
+    }
+    __syncthreads();
+    const int nlive = s_nlive;
     float acc[DW_UPW][2][4];
 #pragma unroll
     for (int k = 0; k < DW_UPW; ++k)
@@ -734,47 +797,49 @@ __global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) acc[k][m][q] = 0.f;
     float bias_acc = 0.f;
-    const int nunit = TB.nunit, nsec = TB.nsec, nbias = TB.nbias, rec = TB.rec;
-    for (long long tile = blockIdx.x; tile < P.ntiles; tile += gridDim.x) {
-        if (!P.flags[tile]) continue;                       // uniform over the CTA
-        const float* src = P.scratch + (size_t)tile * rec;
-        __syncthreads();                                     // previous tile fully consumed
-        for (int s = 0; s < nsec; ++s) {
-            const DwSec sc = TB.sec[s];
-            const int w4 = sc.width >> 2;
-            for (int i = threadIdx.x; i < 16 * w4; i += THREADS) {
-                const int row = i / w4, c4 = i - row * w4;
-                const float4 v = __ldg(reinterpret_cast<const float4*>(src + sc.g_off + row * sc.width) + c4);
-                *reinterpret_cast<float4*>(sm + sc.s_off + row * (sc.width + REC_PAD) + 4 * c4) = v;
-            }
-        }
-        __syncthreads();
+    const int rec4 = rec >> 2;
+    auto issue = [&](int i) {
+        const float* src = P.scratch + (size_t)(t0 + s_live[i]) * rec;
+        float* dst = ring + (i & 1) * rec;
+        for (int c = threadIdx.x; c < rec4; c += THREADS) cp_async16(dst + 4 * c, src + 4 * c);
+    };
+    if (nlive > 0) issue(0);
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+    for (int i = 0; i < nlive; ++i) {
+        if (i + 1 < nlive) issue(i + 1);
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+        asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        __syncthreads();                                     // record i has landed for every thread
+        const float* R = ring + (i & 1) * rec;
         if ((int)threadIdx.x < nbias) {
-            const DwBias b = TB.bias[threadIdx.x];
             float s = 0.f;
 #pragma unroll
-            for (int pt = 0; pt < 16; ++pt) s += sm[b.s_off + pt * b.s_w + b.col];
+            for (int pt = 0; pt < 16; ++pt) s += R[mybias.s_off + pt * mybias.s_w + rec_sw(pt, mybias.col)];
             bias_acc += s;
         }
 #pragma unroll
         for (int k = 0; k < DW_UPW; ++k) {
             const int u = warp + WARPS * k;
             if (u < nunit) {
-                const DwUnit U = TB.unit[u];
+                const int* U = s_unit + u * DW_UNIT_INTS;
+                const int a_off = U[0], a_w = U[1], a_col0 = U[2], b_off = U[3], b_w = U[4], b_col0 = U[5];
+                const int swa = (U[11] & 1) ? (t << 3) : 0, swb = (U[11] & 2) ? (t << 3) : 0;
 #pragma unroll
                 for (int ks = 0; ks < 2; ++ks) {
-                    const float* Ap = sm + U.a_off + (8 * ks + t) * U.a_w + U.a_col0 + g;
-                    const float* Bp = sm + U.b_off + (8 * ks + t) * U.b_w + U.b_col0 + g;
+                    const int row = 8 * ks + t;              // rows row, row + 4: both have (row & 3) == t
+                    const float* Bp = R + b_off + row * b_w + ((b_col0 + g) ^ swb);
                     uint32_t bh[2], bl[2];
                     split_tf32(Bp[0], bh[0], bl[0]);
-                    split_tf32(Bp[4 * U.b_w], bh[1], bl[1]);
+                    split_tf32(Bp[4 * b_w], bh[1], bl[1]);
+                    const float* Ar = R + a_off + row * a_w;
 #pragma unroll
                     for (int m = 0; m < 2; ++m) {
+                        const int c0 = (a_col0 + g + 16 * m) ^ swa, c1 = (a_col0 + g + 16 * m + 8) ^ swa;
                         uint32_t ah[4], al[4];
-                        split_tf32(Ap[16 * m], ah[0], al[0]);
-                        split_tf32(Ap[16 * m + 8], ah[1], al[1]);
-                        split_tf32(Ap[4 * U.a_w + 16 * m], ah[2], al[2]);
-                        split_tf32(Ap[4 * U.a_w + 16 * m + 8], ah[3], al[3]);
+                        split_tf32(Ar[c0], ah[0], al[0]);
+                        split_tf32(Ar[c1], ah[1], al[1]);
+                        split_tf32(Ar[4 * a_w + c0], ah[2], al[2]);
+                        split_tf32(Ar[4 * a_w + c1], ah[3], al[3]);
                         mma_tf32(acc[k][m], al, bh[0], bh[1]);
                         mma_tf32(acc[k][m], ah, bl[0], bl[1]);
                         mma_tf32(acc[k][m], ah, bh[0], bh[1]);
@@ -782,24 +847,25 @@ __global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
                 }
             }
         }
+        __syncthreads();                                     // stage (i & 1) may be refilled
     }
     // flush: C fragment (row 16m + g (+8), col 2t (+1)) of unit u
 #pragma unroll
     for (int k = 0; k < DW_UPW; ++k) {
         const int u = warp + WARPS * k;
         if (u < nunit) {
-            const DwUnit U = TB.unit[u];
+            const int* U = s_unit + u * DW_UNIT_INTS;
 #pragma unroll
             for (int m = 0; m < 2; ++m)
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int row = 16 * m + g + 8 * (q >> 1), col = 2 * t + (q & 1);
-                    if (row < U.rows_valid && col < U.cols_valid && acc[k][m][q] != 0.f)
-                        atomicAdd(P.dflat + U.out_off + row * U.ld_row + col * U.ld_col, acc[k][m][q]);
+                    if (row < U[9] && col < U[10] && acc[k][m][q] != 0.f)
+                        atomicAdd(P.dflat + U[6] + row * U[7] + col * U[8], acc[k][m][q]);
                 }
         }
     }
-    if ((int)threadIdx.x < nbias && bias_acc != 0.f) atomicAdd(P.dflat + TB.bias[threadIdx.x].out_idx, bias_acc);
+    if ((int)threadIdx.x < nbias && bias_acc != 0.f) atomicAdd(P.dflat + mybias.out_idx, bias_acc);
 }
 
 // host: tables of one decoder kind
@@ -819,16 +885,13 @@ static void build_dw_tables(DwTables& T) {
         else numel = i == 10 ? HID : 1;
         acc_off += numel;
     }
-    // sections and their padded shared offsets
-    int s_off = 0;
+    // sections of the record (the shared-memory copy is a verbatim image of it)
     auto add_sec = [&](int g_off, int width) {
         DwSec& s = T.sec[T.nsec++];
-        s.g_off = g_off; s.width = width; s.s_off = s_off;
-        const int r = s_off;
-        s_off += 16 * (width + REC_PAD);
-        return r;
+        s.g_off = g_off; s.width = width;
+        return g_off;
     };
-    int sE = -1, sH[5], sC, sP = -1, sDA[5], sDH[5], sDO, sDE = -1;
+    int sE = -1, sH[5], sC, sP = -1, sDA[5], sDH[5], sDO, sDE = -1, sDE0 = -1;
     if (C::EMBED) sE = add_sec(RC::R_E, EMB_PAD);
     for (int i = 0; i < 5; ++i) sH[i] = add_sec(RC::R_H + i * 16 * HID, HID);
     sC = add_sec(RC::R_C, C::C_IN);
@@ -836,16 +899,16 @@ static void build_dw_tables(DwTables& T) {
     for (int i = 0; i < 5; ++i) sDA[i] = add_sec(RC::R_DA + i * 16 * HID, HID);
     if (C::EMBED) for (int i = 0; i < 5; ++i) sDH[i] = add_sec(RC::R_DH + i * 16 * HID, HID);
     sDO = add_sec(RC::R_DO, HID);
-    if (C::EMBED) sDE = add_sec(RC::R_DE, EMB_PAD);
+    if (C::EMBED) { sDE = add_sec(RC::R_DE, EMB_PAD); sDE0 = add_sec(RC::R_DE0, EMB_PAD); }
     T.rec = RC::REC;
-    T.rec_padded = s_off;
     auto add_unit = [&](int a_off, int a_width, int a_col0, int b_off, int b_width, int b_col0, int out_off,
                         int ld_row, int ld_col, int rows_valid, int cols_valid) {
         DwUnit& u = T.unit[T.nunit++];
-        u.a_off = a_off; u.a_w = a_width + REC_PAD; u.a_col0 = a_col0;
-        u.b_off = b_off; u.b_w = b_width + REC_PAD; u.b_col0 = b_col0;
+        u.a_off = a_off; u.a_w = a_width; u.a_col0 = a_col0;
+        u.b_off = b_off; u.b_w = b_width; u.b_col0 = b_col0;
         u.out_off = out_off; u.ld_row = ld_row; u.ld_col = ld_col;
         u.rows_valid = rows_valid; u.cols_valid = cols_valid;
+        u.sw = (a_width >= 32 ? 1 : 0) | (b_width >= 32 ? 2 : 0);
     };
     // X parts of layer i: (section, width, number of n-tiles, valid features, first input column)
     for (int i = 0; i < 5; ++i) {
@@ -871,11 +934,13 @@ static void build_dw_tables(DwTables& T) {
     for (int n = 0; n < 4; ++n)       // output layer: rows = outputs
         add_unit(sDO, HID, 0, sH[4], HID, 8 * n, off[C::P_WO] + 8 * n, HID, 1, C::NOUT, 8);
     if (C::EMBED)
-        for (int m0 = 0; m0 < EMB_PAD; m0 += 32)   // d(B)[a][f]: rows = features f, cols = axes a
+        for (int m0 = 0; m0 < EMB_PAD; m0 += 32) {  // d(B)[a][f]: rows = features f, cols = axes a
             add_unit(sDE, EMB_PAD, m0, sP, 8, 0, off[C::P_EMB] + m0, 1, EMB, (EMB - m0 < 32 ? EMB - m0 : 32), 3);
+            add_unit(sDE0, EMB_PAD, m0, sP, 8, 0, off[C::P_EMB] + m0, 1, EMB, (EMB - m0 < 32 ? EMB - m0 : 32), 3);
+        }
     auto add_bias = [&](int sec, int width, int col, int out_idx) {
         DwBias& b = T.bias[T.nbias++];
-        b.s_off = sec; b.s_w = width + REC_PAD; b.col = col; b.out_idx = out_idx;
+        b.s_off = sec; b.s_w = width; b.col = col; b.out_idx = out_idx;
     };
     for (int i = 0; i < 5; ++i)
         for (int f = 0; f < HID; ++f) {
@@ -888,6 +953,13 @@ static void build_dw_tables(DwTables& T) {
 // ---- host side -------------------------------------------------------------------------------
 static int g_num_sms = 0;
 static bool g_attr_done = false;
+constexpr int CTR_SLOTS = 256;                   // launches in flight before a counter slot is reused
+__device__ unsigned g_tile_ctr[CTR_SLOTS * 4];
+static unsigned* g_ctr_dev = nullptr;
+struct DwTables;
+static DwTables* g_dw_tables_dev = nullptr;
+static unsigned g_ctr_next = 0;
+static unsigned* next_counters() { return g_ctr_dev + 4 * (g_ctr_next++ % CTR_SLOTS); }
 __device__ DwTables g_dw_tables[4];
 static DwTables g_dw_host[4];
 
@@ -920,7 +992,10 @@ static int init_device() {
     build_dw_tables<KIND_COLOR>(g_dw_host[3]);
     e = cudaMemcpyToSymbol(g_dw_tables, g_dw_host, sizeof(g_dw_host));
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(k_dweight, cudaFuncAttributeMaxDynamicSharedMemorySize, g_dw_host[2].rec_padded * 4);
+        e = cudaFuncSetAttribute(k_dweight, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (DW_HEAD_FLOATS + 2 * REC_MAX) * 4);
+    if (e == cudaSuccess) e = cudaGetSymbolAddress((void**)&g_ctr_dev, g_tile_ctr);
+    if (e == cudaSuccess) e = cudaGetSymbolAddress((void**)&g_dw_tables_dev, g_dw_tables);
     if (e != cudaSuccess) return set_error((int)e, "d(W) tables: %s", cudaGetErrorString(e));
     g_attr_done = true;
     return 0;
@@ -1036,6 +1111,7 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
     sp.flags = 0;
     sp.tile_begin = 0;
     sp.tile_end = (sp.pts.P + 15) / 16;
+    sp.ctr = next_counters();
     timing_mark(0, 0, (cudaStream_t)stream);
     k_decoders_forward<<<ctas, THREADS, max_blob(sp, false) * 4, (cudaStream_t)stream>>>(sp);
     timing_mark(0, 1, (cudaStream_t)stream);
@@ -1101,6 +1177,7 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
     for (long long t0 = 0; t0 < ntiles; t0 += chunk) {
         sp.tile_begin = t0;
         sp.tile_end = t0 + chunk < ntiles ? t0 + chunk : ntiles;
+        sp.ctr = next_counters();
         timing_mark(1, 0, (cudaStream_t)stream);
         k_decoders_backward<<<ctas, THREADS, smem, (cudaStream_t)stream>>>(sp);
         timing_mark(1, 1, (cudaStream_t)stream);
@@ -1112,13 +1189,15 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
             dp.scratch = T.dw_scratch;
             dp.flags = T.dw_flags;
             dp.ntiles = sp.tile_end - sp.tile_begin;
-            DwTables* dev_tab = nullptr;
-            cudaError_t e = cudaGetSymbolAddress((void**)&dev_tab, g_dw_tables);
-            if (e != cudaSuccess) return set_error((int)e, "cudaGetSymbolAddress: %s", cudaGetErrorString(e));
-            dp.tab = dev_tab + T.kind;
+            dp.tab = g_dw_tables_dev + T.kind;
             dp.dflat = d_weight_host[T.kind];
-            int grid = (int)(dp.ntiles < g_num_sms ? dp.ntiles : g_num_sms);
-            k_dweight<<<grid, THREADS, g_dw_host[T.kind].rec_padded * 4, (cudaStream_t)stream>>>(dp);
+            // every CTA owns at most DW_LIVE_MAX consecutive tiles
+            long long grid = dp.ntiles < g_num_sms ? dp.ntiles : g_num_sms;
+            const long long need = (dp.ntiles + DW_LIVE_MAX - 1) / DW_LIVE_MAX;
+            if (grid < need) grid = need;
+            timing_mark(2, 0, (cudaStream_t)stream);
+            k_dweight<<<(int)grid, THREADS, (DW_HEAD_FLOATS + 2 * g_dw_host[T.kind].rec) * 4, (cudaStream_t)stream>>>(dp);
+            timing_mark(2, 1, (cudaStream_t)stream);
             if (int rc = check_launch("k_dweight")) return rc;
         }
     }

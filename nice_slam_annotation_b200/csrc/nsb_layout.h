@@ -129,11 +129,14 @@ struct RecCfg {
     static constexpr int R_DA = R_P + 16 * 8;                  // d(a1)..d(a5)         5 x [16][32]
     static constexpr int R_DH = R_DA + 5 * 16 * HID;           // d(h1)..d(h5)         5 x [16][32]
     static constexpr int R_DO = R_DH + 5 * 16 * HID;           // d(out) (cols < NOUT) [16][32]
-    static constexpr int R_DE = R_DO + 16 * HID;               // d(e) * cos(pB)       [16][96]
-    static constexpr int REC = R_DE + 16 * W_E;
+    static constexpr int R_DE = R_DO + 16 * HID;               // d(e) * cos(pB), layer 3 [16][96]
+    static constexpr int R_DE0 = R_DE + 16 * W_E;              // d(e) * cos(pB), layer 0 [16][96]
+    static constexpr int REC = R_DE0 + 16 * W_E;
 };
 constexpr int REC_MAX = RecCfg<KIND_FINE>::REC;
-// shared-memory copy of a record pads every row by 8 floats (stride = 8 mod 32: the
-// transposed fragment reads of k_dweight are then bank-conflict free)
-constexpr int REC_PAD = 8;
+// Within a section of width >= 32 the element (row, col) is stored at column
+// col ^ ((row & 3) << 3): k_dweight copies a record to shared memory verbatim (one linear
+// async copy) and its transposed fragment reads (4 rows x 8 columns per request) are then
+// bank-conflict free without padding.
+NSB_HD inline int rec_sw(int row, int col) { return col ^ ((row & 3) << 3); }
 }  // namespace nsb

@@ -195,11 +195,14 @@ extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
     if (r->N <= 0) return 0;
     Ws w = carve_ws(r->workspace, r->N, S);
     const double* b6 = &r->scene.bound[0][0];
-    if (r->gt_depth)
+    const float* dmax = r->depth_max;
+    if (r->gt_depth && !dmax) {
         if (int rc = nsb_depth_max(r->gt_depth, r->keep, r->N, w.depth_max, stream)) return rc;
+        dmax = w.depth_max;
+    }
     NsbPoints rays = ray_pts(r, nullptr, 0);
     if (int rc = nsb_sample_z(&rays, r->gt_depth, b6, r->N_samples, Nf, r->lindisp, r->t_uniform, r->t_surface,
-                              r->u, w.depth_max, w.z, stream)) return rc;
+                              r->u, dmax, w.z, stream)) return rc;
     NsbPoints pts = ray_pts(r, w.z, S);
     float *o0, *o1, *rgb;
     stage_planes(r->stage, w, o0, o1, rgb);

@@ -116,11 +116,13 @@ __global__ void k_all_rays(int H, int W, CamDev cam, const float* __restrict__ c
     }
 }
 
-__global__ void k_depth_max(const float* __restrict__ gt, long long n, float* __restrict__ out) {
+__global__ void k_depth_max(const float* __restrict__ gt, const uint8_t* __restrict__ keep, long long n,
+                            float* __restrict__ out) {
     __shared__ float part[32];
     float m = -INFINITY;
     bool nan = false;
     for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+        if (keep && !keep[i]) continue;
         float v = gt[i];
         nan |= (v != v);
         m = fmaxf(m, v);
@@ -360,9 +362,9 @@ extern "C" int nsb_all_rays(int H, int W, float fx, float fy, float cx, float cy
     return check_launch("k_all_rays");
 }
 
-extern "C" int nsb_depth_max(const float* gt_depth, int64_t N, float* out, void* stream) {
+extern "C" int nsb_depth_max(const float* gt_depth, const uint8_t* keep, int64_t N, float* out, void* stream) {
     if (!gt_depth || !out) return set_error(NSB_EINVAL, "null argument");
-    k_depth_max<<<1, 1024, 0, (cudaStream_t)stream>>>(gt_depth, N, out);
+    k_depth_max<<<1, 1024, 0, (cudaStream_t)stream>>>(gt_depth, keep, N, out);
     return check_launch("k_depth_max");
 }
 

@@ -13,7 +13,7 @@ import torch
 
 from . import _lib
 from ._lib import (DEC_COARSE, DEC_COLOR, DEC_FINE, DEC_MIDDLE, GRAD_GRID, GRAD_POINT, GRAD_WEIGHT,
-                   STAGES, NsbGrid, NsbPoints, NsbScene, check, lib)
+                   STAGES, NsbGrid, NsbPoints, NsbRenderCall, NsbScene, check, lib)
 
 GRID_KEYS = ("grid_coarse", "grid_middle", "grid_fine", "grid_color")
 DEC_NAMES = ("coarse_decoder", "middle_decoder", "fine_decoder", "color_decoder")
@@ -198,7 +198,7 @@ def sample_z(rays_o, rays_d, gt_depth, bound, N_samples, N_surface, lindisp=Fals
     if gt_depth is not None:
         gt_depth = gt_depth.reshape(-1).float().contiguous()
         dmax = torch.empty(1, dtype=torch.float32, device=dev)
-        check(lib().nsb_depth_max(_ptr(gt_depth), N, _ptr(dmax), _stream()), "depth_max")
+        check(lib().nsb_depth_max(_ptr(gt_depth), None, N, _ptr(dmax), _stream()), "depth_max")
     if u is not None:
         u = u.to(device=dev, dtype=torch.float32).contiguous()
     rays = ray_points(rays_o, rays_d, None)
@@ -241,8 +241,33 @@ def _gather_scene(stage, bound, c, decoders, enlarge):
     return grids, packed, params
 
 
+def _render_call(meta, rays_o, rays_d, grids, grads, ws, depth, var, color):
+    """NsbRenderCall of one render_batch_ray (forward fields; the backward adds its own)."""
+    dev = rays_o.device
+    call = NsbRenderCall()
+    call.rays_o, call.rays_d = rays_o.data_ptr(), rays_d.data_ptr()
+    call.rays_o_stride, call.rays_d_stride = rays_o.stride(0), rays_d.stride(0)
+    call.N = rays_o.shape[0]
+    gd, keep, u = meta["gt_depth"], meta.get("keep"), meta.get("u")
+    call.gt_depth = 0 if gd is None else gd.data_ptr()
+    call.keep = 0 if keep is None else keep.data_ptr()
+    dmax = meta.get("depth_max")
+    call.depth_max = 0 if dmax is None else dmax.data_ptr()
+    call.N_samples, call.N_surface = meta["N_samples"], meta["N_surface"]
+    call.lindisp, call.stage, call.occupancy = int(meta["lindisp"]), STAGES[meta["stage"]], int(meta["occupancy"])
+    call.t_uniform = _linspace(meta["N_samples"], torch.float32, dev).data_ptr()
+    call.t_surface = _linspace(meta["N_surface"], torch.float64, dev).data_ptr() if meta["N_surface"] > 0 else 0
+    call.u = 0 if u is None else u.data_ptr()
+    call.scene = make_scene(meta["bound"], grids, meta["packed"], grads, meta["coarse_bound_enlarge"])
+    call.workspace, call.workspace_bytes = ws.data_ptr(), ws.numel()
+    call.depth, call.var, call.color = depth.data_ptr(), var.data_ptr(), color.data_ptr()
+    return call
+
+
 class _RenderFn(torch.autograd.Function):
-    """render_batch_ray (src/utils/Renderer.py:95-262) as one autograd node."""
+    """render_batch_ray (src/utils/Renderer.py:95-262) as one autograd node.  Without
+    importance resampling (the NICE configs) forward and backward are ONE library call each
+    (nsb_render_forward / nsb_render_backward)."""
 
     @staticmethod
     def forward(ctx, meta, rays_o, rays_d, *tensors):
@@ -255,6 +280,22 @@ class _RenderFn(torch.autograd.Function):
         dev = rays_o.device
         N = rays_o.shape[0]
         gt_depth = meta["gt_depth"]
+        if meta["N_importance"] == 0:
+            S = meta["N_samples"] + (meta["N_surface"] if gt_depth is not None else 0)
+            depth = torch.empty(N, dtype=torch.float64, device=dev)
+            var = torch.empty(N, dtype=torch.float64, device=dev)
+            color = torch.empty(N, 3, dtype=torch.float32, device=dev)
+            ws = torch.empty(max(lib().nsb_render_workspace_bytes(N, S), 1), dtype=torch.uint8, device=dev)
+            if meta.get("u") is not None:
+                meta["u"] = meta["u"].to(device=dev, dtype=torch.float32).contiguous()
+            if N > 0:
+                call = _render_call(meta, rays_o, rays_d, grids, None, ws, depth, var, color)
+                check(lib().nsb_render_forward(C.byref(call), _stream()), "render_forward")
+            ctx.meta, ctx.kinds, ctx.n_grid, ctx.fused_ws, ctx.S = meta, kinds, n_grid, ws, S
+            ctx.param_shapes = [p.shape for p in flat_params]
+            ctx.save_for_backward(rays_o, rays_d, depth, var, color, *tensors[:n_grid])
+            return depth, var, color
+        ctx.fused_ws = None
         z = sample_z(rays_o, rays_d, gt_depth, bound, meta["N_samples"], meta["N_surface"], meta["lindisp"],
                      meta.get("u"))
         S = z.shape[1]
@@ -298,7 +339,76 @@ class _RenderFn(torch.autograd.Function):
         return depth, var, color
 
     @staticmethod
+    def _backward_fused(ctx, g_depth, g_var, g_color):
+        meta, kinds = ctx.meta, ctx.kinds
+        rays_o, rays_d, depth, var, color = ctx.saved_tensors[:5]
+        grids = dict(zip(kinds, ctx.saved_tensors[5:]))
+        dev, N = rays_o.device, rays_o.shape[0]
+        P = N * ctx.S
+        need = ctx.needs_input_grad          # (meta, rays_o, rays_d, grids..., params...)
+        out = [None] * len(need)
+        if N == 0:
+            return tuple(out)
+        need_rays = need[1] or need[2]
+        need_param = need[3 + ctx.n_grid:]
+        flags, grads = 0, {}
+        for i, k in enumerate(kinds):
+            if need[3 + i]:
+                grads[k] = torch.zeros_like(grids[k], memory_format=torch.preserve_format)
+                flags |= GRAD_GRID
+        call = _render_call(meta, rays_o, rays_d, grids, grads, ctx.fused_ws, depth, var, color)
+        hold = []
+        if g_depth is not None:
+            hold.append(g_depth.double().contiguous())
+            call.g_depth = hold[-1].data_ptr()
+        if g_var is not None:
+            hold.append(g_var.double().contiguous())
+            call.g_var = hold[-1].data_ptr()
+        if g_color is not None:
+            hold.append(g_color.float().contiguous())
+            call.g_color = hold[-1].data_ptr()
+        dw, dw_mask, pi = {}, 0, 0
+        for k in kinds:
+            n = lib().nsb_param_count(k)
+            if any(need_param[pi:pi + n]):
+                dw[k] = torch.zeros(lib().nsb_flat_numel(k), dtype=torch.float32, device=dev)
+                dw_mask |= 1 << k
+                call.d_weight[k] = dw[k].data_ptr()
+            pi += n
+        if dw_mask:
+            flags |= GRAD_WEIGHT
+            nbytes = len(dw) * max(lib().nsb_dweight_scratch_bytes(k, P) for k in dw)
+            hold.append(torch.empty(nbytes, dtype=torch.uint8, device=dev))
+            call.scratch, call.scratch_bytes = hold[-1].data_ptr(), nbytes
+        if need_rays:
+            flags |= GRAD_POINT
+            g_o = torch.empty(N, 3, dtype=torch.float32, device=dev)
+            g_d = torch.empty(N, 3, dtype=torch.float32, device=dev)
+            call.g_rays_o, call.g_rays_d = g_o.data_ptr(), g_d.data_ptr()
+            out[1] = g_o if need[1] else None
+            out[2] = g_d if need[2] else None
+        call.flags, call.dweight_mask = flags, dw_mask
+        check(lib().nsb_render_backward(C.byref(call), _stream()), "render_backward")
+        for i, k in enumerate(kinds):
+            if need[3 + i]:
+                out[3 + i] = grads[k]
+        pi, base = 0, 3 + ctx.n_grid
+        for k in kinds:
+            n = lib().nsb_param_count(k)
+            if k in dw:
+                off = 0
+                for j in range(n):
+                    numel = lib().nsb_param_numel(k, j)
+                    if need_param[pi + j]:
+                        out[base + pi + j] = dw[k][off:off + numel].view(ctx.param_shapes[pi + j])
+                    off += numel
+            pi += n
+        return tuple(out)
+
+    @staticmethod
     def backward(ctx, g_depth, g_var, g_color):
+        if ctx.fused_ws is not None:
+            return _RenderFn._backward_fused(ctx, g_depth, g_var, g_color)
         meta, kinds, planes = ctx.meta, ctx.kinds, ctx.planes
         rays_o, rays_d, z, depth = ctx.saved_tensors[:4]
         grid_list = ctx.saved_tensors[4:]
@@ -387,9 +497,11 @@ class _RenderFn(torch.autograd.Function):
 
 def render_batch_ray(c, decoders, rays_d, rays_o, stage, gt_depth, bound, *, N_samples, N_surface,
                      N_importance=0, lindisp=False, occupancy=True, u=None, u_importance=None,
-                     coarse_bound_enlarge=2.0):
+                     coarse_bound_enlarge=2.0, keep=None):
     """Fused Renderer.render_batch_ray for the NICE decoders.  Differentiable in the grids of
-    ``c``, the decoder parameters and the rays."""
+    ``c``, the decoder parameters and the rays.  ``keep`` ([N] uint8, optional): fixed-shape
+    alternative to compacting the batch after the box pre-filter (dropped rays are excluded
+    from the batch depth max; give them zero loss weight)."""
     if stage not in STAGES:
         raise ValueError(f"unknown stage {stage!r}")
     _require_cuda(rays_o, "rays_o")
@@ -404,8 +516,68 @@ def render_batch_ray(c, decoders, rays_d, rays_o, stage, gt_depth, bound, *, N_s
     meta = dict(stage=stage, bound=torch.as_tensor(bound, dtype=torch.float64, device="cpu"),
                 gt_depth=gt_depth, N_samples=int(N_samples), N_surface=int(N_surface),
                 N_importance=int(N_importance), lindisp=bool(lindisp), occupancy=bool(occupancy), u=u,
-                u_importance=u_importance, packed=packed, coarse_bound_enlarge=float(coarse_bound_enlarge))
+                u_importance=u_importance, packed=packed, coarse_bound_enlarge=float(coarse_bound_enlarge),
+                keep=keep)
+    if keep is not None and N_importance > 0:
+        raise NotImplementedError("keep masks are supported on the single-pass (NICE) render only")
     return _RenderFn.apply(meta, rays_o, rays_d, *[grids[k] for k in kinds], *flat_params)
+
+
+class _LossFn(torch.autograd.Function):
+    """The SLAM step losses (src/Mapper.py:604-612, src/Tracker.py:113-130), value and gradient
+    in one kernel: nsb_mapping_loss / nsb_tracking_loss."""
+
+    @staticmethod
+    def forward(ctx, depth, var, color, gt_depth, gt_color, keep, kind, w_color, use_color, handle_dynamic):
+        dev, N = depth.device, depth.shape[0]
+        loss = torch.zeros(1, dtype=torch.float64, device=dev)
+        g_depth = torch.zeros(N, dtype=torch.float64, device=dev)
+        g_color = torch.zeros(N, 3, dtype=torch.float32, device=dev)
+        if N > 0:
+            depth, color = depth.detach().contiguous(), color.detach().contiguous()
+            if kind == "mapping":
+                check(lib().nsb_mapping_loss(_ptr(depth), _ptr(color), _ptr(gt_depth), _ptr(gt_color), _ptr(keep), N,
+                                             float(w_color), int(use_color), _ptr(loss), _ptr(g_depth), _ptr(g_color),
+                                             _stream()), "mapping_loss")
+            else:
+                var = var.detach().contiguous()
+                check(lib().nsb_tracking_loss(_ptr(depth), _ptr(var), _ptr(color), _ptr(gt_depth), _ptr(gt_color),
+                                              _ptr(keep), N, float(w_color), int(use_color), int(handle_dynamic),
+                                              _ptr(loss), _ptr(g_depth), _ptr(g_color), _stream()), "tracking_loss")
+        ctx.save_for_backward(g_depth, g_color)
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        g_depth, g_color = ctx.saved_tensors
+        return g_depth * g, None, g_color * g.float(), None, None, None, None, None, None, None
+
+
+def _loss_args(depth, color, gt_depth, gt_color, keep):
+    _require_cuda(depth, "depth")
+    gt_depth = gt_depth.detach().reshape(-1).float().contiguous()
+    gt_color = gt_color.detach().reshape(-1, 3).float().contiguous()
+    if keep is not None:
+        keep = keep.to(torch.uint8).contiguous()
+    if depth.dtype != torch.float64:
+        depth = depth.double()
+    if color.dtype != torch.float32:
+        color = color.float()
+    return depth, color, gt_depth, gt_color, keep
+
+
+def mapping_loss(depth, color, gt_depth, gt_color, w_color, use_color=True, keep=None):
+    """sum_{gt>0} |gt - depth| + w_color sum |gt_c - color| (src/Mapper.py:604-612), fp64 scalar."""
+    depth, color, gt_depth, gt_color, keep = _loss_args(depth, color, gt_depth, gt_color, keep)
+    return _LossFn.apply(depth, None, color, gt_depth, gt_color, keep, "mapping", w_color, use_color, False)
+
+
+def tracking_loss(depth, var, color, gt_depth, gt_color, w_color, use_color, handle_dynamic, keep=None):
+    """Tracker loss with the median-based dynamic-object mask (src/Tracker.py:113-130); the
+    uncertainty is detached as in the reference."""
+    depth, color, gt_depth, gt_color, keep = _loss_args(depth, color, gt_depth, gt_color, keep)
+    return _LossFn.apply(depth, var.double(), color, gt_depth, gt_color, keep, "tracking", w_color, use_color,
+                         handle_dynamic)
 
 
 STAGE_SINGLE = 16

@@ -1,0 +1,278 @@
+"""One SLAM optimisation iteration as three library calls: render forward, loss, render
+backward -- no autograd graph, fixed shapes, every buffer allocated once.
+
+This is the engine under ``Mapper.optimize_map`` / ``Tracker.optimize_cam_in_batch`` when the
+iteration has the static shape the fused path wants (NICE decoders, no jitter, pre-filter as a
+mask): the reference's iteration body (src/Mapper.py:598-624, src/Tracker.py:113-132) is ~620
+ATen launches + 3 host syncs, here it is ~10 launches that can be replayed as one CUDA graph.
+
+Mapping shards by rays: every rank renders its slice of the batch against
+replicated grids / decoders, the gradients land in ONE flat bucket (``GradBucket``) that is
+sum-all-reduced in a single NCCL call, after which every rank applies the identical optimiser
+step.  The batch-global scalar ``max(gt_depth)`` (src/utils/Renderer.py:157,194) is MAX-reduced
+so the sharded render equals the unsharded one.
+"""
+import ctypes as C
+
+import torch
+
+from . import fused
+from ._lib import GRAD_GRID, GRAD_POINT, GRAD_WEIGHT, NsbRenderCall, STAGES, check, lib
+from .fused import DEC_NAMES, GRID_KEYS, STAGE_DECODERS, _linspace, _ptr, _stream, canonical_params, pack_table
+
+
+# ---------------------------------------------------------------------------------------
+# gradient bucket (pure torch: also exercised on CPU / gloo by the tests)
+# ---------------------------------------------------------------------------------------
+class GradBucket:
+    """Gradients of a list of leaves as views of one flat fp32 buffer.
+
+    A view has the shape AND the memory layout of its leaf (channels-last grids stay
+    channels-last), so kernels scatter straight into it and ``leaf.grad = view`` costs nothing.
+    ``all_reduce`` is then one collective over the flat buffer, with no flatten / unflatten copies.
+    """
+
+    def __init__(self, leaves, device=None):
+        self.leaves = list(leaves)
+        device = device if device is not None else self.leaves[0].device
+        self.offsets, n = [], 0
+        for p in self.leaves:
+            self.offsets.append(n)
+            n += (p.numel() + 63) // 64 * 64            # 256-byte aligned segments
+        self.flat = torch.zeros(n, dtype=torch.float32, device=device)
+        self.views = [self._view(p, o) for p, o in zip(self.leaves, self.offsets)]
+
+    def _view(self, p, off):
+        seg = self.flat[off:off + p.numel()]
+        if p.dim() == 5 and p.is_contiguous(memory_format=torch.channels_last_3d) and not p.is_contiguous():
+            n, c, z, y, x = p.shape
+            return seg.view(n, z, y, x, c).permute(0, 4, 1, 2, 3)
+        if not p.is_contiguous():
+            raise RuntimeError("GradBucket: leaves must be contiguous or channels_last_3d")
+        return seg.view(p.shape)
+
+    def view_of(self, leaf):
+        for p, v in zip(self.leaves, self.views):
+            if p is leaf:
+                return v
+        raise KeyError("leaf is not in the bucket")
+
+    def zero(self):
+        self.flat.zero_()
+
+    def all_reduce(self, group=None):
+        """SUM over ranks (the mapping loss is a plain sum over rays, src/Mapper.py:605-612)."""
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+
+    def assign(self):
+        """leaf.grad = its view (what optimizer.step() reads)."""
+        for p, v in zip(self.leaves, self.views):
+            p.grad = v
+
+
+def shard_slice(n, world, rank):
+    """Contiguous slice of an n-ray batch owned by ``rank`` (sizes differ by at most one)."""
+    base, rem = divmod(n, world)
+    lo = rank * base + min(rank, rem)
+    return slice(lo, lo + base + (1 if rank < rem else 0))
+
+
+def global_depth_max(gt_depth, keep=None, group=None):
+    """max(gt_depth) over the kept rays of ALL ranks, as a [1] fp32 tensor (Renderer.py:157)."""
+    import torch.distributed as dist
+    g = gt_depth.float()
+    if keep is not None:
+        g = torch.where(keep.bool(), g, torch.full_like(g, float("-inf")))
+    m = g.max().reshape(1) if g.numel() else torch.full((1,), float("-inf"), device=gt_depth.device)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(m, op=dist.ReduceOp.MAX, group=group)
+    return m
+
+
+# ---------------------------------------------------------------------------------------
+# the fused iteration
+# ---------------------------------------------------------------------------------------
+class FusedStep:
+    """Forward + loss + backward of one iteration at a fixed batch size.
+
+    renderer : nice_slam_annotation_b200.utils.Renderer.Renderer (sampling parameters, bound)
+    decoders : NICE module; c : dict of grids ([1,32,Z,Y,X], channels_last_3d)
+    n_rays   : batch size of every call (mask dropped rays with ``keep``)
+    loss     : 'mapping' (Mapper.py:604-612) or 'tracking' (Tracker.py:113-130)
+    grid_grads / decoder_grads : names whose gradient is produced (into ``self.bucket``)
+    ray_grads : also produce d(rays_o), d(rays_d) (tracking, BA)
+    """
+
+    def __init__(self, renderer, decoders, c, stage, n_rays, loss="mapping", w_color=0.2, use_color=True,
+                 handle_dynamic=False, grid_grads=(), decoder_grads=(), ray_grads=False, with_gt_depth=True,
+                 group=None):
+        if not renderer.fixed_shape_ok():
+            raise NotImplementedError("FusedStep needs the NICE decoders, perturb == 0 and N_importance == 0")
+        self.r, self.decoders, self.stage, self.N = renderer, decoders, stage, int(n_rays)
+        self.kinds = STAGE_DECODERS[stage]
+        self.loss_kind, self.w_color, self.use_color, self.handle_dynamic = loss, w_color, use_color, handle_dynamic
+        self.group, self.ray_grads = group, ray_grads
+        self.with_gt_depth = with_gt_depth and stage != "coarse"
+        dev = next(decoders.parameters()).device
+        self.dev = dev
+        self.grids = {k: fused.grid_to_kernel_layout(c[GRID_KEYS[k]]).detach() for k in self.kinds}
+        N = self.N
+        self.S = renderer.N_samples + (renderer.N_surface if self.with_gt_depth else 0)
+        # static inputs
+        self.rays_o = torch.zeros(N, 3, device=dev)
+        self.rays_d = torch.zeros(N, 3, device=dev)
+        self.gt_depth = torch.zeros(N, device=dev)
+        self.gt_color = torch.zeros(N, 3, device=dev)
+        self.keep = torch.ones(N, dtype=torch.uint8, device=dev)
+        self.depth_max = torch.zeros(1, device=dev)
+        # outputs
+        self.depth = torch.zeros(N, dtype=torch.float64, device=dev)
+        self.var = torch.zeros(N, dtype=torch.float64, device=dev)
+        self.color = torch.zeros(N, 3, device=dev)
+        self.loss = torch.zeros(1, dtype=torch.float64, device=dev)
+        self.g_depth = torch.zeros(N, dtype=torch.float64, device=dev)
+        self.g_color = torch.zeros(N, 3, device=dev)
+        self.g_rays_o = torch.zeros(N, 3, device=dev) if ray_grads else None
+        self.g_rays_d = torch.zeros(N, 3, device=dev) if ray_grads else None
+        self.ws = torch.empty(max(lib().nsb_render_workspace_bytes(N, self.S), 1), dtype=torch.uint8, device=dev)
+        # gradient bucket: grids first, then one flat canonical segment per trainable decoder
+        self.grid_grad_kinds = [k for k in self.kinds if GRID_KEYS[k] in grid_grads]
+        self.dec_grad_kinds = [k for k in self.kinds if DEC_NAMES[k] in decoder_grads]
+        leaves = [self.grids[k] for k in self.grid_grad_kinds]
+        self.dw_holders = [torch.empty(lib().nsb_flat_numel(k), device=dev) for k in self.dec_grad_kinds]
+        self.bucket = GradBucket(leaves + self.dw_holders, dev) if (leaves or self.dw_holders) else None
+        self.scratch = None
+        if self.dec_grad_kinds:
+            nbytes = len(self.dec_grad_kinds) * lib().nsb_dweight_scratch_bytes(self.dec_grad_kinds[0], N * self.S)
+            self.scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        # static packed decoder blobs, re-packed in place from the live parameters
+        self.packed, self._pack_args = {}, {}
+        for k in self.kinds:
+            params = [p.detach() for p in canonical_params(getattr(decoders, DEC_NAMES[k]), k)]
+            if any(not p.is_contiguous() for p in params):
+                raise RuntimeError("decoder parameters must be contiguous")
+            ptrs = torch.tensor([p.data_ptr() for p in params], dtype=torch.int64).to(dev)
+            self.packed[k] = torch.empty(lib().nsb_packed_numel(k), device=dev)
+            self._pack_args[k] = (ptrs, params, pack_table(k, dev))
+            self._pack(k)
+        self._call = self._build_call()
+        self.graph = None
+
+    # -- plumbing -----------------------------------------------------------------------
+    def _pack(self, k):
+        ptrs, _, table = self._pack_args[k]
+        check(lib().nsb_pack_weights(k, _ptr(ptrs), _ptr(table), _ptr(self.packed[k]), _stream()), "pack_weights")
+
+    def _build_call(self):
+        r, dev = self.r, self.dev
+        call = NsbRenderCall()
+        call.rays_o, call.rays_d = self.rays_o.data_ptr(), self.rays_d.data_ptr()
+        call.rays_o_stride = call.rays_d_stride = 3
+        call.N = self.N
+        call.gt_depth = self.gt_depth.data_ptr() if self.with_gt_depth else 0
+        call.keep = self.keep.data_ptr()
+        call.depth_max = self.depth_max.data_ptr() if self.with_gt_depth else 0
+        call.N_samples, call.N_surface = r.N_samples, r.N_surface
+        call.lindisp, call.stage, call.occupancy = int(r.lindisp), STAGES[self.stage], int(r.occupancy)
+        call.t_uniform = _linspace(r.N_samples, torch.float32, dev).data_ptr()
+        call.t_surface = _linspace(r.N_surface, torch.float64, dev).data_ptr() if r.N_surface > 0 else 0
+        grads = {k: self.bucket.view_of(self.grids[k]) for k in self.grid_grad_kinds}
+        call.scene = fused.make_scene(r.bound, self.grids, self.packed, grads, r.coarse_bound_enlarge)
+        call.workspace, call.workspace_bytes = self.ws.data_ptr(), self.ws.numel()
+        call.depth, call.var, call.color = self.depth.data_ptr(), self.var.data_ptr(), self.color.data_ptr()
+        call.g_depth, call.g_color = self.g_depth.data_ptr(), self.g_color.data_ptr()
+        flags, mask = (GRAD_GRID if self.grid_grad_kinds else 0), 0
+        for k, h in zip(self.dec_grad_kinds, self.dw_holders):
+            call.d_weight[k] = self.bucket.view_of(h).data_ptr()
+            mask |= 1 << k
+        if mask:
+            flags |= GRAD_WEIGHT
+            call.scratch, call.scratch_bytes = self.scratch.data_ptr(), self.scratch.numel()
+        if self.ray_grads:
+            flags |= GRAD_POINT
+            call.g_rays_o, call.g_rays_d = self.g_rays_o.data_ptr(), self.g_rays_d.data_ptr()
+        call.flags, call.dweight_mask = flags, mask
+        return call
+
+    def load(self, rays_o, rays_d, gt_depth, gt_color, keep=None, depth_max=None):
+        """Copy one batch into the static input buffers (n <= N rays; the rest is masked off)."""
+        n = rays_o.shape[0]
+        if n > self.N:
+            raise ValueError(f"batch of {n} rays exceeds the step's capacity {self.N}")
+        self.rays_o[:n].copy_(rays_o, non_blocking=True)
+        self.rays_d[:n].copy_(rays_d, non_blocking=True)
+        self.gt_depth[:n].copy_(gt_depth.reshape(-1), non_blocking=True)
+        self.gt_color[:n].copy_(gt_color.reshape(-1, 3), non_blocking=True)
+        if keep is None:
+            self.keep[:n].fill_(1)
+        else:
+            self.keep[:n].copy_(keep, non_blocking=True)
+        if n < self.N:
+            self.keep[n:].zero_()
+            self.rays_d[n:].fill_(1.0)           # harmless finite rays behind the mask
+            self.gt_depth[n:].zero_()
+        if self.with_gt_depth:
+            if depth_max is None:
+                depth_max = global_depth_max(self.gt_depth, self.keep, self.group)
+            self.depth_max.copy_(depth_max.reshape(1), non_blocking=True)
+
+    def _launch(self):
+        """memset(bucket) -> re-pack trainable decoders -> forward -> loss -> backward."""
+        s = _stream()
+        if self.bucket is not None:
+            self.bucket.zero()
+        for k in self.dec_grad_kinds:
+            self._pack(k)
+        call = self._call
+        check(lib().nsb_render_forward(C.byref(call), s), "render_forward")
+        gd = _ptr(self.gt_depth)
+        if self.loss_kind == "mapping":
+            check(lib().nsb_mapping_loss(_ptr(self.depth), _ptr(self.color), gd, _ptr(self.gt_color), _ptr(self.keep),
+                                         self.N, float(self.w_color), int(self.use_color), _ptr(self.loss),
+                                         _ptr(self.g_depth), _ptr(self.g_color), s), "mapping_loss")
+        else:
+            check(lib().nsb_tracking_loss(_ptr(self.depth), _ptr(self.var), _ptr(self.color), gd, _ptr(self.gt_color),
+                                          _ptr(self.keep), self.N, float(self.w_color), int(self.use_color),
+                                          int(self.handle_dynamic), _ptr(self.loss), _ptr(self.g_depth),
+                                          _ptr(self.g_color), s), "tracking_loss")
+        check(lib().nsb_render_backward(C.byref(call), s), "render_backward")
+
+    def capture(self):
+        """Record the iteration into a CUDA graph (call once after a warm-up ``run``)."""
+        g = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g):
+            self._launch()
+        self.graph = g
+
+    def run(self, all_reduce=True):
+        """One iteration on the loaded batch.  Returns the loss as a [1] fp64 device tensor (this
+        rank's partial sum when sharded); gradients are in ``self.bucket`` (summed over ranks)."""
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._launch()
+        if all_reduce and self.bucket is not None:
+            self.bucket.all_reduce(self.group)
+        return self.loss
+
+    def decoder_grads(self, kind):
+        """Per-parameter gradient views of a trainable decoder, in state_dict order of
+        ``canonical_params``."""
+        flat = self.bucket.view_of(self.dw_holders[self.dec_grad_kinds.index(kind)])
+        out, off = [], 0
+        for p in self._pack_args[kind][1]:
+            out.append(flat[off:off + p.numel()].view(p.shape))
+            off += p.numel()
+        return out
+
+    def assign_grads(self, c):
+        """Set ``.grad`` of the grid leaves in ``c`` and of the trainable decoder parameters."""
+        for k in self.grid_grad_kinds:
+            c[GRID_KEYS[k]].grad = self.bucket.view_of(self.grids[k])
+        for k in self.dec_grad_kinds:
+            params = canonical_params(getattr(self.decoders, DEC_NAMES[k]), k)
+            for p, g in zip(params, self.decoder_grads(k)):
+                p.grad = g

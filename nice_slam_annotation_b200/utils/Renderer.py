@@ -47,8 +47,15 @@ class Renderer(object):
                 rets.append(fused.eval_points(pi, decoders, c, stage, self.bound, self.coarse_bound_enlarge))
         return torch.cat(rets, dim=0) if len(rets) != 1 else rets[0]
 
-    def render_batch_ray(self, c, decoders, rays_d, rays_o, device, stage, gt_depth=None):
-        """Depth, uncertainty and colour of a batch of rays (Renderer.py:95-262)."""
+    def fixed_shape_ok(self):
+        """True when a pre-filter mask can replace batch compaction without changing any value:
+        no jitter draws (their count depends on the batch size) and a single sampling pass."""
+        return bool(self.nice) and self.perturb == 0. and self.N_importance == 0
+
+    def render_batch_ray(self, c, decoders, rays_d, rays_o, device, stage, gt_depth=None, keep=None):
+        """Depth, uncertainty and colour of a batch of rays (Renderer.py:95-262).  ``keep``
+        (extension, [N] uint8): rays a caller would have dropped by the box pre-filter; they are
+        rendered but excluded from the batch depth max (see fixed_shape_ok)."""
         self._require_nice()
         N = rays_o.shape[0]
         u = u_imp = None
@@ -64,7 +71,7 @@ class Renderer(object):
             None if gt_depth is None else gt_depth.to(device), self.bound,
             N_samples=self.N_samples, N_surface=self.N_surface, N_importance=self.N_importance,
             lindisp=self.lindisp, occupancy=self.occupancy, u=u, u_importance=u_imp,
-            coarse_bound_enlarge=self.coarse_bound_enlarge)
+            coarse_bound_enlarge=self.coarse_bound_enlarge, keep=keep)
 
     def render_img(self, c, decoders, c2w, device, stage, gt_depth=None):
         """Full-image rendering in ray batches (Renderer.py:264-340): depth [H,W] f64,
