@@ -225,6 +225,10 @@ int nsb_pose_grad(const float* g_rays_o, const float* g_rays_d, const int64_t* i
                   const uint8_t* keep, int64_t n, int H0, int W0, int Wc, float fx, float fy,
                   float cx, float cy, const float* cam7, float* d_cam7, void* stream);
 
+/* test hook: D[128,N] = A[128,K] W[N,K]^T on the tcgen05 tensor cores (kind::tf32).  mode bit 0:
+ * A operand from tensor memory instead of shared memory; bit 1: 3xTF32 error compensation. */
+int nsb_tc_selftest(const float* A, const float* W, float* D, int K, int N, int mode, void* stream);
+
 /* ---- whole render call ---------------------------------------------------------------------
  * Renderer.render_batch_ray (src/utils/Renderer.py:95-262) without importance resampling, and
  * its backward, as ONE host call each: depth max -> sample depths -> decoders -> compositing
