@@ -90,10 +90,44 @@ static void put_block(int32_t* tab, int off, int J, int NT, SlotF slot, ColF col
             }
 }
 
+// tcgen05 section (nsb_layout.h TcCfg): constants and K-major operand images
+template <int KIND>
+static void build_tc_table(int32_t* tab) {
+    using C = DecCfg<KIND>;
+    using T = TcCfg<KIND>;
+    if constexpr (T::ENABLED) {
+        for (int a = 0; a < 3; ++a)
+            for (int f = 0; f < EMB; ++f) tab[T::T_B + a * EMB_PAD + f] = enc(C::P_EMB, a * EMB + f);
+        for (int i = 0; i < 5; ++i)
+            for (int k = 0; k < HID; ++k) {
+                tab[T::T_BIAS + i * HID + k] = enc(C::P_B + i, k);
+                tab[T::T_BC + i * HID + k] = enc(C::P_BC + i, k);
+            }
+        for (int k = 0; k < C::NOUT; ++k) tab[T::T_BO + k] = enc(C::P_BO, k);
+        for (int n = 0; n < HID; ++n)
+            for (int k = 0; k < EMB; ++k) {
+                tab[T::T_WE + tc_kmajor_index(n, k, 64)] = enc(C::P_W + 0, n * C::in_dim(0) + k);
+                tab[T::T_WE + tc_kmajor_index(HID + n, k, 64)] = enc(C::P_W + 3, n * C::in_dim(3) + k);
+            }
+        for (int i = 0; i < 5; ++i)
+            for (int n = 0; n < HID; ++n)
+                for (int k = 0; k < T::CIN; ++k)
+                    tab[T::T_WC + tc_kmajor_index(HID * i + n, k, 5 * HID)] = enc(C::P_WC + i, n * T::CIN + k);
+        const int offW[5] = {-1, T::T_W1, T::T_W2, T::T_W3H, T::T_W4};
+        for (int i = 1; i < 5; ++i)
+            for (int n = 0; n < HID; ++n)
+                for (int k = 0; k < HID; ++k)
+                    tab[offW[i] + tc_kmajor_index(n, k, HID)] = enc(C::P_W + i, n * C::in_dim(i) + (i == 3 ? EMB : 0) + k);
+        for (int n = 0; n < C::NOUT; ++n)
+            for (int k = 0; k < HID; ++k) tab[T::T_WO + tc_kmajor_index(n, k, T::NO)] = enc(C::P_WO, n * HID + k);
+    }
+}
+
 template <int KIND>
 static void build_table(int32_t* tab) {
     using C = DecCfg<KIND>;
-    for (int i = 0; i < C::TOTAL; ++i) tab[i] = -1;
+    for (int i = 0; i < BlobCfg<KIND>::TOTAL; ++i) tab[i] = -1;
+    build_tc_table<KIND>(tab + C::TOTAL);
     if (C::EMBED)
         for (int a = 0; a < 3; ++a)
             for (int f = 0; f < EMB; ++f) tab[C::OFF_B + a * EMB_PAD + f] = enc(C::P_EMB, a * EMB + f);
@@ -261,7 +295,7 @@ extern "C" int64_t nsb_flat_numel(int kind) {
 }
 
 extern "C" int64_t nsb_packed_numel(int kind) {
-    KIND_SWITCH(kind, return DecCfg<K>::TOTAL);
+    KIND_SWITCH(kind, return BlobCfg<K>::TOTAL);
     return 0;
 }
 

@@ -25,6 +25,7 @@
 //    transposed chain, turns d(e) into d(p) on the fly, scatters d(c) to the grid gradient
 //    with 128-bit vector reductions (red.global.add.v4.f32) and re-gathers the corners for
 //    the coordinate gradient.  Tiles whose incoming gradient is exactly zero are skipped.
+#include <cstdlib>
 #include <cstring>
 
 #include "nsb_common.cuh"
@@ -950,8 +951,13 @@ static void build_dw_tables(DwTables& T) {
     for (int o = 0; o < C::NOUT; ++o) add_bias(sDO, HID, o, off[C::P_BO] + o);
 }
 
+}  // namespace nsb
+#include "nsb_decoder_tc.cuh"
+namespace nsb {
+
 // ---- host side -------------------------------------------------------------------------------
 static int g_num_sms = 0;
+static int g_use_tc = 1;         // NSB_TC=0 selects the mma.sync kernels (A/B comparisons)
 static bool g_attr_done = false;
 constexpr int CTR_SLOTS = 256;                   // launches in flight before a counter slot is reused
 __device__ unsigned g_tile_ctr[CTR_SLOTS * 4];
@@ -985,7 +991,11 @@ static int init_device() {
     e = cudaFuncSetAttribute(k_decoders_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(k_decoders_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_decoders_forward_tc, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 TcSmem<KIND_FINE>::S_END * 4);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    if (const char* v = getenv("NSB_TC")) g_use_tc = atoi(v);
     build_dw_tables<KIND_COARSE>(g_dw_host[0]);
     build_dw_tables<KIND_MIDDLE>(g_dw_host[1]);
     build_dw_tables<KIND_FINE>(g_dw_host[2]);
@@ -1112,10 +1122,19 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
     sp.tile_begin = 0;
     sp.tile_end = (sp.pts.P + 15) / 16;
     sp.ctr = next_counters();
+    bool tc = g_use_tc != 0;
+    int tc_smem = 0;
+    for (int i = 0; i < sp.ntask; ++i) {
+        const int k = sp.task[i].kind;
+        if (k == KIND_COARSE) tc = false;
+        const int need = k == KIND_FINE ? TcSmem<KIND_FINE>::S_END : TcSmem<KIND_MIDDLE>::S_END;
+        if (need > tc_smem) tc_smem = need;
+    }
     timing_mark(0, 0, (cudaStream_t)stream);
-    k_decoders_forward<<<ctas, THREADS, max_blob(sp, false) * 4, (cudaStream_t)stream>>>(sp);
+    if (tc) k_decoders_forward_tc<<<ctas, TC_THREADS, tc_smem * 4, (cudaStream_t)stream>>>(sp);
+    else k_decoders_forward<<<ctas, THREADS, max_blob(sp, false) * 4, (cudaStream_t)stream>>>(sp);
     timing_mark(0, 1, (cudaStream_t)stream);
-    return check_launch("k_decoders_forward");
+    return check_launch(tc ? "k_decoders_forward_tc" : "k_decoders_forward");
 }
 
 // bytes of one tile's record + flag, sized for the largest decoder

@@ -1,0 +1,311 @@
+// tcgen05 version of the decoder forward (included by nsb_decoder.cu after the shared helpers).
+//
+// Same mathematics as k_decoders_forward -- trilinear gather, fp32 Fourier embedding, the
+// five-layer MLP with per-layer feature injection, 3xTF32 products with fp32 accumulation --
+// mapped on the 5th-generation tensor cores:
+//  * a CTA (128 threads) is bound to one decoder, keeps its weights in shared memory as tf32
+//    hi / lo operand images (UMMA K-major, no swizzle) and loops over 128-point tiles;
+//  * thread i owns point i of the tile == TMEM lane i: it computes the point, its embedding
+//    e = sin(p B) and, after every layer, the activation row h_i, and writes them (split into
+//    hi / lo) to tensor memory, where they are the A operands of the next MMAs (TS form);
+//  * the grid features are gathered cooperatively (8 lanes x 16 B per 128-byte voxel line, so
+//    every request is a fully used line) into a shared-memory operand tile (SS form);
+//  * one elected thread issues the MMAs: the embedding GEMM for layers 0 and 3 (N = 64) and the
+//    feature GEMM for all five layers (N = 160) up front, then the serial chain of 32 x 32
+//    layers; completion comes back through an mbarrier (tcgen05.commit);
+//  * accumulators live in tensor memory and are read back with tcgen05.ld for the bias / ReLU /
+//    feature-add epilogue of each layer.
+//
+// TMEM columns (512 allocated): e hi [0,96) | e lo [96,192) | acc E (layers 0, 3) [192,256) |
+// acc C (5 x 32) [256,416) | acc H [416,448) | acc out [448,464).  h hi / lo alias the first 32
+// columns of e hi / e lo (e is dead once the embedding GEMM has completed).
+#pragma once
+#include "nsb_tc.cuh"
+
+namespace nsb {
+
+constexpr int TC_THREADS = 128;
+constexpr int TM_EHI = 0, TM_ELO = 96, TM_ACCE = 192, TM_ACCC = 256, TM_ACCH = 416, TM_ACCO = 448;
+constexpr int TM_HHI = TM_EHI, TM_HLO = TM_ELO;
+constexpr int TRI_WORDS = 12;
+
+template <int KIND>
+struct TcSmem {      // float offsets in dynamic shared memory
+    using T = TcCfg<KIND>;
+    static constexpr int S_CONST = 0;
+    static constexpr int S_WHI = 640;                          // >= T_CONST_END, 128-byte aligned
+    static constexpr int S_WLO = S_WHI + T::W_FWD;
+    static constexpr int S_CHI = S_WLO + T::W_FWD;             // feature tile hi: 128 x 32, K-major image
+    static constexpr int S_CLO = S_CHI + 128 * CDIM;
+    static constexpr int S_TRI = S_CLO + 128 * CDIM;           // per point: voxel base / steps / coordinates
+    static constexpr int S_END = S_TRI + 128 * TRI_WORDS;
+    static_assert(T::T_CONST_END <= S_WHI, "constants overflow their slot");
+};
+
+// 3xTF32 product D (+)= A W^T with A in tensor memory: per K step of 8, lo*hi + hi*lo + hi*hi.
+// b_hi / b_lo are descriptors of an R-row K-major operand at K = 0; the next K step is 2R
+// 16-byte units further (nsb_tc.cuh).
+__device__ __forceinline__ void mma3_ts(uint32_t d, uint32_t a_hi, uint32_t a_lo, uint64_t b_hi, uint64_t b_lo, int R,
+                                        int ksteps, uint32_t idesc, bool accumulate) {
+    for (int ks = 0; ks < ksteps; ++ks) {
+        const uint64_t off = (uint64_t)(ks * 2 * R);
+        tc::mma_ts(d, a_lo + 8 * ks, b_hi + off, idesc, accumulate || ks > 0);
+        tc::mma_ts(d, a_hi + 8 * ks, b_lo + off, idesc, true);
+        tc::mma_ts(d, a_hi + 8 * ks, b_hi + off, idesc, true);
+    }
+}
+// same with A in shared memory (128-row K-major image)
+__device__ __forceinline__ void mma3_ss(uint32_t d, uint64_t a_hi, uint64_t a_lo, uint64_t b_hi, uint64_t b_lo, int R,
+                                        int ksteps, uint32_t idesc, bool accumulate) {
+    for (int ks = 0; ks < ksteps; ++ks) {
+        const uint64_t off = (uint64_t)(ks * 2 * R), aoff = (uint64_t)(ks * 2 * 128);
+        tc::mma_ss(d, a_lo + aoff, b_hi + off, idesc, accumulate || ks > 0);
+        tc::mma_ss(d, a_hi + aoff, b_lo + off, idesc, true);
+        tc::mma_ss(d, a_hi + aoff, b_hi + off, idesc, true);
+    }
+}
+
+// split 16 values and store them as the hi / lo A-operand columns [col, col + 16) of this lane
+__device__ __forceinline__ void st_split16(uint32_t lane_base, int col_hi, int col_lo, const float (&v)[16]) {
+    float h[16], l[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        uint32_t hi, lo;
+        split_tf32(v[j], hi, lo);
+        h[j] = __uint_as_float(hi);
+        l[j] = __uint_as_float(lo);
+    }
+    tc::tmem_st16(lane_base + col_hi, h);
+    tc::tmem_st16(lane_base + col_lo, l);
+}
+
+// Cooperative trilinear gather of one grid level for the warp's 32 points into the feature
+// operand tile.  The owner thread of a point publishes its voxel addressing (same arithmetic as
+// tri_setup / gather8, so the features are bit-identical to the mma.sync path); then 8 lanes
+// fetch the 8 x 16 B of every corner line.
+__device__ __forceinline__ void tc_gather_level(const GridDev& G, const float (&u)[3], float* s_tri, float* chi,
+                                                float* clo, int warp, int lane) {
+    {
+        Tri t = tri_setup(u, G);
+        float* e = s_tri + (warp * 32 + lane) * TRI_WORDS;
+        reinterpret_cast<int4*>(e)[0] = make_int4(t.base, t.sx, t.sy, t.sz);
+        reinterpret_cast<float4*>(e)[1] = make_float4(t.ix, t.iy, t.iz, t.x0);
+        reinterpret_cast<float2*>(e)[4] = make_float2(t.y0, t.z0);
+    }
+    __syncwarp();
+    const int sub = lane & 7;
+#pragma unroll 2
+    for (int r = 0; r < 8; ++r) {
+        const int q = warp * 32 + 4 * r + (lane >> 3);
+        const float* e = s_tri + q * TRI_WORDS;
+        const int4 a = reinterpret_cast<const int4*>(e)[0];
+        const float4 b = reinterpret_cast<const float4*>(e)[1];
+        const float2 c2 = reinterpret_cast<const float2*>(e)[4];
+        Tri t;
+        t.base = a.x; t.sx = a.y; t.sy = a.z; t.sz = a.w;
+        t.ix = b.x; t.iy = b.y; t.iz = b.z; t.x0 = b.w; t.y0 = c2.x; t.z0 = c2.y;
+        float4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            v[k] = __ldg(reinterpret_cast<const float4*>(G.data + (size_t)tri_offset(t, k) * CDIM + 4 * sub));
+        float f[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float w = tri_weight(t, k);
+            f[0] = fmaf(v[k].x, w, f[0]); f[1] = fmaf(v[k].y, w, f[1]);
+            f[2] = fmaf(v[k].z, w, f[2]); f[3] = fmaf(v[k].w, w, f[3]);
+        }
+        uint32_t h[4], l[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) split_tf32(f[j], h[j], l[j]);
+        const int idx = tc::kmajor_index(q, 4 * sub, 128);
+        *reinterpret_cast<uint4*>(chi + idx) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(clo + idx) = make_uint4(l[0], l[1], l[2], l[3]);
+    }
+    __syncwarp();
+}
+
+template <int KIND>
+__device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task, float* sm) {
+    using C = DecCfg<KIND>;
+    using TT = TcCfg<KIND>;
+    using S = TcSmem<KIND>;
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    __shared__ long long s_tile;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const float* blob = T.packed + C::TOTAL;                   // tcgen05 section of the packed blob
+    if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
+    if (tid == 0) {
+        tc::mbar_init(&bar, 1);
+        tc::mbar_init_fence();
+        s_tile = (long long)atomicAdd(P.ctr + task, 1u);
+    }
+    for (int i = tid; i < TT::T_CONST_END; i += TC_THREADS) sm[S::S_CONST + i] = __ldg(blob + i);
+    for (int i = tid; i < TT::W_FWD / 4; i += TC_THREADS) {
+        const float4 w = __ldg(reinterpret_cast<const float4*>(blob + TT::T_CONST_END) + i);
+        uint32_t h[4], l[4];
+        split_tf32(w.x, h[0], l[0]); split_tf32(w.y, h[1], l[1]);
+        split_tf32(w.z, h[2], l[2]); split_tf32(w.w, h[3], l[3]);
+        reinterpret_cast<uint4*>(sm + S::S_WHI)[i] = make_uint4(h[0], h[1], h[2], h[3]);
+        reinterpret_cast<uint4*>(sm + S::S_WLO)[i] = make_uint4(l[0], l[1], l[2], l[3]);
+    }
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tbase = tmem_slot;
+    const uint32_t lane_base = tc::tmem_addr(tbase, 32 * warp, 0);
+    const float* Bs = sm + S::S_CONST + TT::T_B;
+    const float* bias = sm + S::S_CONST + TT::T_BIAS;
+    const float* biasc = sm + S::S_CONST + TT::T_BC;
+    // operand descriptors at K = 0
+    const uint32_t whi = tc::smem_u32(sm + S::S_WHI), wlo = tc::smem_u32(sm + S::S_WLO);
+    auto wdesc = [&](uint32_t base, int off_floats, int R) {
+        return tc::kmajor_desc(base + 4u * (uint32_t)(off_floats - TT::T_CONST_END), R, 0);
+    };
+    const uint64_t d_chi = tc::kmajor_desc(tc::smem_u32(sm + S::S_CHI), 128, 0);
+    const uint64_t d_clo = tc::kmajor_desc(tc::smem_u32(sm + S::S_CLO), 128, 0);
+    constexpr uint32_t ID64 = tc::idesc_tf32(128, 64), ID160 = tc::idesc_tf32(128, 160), ID32 = tc::idesc_tf32(128, 32),
+                       ID16 = tc::idesc_tf32(128, 16);
+    uint32_t par = 0;                                          // mbarrier phase parity
+    const long long ntiles = (P.pts.P + 127) / 128;
+    for (;;) {
+        const long long tile = s_tile;
+        if (tile >= ntiles) break;
+        // ---- this thread's point --------------------------------------------------------------
+        const long long i = tile * 128 + tid;
+        const bool ok = i < P.pts.P;
+        const long long ii = ok ? i : P.pts.P - 1;
+        float p32[3], u[3];
+        if (P.pts.ro == nullptr && P.pts.p32 != nullptr) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                p32[a] = P.pts.p32[3 * ii + a];
+                u[a] = __fsub_rn(__fmul_rn(__fdiv_rn(__fsub_rn(p32[a], (float)T.lo[a]), (float)T.ext[a]), 2.f), 1.0f);
+            }
+        } else {
+            double p[3];
+            if (P.pts.ro) ray_point(P.pts, ii, p);
+            else { p[0] = P.pts.p64[3 * ii]; p[1] = P.pts.p64[3 * ii + 1]; p[2] = P.pts.p64[3 * ii + 2]; }
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                p32[a] = (float)p[a];
+                u[a] = (float)__dsub_rn(__dmul_rn(__ddiv_rn(__dsub_rn(p[a], T.lo[a]), T.ext[a]), 2.0), 1.0);
+            }
+        }
+        // ---- features of the decoder's own grid -> shared operand tile ---------------------------
+        tc_gather_level(T.own, u, sm + S::S_TRI, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
+        // ---- embedding e = sin(p B) -> tensor memory (hi / lo) ------------------------------------
+#pragma unroll 1
+        for (int c0 = 0; c0 < EMB_PAD; c0 += 16) {
+            float e[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) e[j] = sinf(phase(p32, Bs, c0 + j));
+            st_split16(lane_base, TM_EHI + c0, TM_ELO + c0, e);
+        }
+        tc::tmem_st_wait();
+        tc::fence_async_smem();
+        tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            tc::fence_after_sync();
+            s_tile = (long long)atomicAdd(P.ctr + task, 1u);       // next tile (everyone has read this one)
+            mma3_ts(tbase + TM_ACCE, tbase + TM_EHI, tbase + TM_ELO, wdesc(whi, TT::T_WE, 64), wdesc(wlo, TT::T_WE, 64),
+                    64, EMB_PAD / 8, ID64, false);
+            mma3_ss(tbase + TM_ACCC, d_chi, d_clo, wdesc(whi, TT::T_WC, 160), wdesc(wlo, TT::T_WC, 160), 160, CDIM / 8,
+                    ID160, false);
+            tc::mma_commit(&bar);
+        }
+        tc::mbar_wait(&bar, par);
+        par ^= 1;
+        tc::fence_after_sync();
+        if constexpr (KIND == KIND_FINE) {
+            // second half of the feature GEMM: the middle-grid feature (channels 32..63), no gradient
+            tc_gather_level(T.aux, u, sm + S::S_TRI, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
+            tc::fence_async_smem();
+            tc::fence_before_sync();
+            __syncthreads();
+            if (tid == 0) {
+                tc::fence_after_sync();
+                // K columns 32..63 of the 160-row operand: 4 K steps further
+                const uint64_t koff = (uint64_t)(4 * 2 * 160);
+                mma3_ss(tbase + TM_ACCC, d_chi, d_clo, wdesc(whi, TT::T_WC, 160) + koff, wdesc(wlo, TT::T_WC, 160) + koff,
+                        160, CDIM / 8, ID160, true);
+                tc::mma_commit(&bar);
+            }
+            tc::mbar_wait(&bar, par);
+            par ^= 1;
+            tc::fence_after_sync();
+        }
+        // ---- the layer chain ---------------------------------------------------------------------------
+#pragma unroll 1
+        for (int L = 0; L < 5; ++L) {
+            const int acc_col = L == 0 ? TM_ACCE : (L == 3 ? TM_ACCE + 32 : TM_ACCH);
+            float a[32], cc[32];
+            tc::tmem_ld16(lane_base + acc_col, *reinterpret_cast<float(*)[16]>(a));
+            tc::tmem_ld16(lane_base + acc_col + 16, *reinterpret_cast<float(*)[16]>(a + 16));
+            tc::tmem_ld16(lane_base + TM_ACCC + 32 * L, *reinterpret_cast<float(*)[16]>(cc));
+            tc::tmem_ld16(lane_base + TM_ACCC + 32 * L + 16, *reinterpret_cast<float(*)[16]>(cc + 16));
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                a[j] = (fmaxf(a[j] + bias[32 * L + j], 0.f) + biasc[32 * L + j]) + cc[j];
+            st_split16(lane_base, TM_HHI, TM_HLO, *reinterpret_cast<float(*)[16]>(a));
+            st_split16(lane_base, TM_HHI + 16, TM_HLO + 16, *reinterpret_cast<float(*)[16]>(a + 16));
+            tc::tmem_st_wait();
+            tc::fence_before_sync();
+            __syncthreads();
+            if (tid == 0) {
+                tc::fence_after_sync();
+                if (L < 4) {
+                    const int off = L == 0 ? TT::T_W1 : (L == 1 ? TT::T_W2 : (L == 2 ? TT::T_W3H : TT::T_W4));
+                    // layer 3 accumulates on top of its embedding part (the skip connection [e, h])
+                    mma3_ts(tbase + (L == 2 ? TM_ACCE + 32 : TM_ACCH), tbase + TM_HHI, tbase + TM_HLO, wdesc(whi, off, 32),
+                            wdesc(wlo, off, 32), 32, HID / 8, ID32, L == 2);
+                } else {
+                    mma3_ts(tbase + TM_ACCO, tbase + TM_HHI, tbase + TM_HLO, wdesc(whi, TT::T_WO, TT::NO),
+                            wdesc(wlo, TT::T_WO, TT::NO), TT::NO, HID / 8, ID16, false);
+                }
+                tc::mma_commit(&bar);
+            }
+            tc::mbar_wait(&bar, par);
+            par ^= 1;
+            tc::fence_after_sync();
+        }
+        {
+            float o[16];
+            tc::tmem_ld16(lane_base + TM_ACCO, o);
+            tc::tmem_ld_wait();
+            const float* bo = sm + S::S_CONST + TT::T_BO;
+            if (ok) {
+                if constexpr (C::NOUT == 1) T.out[i] = o[0] + bo[0];
+                else *reinterpret_cast<float4*>(T.out + 4 * i) = make_float4(o[0] + bo[0], o[1] + bo[1], o[2] + bo[2], o[3] + bo[3]);
+            }
+        }
+        // order this tile's tensor-memory reads before the next tile's writes of other threads
+        tc::fence_before_sync();
+        __syncthreads();
+        tc::fence_after_sync();
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc<512>(tbase);
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+k_decoders_forward_tc(const __grid_constant__ StageParams P) {
+    extern __shared__ __align__(16) float sm[];
+    int k = 0;
+    while (k + 1 < P.ntask && (int)blockIdx.x >= P.task[k + 1].cta_begin) ++k;
+    const DecTask& T = P.task[k];
+    switch (T.kind) {
+        case KIND_MIDDLE: tc_forward_cta<KIND_MIDDLE>(P, T, k, sm); break;
+        case KIND_FINE: tc_forward_cta<KIND_FINE>(P, T, k, sm); break;
+        case KIND_COLOR: tc_forward_cta<KIND_COLOR>(P, T, k, sm); break;
+        default: break;
+    }
+    release_counters(P.ctr);
+}
+
+}  // namespace nsb

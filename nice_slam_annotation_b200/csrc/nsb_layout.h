@@ -113,6 +113,45 @@ NSB_HD inline int col_gather(int n, int gamma) { return 8 * (gamma >> 1) + 2 * n
 
 }  // namespace nsb
 
+// ---- tcgen05 blob ------------------------------------------------------------------------------
+// Second section of the packed blob (after DecCfg::TOTAL floats), read by the tcgen05 kernels
+// (nsb_decoder_tc.cu).  Weight blocks are stored as the UMMA "K-major, no swizzle" operand
+// image of an R-row matrix: element (r, k) at float index
+//   ((k / 4) * (R / 8) + r / 8) * 32 + (r % 8) * 4 + (k % 4)          (nsb_tc.cuh kmajor_index)
+// so that a CTA copies them to shared memory verbatim (splitting every value into its tf32
+// hi / lo parts on the way) and addresses them with shared-memory matrix descriptors.
+namespace nsb {
+NSB_HD inline int tc_kmajor_index(int r, int k, int R) {
+    return ((k >> 2) * (R >> 3) + (r >> 3)) * 32 + (r & 7) * 4 + (k & 3);
+}
+template <int KIND>
+struct TcCfg {
+    using C = DecCfg<KIND>;
+    static constexpr bool ENABLED = C::EMBED;                  // coarse (MLP_no_xyz) stays on mma.sync
+    static constexpr int CIN = C::C_IN;
+    static constexpr int NO = 16;                              // padded output rows (UMMA N >= 16 at M = 128)
+    // constants: B [3][96], b [5][32], bc [5][32], bo [16]
+    static constexpr int T_B = 0;
+    static constexpr int T_BIAS = T_B + 3 * EMB_PAD;
+    static constexpr int T_BC = T_BIAS + 5 * HID;
+    static constexpr int T_BO = T_BC + 5 * HID;
+    static constexpr int T_CONST_END = T_BO + NO;              // 624
+    // forward weights (operand B of D = A W^T): R = output features, K = input features
+    static constexpr int T_WE = T_CONST_END;                   // R 64 : [W0 ; W3[:, :93]],  K 96
+    static constexpr int T_WC = T_WE + 64 * EMB_PAD;           // R 160: [Wc0 ; .. ; Wc4],   K CIN
+    static constexpr int T_W1 = T_WC + 5 * HID * CIN;          // R 32, K 32
+    static constexpr int T_W2 = T_W1 + HID * HID;
+    static constexpr int T_W3H = T_W2 + HID * HID;             // W3[:, 93:]
+    static constexpr int T_W4 = T_W3H + HID * HID;
+    static constexpr int T_WO = T_W4 + HID * HID;              // R 16 (rows >= NOUT zero), K 32
+    static constexpr int T_FWD_END = T_WO + NO * HID;
+    static constexpr int W_FWD = T_FWD_END - T_CONST_END;      // forward weight floats
+    static constexpr int TOTAL = ENABLED ? T_FWD_END : 0;
+};
+template <int KIND>
+struct BlobCfg { static constexpr int TOTAL = DecCfg<KIND>::TOTAL + TcCfg<KIND>::TOTAL; };
+}  // namespace nsb
+
 // ---- weight-gradient scratch record ---------------------------------------------------------
 // One record per 16-point tile, written by the backward kernel and consumed by k_dweight:
 // the layer inputs X and the output-side gradients G of every linear layer, each a dense
