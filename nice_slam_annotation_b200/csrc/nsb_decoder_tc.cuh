@@ -3,11 +3,13 @@
 // Same mathematics as k_decoders_forward -- trilinear gather, fp32 Fourier embedding, the
 // five-layer MLP with per-layer feature injection, 3xTF32 products with fp32 accumulation --
 // mapped on the 5th-generation tensor cores:
-//  * a CTA (128 threads) is bound to one decoder, keeps its weights in shared memory as tf32
+//  * a CTA (512 threads) is bound to one decoder, keeps its weights in shared memory as tf32
 //    hi / lo operand images (UMMA K-major, no swizzle) and loops over 128-point tiles;
-//  * thread i owns point i of the tile == TMEM lane i: it computes the point, its embedding
-//    e = sin(p B) and, after every layer, the activation row h_i, and writes them (split into
+//  * point i of the tile == TMEM lane i is served by FOUR threads (warps q, q+4, q+8, q+12 all
+//    address lane quadrant q): each computes a quarter of the point's embedding e = sin(p B)
+//    and, after every layer, a quarter of the activation row h_i, and writes them (split into
 //    hi / lo) to tensor memory, where they are the A operands of the next MMAs (TS form);
+//    sixteen warps per SM instead of four is what hides the sinf / gather / TMEM latencies;
 //  * the grid features are gathered cooperatively (8 lanes x 16 B per 128-byte voxel line, so
 //    every request is a fully used line) into a shared-memory operand tile (SS form);
 //  * one elected thread issues the MMAs: the embedding GEMM for layers 0 and 3 (N = 64) and the
@@ -24,7 +26,8 @@
 
 namespace nsb {
 
-constexpr int TC_THREADS = 128;
+constexpr int TC_THREADS = 512;
+constexpr int TC_PARTS = TC_THREADS / 128;      // threads per point
 constexpr int TM_EHI = 0, TM_ELO = 96, TM_ACCE = 192, TM_ACCC = 256, TM_ACCH = 416, TM_ACCO = 448;
 constexpr int TM_HHI = TM_EHI, TM_HLO = TM_ELO;
 constexpr int TRI_WORDS = 12;
@@ -37,8 +40,8 @@ struct TcSmem {      // float offsets in dynamic shared memory
     static constexpr int S_WLO = S_WHI + T::W_FWD;
     static constexpr int S_CHI = S_WLO + T::W_FWD;             // feature tile hi: 128 x 32, K-major image
     static constexpr int S_CLO = S_CHI + 128 * CDIM;
-    static constexpr int S_TRI = S_CLO + 128 * CDIM;           // per point: voxel base / steps / coordinates
-    static constexpr int S_END = S_TRI + 128 * TRI_WORDS;
+    static constexpr int S_TRI = S_CLO + 128 * CDIM;           // per point and level: voxel base / steps / coordinates
+    static constexpr int S_END = S_TRI + (KIND == KIND_FINE ? 2 : 1) * 128 * TRI_WORDS;
     static_assert(T::T_CONST_END <= S_WHI, "constants overflow their slot");
 };
 
@@ -65,38 +68,37 @@ __device__ __forceinline__ void mma3_ss(uint32_t d, uint64_t a_hi, uint64_t a_lo
     }
 }
 
-// split 16 values and store them as the hi / lo A-operand columns [col, col + 16) of this lane
-__device__ __forceinline__ void st_split16(uint32_t lane_base, int col_hi, int col_lo, const float (&v)[16]) {
-    float h[16], l[16];
+// split 8 values and store them as the hi / lo A-operand columns [col, col + 8) of this lane
+__device__ __forceinline__ void st_split8(uint32_t lane_base, int col_hi, int col_lo, const float (&v)[8]) {
+    float h[8], l[8];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
+    for (int j = 0; j < 8; ++j) {
         uint32_t hi, lo;
         split_tf32(v[j], hi, lo);
         h[j] = __uint_as_float(hi);
         l[j] = __uint_as_float(lo);
     }
-    tc::tmem_st16(lane_base + col_hi, h);
-    tc::tmem_st16(lane_base + col_lo, l);
+    tc::tmem_st8(lane_base + col_hi, h);
+    tc::tmem_st8(lane_base + col_lo, l);
 }
 
-// Cooperative trilinear gather of one grid level for the warp's 32 points into the feature
-// operand tile.  The owner thread of a point publishes its voxel addressing (same arithmetic as
-// tri_setup / gather8, so the features are bit-identical to the mma.sync path); then 8 lanes
-// fetch the 8 x 16 B of every corner line.
-__device__ __forceinline__ void tc_gather_level(const GridDev& G, const float (&u)[3], float* s_tri, float* chi,
-                                                float* clo, int warp, int lane) {
-    {
-        Tri t = tri_setup(u, G);
-        float* e = s_tri + (warp * 32 + lane) * TRI_WORDS;
-        reinterpret_cast<int4*>(e)[0] = make_int4(t.base, t.sx, t.sy, t.sz);
-        reinterpret_cast<float4*>(e)[1] = make_float4(t.ix, t.iy, t.iz, t.x0);
-        reinterpret_cast<float2*>(e)[4] = make_float2(t.y0, t.z0);
-    }
-    __syncwarp();
+// Cooperative trilinear gather of one grid level for the tile's 128 points into the feature
+// operand tile.  One thread per point publishes the voxel addressing (same arithmetic as
+// tri_setup / gather8, so the features are bit-identical to the mma.sync path); after a CTA
+// barrier 8 lanes fetch the 8 x 16 B of every corner line: 4 points per warp per round, 16 warps.
+__device__ __forceinline__ void tc_publish_tri(const GridDev& G, const float (&u)[3], float* s_tri, int row) {
+    Tri t = tri_setup(u, G);
+    float* e = s_tri + row * TRI_WORDS;
+    reinterpret_cast<int4*>(e)[0] = make_int4(t.base, t.sx, t.sy, t.sz);
+    reinterpret_cast<float4*>(e)[1] = make_float4(t.ix, t.iy, t.iz, t.x0);
+    reinterpret_cast<float2*>(e)[4] = make_float2(t.y0, t.z0);
+}
+__device__ __forceinline__ void tc_gather_level(const GridDev& G, const float* s_tri, float* chi, float* clo,
+                                                int warp, int lane) {
     const int sub = lane & 7;
-#pragma unroll 2
-    for (int r = 0; r < 8; ++r) {
-        const int q = warp * 32 + 4 * r + (lane >> 3);
+#pragma unroll
+    for (int r = 0; r < 128 / (4 * (TC_THREADS / 32)); ++r) {
+        const int q = (r * (TC_THREADS / 32) + warp) * 4 + (lane >> 3);
         const float* e = s_tri + q * TRI_WORDS;
         const int4 a = reinterpret_cast<const int4*>(e)[0];
         const float4 b = reinterpret_cast<const float4*>(e)[1];
@@ -122,7 +124,6 @@ __device__ __forceinline__ void tc_gather_level(const GridDev& G, const float (&
         *reinterpret_cast<uint4*>(chi + idx) = make_uint4(h[0], h[1], h[2], h[3]);
         *reinterpret_cast<uint4*>(clo + idx) = make_uint4(l[0], l[1], l[2], l[3]);
     }
-    __syncwarp();
 }
 
 template <int KIND>
@@ -134,6 +135,8 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     __shared__ uint32_t tmem_slot;
     __shared__ long long s_tile;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int quad = warp & 3, part = warp >> 2;               // TMEM lane quadrant, share of the row's work
+    const int row = 32 * quad + lane;                          // point of the tile == TMEM lane
     const float* blob = T.packed + C::TOTAL;                   // tcgen05 section of the packed blob
     if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
     if (tid == 0) {
@@ -142,6 +145,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         s_tile = (long long)atomicAdd(P.ctr + task, 1u);
     }
     for (int i = tid; i < TT::T_CONST_END; i += TC_THREADS) sm[S::S_CONST + i] = __ldg(blob + i);
+#pragma unroll 4
     for (int i = tid; i < TT::W_FWD / 4; i += TC_THREADS) {
         const float4 w = __ldg(reinterpret_cast<const float4*>(blob + TT::T_CONST_END) + i);
         uint32_t h[4], l[4];
@@ -155,10 +159,11 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tbase = tmem_slot;
-    const uint32_t lane_base = tc::tmem_addr(tbase, 32 * warp, 0);
+    const uint32_t lane_base = tc::tmem_addr(tbase, 32 * quad, 0);
     const float* Bs = sm + S::S_CONST + TT::T_B;
     const float* bias = sm + S::S_CONST + TT::T_BIAS;
     const float* biasc = sm + S::S_CONST + TT::T_BC;
+    float* s_tri = sm + S::S_TRI;
     // operand descriptors at K = 0
     const uint32_t whi = tc::smem_u32(sm + S::S_WHI), wlo = tc::smem_u32(sm + S::S_WLO);
     auto wdesc = [&](uint32_t base, int off_floats, int R) {
@@ -168,13 +173,16 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     const uint64_t d_clo = tc::kmajor_desc(tc::smem_u32(sm + S::S_CLO), 128, 0);
     constexpr uint32_t ID64 = tc::idesc_tf32(128, 64), ID160 = tc::idesc_tf32(128, 160), ID32 = tc::idesc_tf32(128, 32),
                        ID16 = tc::idesc_tf32(128, 16);
+    constexpr int EPP = EMB_PAD / TC_PARTS;                    // embedding features per thread (24)
+    constexpr int HPP = HID / TC_PARTS;                        // hidden columns per thread (8)
+    static_assert(EPP % 8 == 0 && HPP == 8, "per-thread shares are whole 8-column TMEM accesses");
     uint32_t par = 0;                                          // mbarrier phase parity
     const long long ntiles = (P.pts.P + 127) / 128;
     for (;;) {
         const long long tile = s_tile;
         if (tile >= ntiles) break;
-        // ---- this thread's point --------------------------------------------------------------
-        const long long i = tile * 128 + tid;
+        // ---- the point of this thread's row (all four threads of a row compute it) ----------------
+        const long long i = tile * 128 + row;
         const bool ok = i < P.pts.P;
         const long long ii = ok ? i : P.pts.P - 1;
         float p32[3], u[3];
@@ -194,15 +202,19 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
                 u[a] = (float)__dsub_rn(__dmul_rn(__ddiv_rn(__dsub_rn(p[a], T.lo[a]), T.ext[a]), 2.0), 1.0);
             }
         }
+        if (part == 0) tc_publish_tri(T.own, u, s_tri, row);
+        if constexpr (KIND == KIND_FINE)
+            if (part == 1) tc_publish_tri(T.aux, u, s_tri + 128 * TRI_WORDS, row);
+        __syncthreads();
         // ---- features of the decoder's own grid -> shared operand tile ---------------------------
-        tc_gather_level(T.own, u, sm + S::S_TRI, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
-        // ---- embedding e = sin(p B) -> tensor memory (hi / lo) ------------------------------------
-#pragma unroll 1
-        for (int c0 = 0; c0 < EMB_PAD; c0 += 16) {
-            float e[16];
+        tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
+        // ---- this thread's quarter of the embedding e = sin(p B) -> tensor memory (hi / lo) --------
 #pragma unroll
-            for (int j = 0; j < 16; ++j) e[j] = sinf(phase(p32, Bs, c0 + j));
-            st_split16(lane_base, TM_EHI + c0, TM_ELO + c0, e);
+        for (int c0 = EPP * part; c0 < EPP * (part + 1); c0 += 8) {
+            float e[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) e[j] = sinf(phase(p32, Bs, c0 + j));
+            st_split8(lane_base, TM_EHI + c0, TM_ELO + c0, e);
         }
         tc::tmem_st_wait();
         tc::fence_async_smem();
@@ -222,7 +234,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         tc::fence_after_sync();
         if constexpr (KIND == KIND_FINE) {
             // second half of the feature GEMM: the middle-grid feature (channels 32..63), no gradient
-            tc_gather_level(T.aux, u, sm + S::S_TRI, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
+            tc_gather_level(T.aux, s_tri + 128 * TRI_WORDS, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
             tc::fence_async_smem();
             tc::fence_before_sync();
             __syncthreads();
@@ -238,21 +250,19 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             par ^= 1;
             tc::fence_after_sync();
         }
-        // ---- the layer chain ---------------------------------------------------------------------------
+        // ---- the layer chain: every thread finishes 8 columns of its row ------------------------------
+        const int hc = HPP * part;
 #pragma unroll 1
         for (int L = 0; L < 5; ++L) {
             const int acc_col = L == 0 ? TM_ACCE : (L == 3 ? TM_ACCE + 32 : TM_ACCH);
-            float a[32], cc[32];
-            tc::tmem_ld16(lane_base + acc_col, *reinterpret_cast<float(*)[16]>(a));
-            tc::tmem_ld16(lane_base + acc_col + 16, *reinterpret_cast<float(*)[16]>(a + 16));
-            tc::tmem_ld16(lane_base + TM_ACCC + 32 * L, *reinterpret_cast<float(*)[16]>(cc));
-            tc::tmem_ld16(lane_base + TM_ACCC + 32 * L + 16, *reinterpret_cast<float(*)[16]>(cc + 16));
+            float a[8], cc[8];
+            tc::tmem_ld8(lane_base + acc_col + hc, a);
+            tc::tmem_ld8(lane_base + TM_ACCC + 32 * L + hc, cc);
             tc::tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-                a[j] = (fmaxf(a[j] + bias[32 * L + j], 0.f) + biasc[32 * L + j]) + cc[j];
-            st_split16(lane_base, TM_HHI, TM_HLO, *reinterpret_cast<float(*)[16]>(a));
-            st_split16(lane_base, TM_HHI + 16, TM_HLO + 16, *reinterpret_cast<float(*)[16]>(a + 16));
+            for (int j = 0; j < 8; ++j)
+                a[j] = (fmaxf(a[j] + bias[32 * L + hc + j], 0.f) + biasc[32 * L + hc + j]) + cc[j];
+            st_split8(lane_base, TM_HHI + hc, TM_HLO + hc, a);
             tc::tmem_st_wait();
             tc::fence_before_sync();
             __syncthreads();
@@ -273,9 +283,9 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             par ^= 1;
             tc::fence_after_sync();
         }
-        {
-            float o[16];
-            tc::tmem_ld16(lane_base + TM_ACCO, o);
+        if (part == 0) {
+            float o[8];
+            tc::tmem_ld8(lane_base + TM_ACCO, o);
             tc::tmem_ld_wait();
             const float* bo = sm + S::S_CONST + TT::T_BO;
             if (ok) {
