@@ -220,7 +220,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
-        if (tid == 0) {
+        if (warp == 0 && tc::elect_one()) {
             tc::fence_after_sync();
             s_tile = (long long)atomicAdd(P.ctr + task, 1u);       // next tile (everyone has read this one)
             mma3_ts(tbase + TM_ACCE, tbase + TM_EHI, tbase + TM_ELO, wdesc(whi, TT::T_WE, 64), wdesc(wlo, TT::T_WE, 64),
@@ -238,7 +238,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             tc::fence_async_smem();
             tc::fence_before_sync();
             __syncthreads();
-            if (tid == 0) {
+            if (warp == 0 && tc::elect_one()) {
                 tc::fence_after_sync();
                 // K columns 32..63 of the 160-row operand: 4 K steps further
                 const uint64_t koff = (uint64_t)(4 * 2 * 160);
@@ -266,7 +266,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             tc::tmem_st_wait();
             tc::fence_before_sync();
             __syncthreads();
-            if (tid == 0) {
+            if (warp == 0 && tc::elect_one()) {
                 tc::fence_after_sync();
                 if (L < 4) {
                     const int off = L == 0 ? TT::T_W1 : (L == 1 ? TT::T_W2 : (L == 2 ? TT::T_W3H : TT::T_W4));
