@@ -18,9 +18,9 @@
 //  * accumulators live in tensor memory and are read back with tcgen05.ld for the bias / ReLU /
 //    feature-add epilogue of each layer.
 //
-// TMEM columns (512 allocated): e hi [0,96) | e lo [96,192) | acc E (layers 0, 3) [192,256) |
-// acc C (5 x 32) [256,416) | acc H [416,448) | acc out [448,464).  h hi / lo alias the first 32
-// columns of e hi / e lo (e is dead once the embedding GEMM has completed).
+// TMEM columns (all 512): e hi [0,96) | e lo [96,192) | acc E (layers 0, 3) [192,256) |
+// acc C (5 x 32) [256,416) | acc H [416,448) (the 16 output columns alias it) | h hi [448,480) |
+// h lo [480,512).
 #pragma once
 #include "nsb_tc.cuh"
 
@@ -28,8 +28,8 @@ namespace nsb {
 
 constexpr int TC_THREADS = 512;
 constexpr int TC_PARTS = TC_THREADS / 128;      // threads per point
-constexpr int TM_EHI = 0, TM_ELO = 96, TM_ACCE = 192, TM_ACCC = 256, TM_ACCH = 416, TM_ACCO = 448;
-constexpr int TM_HHI = TM_EHI, TM_HLO = TM_ELO;
+constexpr int TM_EHI = 0, TM_ELO = 96, TM_ACCE = 192, TM_ACCC = 256, TM_ACCH = 416, TM_ACCO = 416;
+constexpr int TM_HHI = 448, TM_HLO = 480;
 constexpr int TRI_WORDS = 12;
 
 template <int KIND>
@@ -126,6 +126,44 @@ __device__ __forceinline__ void tc_gather_level(const GridDev& G, const float* s
     }
 }
 
+// the point of row `row` of a tile: fp32 position (embedding input) and normalised grid coordinate
+template <int KIND>
+__device__ __forceinline__ void tc_load_point(const PointsDev& q, const DecTask& T, long long tile, int row,
+                                              float (&p32)[3], float (&u)[3], bool& ok, long long& i) {
+    i = tile * 128 + row;
+    ok = i < q.P;
+    const long long ii = ok ? i : q.P - 1;
+    if (q.ro == nullptr && q.p32 != nullptr) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            p32[a] = q.p32[3 * ii + a];
+            u[a] = __fsub_rn(__fmul_rn(__fdiv_rn(__fsub_rn(p32[a], (float)T.lo[a]), (float)T.ext[a]), 2.f), 1.0f);
+        }
+    } else {
+        double p[3];
+        if (q.ro) ray_point(q, ii, p);
+        else { p[0] = q.p64[3 * ii]; p[1] = q.p64[3 * ii + 1]; p[2] = q.p64[3 * ii + 2]; }
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            p32[a] = (float)p[a];
+            u[a] = (float)__dsub_rn(__dmul_rn(__ddiv_rn(__dsub_rn(p[a], T.lo[a]), T.ext[a]), 2.0), 1.0);
+        }
+    }
+}
+
+// 8 embedding features [c0, c0 + 8) of this thread's point -> tensor memory (hi / lo)
+__device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float* Bs, uint32_t lane_base, int c0) {
+    float e[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) e[j] = sinf(phase(p32, Bs, c0 + j));
+    st_split8(lane_base, TM_EHI + c0, TM_ELO + c0, e);
+}
+
+// Software pipeline: the inputs of tile n+1 (point, voxel addressing, feature gather, embedding)
+// are produced in the gaps of tile n's layer chain -- between issuing a layer's MMAs and waiting
+// for them -- so the ALU / memory work of one tile hides the tensor-core round trips of the
+// other.  The feature tile and the e columns are free for tile n+1 as soon as tile n's up-front
+// GEMMs have completed; h has its own columns for that reason.
 template <int KIND>
 __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task, float* sm) {
     using C = DecCfg<KIND>;
@@ -133,7 +171,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     using S = TcSmem<KIND>;
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint32_t tmem_slot;
-    __shared__ long long s_tile;
+    __shared__ long long s_tile[2];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int quad = warp & 3, part = warp >> 2;               // TMEM lane quadrant, share of the row's work
     const int row = 32 * quad + lane;                          // point of the tile == TMEM lane
@@ -142,7 +180,8 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     if (tid == 0) {
         tc::mbar_init(&bar, 1);
         tc::mbar_init_fence();
-        s_tile = (long long)atomicAdd(P.ctr + task, 1u);
+        s_tile[0] = (long long)atomicAdd(P.ctr + task, 1u);
+        s_tile[1] = (long long)atomicAdd(P.ctr + task, 1u);
     }
     for (int i = tid; i < TT::T_CONST_END; i += TC_THREADS) sm[S::S_CONST + i] = __ldg(blob + i);
 #pragma unroll 4
@@ -175,61 +214,44 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
                        ID16 = tc::idesc_tf32(128, 16);
     constexpr int EPP = EMB_PAD / TC_PARTS;                    // embedding features per thread (24)
     constexpr int HPP = HID / TC_PARTS;                        // hidden columns per thread (8)
-    static_assert(EPP % 8 == 0 && HPP == 8, "per-thread shares are whole 8-column TMEM accesses");
+    static_assert(EPP == 24 && HPP == 8, "per-thread shares are whole 8-column TMEM accesses");
     uint32_t par = 0;                                          // mbarrier phase parity
     const long long ntiles = (P.pts.P + 127) / 128;
-    for (;;) {
-        const long long tile = s_tile;
-        if (tile >= ntiles) break;
-        // ---- the point of this thread's row (all four threads of a row compute it) ----------------
-        const long long i = tile * 128 + row;
-        const bool ok = i < P.pts.P;
-        const long long ii = ok ? i : P.pts.P - 1;
-        float p32[3], u[3];
-        if (P.pts.ro == nullptr && P.pts.p32 != nullptr) {
-#pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                p32[a] = P.pts.p32[3 * ii + a];
-                u[a] = __fsub_rn(__fmul_rn(__fdiv_rn(__fsub_rn(p32[a], (float)T.lo[a]), (float)T.ext[a]), 2.f), 1.0f);
-            }
-        } else {
-            double p[3];
-            if (P.pts.ro) ray_point(P.pts, ii, p);
-            else { p[0] = P.pts.p64[3 * ii]; p[1] = P.pts.p64[3 * ii + 1]; p[2] = P.pts.p64[3 * ii + 2]; }
-#pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                p32[a] = (float)p[a];
-                u[a] = (float)__dsub_rn(__dmul_rn(__ddiv_rn(__dsub_rn(p[a], T.lo[a]), T.ext[a]), 2.0), 1.0);
-            }
-        }
+    // the up-front GEMMs of a tile: features x all five fc_c (N = 160) and e x [W0 ; W3e] (N = 64)
+    auto issue_input_gemms = [&]() {
+        mma3_ss(tbase + TM_ACCC, d_chi, d_clo, wdesc(whi, TT::T_WC, 160), wdesc(wlo, TT::T_WC, 160), 160, CDIM / 8,
+                ID160, false);
+        mma3_ts(tbase + TM_ACCE, tbase + TM_EHI, tbase + TM_ELO, wdesc(whi, TT::T_WE, 64), wdesc(wlo, TT::T_WE, 64), 64,
+                EMB_PAD / 8, ID64, false);
+        tc::mma_commit(&bar);
+    };
+
+    // ---- prologue: inputs and up-front GEMMs of the first tile ------------------------------------------
+    long long tile = s_tile[0];
+    int slot = 0;                      // s_tile[slot] is the current tile, s_tile[slot ^ 1] the next
+    float p32[3], u[3];
+    bool ok = false;
+    long long i = 0;
+    if (tile < ntiles) {
+        tc_load_point<KIND>(P.pts, T, tile, row, p32, u, ok, i);
         if (part == 0) tc_publish_tri(T.own, u, s_tri, row);
         if constexpr (KIND == KIND_FINE)
             if (part == 1) tc_publish_tri(T.aux, u, s_tri + 128 * TRI_WORDS, row);
         __syncthreads();
-        // ---- features of the decoder's own grid -> shared operand tile ---------------------------
         tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
-        // ---- this thread's quarter of the embedding e = sin(p B) -> tensor memory (hi / lo) --------
 #pragma unroll
-        for (int c0 = EPP * part; c0 < EPP * (part + 1); c0 += 8) {
-            float e[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) e[j] = sinf(phase(p32, Bs, c0 + j));
-            st_split8(lane_base, TM_EHI + c0, TM_ELO + c0, e);
-        }
+        for (int j = 0; j < 3; ++j) tc_embed8(p32, Bs, lane_base, EPP * part + 8 * j);
         tc::tmem_st_wait();
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
         if (warp == 0 && tc::elect_one()) {
             tc::fence_after_sync();
-            s_tile = (long long)atomicAdd(P.ctr + task, 1u);       // next tile (everyone has read this one)
-            mma3_ts(tbase + TM_ACCE, tbase + TM_EHI, tbase + TM_ELO, wdesc(whi, TT::T_WE, 64), wdesc(wlo, TT::T_WE, 64),
-                    64, EMB_PAD / 8, ID64, false);
-            mma3_ss(tbase + TM_ACCC, d_chi, d_clo, wdesc(whi, TT::T_WC, 160), wdesc(wlo, TT::T_WC, 160), 160, CDIM / 8,
-                    ID160, false);
-            tc::mma_commit(&bar);
+            issue_input_gemms();
         }
-        tc::mbar_wait(&bar, par);
+    }
+    while (tile < ntiles) {
+        tc::mbar_wait(&bar, par);          // up-front GEMMs of this tile
         par ^= 1;
         tc::fence_after_sync();
         if constexpr (KIND == KIND_FINE) {
@@ -240,8 +262,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             __syncthreads();
             if (warp == 0 && tc::elect_one()) {
                 tc::fence_after_sync();
-                // K columns 32..63 of the 160-row operand: 4 K steps further
-                const uint64_t koff = (uint64_t)(4 * 2 * 160);
+                const uint64_t koff = (uint64_t)(4 * 2 * 160);     // K columns 32..63: 4 K steps further
                 mma3_ss(tbase + TM_ACCC, d_chi, d_clo, wdesc(whi, TT::T_WC, 160) + koff, wdesc(wlo, TT::T_WC, 160) + koff,
                         160, CDIM / 8, ID160, true);
                 tc::mma_commit(&bar);
@@ -249,6 +270,18 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             tc::mbar_wait(&bar, par);
             par ^= 1;
             tc::fence_after_sync();
+        }
+        // ---- next tile: point and voxel addressing (published before the chain's first barrier) ----
+        const long long nxt = s_tile[slot ^ 1];
+        const bool has_next = nxt < ntiles;
+        float p32n[3] = {0.f, 0.f, 0.f}, un[3] = {0.f, 0.f, 0.f};
+        bool okn = false;
+        long long in_ = 0;
+        if (has_next) {
+            tc_load_point<KIND>(P.pts, T, nxt, row, p32n, un, okn, in_);
+            if (part == 0) tc_publish_tri(T.own, un, s_tri, row);
+            if constexpr (KIND == KIND_FINE)
+                if (part == 1) tc_publish_tri(T.aux, un, s_tri + 128 * TRI_WORDS, row);
         }
         // ---- the layer chain: every thread finishes 8 columns of its row ------------------------------
         const int hc = HPP * part;
@@ -268,6 +301,9 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             __syncthreads();
             if (warp == 0 && tc::elect_one()) {
                 tc::fence_after_sync();
+                // the tile after next: its slot holds the current tile index, which everyone has
+                // in a register by now, and several barriers separate this store from its readers
+                if (L == 0) s_tile[slot] = (long long)atomicAdd(P.ctr + task, 1u);
                 if (L < 4) {
                     const int off = L == 0 ? TT::T_W1 : (L == 1 ? TT::T_W2 : (L == 2 ? TT::T_W3H : TT::T_W4));
                     // layer 3 accumulates on top of its embedding part (the skip connection [e, h])
@@ -278,6 +314,11 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
                             wdesc(wlo, TT::T_WO, TT::NO), TT::NO, HID / 8, ID16, false);
                 }
                 tc::mma_commit(&bar);
+            }
+            // ---- a slice of the next tile's inputs while the tensor core works ------------------------
+            if (has_next) {
+                if (L == 0) tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
+                else if (L <= 3) tc_embed8(p32n, Bs, lane_base, EPP * part + 8 * (L - 1));
             }
             tc::mbar_wait(&bar, par);
             par ^= 1;
@@ -293,10 +334,23 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
                 else *reinterpret_cast<float4*>(T.out + 4 * i) = make_float4(o[0] + bo[0], o[1] + bo[1], o[2] + bo[2], o[3] + bo[3]);
             }
         }
-        // order this tile's tensor-memory reads before the next tile's writes of other threads
+        // this tile's tensor-memory reads and the next tile's operand writes are complete before
+        // the next tile's up-front GEMMs overwrite the accumulators
+        tc::tmem_st_wait();
+        tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
+        if (has_next && warp == 0 && tc::elect_one()) {
+            tc::fence_after_sync();
+            issue_input_gemms();
+        }
         tc::fence_after_sync();
+        tile = nxt;
+        slot ^= 1;
+        ok = okn;
+        i = in_;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { p32[a] = p32n[a]; u[a] = un[a]; }
     }
     tc::fence_before_sync();
     __syncthreads();
