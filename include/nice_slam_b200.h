@@ -229,6 +229,10 @@ int nsb_pose_grad(const float* g_rays_o, const float* g_rays_d, const int64_t* i
  * A operand from tensor memory instead of shared memory; bit 1: 3xTF32 error compensation. */
 int nsb_tc_selftest(const float* A, const float* W, float* D, int K, int N, int mode, void* stream);
 
+/* micro-benchmark: SM cycles for `count` tf32 MMAs (M 128, width N, K 8) issued back to back into
+ * `nacc` accumulators in rotation; out2[0] = issue cycles, out2[1] = cycles until all completed. */
+int nsb_tc_mma_latency(long long* out2, int N, int count, int nacc, void* stream);
+
 /* ---- whole render call ---------------------------------------------------------------------
  * Renderer.render_batch_ray (src/utils/Renderer.py:95-262) without importance resampling, and
  * its backward, as ONE host call each: depth max -> sample depths -> decoders -> compositing

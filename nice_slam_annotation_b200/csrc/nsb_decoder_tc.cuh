@@ -151,11 +151,33 @@ __device__ __forceinline__ void tc_load_point(const PointsDev& q, const DecTask&
     }
 }
 
+// sin(x) to ~1 ulp for |x| < 1e5: three-term Cody-Waite reduction to [-pi/4, pi/4] and the
+// cephes sinf / cosf minimax polynomials.  This is the fast path of the library sinf without its
+// inlined Payne-Hanek slow path: the embedding evaluates 96 sines per point per decoder, and the
+// inlined library version alone made the tile loop overflow the instruction cache
+// (stall_no_instruction was the top stall, profiles/r01).  |p . B| stays below ~1e3 in any scene
+// (B ~ N(0, 25^2), |p| of order 10 m); larger arguments take the library call, out of line.
+__device__ __noinline__ float sin_slow(float x) { return sinf(x); }
+__device__ __forceinline__ float sin_cw(float x) {
+    if (fabsf(x) > 1.0e5f) return sin_slow(x);
+    const float k = rintf(x * 0.636619772f);
+    float r = fmaf(k, -1.57079601e+00f, x);
+    r = fmaf(k, -3.13916473e-07f, r);
+    r = fmaf(k, -5.39030253e-15f, r);
+    const int q = (int)k;
+    const float r2 = r * r;
+    const float sp = fmaf(r * r2, fmaf(r2, fmaf(r2, -1.9515295891e-4f, 8.3321608736e-3f), -1.6666654611e-1f), r);
+    const float cp = fmaf(r2 * r2, fmaf(r2, fmaf(r2, 2.443315711809948e-5f, -1.388731625493765e-3f), 4.166664568298827e-2f),
+                          fmaf(r2, -0.5f, 1.0f));
+    const float v = (q & 1) ? cp : sp;
+    return (q & 2) ? -v : v;
+}
+
 // 8 embedding features [c0, c0 + 8) of this thread's point -> tensor memory (hi / lo)
 __device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float* Bs, uint32_t lane_base, int c0) {
     float e[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) e[j] = sinf(phase(p32, Bs, c0 + j));
+    for (int j = 0; j < 8; ++j) e[j] = sin_cw(phase(p32, Bs, c0 + j));
     st_split8(lane_base, TM_EHI + c0, TM_ELO + c0, e);
 }
 

@@ -99,9 +99,61 @@ k_tc_selftest(const float* __restrict__ A, const float* __restrict__ W, float* _
     if (warp == 0) tc::tmem_dealloc<512>(tbase);
 }
 
+// Micro-benchmark behind the kernel design: cycles for `count` tf32 MMAs of width N
+// (K = 8 each, A from tensor memory) issued back to back by one thread, accumulating into
+// `nacc` different accumulators in rotation (nacc = 1: one dependent chain).
+__global__ void __launch_bounds__(128, 1) k_tc_mma_latency(long long* out, int N, int count, int nacc) {
+    extern __shared__ __align__(128) float sm[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
+    if (tid == 0) { tc::mbar_init(&bar, 1); tc::mbar_init_fence(); }
+    for (int i = tid; i < 256 * 8; i += 128) sm[i] = 0.f;
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tbase = tmem_slot;
+    {
+        float z[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) z[j] = 0.f;
+        tc::tmem_st16(tc::tmem_addr(tbase, 32 * warp, 0), z);
+        tc::tmem_st_wait();
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0 && tc::elect_one()) {
+        tc::fence_after_sync();
+        const uint32_t idesc = tc::idesc_tf32(128, N);
+        const uint64_t b = tc::kmajor_desc(tc::smem_u32(sm), N, 0);
+        const long long t0 = clock64();
+        for (int i = 0; i < count; ++i)
+            tc::mma_ts(tbase + 16 + (uint32_t)((i % nacc) * N), tbase, b, idesc, i >= nacc);
+        tc::mma_commit(&bar);
+        const long long t1 = clock64();
+        tc::mbar_wait(&bar, 0);
+        const long long t2 = clock64();
+        out[0] = t1 - t0;
+        out[1] = t2 - t0;
+    }
+    __syncthreads();
+    tc::mbar_wait(&bar, 0);
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc<512>(tbase);
+}
+
 }  // namespace nsb
 
 using namespace nsb;
+
+extern "C" int nsb_tc_mma_latency(long long* out2, int N, int count, int nacc, void* stream) {
+    if (!out2 || N < 16 || N > 256 || N % 16 || nacc < 1 || 16 + nacc * N > 512) return set_error(NSB_EINVAL, "bad argument");
+    k_tc_mma_latency<<<1, 128, 256 * 8 * 4, (cudaStream_t)stream>>>(out2, N, count, nacc);
+    return check_launch("k_tc_mma_latency");
+}
 
 extern "C" int nsb_tc_selftest(const float* A, const float* W, float* D, int K, int N, int mode, void* stream) {
     if (!A || !W || !D) return set_error(NSB_EINVAL, "null argument");
