@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "csrc", "libnsb200.so")
+LIB_PATH = os.environ.get("NSB_LIB") or os.path.join(HERE, "csrc", "libnsb200.so")   # NSB_LIB: instrumented builds
 
 NSB_EINVAL, NSB_ENOSYS = -22, -38
 DEC_COARSE, DEC_MIDDLE, DEC_FINE, DEC_COLOR = 0, 1, 2, 3

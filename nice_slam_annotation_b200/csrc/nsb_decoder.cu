@@ -25,6 +25,7 @@
 //    transposed chain, turns d(e) into d(p) on the fly, scatters d(c) to the grid gradient
 //    with 128-bit vector reductions (red.global.add.v4.f32) and re-gathers the corners for
 //    the coordinate gradient.  Tiles whose incoming gradient is exactly zero are skipped.
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -59,6 +60,7 @@ struct StageParams {
     unsigned flags;
     long long tile_begin, tile_end;   // tiles of this launch (backward is chunked for d(W))
     unsigned* ctr;                    // [4]: next tile of task 0..2 (relative to tile_begin), CTAs done
+    long long* prof;                  // NSB_TC_PROFILE builds: per-phase cycle sums of one CTA per task
 };
 
 // Tiles are handed out dynamically: a warp takes the next tile of its CTA's decoder with one
@@ -1035,6 +1037,11 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
             }
             return set_error(NSB_EINVAL, "bad stage %d", stage);
     }
+    // measured cycles per 128-point tile of the tcgen05 forward (in-kernel timers, r01): the fine
+    // decoder pays a second feature pass
+    if (!bwd && g_use_tc)
+        for (int i = 0; i < n; ++i)
+            cost[i] = kinds[i] == KIND_MIDDLE ? 15.f : (kinds[i] == KIND_FINE ? 23.5f : (kinds[i] == KIND_COLOR ? 16.5f : cost[i]));
     const long long tiles = (P + 15) / 16;
     const long long want_ll = (tiles + WARPS - 1) / WARPS;   // CTAs that give every warp one tile
     const int want = want_ll > (1 << 20) ? (1 << 20) : (int)want_ll;
@@ -1122,6 +1129,11 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
     sp.tile_begin = 0;
     sp.tile_end = (sp.pts.P + 15) / 16;
     sp.ctr = next_counters();
+#ifdef NSB_TC_PROFILE
+    static long long* prof_dev = nullptr;
+    if (!prof_dev) cudaMalloc(&prof_dev, 72 * sizeof(long long));
+    sp.prof = prof_dev;
+#endif
     bool tc = g_use_tc != 0;
     int tc_smem = 0;
     for (int i = 0; i < sp.ntask; ++i) {
@@ -1134,6 +1146,20 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
     if (tc) k_decoders_forward_tc<<<ctas, TC_THREADS, tc_smem * 4, (cudaStream_t)stream>>>(sp);
     else k_decoders_forward<<<ctas, THREADS, max_blob(sp, false) * 4, (cudaStream_t)stream>>>(sp);
     timing_mark(0, 1, (cudaStream_t)stream);
+#ifdef NSB_TC_PROFILE
+    if (getenv("NSB_TC_PROFILE_PRINT")) {
+        long long h[72];
+        cudaMemcpy(h, prof_dev, sizeof(h), cudaMemcpyDeviceToHost);
+        const char* names[12] = {"setup+prologue", "wait upfront", "fine pass2", "next point", "epilogue", "barrier", "mma issue",
+                                 "next slice", "wait layer", "output", "end barrier", ""};
+        for (int t = 0; t < sp.ntask; ++t)
+            for (int w = 0; w < 2; ++w) {
+                fprintf(stderr, "[tcprof] task %d kind %d ctas %d %s:", t, sp.task[t].kind, sp.task[t].cta_count, w ? "thread200" : "thread0");
+                for (int k = 0; k < 11; ++k) fprintf(stderr, " %s=%lld", names[k], h[(t * 2 + w) * 12 + k]);
+                fprintf(stderr, "\n");
+            }
+    }
+#endif
     return check_launch(tc ? "k_decoders_forward_tc" : "k_decoders_forward");
 }
 

@@ -35,14 +35,16 @@ constexpr int TRI_WORDS = 12;
 template <int KIND>
 struct TcSmem {      // float offsets in dynamic shared memory
     using T = TcCfg<KIND>;
-    static constexpr int S_CONST = 0;
-    static constexpr int S_WHI = 640;                          // >= T_CONST_END, 128-byte aligned
+    static constexpr int S_CONST = 0;                          // T_CONST_END floats
+    static constexpr int S_BV = 640;                           // embedding matrix as [96] x float4
+    static constexpr int S_WHI = 1024;                         // 128-byte aligned
     static constexpr int S_WLO = S_WHI + T::W_FWD;
     static constexpr int S_CHI = S_WLO + T::W_FWD;             // feature tile hi: 128 x 32, K-major image
     static constexpr int S_CLO = S_CHI + 128 * CDIM;
     static constexpr int S_TRI = S_CLO + 128 * CDIM;           // per point and level: voxel base / steps / coordinates
-    static constexpr int S_END = S_TRI + (KIND == KIND_FINE ? 2 : 1) * 128 * TRI_WORDS;
-    static_assert(T::T_CONST_END <= S_WHI, "constants overflow their slot");
+    static constexpr int S_PT = S_TRI + (KIND == KIND_FINE ? 2 : 1) * 128 * TRI_WORDS;   // per point: p (fp32)
+    static constexpr int S_END = S_PT + 128 * 4;
+    static_assert(T::T_CONST_END <= S_BV, "constants overflow their slot");
 };
 
 // 3xTF32 product D (+)= A W^T with A in tensor memory: per K step of 8, lo*hi + hi*lo + hi*hi.
@@ -151,33 +153,37 @@ __device__ __forceinline__ void tc_load_point(const PointsDev& q, const DecTask&
     }
 }
 
-// sin(x) to ~1 ulp for |x| < 1e5: three-term Cody-Waite reduction to [-pi/4, pi/4] and the
-// cephes sinf / cosf minimax polynomials.  This is the fast path of the library sinf without its
-// inlined Payne-Hanek slow path: the embedding evaluates 96 sines per point per decoder, and the
-// inlined library version alone made the tile loop overflow the instruction cache
-// (stall_no_instruction was the top stall, profiles/r01).  |p . B| stays below ~1e3 in any scene
-// (B ~ N(0, 25^2), |p| of order 10 m); larger arguments take the library call, out of line.
+// sin(x) to ~2 ulp (1.3e-7 absolute) for |x| < 1e5: x = k pi + r by a three-term Cody-Waite
+// reduction, a degree-9 odd minimax polynomial on [-pi/2, pi/2] (approximation error 5e-9) and
+// the sign (-1)^k.  14 instructions instead of the ~27 of the library sinf fast path (whose
+// inlined Payne-Hanek slow path also overflowed the instruction cache): the embedding evaluates
+// 96 sines per point per decoder and was the largest block of issue slots in this kernel
+// (profiles/r01).  |p . B| stays below ~1e3 in any scene (B ~ N(0, 25^2), |p| of order 10 m);
+// larger arguments take the library call, out of line.
 __device__ __noinline__ float sin_slow(float x) { return sinf(x); }
 __device__ __forceinline__ float sin_cw(float x) {
     if (fabsf(x) > 1.0e5f) return sin_slow(x);
-    const float k = rintf(x * 0.636619772f);
-    float r = fmaf(k, -1.57079601e+00f, x);
-    r = fmaf(k, -3.13916473e-07f, r);
-    r = fmaf(k, -5.39030253e-15f, r);
-    const int q = (int)k;
+    const float k = rintf(x * 0.318309886f);
+    float r = fmaf(k, -3.14159202e+00f, x);
+    r = fmaf(k, -6.27832946e-07f, r);
+    r = fmaf(k, -1.078060506e-14f, r);
     const float r2 = r * r;
-    const float sp = fmaf(r * r2, fmaf(r2, fmaf(r2, -1.9515295891e-4f, 8.3321608736e-3f), -1.6666654611e-1f), r);
-    const float cp = fmaf(r2 * r2, fmaf(r2, fmaf(r2, 2.443315711809948e-5f, -1.388731625493765e-3f), 4.166664568298827e-2f),
-                          fmaf(r2, -0.5f, 1.0f));
-    const float v = (q & 1) ? cp : sp;
-    return (q & 2) ? -v : v;
+    float q = fmaf(r2, 2.6000477646e-06f, -1.9806619093e-04f);
+    q = fmaf(r2, q, 8.3330171183e-03f);
+    q = fmaf(r2, q, -1.6666656733e-01f);
+    const float v = fmaf(r * r2, q, r);
+    return __uint_as_float(__float_as_uint(v) ^ ((uint32_t)(int)k << 31));
 }
 
 // 8 embedding features [c0, c0 + 8) of this thread's point -> tensor memory (hi / lo)
-__device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float* Bs, uint32_t lane_base, int c0) {
+// (Bv: [feature] -> (B[0][f], B[1][f], B[2][f], 0); same operation order as phase())
+__device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float4* Bv, uint32_t lane_base, int c0) {
     float e[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) e[j] = sin_cw(phase(p32, Bs, c0 + j));
+    for (int j = 0; j < 8; ++j) {
+        const float4 b = Bv[c0 + j];
+        e[j] = sin_cw(fmaf(p32[2], b.z, fmaf(p32[1], b.y, p32[0] * b.x)));
+    }
     st_split8(lane_base, TM_EHI + c0, TM_ELO + c0, e);
 }
 
@@ -206,6 +212,10 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         s_tile[1] = (long long)atomicAdd(P.ctr + task, 1u);
     }
     for (int i = tid; i < TT::T_CONST_END; i += TC_THREADS) sm[S::S_CONST + i] = __ldg(blob + i);
+    if (tid < EMB_PAD)
+        reinterpret_cast<float4*>(sm + S::S_BV)[tid] =
+            make_float4(__ldg(blob + TT::T_B + tid), __ldg(blob + TT::T_B + EMB_PAD + tid),
+                        __ldg(blob + TT::T_B + 2 * EMB_PAD + tid), 0.f);
 #pragma unroll 4
     for (int i = tid; i < TT::W_FWD / 4; i += TC_THREADS) {
         const float4 w = __ldg(reinterpret_cast<const float4*>(blob + TT::T_CONST_END) + i);
@@ -221,7 +231,8 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     tc::fence_after_sync();
     const uint32_t tbase = tmem_slot;
     const uint32_t lane_base = tc::tmem_addr(tbase, 32 * quad, 0);
-    const float* Bs = sm + S::S_CONST + TT::T_B;
+    const float4* Bv = reinterpret_cast<const float4*>(sm + S::S_BV);
+    float4* s_pt = reinterpret_cast<float4*>(sm + S::S_PT);
     const float* bias = sm + S::S_CONST + TT::T_BIAS;
     const float* biasc = sm + S::S_CONST + TT::T_BC;
     float* s_tri = sm + S::S_TRI;
@@ -239,6 +250,12 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     static_assert(EPP == 24 && HPP == 8, "per-thread shares are whole 8-column TMEM accesses");
     uint32_t par = 0;                                          // mbarrier phase parity
     const long long ntiles = (P.pts.P + 127) / 128;
+#ifdef NSB_TC_PROFILE
+    long long tq[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
+#define TQ(k) { const long long tn_ = clock64(); tq[k] += tn_ - tlast; tlast = tn_; }
+#else
+#define TQ(k)
+#endif
     // the up-front GEMMs of a tile: features x all five fc_c (N = 160) and e x [W0 ; W3e] (N = 64)
     auto issue_input_gemms = [&]() {
         mma3_ss(tbase + TM_ACCC, d_chi, d_clo, wdesc(whi, TT::T_WC, 160), wdesc(wlo, TT::T_WC, 160), 160, CDIM / 8,
@@ -251,18 +268,28 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     // ---- prologue: inputs and up-front GEMMs of the first tile ------------------------------------------
     long long tile = s_tile[0];
     int slot = 0;                      // s_tile[slot] is the current tile, s_tile[slot ^ 1] the next
-    float p32[3], u[3];
-    bool ok = false;
-    long long i = 0;
+    // one thread per point (part 0) evaluates the fp64 point and publishes it for the other three
+    auto publish_point = [&](long long t) {
+        if (part == 0) {
+            float p32[3], u[3];
+            bool ok_;
+            long long i_;
+            tc_load_point<KIND>(P.pts, T, t, row, p32, u, ok_, i_);
+            s_pt[row] = make_float4(p32[0], p32[1], p32[2], 0.f);
+            tc_publish_tri(T.own, u, s_tri, row);
+            if constexpr (KIND == KIND_FINE) tc_publish_tri(T.aux, u, s_tri + 128 * TRI_WORDS, row);
+        }
+    };
     if (tile < ntiles) {
-        tc_load_point<KIND>(P.pts, T, tile, row, p32, u, ok, i);
-        if (part == 0) tc_publish_tri(T.own, u, s_tri, row);
-        if constexpr (KIND == KIND_FINE)
-            if (part == 1) tc_publish_tri(T.aux, u, s_tri + 128 * TRI_WORDS, row);
+        publish_point(tile);
         __syncthreads();
         tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
+        {
+            const float4 pp = s_pt[row];
+            const float p32[3] = {pp.x, pp.y, pp.z};
 #pragma unroll
-        for (int j = 0; j < 3; ++j) tc_embed8(p32, Bs, lane_base, EPP * part + 8 * j);
+            for (int j = 0; j < 3; ++j) tc_embed8(p32, Bv, lane_base, EPP * part + 8 * j);
+        }
         tc::tmem_st_wait();
         tc::fence_async_smem();
         tc::fence_before_sync();
@@ -272,10 +299,12 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             issue_input_gemms();
         }
     }
+    TQ(0)      // set-up + prologue
     while (tile < ntiles) {
         tc::mbar_wait(&bar, par);          // up-front GEMMs of this tile
         par ^= 1;
         tc::fence_after_sync();
+        TQ(1)  // wait for the up-front GEMMs
         if constexpr (KIND == KIND_FINE) {
             // second half of the feature GEMM: the middle-grid feature (channels 32..63), no gradient
             tc_gather_level(T.aux, s_tri + 128 * TRI_WORDS, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
@@ -293,18 +322,12 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             par ^= 1;
             tc::fence_after_sync();
         }
+        TQ(2)  // fine: second feature pass
         // ---- next tile: point and voxel addressing (published before the chain's first barrier) ----
         const long long nxt = s_tile[slot ^ 1];
         const bool has_next = nxt < ntiles;
-        float p32n[3] = {0.f, 0.f, 0.f}, un[3] = {0.f, 0.f, 0.f};
-        bool okn = false;
-        long long in_ = 0;
-        if (has_next) {
-            tc_load_point<KIND>(P.pts, T, nxt, row, p32n, un, okn, in_);
-            if (part == 0) tc_publish_tri(T.own, un, s_tri, row);
-            if constexpr (KIND == KIND_FINE)
-                if (part == 1) tc_publish_tri(T.aux, un, s_tri + 128 * TRI_WORDS, row);
-        }
+        if (has_next) publish_point(nxt);
+        TQ(3)  // next tile's point + publish
         // ---- the layer chain: every thread finishes 8 columns of its row ------------------------------
         const int hc = HPP * part;
 #pragma unroll 1
@@ -320,7 +343,9 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             st_split8(lane_base, TM_HHI + hc, TM_HLO + hc, a);
             tc::tmem_st_wait();
             tc::fence_before_sync();
+            TQ(4)  // layer epilogue (ld, alu, st)
             __syncthreads();
+            TQ(5)  // barrier
             if (warp == 0 && tc::elect_one()) {
                 tc::fence_after_sync();
                 // the tile after next: its slot holds the current tile index, which everyone has
@@ -337,21 +362,29 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
                 }
                 tc::mma_commit(&bar);
             }
+            TQ(6)  // MMA issue (warp 0)
             // ---- a slice of the next tile's inputs while the tensor core works ------------------------
             if (has_next) {
                 if (L == 0) tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
-                else if (L <= 3) tc_embed8(p32n, Bs, lane_base, EPP * part + 8 * (L - 1));
+                else if (L <= 3) {
+                    const float4 pp = s_pt[row];
+                    const float p32n[3] = {pp.x, pp.y, pp.z};
+                    tc_embed8(p32n, Bv, lane_base, EPP * part + 8 * (L - 1));
+                }
             }
+            TQ(7)  // next tile's slice
             tc::mbar_wait(&bar, par);
             par ^= 1;
             tc::fence_after_sync();
+            TQ(8)  // wait for the layer's MMAs
         }
         if (part == 0) {
             float o[8];
             tc::tmem_ld8(lane_base + TM_ACCO, o);
             tc::tmem_ld_wait();
             const float* bo = sm + S::S_CONST + TT::T_BO;
-            if (ok) {
+            const long long i = tile * 128 + row;
+            if (i < P.pts.P) {
                 if constexpr (C::NOUT == 1) T.out[i] = o[0] + bo[0];
                 else *reinterpret_cast<float4*>(T.out + 4 * i) = make_float4(o[0] + bo[0], o[1] + bo[1], o[2] + bo[2], o[3] + bo[3]);
             }
@@ -361,19 +394,21 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         tc::tmem_st_wait();
         tc::fence_async_smem();
         tc::fence_before_sync();
+        TQ(9)  // output
         __syncthreads();
         if (has_next && warp == 0 && tc::elect_one()) {
             tc::fence_after_sync();
             issue_input_gemms();
         }
         tc::fence_after_sync();
+        TQ(10) // end-of-tile barrier + up-front GEMM issue
         tile = nxt;
         slot ^= 1;
-        ok = okn;
-        i = in_;
-#pragma unroll
-        for (int a = 0; a < 3; ++a) { p32[a] = p32n[a]; u[a] = un[a]; }
     }
+#ifdef NSB_TC_PROFILE
+    if ((tid == 0 || tid == 200) && (int)blockIdx.x == T.cta_begin && P.prof)
+        for (int k = 0; k < 12; ++k) P.prof[(task * 2 + (tid != 0)) * 12 + k] = tq[k];
+#endif
     tc::fence_before_sync();
     __syncthreads();
     if (warp == 0) tc::tmem_dealloc<512>(tbase);
