@@ -33,6 +33,9 @@
 
 namespace nsb {
 
+__device__ __noinline__ float sin_slow(float x) { return sinf(x); }
+__device__ __noinline__ float cos_slow(float x) { return cosf(x); }
+
 struct GridDev {
     const float* data;
     float* grad;
@@ -234,10 +237,10 @@ __device__ __forceinline__ void embed_to_smem(const Rows& R, const float* Bs, in
 #pragma unroll 1
     for (int j = 0; j < E_SLABS; ++j) {
         const int f0 = 8 * j + t, f1 = f0 + 4;
-        es[esw(g, f0)] = sinf(phase(R.p[0], Bs, f0));
-        es[esw(g + 8, f0)] = sinf(phase(R.p[1], Bs, f0));
-        es[esw(g, f1)] = sinf(phase(R.p[0], Bs, f1));
-        es[esw(g + 8, f1)] = sinf(phase(R.p[1], Bs, f1));
+        es[esw(g, f0)] = sin_cw(phase(R.p[0], Bs, f0));
+        es[esw(g + 8, f0)] = sin_cw(phase(R.p[1], Bs, f0));
+        es[esw(g, f1)] = sin_cw(phase(R.p[0], Bs, f1));
+        es[esw(g + 8, f1)] = sin_cw(phase(R.p[1], Bs, f1));
     }
 }
 
@@ -461,10 +464,13 @@ k_decoders_forward(const __grid_constant__ StageParams P) {
 
 // ---- backward -------------------------------------------------------------------------------
 // d(a) (A fragments, chain map) -> d(e) = d(a) W^T two n-tiles at a time (rolled over the 6
-// n-tile pairs), consumed on the fly: e = sin(p.B) so d(p_a) += d(e_f) cos(p.B_f) B[a][f].
+// n-tile pairs).  e enters layers 3 and 0: the layer-3 call (last == false) parks its part in
+// the warp's embedding buffer (e itself is dead by then), the layer-0 call adds its own and
+// consumes the sum: e = sin(p.B) so d(p_a) += d(e_f) cos(p.B_f) B[a][f] -- one cosine per
+// feature instead of two.
 __device__ __forceinline__ void embed_grad(const float (&a)[4][4], const float* __restrict__ Ws,
                                            const Rows& R, const float* Bs, int lane, float (&dp)[2][3],
-                                           float* des = nullptr) {
+                                           float* es, bool last, float* des = nullptr) {
     const int t = lane & 3, g = lane >> 2;
     uint32_t ah[4][4], al[4][4];
 #pragma unroll
@@ -495,7 +501,10 @@ __device__ __forceinline__ void embed_grad(const float (&a)[4][4], const float* 
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const int r = q >> 1, f = 8 * (2 * h + nn) + 2 * t + (q & 1);
-                const float v = (nn ? d1[q] : d0[q]) * cosf(phase(R.p[r], Bs, f));
+                float* slot = es + esw(g + 8 * r, f);
+                const float d = nn ? d1[q] : d0[q];
+                if (!last) { *slot = d; continue; }
+                const float v = (d + *slot) * cos_cw(phase(R.p[r], Bs, f));
                 if (des) des[(g + 8 * r) * EMB_PAD + rec_sw(g, f)] = v;   // d(B)[a][f] = sum_points p_a v
                 dp[r][0] = fmaf(v, Bs[f], dp[r][0]);
                 dp[r][1] = fmaf(v, Bs[EMB_PAD + f], dp[r][1]);
@@ -661,8 +670,8 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, int
             if (i == 3 || i == 0) {                                    // input-side part of the layer
                 if constexpr (C::EMBED) {
                     if (want_point || rec)
-                        embed_grad(a, sm + O::TX(i), R, sm + C::OFF_B, lane, dp,
-                                   rec ? rec + (i == 3 ? RC::R_DE : RC::R_DE0) : nullptr);
+                        embed_grad(a, sm + O::TX(i), R, sm + C::OFF_B, lane, dp, es, i == 0,
+                                   rec ? rec + RC::R_DE : nullptr);
                 } else {
                     gemm3<4, 4>(dc, a, sm + O::TX(i), lane);
                 }
@@ -894,7 +903,7 @@ static void build_dw_tables(DwTables& T) {
         s.g_off = g_off; s.width = width;
         return g_off;
     };
-    int sE = -1, sH[5], sC, sP = -1, sDA[5], sDH[5], sDO, sDE = -1, sDE0 = -1;
+    int sE = -1, sH[5], sC, sP = -1, sDA[5], sDH[5], sDO, sDE = -1;
     if (C::EMBED) sE = add_sec(RC::R_E, EMB_PAD);
     for (int i = 0; i < 5; ++i) sH[i] = add_sec(RC::R_H + i * 16 * HID, HID);
     sC = add_sec(RC::R_C, C::C_IN);
@@ -902,7 +911,7 @@ static void build_dw_tables(DwTables& T) {
     for (int i = 0; i < 5; ++i) sDA[i] = add_sec(RC::R_DA + i * 16 * HID, HID);
     if (C::EMBED) for (int i = 0; i < 5; ++i) sDH[i] = add_sec(RC::R_DH + i * 16 * HID, HID);
     sDO = add_sec(RC::R_DO, HID);
-    if (C::EMBED) { sDE = add_sec(RC::R_DE, EMB_PAD); sDE0 = add_sec(RC::R_DE0, EMB_PAD); }
+    if (C::EMBED) sDE = add_sec(RC::R_DE, EMB_PAD);
     T.rec = RC::REC;
     auto add_unit = [&](int a_off, int a_width, int a_col0, int b_off, int b_width, int b_col0, int out_off,
                         int ld_row, int ld_col, int rows_valid, int cols_valid) {
@@ -937,10 +946,8 @@ static void build_dw_tables(DwTables& T) {
     for (int n = 0; n < 4; ++n)       // output layer: rows = outputs
         add_unit(sDO, HID, 0, sH[4], HID, 8 * n, off[C::P_WO] + 8 * n, HID, 1, C::NOUT, 8);
     if (C::EMBED)
-        for (int m0 = 0; m0 < EMB_PAD; m0 += 32) {  // d(B)[a][f]: rows = features f, cols = axes a
+        for (int m0 = 0; m0 < EMB_PAD; m0 += 32)   // d(B)[a][f]: rows = features f, cols = axes a
             add_unit(sDE, EMB_PAD, m0, sP, 8, 0, off[C::P_EMB] + m0, 1, EMB, (EMB - m0 < 32 ? EMB - m0 : 32), 3);
-            add_unit(sDE0, EMB_PAD, m0, sP, 8, 0, off[C::P_EMB] + m0, 1, EMB, (EMB - m0 < 32 ? EMB - m0 : 32), 3);
-        }
     auto add_bias = [&](int sec, int width, int col, int out_idx) {
         DwBias& b = T.bias[T.nbias++];
         b.s_off = sec; b.s_w = width; b.col = col; b.out_idx = out_idx;

@@ -153,28 +153,6 @@ __device__ __forceinline__ void tc_load_point(const PointsDev& q, const DecTask&
     }
 }
 
-// sin(x) to ~2 ulp (1.3e-7 absolute) for |x| < 1e5: x = k pi + r by a three-term Cody-Waite
-// reduction, a degree-9 odd minimax polynomial on [-pi/2, pi/2] (approximation error 5e-9) and
-// the sign (-1)^k.  14 instructions instead of the ~27 of the library sinf fast path (whose
-// inlined Payne-Hanek slow path also overflowed the instruction cache): the embedding evaluates
-// 96 sines per point per decoder and was the largest block of issue slots in this kernel
-// (profiles/r01).  |p . B| stays below ~1e3 in any scene (B ~ N(0, 25^2), |p| of order 10 m);
-// larger arguments take the library call, out of line.
-__device__ __noinline__ float sin_slow(float x) { return sinf(x); }
-__device__ __forceinline__ float sin_cw(float x) {
-    if (fabsf(x) > 1.0e5f) return sin_slow(x);
-    const float k = rintf(x * 0.318309886f);
-    float r = fmaf(k, -3.14159202e+00f, x);
-    r = fmaf(k, -6.27832946e-07f, r);
-    r = fmaf(k, -1.078060506e-14f, r);
-    const float r2 = r * r;
-    float q = fmaf(r2, 2.6000477646e-06f, -1.9806619093e-04f);
-    q = fmaf(r2, q, 8.3330171183e-03f);
-    q = fmaf(r2, q, -1.6666656733e-01f);
-    const float v = fmaf(r * r2, q, r);
-    return __uint_as_float(__float_as_uint(v) ^ ((uint32_t)(int)k << 31));
-}
-
 // 8 embedding features [c0, c0 + 8) of this thread's point -> tensor memory (hi / lo)
 // (Bv: [feature] -> (B[0][f], B[1][f], B[2][f], 0); same operation order as phase())
 __device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float4* Bv, uint32_t lane_base, int c0) {

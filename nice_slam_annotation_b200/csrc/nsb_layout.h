@@ -168,9 +168,8 @@ struct RecCfg {
     static constexpr int R_DA = R_P + 16 * 8;                  // d(a1)..d(a5)         5 x [16][32]
     static constexpr int R_DH = R_DA + 5 * 16 * HID;           // d(h1)..d(h5)         5 x [16][32]
     static constexpr int R_DO = R_DH + 5 * 16 * HID;           // d(out) (cols < NOUT) [16][32]
-    static constexpr int R_DE = R_DO + 16 * HID;               // d(e) * cos(pB), layer 3 [16][96]
-    static constexpr int R_DE0 = R_DE + 16 * W_E;              // d(e) * cos(pB), layer 0 [16][96]
-    static constexpr int REC = R_DE0 + 16 * W_E;
+    static constexpr int R_DE = R_DO + 16 * HID;               // d(e) * cos(pB)       [16][96]
+    static constexpr int REC = R_DE + 16 * W_E;
 };
 constexpr int REC_MAX = RecCfg<KIND_FINE>::REC;
 // Within a section of width >= 32 the element (row, col) is stored at column
