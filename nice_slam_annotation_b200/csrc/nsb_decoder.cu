@@ -715,12 +715,25 @@ k_decoders_backward(const __grid_constant__ StageParams P) {
     int k = 0;
     while (k + 1 < P.ntask && (int)blockIdx.x >= P.task[k + 1].cta_begin) ++k;
     const DecTask& T = P.task[k];
+#ifdef NSB_TC_PROFILE
+    const long long t_start = clock64();
+#endif
     switch (T.kind) {
         case KIND_COARSE: decoder_backward_cta<KIND_COARSE>(P, T, k, sm); break;
         case KIND_MIDDLE: decoder_backward_cta<KIND_MIDDLE>(P, T, k, sm); break;
         case KIND_FINE: decoder_backward_cta<KIND_FINE>(P, T, k, sm); break;
         default: decoder_backward_cta<KIND_COLOR>(P, T, k, sm); break;
     }
+#ifdef NSB_TC_PROFILE
+    if (P.prof) {      // per decoder: slowest and summed warp run time (cycles), warps
+        const long long dt = clock64() - t_start;
+        if ((threadIdx.x & 31) == 0) {
+            atomicMax((unsigned long long*)(P.prof + 36 + 3 * k), (unsigned long long)dt);
+            atomicAdd((unsigned long long*)(P.prof + 36 + 3 * k + 1), (unsigned long long)dt);
+            atomicAdd((unsigned long long*)(P.prof + 36 + 3 * k + 2), 1ull);
+        }
+    }
+#endif
     release_counters(P.ctr);
 }
 
@@ -1022,7 +1035,7 @@ static int init_device() {
 
 // decoders of a stage (decoder.py:336-370) and their relative cost per point
 static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp, float* out_occ0,
-                       float* out_occ1, float* out_rgb, float* d_point, long long P) {
+                       float* out_occ1, float* out_rgb, float* d_point, long long P, unsigned dw_mask = 0) {
     int kinds[3], n = 0;
     float cost[3];
     switch (stage) {
@@ -1049,6 +1062,13 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
     if (!bwd && g_use_tc)
         for (int i = 0; i < n; ++i)
             cost[i] = kinds[i] == KIND_MIDDLE ? 15.f : (kinds[i] == KIND_FINE ? 23.5f : (kinds[i] == KIND_COLOR ? 16.5f : cost[i]));
+    // backward, measured warp run times per decoder (r01): fine 1.16x middle; writing the
+    // weight-gradient records costs a decoder another 1.35x
+    if (bwd)
+        for (int i = 0; i < n; ++i) {
+            if (kinds[i] == KIND_FINE) cost[i] = 35.f;
+            if (dw_mask & (1u << kinds[i])) cost[i] *= 1.35f;
+        }
     const long long tiles = (P + 15) / 16;
     const long long want_ll = (tiles + WARPS - 1) / WARPS;   // CTAs that give every warp one tile
     const int want = want_ll > (1 << 20) ? (1 << 20) : (int)want_ll;
@@ -1193,7 +1213,8 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
     if (sp.pts.P <= 0) return 0;
     if ((flags & NSB_GRAD_POINT) && !d_point) return set_error(NSB_EINVAL, "d_point is NULL");
     int ctas = stage_tasks(*scene, stage, true, sp, nullptr, nullptr, nullptr,
-                           (flags & NSB_GRAD_POINT) ? d_point : nullptr, sp.pts.P);
+                           (flags & NSB_GRAD_POINT) ? d_point : nullptr, sp.pts.P,
+                           (flags & NSB_GRAD_WEIGHT) ? dweight_mask : 0u);
     if (ctas < 0) return ctas;
     sp.d_raw = d_raw;
     sp.flags = flags;
@@ -1226,6 +1247,12 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
             }
     }
     const int smem = max_blob(sp, true) * 4;
+#ifdef NSB_TC_PROFILE
+    static long long* bprof_dev = nullptr;
+    if (!bprof_dev) cudaMalloc(&bprof_dev, 72 * sizeof(long long));
+    cudaMemsetAsync(bprof_dev, 0, 72 * sizeof(long long), (cudaStream_t)stream);
+    sp.prof = bprof_dev;
+#endif
     for (long long t0 = 0; t0 < ntiles; t0 += chunk) {
         sp.tile_begin = t0;
         sp.tile_end = t0 + chunk < ntiles ? t0 + chunk : ntiles;
@@ -1234,6 +1261,16 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
         k_decoders_backward<<<ctas, THREADS, smem, (cudaStream_t)stream>>>(sp);
         timing_mark(1, 1, (cudaStream_t)stream);
         if (int rc = check_launch("k_decoders_backward")) return rc;
+#ifdef NSB_TC_PROFILE
+        if (getenv("NSB_TC_PROFILE_PRINT")) {
+            long long h[72];
+            cudaMemcpy(h, bprof_dev, sizeof(h), cudaMemcpyDeviceToHost);
+            for (int t = 0; t < sp.ntask; ++t)
+                fprintf(stderr, "[bwdprof] task %d kind %d ctas %d: slowest warp %lld cycles, mean %lld, warps %lld\n", t,
+                        sp.task[t].kind, sp.task[t].cta_count, h[36 + 3 * t], h[36 + 3 * t + 1] / (h[36 + 3 * t + 2] ? h[36 + 3 * t + 2] : 1),
+                        h[36 + 3 * t + 2]);
+        }
+#endif
         for (int i = 0; i < sp.ntask && ndw; ++i) {
             const DecTask& T = sp.task[i];
             if (!T.dw_scratch) continue;
