@@ -794,24 +794,50 @@ __global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
     float* ring = sm + DW_HEAD_FLOATS;
     __shared__ int s_nlive;
     const int nunit = TB.nunit, nbias = TB.nbias, rec = TB.rec;
+    const int upw = (nunit + WARPS - 1) / WARPS;             // units per warp (<= DW_UPW)
     for (int i = threadIdx.x; i < nunit * DW_UNIT_INTS; i += THREADS)
         s_unit[i] = reinterpret_cast<const int*>(TB.unit)[i];
     DwBias mybias{0, 0, 0, 0};
     if ((int)threadIdx.x < nbias) mybias = TB.bias[threadIdx.x];
-    // live tiles of this CTA's range, in order (deterministic summation order)
-    const long long per = (P.ntiles + gridDim.x - 1) / gridDim.x;
-    const long long t0 = (long long)blockIdx.x * per;
-    if (warp == 0) {
-        int n = 0;
-        for (int base = 0; base < (int)per; base += 32) {
-            const long long i = t0 + base + lane;
-            const bool live = (base + lane) < per && i < P.ntiles && P.flags[i] != 0;
-            const unsigned m = __ballot_sync(FULL, live);
-            if (live) s_live[n + __popc(m & ((1u << lane) - 1u))] = base + lane;
-            n += __popc(m);
-        }
-        if (lane == 0) s_nlive = n;
+    // Balanced shares of the LIVE tiles: every CTA scans all flags (a few KB), ranks the live
+    // tiles globally and keeps those ranked [b L / G, (b + 1) L / G) -- live tiles cluster along
+    // rays, so equal index ranges left some CTAs with three times the mean (r01 profile).
+    // Order is by tile index: the summation order is deterministic.
+    __shared__ int s_warp_cnt[WARPS];
+    const long long T_ = P.ntiles;
+    const int per_thread = (int)((T_ + THREADS - 1) / THREADS);
+    const long long my0 = (long long)threadIdx.x * per_thread;
+    int mine = 0;
+    for (int j = 0; j < per_thread; ++j) {
+        const long long i = my0 + j;
+        if (i < T_ && P.flags[i] != 0) ++mine;
     }
+    int incl = mine;                                           // inclusive scan over the CTA
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(FULL, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) s_warp_cnt[warp] = incl;
+    __syncthreads();
+    int before = incl - mine, total = 0;
+    for (int w = 0; w < WARPS; ++w) {
+        const int c = s_warp_cnt[w];
+        if (w < warp) before += c;
+        total += c;
+    }
+    const long long lo = (long long)blockIdx.x * total / gridDim.x, hi = (long long)(blockIdx.x + 1) * total / gridDim.x;
+    {
+        int rank = before;
+        for (int j = 0; j < per_thread; ++j) {
+            const long long i = my0 + j;
+            if (i < T_ && P.flags[i] != 0) {
+                if (rank >= lo && rank < hi && rank - lo < DW_LIVE_MAX) s_live[rank - lo] = (int)i;
+                ++rank;
+            }
+        }
+    }
+    if (threadIdx.x == 0) s_nlive = (int)((hi - lo) < DW_LIVE_MAX ? (hi - lo) : DW_LIVE_MAX);
     __syncthreads();
     const int nlive = s_nlive;
     float acc[DW_UPW][2][4];
@@ -824,7 +850,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
     float bias_acc = 0.f;
     const int rec4 = rec >> 2;
     auto issue = [&](int i) {
-        const float* src = P.scratch + (size_t)(t0 + s_live[i]) * rec;
+        const float* src = P.scratch + (size_t)s_live[i] * rec;
         float* dst = ring + (i & 1) * rec;
         for (int c = threadIdx.x; c < rec4; c += THREADS) cp_async16(dst + 4 * c, src + 4 * c);
     };
@@ -842,32 +868,43 @@ __global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
             for (int pt = 0; pt < 16; ++pt) s += R[mybias.s_off + pt * mybias.s_w + rec_sw(pt, mybias.col)];
             bias_acc += s;
         }
+        // a warp owns CONSECUTIVE units: they mostly share their G section (the A operand), which
+        // is then loaded and split once per tile instead of once per unit
+        int prev_a = -1, prev_c = -1;
+        uint32_t ah[2][2][4], al[2][2][4];
 #pragma unroll
         for (int k = 0; k < DW_UPW; ++k) {
-            const int u = warp + WARPS * k;
-            if (u < nunit) {
+            const int u = warp * upw + k;
+            if (k < upw && u < nunit) {
                 const int* U = s_unit + u * DW_UNIT_INTS;
                 const int a_off = U[0], a_w = U[1], a_col0 = U[2], b_off = U[3], b_w = U[4], b_col0 = U[5];
                 const int swa = (U[11] & 1) ? (t << 3) : 0, swb = (U[11] & 2) ? (t << 3) : 0;
+                if (a_off != prev_a || a_col0 != prev_c) {      // uniform over the warp
+                    prev_a = a_off; prev_c = a_col0;
+#pragma unroll
+                    for (int ks = 0; ks < 2; ++ks) {
+                        const float* Ar = R + a_off + (8 * ks + t) * a_w;   // rows 8ks+t, +4: (row & 3) == t
+#pragma unroll
+                        for (int m = 0; m < 2; ++m) {
+                            const int c0 = (a_col0 + g + 16 * m) ^ swa, c1 = (a_col0 + g + 16 * m + 8) ^ swa;
+                            split_tf32(Ar[c0], ah[ks][m][0], al[ks][m][0]);
+                            split_tf32(Ar[c1], ah[ks][m][1], al[ks][m][1]);
+                            split_tf32(Ar[4 * a_w + c0], ah[ks][m][2], al[ks][m][2]);
+                            split_tf32(Ar[4 * a_w + c1], ah[ks][m][3], al[ks][m][3]);
+                        }
+                    }
+                }
 #pragma unroll
                 for (int ks = 0; ks < 2; ++ks) {
-                    const int row = 8 * ks + t;              // rows row, row + 4: both have (row & 3) == t
-                    const float* Bp = R + b_off + row * b_w + ((b_col0 + g) ^ swb);
+                    const float* Bp = R + b_off + (8 * ks + t) * b_w + ((b_col0 + g) ^ swb);
                     uint32_t bh[2], bl[2];
                     split_tf32(Bp[0], bh[0], bl[0]);
                     split_tf32(Bp[4 * b_w], bh[1], bl[1]);
-                    const float* Ar = R + a_off + row * a_w;
 #pragma unroll
                     for (int m = 0; m < 2; ++m) {
-                        const int c0 = (a_col0 + g + 16 * m) ^ swa, c1 = (a_col0 + g + 16 * m + 8) ^ swa;
-                        uint32_t ah[4], al[4];
-                        split_tf32(Ar[c0], ah[0], al[0]);
-                        split_tf32(Ar[c1], ah[1], al[1]);
-                        split_tf32(Ar[4 * a_w + c0], ah[2], al[2]);
-                        split_tf32(Ar[4 * a_w + c1], ah[3], al[3]);
-                        mma_tf32(acc[k][m], al, bh[0], bh[1]);
-                        mma_tf32(acc[k][m], ah, bl[0], bl[1]);
-                        mma_tf32(acc[k][m], ah, bh[0], bh[1]);
+                        mma_tf32(acc[k][m], al[ks][m], bh[0], bh[1]);
+                        mma_tf32(acc[k][m], ah[ks][m], bl[0], bl[1]);
+                        mma_tf32(acc[k][m], ah[ks][m], bh[0], bh[1]);
                     }
                 }
             }
@@ -877,8 +914,8 @@ __global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
     // flush: C fragment (row 16m + g (+8), col 2t (+1)) of unit u
 #pragma unroll
     for (int k = 0; k < DW_UPW; ++k) {
-        const int u = warp + WARPS * k;
-        if (u < nunit) {
+        const int u = warp * upw + k;
+        if (k < upw && u < nunit) {
             const int* U = s_unit + u * DW_UNIT_INTS;
 #pragma unroll
             for (int m = 0; m < 2; ++m)
@@ -1280,9 +1317,9 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
             dp.ntiles = sp.tile_end - sp.tile_begin;
             dp.tab = g_dw_tables_dev + T.kind;
             dp.dflat = d_weight_host[T.kind];
-            // every CTA owns at most DW_LIVE_MAX consecutive tiles
+            // every CTA takes at most DW_LIVE_MAX live tiles (its share is <= ntiles / grid + 1)
             long long grid = dp.ntiles < g_num_sms ? dp.ntiles : g_num_sms;
-            const long long need = (dp.ntiles + DW_LIVE_MAX - 1) / DW_LIVE_MAX;
+            const long long need = (dp.ntiles + DW_LIVE_MAX - 2) / (DW_LIVE_MAX - 1);
             if (grid < need) grid = need;
             timing_mark(2, 0, (cudaStream_t)stream);
             k_dweight<<<(int)grid, THREADS, (DW_HEAD_FLOATS + 2 * g_dw_host[T.kind].rec) * 4, (cudaStream_t)stream>>>(dp);

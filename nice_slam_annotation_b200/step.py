@@ -161,6 +161,10 @@ class FusedStep:
         self.graph = None
 
     # -- plumbing -----------------------------------------------------------------------
+    def _sharded(self):
+        import torch.distributed as dist
+        return dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1
+
     def _pack(self, k):
         ptrs, _, table = self._pack_args[k]
         check(lib().nsb_pack_weights(k, _ptr(ptrs), _ptr(table), _ptr(self.packed[k]), _stream()), "pack_weights")
@@ -173,7 +177,9 @@ class FusedStep:
         call.N = self.N
         call.gt_depth = self.gt_depth.data_ptr() if self.with_gt_depth else 0
         call.keep = self.keep.data_ptr()
-        call.depth_max = self.depth_max.data_ptr() if self.with_gt_depth else 0
+        # sharded: the batch depth max is MAX-reduced over ranks by load(); one rank: the render
+        # call computes it itself (inside the captured graph)
+        call.depth_max = self.depth_max.data_ptr() if (self.with_gt_depth and self._sharded()) else 0
         call.N_samples, call.N_surface = r.N_samples, r.N_surface
         call.lindisp, call.stage, call.occupancy = int(r.lindisp), STAGES[self.stage], int(r.occupancy)
         call.t_uniform = _linspace(r.N_samples, torch.float32, dev).data_ptr()
@@ -213,10 +219,14 @@ class FusedStep:
             self.keep[n:].zero_()
             self.rays_d[n:].fill_(1.0)           # harmless finite rays behind the mask
             self.gt_depth[n:].zero_()
-        if self.with_gt_depth:
+        if self.with_gt_depth and self._sharded():
             if depth_max is None:
-                depth_max = global_depth_max(self.gt_depth, self.keep, self.group)
-            self.depth_max.copy_(depth_max.reshape(1), non_blocking=True)
+                check(lib().nsb_depth_max(_ptr(self.gt_depth), _ptr(self.keep), self.N, _ptr(self.depth_max), _stream()),
+                      "depth_max")
+                import torch.distributed as dist
+                dist.all_reduce(self.depth_max, op=dist.ReduceOp.MAX, group=self.group)
+            else:
+                self.depth_max.copy_(depth_max.reshape(1), non_blocking=True)
 
     def _launch(self):
         """memset(bucket) -> re-pack trainable decoders -> forward -> loss -> backward."""
