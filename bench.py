@@ -233,6 +233,13 @@ def run_ours(args):
         ms_eng = timed(step_engine_host, host_batches, args.steps, args.warmup)
 
     peaks, peak_src = measured_peaks()
+    traffic = args.traffic
+    if traffic is None:                                  # dram bytes of the last committed ncu --set full capture
+        try:
+            t = json.load(open(os.path.join(REPO, "profiles", "ncu_traffic.json")))["k_decoders_backward"]
+            traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
+        except (OSError, KeyError, ValueError):
+            traffic = None
     S = N_SAMPLES + N_SURFACE
     pts = args.rays * S
     achieved = BYTES_PER_POINT_BWD * pts / (bwd_ms * 1e-3) / 1e9
@@ -261,15 +268,18 @@ def run_ours(args):
         "roofline": {"bound": "hbm", "kernel": "k_decoders_backward", "achieved": achieved,
                      "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                      "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)" if peak_src == "measured" else "fallback",
-                     "traffic": args.traffic, "kernel_ms": bwd_ms, "algorithmic_bytes_per_launch": BYTES_PER_POINT_BWD * pts,
+                     "traffic": traffic, "kernel_ms": bwd_ms, "algorithmic_bytes_per_launch": BYTES_PER_POINT_BWD * pts,
                      "forward_kernel_ms": fwd_ms,
                      "forward_achieved_gbs": BYTES_PER_POINT_FWD * pts / (fwd_ms * 1e-3) / 1e9,
                      "dweight_kernel_ms": dw_ms,
                      "how": "CUDA events around each launch on the launching stream, un-graphed pass of the same step"},
         "clocks": clk.summary(),
     }
+    if rank == 0 and world == 1 and not args.no_tracking:
+        out["tracking"] = tracking_bench(dev, iters=max(args.steps, 20) * 5, warmup=args.warmup)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        out["cpu_baseline"] = cpu_baseline(ns, batches, budget_s=20.0)
+        out["torch_cuda_baseline"] = torch_cuda_port(ns, batches, dev)
+        out["cpu_baseline"] = cpu_baseline(ns, batches, budget_s=12.0)
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
@@ -277,16 +287,18 @@ def run_ours(args):
 
 
 # ---------------------------------------------------------------------------------------
-def oracle_step_fn(ns, batches):
-    """The same step on the CPU through the oracle restatement of the reference's torch code."""
+def oracle_step_fn(ns, batches, device="cpu"):
+    """The same step through the oracle restatement of the reference's torch code, on the CPU (or,
+    for the torch-CUDA comparison line, the same torch ops on the GPU)."""
     from oracle import nice_oracle as O
     dec = ns.shared_decoders
-    prm = {k: v.detach().cpu().clone() for k, v in dec.state_dict().items()}
+    prm = {k: v.detach().to(device).clone() for k, v in dec.state_dict().items()}
     for k, v in prm.items():
         v.requires_grad_(k.startswith("color_decoder."))
-    grids = {k: v.detach().cpu().contiguous().clone().requires_grad_(k != "grid_coarse") for k, v in ns.shared_c.items()}
-    bound = ns.bound.cpu()
-    cpu_batches = [tuple(x.cpu() for x in b) for b in batches]
+    grids = {k: v.detach().to(device).contiguous().clone().requires_grad_(k != "grid_coarse")
+             for k, v in ns.shared_c.items()}
+    bound = ns.bound.to(device)
+    cpu_batches = [tuple(x.to(device) for x in b) for b in batches]
 
     def step(i):
         ro, rd, gd, gc = cpu_batches[i % len(cpu_batches)]
@@ -308,11 +320,94 @@ def cpu_baseline(ns, batches, budget_s):
         _, r = step(n)
         n += 1
         rays += r
-        if time.perf_counter() - t0 > budget_s or n >= 10:
+        if time.perf_counter() - t0 > budget_s or n >= 200:
             break
     dt = time.perf_counter() - t0
     return {"value": rays / dt, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "port",
             "sample": f"{n} steps of the same workload (oracle/nice_oracle.py, torch CPU fp32, {dt:.1f} s)"}
+
+
+def torch_cuda_port(ns, batches, dev, steps=20, warmup=3):
+    """north_star's 50x bar is quoted against the reference's torch-CUDA render_batch_ray fwd+bwd.
+    /root/reference is not on this box, so the line times the oracle restatement (the same ATen
+    op sequence) on the GPU: a reported comparison, not a product path."""
+    try:
+        step = oracle_step_fn(ns, batches, device=dev)
+        for i in range(warmup):
+            step(i)
+        torch.cuda.synchronize()
+        ms, rays = [], 0
+        for i in range(steps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rays += step(warmup + i)[1]
+            e1.record()
+            torch.cuda.synchronize()
+            ms.append(e0.elapsed_time(e1))
+        ms.sort()
+        med = ms[len(ms) // 2]
+        return {"value": rays / steps / (med * 1e-3), "unit": "rays/s", "ms_per_step": med, "kind": "port",
+                "sample": f"median of {steps} steps, oracle/nice_oracle.py (torch {torch.__version__}, fp32, "
+                          f"allow_tf32 off) on the same GPU, loss read back each step like the reference"}
+    except Exception as e:                                   # a comparison line must not sink the bench
+        return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+
+
+def tracking_bench(dev, iters, warmup):
+    """BASELINE metric 2, configs[2]: tracking iterations/s at ScanNet shape, 1000 pixels, stage
+    color, pose-gradient backward through the fused render, Adam on the 7 camera parameters.
+    engine = Tracker.optimize_cam_fused (whole iteration replayed as one CUDA graph, no host read
+    per iteration); api = Tracker.optimize_cam_in_batch + torch.optim.Adam + loss.item() per
+    iteration, the reference's own loop shape (Tracker.py:244-275)."""
+    from nice_slam_annotation_b200.Tracker import Tracker
+    from nice_slam_annotation_b200.common import get_tensor_from_camera
+    from nice_slam_annotation_b200.scene import build_scene
+    from nice_slam_annotation_b200.step import TrackingStep
+    ns = build_scene("scannet_scene0000", dev, seed=0, n_frames=2)
+    cfg = ns.cfg
+    cfg["tracking"].update({"pixels": 1000, "iters": 50, "lr": 5e-4, "seperate_LR": True,
+                            "ignore_edge_W": 20, "ignore_edge_H": 20})
+    tr = Tracker(cfg, None, ns)
+    tr.update_para_from_mapping()
+    c2w, depth, color = ns.frames[1]
+    cam0 = get_tensor_from_camera(ns.frames[0][0].cpu()).to(dev).float()       # previous frame's pose as the start
+    ts = TrackingStep(tr, 1000)
+    ts.load_frame(color, depth)
+    ts.reset(cam0)
+    ts.iterate(warmup)
+    ts.capture()
+    ts.reset(cam0)
+    ts.iterate(warmup)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    ts.iterate(iters)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_engine = e0.elapsed_time(e1) / iters
+    _, best = ts.result()
+    # API loop
+    T = cam0[-3:].clone().requires_grad_(True)
+    quad = cam0[:4].clone().requires_grad_(True)
+    opt = torch.optim.Adam([{"params": [T], "lr": 5e-4}, {"params": [quad], "lr": 1e-4}])
+    for _ in range(warmup):
+        tr.optimize_cam_in_batch(torch.cat([quad, T], 0), color, depth, 1000, opt)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(iters):
+        tr.optimize_cam_in_batch(torch.cat([quad, T], 0), color, depth, 1000, opt)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_api = e0.elapsed_time(e1) / iters
+    return {"metric": "tracking iters/s", "value": 1e3 / ms_engine, "unit": "iters/s", "ms_per_iter": ms_engine,
+            "api": {"value": 1e3 / ms_api, "unit": "iters/s", "ms_per_iter": ms_api,
+                    "path": "Tracker.optimize_cam_in_batch + torch.optim.Adam + loss.item() per iteration"},
+            "config": {"workload": "ScanNet scene0000 shape (460x620, 87.9 MB grids) tracking iteration: 1000 pixels x 48 "
+                                   "samples, stage color, tracking loss with the dynamic-object median mask, backward "
+                                   "to the rays, pose gradient, Adam(7 dof)", "iters_timed": iters,
+                       "engine": "Tracker.optimize_cam_fused / step.TrackingStep: one CUDA graph per iteration, "
+                                 "pixel draw + candidate rule on the device"},
+            "final_loss": best}
 
 
 def run_reference(args):
@@ -353,6 +448,7 @@ if __name__ == "__main__":
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rays", type=int, default=1000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-tracking", action="store_true", help="skip the tracking iters/s section")
     ap.add_argument("--no-graph", action="store_true", help="launch the engine step kernel by kernel")
     ap.add_argument("--traffic", type=float, default=None,
                     help="ncu dram bytes per launch of the dominant kernel (profiles/), reported as roofline.traffic")

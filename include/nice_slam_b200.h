@@ -293,6 +293,17 @@ int nsb_tracking_loss(const double* depth, const double* var, const float* color
                       float w_color, int use_color, int handle_dynamic, double* loss,
                       double* g_depth, float* g_color, void* stream);
 
+/* ---- camera optimiser step of the tracker (src/Tracker.py:232-242, 262-275) --------------------
+ * torch.optim.Adam (no weight decay, no amsgrad) on the 7-dof camera tensor [quat(4), t(3)] with
+ * the reference's two learning rates (quaternion: lr_q, translation: lr_t), state m, v [7] and
+ * the step counter step[0] on the device (all zero before the first call).  Then the
+ * reference's candidate rule: if loss[0] < best_loss[0], best_loss = loss and best_cam = the
+ * UPDATED camera tensor (Tracker.py:270-273 clones camera_tensor after optimizer.step()).
+ * Everything stays on the device so a whole tracking iteration can be replayed as a CUDA graph. */
+int nsb_cam_adam(float* cam, const float* d_cam, float* m, float* v, int32_t* step, float lr_q,
+                 float lr_t, float beta1, float beta2, float eps, const double* loss,
+                 double* best_loss, float* best_cam, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

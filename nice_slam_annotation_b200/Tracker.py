@@ -88,6 +88,7 @@ class Tracker(object):
         self.prev_mapping_idx = -1
         self.c = {}
         self.decoders = None
+        self._fused_loop = None
         self.H, self.W, self.fx, self.fy, self.cx, self.cy = slam.H, slam.W, slam.fx, slam.fy, slam.cx, slam.cy
 
     def optimize_cam_in_batch(self, camera_tensor, gt_color, gt_depth, batch_size, optimizer, indices=None):
@@ -133,12 +134,34 @@ class Tracker(object):
         optimizer.zero_grad()
         return loss.item()
 
+    def optimize_cam_fused(self, camera_tensor, gt_color, gt_depth, batch_size, num_iters=None, graph=True):
+        """All camera iterations of one frame (the loop of Tracker.py:244-275 around
+        optimize_cam_in_batch) without a host round trip per iteration: pixel draw, render,
+        loss, pose gradient, Adam and the best-candidate rule run on the device
+        (step.TrackingStep, one CUDA graph replayed ``num_iters`` times).  Returns
+        (candidate_cam_tensor [7], its loss)."""
+        from .step import TrackingStep
+        if not (self.nice and self.renderer.fixed_shape_ok()):
+            raise NotImplementedError("the fused tracking loop needs the NICE decoders, perturb == 0, N_importance == 0")
+        ts = self._fused_loop
+        if ts is None or ts.N != batch_size:
+            ts = self._fused_loop = TrackingStep(self, batch_size)
+        ts.load_frame(gt_color.to(self.device), gt_depth.to(self.device))
+        ts.reset(camera_tensor)
+        if graph and ts.graph is None:
+            ts.iterate(1)                       # warm-up launch outside the capture
+            ts.reset(camera_tensor)
+            ts.capture()
+        ts.iterate(self.num_cam_iters if num_iters is None else num_iters)
+        return ts.result()
+
     def update_para_from_mapping(self):
         """Copy decoders / grids from the mapper's shared state (Tracker.py:137-149).  The copies
         are detached and parameter gradients are switched off: tracking only needs d(camera)
         (the reference computes, and discards, the decoder gradients here)."""
         if self.mapping_idx is None or self.mapping_idx[0] != self.prev_mapping_idx:
             self.decoders = copy.deepcopy(self.shared_decoders).to(self.device)
+            self._fused_loop = None             # its packed weights / grid pointers are stale
             for p in self.decoders.parameters():
                 p.requires_grad_(False)
             for key, val in self.shared_c.items():

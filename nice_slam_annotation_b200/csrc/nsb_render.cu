@@ -246,6 +246,45 @@ extern "C" int nsb_mapping_loss(const double* depth, const float* color, const f
     return check_launch("k_mapping_loss");
 }
 
+// Adam on the 7 camera parameters + the tracker's best-candidate rule (Tracker.py:232-242,262-275).
+// One warp; bias corrections in fp64 like torch's Python scalars.
+__global__ void k_cam_adam(float* cam, const float* d_cam, float* m, float* v, int* step, float lr_q, float lr_t,
+                           float beta1, float beta2, float eps, const double* loss, double* best_loss,
+                           float* best_cam) {
+    const int i = threadIdx.x;
+    const int t = step[0] + 1;
+    __syncwarp();
+    if (i == 0) step[0] = t;
+    float p = 0.f;
+    if (i < 7) {
+        const float g = d_cam[i];
+        const float mi = m[i] + (g - m[i]) * (1.f - beta1);              // exp_avg.lerp_(grad, 1 - beta1)
+        const float vi = v[i] * beta2 + (1.f - beta2) * g * g;
+        m[i] = mi;
+        v[i] = vi;
+        const double bc1 = 1.0 - pow((double)beta1, (double)t), bc2 = 1.0 - pow((double)beta2, (double)t);
+        const float step_size = (float)((double)(i < 4 ? lr_q : lr_t) / bc1);
+        const float denom = sqrtf(vi) / (float)sqrt(bc2) + eps;
+        p = cam[i] - step_size * (mi / denom);
+        cam[i] = p;
+    }
+    if (best_loss && loss[0] < best_loss[0]) {                            // uniform over the warp
+        __syncwarp();
+        if (i < 7) best_cam[i] = p;
+        if (i == 0) best_loss[0] = loss[0];
+    }
+}
+
+extern "C" int nsb_cam_adam(float* cam, const float* d_cam, float* m, float* v, int32_t* step, float lr_q, float lr_t,
+                            float beta1, float beta2, float eps, const double* loss, double* best_loss,
+                            float* best_cam, void* stream) {
+    if (!cam || !d_cam || !m || !v || !step) return set_error(NSB_EINVAL, "null argument");
+    if (best_loss && (!loss || !best_cam)) return set_error(NSB_EINVAL, "best_loss needs loss and best_cam");
+    k_cam_adam<<<1, 32, 0, (cudaStream_t)stream>>>(cam, d_cam, m, v, step, lr_q, lr_t, beta1, beta2, eps, loss,
+                                                   best_loss, best_cam);
+    return check_launch("k_cam_adam");
+}
+
 extern "C" int nsb_tracking_loss(const double* depth, const double* var, const float* color,
                                  const float* gt_depth, const float* gt_color, const uint8_t* keep, int64_t N,
                                  float w_color, int use_color, int handle_dynamic, double* loss,

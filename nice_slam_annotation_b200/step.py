@@ -286,3 +286,99 @@ class FusedStep:
             params = canonical_params(getattr(self.decoders, DEC_NAMES[k]), k)
             for p, g in zip(params, self.decoder_grads(k)):
                 p.grad = g
+
+
+# ---------------------------------------------------------------------------------------
+# the fused tracking iteration
+# ---------------------------------------------------------------------------------------
+class TrackingStep:
+    """One whole camera-tracking iteration on the device (src/Tracker.py:78-135 + the optimiser
+    and candidate bookkeeping of Tracker.run, :232-275): draw pixels -> camera tensor to rays +
+    box pre-filter -> render -> tracking loss -> backward to the rays -> pose gradient -> Adam on
+    the 7 camera parameters -> keep the best candidate.  No host round trip per iteration (the
+    reference reads ``loss.item()`` every iteration), so ``iterate(n)`` replays one CUDA graph n
+    times and the host reads the result once per frame.
+
+    tracker : object with the attributes of nice_slam_annotation_b200.Tracker.Tracker
+              (renderer, decoders, c, bound, H, W, fx, fy, cx, cy, ignore_edge_*, w_color_loss, ...)
+    n_rays  : tracking pixels per iteration (cfg['tracking']['pixels'])
+    """
+
+    def __init__(self, tracker, n_rays, lr=None, separate_lr=None, betas=(0.9, 0.999), eps=1e-8):
+        t = tracker
+        self.t, self.N = t, int(n_rays)
+        dev = next(t.decoders.parameters()).device
+        self.dev = dev
+        self.step = FusedStep(t.renderer, t.decoders, t.c, "color", n_rays, loss="tracking",
+                              w_color=t.w_color_loss, use_color=t.use_color_in_tracking,
+                              handle_dynamic=t.handle_dynamic, ray_grads=True)
+        lr = t.cam_lr if lr is None else lr
+        separate_lr = t.seperate_LR if separate_lr is None else separate_lr
+        # Tracker.py:232-239: translation at cam_lr, quaternion at 0.2 cam_lr when seperate_LR
+        self.lr_t, self.lr_q = float(lr), float(lr) * (0.2 if separate_lr else 1.0)
+        self.betas, self.eps = betas, float(eps)
+        H0, W0 = t.ignore_edge_H, t.ignore_edge_W
+        self.crop = (H0, t.H - H0, W0, t.W - W0)
+        self.intr = tuple(float(x) for x in (t.fx, t.fy, t.cx, t.cy))
+        self.bound6 = fused._bound6(t.bound)
+        self.depth_img = torch.zeros(t.H, t.W, device=dev)
+        self.color_img = torch.zeros(t.H, t.W, 3, device=dev)
+        self.indices = torch.zeros(self.N, dtype=torch.int64, device=dev)
+        self.cam = torch.zeros(7, device=dev)
+        self.d_cam = torch.zeros(7, device=dev)
+        self.m = torch.zeros(7, device=dev)
+        self.v = torch.zeros(7, device=dev)
+        self.count = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.best_loss = torch.full((1,), float("inf"), dtype=torch.float64, device=dev)
+        self.best_cam = torch.zeros(7, device=dev)
+        self.first_loss = torch.zeros(1, dtype=torch.float64, device=dev)
+        self.draw = True            # False: iterate on the indices the caller wrote into self.indices
+        self.graph = None
+
+    def load_frame(self, gt_color, gt_depth):
+        self.depth_img.copy_(gt_depth, non_blocking=True)
+        self.color_img.copy_(gt_color, non_blocking=True)       # fp64 dataset colour is cast here
+
+    def reset(self, camera_tensor):
+        """New frame / new initial pose: camera tensor [quat(4), t(3)], fresh optimiser state
+        (the reference builds a new Adam per frame, Tracker.py:232-242)."""
+        self.cam.copy_(camera_tensor.detach().reshape(7), non_blocking=True)
+        for x in (self.m, self.v, self.count):
+            x.zero_()
+        self.best_loss.fill_(float("inf"))
+        self.best_cam.copy_(self.cam)
+
+    def _launch(self):
+        s, st, L = _stream(), self.step, lib()
+        H0, H1, W0, W1 = self.crop
+        fx, fy, cx, cy = self.intr
+        if self.draw:                                            # common.py:99
+            torch.randint(0, (H1 - H0) * (W1 - W0), (self.N,), device=self.dev, out=self.indices)
+        check(L.nsb_sample_rays(_ptr(self.indices), self.N, H0, H1, W0, W1, self.t.W, fx, fy, cx, cy, None,
+                                _ptr(self.cam), _ptr(self.depth_img), _ptr(self.color_img), 0, self.bound6,
+                                _ptr(st.rays_o), _ptr(st.rays_d), _ptr(st.gt_depth), _ptr(st.gt_color),
+                                _ptr(st.keep), s), "sample_rays")
+        st._launch()
+        check(L.nsb_pose_grad(_ptr(st.g_rays_o), _ptr(st.g_rays_d), _ptr(self.indices), _ptr(st.keep), self.N, H0, W0, W1 - W0,
+                              fx, fy, cx, cy, _ptr(self.cam), _ptr(self.d_cam), s), "pose_grad")
+        check(L.nsb_cam_adam(_ptr(self.cam), _ptr(self.d_cam), _ptr(self.m), _ptr(self.v), _ptr(self.count),
+                             self.lr_q, self.lr_t, self.betas[0], self.betas[1], self.eps, _ptr(st.loss),
+                             _ptr(self.best_loss), _ptr(self.best_cam), s), "cam_adam")
+
+    def capture(self):
+        g = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g):
+            self._launch()
+        self.graph = g
+
+    def iterate(self, n=1):
+        for _ in range(n):
+            if self.graph is not None:
+                self.graph.replay()
+            else:
+                self._launch()
+
+    def result(self):
+        """(candidate camera tensor [7], its loss) -- the one host read of the frame."""
+        return self.best_cam.clone(), float(self.best_loss.item())

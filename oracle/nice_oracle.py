@@ -124,13 +124,13 @@ def sample_z(rays_o, rays_d, gt_depth, bound, N_samples, N_surface, lindisp=Fals
         near = gt_depth.repeat(1, N_samples) * 0.01                 # fp32
         far = torch.clamp(far_bb, 0, torch.max(gt_depth * 1.2))     # fp64
     if N_surface > 0:
-        ts = torch.linspace(0., 1., steps=N_surface).double()
+        ts = torch.linspace(0., 1., steps=N_surface, device=rays_o.device).double()
         nz = (gt_depth > 0).squeeze(-1)
-        z_surf = torch.zeros(N, N_surface, dtype=torch.float64)
+        z_surf = torch.zeros(N, N_surface, dtype=torch.float64, device=rays_o.device)
         g = gt_depth[nz].reshape(-1, 1).repeat(1, N_surface)        # fp32
         z_surf[nz] = 0.95 * g * (1. - ts) + 1.05 * g * ts
         z_surf[~nz] = (0.001 * (1. - ts) + torch.max(gt_depth) * ts)[None]
-    t = torch.linspace(0., 1., steps=N_samples)
+    t = torch.linspace(0., 1., steps=N_samples, device=rays_o.device)
     if not lindisp:
         z = near * (1. - t) + far * t
     else:
@@ -257,7 +257,7 @@ def nice_forward(prm, p64, grids, stage, bound, coarse_bound_enlarge=2):
     if stage == "coarse":
         c = sample_grid_feature(p64, grids["grid_coarse"], bound * coarse_bound_enlarge)
         occ = mlp_no_xyz_forward(_sub(prm, "coarse_decoder."), c)
-        return torch.cat([torch.zeros(P, 3), occ[:, None]], -1)
+        return torch.cat([torch.zeros(P, 3, device=occ.device), occ[:, None]], -1)
 
     def middle():
         c = sample_grid_feature(p64, grids["grid_middle"], bound)
@@ -270,9 +270,9 @@ def nice_forward(prm, p64, grids, stage, bound, coarse_bound_enlarge=2):
         return mlp_forward(_sub(prm, "fine_decoder."), p64, torch.cat([c, cm], 1))
 
     if stage == "middle":
-        return torch.cat([torch.zeros(P, 3), middle()[:, None]], -1)
+        return torch.cat([torch.zeros(P, 3, device=p64.device), middle()[:, None]], -1)
     if stage == "fine":
-        return torch.cat([torch.zeros(P, 3), (fine() + middle())[:, None]], -1)
+        return torch.cat([torch.zeros(P, 3, device=p64.device), (fine() + middle())[:, None]], -1)
     if stage == "color":
         f = fine()
         c = sample_grid_feature(p64, grids["grid_color"], bound)
@@ -285,7 +285,7 @@ def eval_points(p64, prm, grids, stage, bound, nice=True):
     """Renderer.eval_points.  src/utils/Renderer.py:36-93 (chunking omitted: it does not
     change values)."""
     p64 = p64.reshape(-1, 3)
-    mask = torch.ones(p64.shape[0], dtype=torch.bool)
+    mask = torch.ones(p64.shape[0], dtype=torch.bool, device=p64.device)
     for a in range(3):          # 0-dim bound entries: the comparison runs in the dtype of p
         mask = mask & (p64[:, a] < bound[a][1]) & (p64[:, a] > bound[a][0])
     if nice:
@@ -311,7 +311,7 @@ def composite(raw, z_vals, rays_d, occupancy=True):
         dists = torch.cat([dists, torch.full_like(dists[..., :1], 1e10)], -1)
         dists = dists * torch.norm(rays_d[..., None, :], dim=-1)
         alpha = 1. - torch.exp(-torch.relu(raw[..., 3]) * dists)
-    ones = torch.ones((alpha.shape[0], 1), dtype=torch.float32)
+    ones = torch.ones((alpha.shape[0], 1), dtype=torch.float32, device=alpha.device)
     trans = torch.cumprod(torch.cat([ones, (1. - alpha + 1e-10).float()], -1), -1)[:, :-1]
     weights = alpha.float() * trans
     rgb_map = torch.sum(weights[..., None] * rgb, -2)

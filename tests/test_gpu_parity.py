@@ -227,6 +227,62 @@ def test_tracker_iteration_vs_reference(gpu, golden):
     assert_close((cam.detach().cpu() - torch.as_tensor(d["t.cam0"])), d["t.cam1"] - d["t.cam0"], 1e-2, "Adam step")
 
 
+def test_fused_tracking_loop_vs_api_loop(gpu, golden):
+    """Tracker.optimize_cam_fused (pixel -> rays -> render -> loss -> pose gradient -> Adam ->
+    candidate rule as one replayed CUDA graph) follows the same trajectory as the reference-shaped
+    loop of optimize_cam_in_batch + torch.optim.Adam + loss.item() bookkeeping (Tracker.py:244-275)
+    on the same pixel draw; the first iteration is the one the reference golden pins."""
+    from nice_slam_annotation_b200.Tracker import Tracker
+    from nice_slam_annotation_b200.step import TrackingStep
+    d = golden("trained_nice")
+    for separate in (False, True):
+        cfg, ns = _slam_ns(gpu, d, {"tracking": {"seperate_LR": separate}})
+        ns.shared_decoders = gpu.nice_from_state(sub(d, "dec."), d["bound"])
+        ns.shared_c = gpu.grids_from(d)
+        tr = Tracker(cfg, None, ns)
+        tr.update_para_from_mapping()
+        depth = torch.as_tensor(d["depth_img"]).to(gpu.DEV)
+        color = torch.as_tensor(d["color_img"]).to(gpu.DEV)
+        idx = torch.as_tensor(d["t.indices"]).to(gpu.DEV)
+        cam0 = torch.as_tensor(d["t.cam0"]).to(gpu.DEV)
+        iters = 6
+        # reference-shaped loop (Tracker.py:226-275)
+        if separate:
+            T = cam0[-3:].clone().requires_grad_(True)
+            quad = cam0[:4].clone().requires_grad_(True)
+            opt = torch.optim.Adam([{"params": [T], "lr": 1e-3}, {"params": [quad], "lr": 1e-3 * 0.2}])
+            cam_of = lambda: torch.cat([quad, T], 0)
+        else:
+            cam = cam0.clone().requires_grad_(True)
+            opt = torch.optim.Adam([cam], lr=1e-3)
+            cam_of = lambda: cam
+        best, cand, losses = 1e10, None, []
+        for _ in range(iters):
+            loss = tr.optimize_cam_in_batch(cam_of(), color, depth, 150, opt, indices=idx)
+            losses.append(loss)
+            if loss < best:
+                best, cand = loss, cam_of().detach().clone()
+        # fused loop on the same pixels
+        ts = TrackingStep(tr, 150)
+        ts.draw = False
+        ts.indices.copy_(idx)
+        ts.load_frame(color, depth)
+        for graph in (False, True):
+            ts.reset(cam0)
+            if graph:
+                ts.capture()
+            ts.iterate(iters)
+            bc, bl = ts.result()
+            assert abs(bl - best) <= 1e-4 * abs(best), (separate, graph, bl, best)
+            assert_close((ts.cam - cam0).cpu(), (cam_of().detach() - cam0).cpu(), 1e-2, "camera after the loop")
+            assert_close((bc - cam0).cpu(), (cand - cam0).cpu(), 1e-2, "candidate camera")
+        if not separate:
+            assert abs(losses[0] - float(d["t.loss"])) <= 1e-4 * abs(float(d["t.loss"]))
+    # the public entry point: random pixel draw inside the graph, loss must not increase much
+    cam_c, loss_c = tr.optimize_cam_fused(cam0, color, depth, 150, num_iters=10)
+    assert cam_c.shape == (7,) and loss_c > 0 and loss_c < 2 * best
+
+
 def test_mapper_iterations_vs_reference(gpu, golden):
     """Three Mapper.optimize_map iterations (middle, middle, color schedule of a 3-iteration run)
     from the trained state reproduce the reference's updated grids and decoders (golden 'm.*')."""
