@@ -304,6 +304,17 @@ int nsb_cam_adam(float* cam, const float* d_cam, float* m, float* v, int32_t* st
                  float lr_t, float beta1, float beta2, float eps, const double* loss,
                  double* best_loss, float* best_cam, void* stream);
 
+/* ---- optimiser step of the mapper (src/Mapper.py:393-404, 462-482, 625, 633-642) ---------------
+ * torch.optim.Adam (no weight decay, no amsgrad) over a flat fp32 tensor p[n] with gradient g[n] and
+ * state m, v [n]; state2[0] = step counter (device, zero before the first call), state2[1] is a
+ * ticket the kernel uses and leaves zero.  lr is read from the device (lr[0]) so that a captured
+ * CUDA graph follows the stage schedule.  voxel_mask (optional): one byte per 32-float voxel line of a
+ * channels-last grid; lines whose byte is 0 are left untouched -- the reference optimises the
+ * compact copy val[mask] and writes it back every iteration (frustum_feature_selection), which
+ * is the same elementwise update restricted to the mask.  n must be a multiple of 32 with a mask. */
+int nsb_adam(float* p, const float* g, float* m, float* v, int64_t n, const uint8_t* voxel_mask,
+             int32_t* state2, const float* lr, float beta1, float beta2, float eps, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -64,6 +64,10 @@ class Mapper(object):
         # optional iterator of pixel-index tensors replacing the torch.randint draws of
         # get_samples (common.py:99), one per frame per iteration: lets a test share the draws
         self.index_source = None
+        # True: the iterations of optimize_map run as the device-resident loop of map_loop.py
+        # whenever its preconditions hold; False: the autograd path below (same values)
+        self.fused_loop = True
+        self._loops = {}
         self.H, self.W, self.fx, self.fy, self.cx, self.cy = slam.H, slam.W, slam.fx, slam.fy, slam.cx, slam.cy
 
     # ---- callers of the hot path, once per mapped frame ------------------------------------
@@ -81,13 +85,17 @@ class Mapper(object):
         return torch.stack([u, v], -1).float(), zz
 
     def get_mask_from_c2w(self, c2w, key, val_shape, depth_np):
-        """Frustum feature selection (Mapper.py:100-187): boolean mask [X,Y,Z] of the voxels of
-        grid ``key`` seen by the current frame.  ``depth_np`` may be a numpy array or a tensor.
-        Depth is looked up bilinearly (the reference uses cv2.remap INTER_LINEAR, whose 5-bit
-        fixed-point weights differ in the last bits)."""
+        """Frustum feature selection (Mapper.py:100-187): boolean numpy mask [X,Y,Z] of the voxels
+        of grid ``key`` seen by the current frame.  ``depth_np`` may be a numpy array or a tensor."""
+        return self._frustum_mask(c2w, key, val_shape, depth_np).cpu().numpy()
+
+    def _frustum_mask(self, c2w, key, val_shape, depth_np):
+        """get_mask_from_c2w as a device tensor (no host round trip).  Depth is looked up
+        bilinearly (the reference uses cv2.remap INTER_LINEAR, whose 5-bit fixed-point weights
+        differ in the last bits)."""
         dev = self.device
         if key == 'grid_coarse':
-            return np.ones(tuple(val_shape)[::-1]).astype(bool)
+            return torch.ones(tuple(val_shape)[::-1], dtype=torch.bool, device=dev)
         b = torch.as_tensor(self.bound, dtype=torch.float32)
         X, Y, Z = torch.meshgrid(torch.linspace(float(b[0][0]), float(b[0][1]), val_shape[2]),
                                  torch.linspace(float(b[1][0]), float(b[1][1]), val_shape[1]),
@@ -111,7 +119,7 @@ class Mapper(object):
         mask = mask & (0 <= -z) & (-z <= depths.double() + 0.5)
         ray_o = c2w[:3, 3].detach().to(dev).float()
         mask = mask | (((points - ray_o) ** 2).sum(1) < 0.25)
-        return mask.reshape(val_shape[2], val_shape[1], val_shape[0]).cpu().numpy()
+        return mask.reshape(val_shape[2], val_shape[1], val_shape[0])
 
     def keyframe_selection_overlap(self, gt_color, gt_depth, c2w, keyframe_dict, k, N_samples=16, pixels=100):
         """Keyframes whose view overlaps the current frame (Mapper.py:189-293)."""
@@ -168,6 +176,9 @@ class Mapper(object):
                     info.append({'idx': idx, 'gt_c2w': gt_cur_c2w, 'est_c2w': cur_c2w})
             self.selected_keyframes[idx] = info
         pixs_per_image = self.mapping_pixels // len(optimize_frame)
+        if self.fused_loop and self.nice and self.occupancy and self.renderer.fixed_shape_ok():
+            return self._optimize_map_fused(num_joint_iters, lr_factor, optimize_frame, oldest_frame, pixs_per_image,
+                                            cur_gt_color, cur_gt_depth, keyframe_dict, cur_c2w)
 
         decoders_para_list = []
         grid_para = {'grid_coarse': [], 'grid_middle': [], 'grid_fine': [], 'grid_color': []}
@@ -344,6 +355,71 @@ class Mapper(object):
                 else:
                     c2w = get_camera_from_tensor(camera_tensor_list[-1].detach())
                     cur_c2w = torch.cat([c2w, bottom], dim=0).clone()
+            return cur_c2w
+        return None
+
+    def _stage_of(self, joint_iter, num_joint_iters):
+        if self.coarse_mapper:                                # Mapper.py:506-515
+            return 'coarse'
+        if joint_iter <= int(num_joint_iters * self.middle_iter_ratio):
+            return 'middle'
+        if joint_iter <= int(num_joint_iters * self.fine_iter_ratio):
+            return 'fine'
+        return 'color'
+
+    def _optimize_map_fused(self, num_joint_iters, lr_factor, optimize_frame, oldest_frame, pixs_per_image,
+                            cur_gt_color, cur_gt_depth, keyframe_dict, cur_c2w):
+        """The iteration loop of optimize_map (Mapper.py:488-667) through map_loop.MappingLoop: same
+        schedule, same sampled frames, same optimiser arithmetic, no autograd graph and no host
+        round trip per iteration."""
+        from .map_loop import MappingLoop
+        device = self.device
+        bottom = torch.tensor([[0, 0, 0, 1.]], dtype=torch.float32, device=device)
+        frames, ba_slots = [], []
+        for frame in optimize_frame:
+            if frame != -1:
+                depth, color = keyframe_dict[frame]['depth'], keyframe_dict[frame]['color']
+                c2w = keyframe_dict[frame]['est_c2w']
+            else:
+                depth, color, c2w = cur_gt_depth, cur_gt_color, cur_c2w
+            ba = bool(self.BA and frame != oldest_frame)
+            ba_slots.append(ba)
+            frames.append((depth.to(device), color.to(device),
+                           get_tensor_from_camera(c2w).to(device) if ba else c2w.to(device).float()))
+        masked = bool(self.frustum_feature_selection)
+        f64 = False      # the reference casts the sampled colours to fp32 (Mapper.py:575); casting the frame first is the same
+        key = (len(frames), pixs_per_image, tuple(ba_slots), masked, f64)
+        loop = self._loops.get(key)
+        if loop is None or not loop.valid_for(self):
+            self._loops = {k: v for k, v in self._loops.items() if v.valid_for(self)}
+            loop = self._loops[key] = MappingLoop(self, len(frames), pixs_per_image, ba_slots, masked, f64)
+        masks = None
+        if masked:
+            masks = {}
+            for gk in loop.grid_keys:
+                masks[gk] = self._frustum_mask(cur_c2w, gk, self.c[gk].shape[2:], cur_gt_depth).permute(2, 1, 0)
+        loop.begin(frames, masks)
+        prev = None
+        for joint_iter in range(num_joint_iters):
+            self.stage = self._stage_of(joint_iter, num_joint_iters)
+            if self.stage != prev:
+                loop.set_lr(self.stage, lr_factor)
+                prev = self.stage
+            if self.index_source is not None:
+                loop.draw = False
+                for i in range(loop.K):
+                    loop.indices[i * loop.pix:(i + 1) * loop.pix].copy_(next(self.index_source))
+            loop.iterate(self.stage)
+        loop.finish()
+        if self.BA:                                           # Mapper.py:644-667
+            for i, frame in enumerate(optimize_frame):
+                if not ba_slots[i]:
+                    continue
+                c2w = torch.cat([get_camera_from_tensor(loop.camera(i)), bottom], dim=0)
+                if frame != -1:
+                    keyframe_dict[frame]['est_c2w'] = c2w.clone()
+                else:
+                    cur_c2w = c2w.clone()
             return cur_c2w
         return None
 

@@ -96,6 +96,8 @@ _SIGS = {
                                    c_ptr, c_ptr, c_ptr]),
     "nsb_tracking_loss": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_float, C.c_int,
                                     C.c_int, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "nsb_adam": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, c_ptr, c_ptr, c_ptr, C.c_float, C.c_float, C.c_float,
+                           c_ptr]),
     "nsb_cam_adam": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_float, C.c_float, C.c_float, C.c_float,
                                C.c_float, c_ptr, c_ptr, c_ptr, c_ptr]),
 }

@@ -285,6 +285,73 @@ extern "C" int nsb_cam_adam(float* cam, const float* d_cam, float* m, float* v, 
     return check_launch("k_cam_adam");
 }
 
+// Adam over a flat tensor, optionally restricted to masked voxel lines (Mapper.py:462-482 on the
+// compact val[mask] copies + the write-back of :633-642, as one in-place pass).
+__global__ void __launch_bounds__(256) k_adam(float* __restrict__ p, const float* __restrict__ g,
+                                               float* __restrict__ m, float* __restrict__ v, long long n,
+                                               const unsigned char* __restrict__ mask, int* state2,
+                                               const float* __restrict__ lr_dev, float b1, float b2, float eps,
+                                               int vec) {
+    const int t = state2[0] + 1;
+    const double bc1 = 1.0 - pow((double)b1, (double)t), bc2 = 1.0 - pow((double)b2, (double)t);
+    const float step_size = (float)((double)lr_dev[0] / bc1);
+    const float bc2_sqrt = (float)sqrt(bc2);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    if (vec) {
+        const long long n4 = n >> 2;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+            if (mask && !mask[i >> 3]) continue;                 // 8 float4 per 128-byte voxel line
+            const float4 gg = reinterpret_cast<const float4*>(g)[i];
+            float4 pp = reinterpret_cast<float4*>(p)[i], mm = reinterpret_cast<float4*>(m)[i],
+                   vv = reinterpret_cast<float4*>(v)[i];
+            mm.x += (gg.x - mm.x) * (1.f - b1); mm.y += (gg.y - mm.y) * (1.f - b1);
+            mm.z += (gg.z - mm.z) * (1.f - b1); mm.w += (gg.w - mm.w) * (1.f - b1);
+            vv.x = vv.x * b2 + (1.f - b2) * gg.x * gg.x; vv.y = vv.y * b2 + (1.f - b2) * gg.y * gg.y;
+            vv.z = vv.z * b2 + (1.f - b2) * gg.z * gg.z; vv.w = vv.w * b2 + (1.f - b2) * gg.w * gg.w;
+            pp.x -= step_size * (mm.x / (sqrtf(vv.x) / bc2_sqrt + eps));
+            pp.y -= step_size * (mm.y / (sqrtf(vv.y) / bc2_sqrt + eps));
+            pp.z -= step_size * (mm.z / (sqrtf(vv.z) / bc2_sqrt + eps));
+            pp.w -= step_size * (mm.w / (sqrtf(vv.w) / bc2_sqrt + eps));
+            reinterpret_cast<float4*>(p)[i] = pp;
+            reinterpret_cast<float4*>(m)[i] = mm;
+            reinterpret_cast<float4*>(v)[i] = vv;
+        }
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+            if (mask && !mask[i >> 5]) continue;
+            const float gi = g[i];
+            const float mi = m[i] + (gi - m[i]) * (1.f - b1);
+            const float vi = v[i] * b2 + (1.f - b2) * gi * gi;
+            m[i] = mi;
+            v[i] = vi;
+            p[i] -= step_size * (mi / (sqrtf(vi) / bc2_sqrt + eps));
+        }
+    }
+    // the last block to finish publishes the new step count (every block has read the old one by then)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&state2[1], 1) == (int)gridDim.x - 1) {
+            state2[1] = 0;
+            state2[0] = t;
+        }
+    }
+}
+
+extern "C" int nsb_adam(float* p, const float* g, float* m, float* v, int64_t n, const uint8_t* voxel_mask,
+                        int32_t* state2, const float* lr, float beta1, float beta2, float eps, void* stream) {
+    if (!p || !g || !m || !v || !state2 || !lr) return set_error(NSB_EINVAL, "null argument");
+    if (n <= 0) return 0;
+    if (voxel_mask && (n % 32)) return set_error(NSB_EINVAL, "masked Adam needs n to be a multiple of 32 (voxel lines)");
+    const bool vec = (n % 4 == 0) && !(((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15);
+    long long work = vec ? n / 4 : n;
+    long long blocks = (work + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    k_adam<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, (long long)n, voxel_mask, state2, lr, beta1, beta2,
+                                                          eps, vec ? 1 : 0);
+    return check_launch("k_adam");
+}
+
 extern "C" int nsb_tracking_loss(const double* depth, const double* var, const float* color,
                                  const float* gt_depth, const float* gt_color, const uint8_t* keep, int64_t N,
                                  float w_color, int use_color, int handle_dynamic, double* loss,

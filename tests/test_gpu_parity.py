@@ -283,15 +283,18 @@ def test_fused_tracking_loop_vs_api_loop(gpu, golden):
     assert cam_c.shape == (7,) and loss_c > 0 and loss_c < 2 * best
 
 
-def test_mapper_iterations_vs_reference(gpu, golden):
+@pytest.mark.parametrize("fused_loop", [True, False])
+def test_mapper_iterations_vs_reference(gpu, golden, fused_loop):
     """Three Mapper.optimize_map iterations (middle, middle, color schedule of a 3-iteration run)
-    from the trained state reproduce the reference's updated grids and decoders (golden 'm.*')."""
+    from the trained state reproduce the reference's updated grids and decoders (golden 'm.*'),
+    through the device-resident loop (map_loop.MappingLoop) and through the autograd path."""
     from nice_slam_annotation_b200.Mapper import Mapper
     d = golden("trained_nice")
     cfg, ns = _slam_ns(gpu, d)
     ns.shared_decoders = gpu.nice_from_state(sub(d, "dec."), d["bound"])
     ns.shared_c = gpu.grids_from(d)
     mp = Mapper(cfg, None, ns)
+    mp.fused_loop = fused_loop
     mp.index_source = iter([torch.as_tensor(r) for r in d["m.indices"]])
     depth = torch.as_tensor(d["depth_img"]).to(gpu.DEV)
     color = torch.as_tensor(d["color_img"]).to(gpu.DEV)
@@ -317,3 +320,64 @@ def test_mapper_iterations_vs_reference(gpu, golden):
             mostly_close(mp.c[k].detach().cpu(), ref, "grid after 3 iterations: " + k)
     for k, ref in sub(d, "m.dec_after.").items():
         mostly_close(mp.decoders.state_dict()[k].cpu(), ref, "decoder after 3 iterations: " + k, frac=0.99)
+
+
+@pytest.mark.parametrize("frustum,ba", [(True, False), (False, True), (True, True)])
+def test_fused_mapping_loop_vs_autograd_loop(gpu, golden, frustum, ba):
+    """Mapper.optimize_map with frustum feature selection (masked in-place Adam instead of the
+    compact val[mask] copies, Mapper.py:393-404,633-642) and local BA (pose gradient + camera
+    Adam, Mapper.py:430-458,644-667): the device-resident loop follows the autograd path (which
+    the reference golden pins) on the same keyframes and pixel draws."""
+    import numpy as np
+    from nice_slam_annotation_b200.Mapper import Mapper
+    d = golden("trained_nice")
+    depth = torch.as_tensor(d["depth_img"]).to(gpu.DEV)
+    color = torch.as_tensor(d["color_img"]).to(gpu.DEV)
+    c2w = torch.as_tensor(d["c2w"]).to(gpu.DEV).float()
+    if c2w.shape[0] == 3:
+        c2w = torch.cat([c2w, torch.tensor([[0, 0, 0, 1.]], device=gpu.DEV)], 0)
+    iters, pix = 5, 400
+    g = torch.Generator().manual_seed(5)
+    H, W = depth.shape
+    draws = [torch.randint(H * W, (pix // 3,), generator=g) for _ in range(3 * iters)]
+
+    def run(fused_loop):
+        cfg, ns = _slam_ns(gpu, d, {"mapping": {"frustum_feature_selection": frustum, "keyframe_selection_method": "global"}})
+        ns.shared_decoders = gpu.nice_from_state(sub(d, "dec."), d["bound"])
+        ns.shared_c = gpu.grids_from(d)
+        mp = Mapper(cfg, None, ns)
+        mp.fused_loop, mp.BA = fused_loop, ba
+        kf = []
+        for i in range(2):
+            pose = c2w.clone()
+            pose[:3, 3] += 0.02 * (i + 1)
+            kf.append({"gt_c2w": pose.clone(), "idx": i, "color": color, "depth": depth, "est_c2w": pose.clone()})
+        mp.keyframe_dict = kf
+        mp.index_source = iter([x.to(gpu.DEV) for x in draws])
+        np.random.seed(0)
+        out = mp.optimize_map(iters, 1.0, 7, color, depth, c2w, kf, [0, 1], c2w.clone())
+        return mp, kf, out
+
+    ref_mp, ref_kf, ref_out = run(False)
+    mp, kf, out = run(True)
+
+    def mostly_close(a, b, what, tol=2e-3, frac=0.999):
+        err = (a.double() - b.double()).abs()
+        ok = (err <= tol * b.abs().max().clamp_min(1e-30)).double().mean().item()
+        assert ok >= frac, f"{what}: only {ok:.5f} of the elements within {tol:g}"
+
+    for k in ("grid_middle", "grid_fine", "grid_color"):
+        moved_ref = (ref_mp.c[k].detach() != torch.as_tensor(d["c." + k]).to(gpu.DEV))
+        moved = (mp.c[k].detach() != torch.as_tensor(d["c." + k]).to(gpu.DEV))
+        assert moved_ref.any() and (moved_ref != moved).double().mean().item() < 1e-3, "touched voxels differ: " + k
+        mostly_close(mp.c[k].detach(), ref_mp.c[k].detach(), "grid " + k)
+    sd, sd_ref = mp.decoders.state_dict(), ref_mp.decoders.state_dict()
+    for k in sd:
+        mostly_close(sd[k], sd_ref[k], "decoder " + k, frac=0.99)
+    if ba:
+        assert_close(out.cpu() - c2w.cpu(), ref_out.cpu() - c2w.cpu(), 5e-2, "BA: current pose update")
+        assert float((out - c2w).abs().max()) > 0
+        for a, b in zip(kf, ref_kf):
+            assert torch.allclose(a["est_c2w"], b["est_c2w"], atol=1e-4), "BA: keyframe pose"
+    else:
+        assert out is None and ref_out is None
