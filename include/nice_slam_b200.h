@@ -76,6 +76,10 @@ typedef struct NsbPoints {
     const double* p64;     /* [P,3] explicit points (fp64), or NULL */
     const float* p32;      /* [P,3] explicit points (fp32), or NULL */
     int64_t P;             /* number of points (N*S in ray mode) */
+    uint32_t* relu_masks;  /* optional [n decoders of the stage][P][8] words (opaque: the ReLU sign bits of the
+                            * five layers of every point).  nsb_decoders_forward writes them,
+                            * nsb_decoders_backward of the SAME points / stage / weights reads them and skips
+                            * the forward recomputation for decoders without a weight gradient.  NULL: recompute. */
 } NsbPoints;
 
 /* Scene of one call: bound (src/NICE_SLAM.py:188-208), grids, packed decoders. */

@@ -27,7 +27,7 @@ class NsbGrid(C.Structure):
 class NsbPoints(C.Structure):
     _fields_ = [("rays_o", c_ptr), ("rays_d", c_ptr), ("rays_o_stride", C.c_int64),
                 ("rays_d_stride", C.c_int64), ("z", c_ptr), ("N", C.c_int64), ("S", C.c_int32),
-                ("p64", c_ptr), ("p32", c_ptr), ("P", C.c_int64)]
+                ("p64", c_ptr), ("p32", c_ptr), ("P", C.c_int64), ("relu_masks", c_ptr)]
 
 
 class NsbScene(C.Structure):

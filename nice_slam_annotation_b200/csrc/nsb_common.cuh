@@ -28,6 +28,7 @@ struct PointsDev {
     const double* p64;
     const float* p32;
     long long P;
+    unsigned* relu;      // NsbPoints::relu_masks
 };
 
 inline PointsDev to_dev(const NsbPoints& p) {
@@ -35,6 +36,7 @@ inline PointsDev to_dev(const NsbPoints& p) {
     d.ro = p.rays_o; d.rd = p.rays_d; d.so = p.rays_o_stride; d.sd = p.rays_d_stride;
     d.z = p.z; d.N = p.N; d.S = p.S; d.p64 = p.p64; d.p32 = p.p32;
     d.P = p.rays_o ? p.N * (long long)p.S : p.P;
+    d.relu = p.relu_masks;
     return d;
 }
 

@@ -53,6 +53,7 @@ struct DecTask {
     float* d_point;   // backward: [P,3] plane or NULL
     float* dw_scratch;         // backward: weight-gradient records of this launch's tiles, or NULL
     unsigned char* dw_flags;   // one byte per tile: record written
+    unsigned* relu;            // [P][8] ReLU sign words of this decoder (forward writes, backward reads) or NULL
 };
 
 struct StageParams {
@@ -596,7 +597,30 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, int
         }
         Rows R;
         Masks mk;
-        {
+        if (!rec && T.relu) {
+            // the forward saved the ReLU signs: no recomputation (gather, embedding, six layers).
+            // Saved as bytes [point][part n = feature / 8][layer]; lane (g, t) needs bits 2t, 2t + 1 of
+            // byte (n, layer) of points g and g + 8 for its C-fragment columns 8n + 2t (+1)
+            load_rows<KIND>(P.pts, T, tile, lane, R);
+            const int g = lane >> 2;
+            const long long i0 = tile * 16 + g, i1 = i0 + 8;
+            const uint4* src = reinterpret_cast<const uint4*>(T.relu);
+            const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+            const uint4 a0 = i0 < P.pts.P ? __ldg(src + 2 * i0) : z4, b0 = i0 < P.pts.P ? __ldg(src + 2 * i0 + 1) : z4;
+            const uint4 a1 = i1 < P.pts.P ? __ldg(src + 2 * i1) : z4, b1 = i1 < P.pts.P ? __ldg(src + 2 * i1 + 1) : z4;
+            const unsigned lo0[4] = {a0.x, a0.z, b0.x, b0.z}, hi0[4] = {a0.y, a0.w, b0.y, b0.w};
+            const unsigned lo1[4] = {a1.x, a1.z, b1.x, b1.z}, hi1[4] = {a1.y, a1.w, b1.y, b1.w};
+#pragma unroll
+            for (int i = 0; i < 5; ++i) {
+                unsigned bits = 0;
+#pragma unroll
+                for (int n = 0; n < 4; ++n) {
+                    const unsigned y0 = i < 4 ? lo0[n] >> (8 * i) : hi0[n], y1 = i < 4 ? lo1[n] >> (8 * i) : hi1[n];
+                    bits |= (((y0 >> (2 * t)) & 3u) | (((y1 >> (2 * t)) & 3u) << 2)) << (4 * n);
+                }
+                mk.set(i, bits);
+            }
+        } else {
             float c[C::CS][4];
             float out[4];
             tile_inputs<KIND>(P.pts, T, sm, es, tile, lane, R, c);
@@ -1017,6 +1041,7 @@ namespace nsb {
 // ---- host side -------------------------------------------------------------------------------
 static int g_num_sms = 0;
 static int g_use_tc = 1;         // NSB_TC=0 selects the mma.sync kernels (A/B comparisons)
+static float g_saved_cost = 0.3f; // backward cost of a decoder that skips the recomputation, relative (NSB_SAVED_COST; swept on B200, r01)
 static bool g_attr_done = false;
 constexpr int CTR_SLOTS = 256;                   // launches in flight before a counter slot is reused
 __device__ unsigned g_tile_ctr[CTR_SLOTS * 4];
@@ -1055,6 +1080,7 @@ static int init_device() {
                                  TcSmem<KIND_FINE>::S_END * 4);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     if (const char* v = getenv("NSB_TC")) g_use_tc = atoi(v);
+    if (const char* v = getenv("NSB_SAVED_COST")) g_saved_cost = (float)atof(v);
     build_dw_tables<KIND_COARSE>(g_dw_host[0]);
     build_dw_tables<KIND_MIDDLE>(g_dw_host[1]);
     build_dw_tables<KIND_FINE>(g_dw_host[2]);
@@ -1101,10 +1127,13 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
             cost[i] = kinds[i] == KIND_MIDDLE ? 15.f : (kinds[i] == KIND_FINE ? 23.5f : (kinds[i] == KIND_COLOR ? 16.5f : cost[i]));
     // backward, measured warp run times per decoder (r01): fine 1.16x middle; writing the
     // weight-gradient records costs a decoder another 1.35x
+    // a decoder without a weight gradient whose forward saved its ReLU signs skips the recomputation
+    const bool saved = sp.pts.relu != nullptr && g_use_tc;
     if (bwd)
         for (int i = 0; i < n; ++i) {
             if (kinds[i] == KIND_FINE) cost[i] = 35.f;
             if (dw_mask & (1u << kinds[i])) cost[i] *= 1.35f;
+            else if (saved && kinds[i] != KIND_COARSE) cost[i] *= g_saved_cost;
         }
     const long long tiles = (P + 15) / 16;
     const long long want_ll = (tiles + WARPS - 1) / WARPS;   // CTAs that give every warp one tile
@@ -1153,6 +1182,7 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
         T.d_point = d_point ? d_point + (size_t)i * P * 3 : nullptr;
         T.dw_scratch = nullptr;
         T.dw_flags = nullptr;
+        T.relu = (saved && k != KIND_COARSE) ? sp.pts.relu + (size_t)i * P * 8 : nullptr;
         int share = share_of[i];
         if (share > want) share = want;
         T.cta_begin = begin;

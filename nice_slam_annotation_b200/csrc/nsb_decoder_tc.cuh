@@ -308,6 +308,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         TQ(3)  // next tile's point + publish
         // ---- the layer chain: every thread finishes 8 columns of its row ------------------------------
         const int hc = HPP * part;
+        unsigned relu_lo = 0, relu_hi = 0;
 #pragma unroll 1
         for (int L = 0; L < 5; ++L) {
             const int acc_col = L == 0 ? TM_ACCE : (L == 3 ? TM_ACCE + 32 : TM_ACCH);
@@ -315,9 +316,15 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             tc::tmem_ld8(lane_base + acc_col + hc, a);
             tc::tmem_ld8(lane_base + TM_ACCC + 32 * L + hc, cc);
             tc::tmem_ld_wait();
+            unsigned sign = 0;
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-                a[j] = (fmaxf(a[j] + bias[32 * L + hc + j], 0.f) + biasc[32 * L + hc + j]) + cc[j];
+            for (int j = 0; j < 8; ++j) {
+                const float pre = a[j] + bias[32 * L + hc + j];
+                sign |= (pre > 0.f ? 1u : 0u) << j;
+                a[j] = (fmaxf(pre, 0.f) + biasc[32 * L + hc + j]) + cc[j];
+            }
+            if (L < 4) relu_lo |= sign << (8 * L);      // signs of features 8 part .. 8 part + 7, one byte per layer
+            else relu_hi = sign;
             st_split8(lane_base, TM_HHI + hc, TM_HLO + hc, a);
             tc::tmem_st_wait();
             tc::fence_before_sync();
@@ -355,6 +362,10 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             par ^= 1;
             tc::fence_after_sync();
             TQ(8)  // wait for the layer's MMAs
+        }
+        if (T.relu) {      // 8 bytes per (point, part): layers 0..4 (+ padding), one coalesced 4 KB store per tile
+            const long long i = tile * 128 + row;
+            if (i < P.pts.P) reinterpret_cast<uint2*>(T.relu)[i * 4 + part] = make_uint2(relu_lo, relu_hi);
         }
         if (part == 0) {
             float o[8];

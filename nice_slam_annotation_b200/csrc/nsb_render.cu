@@ -22,6 +22,7 @@ struct Ws {
     float* depth_max;
     double* z;
     float *occ0, *occ1, *rgb, *d_raw, *d_point, *d_dnorm;
+    uint32_t* relu;     // [3][P][8] ReLU sign words, forward -> backward
 };
 
 static Ws carve_ws(void* base, int64_t N, int S) {
@@ -36,6 +37,7 @@ static Ws carve_ws(void* base, int64_t N, int S) {
     w.d_raw = c.take<float>(4 * P);
     w.d_point = c.take<float>(9 * P);
     w.d_dnorm = c.take<float>(3 * N);
+    w.relu = c.take<uint32_t>(24 * P);
     return w;
 }
 
@@ -183,7 +185,7 @@ using namespace nsb;
 extern "C" int64_t nsb_render_workspace_bytes(int64_t N, int S) {
     const int64_t P = N * S;
     // depth_max, z, occ0, occ1, rgb, d_raw, d_point (3 planes), d_dnorm, each rounded to 256 B
-    return 256 * 10 + 256 + P * 8 + P * 4 * 2 + P * 16 * 2 + P * 36 + N * 12;
+    return 256 * 11 + 256 + P * 8 + P * 4 * 2 + P * 16 * 2 + P * 36 + N * 12 + P * 96;
 }
 
 extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
@@ -204,6 +206,7 @@ extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
     if (int rc = nsb_sample_z(&rays, r->gt_depth, b6, r->N_samples, Nf, r->lindisp, r->t_uniform, r->t_surface,
                               r->u, dmax, w.z, stream)) return rc;
     NsbPoints pts = ray_pts(r, w.z, S);
+    pts.relu_masks = w.relu;
     float *o0, *o1, *rgb;
     stage_planes(r->stage, w, o0, o1, rgb);
     if (int rc = nsb_decoders_forward(&pts, &r->scene, r->stage, o0, o1, rgb, stream)) return rc;
@@ -219,6 +222,7 @@ extern "C" int nsb_render_backward(const NsbRenderCall* r, void* stream) {
     Ws w = carve_ws(r->workspace, r->N, S);
     const double* b6 = &r->scene.bound[0][0];
     NsbPoints pts = ray_pts(r, w.z, S);
+    pts.relu_masks = w.relu;             // written by nsb_render_forward of this call
     float *o0, *o1, *rgb;
     stage_planes(r->stage, w, o0, o1, rgb);
     const bool want_rays = (r->flags & NSB_GRAD_POINT) != 0;
