@@ -319,6 +319,55 @@ int nsb_cam_adam(float* cam, const float* d_cam, float* m, float* v, int32_t* st
 int nsb_adam(float* p, const float* g, float* m, float* v, int64_t n, const uint8_t* voxel_mask,
              int32_t* state2, const float* lr, float beta1, float beta2, float eps, void* stream);
 
+/* ---- iMAP* decoder: the single MLP of configs/imap.yaml ----------------------------------------
+ * src/conv_onet/config.py:33-37 builds MLP(dim 3, c_dim 0, color, hidden_size 256, skips [],
+ * n_blocks 4); forward = src/conv_onet/models/decoder.py:190-219 without grid features:
+ * e = sin(p.float() @ B); h = relu(W_i h + b_i) four times; raw = Wo h + bo ([rgb(3), density]).
+ * Parameters are the LIVE fp32 tensors of the nn.Module in their torch layout (weight [out, in],
+ * row-major); nothing is packed.  hidden: a multiple of 16 up to 256.
+ * The layers run as chained 3xTF32 GEMMs on the tcgen05 tensor cores (csrc/nsb_gemm.cu). */
+typedef struct NsbImapDecoder {
+    const float* B;    /* embedder._B [3, 93] */
+    const float* W[4]; /* pts_linears.i.weight: [hidden, 93], then [hidden, hidden] */
+    const float* b[4]; /* pts_linears.i.bias [hidden] */
+    const float* Wo;   /* output_linear.weight [4, hidden] */
+    const float* bo;   /* output_linear.bias [4] */
+    int32_t hidden;
+} NsbImapDecoder;
+
+/* gradient targets, same shapes, ACCUMULATED into (the caller zeroes them) */
+typedef struct NsbImapGrads {
+    float* B;
+    float* W[4];
+    float* b[4];
+    float* Wo;
+    float* bo;
+} NsbImapGrads;
+
+/* forward of all points -> raw [P, 4].  workspace: nsb_imap_workspace_floats(P, hidden, save)
+ * floats.  save != 0 keeps the embedding and the four activations of every point for
+ * nsb_imap_backward; save == 0 runs in a fixed-size workspace (points are processed in chunks). */
+int64_t nsb_imap_workspace_floats(int64_t P, int hidden, int save);
+int nsb_imap_forward(const NsbPoints* pts, const NsbImapDecoder* dec, float* raw, float* workspace,
+                     int save, void* stream);
+
+/* backward: d_raw [P, 4] -> parameter gradients (NSB_GRAD_WEIGHT, into *grads) and / or
+ * d_point [P, 3] (NSB_GRAD_POINT, overwritten).  workspace: the one a save != 0 forward of the SAME
+ * points and parameters filled; scratch: nsb_imap_backward_scratch_floats(P, hidden) floats. */
+int64_t nsb_imap_backward_scratch_floats(int64_t P, int hidden);
+int nsb_imap_backward(const NsbPoints* pts, const NsbImapDecoder* dec, const float* workspace,
+                      const float* d_raw, unsigned flags, const NsbImapGrads* grads, float* d_point,
+                      float* scratch, void* stream);
+
+/* test hook: one fp32-accurate GEMM through the chained tcgen05 kernel.
+ * C[m, n] = epi(sum_k A(m, k) B(n, k)), m < M, n < N_valid <= 256.  a_rc / b_rc = 0: element (r, k)
+ * at p[r * ld + k]; 1: at p[k * ld + r].  epi: 0 store, 1 +bias & ReLU, 2 +bias, 3 zero where
+ * mask[m, n] <= 0, 4 atomic accumulate (required for n_split > 1).  colsum (optional, a_rc = 1):
+ * colsum[m] += sum_k A(m, k). */
+int nsb_gemm3x(const float* A, int64_t lda, int a_rc, const float* B, int64_t ldb, int b_rc, float* C,
+               int64_t ldc, int64_t M, int N_valid, int64_t K, int epi, const float* bias,
+               const float* mask, int64_t ldmask, float* colsum, int n_split, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -48,6 +48,15 @@ class NsbRenderCall(C.Structure):
                 ("scratch", c_ptr), ("scratch_bytes", C.c_int64), ("g_rays_o", c_ptr), ("g_rays_d", c_ptr)]
 
 
+class NsbImapDecoder(C.Structure):
+    _fields_ = [("B", c_ptr), ("W", c_ptr * 4), ("b", c_ptr * 4), ("Wo", c_ptr), ("bo", c_ptr),
+                ("hidden", C.c_int32)]
+
+
+class NsbImapGrads(C.Structure):
+    _fields_ = [("B", c_ptr), ("W", c_ptr * 4), ("b", c_ptr * 4), ("Wo", c_ptr), ("bo", c_ptr)]
+
+
 _SIGS = {
     "nsb_version": (C.c_int, []),
     "nsb_last_error": (C.c_char_p, []),
@@ -98,6 +107,13 @@ _SIGS = {
                                     C.c_int, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_adam": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, c_ptr, c_ptr, c_ptr, C.c_float, C.c_float, C.c_float,
                            c_ptr]),
+    "nsb_imap_workspace_floats": (C.c_int64, [C.c_int64, C.c_int, C.c_int]),
+    "nsb_imap_forward": (C.c_int, [C.POINTER(NsbPoints), C.POINTER(NsbImapDecoder), c_ptr, c_ptr, C.c_int, c_ptr]),
+    "nsb_imap_backward_scratch_floats": (C.c_int64, [C.c_int64, C.c_int]),
+    "nsb_imap_backward": (C.c_int, [C.POINTER(NsbPoints), C.POINTER(NsbImapDecoder), c_ptr, c_ptr, C.c_uint,
+                                    C.POINTER(NsbImapGrads), c_ptr, c_ptr, c_ptr]),
+    "nsb_gemm3x": (C.c_int, [c_ptr, C.c_int64, C.c_int, c_ptr, C.c_int64, C.c_int, c_ptr, C.c_int64, C.c_int64,
+                             C.c_int, C.c_int64, C.c_int, c_ptr, c_ptr, C.c_int64, c_ptr, C.c_int, c_ptr]),
     "nsb_cam_adam": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_float, C.c_float, C.c_float, C.c_float,
                                C.c_float, c_ptr, c_ptr, c_ptr, c_ptr]),
 }

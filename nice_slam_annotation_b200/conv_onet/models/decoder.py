@@ -83,6 +83,8 @@ class MLP(nn.Module):
         self.sample_mode = sample_mode
 
     def kind(self):
+        if self.c_dim == 0:
+            raise RuntimeError("the single-MLP (iMAP*) decoder is not a NICE sub-decoder")
         _check_supported(self.name, self.hidden_size, self.n_blocks, self.skips, self.c_dim, (32, 64),
                          self.pos_embedding_method)
         if self.color:
@@ -91,6 +93,9 @@ class MLP(nn.Module):
 
     def forward(self, p, c_grid=None):
         """Raw decoder output for points p ([1,N,3] or [N,3]): [N] or [N,4] (colour)."""
+        if self.c_dim == 0:                 # iMAP*: no feature grid (config.py:33-37)
+            from ... import imap
+            return imap.eval_points(p, self)
         return fused.decoder_forward_single(self, self.kind(), p, c_grid)
 
 

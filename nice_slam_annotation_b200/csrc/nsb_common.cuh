@@ -175,8 +175,8 @@ __device__ __forceinline__ void chain(float (&a)[J][4], const float (&c)[J][4]) 
 // per point per decoder -- the largest block of issue slots in these kernels (profiles/r01).
 // |p . B| stays below ~1e3 in any scene (B ~ N(0, 25^2), |p| of order 10 m); larger arguments
 // take the library call, out of line.
-__device__ __noinline__ float sin_slow(float x);
-__device__ __noinline__ float cos_slow(float x);
+static __device__ __noinline__ float sin_slow(float x) { return sinf(x); }
+static __device__ __noinline__ float cos_slow(float x) { return cosf(x); }
 __device__ __forceinline__ float reduce_pi(float x, float& k) {
     k = rintf(x * 0.318309886f);
     float r = fmaf(k, -3.14159202e+00f, x);

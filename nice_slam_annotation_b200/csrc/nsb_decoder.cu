@@ -33,8 +33,6 @@
 
 namespace nsb {
 
-__device__ __noinline__ float sin_slow(float x) { return sinf(x); }
-__device__ __noinline__ float cos_slow(float x) { return cosf(x); }
 
 struct GridDev {
     const float* data;

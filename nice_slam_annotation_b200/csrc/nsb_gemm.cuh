@@ -1,0 +1,66 @@
+// Batched / chained fp32-accurate GEMM on the tcgen05 tensor cores (3xTF32), the dense contraction
+// behind the iMAP* decoder (src/conv_onet/models/decoder.py:93-219 with hidden_size 256, c_dim 0).
+//
+//   C[m, n] = epilogue( sum_k A(m, k) * B(n, k) ),   m < M (points or output features), n < N <= 256
+//
+// Operands are plain fp32 arrays in global memory, addressed either with k contiguous ("KC":
+// element (r, k) at p[r * ld + k]) or with the row index contiguous ("RC": p[k * ld + r]), so the
+// forward layers (X W^T), the input-gradient layers (G W) and the weight gradients (G^T X) all read
+// the live torch tensors without a packing pass.  Producer warps split every value into tf32 hi/lo
+// and write K-major core-matrix images to shared memory; one thread issues three MMAs per K step
+// (hi*hi + lo*hi + hi*lo, fp32 accumulate in tensor memory); four epilogue warps read the
+// accumulator back (tcgen05.ld) and apply bias / ReLU / ReLU-mask / atomic accumulation.
+//
+// A batch is either a CHAIN (all layers share the row dimension; a CTA carries a pair of 128-row
+// tiles through every layer, layer l+1 of a tile reading what layer l of the same CTA wrote, so the
+// activations of a tile stay in L1/L2 and the whole MLP is one launch) or a list of INDEPENDENT
+// GEMMs with split-K (the weight gradients: K = points), whose partial sums are accumulated with
+// fp32 atomics.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace nsb {
+
+enum GemmEpi : int {
+    GEMM_EPI_STORE = 0,      // C = acc
+    GEMM_EPI_BIAS_RELU = 1,  // C = max(acc + bias[n], 0)
+    GEMM_EPI_BIAS = 2,       // C = acc + bias[n]
+    GEMM_EPI_MASK = 3,       // C = mask[m, n] > 0 ? acc : 0        (ReLU adjoint)
+    GEMM_EPI_ATOMIC = 4,     // C += acc                            (split-K partial sums)
+};
+
+struct GemmLayer {
+    const float* A;
+    long long lda;
+    const float* B;
+    long long ldb;
+    float* C;
+    long long ldc;
+    const float* bias;
+    const float* mask;
+    long long ldmask;
+    float* colsum;      // optional (RC-addressed A only): colsum[m] += sum_k A(m, k)
+    long long M;        // valid rows of A / C (independent mode; a chain uses GemmBatch::M)
+    long long K;        // valid reduction length
+    long long k_per_split;   // multiple of 16 (independent mode)
+    int a_rc, b_rc;     // 0: k contiguous, 1: row contiguous
+    int N, N_valid;     // MMA width (multiple of 16, <= 256) and valid columns
+    int epi;
+    int m_tiles, n_split;    // independent mode
+};
+
+constexpr int GEMM_MAX_LAYERS = 6;
+
+struct GemmBatch {
+    int n_layers;
+    int chain;
+    long long M;        // chain: rows shared by all layers
+    int m_tiles;        // chain: ceil(M / 128)
+    GemmLayer L[GEMM_MAX_LAYERS];
+};
+
+// validates the batch, fills m_tiles, launches k_gemm3x on `stream`
+int gemm3x_launch(GemmBatch& gb, cudaStream_t stream);
+
+}  // namespace nsb

@@ -84,7 +84,9 @@ def build_scene(shape="replica_room0", device="cuda:0", seed=0, n_frames=5, cfg=
     read from the reference's NICE_SLAM object, plus ``frames`` = [(c2w, depth, color)]."""
     from .utils.Renderer import Renderer
     H, W, fx, fy, cx, cy, bnd = synth.SHAPES[shape]
-    cfg = cfg or base_cfg(device)
+    if cfg is None:
+        cfg = base_cfg(device)
+        cfg["grid_len"].update(synth.GRID_LEN.get(shape, {}))
     torch.manual_seed(seed)
     bound = load_bound(bnd, cfg["scale"])
     decoders = conv_config.get_model(cfg, nice=True)

@@ -24,7 +24,12 @@ SHAPES = {
                           [[-2.0, 11.0], [-2.0, 11.5], [-2.0, 5.5]]),
     "apartment": (720, 1280, 607.4694213867188, 607.4534912109375, 636.9967041015625, 369.2689514160156,
                   [[-5.8, 11.3], [-4.0, 4.5], [-7.9, 4.9]]),
+    # configs/TUM_RGBD/freiburg3_office.yaml: 480x640 resized to 384x512, crop_edge 8; 127^3 fine/colour grids
+    "tum_fr3_office": (368, 496, 428.32, 431.36, 248.08, 190.08,
+                       [[-5.0, 5.0], [-5.0, 5.0], [-5.0, 5.0]]),
 }
+# per-shape grid_len overrides of the dataset configs (configs/TUM_RGBD/tum.yaml:12-16)
+GRID_LEN = {"tum_fr3_office": {"coarse": 2, "middle": 0.16, "fine": 0.08, "color": 0.08}}
 
 
 def look_at(eye, target, up=(0.0, 0.0, 1.0)):

@@ -3,7 +3,7 @@ sm_100a kernels.  Drop-in for ``src.utils.Renderer.Renderer``: same constructor,
 methods, same return shapes and dtypes (depth / uncertainty fp64, colour fp32)."""
 import torch
 
-from .. import fused
+from .. import fused, imap
 from ..common import get_rays
 
 
@@ -25,19 +25,15 @@ class Renderer(object):
         self.coarse_bound_enlarge = cfg.get('model', {}).get('coarse_bound_enlarge', 2)
         self.H, self.W, self.fx, self.fy, self.cx, self.cy = slam.H, slam.W, slam.fx, slam.fy, slam.cx, slam.cy
 
-    def _require_nice(self):
-        if not self.nice:
-            raise NotImplementedError(
-                "the iMAP* decoder (single 4x256 MLP, configs/imap.yaml) has no sm_100a kernel yet; "
-                "the fused path covers the NICE-SLAM decoders (see DESIGN.md, scope table)")
-
     def eval_points(self, p, decoders, c=None, stage='color', device='cuda:0'):
         """Occupancy (and colour) of points p [N,3] -> raw [N,4] fp32 (Renderer.py:36-93).
         Differentiable when any input requires grad."""
-        self._require_nice()
         p = p.to(device)
         rets = []
         for pi in torch.split(p, self.points_batch_size):      # Renderer.py:51
+            if not self.nice:                                  # Renderer.py:73-74: decoders(pi, c_grid=None)
+                rets.append(imap.eval_points(pi, decoders, self.bound))
+                continue
             needs_grad = torch.is_grad_enabled() and (
                 pi.requires_grad or any(g.requires_grad for g in c.values())
                 or any(q.requires_grad for q in decoders.parameters()))
@@ -56,7 +52,6 @@ class Renderer(object):
         """Depth, uncertainty and colour of a batch of rays (Renderer.py:95-262).  ``keep``
         (extension, [N] uint8): rays a caller would have dropped by the box pre-filter; they are
         rendered but excluded from the batch depth max (see fixed_shape_ok)."""
-        self._require_nice()
         N = rays_o.shape[0]
         u = u_imp = None
         if self.perturb > 0.:
@@ -66,6 +61,13 @@ class Renderer(object):
             u = torch.rand(N, n_first)
             if self.N_importance > 0:
                 u_imp = torch.rand(N, self.N_importance)
+        if not self.nice:
+            if keep is not None:
+                raise NotImplementedError("keep masks are supported on the single-pass (NICE) render only")
+            return imap.render_batch_ray(
+                decoders, rays_d.to(device), rays_o.to(device), None if gt_depth is None else gt_depth.to(device),
+                self.bound, N_samples=self.N_samples, N_surface=self.N_surface, N_importance=self.N_importance,
+                lindisp=self.lindisp, occupancy=self.occupancy, u=u, u_importance=u_imp)
         return fused.render_batch_ray(
             c, decoders, rays_d.to(device), rays_o.to(device), stage,
             None if gt_depth is None else gt_depth.to(device), self.bound,

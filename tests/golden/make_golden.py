@@ -283,15 +283,16 @@ def gen_units():
     print("units ok")
 
 
-def gen_imap():
+def gen_imap(hidden=64, name="imap"):
     """iMAP*: single MLP without grids, density compositing, importance resampling,
-    regulariser (configs/imap.yaml; Renderer.py:244-259,343-409).  The golden MLP is the
-    reference MLP class at hidden 64 (config uses 256) to keep the fixture small."""
+    regulariser (configs/imap.yaml; Renderer.py:244-259,343-409).  ``imap``: the reference MLP
+    class at hidden 64 (small fixture for the oracle); ``imap256``: the factory's own width 256
+    (src/conv_onet/config.py:33-37), the case the tensor-core kernels are built for."""
     cfg = load_cfg(False)
     cam = (48, 64, 60.0, 60.0, 31.5, 23.5)
     bound = [[-6.0, 9.0], [-5.0, 7.0], [-4.0, 5.0]]          # metres; cfg scale 0.1 applies
     torch.manual_seed(0)
-    dec = RefMLP(name="", dim=3, c_dim=0, color=True, hidden_size=64, skips=[], n_blocks=4,
+    dec = RefMLP(name="", dim=3, c_dim=0, color=True, hidden_size=hidden, skips=[], n_blocks=4,
                  pos_embedding_method="fourier")
     with torch.no_grad():
         dec.embedder._B.mul_(0.2)                            # keep densities moderate
@@ -326,8 +327,8 @@ def gen_imap():
     torch.manual_seed(31)
     sig = slam.renderer.regulation({}, dec, rd, ro, gd, "cpu", "color")
     out["reg.u"], out["reg.sigma"] = ur.numpy(), sig.detach().numpy()
-    np.savez_compressed(os.path.join(HERE, "imap.npz"), **out)
-    print("imap ok", float(r["depth"].mean()))
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, "ok", float(r["depth"].mean()))
 
 
 def _make_worker(cls, slam, cfg, **extra):
@@ -438,7 +439,7 @@ def gen_trained():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["small", "variants", "units", "imap", "trained"]
+    which = sys.argv[1:] or ["small", "variants", "units", "imap", "imap256", "trained"]
     torch.set_num_threads(1)
     if "small" in which:
         gen_small_nice()
@@ -448,6 +449,8 @@ if __name__ == "__main__":
         gen_units()
     if "imap" in which:
         gen_imap()
+    if "imap256" in which:
+        gen_imap(256, "imap256")
     if "trained" in which:
         gen_trained()
     for f in sorted(os.listdir(HERE)):
