@@ -156,8 +156,29 @@ def run_ours(args):
 
     # ---- engine path (value): forward + loss + backward as 3 library calls, CUDA-graph replay,
     #      gradients in one flat bucket, ONE NCCL all-reduce per step when sharded
-    step = FusedStep(ns.renderer, dec, grids, STAGE, args.rays, loss="mapping", w_color=W_COLOR, use_color=True,
-                     grid_grads=("grid_middle", "grid_fine", "grid_color"), decoder_grads=("color_decoder",))
+    #      gradient exchange when sharded: the bucket lives in symmetric memory and ONE kernel
+    #      (nsb_bucket_allreduce: multimem.ld_reduce / multimem.st through the NVSwitch, or peer ld/st) runs
+    #      inside the same CUDA graph; --nccl-exchange (or no symmetric memory) falls back to a NCCL call
+    peers, exchange = None, "none (1 GPU)"
+    if world > 1:
+        exchange = "NCCL all-reduce of the flat gradient bucket, one call per step"
+        if not args.nccl_exchange:
+            try:
+                from nice_slam_annotation_b200.peers import PeerGroup
+                peers = PeerGroup(device=torch.device(dev))
+                exchange = ("nsb_bucket_allreduce: one kernel over symmetric memory ("
+                            + ("NVLS multimem.ld_reduce / multimem.st" if peers.multicast else "peer ld / st over NVLink")
+                            + "), inside the step's CUDA graph")
+            except Exception as e:                                   # noqa: BLE001 - report and use NCCL
+                exchange += f" (symmetric memory unavailable: {type(e).__name__}: {e})"
+                peers = None
+        flag = torch.tensor([1 if peers is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if peers is not None and int(flag.item()) == 0:
+            peers = None
+    step_kw = dict(loss="mapping", w_color=W_COLOR, use_color=True,
+                   grid_grads=("grid_middle", "grid_fine", "grid_color"), decoder_grads=("color_decoder",))
+    step = FusedStep(ns.renderer, dec, grids, STAGE, args.rays, peers=peers, **step_kw)
 
     def step_device(b):
         step.load(*b)
@@ -230,6 +251,13 @@ def run_ours(args):
         else:
             launches = int(L.nsb_launch_count(0) * args.steps / (args.steps + args.warmup))
         host_batches = [tuple(x.cpu().pin_memory() for x in b) for b in batches]
+        ms_nccl = None
+        if peers is not None:                            # the same step with the NCCL all-reduce, for comparison
+            step_peer, step = step, FusedStep(ns.renderer, dec, grids, STAGE, args.rays, **step_kw)
+            if not args.no_graph:
+                step.load(*batches[0]); step.run(); step.capture()
+            ms_nccl = timed(step_device, batches, args.steps, args.warmup)
+            step = step_peer
         ms_e2e = timed(step_e2e, host_batches, args.steps, args.warmup)
         ms_eng = timed(step_engine_host, host_batches, args.steps, args.warmup)
 
@@ -259,7 +287,8 @@ def run_ours(args):
                    "engine": "FusedStep: render forward + loss + render backward as 3 library calls"
                              + ("" if args.no_graph else ", replayed as one CUDA graph"),
                    "parallelism": f"rays sharded over {world} GPU(s), grids+decoders replicated"
-                                  + (", one NCCL all-reduce of the flat gradient bucket per step" if world > 1 else "")},
+                                  + ("; gradient exchange: " + exchange if world > 1 else ""),
+                   "exchange": exchange, "ms_per_step_with_nccl_allreduce": ms_nccl},
         "e2e": {"value": world * n_rays / (ms_eng * 1e-3), "unit": "rays/s", "ms_per_step": ms_eng,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
                 "api": "FusedStep.load(ray batch in pinned host memory) + run() + loss.item(): the engine call "
@@ -490,6 +519,8 @@ if __name__ == "__main__":
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-tracking", action="store_true", help="skip the tracking iters/s section")
     ap.add_argument("--no-graph", action="store_true", help="launch the engine step kernel by kernel")
+    ap.add_argument("--nccl-exchange", action="store_true",
+                    help="N > 1: all-reduce the gradient bucket with NCCL instead of the peer-memory kernel")
     ap.add_argument("--traffic", type=float, default=None,
                     help="ncu dram bytes per launch of the dominant kernel (profiles/), reported as roofline.traffic")
     a = ap.parse_args()

@@ -319,6 +319,44 @@ int nsb_cam_adam(float* cam, const float* d_cam, float* m, float* v, int32_t* st
 int nsb_adam(float* p, const float* g, float* m, float* v, int64_t n, const uint8_t* voxel_mask,
              int32_t* state2, const float* lr, float beta1, float beta2, float eps, void* stream);
 
+/* ---- gradient exchange of the sharded mapping step over NVLink peer memory -------
+ * The reference maps on one GPU; its loss is a plain sum over rays (src/Mapper.py:605-612), so ranks
+ * that render disjoint ray slices hold partial gradients that add.  The gradient bucket of every rank
+ * (and, for the fused optimiser, the parameter buffer) lives in SYMMETRIC memory: the same allocation
+ * size on every rank, every rank's copy mapped into this process (peer pointers), and -- when the
+ * NVSwitch fabric offers NVLS -- one multicast mapping of all copies (NULL otherwise).  The host side
+ * obtains the mappings from torch.distributed._symmetric_memory (plumbing only).
+ * signal: per-rank pad of nsb_exchange_signal_words() zero-initialised 32-bit words, symmetric too.
+ * error (optional, local): set to 1 if a peer did not arrive within ~20 s.
+ * Every rank must issue the same sequence of exchange calls with the same offsets and sizes. */
+#define NSB_MAX_PEERS 8
+typedef struct NsbPeers {
+    int32_t rank, world;
+    float* bucket[NSB_MAX_PEERS];   /* gradient bucket of rank i as mapped here; bucket[rank] is the local copy */
+    float* bucket_multicast;        /* multicast mapping of the bucket, or NULL */
+    float* param[NSB_MAX_PEERS];    /* parameter buffer of rank i (nsb_bucket_reduce_adam only) */
+    float* param_multicast;
+    uint32_t* signal[NSB_MAX_PEERS];
+    int32_t* error;
+} NsbPeers;
+int64_t nsb_exchange_signal_words(void);
+
+/* SUM all-reduce of bucket[offset, offset + n) over the ranks, in place in every copy, as ONE kernel:
+ * rank r reduces the r-th slice of the range (multimem.ld_reduce through the switch, or peer loads in
+ * rank order) and stores the sum into every copy (multimem.st / peer stores); block-wise flag barriers
+ * before and after.  Replaces dist.all_reduce on the flat gradient bucket.  offset, n: multiples of 4. */
+int nsb_bucket_allreduce(const NsbPeers* peers, int64_t offset, int64_t n, void* stream);
+
+/* The same reduction fused with the mapper's Adam step (src/Mapper.py:462-482, 633-642; semantics of
+ * nsb_adam): rank r sums the r-th slice of bucket[offset, offset + n), updates
+ * param[param_offset + slice] with ITS moments m_slice / v_slice (nsb_exchange_slice() floats each --
+ * the optimiser state is sharded over the ranks) and stores the new parameters into every rank's
+ * copy.  voxel_mask: one byte per 32 floats of the WHOLE range (identical on every rank), or NULL. */
+int64_t nsb_exchange_slice(int rank, int world, int64_t n, int64_t* lo);
+int nsb_bucket_reduce_adam(const NsbPeers* peers, int64_t offset, int64_t n, int64_t param_offset,
+                           float* m_slice, float* v_slice, const uint8_t* voxel_mask, int32_t* state2,
+                           const float* lr, float beta1, float beta2, float eps, void* stream);
+
 /* ---- iMAP* decoder: the single MLP of configs/imap.yaml ----------------------------------------
  * src/conv_onet/config.py:33-37 builds MLP(dim 3, c_dim 0, color, hidden_size 256, skips [],
  * n_blocks 4); forward = src/conv_onet/models/decoder.py:190-219 without grid features:

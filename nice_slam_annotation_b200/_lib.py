@@ -57,6 +57,15 @@ class NsbImapGrads(C.Structure):
     _fields_ = [("B", c_ptr), ("W", c_ptr * 4), ("b", c_ptr * 4), ("Wo", c_ptr), ("bo", c_ptr)]
 
 
+NSB_MAX_PEERS = 8
+
+
+class NsbPeers(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("bucket", c_ptr * NSB_MAX_PEERS),
+                ("bucket_multicast", c_ptr), ("param", c_ptr * NSB_MAX_PEERS), ("param_multicast", c_ptr),
+                ("signal", c_ptr * NSB_MAX_PEERS), ("error", c_ptr)]
+
+
 _SIGS = {
     "nsb_version": (C.c_int, []),
     "nsb_last_error": (C.c_char_p, []),
@@ -107,6 +116,11 @@ _SIGS = {
                                     C.c_int, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_adam": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, c_ptr, c_ptr, c_ptr, C.c_float, C.c_float, C.c_float,
                            c_ptr]),
+    "nsb_exchange_signal_words": (C.c_int64, []),
+    "nsb_bucket_allreduce": (C.c_int, [C.POINTER(NsbPeers), C.c_int64, C.c_int64, c_ptr]),
+    "nsb_exchange_slice": (C.c_int64, [C.c_int, C.c_int, C.c_int64, c_ptr]),
+    "nsb_bucket_reduce_adam": (C.c_int, [C.POINTER(NsbPeers), C.c_int64, C.c_int64, C.c_int64, c_ptr, c_ptr, c_ptr,
+                                         c_ptr, c_ptr, C.c_float, C.c_float, C.c_float, c_ptr]),
     "nsb_imap_workspace_floats": (C.c_int64, [C.c_int64, C.c_int, C.c_int]),
     "nsb_imap_forward": (C.c_int, [C.POINTER(NsbPoints), C.POINTER(NsbImapDecoder), c_ptr, c_ptr, C.c_int, c_ptr]),
     "nsb_imap_backward_scratch_floats": (C.c_int64, [C.c_int64, C.c_int]),

@@ -1,0 +1,256 @@
+// Gradient exchange of the sharded mapping step over NVLink / NVSwitch peer memory.
+//
+// Mapping rays shard across the GPUs of one box; every rank scatters its partial gradients into its
+// copy of ONE flat bucket that lives in symmetric memory (every rank's copy is mapped into every
+// process, plus -- when the fabric offers NVLS -- one multicast mapping of all copies).  The kernels
+// here replace "NCCL all-reduce, then the same optimiser step on every rank":
+//
+//   k_exchange<false>   two-shot all-reduce.  Rank r owns the r-th slice of the range: it reads that
+//                       slice of every copy (multimem.ld_reduce: the switch adds the copies; without
+//                       NVLS: one 16-byte peer load per copy) and stores the sum into every copy
+//                       (multimem.st, or one peer store per copy).
+//   k_exchange<true>    the same reduction fused with the mapper's masked Adam (src/Mapper.py:462-482,
+//                       633-642): the owner keeps the Adam moments of ITS slice only, updates the
+//                       parameters of the slice and stores the new parameters into every rank's copy
+//                       of the parameter buffer.  The gradient sum never travels back and the
+//                       optimiser state is sharded world-ways.
+//
+// Ranks meet at two block-wise barriers through words of a symmetric signal pad (CTA b of every
+// rank exchanges flags with CTA b of every other rank): one before the first peer read (every rank
+// has finished its backward scatter), one after the last peer store.  A flag is a compare-and-swap
+// 0 -> 1 by the sender and 1 -> 0 by the receiver, so the pad is all zero again when the kernel
+// ends and the launch can be replayed inside a CUDA graph.  A wait that lasts longer than
+// ~20 s sets *error and gives up, so a lost peer cannot hang the GPU.
+#include "nsb_common.cuh"
+
+namespace nsb {
+
+constexpr int X_THREADS = 512;
+constexpr int X_MAX_BLOCKS = 64;        // CTAs of one exchange: enough 16-byte requests in flight for NVLink
+constexpr int X_UNROLL = 4;
+
+struct PeersDev {
+    int rank, world;
+    float* bucket[NSB_MAX_PEERS];
+    float* param[NSB_MAX_PEERS];
+    float* bucket_mc;
+    float* param_mc;
+    unsigned* signal[NSB_MAX_PEERS];
+    int* error;
+};
+
+__device__ __forceinline__ unsigned cas_release_sys(unsigned* p, unsigned cmp, unsigned val) {
+    unsigned old;
+    asm volatile("atom.global.release.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(p), "r"(cmp), "r"(val) : "memory");
+    return old;
+}
+__device__ __forceinline__ unsigned cas_acquire_sys(unsigned* p, unsigned cmp, unsigned val) {
+    unsigned old;
+    asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(p), "r"(cmp), "r"(val) : "memory");
+    return old;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// CTA-wise barrier over all ranks: thread t < world talks to rank t.  `slot` selects this CTA's
+// words of the pad for this phase: word slot + s of rank d's pad is written by rank s only.
+__device__ __forceinline__ void peer_barrier(const PeersDev& g, int slot) {
+    __syncthreads();
+    const int t = threadIdx.x;
+    if (t < g.world && t != g.rank) {
+        const unsigned long long t0 = globaltimer_ns();
+        bool ok = true;
+        __threadfence_system();
+        while (cas_release_sys(g.signal[t] + slot + g.rank, 0u, 1u) != 0u)
+            if (globaltimer_ns() - t0 > 20000000000ull) { ok = false; break; }
+        while (ok && cas_acquire_sys(g.signal[g.rank] + slot + t, 1u, 0u) != 1u)
+            if (globaltimer_ns() - t0 > 20000000000ull) { ok = false; break; }
+        __threadfence_system();
+        if (!ok && g.error) *g.error = 1;
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float4 mc_ld_reduce(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mc_st(float* mc, const float4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 :: "l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// peer copies are read past the (incoherent) L1
+__device__ __forceinline__ float4 peer_ld(const float* p) {
+    float4 v;
+    asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void peer_st(float* p, const float4& v) {
+    asm volatile("st.volatile.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__device__ __forceinline__ float4 reduce_at(const PeersDev& g, long long off) {
+    if (g.bucket_mc) return mc_ld_reduce(g.bucket_mc + off);
+    float4 s = peer_ld(g.bucket[0] + off);
+    for (int r = 1; r < g.world; ++r) {                         // fixed rank order: every slice sums the same way
+        const float4 v = peer_ld(g.bucket[r] + off);
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    return s;
+}
+
+struct AdamDev {
+    float* m;                  // moments of the OWNED slice: element i of the range lives at m[i - lo4*4]
+    float* v;
+    const unsigned char* mask; // voxel mask of the whole range (one byte per 32 floats) or null
+    int* state2;
+    const float* lr;
+    float b1, b2, eps;
+    long long p_off;           // float offset of the range inside the parameter buffers
+};
+
+__device__ __forceinline__ float adam1(float& p, float g, float& m, float& v, float b1, float b2, float eps,
+                                       float step_size, float bc2_sqrt) {
+    m += (g - m) * (1.f - b1);
+    v = v * b2 + (1.f - b2) * g * g;
+    p -= step_size * (m / (sqrtf(v) / bc2_sqrt + eps));
+    return p;
+}
+
+// range = floats [off, off + 4 * n4) of the bucket; rank r owns vectors [r * per, min(n4, (r + 1) * per))
+template <bool ADAM>
+__global__ void __launch_bounds__(X_THREADS) k_exchange(const __grid_constant__ PeersDev g, long long off,
+                                                         long long n4, long long per, const __grid_constant__ AdamDev a) {
+    const int nb = gridDim.x;
+    peer_barrier(g, (0 * X_MAX_BLOCKS + blockIdx.x) * NSB_MAX_PEERS);
+    const long long lo = g.rank * per, hi = min(n4, lo + per);
+    float step_size = 0.f, bc2_sqrt = 1.f;
+    if (ADAM) {                                                 // same scalars as k_adam (nsb_render.cu)
+        const int t = a.state2[0] + 1;
+        const double bc1 = 1.0 - pow((double)a.b1, (double)t), bc2 = 1.0 - pow((double)a.b2, (double)t);
+        step_size = (float)((double)a.lr[0] / bc1);
+        bc2_sqrt = (float)sqrt(bc2);
+    }
+    const long long stride = (long long)nb * X_THREADS;
+    for (long long i0 = lo + (long long)blockIdx.x * X_THREADS + threadIdx.x; i0 < hi; i0 += stride * X_UNROLL) {
+        float4 s[X_UNROLL];
+#pragma unroll
+        for (int u = 0; u < X_UNROLL; ++u) {
+            const long long i = i0 + u * stride;
+            if (i < hi && !(ADAM && a.mask && !a.mask[i >> 3])) s[u] = reduce_at(g, off + 4 * i);
+        }
+#pragma unroll
+        for (int u = 0; u < X_UNROLL; ++u) {
+            const long long i = i0 + u * stride;
+            if (i >= hi) continue;
+            if (ADAM) {
+                if (a.mask && !a.mask[i >> 3]) continue;        // outside the frustum: parameters untouched
+                const long long po = a.p_off + 4 * i;
+                float4 p = *reinterpret_cast<const float4*>(g.param[g.rank] + po);
+                float4 m = reinterpret_cast<float4*>(a.m)[i - lo], v = reinterpret_cast<float4*>(a.v)[i - lo];
+                adam1(p.x, s[u].x, m.x, v.x, a.b1, a.b2, a.eps, step_size, bc2_sqrt);
+                adam1(p.y, s[u].y, m.y, v.y, a.b1, a.b2, a.eps, step_size, bc2_sqrt);
+                adam1(p.z, s[u].z, m.z, v.z, a.b1, a.b2, a.eps, step_size, bc2_sqrt);
+                adam1(p.w, s[u].w, m.w, v.w, a.b1, a.b2, a.eps, step_size, bc2_sqrt);
+                reinterpret_cast<float4*>(a.m)[i - lo] = m;
+                reinterpret_cast<float4*>(a.v)[i - lo] = v;
+                if (g.param_mc) mc_st(g.param_mc + po, p);
+                else
+                    for (int r = 0; r < g.world; ++r) peer_st(g.param[r] + po, p);
+            } else {
+                if (g.bucket_mc) mc_st(g.bucket_mc + off + 4 * i, s[u]);
+                else
+                    for (int r = 0; r < g.world; ++r) peer_st(g.bucket[r] + off + 4 * i, s[u]);
+            }
+        }
+    }
+    peer_barrier(g, (1 * X_MAX_BLOCKS + blockIdx.x) * NSB_MAX_PEERS);
+    if (ADAM) {
+        // the last CTA to finish publishes the new step count (every CTA has read the old one by then)
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (atomicAdd(&a.state2[1], 1) == nb - 1) {
+                a.state2[1] = 0;
+                a.state2[0] += 1;
+            }
+        }
+    }
+}
+
+static int blocks_for(long long per) {
+    long long b = (per + (long long)X_THREADS * X_UNROLL - 1) / ((long long)X_THREADS * X_UNROLL);
+    return (int)(b < 1 ? 1 : (b > X_MAX_BLOCKS ? X_MAX_BLOCKS : b));
+}
+
+static int to_dev(const NsbPeers* p, PeersDev& g, bool need_param) {
+    if (!p) return set_error(NSB_EINVAL, "null peer group");
+    if (p->world < 1 || p->world > NSB_MAX_PEERS || p->rank < 0 || p->rank >= p->world)
+        return set_error(NSB_EINVAL, "peer group: rank %d of %d", p->rank, p->world);
+    g.rank = p->rank; g.world = p->world;
+    for (int r = 0; r < NSB_MAX_PEERS; ++r) {
+        g.bucket[r] = r < p->world ? p->bucket[r] : nullptr;
+        g.param[r] = r < p->world ? p->param[r] : nullptr;
+        g.signal[r] = r < p->world ? p->signal[r] : nullptr;
+        if (r < p->world && (!g.bucket[r] || !g.signal[r] || (need_param && !g.param[r])))
+            return set_error(NSB_EINVAL, "peer group: missing mapping of rank %d", r);
+    }
+    g.bucket_mc = p->bucket_multicast;
+    g.param_mc = p->param_multicast;
+    g.error = p->error;
+    return 0;
+}
+
+}  // namespace nsb
+
+using namespace nsb;
+
+extern "C" int64_t nsb_exchange_signal_words(void) { return 2ll * X_MAX_BLOCKS * NSB_MAX_PEERS; }
+
+extern "C" int nsb_bucket_allreduce(const NsbPeers* peers, int64_t offset, int64_t n, void* stream) {
+    PeersDev g;
+    if (int e = to_dev(peers, g, false)) return e;
+    if (n <= 0) return 0;
+    if ((offset | n) & 3) return set_error(NSB_EINVAL, "exchange: offset and n must be multiples of 4 floats");
+    for (int r = 0; r < g.world; ++r)
+        if ((uintptr_t)g.bucket[r] & 15) return set_error(NSB_EINVAL, "exchange: buffers must be 16-byte aligned");
+    const long long n4 = n / 4, per = (n4 + g.world - 1) / g.world;
+    AdamDev a = {};
+    k_exchange<false><<<blocks_for(per), X_THREADS, 0, (cudaStream_t)stream>>>(g, (long long)offset, n4, per, a);
+    return check_launch("k_exchange");
+}
+
+extern "C" int64_t nsb_exchange_slice(int rank, int world, int64_t n, int64_t* lo) {
+    if (world < 1 || rank < 0 || rank >= world || n < 0 || (n & 3)) return -1;
+    const long long n4 = n / 4, per = (n4 + world - 1) / world;
+    const long long a = (long long)rank * per, b = a + per < n4 ? a + per : n4;
+    if (lo) *lo = 4 * (a < n4 ? a : n4);
+    return b > a ? 4 * (b - a) : 0;
+}
+
+extern "C" int nsb_bucket_reduce_adam(const NsbPeers* peers, int64_t offset, int64_t n, int64_t param_offset, float* m_slice,
+                                      float* v_slice, const uint8_t* voxel_mask, int32_t* state2, const float* lr,
+                                      float beta1, float beta2, float eps, void* stream) {
+    PeersDev g;
+    if (int e = to_dev(peers, g, true)) return e;
+    if (n <= 0) return 0;
+    if (!m_slice || !v_slice || !state2 || !lr) return set_error(NSB_EINVAL, "null argument");
+    if ((offset | n | param_offset) & 3) return set_error(NSB_EINVAL, "exchange: offsets and n must be multiples of 4 floats");
+    if (voxel_mask && (n % 32)) return set_error(NSB_EINVAL, "masked Adam needs n to be a multiple of 32 (voxel lines)");
+    for (int r = 0; r < g.world; ++r)
+        if (((uintptr_t)g.bucket[r] | (uintptr_t)g.param[r]) & 15)
+            return set_error(NSB_EINVAL, "exchange: buffers must be 16-byte aligned");
+    if (((uintptr_t)m_slice | (uintptr_t)v_slice) & 15) return set_error(NSB_EINVAL, "exchange: moments must be 16-byte aligned");
+    const long long n4 = n / 4, per = (n4 + g.world - 1) / g.world;
+    AdamDev a;
+    a.m = m_slice; a.v = v_slice; a.mask = voxel_mask; a.state2 = state2; a.lr = lr;
+    a.b1 = beta1; a.b2 = beta2; a.eps = eps; a.p_off = (long long)param_offset;
+    k_exchange<true><<<blocks_for(per), X_THREADS, 0, (cudaStream_t)stream>>>(g, (long long)offset, n4, per, a);
+    return check_launch("k_exchange_adam");
+}

@@ -88,7 +88,7 @@ class MappingLoop:
     masked : frustum_feature_selection (a voxel mask per grid is loaded per call)
     """
 
-    def __init__(self, mapper, n_frames, pixs, ba_slots=None, masked=True, color_f64=False, group=None):
+    def __init__(self, mapper, n_frames, pixs, ba_slots=None, masked=True, color_f64=False, group=None, peers=None):
         mp = self.mp = mapper
         self.K, self.pix = int(n_frames), int(pixs)
         self.N = self.K * self.pix
@@ -143,7 +143,7 @@ class MappingLoop:
                 mp.renderer, mp.decoders, mp.c, st, self.N, loss="mapping", w_color=mp.w_color_loss,
                 use_color=(st == "color"), grid_grads=tuple(GRID_KEYS[k] for k in kinds),
                 decoder_grads=tuple(n for n in self.train_dec if self.dec_kind[n] in kinds),
-                ray_grads=any(self.ba), with_gt_depth=not mp.coarse_mapper, group=group)
+                ray_grads=any(self.ba), with_gt_depth=not mp.coarse_mapper, group=group, peers=peers)
 
     # -- per call ---------------------------------------------------------------------------
     def valid_for(self, mapper):
@@ -225,21 +225,21 @@ class MappingLoop:
         st = self.steps[stage]
         self._sample(st)
         st._launch()
-        if st._sharded():
-            st.bucket.all_reduce(self.group)
+        if st._sharded() and st.bucket.peers is None:
+            st.bucket.all_reduce(self.group)                     # NCCL; the peer exchange ran inside st._launch
         self._update(stage, st)
 
     def iterate(self, stage, graph=True):
         """One mapping iteration of ``stage`` (call ``set_lr`` when the stage changes)."""
         st = self.steps[stage]
-        if not graph or st._sharded():
+        if not graph or (st._sharded() and st.bucket.peers is None):    # NCCL calls are not captured
             self._launch(stage)
             return
         g = self.graphs.get(stage)
         if g is None:
             # warm-up outside the capture must not advance the optimiser: run render only
             self._sample(st)
-            st._launch()
+            st._launch(exchange=False)
             g = torch.cuda.CUDAGraph()
             torch.cuda.synchronize()
             with torch.cuda.graph(g):

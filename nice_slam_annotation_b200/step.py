@@ -32,14 +32,21 @@ class GradBucket:
     ``all_reduce`` is then one collective over the flat buffer, with no flatten / unflatten copies.
     """
 
-    def __init__(self, leaves, device=None):
+    def __init__(self, leaves, device=None, peers=None):
         self.leaves = list(leaves)
         device = device if device is not None else self.leaves[0].device
         self.offsets, n = [], 0
         for p in self.leaves:
             self.offsets.append(n)
             n += (p.numel() + 63) // 64 * 64            # 256-byte aligned segments
-        self.flat = torch.zeros(n, dtype=torch.float32, device=device)
+        # peers (peers.PeerGroup): the bucket lives in symmetric memory and all_reduce is ONE kernel over
+        # NVLink peer / multicast mappings (csrc/nsb_exchange.cu) instead of a NCCL call
+        self.peers = peers
+        if peers is not None:
+            self.flat = peers.alloc(n)
+            self._px = peers.struct(self.flat)
+        else:
+            self.flat = torch.zeros(n, dtype=torch.float32, device=device)
         self.views = [self._view(p, o) for p, o in zip(self.leaves, self.offsets)]
 
     def _view(self, p, off):
@@ -62,6 +69,9 @@ class GradBucket:
 
     def all_reduce(self, group=None):
         """SUM over ranks (the mapping loss is a plain sum over rays, src/Mapper.py:605-612)."""
+        if self.peers is not None:
+            check(lib().nsb_bucket_allreduce(C.byref(self._px), 0, self.flat.numel(), _stream()), "bucket_allreduce")
+            return
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
@@ -107,7 +117,7 @@ class FusedStep:
 
     def __init__(self, renderer, decoders, c, stage, n_rays, loss="mapping", w_color=0.2, use_color=True,
                  handle_dynamic=False, grid_grads=(), decoder_grads=(), ray_grads=False, with_gt_depth=True,
-                 group=None):
+                 group=None, peers=None):
         if not renderer.fixed_shape_ok():
             raise NotImplementedError("FusedStep needs the NICE decoders, perturb == 0 and N_importance == 0")
         self.r, self.decoders, self.stage, self.N = renderer, decoders, stage, int(n_rays)
@@ -142,7 +152,7 @@ class FusedStep:
         self.dec_grad_kinds = [k for k in self.kinds if DEC_NAMES[k] in decoder_grads]
         leaves = [self.grids[k] for k in self.grid_grad_kinds]
         self.dw_holders = [torch.empty(lib().nsb_flat_numel(k), device=dev) for k in self.dec_grad_kinds]
-        self.bucket = GradBucket(leaves + self.dw_holders, dev) if (leaves or self.dw_holders) else None
+        self.bucket = GradBucket(leaves + self.dw_holders, dev, peers) if (leaves or self.dw_holders) else None
         self.scratch = None
         if self.dec_grad_kinds:
             nbytes = len(self.dec_grad_kinds) * lib().nsb_dweight_scratch_bytes(self.dec_grad_kinds[0], N * self.S)
@@ -228,8 +238,9 @@ class FusedStep:
             else:
                 self.depth_max.copy_(depth_max.reshape(1), non_blocking=True)
 
-    def _launch(self):
-        """memset(bucket) -> re-pack trainable decoders -> forward -> loss -> backward."""
+    def _launch(self, exchange=True):
+        """memset(bucket) -> re-pack trainable decoders -> forward -> loss -> backward
+        [-> peer-memory all-reduce of the bucket when it lives in symmetric memory]."""
         s = _stream()
         if self.bucket is not None:
             self.bucket.zero()
@@ -248,6 +259,8 @@ class FusedStep:
                                           int(self.handle_dynamic), _ptr(self.loss), _ptr(self.g_depth),
                                           _ptr(self.g_color), s), "tracking_loss")
         check(lib().nsb_render_backward(C.byref(call), s), "render_backward")
+        if exchange and self.bucket is not None and self.bucket.peers is not None:
+            self.bucket.all_reduce()
 
     def capture(self):
         """Record the iteration into a CUDA graph (call once after a warm-up ``run``)."""
@@ -264,8 +277,8 @@ class FusedStep:
             self.graph.replay()
         else:
             self._launch()
-        if all_reduce and self.bucket is not None:
-            self.bucket.all_reduce(self.group)
+        if all_reduce and self.bucket is not None and self.bucket.peers is None:
+            self.bucket.all_reduce(self.group)         # NCCL; the peer-memory exchange is part of _launch
         return self.loss
 
     def decoder_grads(self, kind):
