@@ -167,7 +167,8 @@ def run_ours(args):
                 from nice_slam_annotation_b200.peers import PeerGroup
                 peers = PeerGroup(device=torch.device(dev))
                 exchange = ("nsb_bucket_allreduce: one kernel over symmetric memory ("
-                            + ("NVLS multimem.ld_reduce / multimem.st" if peers.multicast else "peer ld / st over NVLink")
+                            + ("NVLS multimem.ld_reduce / multimem.st" if (peers.multicast and world > 2)
+                               else "peer ld / st over NVLink")
                             + "), inside the step's CUDA graph")
             except Exception as e:                                   # noqa: BLE001 - report and use NCCL
                 exchange += f" (symmetric memory unavailable: {type(e).__name__}: {e})"

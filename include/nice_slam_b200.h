@@ -276,6 +276,14 @@ typedef struct NsbRenderCall {
     int64_t scratch_bytes;
     float* g_rays_o; /* [N,3] with NSB_GRAD_POINT */
     float* g_rays_d;
+    /* fused mapping loss (src/Mapper.py:604-612), optional: with loss != NULL nsb_render_forward stops
+     * after the decoders and nsb_render_backward runs compositing + loss + the adjoint of both as ONE
+     * kernel (nsb_composite_mapping): depth / var / color and loss[0] are then written by
+     * nsb_render_backward and g_depth / g_var / g_color are ignored.  Needs gt_depth. */
+    const float* gt_color; /* [N,3] */
+    float w_color;
+    int32_t use_color;
+    double* loss; /* [1] */
 } NsbRenderCall;
 
 int64_t nsb_render_workspace_bytes(int64_t N, int S);
@@ -292,6 +300,16 @@ int nsb_render_backward(const NsbRenderCall* call, void* stream);
 int nsb_mapping_loss(const double* depth, const float* color, const float* gt_depth,
                      const float* gt_color, const uint8_t* keep, int64_t N, float w_color,
                      int use_color, double* loss, double* g_depth, float* g_color, void* stream);
+/* Compositing (src/common.py:215-256) + the mapping loss + the adjoint of both in one kernel, one warp
+ * per ray: writes depth/var/rgb [N], d_raw [P,4] (the decoders' incoming gradient) and loss[0].
+ * partials: nsb_composite_mapping_partials(N) doubles of scratch; ticket: one 32-bit word that is 0 on
+ * entry (left 0 on exit).  The loss is summed in a fixed order (deterministic). */
+int64_t nsb_composite_mapping_partials(int64_t N);
+int nsb_composite_mapping(const NsbPoints* rays, const double* bound6_host, int stage, int occupancy,
+                          const float* out_occ0, const float* out_occ1, const float* out_rgb,
+                          const float* gt_depth, const float* gt_color, const uint8_t* keep, float w_color,
+                          int use_color, double* depth, double* var, float* rgb, float* d_raw,
+                          double* partials, uint32_t* ticket, double* loss, void* stream);
 int nsb_tracking_loss(const double* depth, const double* var, const float* color,
                       const float* gt_depth, const float* gt_color, const uint8_t* keep, int64_t N,
                       float w_color, int use_color, int handle_dynamic, double* loss,

@@ -45,7 +45,8 @@ class NsbRenderCall(C.Structure):
                 ("depth", c_ptr), ("var", c_ptr), ("color", c_ptr),
                 ("g_depth", c_ptr), ("g_var", c_ptr), ("g_color", c_ptr),
                 ("flags", C.c_uint32), ("dweight_mask", C.c_uint32), ("d_weight", c_ptr * 4),
-                ("scratch", c_ptr), ("scratch_bytes", C.c_int64), ("g_rays_o", c_ptr), ("g_rays_d", c_ptr)]
+                ("scratch", c_ptr), ("scratch_bytes", C.c_int64), ("g_rays_o", c_ptr), ("g_rays_d", c_ptr),
+                ("gt_color", c_ptr), ("w_color", C.c_float), ("use_color", C.c_int32), ("loss", c_ptr)]
 
 
 class NsbImapDecoder(C.Structure):
@@ -112,6 +113,10 @@ _SIGS = {
     "nsb_render_backward": (C.c_int, [C.POINTER(NsbRenderCall), c_ptr]),
     "nsb_mapping_loss": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_float, C.c_int, c_ptr,
                                    c_ptr, c_ptr, c_ptr]),
+    "nsb_composite_mapping_partials": (C.c_int64, [C.c_int64]),
+    "nsb_composite_mapping": (C.c_int, [C.POINTER(NsbPoints), c_ptr, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                                        c_ptr, C.c_float, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                                        c_ptr]),
     "nsb_tracking_loss": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_float, C.c_int,
                                     C.c_int, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_adam": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, c_ptr, c_ptr, c_ptr, C.c_float, C.c_float, C.c_float,

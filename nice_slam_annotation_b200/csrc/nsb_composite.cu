@@ -241,6 +241,142 @@ __global__ void k_composite_bwd(CompParams c, const double* __restrict__ depth,
     }
 }
 
+// Mapping iteration middle section as ONE kernel: compositing (k_composite_fwd), the mapping loss
+// sum_{gt>0} |gt - depth| + w sum |gt_c - color| with its gradient (Mapper.py:604-612; no cross-ray
+// term, unlike the tracker's median mask) and the compositing adjoint (k_composite_bwd with
+// g_var = 0), without re-reading the decoder planes or round-tripping depth / g_depth through HBM.
+// Loss: per-block partial sums, the last block to arrive adds them in block order (deterministic)
+// and re-arms the ticket.  ticket[0] must be 0 on entry (k_sample_z of the same call zeroes it).
+__global__ void __launch_bounds__(128) k_composite_map(CompParams c, const float* __restrict__ gt_depth,
+                                                        const float* __restrict__ gt_color,
+                                                        const uint8_t* __restrict__ keep, float w_color, int use_color,
+                                                        double* __restrict__ depth, double* __restrict__ var,
+                                                        float* __restrict__ rgb_out, float* __restrict__ d_raw,
+                                                        double* __restrict__ partials, unsigned* __restrict__ ticket,
+                                                        double* __restrict__ loss) {
+    __shared__ double s_part[4];
+    __shared__ bool s_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long ray = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const int S = c.q.S, CH = (S + 31) / 32;
+    const bool color = c.rgb && c.stage == NSB_STAGE_COLOR;
+    double ray_loss = 0.0;
+    if (ray < c.q.N) {
+        const float dnorm = c.occupancy ? 0.f : ray_dnorm(c.q, ray);
+        RaySamples R;
+        ray_alpha(c, ray, lane, CH, dnorm, R);
+        double dsum = 0.0;
+        float col[3] = {0.f, 0.f, 0.f};
+        float w[MAX_CH];
+        double zz[MAX_CH];
+        float4 cv[MAX_CH];
+#pragma unroll
+        for (int k = 0; k < MAX_CH; ++k) {
+            if (k < R.n) {
+                const long long i = ray * S + R.s0 + k;
+                w[k] = R.alpha[k] * R.trans[k];
+                zz[k] = c.q.z[i];
+                dsum += (double)w[k] * zz[k];
+                cv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (color) {
+                    cv[k] = *reinterpret_cast<const float4*>(c.rgb + 4 * i);
+                    col[0] = fmaf(w[k], cv[k].x, col[0]);
+                    col[1] = fmaf(w[k], cv[k].y, col[1]);
+                    col[2] = fmaf(w[k], cv[k].z, col[2]);
+                }
+            }
+        }
+        const double D = warp_sum_d(dsum);
+        double vsum = 0.0;
+#pragma unroll
+        for (int k = 0; k < MAX_CH; ++k)
+            if (k < R.n) { const double t = zz[k] - D; vsum += (double)w[k] * t * t; }
+        const double V = warp_sum_d(vsum);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) col[a] = warp_sum_f(col[a]);
+        if (lane == 0) {
+            depth[ray] = D;
+            var[ray] = V;
+            rgb_out[3 * ray] = col[0];
+            rgb_out[3 * ray + 1] = col[1];
+            rgb_out[3 * ray + 2] = col[2];
+        }
+        // loss of this ray and its gradient (every lane holds D and col)
+        const bool live = !keep || keep[ray];
+        double gd = 0.0;
+        float gc[3] = {0.f, 0.f, 0.f};
+        const float gdv = gt_depth[ray];
+        if (live && gdv > 0.f) {
+            const double diff = (double)gdv - D;
+            ray_loss += fabs(diff);
+            gd = diff > 0 ? -1.0 : (diff < 0 ? 1.0 : 0.0);
+        }
+        if (live && use_color)
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const float diff = gt_color[3 * ray + a] - col[a];
+                ray_loss += (double)(w_color * fabsf(diff));
+                gc[a] = diff > 0 ? -w_color : (diff < 0 ? w_color : 0.f);
+            }
+        if (!color) gc[0] = gc[1] = gc[2] = 0.f;
+        // adjoint (k_composite_bwd with g_var = 0)
+        float G[MAX_CH], suf[MAX_CH];
+        float lane_total = 0.f;
+#pragma unroll
+        for (int k = MAX_CH - 1; k >= 0; --k) {
+            if (k < R.n) {
+                const long long i = ray * S + R.s0 + k;
+                const double g = gd * zz[k];
+                const float rgbdot = color ? gc[0] * cv[k].x + gc[1] * cv[k].y + gc[2] * cv[k].z : 0.f;
+                G[k] = (float)g + rgbdot;
+                suf[k] = lane_total;
+                lane_total += G[k] * w[k];
+                d_raw[4 * i] = w[k] * gc[0];
+                d_raw[4 * i + 1] = w[k] * gc[1];
+                d_raw[4 * i + 2] = w[k] * gc[2];
+            }
+        }
+        float incl = lane_total;
+        for (int d = 1; d < 32; d <<= 1) {
+            float o = __shfl_down_sync(FULL, incl, d);
+            if (lane + d < 32) incl += o;
+        }
+        float excl = __shfl_down_sync(FULL, incl, 1);
+        if (lane == 31) excl = 0.f;
+#pragma unroll
+        for (int k = 0; k < MAX_CH; ++k) {
+            if (k < R.n) {
+                const long long i = ray * S + R.s0 + k;
+                const float a = R.alpha[k];
+                const float later = suf[k] + excl;
+                const float dalpha = G[k] * R.trans[k] - later / ((1.f - a) + 1e-10f);
+                float ds;
+                if (c.occupancy) ds = dalpha * (1.f - a) * a * 10.f;
+                else ds = R.sig[k] > 0.f ? dalpha * (1.f - a) * R.dist[k] : 0.f;
+                d_raw[4 * i + 3] = R.inb[k] ? ds : 0.f;
+            }
+        }
+    }
+    // ---- loss: warp 0 lane 0 of each warp holds ray_loss (identical on all lanes) ----
+    if (lane == 0) s_part[warp] = ray_loss;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += s_part[k];
+        partials[blockIdx.x] = t;
+        __threadfence();
+        s_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last && warp == 0) {
+        __threadfence();
+        double t = 0.0;
+        for (unsigned b = lane; b < gridDim.x; b += 32) t += __ldcg(partials + b);
+        t = warp_sum_d(t);
+        if (lane == 0) { loss[0] = t; *ticket = 0u; }
+    }
+}
+
 __global__ void k_assemble_raw(CompParams c, float* __restrict__ raw, uint8_t* __restrict__ inbound) {
     long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (i >= c.q.P) return;
@@ -428,4 +564,22 @@ extern "C" int nsb_pose_grad(const float* g_rays_o, const float* g_rays_d, const
     k_pose_grad<<<1, 256, 0, (cudaStream_t)stream>>>(g_rays_o, g_rays_d, indices, keep, n, H0, W0, Wc, fx, fy,
                                                      cx, cy, cam7, d_cam7);
     return check_launch("k_pose_grad");
+}
+
+extern "C" int64_t nsb_composite_mapping_partials(int64_t N) { return (N * 32 + 127) / 128; }
+
+extern "C" int nsb_composite_mapping(const NsbPoints* rays, const double* bound6_host, int stage, int occupancy,
+                                     const float* out_occ0, const float* out_occ1, const float* out_rgb,
+                                     const float* gt_depth, const float* gt_color, const uint8_t* keep, float w_color,
+                                     int use_color, double* depth, double* var, float* rgb, float* d_raw,
+                                     double* partials, uint32_t* ticket, double* loss, void* stream) {
+    CompParams c;
+    if (int rc = comp_params(rays, bound6_host, stage, occupancy, out_occ0, out_occ1, out_rgb, true, c)) return rc;
+    if (!gt_depth || !gt_color || !depth || !var || !rgb || !d_raw || !partials || !ticket || !loss)
+        return set_error(NSB_EINVAL, "null argument");
+    if (c.q.N <= 0) return 0;
+    const int bs = 128;
+    k_composite_map<<<(unsigned)((c.q.N * 32 + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(
+        c, gt_depth, gt_color, keep, w_color, use_color, depth, var, rgb, d_raw, partials, ticket, loss);
+    return check_launch("k_composite_map");
 }

@@ -21,13 +21,14 @@
 // 0 -> 1 by the sender and 1 -> 0 by the receiver, so the pad is all zero again when the kernel
 // ends and the launch can be replayed inside a CUDA graph.  A wait that lasts longer than
 // ~20 s sets *error and gives up, so a lost peer cannot hang the GPU.
+#include <stdlib.h>
 #include "nsb_common.cuh"
 
 namespace nsb {
 
 constexpr int X_THREADS = 512;
-constexpr int X_MAX_BLOCKS = 64;        // CTAs of one exchange: enough 16-byte requests in flight for NVLink
-constexpr int X_UNROLL = 4;
+constexpr int X_MAX_BLOCKS = 148;       // upper bound of the CTAs of one exchange (sizes the signal pad)
+constexpr int X_UNROLL = 8;             // 16-byte requests in flight per thread
 
 struct PeersDev {
     int rank, world;
@@ -184,9 +185,18 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange(const __grid_constant__ 
     }
 }
 
+// CTAs of one exchange: NVLink round trips are several microseconds, so the wire is only full with
+// ~10 MB of 16-byte requests in flight (CTAs x 512 threads x X_UNROLL x 16 B).  Every rank must pick
+// the same count (CTA b of every rank meets CTA b of every other).  NSB_X_BLOCKS overrides (tuning).
 static int blocks_for(long long per) {
+    static int cap = 0;
+    if (!cap) {
+        const char* e = getenv("NSB_X_BLOCKS");
+        int v = e ? atoi(e) : 0;
+        cap = (v >= 1 && v <= X_MAX_BLOCKS) ? v : 128;
+    }
     long long b = (per + (long long)X_THREADS * X_UNROLL - 1) / ((long long)X_THREADS * X_UNROLL);
-    return (int)(b < 1 ? 1 : (b > X_MAX_BLOCKS ? X_MAX_BLOCKS : b));
+    return (int)(b < 1 ? 1 : (b > cap ? cap : b));
 }
 
 static int to_dev(const NsbPeers* p, PeersDev& g, bool need_param) {

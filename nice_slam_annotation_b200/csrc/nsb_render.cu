@@ -23,7 +23,13 @@ struct Ws {
     double* z;
     float *occ0, *occ1, *rgb, *d_raw, *d_point, *d_dnorm;
     uint32_t* relu;     // [3][P][8] ReLU sign words, forward -> backward
+    uint32_t* ticket;   // fused mapping loss: arrival counter (zeroed by k_sample_z) ...
+    double* partials;   // ... and per-block partial sums
 };
+
+int sample_z_impl(const NsbPoints* rays, const float* gt_depth, const double* bound6_host, int N_samples,
+                  int N_surface, int lindisp, const float* t_uniform, const double* t_surface, const float* u,
+                  const float* depth_max, double* z_out, unsigned* zero_word, void* stream);
 
 static Ws carve_ws(void* base, int64_t N, int S) {
     Carve c(base);
@@ -38,6 +44,8 @@ static Ws carve_ws(void* base, int64_t N, int S) {
     w.d_point = c.take<float>(9 * P);
     w.d_dnorm = c.take<float>(3 * N);
     w.relu = c.take<uint32_t>(24 * P);
+    w.ticket = c.take<uint32_t>(64);
+    w.partials = c.take<double>(N / 4 + 1);
     return w;
 }
 
@@ -185,7 +193,8 @@ using namespace nsb;
 extern "C" int64_t nsb_render_workspace_bytes(int64_t N, int S) {
     const int64_t P = N * S;
     // depth_max, z, occ0, occ1, rgb, d_raw, d_point (3 planes), d_dnorm, each rounded to 256 B
-    return 256 * 11 + 256 + P * 8 + P * 4 * 2 + P * 16 * 2 + P * 36 + N * 12 + P * 96;
+    // ... relu sign words, ticket, loss partials
+    return 256 * 13 + 256 + P * 8 + P * 4 * 2 + P * 16 * 2 + P * 36 + N * 12 + P * 96 + 256 + (N / 4 + 1) * 8;
 }
 
 extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
@@ -203,13 +212,16 @@ extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
         dmax = w.depth_max;
     }
     NsbPoints rays = ray_pts(r, nullptr, 0);
-    if (int rc = nsb_sample_z(&rays, r->gt_depth, b6, r->N_samples, Nf, r->lindisp, r->t_uniform, r->t_surface,
-                              r->u, dmax, w.z, stream)) return rc;
+    const bool fused_loss = r->loss != nullptr;
+    if (fused_loss && (!r->gt_depth || !r->gt_color)) return set_error(NSB_EINVAL, "fused mapping loss needs gt_depth and gt_color");
+    if (int rc = sample_z_impl(&rays, r->gt_depth, b6, r->N_samples, Nf, r->lindisp, r->t_uniform, r->t_surface,
+                               r->u, dmax, w.z, fused_loss ? w.ticket : nullptr, stream)) return rc;
     NsbPoints pts = ray_pts(r, w.z, S);
     pts.relu_masks = w.relu;
     float *o0, *o1, *rgb;
     stage_planes(r->stage, w, o0, o1, rgb);
     if (int rc = nsb_decoders_forward(&pts, &r->scene, r->stage, o0, o1, rgb, stream)) return rc;
+    if (fused_loss) return 0;     // compositing, loss and adjoint run as one kernel in nsb_render_backward
     return nsb_composite_forward(&pts, b6, r->stage, r->occupancy, o0, o1, rgb, r->depth, r->var, r->color,
                                  nullptr, stream);
 }
@@ -227,8 +239,14 @@ extern "C" int nsb_render_backward(const NsbRenderCall* r, void* stream) {
     stage_planes(r->stage, w, o0, o1, rgb);
     const bool want_rays = (r->flags & NSB_GRAD_POINT) != 0;
     float* dn = (!r->occupancy && want_rays) ? w.d_dnorm : nullptr;
-    if (int rc = nsb_composite_backward(&pts, b6, r->stage, r->occupancy, o0, o1, rgb, r->depth, r->g_depth,
-                                        r->g_var, r->g_color, w.d_raw, dn, stream)) return rc;
+    if (r->loss) {
+        if (dn) return set_error(NSB_EINVAL, "fused mapping loss: density-mode ray gradients are not supported");
+        if (!r->var || !r->color) return set_error(NSB_EINVAL, "null argument");
+        if (int rc = nsb_composite_mapping(&pts, b6, r->stage, r->occupancy, o0, o1, rgb, r->gt_depth, r->gt_color,
+                                           r->keep, r->w_color, r->use_color, r->depth, r->var, r->color, w.d_raw,
+                                           w.partials, w.ticket, r->loss, stream)) return rc;
+    } else if (int rc = nsb_composite_backward(&pts, b6, r->stage, r->occupancy, o0, o1, rgb, r->depth, r->g_depth,
+                                               r->g_var, r->g_color, w.d_raw, dn, stream)) return rc;
     if (r->flags)
         if (int rc = nsb_decoders_backward(&pts, &r->scene, r->stage, w.d_raw, r->flags, r->dweight_mask,
                                            r->d_weight, w.d_point, r->scratch, r->scratch_bytes, stream)) return rc;

@@ -169,77 +169,81 @@ __device__ __forceinline__ void merge_sorted(const double* a, int na, const doub
     while (j < nb) out[k++] = b[j++];
 }
 
-__global__ void k_sample_z(PointsDev q, const float* __restrict__ gt_depth, BoundDev bound,
+// One thread per (ray, sample): the thread evaluates its own depth (uniform or surface list,
+// jitter from its two neighbours), the block ranks the S values of each ray against each other
+// in shared memory (NaNs last, ties by position: a stable ascending sort, i.e. what
+// torch.sort(torch.cat([z_uniform, z_surface])) returns) and writes z[rank].
+__global__ void __launch_bounds__(256) k_sample_z(PointsDev q, const float* __restrict__ gt_depth, BoundDev bound,
                            int Ns, int Nf, int lindisp, const float* __restrict__ t_uniform,
                            const double* __restrict__ t_surface, const float* __restrict__ u,
-                           const float* __restrict__ depth_max, double* __restrict__ z_out) {
-    long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (r >= q.N) return;
-    float o[3], d[3];
+                           const float* __restrict__ depth_max, double* __restrict__ z_out, int rays_per_block,
+                           unsigned* __restrict__ zero_word) {
+    extern __shared__ double sh_z[];
+    const int S = Ns + Nf;
+    const int local = threadIdx.x / S, k = threadIdx.x - local * S;
+    const long long r = blockIdx.x * (long long)rays_per_block + local;
+    if (zero_word && blockIdx.x == 0 && threadIdx.x == 0) *zero_word = 0u;
+    const bool live = local < rays_per_block && r < q.N;
+    double v = 0.0;
+    if (live) {
+        if (k < Ns) {
+            float o[3], d[3];
 #pragma unroll
-    for (int a = 0; a < 3; ++a) { o[a] = q.ro[r * q.so + a]; d[a] = q.rd[r * q.sd + a]; }
-    const double far_bb = __dadd_rn(box_exit(o, d, bound), 0.01);
-    double zu[MAX_LIST], zs[MAX_LIST];
-    float near;
-    double far;
-    float g = 0.f;
-    if (gt_depth) {
-        g = gt_depth[r];
-        near = __fmul_rn(g, 0.01f);
-        const double cap = (double)__fmul_rn(depth_max[0], 1.2f);     // max(gt_depth * 1.2)
-        far = tmin(tmax(far_bb, 0.0), cap);                            // torch.clamp(far_bb, 0, cap)
-        if (far_bb != far_bb) far = far_bb;
-    } else {
-        near = 0.01f;
-        far = far_bb;
-    }
-    for (int k = 0; k < Ns; ++k) {
-        const float t = t_uniform[k];
-        const float omt = __fsub_rn(1.f, t);
-        if (!lindisp) {
-            zu[k] = __dadd_rn((double)__fmul_rn(near, omt), __dmul_rn(far, (double)t));
-        } else {
-            const float inv_near = gt_depth ? __fdiv_rn(1.f, near) : 100.f;
-            const double s = __dadd_rn((double)__fmul_rn(inv_near, omt),
-                                       __dmul_rn(__ddiv_rn(1.0, far), (double)t));
-            zu[k] = __ddiv_rn(1.0, s);
-        }
-    }
-    if (u) {   // stratified jitter (Renderer.py:212-219)
-        double prev = zu[0], lower = zu[0];
-        for (int k = 0; k < Ns; ++k) {
-            const double cur = zu[k];
-            const double upper = (k + 1 < Ns) ? __dmul_rn(0.5, __dadd_rn(zu[k + 1], cur)) : cur;
-            if (k > 0) lower = __dmul_rn(0.5, __dadd_rn(cur, prev));
-            prev = cur;
-            zu[k] = __dadd_rn(lower, __dmul_rn(__dsub_rn(upper, lower), (double)u[r * Ns + k]));
-        }
-    }
-    double* out = z_out + r * (long long)(Ns + Nf);
-    if (Nf > 0 && gt_depth) {
-        if (g > 0.f) {       // 0.95 d .. 1.05 d (Renderer.py:177-185)
-            const double a = (double)__fmul_rn(0.95f, g), b = (double)__fmul_rn(1.05f, g);
-            for (int k = 0; k < Nf; ++k) {
-                const double ts = t_surface[k];
-                zs[k] = __dadd_rn(__dmul_rn(a, __dsub_rn(1.0, ts)), __dmul_rn(b, ts));
+            for (int a = 0; a < 3; ++a) { o[a] = q.ro[r * q.so + a]; d[a] = q.rd[r * q.sd + a]; }
+            const double far_bb = __dadd_rn(box_exit(o, d, bound), 0.01);
+            float near;
+            double far;
+            if (gt_depth) {
+                near = __fmul_rn(gt_depth[r], 0.01f);
+                const double cap = (double)__fmul_rn(depth_max[0], 1.2f);     // max(gt_depth * 1.2)
+                far = tmin(tmax(far_bb, 0.0), cap);                            // torch.clamp(far_bb, 0, cap)
+                if (far_bb != far_bb) far = far_bb;
+            } else {
+                near = 0.01f;
+                far = far_bb;
             }
-        } else {             // no sensor depth: 0.001 .. max depth of the batch (Renderer.py:191-200)
-            const double fs = (double)depth_max[0];
-            for (int k = 0; k < Nf; ++k) {
-                const double ts = t_surface[k];
-                zs[k] = __dadd_rn(__dmul_rn(0.001, __dsub_rn(1.0, ts)), __dmul_rn(fs, ts));
+            auto uniform_z = [&](int kk) -> double {
+                const float t = t_uniform[kk];
+                const float omt = __fsub_rn(1.f, t);
+                if (!lindisp) return __dadd_rn((double)__fmul_rn(near, omt), __dmul_rn(far, (double)t));
+                const float inv_near = gt_depth ? __fdiv_rn(1.f, near) : 100.f;
+                const double s = __dadd_rn((double)__fmul_rn(inv_near, omt), __dmul_rn(__ddiv_rn(1.0, far), (double)t));
+                return __ddiv_rn(1.0, s);
+            };
+            v = uniform_z(k);
+            if (u) {   // stratified jitter (Renderer.py:212-219)
+                const double lower = k > 0 ? __dmul_rn(0.5, __dadd_rn(v, uniform_z(k - 1))) : v;
+                const double upper = (k + 1 < Ns) ? __dmul_rn(0.5, __dadd_rn(uniform_z(k + 1), v)) : v;
+                v = __dadd_rn(lower, __dmul_rn(__dsub_rn(upper, lower), (double)u[r * Ns + k]));
+            }
+        } else {
+            const double ts = t_surface[k - Ns];
+            const float g = gt_depth[r];
+            if (g > 0.f) {       // 0.95 d .. 1.05 d (Renderer.py:177-185)
+                const double a = (double)__fmul_rn(0.95f, g), b = (double)__fmul_rn(1.05f, g);
+                v = __dadd_rn(__dmul_rn(a, __dsub_rn(1.0, ts)), __dmul_rn(b, ts));
+            } else {             // no sensor depth: 0.001 .. max depth of the batch (Renderer.py:191-200)
+                v = __dadd_rn(__dmul_rn(0.001, __dsub_rn(1.0, ts)), __dmul_rn((double)depth_max[0], ts));
             }
         }
-        if (is_sorted(zu, Ns) && is_sorted(zs, Nf)) {
-            merge_sorted(zu, Ns, zs, Nf, out);
-        } else {
-            for (int k = 0; k < Ns; ++k) out[k] = zu[k];
-            for (int k = 0; k < Nf; ++k) out[Ns + k] = zs[k];
-            insertion_sort(out, Ns + Nf);
-        }
-    } else {
-        for (int k = 0; k < Ns; ++k) out[k] = zu[k];
+        sh_z[threadIdx.x] = v;
     }
+    __syncthreads();
+    if (!live) return;
+    int rank = k;
+    if (Nf > 0) {                 // the uniform list alone is written in place, unsorted, like the reference
+        rank = 0;
+        const double* row = sh_z + local * S;
+        const bool vnan = v != v;
+        for (int j = 0; j < S; ++j) {
+            const double w = row[j];
+            const bool wnan = w != w;
+            const bool w_less = (w < v) || (!wnan && vnan);
+            const bool v_less = (v < w) || (!vnan && wnan);
+            rank += (w_less || (!v_less && j < k)) ? 1 : 0;
+        }
+    }
+    z_out[r * (long long)S + rank] = v;
 }
 
 // sample_pdf (common.py:19-63) on bins = mid(z), weights = w[1:-1]; then the sort-merge of
@@ -362,16 +366,28 @@ extern "C" int nsb_all_rays(int H, int W, float fx, float fy, float cx, float cy
     return check_launch("k_all_rays");
 }
 
+namespace nsb {
+int launch_sample_z(const PointsDev& q, const float* gt_depth, const BoundDev& bound, int Ns, int Nf, int lindisp,
+                    const float* t_uniform, const double* t_surface, const float* u, const float* depth_max,
+                    double* z_out, unsigned* zero_word, void* stream) {
+    const int S = Ns + Nf;
+    const int rpb = S >= 256 ? 1 : 256 / S;
+    k_sample_z<<<blocks_for(q.N, rpb), rpb * S, rpb * S * sizeof(double), (cudaStream_t)stream>>>(
+        q, gt_depth, bound, Ns, Nf, lindisp, t_uniform, t_surface, u, depth_max, z_out, rpb, zero_word);
+    return check_launch("k_sample_z");
+}
+}  // namespace nsb
+
 extern "C" int nsb_depth_max(const float* gt_depth, const uint8_t* keep, int64_t N, float* out, void* stream) {
     if (!gt_depth || !out) return set_error(NSB_EINVAL, "null argument");
     k_depth_max<<<1, 1024, 0, (cudaStream_t)stream>>>(gt_depth, keep, N, out);
     return check_launch("k_depth_max");
 }
 
-extern "C" int nsb_sample_z(const NsbPoints* rays, const float* gt_depth, const double* bound6_host,
-                            int N_samples, int N_surface, int lindisp, const float* t_uniform,
-                            const double* t_surface, const float* u, const float* depth_max,
-                            double* z_out, void* stream) {
+namespace nsb {
+int sample_z_impl(const NsbPoints* rays, const float* gt_depth, const double* bound6_host, int N_samples,
+                  int N_surface, int lindisp, const float* t_uniform, const double* t_surface, const float* u,
+                  const float* depth_max, double* z_out, unsigned* zero_word, void* stream) {
     if (!rays || !rays->rays_o || !rays->rays_d || !bound6_host || !t_uniform || !z_out)
         return set_error(NSB_EINVAL, "null argument");
     if (N_samples < 1 || N_samples > MAX_LIST || N_surface < 0 || N_surface > MAX_LIST)
@@ -381,10 +397,17 @@ extern "C" int nsb_sample_z(const NsbPoints* rays, const float* gt_depth, const 
     if (N_surface > 0 && !t_surface) return set_error(NSB_EINVAL, "t_surface is NULL");
     if (rays->N <= 0) return 0;
     PointsDev q = to_dev(*rays);
-    k_sample_z<<<blocks_for(q.N, 64), 64, 0, (cudaStream_t)stream>>>(
-        q, gt_depth, to_bound(bound6_host), N_samples, N_surface, lindisp, t_uniform, t_surface, u,
-        depth_max, z_out);
-    return check_launch("k_sample_z");
+    return launch_sample_z(q, gt_depth, to_bound(bound6_host), N_samples, N_surface, lindisp, t_uniform, t_surface,
+                           u, depth_max, z_out, zero_word, stream);
+}
+}  // namespace nsb
+
+extern "C" int nsb_sample_z(const NsbPoints* rays, const float* gt_depth, const double* bound6_host,
+                            int N_samples, int N_surface, int lindisp, const float* t_uniform,
+                            const double* t_surface, const float* u, const float* depth_max,
+                            double* z_out, void* stream) {
+    return sample_z_impl(rays, gt_depth, bound6_host, N_samples, N_surface, lindisp, t_uniform, t_surface, u,
+                         depth_max, z_out, nullptr, stream);
 }
 
 extern "C" int nsb_importance_z(const double* z, const float* weights, int64_t N, int S, int N_imp,

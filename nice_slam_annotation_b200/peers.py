@@ -62,9 +62,14 @@ class PeerGroup:
                 return [p + off for p in h.buffer_ptrs], (h.multicast_ptr + off if h.multicast_ptr else 0)
         raise RuntimeError("tensor does not live in this group's symmetric memory")
 
-    def struct(self, bucket, param=None, use_multicast=True):
+    def struct(self, bucket, param=None, use_multicast=None):
         """NsbPeers for a gradient bucket (and optionally the parameter buffer the fused optimiser
-        writes), both flat tensors from ``alloc``."""
+        writes), both flat tensors from ``alloc``.  use_multicast=None picks the faster path: with two
+        ranks the in-switch reduction moves MORE bytes per link than plain peer loads / stores (both
+        copies of a slice travel to the switch) and measures slower on B200 (48.5 MB: 0.155 ms vs
+        0.102 ms, NCCL 0.114 ms); from four ranks on it moves fewer."""
+        if use_multicast is None:
+            use_multicast = self.world > 2
         s = NsbPeers()
         s.rank, s.world = self.rank, self.world
         bp, bmc = self._ptrs(bucket)

@@ -169,6 +169,7 @@ class FusedStep:
             self._pack(k)
         self._call = self._build_call()
         self.graph = None
+        self._side = None
 
     # -- plumbing -----------------------------------------------------------------------
     def _sharded(self):
@@ -210,6 +211,11 @@ class FusedStep:
             flags |= GRAD_POINT
             call.g_rays_o, call.g_rays_d = self.g_rays_o.data_ptr(), self.g_rays_d.data_ptr()
         call.flags, call.dweight_mask = flags, mask
+        # mapping: compositing + loss + their adjoint run as one kernel inside nsb_render_backward
+        self.fused_loss = self.loss_kind == "mapping" and self.with_gt_depth and bool(r.occupancy)
+        if self.fused_loss:
+            call.gt_color, call.loss = self.gt_color.data_ptr(), self.loss.data_ptr()
+            call.w_color, call.use_color = float(self.w_color), int(self.use_color)
         return call
 
     def load(self, rays_o, rays_d, gt_depth, gt_color, keep=None, depth_max=None):
@@ -242,14 +248,27 @@ class FusedStep:
         """memset(bucket) -> re-pack trainable decoders -> forward -> loss -> backward
         [-> peer-memory all-reduce of the bucket when it lives in symmetric memory]."""
         s = _stream()
+        # the bucket memset (48 MB at Replica scale) has no consumer before the backward: it runs on a
+        # side branch, under the forward
+        joined = None
         if self.bucket is not None:
-            self.bucket.zero()
+            main = torch.cuda.current_stream()
+            if self._side is None:
+                self._side = torch.cuda.Stream()
+            self._side.wait_stream(main)
+            with torch.cuda.stream(self._side):
+                self.bucket.zero()
+            joined = self._side
         for k in self.dec_grad_kinds:
             self._pack(k)
         call = self._call
         check(lib().nsb_render_forward(C.byref(call), s), "render_forward")
+        if joined is not None:
+            torch.cuda.current_stream().wait_stream(joined)
         gd = _ptr(self.gt_depth)
-        if self.loss_kind == "mapping":
+        if self.fused_loss:
+            pass
+        elif self.loss_kind == "mapping":
             check(lib().nsb_mapping_loss(_ptr(self.depth), _ptr(self.color), gd, _ptr(self.gt_color), _ptr(self.keep),
                                          self.N, float(self.w_color), int(self.use_color), _ptr(self.loss),
                                          _ptr(self.g_depth), _ptr(self.g_color), s), "mapping_loss")
