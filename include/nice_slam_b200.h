@@ -337,6 +337,28 @@ int nsb_cam_adam(float* cam, const float* d_cam, float* m, float* v, int32_t* st
 int nsb_adam(float* p, const float* g, float* m, float* v, int64_t n, const uint8_t* voxel_mask,
              int32_t* state2, const float* lr, float beta1, float beta2, float eps, void* stream);
 
+/* ---- once per mapped frame: frustum feature selection and keyframe overlap ----------
+ * nsb_frustum_mask = Mapper.get_mask_from_c2w (src/Mapper.py:100-187): voxel centres of a grid
+ * (xs [nx], ys [ny], zs [nz]: the torch.linspace values of the bound, device) are projected into the
+ * current frame (w2c = np.linalg.inv(c2w) float32 row-major [16] and cam_pos = c2w[:3,3], both HOST),
+ * the depth image (device [H,W] fp32) is looked up as cv2.remap INTER_LINEAR does (1/32-pixel fixed
+ * point, BORDER_CONSTANT 0; zero look-ups take the maximum look-up), and a voxel is selected when it
+ * projects inside the image with 0 <= -z <= depth + 0.5, or lies within 0.5 m of the camera.  Outputs
+ * (either may be NULL): mask_xyz [nx,ny,nz] (the reference's array) and mask_zyx [nz,ny,nx] (one byte per
+ * 128-byte voxel line of a channels-last grid: what nsb_adam / nsb_bucket_reduce_adam take).  scratch:
+ * one device word.  Bit-exact with the reference (tests/golden/frustum.npz).
+ * nsb_keyframe_overlap = the scores of Mapper.keyframe_selection_overlap (src/Mapper.py:189-293): for
+ * every keyframe k (w2c [K,16] fp32 device) the number of the N x N_samples points o + d z,
+ * z = 0.8 gt (1 - t) + (gt + 0.5) t, that project inside its image shrunk by `edge` pixels with
+ * camera z < 0; percent_inside = counts[k] / (N N_samples). */
+int nsb_frustum_mask(const float* w2c_host, const float* cam_pos_host, const float* xs, const float* ys,
+                     const float* zs, int nx, int ny, int nz, const float* depth, int H, int W, double fx,
+                     double fy, double cx, double cy, uint32_t* scratch, uint8_t* mask_xyz, uint8_t* mask_zyx,
+                     void* stream);
+int nsb_keyframe_overlap(const float* rays_o, const float* rays_d, const float* gt_depth, int64_t N,
+                         int N_samples, const float* t_vals, const float* w2c, int K, int H, int W, double fx,
+                         double fy, double cx, double cy, int edge, int32_t* counts, void* stream);
+
 /* ---- gradient exchange of the sharded mapping step over NVLink peer memory -------
  * The reference maps on one GPU; its loss is a plain sum over rays (src/Mapper.py:605-612), so ranks
  * that render disjoint ray slices hold partial gradients that add.  The gradient bucket of every rank

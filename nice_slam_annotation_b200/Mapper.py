@@ -7,14 +7,15 @@ while keeping the reference's logical shape [1,32,Z,Y,X]; everything the referen
 them (boolean-mask indexing, Adam, checkpointing) works unchanged on such tensors.
 
 ``get_mask_from_c2w`` and ``keyframe_selection_overlap`` (Mapper.py:100-293) are callers of
-the path that run once per mapped frame; they are restated here with torch ops on the
-device (SURVEY.md 8f-2 marks them "next"; they are not kernels yet).  The frame loop
+the path that run once per mapped frame: both are kernels
+(csrc/nsb_frustum.cu), bit-exact with the reference's numpy + cv2.remap pass.  The frame loop
 ``run()`` stays with the reference.
 """
 import numpy as np
 import torch
 
 from . import fused
+from ._lib import check, lib
 from .common import get_camera_from_tensor, get_samples, get_tensor_from_camera, random_select
 
 
@@ -70,56 +71,65 @@ class Mapper(object):
         self._loops = {}
         self.H, self.W, self.fx, self.fy, self.cx, self.cy = slam.H, slam.W, slam.fx, slam.fy, slam.cx, slam.cy
 
-    # ---- callers of the hot path, once per mapped frame ------------------------------------
-    def _project(self, points, c2w):
-        """world points [P,3] -> pixel uv [P,2], camera z [P] (Mapper.py:129-146,256-271)."""
-        c2w = c2w.detach().to(points.device).double()
-        if c2w.shape[0] == 3:
-            c2w = torch.cat([c2w, torch.tensor([[0, 0, 0, 1.]], dtype=torch.float64, device=points.device)], 0)
-        w2c = torch.linalg.inv(c2w)
-        cam = points.double() @ w2c[:3, :3].T + w2c[:3, 3]
-        x, y, z = -cam[:, 0], cam[:, 1], cam[:, 2]
-        zz = z + 1e-5
-        u = (self.fx * x + self.cx * z) / zz
-        v = (self.fy * y + self.cy * z) / zz
-        return torch.stack([u, v], -1).float(), zz
+    # ---- callers of the hot path, once per mapped frame (kernels: csrc/nsb_frustum.cu) -------
+    @staticmethod
+    def _w2c_host(c2w):
+        """np.linalg.inv of the float32 pose on the host, as the reference does (Mapper.py:121-122,
+        225-226): 16 floats of scalar prep, so the kernels see bit-identical matrices."""
+        m = np.asarray(c2w.detach().cpu().numpy() if torch.is_tensor(c2w) else c2w, dtype=np.float32)
+        if m.shape[-2] == 3:
+            pad = np.broadcast_to(np.array([[0, 0, 0, 1]], dtype=np.float32), m.shape[:-2] + (1, 4))
+            m = np.concatenate([m, pad], -2)
+        return m, np.linalg.inv(m)
 
     def get_mask_from_c2w(self, c2w, key, val_shape, depth_np):
         """Frustum feature selection (Mapper.py:100-187): boolean numpy mask [X,Y,Z] of the voxels
         of grid ``key`` seen by the current frame.  ``depth_np`` may be a numpy array or a tensor."""
-        return self._frustum_mask(c2w, key, val_shape, depth_np).cpu().numpy()
+        return self._frustum_mask(c2w, key, val_shape, depth_np, order='xyz').cpu().numpy()
 
-    def _frustum_mask(self, c2w, key, val_shape, depth_np):
-        """get_mask_from_c2w as a device tensor (no host round trip).  Depth is looked up
-        bilinearly (the reference uses cv2.remap INTER_LINEAR, whose 5-bit fixed-point weights
-        differ in the last bits)."""
+    def _frustum_mask(self, c2w, key, val_shape, depth_np, order='zyx'):
+        """get_mask_from_c2w as a device tensor (nsb_frustum_mask, bit-exact with the reference's
+        numpy + cv2.remap pass): bool [X,Y,Z] (order='xyz', the reference's array) or [Z,Y,X]
+        (order='zyx', one flag per voxel line of the channels-last grid)."""
         dev = self.device
+        nz, ny, nx = (int(v) for v in val_shape)
         if key == 'grid_coarse':
-            return torch.ones(tuple(val_shape)[::-1], dtype=torch.bool, device=dev)
-        b = torch.as_tensor(self.bound, dtype=torch.float32)
-        X, Y, Z = torch.meshgrid(torch.linspace(float(b[0][0]), float(b[0][1]), val_shape[2]),
-                                 torch.linspace(float(b[1][0]), float(b[1][1]), val_shape[1]),
-                                 torch.linspace(float(b[2][0]), float(b[2][1]), val_shape[0]), indexing='ij')
-        points = torch.stack([X, Y, Z], dim=-1).reshape(-1, 3).to(dev)
-        depth = torch.as_tensor(depth_np, dtype=torch.float32, device=dev)
-        uv, z = self._project(points, c2w)
-        H, W = self.H, self.W
-        x0 = torch.floor(uv[:, 0])
-        y0 = torch.floor(uv[:, 1])
-        wx, wy = uv[:, 0] - x0, uv[:, 1] - y0
+            return torch.ones((nx, ny, nz) if order == 'xyz' else (nz, ny, nx), dtype=torch.bool, device=dev)
+        b = self.bound
+        xs = torch.linspace(float(b[0][0]), float(b[0][1]), nx).to(dev)
+        ys = torch.linspace(float(b[1][0]), float(b[1][1]), ny).to(dev)
+        zs = torch.linspace(float(b[2][0]), float(b[2][1]), nz).to(dev)
+        depth = torch.as_tensor(depth_np, dtype=torch.float32).to(dev).contiguous()
+        m, w2c = self._w2c_host(c2w)
+        w2c = np.ascontiguousarray(w2c, dtype=np.float32)
+        cam = np.ascontiguousarray(m[:3, 3], dtype=np.float32)
+        out = torch.empty((nx, ny, nz) if order == 'xyz' else (nz, ny, nx), dtype=torch.uint8, device=dev)
+        scratch = torch.empty(1, dtype=torch.int32, device=dev)
+        check(lib().nsb_frustum_mask(w2c.ctypes.data, cam.ctypes.data, fused._ptr(xs), fused._ptr(ys), fused._ptr(zs),
+                                     nx, ny, nz, fused._ptr(depth), int(self.H), int(self.W), float(self.fx),
+                                     float(self.fy), float(self.cx), float(self.cy), fused._ptr(scratch),
+                                     fused._ptr(out) if order == 'xyz' else None,
+                                     fused._ptr(out) if order != 'xyz' else None, fused._stream()), "frustum_mask")
+        return out.bool()
 
-        def tap(xi, yi):        # BORDER_CONSTANT 0 outside the image, as cv2.remap defaults to
-            ok = (xi >= 0) & (xi < W) & (yi >= 0) & (yi < H)
-            v = depth[yi.clamp(0, H - 1).long(), xi.clamp(0, W - 1).long()]
-            return torch.where(ok, v, torch.zeros_like(v))
-        depths = (tap(x0, y0) * (1 - wx) * (1 - wy) + tap(x0 + 1, y0) * wx * (1 - wy) +
-                  tap(x0, y0 + 1) * (1 - wx) * wy + tap(x0 + 1, y0 + 1) * wx * wy)
-        mask = (uv[:, 0] < W) & (uv[:, 0] > 0) & (uv[:, 1] < H) & (uv[:, 1] > 0)
-        depths = torch.where(depths == 0, depths.max(), depths)
-        mask = mask & (0 <= -z) & (-z <= depths.double() + 0.5)
-        ray_o = c2w[:3, 3].detach().to(dev).float()
-        mask = mask | (((points - ray_o) ** 2).sum(1) < 0.25)
-        return mask.reshape(val_shape[2], val_shape[1], val_shape[0])
+    def keyframe_overlap_scores(self, rays_o, rays_d, gt_depth, keyframe_c2ws, N_samples=16, edge=20):
+        """percent_inside of every keyframe (Mapper.py:224-252) as one kernel launch
+        (nsb_keyframe_overlap): float64 numpy [K]."""
+        dev = self.device
+        K = len(keyframe_c2ws)
+        if K == 0:
+            return np.zeros(0)
+        _, w2c = self._w2c_host(torch.stack([torch.as_tensor(c).detach().cpu().float() for c in keyframe_c2ws]))
+        w2c = torch.from_numpy(np.ascontiguousarray(w2c, dtype=np.float32)).to(dev)
+        ro, rd = rays_o.detach().float().contiguous(), rays_d.detach().float().contiguous()
+        gd = gt_depth.detach().float().reshape(-1).contiguous()
+        t_vals = torch.linspace(0., 1., steps=N_samples).to(dev)
+        counts = torch.zeros(K, dtype=torch.int32, device=dev)
+        check(lib().nsb_keyframe_overlap(fused._ptr(ro), fused._ptr(rd), fused._ptr(gd), ro.shape[0], N_samples,
+                                         fused._ptr(t_vals), fused._ptr(w2c), K, int(self.H), int(self.W),
+                                         float(self.fx), float(self.fy), float(self.cx), float(self.cy), int(edge),
+                                         fused._ptr(counts), fused._stream()), "keyframe_overlap")
+        return counts.cpu().numpy() / float(ro.shape[0] * N_samples)
 
     def keyframe_selection_overlap(self, gt_color, gt_depth, c2w, keyframe_dict, k, N_samples=16, pixels=100):
         """Keyframes whose view overlaps the current frame (Mapper.py:189-293)."""
@@ -127,16 +137,8 @@ class Mapper(object):
         H, W, fx, fy, cx, cy = self.H, self.W, self.fx, self.fy, self.cx, self.cy
         rays_o, rays_d, gt_depth, gt_color = get_samples(
             0, H, 0, W, pixels, H, W, fx, fy, cx, cy, c2w, gt_depth.to(device), gt_color.to(device), device)
-        gt_depth = gt_depth.reshape(-1, 1).repeat(1, N_samples)
-        t_vals = torch.linspace(0., 1., steps=N_samples).to(device)
-        z_vals = gt_depth * 0.8 * (1. - t_vals) + (gt_depth + 0.5) * t_vals
-        pts = (rays_o[..., None, :] + rays_d[..., None, :] * z_vals[..., :, None]).reshape(-1, 3).detach()
-        list_keyframe = []
-        edge = 20
-        for keyframeid, keyframe in enumerate(keyframe_dict):
-            uv, z = self._project(pts, keyframe['est_c2w'])
-            mask = (uv[:, 0] < W - edge) & (uv[:, 0] > edge) & (uv[:, 1] < H - edge) & (uv[:, 1] > edge) & (z < 0)
-            list_keyframe.append({'id': keyframeid, 'percent_inside': float(mask.sum()) / uv.shape[0]})
+        scores = self.keyframe_overlap_scores(rays_o, rays_d, gt_depth, [kf['est_c2w'] for kf in keyframe_dict], N_samples)
+        list_keyframe = [{'id': i, 'percent_inside': s} for i, s in enumerate(scores)]
         list_keyframe = sorted(list_keyframe, key=lambda i: i['percent_inside'], reverse=True)
         selected = [dic['id'] for dic in list_keyframe if dic['percent_inside'] > 0.00]
         return list(np.random.permutation(np.array(selected))[:k])
@@ -397,7 +399,7 @@ class Mapper(object):
         if masked:
             masks = {}
             for gk in loop.grid_keys:
-                masks[gk] = self._frustum_mask(cur_c2w, gk, self.c[gk].shape[2:], cur_gt_depth).permute(2, 1, 0)
+                masks[gk] = self._frustum_mask(cur_c2w, gk, self.c[gk].shape[2:], cur_gt_depth)
         loop.begin(frames, masks)
         prev = None
         for joint_iter in range(num_joint_iters):

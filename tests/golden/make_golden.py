@@ -438,8 +438,57 @@ def gen_trained():
           "L1", np.abs(d - gd.numpy())[gd.numpy() > 0].mean())
 
 
+def gen_frustum():
+    """f2: Mapper.get_mask_from_c2w (cv2.remap inside) and the keyframe scores of
+    Mapper.keyframe_selection_overlap, from the reference itself."""
+    import src.Mapper as ref_mapper
+    cfg = load_cfg(True)
+    cfg["grid_len"].update({"coarse": 1.0, "middle": 0.16, "fine": 0.08, "color": 0.08})
+    cam = (60, 80, 70.0, 70.0, 39.5, 29.5)
+    bound = [[-1.4, 1.6], [-1.1, 1.3], [-1.0, 1.1]]
+    slam = build_scene(cfg, cam, bound, seed=0)
+    mapper = make_mapper(slam, cfg, frustum=True)
+    out = {"bound": slam.bound.numpy(), "cam": np.array(cam)}
+    room = torch.stack([slam.bound[:, 0] + 0.3, slam.bound[:, 1] - 0.3], 1)
+    poses = synth.orbit_poses(room, 6, seed=4)
+    n_mask = 0
+    for i in (0, 2, 5):
+        c2w = poses[i].float()
+        depth, color = synth.make_frame(*cam, room, poses[i], zero_frac=0.05, seed=10 + i)
+        out[f"f{i}.c2w"], out[f"f{i}.depth"] = c2w.numpy(), depth.numpy()
+        for key in ("grid_coarse", "grid_middle", "grid_fine"):
+            val_shape = slam.shared_c[key].shape[2:]
+            m = mapper.get_mask_from_c2w(c2w, key, val_shape, depth.numpy())
+            out[f"f{i}.{key}.shape"] = np.array(val_shape)
+            out[f"f{i}.{key}.mask"] = np.packbits(np.asarray(m).reshape(-1))
+            n_mask += 1
+            print("frustum", i, key, tuple(val_shape), float(np.asarray(m).mean()))
+    # keyframe scores: spy on the sort of list_keyframe (Mapper.py:254)
+    seen = {}
+
+    def spy_sorted(lst, **kw):
+        seen["scores"] = [d["percent_inside"] for d in lst]
+        return sorted(lst, **kw)
+    ref_mapper.sorted = spy_sorted
+    c2w = poses[0].float()
+    depth, color = synth.make_frame(*cam, room, poses[0], zero_frac=0.0, seed=3)
+    kfs = [{"est_c2w": p.float()} for p in poses]
+    torch.manual_seed(77)
+    out["k.indices"] = torch.randint(cam[0] * cam[1], (100,)).numpy()
+    torch.manual_seed(77)
+    np.random.seed(0)
+    sel = mapper.keyframe_selection_overlap(color, depth, c2w, kfs, 3)
+    del ref_mapper.sorted
+    out["k.c2w"], out["k.depth"], out["k.color"] = c2w.numpy(), depth.numpy(), color.numpy()
+    out["k.kf_c2w"] = np.stack([p.float().numpy() for p in poses])
+    out["k.scores"] = np.array(seen["scores"], dtype=np.float64)
+    out["k.selected"] = np.array(sel)
+    print("keyframe scores", out["k.scores"], "selected", sel)
+    np.savez_compressed(os.path.join(HERE, "frustum.npz"), **out)
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["small", "variants", "units", "imap", "imap256", "trained"]
+    which = sys.argv[1:] or ["small", "variants", "units", "imap", "imap256", "trained", "frustum"]
     torch.set_num_threads(1)
     if "small" in which:
         gen_small_nice()
@@ -453,6 +502,8 @@ if __name__ == "__main__":
         gen_imap(256, "imap256")
     if "trained" in which:
         gen_trained()
+    if "frustum" in which:
+        gen_frustum()
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)) // 1024, "KiB")
