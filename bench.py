@@ -252,12 +252,19 @@ def run_ours(args):
         else:
             launches = int(L.nsb_launch_count(0) * args.steps / (args.steps + args.warmup))
         host_batches = [tuple(x.cpu().pin_memory() for x in b) for b in batches]
-        ms_nccl = None
+        ms_nccl = x_err = None
+        x_err = None
         if peers is not None:                            # the same step with the NCCL all-reduce, for comparison
             step_peer, step = step, FusedStep(ns.renderer, dec, grids, STAGE, args.rays, **step_kw)
             if not args.no_graph:
                 step.load(*batches[0]); step.run(); step.capture()
             ms_nccl = timed(step_device, batches, args.steps, args.warmup)
+            # the two exchanges must agree (atomic scatter order differs between runs: not bit-exact)
+            step.load(*batches[0]); step.run()
+            step_peer.load(*batches[0]); step_peer.run()
+            torch.cuda.synchronize()
+            x_err = float((step.bucket.flat - step_peer.bucket.flat).abs().max() / step.bucket.flat.abs().max())
+            peers.check_error()
             step = step_peer
         ms_e2e = timed(step_e2e, host_batches, args.steps, args.warmup)
         ms_eng = timed(step_engine_host, host_batches, args.steps, args.warmup)
@@ -289,7 +296,8 @@ def run_ours(args):
                              + ("" if args.no_graph else ", replayed as one CUDA graph"),
                    "parallelism": f"rays sharded over {world} GPU(s), grids+decoders replicated"
                                   + ("; gradient exchange: " + exchange if world > 1 else ""),
-                   "exchange": exchange, "ms_per_step_with_nccl_allreduce": ms_nccl},
+                   "exchange": exchange, "ms_per_step_with_nccl_allreduce": ms_nccl,
+                   "exchange_max_rel_diff_vs_nccl": x_err},
         "e2e": {"value": world * n_rays / (ms_eng * 1e-3), "unit": "rays/s", "ms_per_step": ms_eng,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
                 "api": "FusedStep.load(ray batch in pinned host memory) + run() + loss.item(): the engine call "
@@ -315,6 +323,7 @@ def run_ours(args):
         out["torch_cuda_baseline"] = torch_cuda_port(ns, batches, dev)
         out["cpu_baseline"] = cpu_baseline(ns, batches, budget_s=12.0)
     if rank == 0 and world == 1 and not args.no_tracking:
+        out["bulk_forward"] = bulk_forward_bench(ns, dev)
         out["optimize_map"] = optimize_map_bench(ns, dev)              # last: it trains the scene
     if rank == 0:
         print(json.dumps(out), flush=True)
@@ -444,6 +453,37 @@ def tracking_bench(dev, iters, warmup):
                        "engine": "Tracker.optimize_cam_fused / step.TrackingStep: one CUDA graph per iteration, "
                                  "pixel draw + candidate rule on the device"},
             "final_loss": best}
+
+
+def bulk_forward_bench(ns, dev):
+    """SURVEY.md 8 f3, the bulk forward consumers: Renderer.render_img (Renderer.py:264-340, the whole
+    680x1200 frame in 100k-ray batches, what the visualiser calls) and Renderer.eval_points on a
+    256^3 query lattice in 500k-point batches (what Mesher.get_mesh issues, Mesher.py:563-575)."""
+    c2w, depth, color = ns.frames[-1]
+    r, dec, c = ns.renderer, ns.shared_decoders, ns.shared_c
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def timed(fn, reps):
+        fn()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+    ms_img = timed(lambda: r.render_img(c, dec, c2w, dev, "color", gt_depth=depth), 3)
+    n = 256
+    b = torch.as_tensor(ns.bound, dtype=torch.float32)
+    ax = [torch.linspace(float(b[a][0]) + 0.01, float(b[a][1]) - 0.01, n, device=dev) for a in range(3)]
+    pts = torch.stack(torch.meshgrid(*ax, indexing="ij"), -1).reshape(-1, 3)
+    with torch.no_grad():
+        ms_pts = timed(lambda: r.eval_points(pts, dec, c, "color", dev), 2)
+    H, W = r.H, r.W
+    return {"render_img": {"rays": H * W, "ms": ms_img, "rays_per_s": H * W / (ms_img * 1e-3),
+                           "what": "Renderer.render_img, stage color, gt depth given, 100k-ray batches, forward only"},
+            "eval_points": {"points": n ** 3, "ms": ms_pts, "points_per_s": n ** 3 / (ms_pts * 1e-3),
+                            "what": "Renderer.eval_points, 256^3 lattice inside the bound, 500k-point batches, stage color"}}
 
 
 def optimize_map_bench(ns, dev, iters=60):

@@ -136,3 +136,22 @@ def test_fused_losses_vs_oracle(scene, handle_dynamic):
     assert_close(l1.detach().cpu().reshape(1), l0.detach().reshape(1), 1e-6, "mapping loss")
     assert_close(d1.grad.cpu(), d0.grad, 1e-7, "d loss/d depth")
     assert_close(c1.grad.cpu(), c0.grad, 1e-6, "d loss/d color")
+
+
+def test_render_img_vs_oracle(scene):
+    """f3: Renderer.render_img (Renderer.py:264-340) = get_rays + render_batch_ray over the whole
+    frame (one 100k-ray batch here), against the oracle on every pixel."""
+    ns = scene
+    c2w, depth, color = ns.frames[0]
+    H, W = ns.renderer.H, ns.renderer.W
+    d, v, col = ns.renderer.render_img(ns.shared_c, ns.shared_decoders, c2w, "cuda:0", "color", gt_depth=depth)
+    assert d.shape == (H, W) and d.dtype == torch.float64 and v.dtype == torch.float64 and col.shape == (H, W, 3)
+    prm = {k: t.detach().cpu() for k, t in ns.shared_decoders.state_dict().items()}
+    cg = {k: t.detach().cpu().contiguous() for k, t in ns.shared_c.items()}
+    ro, rd = O.get_rays(H, W, ns.fx, ns.fy, ns.cx, ns.cy, c2w.cpu())
+    with torch.no_grad():
+        d0, v0, c0 = O.render_batch_ray(prm, cg, rd.reshape(-1, 3), ro.reshape(-1, 3), "color", depth.cpu().reshape(-1),
+                                        ns.bound)
+    assert_close(d.cpu().reshape(-1), d0, 1e-4, "depth")
+    assert_close(v.cpu().reshape(-1), v0, 1e-4, "var")
+    assert_close(col.cpu().reshape(-1, 3), c0, 1e-4, "color")
