@@ -378,6 +378,9 @@ typedef struct NsbPeers {
     float* param_multicast;
     uint32_t* signal[NSB_MAX_PEERS];
     int32_t* error;
+    float* scalar[NSB_MAX_PEERS];     /* nsb_depth_max_peers only: one symmetric float per rank */
+    uint32_t* touched[NSB_MAX_PEERS]; /* nsb_bucket_allreduce_sparse only: per-rank symmetric scratch of
+                                       * nsb_exchange_touched_words(bucket floats) words, mapped like bucket */
 } NsbPeers;
 int64_t nsb_exchange_signal_words(void);
 
@@ -386,6 +389,16 @@ int64_t nsb_exchange_signal_words(void);
  * rank order) and stores the sum into every copy (multimem.st / peer stores); block-wise flag barriers
  * before and after.  Replaces dist.all_reduce on the flat gradient bucket.  offset, n: multiples of 4. */
 int nsb_bucket_allreduce(const NsbPeers* peers, int64_t offset, int64_t n, void* stream);
+/* The same sum, moving only the 128-byte lines some rank touched: every rank scans its copy and
+ * publishes one bit per line (peers->touched), owners reduce the union.  A mapping step touches 16-39 % of
+ * the lines of a Replica-scale bucket, so this is the exchange of the sharded step; lines that are zero
+ * on every rank are left alone (they stay zero).  offset: multiple of 32 floats; buffers 128-byte aligned. */
+int64_t nsb_exchange_touched_words(int64_t n);
+/* nsb_depth_max over the kept rays of ALL ranks (the render's one batch-global scalar, Renderer.py:157),
+ * through peers->scalar: what a rank that renders a shard passes as NsbRenderCall.depth_max. */
+int nsb_depth_max_peers(const NsbPeers* peers, const float* gt_depth, const uint8_t* keep, int64_t N,
+                        float* out, void* stream);
+int nsb_bucket_allreduce_sparse(const NsbPeers* peers, int64_t offset, int64_t n, void* stream);
 
 /* The same reduction fused with the mapper's Adam step (src/Mapper.py:462-482, 633-642; semantics of
  * nsb_adam): rank r sums the r-th slice of bucket[offset, offset + n), updates

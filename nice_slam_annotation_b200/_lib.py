@@ -64,7 +64,8 @@ NSB_MAX_PEERS = 8
 class NsbPeers(C.Structure):
     _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("bucket", c_ptr * NSB_MAX_PEERS),
                 ("bucket_multicast", c_ptr), ("param", c_ptr * NSB_MAX_PEERS), ("param_multicast", c_ptr),
-                ("signal", c_ptr * NSB_MAX_PEERS), ("error", c_ptr)]
+                ("signal", c_ptr * NSB_MAX_PEERS), ("error", c_ptr), ("scalar", c_ptr * NSB_MAX_PEERS),
+                ("touched", c_ptr * NSB_MAX_PEERS)]
 
 
 _SIGS = {
@@ -128,6 +129,9 @@ _SIGS = {
     "nsb_exchange_signal_words": (C.c_int64, []),
     "nsb_bucket_allreduce": (C.c_int, [C.POINTER(NsbPeers), C.c_int64, C.c_int64, c_ptr]),
     "nsb_exchange_slice": (C.c_int64, [C.c_int, C.c_int, C.c_int64, c_ptr]),
+    "nsb_exchange_touched_words": (C.c_int64, [C.c_int64]),
+    "nsb_depth_max_peers": (C.c_int, [C.POINTER(NsbPeers), c_ptr, c_ptr, C.c_int64, c_ptr, c_ptr]),
+    "nsb_bucket_allreduce_sparse": (C.c_int, [C.POINTER(NsbPeers), C.c_int64, C.c_int64, c_ptr]),
     "nsb_bucket_reduce_adam": (C.c_int, [C.POINTER(NsbPeers), C.c_int64, C.c_int64, C.c_int64, c_ptr, c_ptr, c_ptr,
                                          c_ptr, c_ptr, C.c_float, C.c_float, C.c_float, c_ptr]),
     "nsb_imap_workspace_floats": (C.c_int64, [C.c_int64, C.c_int, C.c_int]),

@@ -37,6 +37,8 @@ struct PeersDev {
     float* bucket_mc;
     float* param_mc;
     unsigned* signal[NSB_MAX_PEERS];
+    unsigned* touched[NSB_MAX_PEERS];
+    float* scalar[NSB_MAX_PEERS];
     int* error;
 };
 
@@ -185,9 +187,126 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange(const __grid_constant__ 
     }
 }
 
+// Sparse two-shot all-reduce.  One mapping step touches 16 % (1000 rays) to 39 % (8000 rays) of the
+// 128-byte voxel lines of the Replica bucket (scripts/bucket_sparsity.py), so most of a dense
+// exchange moves zeros.  Unit = 32 lines (4 KB); rank o owns units [o * per_u, (o + 1) * per_u).
+//   A  every rank scans its local copy and publishes one bit per line (word per unit) in symmetric memory
+//   -- barrier --
+//   C  the owner ORs the words of all ranks and reduces / stores only lines some rank touched
+//   -- barrier --
+// Untouched lines are zero in every copy and stay so.  CTA b meets CTA b of the peers only, so the
+// units CTA b scans in A (for every owner) are exactly the units CTA b of that owner handles in C.
+constexpr int X_WARPS = X_THREADS / 32;
+__device__ __forceinline__ bool line_on(unsigned word, int j, int lane) { return (word >> (4 * j + (lane >> 3))) & 1u; }
+
+__global__ void __launch_bounds__(X_THREADS) k_exchange_sparse(const __grid_constant__ PeersDev g, long long off,
+                                                                long long n4, long long n_units, long long per_u) {
+    const int lane = threadIdx.x & 31;
+    const long long gw = (long long)blockIdx.x * X_WARPS + (threadIdx.x >> 5), nw = (long long)gridDim.x * X_WARPS;
+    // ---- A: touched bits of the local copy, pushed to the owner of each unit (posted peer stores: the
+    //         owner later reads every rank's word from its OWN memory, no NVLink round trip)
+    const float4* mine = reinterpret_cast<const float4*>(g.bucket[g.rank] + off);
+    for (int o = 0; o < g.world; ++o)
+        for (long long v = gw; v < per_u; v += nw) {
+            const long long u = o * per_u + v;
+            if (u >= n_units) break;
+            unsigned word = 0u;
+            float4 x[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const long long i4 = u * 256 + j * 32 + lane;
+                x[j] = i4 < n4 ? __ldcg(mine + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const bool nz = (x[j].x != 0.f) | (x[j].y != 0.f) | (x[j].z != 0.f) | (x[j].w != 0.f);
+                const unsigned b = __ballot_sync(FULL, nz);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) word |= ((b >> (8 * q)) & 0xffu) ? (1u << (4 * j + q)) : 0u;
+            }
+            if (lane == 0) {
+                unsigned* dst = g.touched[o] + g.rank * per_u + v;
+                asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(dst), "r"(word) : "memory");
+            }
+        }
+    peer_barrier(g, (0 * X_MAX_BLOCKS + blockIdx.x) * NSB_MAX_PEERS);
+    // ---- C: reduce the lines of my units that some rank touched, two units per pass (16 requests in
+    //         flight per lane)
+    const unsigned* words = g.touched[g.rank];
+    for (long long v0 = gw; v0 < per_u; v0 += 2 * nw) {
+        const long long v[2] = {v0, v0 + nw};
+        unsigned word[2];
+        float4 s[2][8];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            unsigned w = 0u;
+            const bool live = v[k] < per_u && g.rank * per_u + v[k] < n_units;
+            if (live && lane < g.world) {
+                const unsigned* p = words + lane * per_u + v[k];
+                asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(w) : "l"(p) : "memory");
+            }
+            word[k] = __reduce_or_sync(FULL, w);
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            if (!word[k]) continue;
+            const long long u = g.rank * per_u + v[k];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const long long i4 = u * 256 + j * 32 + lane;
+                if (line_on(word[k], j, lane) && i4 < n4) s[k][j] = reduce_at(g, off + 4 * i4);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            if (!word[k]) continue;
+            const long long u = g.rank * per_u + v[k];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const long long i4 = u * 256 + j * 32 + lane;
+                if (!(line_on(word[k], j, lane) && i4 < n4)) continue;
+                if (g.bucket_mc) mc_st(g.bucket_mc + off + 4 * i4, s[k][j]);
+                else
+                    for (int r = 0; r < g.world; ++r) peer_st(g.bucket[r] + off + 4 * i4, s[k][j]);
+            }
+        }
+    }
+    peer_barrier(g, (1 * X_MAX_BLOCKS + blockIdx.x) * NSB_MAX_PEERS);
+}
+
 // CTAs of one exchange: NVLink round trips are several microseconds, so the wire is only full with
 // ~10 MB of 16-byte requests in flight (CTAs x 512 threads x X_UNROLL x 16 B).  Every rank must pick
 // the same count (CTA b of every rank meets CTA b of every other).  NSB_X_BLOCKS overrides (tuning).
+// max(gt_depth) over the kept rays of ALL ranks (src/utils/Renderer.py:157,194 on the whole batch): the
+// one batch-global scalar of the render.  One CTA: local max -> own symmetric slot -> barrier -> max of
+// every rank's slot -> barrier (slots are free again).  NaN propagates like torch.max.
+__device__ __forceinline__ float nanmax(float a, float b) { return (b > a || b != b) ? b : a; }
+__global__ void __launch_bounds__(1024) k_depth_max_peers(const __grid_constant__ PeersDev g, const float* __restrict__ gt,
+                                                           const uint8_t* __restrict__ keep, long long n,
+                                                           float* __restrict__ out) {
+    __shared__ float part[32];
+    float m = -INFINITY;
+    for (long long i = threadIdx.x; i < n; i += blockDim.x)
+        if (!keep || keep[i]) m = nanmax(m, gt[i]);
+    for (int s = 16; s > 0; s >>= 1) m = nanmax(m, __shfl_xor_sync(FULL, m, s));
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        m = threadIdx.x < (blockDim.x >> 5) ? part[threadIdx.x] : -INFINITY;
+        for (int s = 16; s > 0; s >>= 1) m = nanmax(m, __shfl_xor_sync(FULL, m, s));
+        if (threadIdx.x == 0) asm volatile("st.volatile.global.f32 [%0], %1;" :: "l"(g.scalar[g.rank]), "f"(m) : "memory");
+    }
+    peer_barrier(g, 0);
+    if (threadIdx.x < 32) {
+        float v = -INFINITY;
+        if (threadIdx.x < g.world)
+            asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(g.scalar[threadIdx.x]) : "memory");
+        for (int s = 16; s > 0; s >>= 1) v = nanmax(v, __shfl_xor_sync(FULL, v, s));
+        if (threadIdx.x == 0) out[0] = v;
+    }
+    peer_barrier(g, X_MAX_BLOCKS * NSB_MAX_PEERS);
+}
+
 static int blocks_for(long long per) {
     static int cap = 0;
     if (!cap) {
@@ -208,6 +327,8 @@ static int to_dev(const NsbPeers* p, PeersDev& g, bool need_param) {
         g.bucket[r] = r < p->world ? p->bucket[r] : nullptr;
         g.param[r] = r < p->world ? p->param[r] : nullptr;
         g.signal[r] = r < p->world ? p->signal[r] : nullptr;
+        g.touched[r] = r < p->world ? p->touched[r] : nullptr;
+        g.scalar[r] = r < p->world ? p->scalar[r] : nullptr;
         if (r < p->world && (!g.bucket[r] || !g.signal[r] || (need_param && !g.param[r])))
             return set_error(NSB_EINVAL, "peer group: missing mapping of rank %d", r);
     }
@@ -263,4 +384,35 @@ extern "C" int nsb_bucket_reduce_adam(const NsbPeers* peers, int64_t offset, int
     a.b1 = beta1; a.b2 = beta2; a.eps = eps; a.p_off = (long long)param_offset;
     k_exchange<true><<<blocks_for(per), X_THREADS, 0, (cudaStream_t)stream>>>(g, (long long)offset, n4, per, a);
     return check_launch("k_exchange_adam");
+}
+
+extern "C" int64_t nsb_exchange_touched_words(int64_t n) { return n <= 0 ? 0 : (n + 1023) / 1024 + NSB_MAX_PEERS; }
+
+extern "C" int nsb_bucket_allreduce_sparse(const NsbPeers* peers, int64_t offset, int64_t n, void* stream) {
+    PeersDev g;
+    if (int e = to_dev(peers, g, false)) return e;
+    if (n <= 0) return 0;
+    if ((offset & 31) || (n & 3)) return set_error(NSB_EINVAL, "sparse exchange: offset must be a multiple of 32 floats, n of 4");
+    for (int r = 0; r < g.world; ++r) {
+        if ((uintptr_t)g.bucket[r] & 127) return set_error(NSB_EINVAL, "sparse exchange: buffers must be 128-byte aligned");
+        if (!g.touched[r]) return set_error(NSB_EINVAL, "sparse exchange: missing touched-line words of rank %d", r);
+    }
+    const long long n4 = n / 4, n_units = (n4 + 255) / 256, per_u = (n_units + g.world - 1) / g.world;
+    // one warp per unit and pass; the scan covers world x per_u units
+    long long b = (per_u + X_WARPS - 1) / X_WARPS;
+    const int cap = blocks_for(1ll << 40);
+    const int nb = (int)(b < 1 ? 1 : (b > cap ? cap : b));
+    k_exchange_sparse<<<nb, X_THREADS, 0, (cudaStream_t)stream>>>(g, (long long)offset, n4, n_units, per_u);
+    return check_launch("k_exchange_sparse");
+}
+
+extern "C" int nsb_depth_max_peers(const NsbPeers* peers, const float* gt_depth, const uint8_t* keep, int64_t N,
+                                   float* out, void* stream) {
+    PeersDev g;
+    if (int e = to_dev(peers, g, false)) return e;
+    if (!gt_depth || !out) return set_error(NSB_EINVAL, "null argument");
+    for (int r = 0; r < g.world; ++r)
+        if (!g.scalar[r]) return set_error(NSB_EINVAL, "depth max: missing scalar slot of rank %d", r);
+    k_depth_max_peers<<<1, 1024, 0, (cudaStream_t)stream>>>(g, gt_depth, keep, (long long)N, out);
+    return check_launch("k_depth_max_peers");
 }

@@ -224,6 +224,10 @@ class MappingLoop:
     def _launch(self, stage):
         st = self.steps[stage]
         self._sample(st)
+        if st._sharded() and st.with_gt_depth and not st._peer_max:       # batch depth max over all ranks (NCCL)
+            import torch.distributed as dist
+            check(lib().nsb_depth_max(_ptr(st.gt_depth), _ptr(st.keep), st.N, _ptr(st.depth_max), _stream()), "depth_max")
+            dist.all_reduce(st.depth_max, op=dist.ReduceOp.MAX, group=self.group)
         st._launch()
         if st._sharded() and st.bucket.peers is None:
             st.bucket.all_reduce(self.group)                     # NCCL; the peer exchange ran inside st._launch

@@ -38,6 +38,7 @@ class PeerGroup:
         self._handles = {}
         words = int(lib().nsb_exchange_signal_words())
         self.signal = self._symmetric(words, torch.int32)
+        self.scalar = self._symmetric(64, torch.float32)
         self.error = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.multicast = bool(self._handles[self.signal.data_ptr()].multicast_ptr)
 
@@ -62,7 +63,11 @@ class PeerGroup:
                 return [p + off for p in h.buffer_ptrs], (h.multicast_ptr + off if h.multicast_ptr else 0)
         raise RuntimeError("tensor does not live in this group's symmetric memory")
 
-    def struct(self, bucket, param=None, use_multicast=None):
+    def alloc_touched(self, n):
+        """Symmetric scratch of the sparse exchange for a bucket of n floats (one bit per 128-byte line)."""
+        return self._symmetric(int(lib().nsb_exchange_touched_words(int(n))), torch.int32)
+
+    def struct(self, bucket, param=None, use_multicast=None, touched=None):
         """NsbPeers for a gradient bucket (and optionally the parameter buffer the fused optimiser
         writes), both flat tensors from ``alloc``.  use_multicast=None picks the faster path: with two
         ranks the in-switch reduction moves MORE bytes per link than plain peer loads / stores (both
@@ -82,6 +87,13 @@ class PeerGroup:
             for r in range(self.world):
                 s.param[r] = pp[r]
             s.param_multicast = pmc if use_multicast else 0
+        cp, _ = self._ptrs(self.scalar)
+        for r in range(self.world):
+            s.scalar[r] = cp[r]
+        if touched is not None:
+            tp, _ = self._ptrs(touched)
+            for r in range(self.world):
+                s.touched[r] = tp[r]
         s.error = self.error.data_ptr()
         return s
 

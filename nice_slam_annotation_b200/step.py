@@ -13,6 +13,7 @@ step.  The batch-global scalar ``max(gt_depth)`` (src/utils/Renderer.py:157,194)
 so the sharded render equals the unsharded one.
 """
 import ctypes as C
+import os
 
 import torch
 
@@ -44,7 +45,10 @@ class GradBucket:
         self.peers = peers
         if peers is not None:
             self.flat = peers.alloc(n)
-            self._px = peers.struct(self.flat)
+            # sparse exchange (only the voxel lines some rank touched travel); NSB_X_DENSE=1 keeps the dense one
+            self.sparse = os.environ.get("NSB_X_DENSE", "0") != "1"
+            self.touched = peers.alloc_touched(n) if self.sparse else None
+            self._px = peers.struct(self.flat, touched=self.touched)
         else:
             self.flat = torch.zeros(n, dtype=torch.float32, device=device)
         self.views = [self._view(p, o) for p, o in zip(self.leaves, self.offsets)]
@@ -70,7 +74,8 @@ class GradBucket:
     def all_reduce(self, group=None):
         """SUM over ranks (the mapping loss is a plain sum over rays, src/Mapper.py:605-612)."""
         if self.peers is not None:
-            check(lib().nsb_bucket_allreduce(C.byref(self._px), 0, self.flat.numel(), _stream()), "bucket_allreduce")
+            fn = lib().nsb_bucket_allreduce_sparse if self.sparse else lib().nsb_bucket_allreduce
+            check(fn(C.byref(self._px), 0, self.flat.numel(), _stream()), "bucket_allreduce")
             return
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
@@ -170,6 +175,7 @@ class FusedStep:
         self._call = self._build_call()
         self.graph = None
         self._side = None
+        self._peer_max = bool(self.with_gt_depth and self._sharded() and peers is not None and self.bucket is not None)
 
     # -- plumbing -----------------------------------------------------------------------
     def _sharded(self):
@@ -235,14 +241,17 @@ class FusedStep:
             self.keep[n:].zero_()
             self.rays_d[n:].fill_(1.0)           # harmless finite rays behind the mask
             self.gt_depth[n:].zero_()
+        self._peer_max = False
         if self.with_gt_depth and self._sharded():
-            if depth_max is None:
+            if depth_max is not None:
+                self.depth_max.copy_(depth_max.reshape(1), non_blocking=True)
+            elif self.bucket is not None and self.bucket.peers is not None:
+                self._peer_max = True        # nsb_depth_max_peers at the head of _launch (inside the graph)
+            else:
                 check(lib().nsb_depth_max(_ptr(self.gt_depth), _ptr(self.keep), self.N, _ptr(self.depth_max), _stream()),
                       "depth_max")
                 import torch.distributed as dist
                 dist.all_reduce(self.depth_max, op=dist.ReduceOp.MAX, group=self.group)
-            else:
-                self.depth_max.copy_(depth_max.reshape(1), non_blocking=True)
 
     def _launch(self, exchange=True):
         """memset(bucket) -> re-pack trainable decoders -> forward -> loss -> backward
@@ -262,6 +271,9 @@ class FusedStep:
         for k in self.dec_grad_kinds:
             self._pack(k)
         call = self._call
+        if self._peer_max:                       # batch depth max over all ranks, through peer memory
+            check(lib().nsb_depth_max_peers(C.byref(self.bucket._px), _ptr(self.gt_depth), _ptr(self.keep), self.N,
+                                            _ptr(self.depth_max), s), "depth_max_peers")
         check(lib().nsb_render_forward(C.byref(call), s), "render_forward")
         if joined is not None:
             torch.cuda.current_stream().wait_stream(joined)

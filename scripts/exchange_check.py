@@ -88,6 +88,36 @@ def main():
         out["checks"]["allreduce_" + name] = {"max_rel_err": worst}
     pg.check_error()
 
+    # ---- sparse all-reduce (touched 128-byte lines only) vs NCCL --------------------------------
+    n_sp = 32 * 40013 + 4 * 5                            # ragged: partial last line, partial last unit
+    sp = pg.alloc(n_sp)
+    tw = pg.alloc_touched(n_sp)
+    for name, mc in paths:
+        px = pg.struct(sp, use_multicast=mc, touched=tw)
+        for frac in (0.0, 0.05, 0.4, 1.0):
+            g = torch.Generator(device=dev).manual_seed(31 * rank + int(frac * 100))
+            lines = (torch.rand((n_sp + 31) // 32, device=dev, generator=g) < frac)
+            x = torch.randn(n_sp, device=dev, generator=g) * lines.repeat_interleave(32)[:n_sp]
+            ref = x.clone()
+            dist.all_reduce(ref)
+            for rep in range(2):                          # twice: the scratch words are reused
+                sp.copy_(x)
+                torch.cuda.synchronize(); dist.barrier()
+                check(L.nsb_bucket_allreduce_sparse(C.byref(px), 0, n_sp, s()), "allreduce_sparse")
+                torch.cuda.synchronize(); dist.barrier()
+                err = (sp - ref).abs().max().item() / max(ref.abs().max().item(), 1e-30)
+                assert err < 1e-6, (name, frac, rep, err)
+        # a sub-range at a line-aligned offset leaves the rest alone
+        sp.fill_(float(rank + 1))
+        torch.cuda.synchronize(); dist.barrier()
+        check(L.nsb_bucket_allreduce_sparse(C.byref(px), 64, 4 * 2999, s()), "allreduce_sparse")
+        torch.cuda.synchronize(); dist.barrier()
+        tot = float(sum(range(1, world + 1)))
+        assert bool((sp[64:64 + 4 * 2999] == tot).all()) and bool((sp[:64] == rank + 1).all()) \
+            and bool((sp[64 + 4 * 2999:] == rank + 1).all()), name
+        out["checks"]["allreduce_sparse_" + name] = {"max_rel_err": err}
+    pg.check_error()
+
     # ---- fused reduce + Adam vs all-reduce + nsb_adam -----------------------------------------
     n = 32 * 4099                                        # 4099 voxel lines: ragged over the ranks
     grad, param = pg.alloc(n), pg.alloc(n)
@@ -164,6 +194,21 @@ def main():
         t[f"reduce_adam_{name}_ms"] = ev_time(lambda: check(L.nsb_bucket_reduce_adam(
             C.byref(px), 0, nb, 0, m_own.data_ptr(), v_own.data_ptr(), None, st.data_ptr(), lr.data_ptr(),
             0.9, 0.999, 1e-8, s())))
+    # sparse exchange at the touched fractions of a mapping step (scripts/bucket_sparsity.py: 16 % of the
+    # lines per 1000 rays; the union over ranks grows towards 39 % at 8000 rays)
+    twb = pg.alloc_touched(nb)
+    for frac in (0.16, 0.39, 1.0):
+        g = torch.Generator(device=dev).manual_seed(7 + rank)
+        keep_l = (torch.rand(nb // 32, device=dev, generator=g) < (frac / world if frac < 1 else 1.0) * 1.0)
+        src = torch.randn(nb, device=dev, generator=g) * keep_l.repeat_interleave(32)
+        for name, mc in paths:
+            px = pg.struct(big, use_multicast=mc, touched=twb)
+
+            def run():
+                big.copy_(src)
+                check(L.nsb_bucket_allreduce_sparse(C.byref(px), 0, nb, s()))
+            t_copy = ev_time(lambda: big.copy_(src))
+            t[f"sparse_{name}_union{int(frac * 100)}pct_ms"] = ev_time(run) - t_copy
     # what the fused kernel replaces: all-reduce, then Adam over the whole bucket on every rank
     m_f, v_f, p_f = torch.zeros(nb, device=dev), torch.zeros(nb, device=dev), torch.zeros(nb, device=dev)
     st = torch.zeros(2, dtype=torch.int32, device=dev)
