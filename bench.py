@@ -203,6 +203,10 @@ def run_ours(args):
         step.load(*hb)                                              # pinned host -> static device buffers
         return step.run().item()
 
+    def step_engine_packed(pb):
+        step.load_packed(pb)                                        # ONE pinned [n,10] array -> one H2D copy + one kernel
+        return step.run().item()
+
     def timed(fn, items, steps, warmup, after_warmup=None):
         for i in range(warmup):
             fn(items[i % len(items)])
@@ -267,7 +271,13 @@ def run_ours(args):
             peers.check_error()
             step = step_peer
         ms_e2e = timed(step_e2e, host_batches, args.steps, args.warmup)
-        ms_eng = timed(step_engine_host, host_batches, args.steps, args.warmup)
+        ms_eng4 = timed(step_engine_host, host_batches, args.steps, args.warmup)
+        packed_ok = world == 1 or step._peer_max
+        if packed_ok:
+            packed_batches = [FusedStep.pack_batch(*b) for b in batches]
+            ms_eng = timed(step_engine_packed, packed_batches, args.steps, args.warmup)
+        else:
+            ms_eng = ms_eng4
 
     peaks, peak_src = measured_peaks()
     traffic = args.traffic
@@ -300,9 +310,11 @@ def run_ours(args):
                    "exchange_max_rel_diff_vs_nccl": x_err},
         "e2e": {"value": world * n_rays / (ms_eng * 1e-3), "unit": "rays/s", "ms_per_step": ms_eng,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
-                "api": "FusedStep.load(ray batch in pinned host memory) + run() + loss.item(): the engine call "
-                       "Mapper.optimize_map makes per iteration (3 C-ABI calls: nsb_render_forward, nsb_mapping_loss, "
-                       "nsb_render_backward)"},
+                "api": ("FusedStep.load_packed(ray batch as one pinned [n,10] host array: 1 H2D copy + nsb_load_batch_packed)"
+                        if packed_ok else "FusedStep.load(4 pinned host tensors)")
+                       + " + run() + loss.item(): the engine call Mapper.optimize_map makes per iteration (2 C-ABI calls: "
+                         "nsb_render_forward, nsb_render_backward with the fused mapping loss), loss read back every step",
+                "ms_per_step_from_4_host_tensors": ms_eng4},
         "e2e_autograd": {"value": world * n_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e,
                          "api": "Renderer.render_batch_ray + mapping loss + loss.backward() (torch autograd around the "
                                 "same kernels), ray batch in pinned host memory"},

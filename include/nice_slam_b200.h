@@ -286,6 +286,18 @@ typedef struct NsbRenderCall {
     double* loss; /* [1] */
 } NsbRenderCall;
 
+/* One ray batch (contiguous [n,3] / [n] device tensors, n <= N) into the fixed-shape input buffers of a
+ * render call that is replayed as a CUDA graph: rays n..N-1 are masked off (keep = 0).  keep may be NULL
+ * (all n rays kept; it may alias dst_keep).  rays_o == NULL: the n live entries are already in place (a
+ * caller that copied them from host memory) and only keep and the tail are written.  One launch instead
+ * of a copy per tensor. */
+int nsb_load_batch(const float* rays_o, const float* rays_d, const float* gt_depth, const float* gt_color,
+                   const uint8_t* keep, int64_t n, int64_t N, float* dst_rays_o, float* dst_rays_d,
+                   float* dst_gt_depth, float* dst_gt_color, uint8_t* dst_keep, void* stream);
+/* The same from ONE packed [n,10] fp32 array (rays_o 3, rays_d 3, gt_depth 1, gt_color 3 per ray). */
+int nsb_load_batch_packed(const float* packed, const uint8_t* keep, int64_t n, int64_t N, float* dst_rays_o,
+                          float* dst_rays_d, float* dst_gt_depth, float* dst_gt_color, uint8_t* dst_keep,
+                          void* stream);
 int64_t nsb_render_workspace_bytes(int64_t N, int S);
 int nsb_render_forward(const NsbRenderCall* call, void* stream);
 int nsb_render_backward(const NsbRenderCall* call, void* stream);

@@ -367,6 +367,46 @@ extern "C" int nsb_all_rays(int H, int W, float fx, float fy, float cx, float cy
 }
 
 namespace nsb {
+// one batch into the fixed-shape input buffers of an engine step: n <= N rays are copied, the rest is
+// masked off (keep = 0) behind harmless finite rays
+__global__ void k_load_batch(const float* __restrict__ ro, const float* __restrict__ rd, const float* __restrict__ gd,
+                             const float* __restrict__ gc, const uint8_t* __restrict__ keep, long long n, long long N,
+                             float* __restrict__ d_ro, float* __restrict__ d_rd, float* __restrict__ d_gd,
+                             float* __restrict__ d_gc, uint8_t* __restrict__ d_keep) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const bool live = i < n;
+    if (!live || ro) {          // ro == NULL: the live entries are already in place (copied by the caller)
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            d_ro[3 * i + a] = live ? ro[3 * i + a] : 0.f;
+            d_rd[3 * i + a] = live ? rd[3 * i + a] : 1.f;
+            d_gc[3 * i + a] = live ? gc[3 * i + a] : 0.f;
+        }
+        d_gd[i] = live ? gd[i] : 0.f;
+    }
+    d_keep[i] = live ? (keep ? keep[i] : (uint8_t)1) : (uint8_t)0;
+}
+
+// the same from one packed [n,10] array (rays_o 3, rays_d 3, gt_depth 1, gt_color 3 per ray): what a host
+// producer hands over with a single H2D copy
+__global__ void k_load_batch_packed(const float* __restrict__ src, const uint8_t* __restrict__ keep, long long n,
+                                    long long N, float* __restrict__ d_ro, float* __restrict__ d_rd,
+                                    float* __restrict__ d_gd, float* __restrict__ d_gc, uint8_t* __restrict__ d_keep) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const bool live = i < n;
+    const float* r = src + 10 * i;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        d_ro[3 * i + a] = live ? r[a] : 0.f;
+        d_rd[3 * i + a] = live ? r[3 + a] : 1.f;
+        d_gc[3 * i + a] = live ? r[7 + a] : 0.f;
+    }
+    d_gd[i] = live ? r[6] : 0.f;
+    d_keep[i] = live ? (keep ? keep[i] : (uint8_t)1) : (uint8_t)0;
+}
+
 int launch_sample_z(const PointsDev& q, const float* gt_depth, const BoundDev& bound, int Ns, int Nf, int lindisp,
                     const float* t_uniform, const double* t_surface, const float* u, const float* depth_max,
                     double* z_out, unsigned* zero_word, void* stream) {
@@ -430,4 +470,29 @@ extern "C" int nsb_sample_pdf(const double* bins, const float* weights, int64_t 
     k_sample_pdf<<<blocks_for(N, 64), 64, 0, (cudaStream_t)stream>>>(bins, weights, N, M, N_samples, u,
                                                                     u_row_stride, samples);
     return check_launch("k_sample_pdf");
+}
+
+extern "C" int nsb_load_batch(const float* rays_o, const float* rays_d, const float* gt_depth, const float* gt_color,
+                              const uint8_t* keep, int64_t n, int64_t N, float* dst_rays_o, float* dst_rays_d,
+                              float* dst_gt_depth, float* dst_gt_color, uint8_t* dst_keep, void* stream) {
+    if (!dst_rays_o || !dst_rays_d || !dst_gt_depth || !dst_gt_color || !dst_keep) return set_error(NSB_EINVAL, "null argument");
+    if (n < 0 || n > N) return set_error(NSB_EINVAL, "batch of %lld rays exceeds the capacity %lld", (long long)n, (long long)N);
+    if (rays_o && (!rays_d || !gt_depth || !gt_color)) return set_error(NSB_EINVAL, "null argument");
+    if (N <= 0) return 0;
+    k_load_batch<<<blocks_for(N, 256), 256, 0, (cudaStream_t)stream>>>(rays_o, rays_d, gt_depth, gt_color, keep, n, N,
+                                                                      dst_rays_o, dst_rays_d, dst_gt_depth, dst_gt_color,
+                                                                      dst_keep);
+    return check_launch("k_load_batch");
+}
+
+extern "C" int nsb_load_batch_packed(const float* packed, const uint8_t* keep, int64_t n, int64_t N, float* dst_rays_o,
+                                     float* dst_rays_d, float* dst_gt_depth, float* dst_gt_color, uint8_t* dst_keep,
+                                     void* stream) {
+    if (!dst_rays_o || !dst_rays_d || !dst_gt_depth || !dst_gt_color || !dst_keep) return set_error(NSB_EINVAL, "null argument");
+    if (n < 0 || n > N) return set_error(NSB_EINVAL, "batch of %lld rays exceeds the capacity %lld", (long long)n, (long long)N);
+    if (n > 0 && !packed) return set_error(NSB_EINVAL, "null argument");
+    if (N <= 0) return 0;
+    k_load_batch_packed<<<blocks_for(N, 256), 256, 0, (cudaStream_t)stream>>>(packed, keep, n, N, dst_rays_o, dst_rays_d,
+                                                                             dst_gt_depth, dst_gt_color, dst_keep);
+    return check_launch("k_load_batch_packed");
 }

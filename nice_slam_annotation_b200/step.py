@@ -175,6 +175,7 @@ class FusedStep:
         self._call = self._build_call()
         self.graph = None
         self._side = None
+        self._packed_dev = None
         self._peer_max = bool(self.with_gt_depth and self._sharded() and peers is not None and self.bucket is not None)
 
     # -- plumbing -----------------------------------------------------------------------
@@ -229,18 +230,22 @@ class FusedStep:
         n = rays_o.shape[0]
         if n > self.N:
             raise ValueError(f"batch of {n} rays exceeds the step's capacity {self.N}")
-        self.rays_o[:n].copy_(rays_o, non_blocking=True)
-        self.rays_d[:n].copy_(rays_d, non_blocking=True)
-        self.gt_depth[:n].copy_(gt_depth.reshape(-1), non_blocking=True)
-        self.gt_color[:n].copy_(gt_color.reshape(-1, 3), non_blocking=True)
-        if keep is None:
-            self.keep[:n].fill_(1)
+        if rays_o.is_cuda:
+            src = [rays_o.float().contiguous(), rays_d.float().contiguous(), gt_depth.reshape(-1).float().contiguous(),
+                   gt_color.reshape(-1, 3).float().contiguous(), None if keep is None else keep.to(torch.uint8).contiguous()]
         else:
-            self.keep[:n].copy_(keep, non_blocking=True)
-        if n < self.N:
-            self.keep[n:].zero_()
-            self.rays_d[n:].fill_(1.0)           # harmless finite rays behind the mask
-            self.gt_depth[n:].zero_()
+            # host batch: asynchronous H2D copies straight into the static buffers, then ONE kernel that
+            # masks the tail off (no source pointers: the live entries are already in place)
+            self.rays_o[:n].copy_(rays_o, non_blocking=True)
+            self.rays_d[:n].copy_(rays_d, non_blocking=True)
+            self.gt_depth[:n].copy_(gt_depth.reshape(-1), non_blocking=True)
+            self.gt_color[:n].copy_(gt_color.reshape(-1, 3), non_blocking=True)
+            if keep is not None:
+                self.keep[:n].copy_(keep, non_blocking=True)
+            src = [None, None, None, None, None if keep is None else self.keep]
+        check(lib().nsb_load_batch(_ptr(src[0]), _ptr(src[1]), _ptr(src[2]), _ptr(src[3]), _ptr(src[4]), n, self.N,
+                                   _ptr(self.rays_o), _ptr(self.rays_d), _ptr(self.gt_depth), _ptr(self.gt_color),
+                                   _ptr(self.keep), _stream()), "load_batch")
         self._peer_max = False
         if self.with_gt_depth and self._sharded():
             if depth_max is not None:
@@ -252,6 +257,33 @@ class FusedStep:
                       "depth_max")
                 import torch.distributed as dist
                 dist.all_reduce(self.depth_max, op=dist.ReduceOp.MAX, group=self.group)
+
+    @staticmethod
+    def pack_batch(rays_o, rays_d, gt_depth, gt_color, pin=True):
+        """One [n,10] fp32 host array (rays_o 3, rays_d 3, gt_depth 1, gt_color 3 per ray) for
+        ``load_packed``: a producer on the host hands a batch over with a single H2D copy."""
+        p = torch.cat([rays_o.float().reshape(-1, 3).cpu(), rays_d.float().reshape(-1, 3).cpu(),
+                       gt_depth.float().reshape(-1, 1).cpu(), gt_color.float().reshape(-1, 3).cpu()], 1).contiguous()
+        return p.pin_memory() if pin and torch.cuda.is_available() else p
+
+    def load_packed(self, packed, keep=None):
+        """``load`` from one packed [n,10] tensor (host, ideally pinned, or device): one copy + one kernel."""
+        n = packed.shape[0]
+        if n > self.N or packed.shape[1] != 10 or packed.dtype != torch.float32:
+            raise ValueError("load_packed wants a float32 [n<=N, 10] tensor")
+        if self._sharded() and not self._peer_max:
+            raise NotImplementedError("load_packed on a sharded step needs the peer-memory depth max")
+        if packed.is_cuda:
+            dev = packed.contiguous()
+        else:
+            if self._packed_dev is None:
+                self._packed_dev = torch.empty(self.N, 10, device=self.dev)
+            dev = self._packed_dev[:n]
+            dev.copy_(packed, non_blocking=True)
+        kp = None if keep is None else keep.to(self.dev, torch.uint8, non_blocking=True).contiguous()
+        check(lib().nsb_load_batch_packed(_ptr(dev), _ptr(kp), n, self.N, _ptr(self.rays_o), _ptr(self.rays_d),
+                                          _ptr(self.gt_depth), _ptr(self.gt_color), _ptr(self.keep), _stream()),
+              "load_batch_packed")
 
     def _launch(self, exchange=True):
         """memset(bucket) -> re-pack trainable decoders -> forward -> loss -> backward
