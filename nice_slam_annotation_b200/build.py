@@ -22,6 +22,10 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "--extended-lambda"]
 
 
+# extra flags for one-off instrumented builds, e.g. NSB_NVCC_EXTRA="-DNSB_TC_PROFILE" (in-kernel phase timers)
+NVCC_FLAGS += os.environ.get("NSB_NVCC_EXTRA", "").split()
+
+
 def _nvcc():
     exe = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(exe):

@@ -1153,6 +1153,14 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
         for (int i = 1; i < n; ++i) if (frac[i] > frac[best]) best = i;
         share_of[best]++; frac[best] = -1.f; used++;
     }
+    // tuning hook: NSB_BWD_SHARES="a,b,c" / NSB_FWD_SHARES forces the CTA split of a 3-decoder stage
+    if (n == 3)
+        if (const char* e = getenv(bwd ? "NSB_BWD_SHARES" : "NSB_FWD_SHARES")) {
+            int a = 0, b = 0, c = 0;
+            if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a > 0 && b > 0 && c > 0 && a + b + c <= g_num_sms) {
+                share_of[0] = a; share_of[1] = b; share_of[2] = c;
+            }
+        }
     int begin = 0;
     for (int i = 0; i < n; ++i) {
         DecTask& T = sp.task[i];

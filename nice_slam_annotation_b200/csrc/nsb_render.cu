@@ -29,7 +29,7 @@ struct Ws {
 
 int sample_z_impl(const NsbPoints* rays, const float* gt_depth, const double* bound6_host, int N_samples,
                   int N_surface, int lindisp, const float* t_uniform, const double* t_surface, const float* u,
-                  const float* depth_max, double* z_out, unsigned* zero_word, void* stream);
+                  const float* depth_max, double* z_out, unsigned* zero_word, const uint8_t* keep, void* stream);
 
 static Ws carve_ws(void* base, int64_t N, int S) {
     Carve c(base);
@@ -207,7 +207,7 @@ extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
     Ws w = carve_ws(r->workspace, r->N, S);
     const double* b6 = &r->scene.bound[0][0];
     const float* dmax = r->depth_max;
-    if (r->gt_depth && !dmax) {
+    if (r->gt_depth && !dmax && r->N > 4096) {      // small batches: k_sample_z reduces the max in every block
         if (int rc = nsb_depth_max(r->gt_depth, r->keep, r->N, w.depth_max, stream)) return rc;
         dmax = w.depth_max;
     }
@@ -215,7 +215,7 @@ extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
     const bool fused_loss = r->loss != nullptr;
     if (fused_loss && (!r->gt_depth || !r->gt_color)) return set_error(NSB_EINVAL, "fused mapping loss needs gt_depth and gt_color");
     if (int rc = sample_z_impl(&rays, r->gt_depth, b6, r->N_samples, Nf, r->lindisp, r->t_uniform, r->t_surface,
-                               r->u, dmax, w.z, fused_loss ? w.ticket : nullptr, stream)) return rc;
+                               r->u, dmax, w.z, fused_loss ? w.ticket : nullptr, r->keep, stream)) return rc;
     NsbPoints pts = ray_pts(r, w.z, S);
     pts.relu_masks = w.relu;
     float *o0, *o1, *rgb;

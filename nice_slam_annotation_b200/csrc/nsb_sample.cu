@@ -7,6 +7,7 @@
 
 namespace nsb {
 
+constexpr int SAMPLE_Z_INLINE_MAX = 4096;   // up to here k_sample_z reduces the batch depth max in every block
 constexpr int MAX_LIST = 128;   // per-ray limit of N_samples, N_surface, N_importance each
 
 struct CamDev {
@@ -177,9 +178,30 @@ __global__ void __launch_bounds__(256) k_sample_z(PointsDev q, const float* __re
                            int Ns, int Nf, int lindisp, const float* __restrict__ t_uniform,
                            const double* __restrict__ t_surface, const float* __restrict__ u,
                            const float* __restrict__ depth_max, double* __restrict__ z_out, int rays_per_block,
-                           unsigned* __restrict__ zero_word) {
+                           unsigned* __restrict__ zero_word, const uint8_t* __restrict__ keep) {
     extern __shared__ double sh_z[];
+    __shared__ float s_part[8];
+    __shared__ float s_dmax;
     const int S = Ns + Nf;
+    if (gt_depth && !depth_max) {
+        // small batches: every block reduces the batch depth max itself (k_depth_max's rule: kept rays,
+        // NaN propagates) instead of waiting for a separate launch
+        float m = -INFINITY;
+        for (long long i = threadIdx.x; i < q.N; i += blockDim.x)
+            if (!keep || keep[i]) { const float v = gt_depth[i]; m = (v > m || v != v) ? v : m; }
+        for (int sft = 16; sft > 0; sft >>= 1) { const float o = __shfl_xor_sync(FULL, m, sft); m = (o > m || o != o) ? o : m; }
+        if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = m;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { const float o = s_part[w]; m = (o > m || o != o) ? o : m; }
+            s_dmax = m;
+        }
+        __syncthreads();
+    } else if (threadIdx.x == 0) {
+        s_dmax = depth_max ? depth_max[0] : 0.f;
+    }
+    if (!(gt_depth && !depth_max)) __syncthreads();
+    const float dmax = s_dmax;
     const int local = threadIdx.x / S, k = threadIdx.x - local * S;
     const long long r = blockIdx.x * (long long)rays_per_block + local;
     if (zero_word && blockIdx.x == 0 && threadIdx.x == 0) *zero_word = 0u;
@@ -195,7 +217,7 @@ __global__ void __launch_bounds__(256) k_sample_z(PointsDev q, const float* __re
             double far;
             if (gt_depth) {
                 near = __fmul_rn(gt_depth[r], 0.01f);
-                const double cap = (double)__fmul_rn(depth_max[0], 1.2f);     // max(gt_depth * 1.2)
+                const double cap = (double)__fmul_rn(dmax, 1.2f);             // max(gt_depth * 1.2)
                 far = tmin(tmax(far_bb, 0.0), cap);                            // torch.clamp(far_bb, 0, cap)
                 if (far_bb != far_bb) far = far_bb;
             } else {
@@ -223,7 +245,7 @@ __global__ void __launch_bounds__(256) k_sample_z(PointsDev q, const float* __re
                 const double a = (double)__fmul_rn(0.95f, g), b = (double)__fmul_rn(1.05f, g);
                 v = __dadd_rn(__dmul_rn(a, __dsub_rn(1.0, ts)), __dmul_rn(b, ts));
             } else {             // no sensor depth: 0.001 .. max depth of the batch (Renderer.py:191-200)
-                v = __dadd_rn(__dmul_rn(0.001, __dsub_rn(1.0, ts)), __dmul_rn((double)depth_max[0], ts));
+                v = __dadd_rn(__dmul_rn(0.001, __dsub_rn(1.0, ts)), __dmul_rn((double)dmax, ts));
             }
         }
         sh_z[threadIdx.x] = v;
@@ -409,11 +431,12 @@ __global__ void k_load_batch_packed(const float* __restrict__ src, const uint8_t
 
 int launch_sample_z(const PointsDev& q, const float* gt_depth, const BoundDev& bound, int Ns, int Nf, int lindisp,
                     const float* t_uniform, const double* t_surface, const float* u, const float* depth_max,
-                    double* z_out, unsigned* zero_word, void* stream) {
+                    double* z_out, unsigned* zero_word, const uint8_t* keep, void* stream) {
     const int S = Ns + Nf;
     const int rpb = S >= 256 ? 1 : 256 / S;
-    k_sample_z<<<blocks_for(q.N, rpb), rpb * S, rpb * S * sizeof(double), (cudaStream_t)stream>>>(
-        q, gt_depth, bound, Ns, Nf, lindisp, t_uniform, t_surface, u, depth_max, z_out, rpb, zero_word);
+    const int threads = (rpb * S + 31) / 32 * 32;             // whole warps (the in-block depth max shuffles)
+    k_sample_z<<<blocks_for(q.N, rpb), threads, threads * sizeof(double), (cudaStream_t)stream>>>(
+        q, gt_depth, bound, Ns, Nf, lindisp, t_uniform, t_surface, u, depth_max, z_out, rpb, zero_word, keep);
     return check_launch("k_sample_z");
 }
 }  // namespace nsb
@@ -427,18 +450,19 @@ extern "C" int nsb_depth_max(const float* gt_depth, const uint8_t* keep, int64_t
 namespace nsb {
 int sample_z_impl(const NsbPoints* rays, const float* gt_depth, const double* bound6_host, int N_samples,
                   int N_surface, int lindisp, const float* t_uniform, const double* t_surface, const float* u,
-                  const float* depth_max, double* z_out, unsigned* zero_word, void* stream) {
+                  const float* depth_max, double* z_out, unsigned* zero_word, const uint8_t* keep, void* stream) {
     if (!rays || !rays->rays_o || !rays->rays_d || !bound6_host || !t_uniform || !z_out)
         return set_error(NSB_EINVAL, "null argument");
     if (N_samples < 1 || N_samples > MAX_LIST || N_surface < 0 || N_surface > MAX_LIST)
         return set_error(NSB_EINVAL, "N_samples / N_surface out of range (1..%d)", MAX_LIST);
     if (!gt_depth) N_surface = 0;
-    if (gt_depth && !depth_max) return set_error(NSB_EINVAL, "depth_max is required with gt_depth");
+    if (gt_depth && !depth_max && rays->N > SAMPLE_Z_INLINE_MAX)
+        return set_error(NSB_EINVAL, "depth_max is required with gt_depth (batches above %d rays)", SAMPLE_Z_INLINE_MAX);
     if (N_surface > 0 && !t_surface) return set_error(NSB_EINVAL, "t_surface is NULL");
     if (rays->N <= 0) return 0;
     PointsDev q = to_dev(*rays);
     return launch_sample_z(q, gt_depth, to_bound(bound6_host), N_samples, N_surface, lindisp, t_uniform, t_surface,
-                           u, depth_max, z_out, zero_word, stream);
+                           u, depth_max, z_out, zero_word, keep, stream);
 }
 }  // namespace nsb
 
@@ -446,8 +470,9 @@ extern "C" int nsb_sample_z(const NsbPoints* rays, const float* gt_depth, const 
                             int N_samples, int N_surface, int lindisp, const float* t_uniform,
                             const double* t_surface, const float* u, const float* depth_max,
                             double* z_out, void* stream) {
+    if (gt_depth && !depth_max) return set_error(NSB_EINVAL, "depth_max is required with gt_depth");
     return sample_z_impl(rays, gt_depth, bound6_host, N_samples, N_surface, lindisp, t_uniform, t_surface, u,
-                         depth_max, z_out, nullptr, stream);
+                         depth_max, z_out, nullptr, nullptr, stream);
 }
 
 extern "C" int nsb_importance_z(const double* z, const float* weights, int64_t N, int S, int N_imp,
