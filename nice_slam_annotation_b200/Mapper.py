@@ -69,6 +69,8 @@ class Mapper(object):
         # whenever its preconditions hold; False: the autograd path below (same values)
         self.fused_loop = True
         self._loops = {}
+        # ray-sharded mapping over the GPUs of one box: see enable_sharding
+        self.shard_group, self.shard_peers, self.shard_world, self.shard_rank = None, None, 1, 0
         self.H, self.W, self.fx, self.fy, self.cx, self.cy = slam.H, slam.W, slam.fx, slam.fy, slam.cx, slam.cy
 
     # ---- callers of the hot path, once per mapped frame (kernels: csrc/nsb_frustum.cu) -------
@@ -143,7 +145,27 @@ class Mapper(object):
         selected = [dic['id'] for dic in list_keyframe if dic['percent_inside'] > 0.00]
         return list(np.random.permutation(np.array(selected))[:k])
 
-    # ---- the mapping optimisation ----------------------------------------------------------
+    # ---- ray-sharded mapping ----------------------------------------------------------------
+    def enable_sharding(self, group=None, peer_memory=True):
+        """Shard the rays of every optimize_map iteration over the ranks of ``group`` (default: the
+        world group; one process per GPU, all ranks call optimize_map with the same arguments and hold
+        identical grids / decoders).  Every rank samples mapping_pixels / world pixels per iteration,
+        the gradients are summed over ranks (peer-memory exchange kernels inside the iteration's CUDA
+        graph when ``peer_memory``, else one NCCL all-reduce), and every rank applies the identical
+        optimiser step, so the replicas stay bit-identical.  Give every rank its own RNG stream
+        (``torch.cuda.manual_seed(seed + rank)``) so that the ranks draw different pixels."""
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError("enable_sharding needs an initialised torch.distributed process group")
+        self.shard_group = group
+        self.shard_world, self.shard_rank = dist.get_world_size(group), dist.get_rank(group)
+        self.shard_peers = None
+        if peer_memory and self.shard_world > 1:
+            from .peers import PeerGroup
+            self.shard_peers = PeerGroup(group, device=torch.device(self.device))
+        self._loops = {}
+
+        # ---- the mapping optimisation ----------------------------------------------------------
     def optimize_map(self, num_joint_iters, lr_factor, idx, cur_gt_color, cur_gt_depth, gt_cur_c2w,
                      keyframe_dict, keyframe_list, cur_c2w):
         """Mapping iterations: sample pixels from the selected keyframes, optimise the scene
@@ -163,6 +185,13 @@ class Mapper(object):
             else:
                 optimize_frame = self.keyframe_selection_overlap(
                     cur_gt_color, cur_gt_depth, cur_c2w, keyframe_dict[:-1], num)
+        if self.shard_world > 1:
+            # the selection draws random numbers: every rank optimises the frames rank 0 picked
+            import torch.distributed as dist
+            box = [[int(f) for f in optimize_frame]]
+            dist.broadcast_object_list(box, src=dist.get_global_rank(self.shard_group, 0) if self.shard_group is not None else 0,
+                                       group=self.shard_group)
+            optimize_frame = list(box[0])
         oldest_frame = None
         if len(keyframe_list) > 0:
             optimize_frame = optimize_frame + [len(keyframe_list) - 1]
@@ -182,6 +211,9 @@ class Mapper(object):
             return self._optimize_map_fused(num_joint_iters, lr_factor, optimize_frame, oldest_frame, pixs_per_image,
                                             cur_gt_color, cur_gt_depth, keyframe_dict, cur_c2w)
 
+        if self.shard_world > 1:
+            raise NotImplementedError("ray-sharded mapping runs on the fused loop only (NICE decoders, occupancy, "
+                                      "no jitter / importance sampling, fused_loop = True)")
         decoders_para_list = []
         grid_para = {'grid_coarse': [], 'grid_middle': [], 'grid_fine': [], 'grid_color': []}
         if self.nice:
@@ -390,11 +422,15 @@ class Mapper(object):
                            get_tensor_from_camera(c2w).to(device) if ba else c2w.to(device).float()))
         masked = bool(self.frustum_feature_selection)
         f64 = False      # the reference casts the sampled colours to fp32 (Mapper.py:575); casting the frame first is the same
-        key = (len(frames), pixs_per_image, tuple(ba_slots), masked, f64)
+        if self.shard_world > 1:                              # every rank renders its share of the pixels
+            pixs_per_image = max(1, pixs_per_image // self.shard_world)
+        key = (len(frames), pixs_per_image, tuple(ba_slots), masked, f64, self.shard_world)
         loop = self._loops.get(key)
         if loop is None or not loop.valid_for(self):
             self._loops = {k: v for k, v in self._loops.items() if v.valid_for(self)}
-            loop = self._loops[key] = MappingLoop(self, len(frames), pixs_per_image, ba_slots, masked, f64)
+            loop = self._loops[key] = MappingLoop(self, len(frames), pixs_per_image, ba_slots, masked, f64,
+                                                  group=self.shard_group if self.shard_world > 1 else None,
+                                                  peers=self.shard_peers, sharded=self.shard_world > 1)
         masks = None
         if masked:
             masks = {}

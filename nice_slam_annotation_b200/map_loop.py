@@ -88,7 +88,8 @@ class MappingLoop:
     masked : frustum_feature_selection (a voxel mask per grid is loaded per call)
     """
 
-    def __init__(self, mapper, n_frames, pixs, ba_slots=None, masked=True, color_f64=False, group=None, peers=None):
+    def __init__(self, mapper, n_frames, pixs, ba_slots=None, masked=True, color_f64=False, group=None, peers=None,
+                 sharded=None):
         mp = self.mp = mapper
         self.K, self.pix = int(n_frames), int(pixs)
         self.N = self.K * self.pix
@@ -102,7 +103,14 @@ class MappingLoop:
         self.color = torch.zeros(self.K, H, W, 3, dtype=torch.float64 if color_f64 else torch.float32, device=dev)
         self.c2w = torch.zeros(self.K, 12, device=dev)
         self.cam = torch.zeros(self.K, 7, device=dev)
-        self.d_cam = torch.zeros(self.K, 7, device=dev)
+        # camera gradients: rows of 8 floats; in symmetric memory when ranks exchange through peer memory
+        self.peers = peers
+        if peers is not None:
+            self._d_cam_flat = peers.alloc(self.K * 8)
+            self._d_cam_px = peers.struct(self._d_cam_flat, use_multicast=False)
+        else:
+            self._d_cam_flat = torch.zeros(self.K * 8, device=dev)
+        self.d_cam = self._d_cam_flat.view(self.K, 8)[:, :7]
         self.cam_m = torch.zeros(self.K, 7, device=dev)
         self.cam_v = torch.zeros(self.K, 7, device=dev)
         self.cam_t = torch.zeros(self.K, 1, dtype=torch.int32, device=dev)
@@ -143,7 +151,7 @@ class MappingLoop:
                 mp.renderer, mp.decoders, mp.c, st, self.N, loss="mapping", w_color=mp.w_color_loss,
                 use_color=(st == "color"), grid_grads=tuple(GRID_KEYS[k] for k in kinds),
                 decoder_grads=tuple(n for n in self.train_dec if self.dec_kind[n] in kinds),
-                ray_grads=any(self.ba), with_gt_depth=not mp.coarse_mapper, group=group, peers=peers)
+                ray_grads=any(self.ba), with_gt_depth=not mp.coarse_mapper, group=group, peers=peers, sharded=sharded)
 
     # -- per call ---------------------------------------------------------------------------
     def valid_for(self, mapper):
@@ -217,6 +225,17 @@ class MappingLoop:
             check(L.nsb_pose_grad(_ptr(st.g_rays_o[a:b]), _ptr(st.g_rays_d[a:b]), _ptr(self.indices[a:b]),
                                   _ptr(st.keep[a:b]), self.pix, 0, 0, mp.W, fx, fy, cx, cy, _ptr(self.cam[i]),
                                   _ptr(self.d_cam[i]), s), "pose_grad")
+        if any(self.ba) and st._sharded():
+            # the pose gradient is linear in the ray gradients: partial d(camera) of the ranks add
+            if self.peers is not None:
+                import ctypes as C
+                check(L.nsb_bucket_allreduce(C.byref(self._d_cam_px), 0, self.K * 8, s), "cam_allreduce")
+            else:
+                import torch.distributed as dist
+                dist.all_reduce(self._d_cam_flat, group=self.group)
+        for i in range(self.K):
+            if not self.ba[i]:
+                continue
             check(L.nsb_cam_adam(_ptr(self.cam[i]), _ptr(self.d_cam[i]), _ptr(self.cam_m[i]), _ptr(self.cam_v[i]),
                                  _ptr(self.cam_t[i]), lr_cam, lr_cam, BETAS[0], BETAS[1], EPS, None, None, None, s),
                   "cam_adam")

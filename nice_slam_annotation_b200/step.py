@@ -122,13 +122,17 @@ class FusedStep:
 
     def __init__(self, renderer, decoders, c, stage, n_rays, loss="mapping", w_color=0.2, use_color=True,
                  handle_dynamic=False, grid_grads=(), decoder_grads=(), ray_grads=False, with_gt_depth=True,
-                 group=None, peers=None):
+                 group=None, peers=None, sharded=None):
         if not renderer.fixed_shape_ok():
             raise NotImplementedError("FusedStep needs the NICE decoders, perturb == 0 and N_importance == 0")
         self.r, self.decoders, self.stage, self.N = renderer, decoders, stage, int(n_rays)
         self.kinds = STAGE_DECODERS[stage]
         self.loss_kind, self.w_color, self.use_color, self.handle_dynamic = loss, w_color, use_color, handle_dynamic
         self.group, self.ray_grads = group, ray_grads
+        # sharded: this step renders a slice of a batch that other ranks complete (gradients are summed over
+        # ``group``).  None = yes whenever a process group with more than one rank is initialised; pass
+        # False for a step that is whole on this rank although torch.distributed is up.
+        self._sharded_flag = sharded
         self.with_gt_depth = with_gt_depth and stage != "coarse"
         dev = next(decoders.parameters()).device
         self.dev = dev
@@ -181,6 +185,8 @@ class FusedStep:
     # -- plumbing -----------------------------------------------------------------------
     def _sharded(self):
         import torch.distributed as dist
+        if self._sharded_flag is False:
+            return False
         return dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1
 
     def _pack(self, k):
@@ -387,7 +393,7 @@ class TrackingStep:
         self.dev = dev
         self.step = FusedStep(t.renderer, t.decoders, t.c, "color", n_rays, loss="tracking",
                               w_color=t.w_color_loss, use_color=t.use_color_in_tracking,
-                              handle_dynamic=t.handle_dynamic, ray_grads=True)
+                              handle_dynamic=t.handle_dynamic, ray_grads=True, sharded=False)   # tracking: replicas only
         lr = t.cam_lr if lr is None else lr
         separate_lr = t.seperate_LR if separate_lr is None else separate_lr
         # Tracker.py:232-239: translation at cam_lr, quaternion at 0.2 cam_lr when seperate_LR

@@ -53,3 +53,21 @@ def test_exchange_two_gpus(tmp_path):
     res = json.load(open(out))
     assert res["checks"]["graph_replay"] is True
     assert any(k.startswith("reduce_adam_") for k in res["checks"])
+
+
+@pytest.mark.gpu
+def test_sharded_mapper_two_gpus(tmp_path):
+    """Mapper.optimize_map after enable_sharding (rays of every iteration split over 2 ranks, gradients
+    summed through the peer-memory exchange inside the iteration's CUDA graph, identical Adam step on
+    every rank) reproduces the single-GPU call, with frustum masks and with local BA, and the replicas
+    stay bit-identical (scripts/sharded_map_check.py)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs on one box")
+    out = tmp_path / "s.json"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29534", os.path.join(REPO, "scripts", "sharded_map_check.py"), "--iters", "6",
+           "--json", str(out)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=REPO)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    res = json.load(open(out))
+    assert set(res["checks"]) == {"no_BA", "BA"}
