@@ -163,3 +163,35 @@ def test_replica_backward_is_linear_in_the_incoming_gradient(replica):
     g12 = grads(0.7 * w[0][0] - 1.3 * w[1][0], 0.7 * w[0][1] - 1.3 * w[1][1])
     for x1, x2, x12 in zip(g1, g2, g12):
         assert_close(x12, 0.7 * x1 - 1.3 * x2, 1e-4, "linearity")
+
+
+def test_sample_depths_adversarial_rays_bit_exact(replica):
+    """k_sample_z ranks the S depths of a ray against each other (stable, NaNs last): rays that leave
+    the box before their near plane (descending uniform list), origins outside the box, zero / huge / NaN
+    sensor depths and NaN directions must still give exactly torch.sort's answer (Renderer.py:223)."""
+    from nice_slam_annotation_b200 import fused
+    ns = replica
+    g = torch.Generator().manual_seed(21)
+    n = 512
+    lo, hi = ns.bound[:, 0].float(), ns.bound[:, 1].float()
+    ro = lo + (hi - lo) * (torch.rand(n, 3, generator=g) * 1.6 - 0.3)          # some origins outside the box
+    rd = torch.randn(n, 3, generator=g)
+    rd[::7] *= 1e-3
+    rd[5::11, 1] = 0.0                                                         # axis-parallel components
+    gd = torch.rand(n, generator=g) * 12
+    gd[::5] = 0.0
+    gd[3::13] = 1e4
+    gd[1::97] = float("nan")
+    rd[2::101, 0] = float("nan")
+    for depth in (gd, None):
+        z_ref = O.sample_z(ro, rd, depth, ns.bound, 32, 16)
+        z = fused.sample_z(ro.to(DEV), rd.to(DEV), None if depth is None else depth.to(DEV), ns.bound, 32, 16).cpu()
+        same = (z == z_ref) | (z.isnan() & z_ref.isnan())
+        assert bool(same.all()), int((~same).sum())
+    # jitter + lindisp
+    u = torch.rand(n, 32, generator=g)
+    ok = ~(gd.isnan() | rd.isnan().any(1))
+    z_ref = O.sample_z(ro[ok], rd[ok], gd[ok], ns.bound, 32, 16, lindisp=True, u=u[ok])
+    z = fused.sample_z(ro[ok].to(DEV), rd[ok].to(DEV), gd[ok].to(DEV), ns.bound, 32, 16, lindisp=True, u=u[ok].to(DEV)).cpu()
+    same = (z == z_ref) | (z.isnan() & z_ref.isnan())
+    assert bool(same.all()), int((~same).sum())
