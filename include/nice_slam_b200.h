@@ -80,6 +80,14 @@ typedef struct NsbPoints {
                             * five layers of every point).  nsb_decoders_forward writes them,
                             * nsb_decoders_backward of the SAME points / stage / weights reads them and skips
                             * the forward recomputation for decoders without a weight gradient.  NULL: recompute. */
+    /* optional: the scratch / size / dweight_mask that nsb_decoders_backward of the SAME points will be
+     * given.  nsb_decoders_forward then deposits the layer inputs (embedding, features, hidden
+     * activations) of the trained decoders into the weight-gradient records, and the backward skips their
+     * recomputation too.  Needs relu_masks and a scratch that holds the whole batch
+     * (nsb_dweight_scratch_bytes); otherwise, or with NULL, nothing changes. */
+    void* x_scratch;
+    int64_t x_scratch_bytes;
+    uint32_t x_mask;
 } NsbPoints;
 
 /* Scene of one call: bound (src/NICE_SLAM.py:188-208), grids, packed decoders. */
@@ -284,6 +292,11 @@ typedef struct NsbRenderCall {
     float w_color;
     int32_t use_color;
     double* loss; /* [1] */
+    /* opt-in: nsb_render_forward deposits the layer inputs of the trained decoders (dweight_mask) into the
+     * weight-gradient records in `scratch`, and nsb_render_backward skips their recomputation.  flags,
+     * dweight_mask, scratch and this field must then be the same in the forward and the backward call of
+     * a step (they are when one struct serves both), and scratch must hold the whole batch. */
+    int32_t deposit_dweight_inputs;
 } NsbRenderCall;
 
 /* One ray batch (contiguous [n,3] / [n] device tensors, n <= N) into the fixed-shape input buffers of a

@@ -27,7 +27,8 @@ class NsbGrid(C.Structure):
 class NsbPoints(C.Structure):
     _fields_ = [("rays_o", c_ptr), ("rays_d", c_ptr), ("rays_o_stride", C.c_int64),
                 ("rays_d_stride", C.c_int64), ("z", c_ptr), ("N", C.c_int64), ("S", C.c_int32),
-                ("p64", c_ptr), ("p32", c_ptr), ("P", C.c_int64), ("relu_masks", c_ptr)]
+                ("p64", c_ptr), ("p32", c_ptr), ("P", C.c_int64), ("relu_masks", c_ptr),
+                ("x_scratch", c_ptr), ("x_scratch_bytes", C.c_int64), ("x_mask", C.c_uint32)]
 
 
 class NsbScene(C.Structure):
@@ -46,7 +47,8 @@ class NsbRenderCall(C.Structure):
                 ("g_depth", c_ptr), ("g_var", c_ptr), ("g_color", c_ptr),
                 ("flags", C.c_uint32), ("dweight_mask", C.c_uint32), ("d_weight", c_ptr * 4),
                 ("scratch", c_ptr), ("scratch_bytes", C.c_int64), ("g_rays_o", c_ptr), ("g_rays_d", c_ptr),
-                ("gt_color", c_ptr), ("w_color", C.c_float), ("use_color", C.c_int32), ("loss", c_ptr)]
+                ("gt_color", c_ptr), ("w_color", C.c_float), ("use_color", C.c_int32), ("loss", c_ptr),
+                ("deposit_dweight_inputs", C.c_int32)]
 
 
 class NsbImapDecoder(C.Structure):

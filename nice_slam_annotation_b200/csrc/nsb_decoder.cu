@@ -52,6 +52,7 @@ struct DecTask {
     float* dw_scratch;         // backward: weight-gradient records of this launch's tiles, or NULL
     unsigned char* dw_flags;   // one byte per tile: record written
     unsigned* relu;            // [P][8] ReLU sign words of this decoder (forward writes, backward reads) or NULL
+    int x_saved;               // backward: the forward deposited the X sections (e, c, h1..h5) of the records
 };
 
 struct StageParams {
@@ -595,7 +596,7 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, int
         }
         Rows R;
         Masks mk;
-        if (!rec && T.relu) {
+        if (T.relu && (!rec || T.x_saved)) {
             // the forward saved the ReLU signs: no recomputation (gather, embedding, six layers).
             // Saved as bytes [point][part n = feature / 8][layer]; lane (g, t) needs bits 2t, 2t + 1 of
             // byte (n, layer) of points g and g + 8 for its C-fragment columns 8n + 2t (+1)
@@ -646,32 +647,36 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, int
                     *reinterpret_cast<float4*>(c1) = make_float4(c[j0][1], c[j0][3], c[j0 + 1][1], c[j0 + 1][3]);
                     *reinterpret_cast<float4*>(c1 + 4) = make_float4(c[j0 + 2][1], c[j0 + 2][3], c[j0 + 3][1], c[j0 + 3][3]);
                 }
+            }
+        }
+        if (rec) {          // sections both paths write: the live flag, p and d(out)
+            const int g = lane >> 2;
+            if (lane == 0) T.dw_flags[tile - P.tile_begin] = 1;
                 // p: [16][8] (cols 0..2), d(out): [16][32] (cols < NOUT, rest zero)
-                {
-                    float* p0 = rec + RC::R_P + g * 8, * p1 = rec + RC::R_P + (g + 8) * 8;
-                    if (t == 0) {
-                        *reinterpret_cast<float4*>(p0) = make_float4(R.p[0][0], R.p[0][1], R.p[0][2], 0.f);
-                        *reinterpret_cast<float4*>(p1) = make_float4(R.p[1][0], R.p[1][1], R.p[1][2], 0.f);
-                    } else if (t == 1) {
-                        *reinterpret_cast<float4*>(p0 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
-                        *reinterpret_cast<float4*>(p1 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
-                    }
-                    // gather the (up to 4) output gradients of the row from lanes t = 0..3
-                    float d0[4], d1[4];
-#pragma unroll
-                    for (int o = 0; o < 4; ++o) {
-                        d0[o] = __shfl_sync(FULL, dA[0][0], (lane & ~3) | o);
-                        d1[o] = __shfl_sync(FULL, dA[0][1], (lane & ~3) | o);
-                    }
-                    // logical columns 8t..8t+7 of the row; the row's data (cols 0..3) is lane t == 0's
-                    float* o0 = rec + RC::R_DO + g * HID + rec_sw(g, 8 * t);
-                    float* o1 = rec + RC::R_DO + (g + 8) * HID + rec_sw(g, 8 * t);
-                    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                    *reinterpret_cast<float4*>(o0) = t == 0 ? make_float4(d0[0], d0[1], d0[2], d0[3]) : z4;
-                    *reinterpret_cast<float4*>(o1) = t == 0 ? make_float4(d1[0], d1[1], d1[2], d1[3]) : z4;
-                    *reinterpret_cast<float4*>(o0 + 4) = z4;
-                    *reinterpret_cast<float4*>(o1 + 4) = z4;
+            {
+                float* p0 = rec + RC::R_P + g * 8, * p1 = rec + RC::R_P + (g + 8) * 8;
+                if (t == 0) {
+                    *reinterpret_cast<float4*>(p0) = make_float4(R.p[0][0], R.p[0][1], R.p[0][2], 0.f);
+                    *reinterpret_cast<float4*>(p1) = make_float4(R.p[1][0], R.p[1][1], R.p[1][2], 0.f);
+                } else if (t == 1) {
+                    *reinterpret_cast<float4*>(p0 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+                    *reinterpret_cast<float4*>(p1 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
                 }
+                // gather the (up to 4) output gradients of the row from lanes t = 0..3
+                float d0[4], d1[4];
+#pragma unroll
+                for (int o = 0; o < 4; ++o) {
+                    d0[o] = __shfl_sync(FULL, dA[0][0], (lane & ~3) | o);
+                    d1[o] = __shfl_sync(FULL, dA[0][1], (lane & ~3) | o);
+                }
+                // logical columns 8t..8t+7 of the row; the row's data (cols 0..3) is lane t == 0's
+                float* o0 = rec + RC::R_DO + g * HID + rec_sw(g, 8 * t);
+                float* o1 = rec + RC::R_DO + (g + 8) * HID + rec_sw(g, 8 * t);
+                const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                *reinterpret_cast<float4*>(o0) = t == 0 ? make_float4(d0[0], d0[1], d0[2], d0[3]) : z4;
+                *reinterpret_cast<float4*>(o1) = t == 0 ? make_float4(d1[0], d1[1], d1[2], d1[3]) : z4;
+                *reinterpret_cast<float4*>(o0 + 4) = z4;
+                *reinterpret_cast<float4*>(o1 + 4) = z4;
             }
         }
         float dp[2][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
@@ -1039,6 +1044,9 @@ namespace nsb {
 // ---- host side -------------------------------------------------------------------------------
 static int g_num_sms = 0;
 static int g_use_tc = 1;         // NSB_TC=0 selects the mma.sync kernels (A/B comparisons)
+static float g_xsaved_cost = 0.62f;  // backward cost of a decoder whose records' X sections the forward deposited: no
+                                     // recomputation, but the G sections are still written (NSB_XSAVED_COST)
+static float g_xfwd_cost = 1.5f;     // forward cost of depositing them (NSB_XFWD_COST)
 static float g_saved_cost = 0.3f; // backward cost of a decoder that skips the recomputation, relative (NSB_SAVED_COST; swept on B200, r01)
 static bool g_attr_done = false;
 constexpr int CTR_SLOTS = 256;                   // launches in flight before a counter slot is reused
@@ -1079,6 +1087,8 @@ static int init_device() {
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     if (const char* v = getenv("NSB_TC")) g_use_tc = atoi(v);
     if (const char* v = getenv("NSB_SAVED_COST")) g_saved_cost = (float)atof(v);
+    if (const char* v = getenv("NSB_XSAVED_COST")) g_xsaved_cost = (float)atof(v);
+    if (const char* v = getenv("NSB_XFWD_COST")) g_xfwd_cost = (float)atof(v);
     build_dw_tables<KIND_COARSE>(g_dw_host[0]);
     build_dw_tables<KIND_MIDDLE>(g_dw_host[1]);
     build_dw_tables<KIND_FINE>(g_dw_host[2]);
@@ -1096,7 +1106,8 @@ static int init_device() {
 
 // decoders of a stage (decoder.py:336-370) and their relative cost per point
 static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp, float* out_occ0,
-                       float* out_occ1, float* out_rgb, float* d_point, long long P, unsigned dw_mask = 0) {
+                       float* out_occ1, float* out_rgb, float* d_point, long long P, unsigned dw_mask = 0,
+                       unsigned x_mask = 0) {
     int kinds[3], n = 0;
     float cost[3];
     switch (stage) {
@@ -1123,6 +1134,9 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
     if (!bwd && g_use_tc)
         for (int i = 0; i < n; ++i)
             cost[i] = kinds[i] == KIND_MIDDLE ? 15.f : (kinds[i] == KIND_FINE ? 23.5f : (kinds[i] == KIND_COLOR ? 16.5f : cost[i]));
+    if (!bwd && g_use_tc)                      // forward that also deposits the X sections of the d(W) records
+        for (int i = 0; i < n; ++i)
+            if (x_mask & (1u << kinds[i])) cost[i] *= g_xfwd_cost;
     // backward, measured warp run times per decoder (r01): fine 1.16x middle; writing the
     // weight-gradient records costs a decoder another 1.35x
     // a decoder without a weight gradient whose forward saved its ReLU signs skips the recomputation
@@ -1130,7 +1144,7 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
     if (bwd)
         for (int i = 0; i < n; ++i) {
             if (kinds[i] == KIND_FINE) cost[i] = 35.f;
-            if (dw_mask & (1u << kinds[i])) cost[i] *= 1.35f;
+            if (dw_mask & (1u << kinds[i])) cost[i] *= (saved && (x_mask & (1u << kinds[i]))) ? g_xsaved_cost * g_saved_cost / 0.3f : 1.35f;
             else if (saved && kinds[i] != KIND_COARSE) cost[i] *= g_saved_cost;
         }
     const long long tiles = (P + 15) / 16;
@@ -1189,6 +1203,7 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
         T.dw_scratch = nullptr;
         T.dw_flags = nullptr;
         T.relu = (saved && k != KIND_COARSE) ? sp.pts.relu + (size_t)i * P * 8 : nullptr;
+        T.x_saved = (bwd && saved && (x_mask & (1u << k))) ? 1 : 0;
         int share = share_of[i];
         if (share > want) share = want;
         T.cta_begin = begin;
@@ -1213,6 +1228,33 @@ static int max_blob(const StageParams& sp, bool bwd) {
 
 using namespace nsb;
 
+// bytes of one tile's record + flag, sized for the largest decoder
+static const int64_t kDwTileBytes = (int64_t)REC_MAX * 4 + 1;
+static const int64_t kDwMaxTiles = 4096;     // 64 Ki points per chunk
+
+// Weight-gradient scratch layout: [records of trained decoder 0 | 1 | ... | flags ...], `chunk` tiles per
+// decoder (the backward runs in chunks when the scratch is smaller than the batch).  Returns chunk (0:
+// too small) and the number of trained decoders of the stage.
+static long long dw_layout(const int* kinds, int ntask, unsigned mask, int64_t scratch_bytes, long long ntiles, int& ndw) {
+    ndw = 0;
+    for (int i = 0; i < ntask; ++i)
+        if (mask & (1u << kinds[i])) ++ndw;
+    if (!ndw) return ntiles;
+    long long chunk = ((scratch_bytes - 256) / ndw) / kDwTileBytes;
+    return chunk > ntiles ? ntiles : chunk;
+}
+// The forward deposits the X sections of the records (and the backward then skips the recomputation of the
+// trained decoders) when the points carry the backward's scratch and it holds the whole batch at once.
+static bool x_deposit_ok(const NsbPoints& pts, const StageParams& sp, long long ntiles) {
+    if (!g_use_tc || !pts.x_scratch || !pts.x_mask || !sp.pts.relu) return false;
+    int kinds[3], ndw;
+    for (int i = 0; i < sp.ntask; ++i) {
+        kinds[i] = sp.task[i].kind;
+        if (kinds[i] == KIND_COARSE) return false;
+    }
+    return dw_layout(kinds, sp.ntask, pts.x_mask, pts.x_scratch_bytes, ntiles, ndw) == ntiles && ndw > 0;
+}
+
 extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene, int stage,
                                     float* out_occ0, float* out_occ1, float* out_rgb,
                                     void* stream) {
@@ -1224,6 +1266,14 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
     if (!sp.pts.ro && !sp.pts.p64 && !sp.pts.p32) return set_error(NSB_EINVAL, "no points given");
     int ctas = stage_tasks(*scene, stage, false, sp, out_occ0, out_occ1, out_rgb, nullptr, sp.pts.P);
     if (ctas < 0) return ctas;
+    if (x_deposit_ok(*pts, sp, (sp.pts.P + 15) / 16)) {
+        ctas = stage_tasks(*scene, stage, false, sp, out_occ0, out_occ1, out_rgb, nullptr, sp.pts.P, 0u, pts->x_mask);
+        const long long nt = (sp.pts.P + 15) / 16;
+        char* base = (char*)(((uintptr_t)pts->x_scratch + 255) & ~(uintptr_t)255);
+        int k = 0;
+        for (int i = 0; i < sp.ntask; ++i)
+            if (pts->x_mask & (1u << sp.task[i].kind)) sp.task[i].dw_scratch = (float*)(base + (size_t)(k++) * nt * REC_MAX * 4);
+    }
     sp.d_raw = nullptr;
     sp.flags = 0;
     sp.tile_begin = 0;
@@ -1263,9 +1313,6 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
     return check_launch(tc ? "k_decoders_forward_tc" : "k_decoders_forward");
 }
 
-// bytes of one tile's record + flag, sized for the largest decoder
-static const int64_t kDwTileBytes = (int64_t)REC_MAX * 4 + 1;
-static const int64_t kDwMaxTiles = 4096;     // 64 Ki points per chunk
 
 extern "C" int64_t nsb_dweight_scratch_bytes(int kind, int64_t P) {
     (void)kind;
@@ -1285,10 +1332,17 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
     sp.pts = to_dev(*pts);
     if (sp.pts.P <= 0) return 0;
     if ((flags & NSB_GRAD_POINT) && !d_point) return set_error(NSB_EINVAL, "d_point is NULL");
+    const unsigned dwm = (flags & NSB_GRAD_WEIGHT) ? dweight_mask : 0u;
     int ctas = stage_tasks(*scene, stage, true, sp, nullptr, nullptr, nullptr,
-                           (flags & NSB_GRAD_POINT) ? d_point : nullptr, sp.pts.P,
-                           (flags & NSB_GRAD_WEIGHT) ? dweight_mask : 0u);
+                           (flags & NSB_GRAD_POINT) ? d_point : nullptr, sp.pts.P, dwm);
     if (ctas < 0) return ctas;
+    // did the forward of these points deposit the X sections of the records into THIS scratch?
+    if (dwm && pts->x_scratch == scratch && pts->x_scratch_bytes == scratch_bytes && pts->x_mask == dwm &&
+        x_deposit_ok(*pts, sp, (sp.pts.P + 15) / 16)) {
+        ctas = stage_tasks(*scene, stage, true, sp, nullptr, nullptr, nullptr,
+                           (flags & NSB_GRAD_POINT) ? d_point : nullptr, sp.pts.P, dwm, dwm);
+        if (ctas < 0) return ctas;
+    }
     sp.d_raw = d_raw;
     sp.flags = flags;
     const long long ntiles = (sp.pts.P + 15) / 16;

@@ -95,8 +95,12 @@ __device__ __forceinline__ void tc_publish_tri(const GridDev& G, const float (&u
     reinterpret_cast<float4*>(e)[1] = make_float4(t.ix, t.iy, t.iz, t.x0);
     reinterpret_cast<float2*>(e)[4] = make_float2(t.y0, t.z0);
 }
+// xrec (optional): weight-gradient records of the tile's eight 16-point sub-tiles (stride rec_stride floats),
+// already offset to the c section and the level's first column: the fp32 features are deposited there
+// for k_dweight, so that the backward does not have to recompute them (RecCfg in nsb_layout.h)
 __device__ __forceinline__ void tc_gather_level(const GridDev& G, const float* s_tri, float* chi, float* clo,
-                                                int warp, int lane) {
+                                                int warp, int lane, float* xrec = nullptr, int rec_stride = 0,
+                                                int c_in = 0, int rows_ok = 128) {
     const int sub = lane & 7;
 #pragma unroll
     for (int r = 0; r < 128 / (4 * (TC_THREADS / 32)); ++r) {
@@ -125,6 +129,11 @@ __device__ __forceinline__ void tc_gather_level(const GridDev& G, const float* s
         const int idx = tc::kmajor_index(q, 4 * sub, 128);
         *reinterpret_cast<uint4*>(chi + idx) = make_uint4(h[0], h[1], h[2], h[3]);
         *reinterpret_cast<uint4*>(clo + idx) = make_uint4(l[0], l[1], l[2], l[3]);
+        if (xrec && q < rows_ok) {
+            const int rr = q & 15;
+            *reinterpret_cast<float4*>(xrec + (size_t)(q >> 4) * rec_stride + rr * c_in + rec_sw(rr, 4 * sub)) =
+                make_float4(f[0], f[1], f[2], f[3]);
+        }
     }
 }
 
@@ -155,7 +164,9 @@ __device__ __forceinline__ void tc_load_point(const PointsDev& q, const DecTask&
 
 // 8 embedding features [c0, c0 + 8) of this thread's point -> tensor memory (hi / lo)
 // (Bv: [feature] -> (B[0][f], B[1][f], B[2][f], 0); same operation order as phase())
-__device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float4* Bv, uint32_t lane_base, int c0) {
+// erow (optional): this point's row of the record's e section ([16][96], rec_sw columns), r its row index
+__device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float4* Bv, uint32_t lane_base, int c0,
+                                          float* erow = nullptr, int r = 0) {
     float e[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -163,6 +174,11 @@ __device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float4* B
         e[j] = sin_cw(fmaf(p32[2], b.z, fmaf(p32[1], b.y, p32[0] * b.x)));
     }
     st_split8(lane_base, TM_EHI + c0, TM_ELO + c0, e);
+    if (erow) {
+        float* d = erow + rec_sw(r, c0);
+        *reinterpret_cast<float4*>(d) = make_float4(e[0], e[1], e[2], e[3]);
+        *reinterpret_cast<float4*>(d + 4) = make_float4(e[4], e[5], e[6], e[7]);
+    }
 }
 
 // Software pipeline: the inputs of tile n+1 (point, voxel addressing, feature gather, embedding)
@@ -228,6 +244,23 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     static_assert(EPP == 24 && HPP == 8, "per-thread shares are whole 8-column TMEM accesses");
     uint32_t par = 0;                                          // mbarrier phase parity
     const long long ntiles = (P.pts.P + 127) / 128;
+    // X sections of the weight-gradient records (e, c, h1..h5), written here when the backward of these
+    // points wants d(W) of this decoder: its backward then skips the recomputation (DecTask::dw_scratch)
+    using RC = RecCfg<KIND>;
+    float* const xrec = T.dw_scratch;
+    const long long rows_total = (P.pts.P + 15) / 16 * 16;     // whole 16-point records (padded rows hold finite values)
+    auto rec_row = [&](long long t_, int section, int width) -> float* {      // this thread's row of a section
+        const long long i_ = t_ * 128 + row;
+        if (!xrec || i_ >= rows_total) return nullptr;
+        return xrec + (size_t)(i_ >> 4) * RC::REC + section + (row & 15) * width;
+    };
+    auto rec_tile = [&](long long t_, int section) -> float* {                // first record of a 128-point tile
+        return xrec ? xrec + (size_t)(t_ * 8) * RC::REC + section : nullptr;
+    };
+    auto rows_ok = [&](long long t_) -> int {
+        const long long left = rows_total - t_ * 128;
+        return left >= 128 ? 128 : (left > 0 ? (int)left : 0);
+    };
 #ifdef NSB_TC_PROFILE
     long long tq[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
 #define TQ(k) { const long long tn_ = clock64(); tq[k] += tn_ - tlast; tlast = tn_; }
@@ -261,12 +294,14 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     if (tile < ntiles) {
         publish_point(tile);
         __syncthreads();
-        tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
+        tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane, rec_tile(tile, RC::R_C), RC::REC, C::C_IN,
+                        rows_ok(tile));
         {
             const float4 pp = s_pt[row];
             const float p32[3] = {pp.x, pp.y, pp.z};
+            float* er = rec_row(tile, RC::R_E, EMB_PAD);
 #pragma unroll
-            for (int j = 0; j < 3; ++j) tc_embed8(p32, Bv, lane_base, EPP * part + 8 * j);
+            for (int j = 0; j < 3; ++j) tc_embed8(p32, Bv, lane_base, EPP * part + 8 * j, er, row & 15);
         }
         tc::tmem_st_wait();
         tc::fence_async_smem();
@@ -285,7 +320,8 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         TQ(1)  // wait for the up-front GEMMs
         if constexpr (KIND == KIND_FINE) {
             // second half of the feature GEMM: the middle-grid feature (channels 32..63), no gradient
-            tc_gather_level(T.aux, s_tri + 128 * TRI_WORDS, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
+            tc_gather_level(T.aux, s_tri + 128 * TRI_WORDS, sm + S::S_CHI, sm + S::S_CLO, warp, lane,
+                            xrec ? rec_tile(tile, RC::R_C) + 32 : nullptr, RC::REC, C::C_IN, rows_ok(tile));
             tc::fence_async_smem();
             tc::fence_before_sync();
             __syncthreads();
@@ -326,6 +362,11 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             if (L < 4) relu_lo |= sign << (8 * L);      // signs of features 8 part .. 8 part + 7, one byte per layer
             else relu_hi = sign;
             st_split8(lane_base, TM_HHI + hc, TM_HLO + hc, a);
+            if (float* hr = rec_row(tile, RC::R_H + L * 16 * HID, HID)) {        // h_{L+1}: input of the next layer's d(W)
+                float* d = hr + rec_sw(row & 15, hc);
+                *reinterpret_cast<float4*>(d) = make_float4(a[0], a[1], a[2], a[3]);
+                *reinterpret_cast<float4*>(d + 4) = make_float4(a[4], a[5], a[6], a[7]);
+            }
             tc::tmem_st_wait();
             tc::fence_before_sync();
             TQ(4)  // layer epilogue (ld, alu, st)
@@ -350,11 +391,12 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             TQ(6)  // MMA issue (warp 0)
             // ---- a slice of the next tile's inputs while the tensor core works ------------------------
             if (has_next) {
-                if (L == 0) tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane);
+                if (L == 0) tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane, rec_tile(nxt, RC::R_C),
+                                            RC::REC, C::C_IN, rows_ok(nxt));
                 else if (L <= 3) {
                     const float4 pp = s_pt[row];
                     const float p32n[3] = {pp.x, pp.y, pp.z};
-                    tc_embed8(p32n, Bv, lane_base, EPP * part + 8 * (L - 1));
+                    tc_embed8(p32n, Bv, lane_base, EPP * part + 8 * (L - 1), rec_row(nxt, RC::R_E, EMB_PAD), row & 15);
                 }
             }
             TQ(7)  // next tile's slice

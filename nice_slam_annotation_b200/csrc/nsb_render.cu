@@ -54,6 +54,9 @@ static NsbPoints ray_pts(const NsbRenderCall* r, const double* z, int S) {
     p.rays_o = r->rays_o; p.rays_d = r->rays_d;
     p.rays_o_stride = r->rays_o_stride; p.rays_d_stride = r->rays_d_stride;
     p.z = z; p.N = r->N; p.S = S; p.P = r->N * S;
+    if (r->deposit_dweight_inputs && (r->flags & NSB_GRAD_WEIGHT) && r->dweight_mask && r->scratch) {
+        p.x_scratch = r->scratch; p.x_scratch_bytes = r->scratch_bytes; p.x_mask = r->dweight_mask;
+    }
     return p;
 }
 

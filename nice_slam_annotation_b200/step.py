@@ -224,6 +224,9 @@ class FusedStep:
             flags |= GRAD_POINT
             call.g_rays_o, call.g_rays_d = self.g_rays_o.data_ptr(), self.g_rays_d.data_ptr()
         call.flags, call.dweight_mask = flags, mask
+        # one struct serves the forward and the backward call: the forward may deposit the trained decoders'
+        # layer inputs into the weight-gradient records (the backward then skips their recomputation)
+        call.deposit_dweight_inputs = 1 if (mask and os.environ.get("NSB_DEPOSIT", "1") != "0") else 0
         # mapping: compositing + loss + their adjoint run as one kernel inside nsb_render_backward
         self.fused_loss = self.loss_kind == "mapping" and self.with_gt_depth and bool(r.occupancy)
         if self.fused_loss:
