@@ -447,13 +447,13 @@ __global__ void k_pose_grad(const float* __restrict__ g_o, const float* __restri
         if (lane == 0) red[k][warp] = v;
     }
     __syncthreads();
+    if (warp != 0) return;
+    const int nw = blockDim.x >> 5;
+    for (int k = 0; k < 12; ++k) acc[k] = warp_sum_d(lane < nw ? red[k][lane] : 0.0);
     if (threadIdx.x == 0) {
         double dR[3][3], dt[3];
-        const int nw = blockDim.x >> 5;
         for (int k = 0; k < 12; ++k) {
-            double v = 0.0;
-            for (int w = 0; w < nw; ++w) v += red[k][w];
-            if (k < 9) dR[k / 3][k % 3] = v; else dt[k - 9] = v;
+            if (k < 9) dR[k / 3][k % 3] = acc[k]; else dt[k - 9] = acc[k];
         }
         const double qr = cam7[0], qi = cam7[1], qj = cam7[2], qk = cam7[3];
         const double nrm = qr * qr + qi * qi + qj * qj + qk * qk;
@@ -561,7 +561,7 @@ extern "C" int nsb_pose_grad(const float* g_rays_o, const float* g_rays_d, const
                              const uint8_t* keep, int64_t n, int H0, int W0, int Wc, float fx, float fy,
                              float cx, float cy, const float* cam7, float* d_cam7, void* stream) {
     if (!g_rays_o || !g_rays_d || !indices || !cam7 || !d_cam7) return set_error(NSB_EINVAL, "null argument");
-    k_pose_grad<<<1, 256, 0, (cudaStream_t)stream>>>(g_rays_o, g_rays_d, indices, keep, n, H0, W0, Wc, fx, fy,
+    k_pose_grad<<<1, 1024, 0, (cudaStream_t)stream>>>(g_rays_o, g_rays_d, indices, keep, n, H0, W0, Wc, fx, fy,
                                                      cx, cy, cam7, d_cam7);
     return check_launch("k_pose_grad");
 }

@@ -107,6 +107,50 @@ __global__ void k_mapping_loss(const double* __restrict__ depth, const float* __
     }
 }
 
+// Median of the live depth residuals |gt - depth| / sqrt(var + 1e-10) (Tracker.py:118-121, torch.median = the
+// lower middle of the sorted values, NaN if any value is NaN) by rank counting over many blocks: every block
+// holds all N residuals in shared memory, every warp ranks one of them (lanes stride the others, ties by
+// position), and the one whose rank is (n_live - 1) / 2 writes out[0].  1000 rays: 32 blocks, 32 compares per
+// lane, where the single-block bitonic sort below needs 55 barrier-separated stages.
+__global__ void k_residual_median(const double* __restrict__ depth, const double* __restrict__ var,
+                                  const float* __restrict__ gd, const uint8_t* __restrict__ keep, int N,
+                                  double* __restrict__ out) {
+    extern __shared__ double sh[];      // N doubles
+    __shared__ int s_live;
+    if (threadIdx.x == 0) s_live = 0;
+    __syncthreads();
+    int live_local = 0, nan_local = 0;
+    for (int i = threadIdx.x; i < N; i += blockDim.x) {
+        double v = INFINITY;
+        if (!keep || keep[i]) {
+            v = fabs((double)gd[i] - depth[i]) / sqrt(var[i] + 1e-10);
+            ++live_local;
+            nan_local |= v != v;
+        }
+        sh[i] = v;
+    }
+    if (live_local) atomicAdd(&s_live, live_local);
+    const int any_nan = __syncthreads_or(nan_local);
+    const int n_live = s_live;
+    if (n_live == 0 || any_nan) {        // torch.median: NaN as soon as one value is NaN
+        if (blockIdx.x == 0 && threadIdx.x == 0)
+            out[0] = any_nan ? __longlong_as_double(0x7ff8000000000000ll) : INFINITY;
+        return;
+    }
+    const int want = (n_live - 1) / 2;
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= N) return;
+    const double a = sh[i];
+    int rank = 0;
+    for (int j = lane; j < N; j += 32) {
+        const double b = sh[j];
+        rank += (b < a || (b == a && j < i)) ? 1 : 0;
+    }
+    for (int s = 16; s > 0; s >>= 1) rank += __shfl_xor_sync(FULL, rank, s);
+    if (lane == 0 && rank == want) out[0] = a;
+}
+
 // Tracking (Tracker.py:117-130): tmp = |gt - d| / sqrt(var + 1e-10); mask = tmp < 10 median(tmp)
 // & gt > 0 (handle_dynamic) or gt > 0; loss = sum_mask tmp + w sum_mask |gt_c - c|.  The median
 // is torch's lower median of the live rays, found by a bitonic sort in shared memory.
@@ -114,8 +158,8 @@ __global__ void k_tracking_loss(const double* __restrict__ depth, const double* 
                                 const float* __restrict__ color, const float* __restrict__ gd,
                                 const float* __restrict__ gc, const uint8_t* __restrict__ keep, long long N,
                                 int npow2, float w_color, int use_color, int handle_dynamic,
-                                double* __restrict__ loss, double* __restrict__ g_depth,
-                                float* __restrict__ g_color) {
+                                const double* median, double* __restrict__ loss,
+                                double* __restrict__ g_depth, float* __restrict__ g_color) {
     extern __shared__ double sh[];      // npow2 doubles
     __shared__ double part[32];
     __shared__ int s_live;
@@ -133,7 +177,9 @@ __global__ void k_tracking_loss(const double* __restrict__ depth, const double* 
     atomicAdd(&s_live, live_local);
     __syncthreads();
     double thr = INFINITY;
-    if (handle_dynamic) {
+    if (handle_dynamic && median) {
+        thr = 10.0 * median[0];          // k_residual_median ran before this kernel
+    } else if (handle_dynamic) {
         for (int k = 2; k <= npow2; k <<= 1)
             for (int j = k >> 1; j > 0; j >>= 1) {
                 for (int i = threadIdx.x; i < npow2; i += blockDim.x) {
@@ -149,7 +195,8 @@ __global__ void k_tracking_loss(const double* __restrict__ depth, const double* 
                 __syncthreads();
             }
         const int n_live = s_live;
-        thr = n_live > 0 ? 10.0 * sh[(n_live - 1) / 2] : INFINITY;
+        // torch.median returns NaN as soon as one value is NaN (they sort last)
+        thr = n_live > 0 ? 10.0 * (sh[npow2 - 1] != sh[npow2 - 1] ? sh[npow2 - 1] : sh[(n_live - 1) / 2]) : INFINITY;
     }
     __syncthreads();
     double acc = 0.0;
@@ -392,8 +439,17 @@ extern "C" int nsb_tracking_loss(const double* depth, const double* var, const f
         if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
         attr = true;
     }
-    k_tracking_loss<<<1, 1024, npow2 * 8, (cudaStream_t)stream>>>(depth, var, color, gt_depth, gt_color, keep, N,
-                                                                npow2, w_color, use_color, handle_dynamic, loss,
-                                                                g_depth, g_color);
+    const double* median = nullptr;
+    if (handle_dynamic && N > 0 && N <= 4096) {
+        // loss[0] carries the median between the two kernels; the second overwrites it with the loss
+        const int warps = 32;
+        k_residual_median<<<(unsigned)((N + warps - 1) / warps), warps * 32, N * 8, (cudaStream_t)stream>>>(
+            depth, var, gt_depth, keep, (int)N, loss);
+        if (int rc = check_launch("k_residual_median")) return rc;
+        median = loss;
+    }
+    k_tracking_loss<<<1, 1024, median ? 8 : npow2 * 8, (cudaStream_t)stream>>>(
+        depth, var, color, gt_depth, gt_color, keep, N, median ? 1 : npow2, w_color, use_color, handle_dynamic,
+        median, loss, g_depth, g_color);
     return check_launch("k_tracking_loss");
 }

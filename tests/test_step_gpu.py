@@ -138,6 +138,40 @@ def test_fused_losses_vs_oracle(scene, handle_dynamic):
     assert_close(c1.grad.cpu(), c0.grad, 1e-6, "d loss/d color")
 
 
+@pytest.mark.parametrize("n", [1, 2, 33, 1000, 4096, 5000])
+def test_tracking_loss_median_edge_cases(scene, n):
+    """The dynamic-object threshold is 10 x torch.median of the live residuals (Tracker.py:118-121): ties, a
+    NaN residual (the median is NaN then), masked rays and both median paths (rank counting <= 4096 rays,
+    sort above)."""
+    from nice_slam_annotation_b200 import fused
+    g = torch.Generator().manual_seed(n)
+    depth = torch.rand(n, generator=g, dtype=torch.float64) * 3 + 0.2
+    var = torch.rand(n, generator=g, dtype=torch.float64) * 0.1
+    gd = torch.rand(n, generator=g) * 3 + 0.2
+    if n > 8:
+        depth[5:n // 2] = depth[4]; var[5:n // 2] = var[4]; gd[5:n // 2] = gd[4]     # ties around the median
+        gd[-3:] += 40.0                                                                # above the threshold
+    color = torch.rand(n, 3, generator=g)
+    gc = torch.rand(n, 3, generator=g)
+    keep = torch.rand(n, generator=g) > 0.2 if n > 2 else torch.ones(n, dtype=torch.bool)
+    for case, kp in enumerate((None, keep, None)):
+        sel = slice(None) if kp is None else kp
+        if case == 2:
+            depth[n // 2] = float("nan")        # torch.median is NaN then: nothing passes the threshold
+        d0 = depth.clone().requires_grad_(True)
+        l0 = O.tracking_loss(d0[sel], var[sel], color[sel], gd[sel], gc[sel], w_color=0.5, use_color=True,
+                             handle_dynamic=True)
+        l0.backward()
+        d1 = depth.to(DEV).requires_grad_(True)
+        l1 = fused.tracking_loss(d1, var.to(DEV), color.to(DEV), gd.to(DEV), gc.to(DEV), 0.5, True, True,
+                                 keep=None if kp is None else kp.to(DEV))
+        l1.backward()
+        assert_close(l1.detach().cpu().reshape(1), l0.detach().reshape(1), 1e-7, "tracking loss")
+        g1, g0 = torch.nan_to_num(d1.grad.cpu()), torch.nan_to_num(d0.grad)
+        assert torch.equal(g1 != 0, g0 != 0), "threshold mask"
+        assert_close(g1, g0, 1e-12, "d loss/d depth")
+
+
 def test_render_img_vs_oracle(scene):
     """f3: Renderer.render_img (Renderer.py:264-340) = get_rays + render_batch_ray over the whole
     frame (one 100k-ray batch here), against the oracle on every pixel."""
