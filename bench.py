@@ -180,6 +180,10 @@ def run_ours(args):
     step_kw = dict(loss="mapping", w_color=W_COLOR, use_color=True,
                    grid_grads=("grid_middle", "grid_fine", "grid_color"), decoder_grads=("color_decoder",))
     step = FusedStep(ns.renderer, dec, grids, STAGE, args.rays, peers=peers, **step_kw)
+    if peers is not None and step.bucket.sparse:
+        exchange = ("nsb_bucket_allreduce_sparse: one kernel over symmetric memory (touched-line words pushed to the "
+                    "slice owner, only voxel lines some rank touched are reduced and stored back, peer ld / st over "
+                    "NVLink), inside the step's CUDA graph; depth max over ranks: nsb_depth_max_peers in the same graph")
 
     def step_device(b):
         step.load(*b)
@@ -243,6 +247,9 @@ def run_ours(args):
             L.nsb_timing(1)
         timed(step_device, batches, max(args.steps // 2, 3), args.warmup, start_timing)
         (fwd_ms, _), (bwd_ms, _), (dw_ms, _) = kernel_ms(0), kernel_ms(1), kernel_ms(2)
+        x_kernel_ms = dmax_kernel_ms = None
+        if world > 1:       # includes the wait for the slowest rank at the kernels' opening barriers
+            x_kernel_ms, dmax_kernel_ms = kernel_ms(3)[0] or None, kernel_ms(4)[0] or None
         L.nsb_timing(0)
         # (2) value: graph replay
         L.nsb_launch_count(1)
@@ -306,7 +313,8 @@ def run_ours(args):
                              + ("" if args.no_graph else ", replayed as one CUDA graph"),
                    "parallelism": f"rays sharded over {world} GPU(s), grids+decoders replicated"
                                   + ("; gradient exchange: " + exchange if world > 1 else ""),
-                   "exchange": exchange, "ms_per_step_with_nccl_allreduce": ms_nccl,
+                   "exchange": exchange, "exchange_kernel_ms": x_kernel_ms, "depth_max_peers_kernel_ms": dmax_kernel_ms,
+                   "ms_per_step_with_nccl_allreduce": ms_nccl,
                    "exchange_max_rel_diff_vs_nccl": x_err},
         "e2e": {"value": world * n_rays / (ms_eng * 1e-3), "unit": "rays/s", "ms_per_step": ms_eng,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,

@@ -29,10 +29,10 @@ int check_launch(const char* what) {
 // ---- optional device-side timing of the two decoder kernels (bench.py roofline) ---------------
 constexpr int TIMING_MAX = 4096;
 static bool g_timing = false;
-constexpr int TIMING_SLOTS = 3;      // 0 decoder forward, 1 decoder backward, 2 weight gradients
+constexpr int TIMING_SLOTS = 5;      // 0 decoder forward, 1 decoder backward, 2 weight gradients, 3 exchange, 4 depth max over peers
 static cudaEvent_t g_ev[TIMING_SLOTS][TIMING_MAX][2];
-static int g_ev_created[TIMING_SLOTS] = {0, 0, 0};
-static int g_ev_used[TIMING_SLOTS] = {0, 0, 0};
+static int g_ev_created[TIMING_SLOTS] = {};
+static int g_ev_used[TIMING_SLOTS] = {};
 
 void timing_mark(int which, int phase, cudaStream_t s) {
     if (!g_timing) return;

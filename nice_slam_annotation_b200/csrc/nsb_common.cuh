@@ -15,7 +15,7 @@ constexpr unsigned FULL = 0xffffffffu;
 // ---- host-side error plumbing (nsb_api.cu) -------------------------------------------
 int set_error(int code, const char* fmt, ...);
 int check_launch(const char* what);
-void timing_mark(int which, int phase, cudaStream_t s);   // which: 0 decoder forward, 1 decoder backward, 2 weight gradients
+void timing_mark(int which, int phase, cudaStream_t s);   // which: 0 decoder forward, 1 decoder backward, 2 weight gradients, 3 gradient exchange, 4 depth max over peers
 
 // ---- points -------------------------------------------------------------------------
 struct PointsDev {

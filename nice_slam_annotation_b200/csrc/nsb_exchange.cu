@@ -353,7 +353,9 @@ extern "C" int nsb_bucket_allreduce(const NsbPeers* peers, int64_t offset, int64
         if ((uintptr_t)g.bucket[r] & 15) return set_error(NSB_EINVAL, "exchange: buffers must be 16-byte aligned");
     const long long n4 = n / 4, per = (n4 + g.world - 1) / g.world;
     AdamDev a = {};
+    timing_mark(3, 0, (cudaStream_t)stream);
     k_exchange<false><<<blocks_for(per), X_THREADS, 0, (cudaStream_t)stream>>>(g, (long long)offset, n4, per, a);
+    timing_mark(3, 1, (cudaStream_t)stream);
     return check_launch("k_exchange");
 }
 
@@ -382,7 +384,9 @@ extern "C" int nsb_bucket_reduce_adam(const NsbPeers* peers, int64_t offset, int
     AdamDev a;
     a.m = m_slice; a.v = v_slice; a.mask = voxel_mask; a.state2 = state2; a.lr = lr;
     a.b1 = beta1; a.b2 = beta2; a.eps = eps; a.p_off = (long long)param_offset;
+    timing_mark(3, 0, (cudaStream_t)stream);
     k_exchange<true><<<blocks_for(per), X_THREADS, 0, (cudaStream_t)stream>>>(g, (long long)offset, n4, per, a);
+    timing_mark(3, 1, (cudaStream_t)stream);
     return check_launch("k_exchange_adam");
 }
 
@@ -402,7 +406,9 @@ extern "C" int nsb_bucket_allreduce_sparse(const NsbPeers* peers, int64_t offset
     long long b = (per_u + X_WARPS - 1) / X_WARPS;
     const int cap = blocks_for(1ll << 40);
     const int nb = (int)(b < 1 ? 1 : (b > cap ? cap : b));
+    timing_mark(3, 0, (cudaStream_t)stream);
     k_exchange_sparse<<<nb, X_THREADS, 0, (cudaStream_t)stream>>>(g, (long long)offset, n4, n_units, per_u);
+    timing_mark(3, 1, (cudaStream_t)stream);
     return check_launch("k_exchange_sparse");
 }
 
@@ -413,6 +419,8 @@ extern "C" int nsb_depth_max_peers(const NsbPeers* peers, const float* gt_depth,
     if (!gt_depth || !out) return set_error(NSB_EINVAL, "null argument");
     for (int r = 0; r < g.world; ++r)
         if (!g.scalar[r]) return set_error(NSB_EINVAL, "depth max: missing scalar slot of rank %d", r);
+    timing_mark(4, 0, (cudaStream_t)stream);
     k_depth_max_peers<<<1, 1024, 0, (cudaStream_t)stream>>>(g, gt_depth, keep, (long long)N, out);
+    timing_mark(4, 1, (cudaStream_t)stream);
     return check_launch("k_depth_max_peers");
 }
