@@ -344,6 +344,7 @@ def run_ours(args):
         out["cpu_baseline"] = cpu_baseline(ns, batches, budget_s=12.0)
     if rank == 0 and world == 1 and not args.no_tracking:
         out["bulk_forward"] = bulk_forward_bench(ns, dev)
+        out["mesh_depth"] = mesh_depth_bench(dev)
         out["optimize_map"] = optimize_map_bench(ns, dev)              # last: it trains the scene
     if rank == 0:
         print(json.dumps(out), flush=True)
@@ -504,6 +505,47 @@ def bulk_forward_bench(ns, dev):
                            "what": "Renderer.render_img, stage color, gt depth given, 100k-ray batches, forward only"},
             "eval_points": {"points": n ** 3, "ms": ms_pts, "points_per_s": n ** 3 / (ms_pts * 1e-3),
                             "what": "Renderer.eval_points, 256^3 lattice inside the bound, 500k-point batches, stage color"}}
+
+
+def mesh_depth_bench(dev, n=200, views=64):
+    """f4: depth images of a triangle mesh at the size of eval_recon.calc_2d_metric (500 x 500, focal 300,
+    eval_recon.py:137-144): a box room of 12 n^2 triangles from ``views`` random poses inside it."""
+    import numpy as np
+    from nice_slam_annotation_b200.tools.eval_recon import render_mesh_depth, viewmatrix
+    lo, hi = np.array([-2.0, -1.5, -2.5]), np.array([2.0, 1.5, 2.5])
+    verts, tris, s = [], [], np.linspace(0.0, 1.0, n + 1)
+    for axis in range(3):
+        a, b = [k for k in range(3) if k != axis]
+        for side in (lo[axis], hi[axis]):
+            base = sum(len(v) for v in verts)
+            ga, gb = np.meshgrid(lo[a] + s * (hi[a] - lo[a]), lo[b] + s * (hi[b] - lo[b]), indexing="ij")
+            p = np.zeros((n + 1, n + 1, 3))
+            p[..., axis], p[..., a], p[..., b] = side, ga, gb
+            verts.append(p.reshape(-1, 3))
+            i, j = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+            q = (base + i * (n + 1) + j).reshape(-1)
+            tris += [np.stack([q, q + 1, q + n + 2], 1), np.stack([q, q + n + 2, q + n + 1], 1)]
+    v = torch.as_tensor(np.concatenate(verts), dtype=torch.float32, device=dev)
+    t = torch.as_tensor(np.concatenate(tris), dtype=torch.int32, device=dev)
+    rng = np.random.default_rng(0)
+    c2ws = np.tile(np.eye(4), (views, 1, 1))
+    for k in range(views):
+        c2ws[k, :3] = viewmatrix(rng.uniform(-1, 1, 3), np.array([0.0, 0.0, -1.0]), rng.uniform(lo + 0.4, hi - 0.4))
+    fn = lambda: render_mesh_depth(v, t, c2ws, 500, 500, 300.0, 300.0, 249.5, 249.5, device=dev)
+    d = fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(3):
+        d = fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 3
+    return {"triangles": int(t.shape[0]), "views": views, "image": "500x500", "ms": ms,
+            "images_per_s": views / (ms * 1e-3), "covered": float((d > 0).float().mean()),
+            "what": "tools.eval_recon.render_mesh_depth (nsb_mesh_depth): headless ray-cast of the depth buffer "
+                    "calc_2d_metric reads from an Open3D GL window (unavailable on this box), incl. the host-side "
+                    "pose inversion and upload"}
 
 
 def optimize_map_bench(ns, dev, iters=60):

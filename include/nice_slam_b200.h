@@ -384,6 +384,20 @@ int nsb_keyframe_overlap(const float* rays_o, const float* rays_d, const float* 
                          int N_samples, const float* t_vals, const float* w2c, int K, int H, int W, double fx,
                          double fy, double cx, double cy, int edge, int32_t* counts, void* stream);
 
+/* ---- mesh depth images for the 2-D reconstruction metric -----------------------------
+ * Replaces the Open3D GL window of calc_2d_metric (src/tools/eval_recon.py:131-210: add_geometry,
+ * convert_from_pinhole_camera_parameters, capture_depth_float_buffer(True), back faces shown) by a headless
+ * ray-cast: depth [K,H,W] fp32 = z-depth of the nearest triangle of the mesh (vertices [V,3] fp32,
+ * triangles [T,3] int32, device) seen through pixel (u, v) of view k (w2c [K,16] fp32 row-major device = the
+ * extrinsic np.linalg.inv(c2w); camera looks down +z, y down), 0 where nothing is hit within
+ * [z_near, z_far].  workspace: nsb_mesh_depth_workspace_bytes(T, K) bytes (may be NULL: slower on meshes
+ * with triangles that cover many pixels).  The intersection arithmetic is fixed operation by operation
+ * (oracle/mesh_oracle.py), the images agree with the oracle bit for bit. */
+int64_t nsb_mesh_depth_workspace_bytes(int64_t n_triangles, int K);
+int nsb_mesh_depth(const float* vertices, int64_t n_vertices, const int32_t* triangles, int64_t n_triangles,
+                   const float* w2c, int K, int H, int W, float fx, float fy, float cx, float cy, float z_near,
+                   float z_far, void* workspace, int64_t workspace_bytes, float* depth, void* stream);
+
 /* ---- gradient exchange of the sharded mapping step over NVLink peer memory -------
  * The reference maps on one GPU; its loss is a plain sum over rays (src/Mapper.py:605-612), so ranks
  * that render disjoint ray slices hold partial gradients that add.  The gradient bucket of every rank

@@ -131,6 +131,9 @@ _SIGS = {
                                    C.c_double, C.c_double, C.c_double, C.c_double, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_keyframe_overlap": (C.c_int, [c_ptr, c_ptr, c_ptr, C.c_int64, C.c_int, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int,
                                        C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, c_ptr, c_ptr]),
+    "nsb_mesh_depth_workspace_bytes": (C.c_int64, [C.c_int64, C.c_int]),
+    "nsb_mesh_depth": (C.c_int, [c_ptr, C.c_int64, c_ptr, C.c_int64, c_ptr, C.c_int, C.c_int, C.c_int, C.c_float,
+                                 C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, C.c_int64, c_ptr, c_ptr]),
     "nsb_exchange_signal_words": (C.c_int64, []),
     "nsb_bucket_allreduce": (C.c_int, [C.POINTER(NsbPeers), C.c_int64, C.c_int64, c_ptr]),
     "nsb_exchange_slice": (C.c_int64, [C.c_int, C.c_int, C.c_int64, c_ptr]),
