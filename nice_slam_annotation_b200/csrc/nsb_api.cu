@@ -26,6 +26,21 @@ int check_launch(const char* what) {
     return 0;
 }
 
+static thread_local bool g_pdl_next = false;
+static int g_pdl_enabled = -1;
+void pdl_allow_next(bool on) {
+    if (g_pdl_enabled < 0) {
+        const char* e = getenv("NSB_PDL");
+        g_pdl_enabled = (e && e[0] == '0') ? 0 : 1;
+    }
+    g_pdl_next = on && g_pdl_enabled == 1;
+}
+bool pdl_take() {
+    const bool v = g_pdl_next;
+    g_pdl_next = false;
+    return v;
+}
+
 // ---- optional device-side timing of the two decoder kernels (bench.py roofline) ---------------
 constexpr int TIMING_MAX = 4096;
 static bool g_timing = false;

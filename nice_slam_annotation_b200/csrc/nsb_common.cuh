@@ -15,6 +15,16 @@ constexpr unsigned FULL = 0xffffffffu;
 // ---- host-side error plumbing (nsb_api.cu) -------------------------------------------
 int set_error(int code, const char* fmt, ...);
 int check_launch(const char* what);
+// Programmatic dependent launch: nsb_render_forward / nsb_render_backward know that the kernel just before a
+// decoder kernel (k_sample_z, k_composite_*) does not produce what the decoder kernel's prologue reads (packed
+// weights, tile counters), so they allow the next decoder launch to start while that kernel drains; the
+// decoder kernels call pdl_wait() before they touch anything else.  Other callers get ordinary launches.
+void pdl_allow_next(bool on);
+bool pdl_take();
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
 void timing_mark(int which, int phase, cudaStream_t s);   // which: 0 decoder forward, 1 decoder backward, 2 weight gradients, 3 gradient exchange, 4 depth max over peers
 
 // ---- points -------------------------------------------------------------------------

@@ -152,6 +152,7 @@ __global__ void k_composite_bwd(CompParams c, const double* __restrict__ depth,
                                 const double* __restrict__ g_depth, const double* __restrict__ g_var,
                                 const float* __restrict__ g_rgb, float* __restrict__ d_raw,
                                 float* __restrict__ d_dnorm) {
+    pdl_launch_dependents();     // the backward decoder kernel may stage its weights meanwhile
     const int lane = threadIdx.x & 31;
     const long long ray = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
     if (ray >= c.q.N) return;
@@ -254,6 +255,7 @@ __global__ void __launch_bounds__(128) k_composite_map(CompParams c, const float
                                                         float* __restrict__ rgb_out, float* __restrict__ d_raw,
                                                         double* __restrict__ partials, unsigned* __restrict__ ticket,
                                                         double* __restrict__ loss) {
+    pdl_launch_dependents();     // the backward decoder kernel may stage its weights meanwhile
     __shared__ double s_part[4];
     __shared__ bool s_last;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

@@ -554,6 +554,7 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, int
     using C = DecCfg<KIND>;
     using O = Off<KIND>;
     stage_weights(sm, T.packed, C::TOTAL);
+    pdl_wait();                 // everything below reads what the kernel before this one wrote
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, t = lane & 3;
     float* es = sm + C::TOTAL + warp * E_BUF;
     const long long ntiles = (P.pts.P + 15) / 16;
@@ -1293,8 +1294,17 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
         if (need > tc_smem) tc_smem = need;
     }
     timing_mark(0, 0, (cudaStream_t)stream);
-    if (tc) k_decoders_forward_tc<<<ctas, TC_THREADS, tc_smem * 4, (cudaStream_t)stream>>>(sp);
-    else k_decoders_forward<<<ctas, THREADS, max_blob(sp, false) * 4, (cudaStream_t)stream>>>(sp);
+    const bool pdl = pdl_take();
+    if (tc) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(TC_THREADS);
+        cfg.dynamicSmemBytes = (size_t)tc_smem * 4; cfg.stream = (cudaStream_t)stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+        cudaLaunchKernelEx(&cfg, k_decoders_forward_tc, sp);
+    } else k_decoders_forward<<<ctas, THREADS, max_blob(sp, false) * 4, (cudaStream_t)stream>>>(sp);
     timing_mark(0, 1, (cudaStream_t)stream);
 #ifdef NSB_TC_PROFILE
     if (getenv("NSB_TC_PROFILE_PRINT")) {
@@ -1380,12 +1390,22 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
     cudaMemsetAsync(bprof_dev, 0, 72 * sizeof(long long), (cudaStream_t)stream);
     sp.prof = bprof_dev;
 #endif
+    const bool pdl = pdl_take();
     for (long long t0 = 0; t0 < ntiles; t0 += chunk) {
         sp.tile_begin = t0;
         sp.tile_end = t0 + chunk < ntiles ? t0 + chunk : ntiles;
         sp.ctr = next_counters();
         timing_mark(1, 0, (cudaStream_t)stream);
-        k_decoders_backward<<<ctas, THREADS, smem, (cudaStream_t)stream>>>(sp);
+        {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(THREADS);
+            cfg.dynamicSmemBytes = (size_t)smem; cfg.stream = (cudaStream_t)stream;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = at; cfg.numAttrs = (pdl && t0 == 0) ? 1 : 0;
+            cudaLaunchKernelEx(&cfg, k_decoders_backward, sp);
+        }
         timing_mark(1, 1, (cudaStream_t)stream);
         if (int rc = check_launch("k_decoders_backward")) return rc;
 #ifdef NSB_TC_PROFILE

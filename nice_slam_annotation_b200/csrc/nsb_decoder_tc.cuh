@@ -223,6 +223,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
+    pdl_wait();                 // weights, TMEM and counters are set up; the points come from the kernel before
     const uint32_t tbase = tmem_slot;
     const uint32_t lane_base = tc::tmem_addr(tbase, 32 * quad, 0);
     const float4* Bv = reinterpret_cast<const float4*>(sm + S::S_BV);

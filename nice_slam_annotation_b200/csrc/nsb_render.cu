@@ -270,6 +270,7 @@ extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
     pts.relu_masks = w.relu;
     float *o0, *o1, *rgb;
     stage_planes(r->stage, w, o0, o1, rgb);
+    pdl_allow_next(true);         // the decoder kernel's prologue may overlap k_sample_z
     if (int rc = nsb_decoders_forward(&pts, &r->scene, r->stage, o0, o1, rgb, stream)) return rc;
     if (fused_loss) return 0;     // compositing, loss and adjoint run as one kernel in nsb_render_backward
     return nsb_composite_forward(&pts, b6, r->stage, r->occupancy, o0, o1, rgb, r->depth, r->var, r->color,
@@ -297,9 +298,11 @@ extern "C" int nsb_render_backward(const NsbRenderCall* r, void* stream) {
                                            w.partials, w.ticket, r->loss, stream)) return rc;
     } else if (int rc = nsb_composite_backward(&pts, b6, r->stage, r->occupancy, o0, o1, rgb, r->depth, r->g_depth,
                                                r->g_var, r->g_color, w.d_raw, dn, stream)) return rc;
+    pdl_allow_next(true);         // ... and the backward kernel's weight staging the compositing kernel
     if (r->flags)
         if (int rc = nsb_decoders_backward(&pts, &r->scene, r->stage, w.d_raw, r->flags, r->dweight_mask,
                                            r->d_weight, w.d_point, r->scratch, r->scratch_bytes, stream)) return rc;
+    pdl_allow_next(false);
     if (want_rays) {
         if (!r->g_rays_o || !r->g_rays_d) return set_error(NSB_EINVAL, "ray gradient outputs are NULL");
         const int ndec = r->stage == NSB_STAGE_COLOR ? 3 : (r->stage == NSB_STAGE_FINE ? 2 : 1);

@@ -182,6 +182,7 @@ __global__ void __launch_bounds__(256) k_sample_z(PointsDev q, const float* __re
     extern __shared__ double sh_z[];
     __shared__ float s_part[8];
     __shared__ float s_dmax;
+    pdl_launch_dependents();     // a decoder kernel launched with the PDL attribute may set itself up meanwhile
     const int S = Ns + Nf;
     if (gt_depth && !depth_max) {
         // small batches: every block reduces the batch depth max itself (k_depth_max's rule: kept rays,
