@@ -945,13 +945,15 @@ __global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
         const int u = warp * upw + k;
         if (k < upw && u < nunit) {
             const int* U = s_unit + u * DW_UNIT_INTS;
+            // table entries in registers: the atomics below would otherwise force a reload per element
+            const int out_off = U[6], ld_row = U[7], ld_col = U[8], rows_valid = U[9], cols_valid = U[10];
 #pragma unroll
             for (int m = 0; m < 2; ++m)
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int row = 16 * m + g + 8 * (q >> 1), col = 2 * t + (q & 1);
-                    if (row < U[9] && col < U[10] && acc[k][m][q] != 0.f)
-                        atomicAdd(P.dflat + U[6] + row * U[7] + col * U[8], acc[k][m][q]);
+                    if (row < rows_valid && col < cols_valid && acc[k][m][q] != 0.f)
+                        atomicAdd(P.dflat + out_off + row * ld_row + col * ld_col, acc[k][m][q]);
                 }
         }
     }
