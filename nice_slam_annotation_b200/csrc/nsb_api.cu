@@ -28,13 +28,14 @@ int check_launch(const char* what) {
 
 static thread_local bool g_pdl_next = false;
 static int g_pdl_enabled = -1;
-void pdl_allow_next(bool on) {
+bool pdl_enabled() {
     if (g_pdl_enabled < 0) {
         const char* e = getenv("NSB_PDL");
         g_pdl_enabled = (e && e[0] == '0') ? 0 : 1;
     }
-    g_pdl_next = on && g_pdl_enabled == 1;
+    return g_pdl_enabled == 1;
 }
+void pdl_allow_next(bool on) { g_pdl_next = on && pdl_enabled(); }
 bool pdl_take() {
     const bool v = g_pdl_next;
     g_pdl_next = false;
@@ -225,6 +226,8 @@ static void build_table(int32_t* tab) {
 
 __global__ void k_pack(const float* const* __restrict__ ptrs, const int32_t* __restrict__ table,
                        float* __restrict__ out, int n) {
+    pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     int32_t e = table[i];
@@ -343,6 +346,6 @@ extern "C" int nsb_pack_weights(int kind, const float* const* param_ptrs, const 
     if (!param_ptrs || !table || !packed) return set_error(NSB_EINVAL, "null argument");
     int64_t n = nsb_packed_numel(kind);
     if (n < 0) return (int)n;
-    k_pack<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(param_ptrs, table, packed, (int)n);
+    launch_pdl(k_pack, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, (cudaStream_t)stream, param_ptrs, table, packed, (int)n);
     return check_launch("k_pack");
 }

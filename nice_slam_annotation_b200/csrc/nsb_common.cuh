@@ -21,9 +21,26 @@ int check_launch(const char* what);
 // decoder kernels call pdl_wait() before they touch anything else.  Other callers get ordinary launches.
 void pdl_allow_next(bool on);
 bool pdl_take();
+bool pdl_enabled();              // NSB_PDL=0 turns every programmatic launch into an ordinary one
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
+#ifdef __CUDACC__
+// Launch of a kernel that calls pdl_wait() before its first memory access: it may be scheduled while the kernel
+// before it in the stream drains (that kernel calls pdl_launch_dependents() first thing), which hides the
+// launch latency between the many short kernels of a step; the order of all memory accesses is the stream's.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 #endif
 void timing_mark(int which, int phase, cudaStream_t s);   // which: 0 decoder forward, 1 decoder backward, 2 weight gradients, 3 gradient exchange, 4 depth max over peers
 

@@ -102,6 +102,8 @@ __device__ __forceinline__ float ray_dnorm(const PointsDev& q, long long ray) {
 
 __global__ void k_composite_fwd(CompParams c, double* __restrict__ depth, double* __restrict__ var,
                                 float* __restrict__ rgb_out, float* __restrict__ weights) {
+    pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     const int lane = threadIdx.x & 31;
     const long long ray = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
     if (ray >= c.q.N) return;
@@ -153,6 +155,7 @@ __global__ void k_composite_bwd(CompParams c, const double* __restrict__ depth,
                                 const float* __restrict__ g_rgb, float* __restrict__ d_raw,
                                 float* __restrict__ d_dnorm) {
     pdl_launch_dependents();     // the backward decoder kernel may stage its weights meanwhile
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     const int lane = threadIdx.x & 31;
     const long long ray = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
     if (ray >= c.q.N) return;
@@ -256,6 +259,7 @@ __global__ void __launch_bounds__(128) k_composite_map(CompParams c, const float
                                                         double* __restrict__ partials, unsigned* __restrict__ ticket,
                                                         double* __restrict__ loss) {
     pdl_launch_dependents();     // the backward decoder kernel may stage its weights meanwhile
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     __shared__ double s_part[4];
     __shared__ bool s_last;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -397,6 +401,8 @@ __global__ void k_assemble_raw(CompParams c, float* __restrict__ raw, uint8_t* _
 __global__ void k_ray_grad_reduce(PointsDev q, const float* __restrict__ d_point, int ndec,
                                   const float* __restrict__ d_dnorm, float* __restrict__ g_o,
                                   float* __restrict__ g_d) {
+    pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     const int lane = threadIdx.x & 31;
     const long long ray = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
     if (ray >= q.N) return;
@@ -430,6 +436,8 @@ __global__ void k_pose_grad(const float* __restrict__ g_o, const float* __restri
                             const int64_t* __restrict__ indices, const uint8_t* __restrict__ keep,
                             long long n, int H0, int W0, int wc, float fx, float fy, float cx,
                             float cy, const float* __restrict__ cam7, float* __restrict__ d_cam7) {
+    pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     __shared__ double red[12][32];
     double acc[12];
     for (int k = 0; k < 12; ++k) acc[k] = 0.0;
@@ -516,7 +524,7 @@ extern "C" int nsb_composite_forward(const NsbPoints* rays, const double* bound6
     if (!depth || !var || !rgb) return set_error(NSB_EINVAL, "null output");
     if (c.q.N <= 0) return 0;
     const int bs = 128;
-    k_composite_fwd<<<(unsigned)((c.q.N * 32 + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(c, depth, var, rgb, weights);
+    launch_pdl(k_composite_fwd, dim3((unsigned)((c.q.N * 32 + bs - 1) / bs)), dim3(bs), 0, (cudaStream_t)stream, c, depth, var, rgb, weights);
     return check_launch("k_composite_fwd");
 }
 
@@ -530,7 +538,7 @@ extern "C" int nsb_composite_backward(const NsbPoints* rays, const double* bound
     if (!depth || !d_raw) return set_error(NSB_EINVAL, "null argument");
     if (c.q.N <= 0) return 0;
     const int bs = 128;
-    k_composite_bwd<<<(unsigned)((c.q.N * 32 + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(
+    launch_pdl(k_composite_bwd, dim3((unsigned)((c.q.N * 32 + bs - 1) / bs)), dim3(bs), 0, (cudaStream_t)stream, 
         c, depth, g_depth, g_var, g_rgb, d_raw, d_rays_d_norm);
     return check_launch("k_composite_bwd");
 }
@@ -554,7 +562,7 @@ extern "C" int nsb_ray_grad_reduce(const NsbPoints* rays, const float* d_point, 
     if (!q.z) return set_error(NSB_EINVAL, "ray mode required");
     if (q.N <= 0) return 0;
     const int bs = 128;
-    k_ray_grad_reduce<<<(unsigned)((q.N * 32 + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(
+    launch_pdl(k_ray_grad_reduce, dim3((unsigned)((q.N * 32 + bs - 1) / bs)), dim3(bs), 0, (cudaStream_t)stream, 
         q, d_point, ndec, d_rays_d_norm, g_rays_o, g_rays_d);
     return check_launch("k_ray_grad_reduce");
 }
@@ -563,7 +571,7 @@ extern "C" int nsb_pose_grad(const float* g_rays_o, const float* g_rays_d, const
                              const uint8_t* keep, int64_t n, int H0, int W0, int Wc, float fx, float fy,
                              float cx, float cy, const float* cam7, float* d_cam7, void* stream) {
     if (!g_rays_o || !g_rays_d || !indices || !cam7 || !d_cam7) return set_error(NSB_EINVAL, "null argument");
-    k_pose_grad<<<1, 1024, 0, (cudaStream_t)stream>>>(g_rays_o, g_rays_d, indices, keep, n, H0, W0, Wc, fx, fy,
+    launch_pdl(k_pose_grad, dim3(1), dim3(1024), 0, (cudaStream_t)stream, g_rays_o, g_rays_d, indices, keep, n, H0, W0, Wc, fx, fy,
                                                      cx, cy, cam7, d_cam7);
     return check_launch("k_pose_grad");
 }
@@ -581,7 +589,7 @@ extern "C" int nsb_composite_mapping(const NsbPoints* rays, const double* bound6
         return set_error(NSB_EINVAL, "null argument");
     if (c.q.N <= 0) return 0;
     const int bs = 128;
-    k_composite_map<<<(unsigned)((c.q.N * 32 + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(
+    launch_pdl(k_composite_map, dim3((unsigned)((c.q.N * 32 + bs - 1) / bs)), dim3(bs), 0, (cudaStream_t)stream, 
         c, gt_depth, gt_color, keep, w_color, use_color, depth, var, rgb, d_raw, partials, ticket, loss);
     return check_launch("k_composite_map");
 }

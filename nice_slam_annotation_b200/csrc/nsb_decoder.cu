@@ -740,6 +740,7 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, int
 __global__ void __launch_bounds__(THREADS, 1)
 k_decoders_backward(const __grid_constant__ StageParams P) {
     extern __shared__ __align__(16) float sm[];
+    pdl_launch_dependents();     // k_dweight / k_ray_grad_reduce may be scheduled as CTAs of this kernel retire
     int k = 0;
     while (k + 1 < P.ntask && (int)blockIdx.x >= P.task[k + 1].cta_begin) ++k;
     const DecTask& T = P.task[k];
@@ -815,6 +816,7 @@ __device__ __forceinline__ void cp_async16(float* smem_dst, const float* gmem_sr
 
 __global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
     extern __shared__ __align__(16) float sm[];
+    pdl_launch_dependents();
     const DwTables& TB = *P.tab;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
     int* s_unit = reinterpret_cast<int*>(sm);
@@ -827,6 +829,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
         s_unit[i] = reinterpret_cast<const int*>(TB.unit)[i];
     DwBias mybias{0, 0, 0, 0};
     if ((int)threadIdx.x < nbias) mybias = TB.bias[threadIdx.x];
+    pdl_wait();                  // the tables are constants; flags and records come from the backward kernel
     // Balanced shares of the LIVE tiles: every CTA scans all flags (a few KB), ranks the live
     // tiles globally and keeps those ranked [b L / G, (b + 1) L / G) -- live tiles cluster along
     // rays, so equal index ranges left some CTAs with three times the mean (r01 profile).
@@ -1434,7 +1437,7 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
             const long long need = (dp.ntiles + DW_LIVE_MAX - 2) / (DW_LIVE_MAX - 1);
             if (grid < need) grid = need;
             timing_mark(2, 0, (cudaStream_t)stream);
-            k_dweight<<<(int)grid, THREADS, (DW_HEAD_FLOATS + 2 * g_dw_host[T.kind].rec) * 4, (cudaStream_t)stream>>>(dp);
+            launch_pdl(k_dweight, dim3((unsigned)grid), dim3(THREADS), (size_t)(DW_HEAD_FLOATS + 2 * g_dw_host[T.kind].rec) * 4, (cudaStream_t)stream, dp);
             timing_mark(2, 1, (cudaStream_t)stream);
             if (int rc = check_launch("k_dweight")) return rc;
         }

@@ -449,6 +449,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_decoders_forward_tc(const __grid_constant__ StageParams P) {
     extern __shared__ __align__(16) float sm[];
+    pdl_launch_dependents();     // the compositing kernel may be scheduled as CTAs of this kernel retire
     int k = 0;
     while (k + 1 < P.ntask && (int)blockIdx.x >= P.task[k + 1].cta_begin) ++k;
     const DecTask& T = P.task[k];

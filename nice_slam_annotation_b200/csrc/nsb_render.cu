@@ -73,6 +73,8 @@ __global__ void k_mapping_loss(const double* __restrict__ depth, const float* __
                                const uint8_t* __restrict__ keep, long long N, float w_color, int use_color,
                                double* __restrict__ loss, double* __restrict__ g_depth,
                                float* __restrict__ g_color) {
+    pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     __shared__ double part[32];
     double acc = 0.0;
     for (long long i = threadIdx.x; i < N; i += blockDim.x) {
@@ -115,6 +117,8 @@ __global__ void k_mapping_loss(const double* __restrict__ depth, const float* __
 __global__ void k_residual_median(const double* __restrict__ depth, const double* __restrict__ var,
                                   const float* __restrict__ gd, const uint8_t* __restrict__ keep, int N,
                                   double* __restrict__ out) {
+    pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     extern __shared__ double sh[];      // N doubles
     __shared__ int s_live;
     if (threadIdx.x == 0) s_live = 0;
@@ -160,6 +164,8 @@ __global__ void k_tracking_loss(const double* __restrict__ depth, const double* 
                                 int npow2, float w_color, int use_color, int handle_dynamic,
                                 const double* median, double* __restrict__ loss,
                                 double* __restrict__ g_depth, float* __restrict__ g_color) {
+    pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     extern __shared__ double sh[];      // npow2 doubles
     __shared__ double part[32];
     __shared__ int s_live;
@@ -316,7 +322,7 @@ extern "C" int nsb_mapping_loss(const double* depth, const float* color, const f
                                 int use_color, double* loss, double* g_depth, float* g_color, void* stream) {
     if (!depth || !color || !gt_depth || !gt_color || !loss || !g_depth || !g_color)
         return set_error(NSB_EINVAL, "null argument");
-    k_mapping_loss<<<1, 1024, 0, (cudaStream_t)stream>>>(depth, color, gt_depth, gt_color, keep, N, w_color,
+    launch_pdl(k_mapping_loss, dim3(1), dim3(1024), 0, (cudaStream_t)stream, depth, color, gt_depth, gt_color, keep, N, w_color,
                                                        use_color, loss, g_depth, g_color);
     return check_launch("k_mapping_loss");
 }
@@ -326,6 +332,8 @@ extern "C" int nsb_mapping_loss(const double* depth, const float* color, const f
 __global__ void k_cam_adam(float* cam, const float* d_cam, float* m, float* v, int* step, float lr_q, float lr_t,
                            float beta1, float beta2, float eps, const double* loss, double* best_loss,
                            float* best_cam) {
+    pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     const int i = threadIdx.x;
     const int t = step[0] + 1;
     __syncwarp();
@@ -355,7 +363,7 @@ extern "C" int nsb_cam_adam(float* cam, const float* d_cam, float* m, float* v, 
                             float* best_cam, void* stream) {
     if (!cam || !d_cam || !m || !v || !step) return set_error(NSB_EINVAL, "null argument");
     if (best_loss && (!loss || !best_cam)) return set_error(NSB_EINVAL, "best_loss needs loss and best_cam");
-    k_cam_adam<<<1, 32, 0, (cudaStream_t)stream>>>(cam, d_cam, m, v, step, lr_q, lr_t, beta1, beta2, eps, loss,
+    launch_pdl(k_cam_adam, dim3(1), dim3(32), 0, (cudaStream_t)stream, cam, d_cam, m, v, step, lr_q, lr_t, beta1, beta2, eps, loss,
                                                    best_loss, best_cam);
     return check_launch("k_cam_adam");
 }
@@ -446,12 +454,12 @@ extern "C" int nsb_tracking_loss(const double* depth, const double* var, const f
     if (handle_dynamic && N > 0 && N <= 4096) {
         // loss[0] carries the median between the two kernels; the second overwrites it with the loss
         const int warps = 32;
-        k_residual_median<<<(unsigned)((N + warps - 1) / warps), warps * 32, N * 8, (cudaStream_t)stream>>>(
+        launch_pdl(k_residual_median, dim3((unsigned)((N + warps - 1) / warps)), dim3(warps * 32), (size_t)N * 8, (cudaStream_t)stream,
             depth, var, gt_depth, keep, (int)N, loss);
         if (int rc = check_launch("k_residual_median")) return rc;
         median = loss;
     }
-    k_tracking_loss<<<1, 1024, median ? 8 : npow2 * 8, (cudaStream_t)stream>>>(
+    launch_pdl(k_tracking_loss, dim3(1), dim3(1024), (size_t)(median ? 8 : npow2 * 8), (cudaStream_t)stream,
         depth, var, color, gt_depth, gt_color, keep, N, median ? 1 : npow2, w_color, use_color, handle_dynamic,
         median, loss, g_depth, g_color);
     return check_launch("k_tracking_loss");

@@ -71,6 +71,8 @@ __global__ void k_sample_rays(const int64_t* __restrict__ indices, long long n, 
                               float* __restrict__ rays_o, float* __restrict__ rays_d,
                               float* __restrict__ gt_depth, float* __restrict__ gt_color,
                               uint8_t* __restrict__ keep) {
+    pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (r >= n) return;
     long long idx = indices[r];
@@ -183,6 +185,7 @@ __global__ void __launch_bounds__(256) k_sample_z(PointsDev q, const float* __re
     __shared__ float s_part[8];
     __shared__ float s_dmax;
     pdl_launch_dependents();     // a decoder kernel launched with the PDL attribute may set itself up meanwhile
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     const int S = Ns + Nf;
     if (gt_depth && !depth_max) {
         // small batches: every block reduces the batch depth max itself (k_depth_max's rule: kept rays,
@@ -374,7 +377,7 @@ extern "C" int nsb_sample_rays(const int64_t* indices, int64_t n, int H0, int H1
     BoundDev b{};
     if (bound6_host) b = to_bound(bound6_host);
     CamDev cam{fx, fy, cx, cy};
-    k_sample_rays<<<blocks_for(n, 128), 128, 0, (cudaStream_t)stream>>>(
+    launch_pdl(k_sample_rays, dim3(blocks_for(n, 128)), dim3(128), 0, (cudaStream_t)stream,
         indices, n, H0, W0, H1 - H0, W1 - W0, W_img, cam, c2w, cam7, depth_img, color_img, color_is_f64, b,
         bound6_host != nullptr, rays_o, rays_d, gt_depth, gt_color, keep);
     return check_launch("k_sample_rays");
@@ -396,6 +399,8 @@ __global__ void k_load_batch(const float* __restrict__ ro, const float* __restri
                              const float* __restrict__ gc, const uint8_t* __restrict__ keep, long long n, long long N,
                              float* __restrict__ d_ro, float* __restrict__ d_rd, float* __restrict__ d_gd,
                              float* __restrict__ d_gc, uint8_t* __restrict__ d_keep) {
+    pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (i >= N) return;
     const bool live = i < n;
@@ -416,6 +421,8 @@ __global__ void k_load_batch(const float* __restrict__ ro, const float* __restri
 __global__ void k_load_batch_packed(const float* __restrict__ src, const uint8_t* __restrict__ keep, long long n,
                                     long long N, float* __restrict__ d_ro, float* __restrict__ d_rd,
                                     float* __restrict__ d_gd, float* __restrict__ d_gc, uint8_t* __restrict__ d_keep) {
+    pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
+    pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (i >= N) return;
     const bool live = i < n;
@@ -436,7 +443,7 @@ int launch_sample_z(const PointsDev& q, const float* gt_depth, const BoundDev& b
     const int S = Ns + Nf;
     const int rpb = S >= 256 ? 1 : 256 / S;
     const int threads = (rpb * S + 31) / 32 * 32;             // whole warps (the in-block depth max shuffles)
-    k_sample_z<<<blocks_for(q.N, rpb), threads, threads * sizeof(double), (cudaStream_t)stream>>>(
+    launch_pdl(k_sample_z, dim3(blocks_for(q.N, rpb)), dim3(threads), threads * sizeof(double), (cudaStream_t)stream,
         q, gt_depth, bound, Ns, Nf, lindisp, t_uniform, t_surface, u, depth_max, z_out, rpb, zero_word, keep);
     return check_launch("k_sample_z");
 }
@@ -505,7 +512,7 @@ extern "C" int nsb_load_batch(const float* rays_o, const float* rays_d, const fl
     if (n < 0 || n > N) return set_error(NSB_EINVAL, "batch of %lld rays exceeds the capacity %lld", (long long)n, (long long)N);
     if (rays_o && (!rays_d || !gt_depth || !gt_color)) return set_error(NSB_EINVAL, "null argument");
     if (N <= 0) return 0;
-    k_load_batch<<<blocks_for(N, 256), 256, 0, (cudaStream_t)stream>>>(rays_o, rays_d, gt_depth, gt_color, keep, n, N,
+    launch_pdl(k_load_batch, dim3(blocks_for(N, 256)), dim3(256), 0, (cudaStream_t)stream, rays_o, rays_d, gt_depth, gt_color, keep, n, N,
                                                                       dst_rays_o, dst_rays_d, dst_gt_depth, dst_gt_color,
                                                                       dst_keep);
     return check_launch("k_load_batch");
@@ -518,7 +525,7 @@ extern "C" int nsb_load_batch_packed(const float* packed, const uint8_t* keep, i
     if (n < 0 || n > N) return set_error(NSB_EINVAL, "batch of %lld rays exceeds the capacity %lld", (long long)n, (long long)N);
     if (n > 0 && !packed) return set_error(NSB_EINVAL, "null argument");
     if (N <= 0) return 0;
-    k_load_batch_packed<<<blocks_for(N, 256), 256, 0, (cudaStream_t)stream>>>(packed, keep, n, N, dst_rays_o, dst_rays_d,
+    launch_pdl(k_load_batch_packed, dim3(blocks_for(N, 256)), dim3(256), 0, (cudaStream_t)stream, packed, keep, n, N, dst_rays_o, dst_rays_d,
                                                                              dst_gt_depth, dst_gt_color, dst_keep);
     return check_launch("k_load_batch_packed");
 }
