@@ -182,8 +182,9 @@ def run_ours(args):
     step = FusedStep(ns.renderer, dec, grids, STAGE, args.rays, peers=peers, **step_kw)
     if peers is not None and step.bucket.sparse:
         exchange = ("nsb_bucket_allreduce_sparse: one kernel over symmetric memory (touched-line words pushed to the "
-                    "slice owner, only voxel lines some rank touched are reduced and stored back, peer ld / st over "
-                    "NVLink), inside the step's CUDA graph; depth max over ranks: nsb_depth_max_peers in the same graph")
+                    "slice owner, only voxel lines some rank touched are reduced and stored back, "
+                    + ("NVLS multimem.ld_reduce / multimem.st" if peers.multicast else "peer ld / st over NVLink")
+                    + "), inside the step's CUDA graph; depth max over ranks: nsb_depth_max_peers in the same graph")
 
     def step_device(b):
         step.load(*b)

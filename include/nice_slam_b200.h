@@ -417,7 +417,7 @@ typedef struct NsbPeers {
     float* param_multicast;
     uint32_t* signal[NSB_MAX_PEERS];
     int32_t* error;
-    float* scalar[NSB_MAX_PEERS];     /* nsb_depth_max_peers only: one symmetric float per rank */
+    float* scalar[NSB_MAX_PEERS];     /* nsb_depth_max_peers only: a symmetric, zero-initialised pad of 64 words per rank */
     uint32_t* touched[NSB_MAX_PEERS]; /* nsb_bucket_allreduce_sparse only: per-rank symmetric scratch of
                                        * nsb_exchange_touched_words(bucket floats) words, mapped like bucket */
 } NsbPeers;
@@ -434,7 +434,9 @@ int nsb_bucket_allreduce(const NsbPeers* peers, int64_t offset, int64_t n, void*
  * on every rank are left alone (they stay zero).  offset: multiple of 32 floats; buffers 128-byte aligned. */
 int64_t nsb_exchange_touched_words(int64_t n);
 /* nsb_depth_max over the kept rays of ALL ranks (the render's one batch-global scalar, Renderer.py:157),
- * through peers->scalar: what a rank that renders a shard passes as NsbRenderCall.depth_max. */
+ * through peers->scalar: what a rank that renders a shard passes as NsbRenderCall.depth_max.  Every rank posts
+ * (call number, local max) into its slot of every rank's pad and waits for the peers' values of the same call:
+ * all ranks must make the same sequence of calls. */
 int nsb_depth_max_peers(const NsbPeers* peers, const float* gt_depth, const uint8_t* keep, int64_t N,
                         float* out, void* stream);
 int nsb_bucket_allreduce_sparse(const NsbPeers* peers, int64_t offset, int64_t n, void* stream);

@@ -42,16 +42,6 @@ struct PeersDev {
     int* error;
 };
 
-__device__ __forceinline__ unsigned cas_release_sys(unsigned* p, unsigned cmp, unsigned val) {
-    unsigned old;
-    asm volatile("atom.global.release.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(p), "r"(cmp), "r"(val) : "memory");
-    return old;
-}
-__device__ __forceinline__ unsigned cas_acquire_sys(unsigned* p, unsigned cmp, unsigned val) {
-    unsigned old;
-    asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(p), "r"(cmp), "r"(val) : "memory");
-    return old;
-}
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -60,16 +50,30 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 
 // CTA-wise barrier over all ranks: thread t < world talks to rank t.  `slot` selects this CTA's
 // words of the pad for this phase: word slot + s of rank d's pad is written by rank s only.
+// Epoch flags: the n-th barrier on a slot posts the number n into the peer's word (a store, no NVLink round
+// trip) and spins on its own word until the peer's n has arrived; the count of what this rank has sent lives
+// in the second half of its own pad.  Every rank runs the same sequence of barriers on a slot.
+constexpr int SIGNAL_WORDS = 2 * X_MAX_BLOCKS * NSB_MAX_PEERS;
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void peer_barrier(const PeersDev& g, int slot) {
     __syncthreads();
     const int t = threadIdx.x;
     if (t < g.world && t != g.rank) {
         const unsigned long long t0 = globaltimer_ns();
         bool ok = true;
+        unsigned* sent = g.signal[g.rank] + SIGNAL_WORDS + slot + t;
+        const unsigned e = *sent + 1u;
+        *sent = e;
         __threadfence_system();
-        while (cas_release_sys(g.signal[t] + slot + g.rank, 0u, 1u) != 0u)
-            if (globaltimer_ns() - t0 > 20000000000ull) { ok = false; break; }
-        while (ok && cas_acquire_sys(g.signal[g.rank] + slot + t, 1u, 0u) != 1u)
+        st_release_sys(g.signal[t] + slot + g.rank, e);
+        while ((int)(ld_acquire_sys(g.signal[g.rank] + slot + t) - e) < 0)
             if (globaltimer_ns() - t0 > 20000000000ull) { ok = false; break; }
         __threadfence_system();
         if (!ok && g.error) *g.error = 1;
@@ -281,9 +285,15 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange_sparse(const __grid_cons
 // one batch-global scalar of the render.  One CTA: local max -> own symmetric slot -> barrier -> max of
 // every rank's slot -> barrier (slots are free again).  NaN propagates like torch.max.
 __device__ __forceinline__ float nanmax(float a, float b) { return (b > a || b != b) ? b : a; }
+// Batch depth max over all ranks, push model: every rank posts (step number, local max) as ONE 8-byte store
+// into its slot of every rank's scalar pad and spins on its own pad until every peer's value of this step has
+// arrived -- one NVLink one-way latency, no barrier, no remote load.  Slots are double-buffered by the step's
+// parity: a rank cannot be two steps ahead of a peer, it needs that peer's value of every step.
+// pad (64 words per rank): u64 slot[2][NSB_MAX_PEERS] at words 0..31, the step counter at word 40.
 __global__ void __launch_bounds__(1024) k_depth_max_peers(const __grid_constant__ PeersDev g, const float* __restrict__ gt,
                                                            const uint8_t* __restrict__ keep, long long n,
                                                            float* __restrict__ out) {
+    static_assert(NSB_MAX_PEERS <= 8, "scalar pad layout");
     __shared__ float part[32];
     float m = -INFINITY;
     for (long long i = threadIdx.x; i < n; i += blockDim.x)
@@ -291,20 +301,32 @@ __global__ void __launch_bounds__(1024) k_depth_max_peers(const __grid_constant_
     for (int s = 16; s > 0; s >>= 1) m = nanmax(m, __shfl_xor_sync(FULL, m, s));
     if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = m;
     __syncthreads();
-    if (threadIdx.x < 32) {
-        m = threadIdx.x < (blockDim.x >> 5) ? part[threadIdx.x] : -INFINITY;
-        for (int s = 16; s > 0; s >>= 1) m = nanmax(m, __shfl_xor_sync(FULL, m, s));
-        if (threadIdx.x == 0) asm volatile("st.volatile.global.f32 [%0], %1;" :: "l"(g.scalar[g.rank]), "f"(m) : "memory");
+    if (threadIdx.x >= 32) return;
+    m = threadIdx.x < (blockDim.x >> 5) ? part[threadIdx.x] : -INFINITY;
+    for (int s = 16; s > 0; s >>= 1) m = nanmax(m, __shfl_xor_sync(FULL, m, s));
+    unsigned* counter = reinterpret_cast<unsigned*>(g.scalar[g.rank]) + 40;
+    unsigned seq = 0;
+    if (threadIdx.x == 0) { seq = *counter + 1u; *counter = seq; }
+    seq = __shfl_sync(FULL, seq, 0);
+    const int t = threadIdx.x;
+    float v = -INFINITY;
+    if (t < g.world) {
+        const unsigned long long word = ((unsigned long long)seq << 32) | __float_as_uint(m);
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(g.scalar[t]) + (seq & 1u) * NSB_MAX_PEERS + g.rank;
+        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" :: "l"(dst), "l"(word) : "memory");
+        const unsigned long long* src =
+            reinterpret_cast<const unsigned long long*>(g.scalar[g.rank]) + (seq & 1u) * NSB_MAX_PEERS + t;
+        const unsigned long long t0 = globaltimer_ns();
+        unsigned long long got;
+        for (;;) {
+            asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(got) : "l"(src) : "memory");
+            if ((unsigned)(got >> 32) == seq) break;
+            if (globaltimer_ns() - t0 > 20000000000ull) { if (g.error) *g.error = 1; break; }
+        }
+        v = __uint_as_float((unsigned)got);
     }
-    peer_barrier(g, 0);
-    if (threadIdx.x < 32) {
-        float v = -INFINITY;
-        if (threadIdx.x < g.world)
-            asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(g.scalar[threadIdx.x]) : "memory");
-        for (int s = 16; s > 0; s >>= 1) v = nanmax(v, __shfl_xor_sync(FULL, v, s));
-        if (threadIdx.x == 0) out[0] = v;
-    }
-    peer_barrier(g, X_MAX_BLOCKS * NSB_MAX_PEERS);
+    for (int s = 16; s > 0; s >>= 1) v = nanmax(v, __shfl_xor_sync(FULL, v, s));
+    if (t == 0) out[0] = v;
 }
 
 static int blocks_for(long long per) {
@@ -342,7 +364,7 @@ static int to_dev(const NsbPeers* p, PeersDev& g, bool need_param) {
 
 using namespace nsb;
 
-extern "C" int64_t nsb_exchange_signal_words(void) { return 2ll * X_MAX_BLOCKS * NSB_MAX_PEERS; }
+extern "C" int64_t nsb_exchange_signal_words(void) { return 2ll * SIGNAL_WORDS; }
 
 extern "C" int nsb_bucket_allreduce(const NsbPeers* peers, int64_t offset, int64_t n, void* stream) {
     PeersDev g;
