@@ -1052,7 +1052,7 @@ static int g_num_sms = 0;
 static int g_use_tc = 1;         // NSB_TC=0 selects the mma.sync kernels (A/B comparisons)
 static float g_xsaved_cost = 0.62f;  // backward cost of a decoder whose records' X sections the forward deposited: no
                                      // recomputation, but the G sections are still written (NSB_XSAVED_COST)
-static float g_xfwd_cost = 1.5f;     // forward cost of depositing them (NSB_XFWD_COST)
+static float g_xfwd_cost = 1.4f;     // forward cost of depositing them (NSB_XFWD_COST)
 static float g_saved_cost = 0.3f; // backward cost of a decoder that skips the recomputation, relative (NSB_SAVED_COST; swept on B200, r01)
 static bool g_attr_done = false;
 constexpr int CTR_SLOTS = 256;                   // launches in flight before a counter slot is reused
@@ -1139,7 +1139,7 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
     // decoder pays a second feature pass
     if (!bwd && g_use_tc)
         for (int i = 0; i < n; ++i)
-            cost[i] = kinds[i] == KIND_MIDDLE ? 15.f : (kinds[i] == KIND_FINE ? 23.5f : (kinds[i] == KIND_COLOR ? 16.5f : cost[i]));
+            cost[i] = kinds[i] == KIND_MIDDLE ? 15.f : (kinds[i] == KIND_FINE ? 21.5f : (kinds[i] == KIND_COLOR ? 16.f : cost[i]));
     if (!bwd && g_use_tc)                      // forward that also deposits the X sections of the d(W) records
         for (int i = 0; i < n; ++i)
             if (x_mask & (1u << kinds[i])) cost[i] *= g_xfwd_cost;
@@ -1172,6 +1172,41 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
         int best = 0;
         for (int i = 1; i < n; ++i) if (frac[i] > frac[best]) best = i;
         share_of[best]++; frac[best] = -1.f; used++;
+    }
+    // tcgen05 forward: a CTA runs whole 128-point tiles, and at 1000 rays a decoder has only 375 of them, 6-11 per
+    // CTA -- the kernel lasts max_i ceil(tiles / share_i) * cost_i, which the proportional split misses by up
+    // to a tile (measured: 35/55/58 CTAs 115 us, 38/54/56 CTAs 109 us).  Exact search over the splits, cached.
+    if (!bwd && g_use_tc && n >= 2 && !getenv("NSB_FWD_SHARES")) {
+        struct Key { long long tiles; int n, sms; float c[3]; int share[3]; };
+        static thread_local Key cache[8];
+        static thread_local int cache_next = 0;
+        const long long t128 = (P + 127) / 128;
+        const Key* hit = nullptr;
+        for (const Key& k : cache)
+            if (k.tiles == t128 && k.n == n && k.sms == g_num_sms && k.c[0] == cost[0] && k.c[1] == cost[1] &&
+                (n < 3 || k.c[2] == cost[2])) hit = &k;
+        if (!hit && t128 >= n && t128 <= 64ll * g_num_sms) {
+            auto span = [&](int i, int sh) { return (float)((t128 + sh - 1) / sh) * cost[i]; };
+            float best = INFINITY, best_sum = INFINITY;
+            int bs[3] = {share_of[0], share_of[1], n == 3 ? share_of[2] : 0};
+            for (int a = 1; a <= g_num_sms - (n - 1); ++a) {
+                const float sa = span(0, a);
+                if (sa > best) continue;
+                const int b_hi = n == 3 ? g_num_sms - a - 1 : g_num_sms - a;
+                for (int b = n == 3 ? 1 : b_hi; b <= b_hi; ++b) {
+                    const float sb = span(1, b), sc3 = n == 3 ? span(2, g_num_sms - a - b) : 0.f;
+                    const float m = fmaxf(sa, fmaxf(sb, sc3)), sum = sa + sb + sc3;
+                    if (m < best || (m == best && sum < best_sum)) {
+                        best = m; best_sum = sum; bs[0] = a; bs[1] = b; bs[2] = n == 3 ? g_num_sms - a - b : 0;
+                    }
+                }
+            }
+            Key& k = cache[cache_next++ % 8];
+            k.tiles = t128; k.n = n; k.sms = g_num_sms;
+            for (int i = 0; i < 3; ++i) { k.c[i] = i < n ? cost[i] : 0.f; k.share[i] = bs[i]; }
+            hit = &k;
+        }
+        if (hit) for (int i = 0; i < n; ++i) share_of[i] = hit->share[i];
     }
     // tuning hook: NSB_BWD_SHARES="a,b,c" / NSB_FWD_SHARES forces the CTA split of a 3-decoder stage
     if (n == 3)
