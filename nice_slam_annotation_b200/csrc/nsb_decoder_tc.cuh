@@ -162,6 +162,14 @@ __device__ __forceinline__ void tc_load_point(const PointsDev& q, const DecTask&
     }
 }
 
+// one 256-bit store (sm_100: STG.256) of eight consecutive floats at a 32-byte aligned address: a whole sector
+// per request, where two float4 stores cost the L2 two partial-sector writes
+__device__ __forceinline__ void st_global_v8(float* d, const float (&v)[8]) {
+    asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 :: "l"(d), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+                 : "memory");
+}
+
 // 8 embedding features [c0, c0 + 8) of this thread's point -> tensor memory (hi / lo)
 // (Bv: [feature] -> (B[0][f], B[1][f], B[2][f], 0); same operation order as phase())
 // erow (optional): this point's row of the record's e section ([16][96], rec_sw columns), r its row index
@@ -175,9 +183,7 @@ __device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float4* B
     }
     st_split8(lane_base, TM_EHI + c0, TM_ELO + c0, e);
     if (erow) {
-        float* d = erow + rec_sw(r, c0);
-        *reinterpret_cast<float4*>(d) = make_float4(e[0], e[1], e[2], e[3]);
-        *reinterpret_cast<float4*>(d + 4) = make_float4(e[4], e[5], e[6], e[7]);
+        st_global_v8(erow + rec_sw(r, c0), e);
     }
 }
 
@@ -364,9 +370,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             else relu_hi = sign;
             st_split8(lane_base, TM_HHI + hc, TM_HLO + hc, a);
             if (float* hr = rec_row(tile, RC::R_H + L * 16 * HID, HID)) {        // h_{L+1}: input of the next layer's d(W)
-                float* d = hr + rec_sw(row & 15, hc);
-                *reinterpret_cast<float4*>(d) = make_float4(a[0], a[1], a[2], a[3]);
-                *reinterpret_cast<float4*>(d + 4) = make_float4(a[4], a[5], a[6], a[7]);
+                st_global_v8(hr + rec_sw(row & 15, hc), a);
             }
             tc::tmem_st_wait();
             tc::fence_before_sync();
