@@ -209,6 +209,8 @@ def run_ours(args):
         return step.run().item()
 
     def step_engine_packed(pb):
+        if step.graph_host is not None:                             # H2D + batch load + iteration + D2H as ONE graph
+            return step.step_from_host(pb)
         step.load_packed(pb)                                        # ONE pinned [n,10] array -> one H2D copy + one kernel
         return step.run().item()
 
@@ -283,6 +285,8 @@ def run_ours(args):
         packed_ok = world == 1 or step._peer_max
         if packed_ok:
             packed_batches = [FusedStep.pack_batch(*b) for b in batches]
+            if not args.no_graph:
+                step.capture_host()
             ms_eng = timed(step_engine_packed, packed_batches, args.steps, args.warmup)
         else:
             ms_eng = ms_eng4
@@ -319,9 +323,14 @@ def run_ours(args):
                    "exchange_max_rel_diff_vs_nccl": x_err},
         "e2e": {"value": world * n_rays / (ms_eng * 1e-3), "unit": "rays/s", "ms_per_step": ms_eng,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
-                "api": ("FusedStep.load_packed(ray batch as one pinned [n,10] host array: 1 H2D copy + nsb_load_batch_packed)"
-                        if packed_ok else "FusedStep.load(4 pinned host tensors)")
-                       + " + run() + loss.item(): the engine call Mapper.optimize_map makes per iteration (2 C-ABI calls: "
+                "api": (("FusedStep.step_from_host(ray batch as one pinned [n,10] host array): memcpy into the pinned staging "
+                         "buffer, then H2D copy + nsb_load_batch_packed + the iteration + D2H copy of the loss replayed as ONE "
+                         "CUDA graph, stream synchronise, loss returned as a float"
+                         if step.graph_host is not None else
+                         "FusedStep.load_packed(ray batch as one pinned [n,10] host array: 1 H2D copy + nsb_load_batch_packed) "
+                         "+ run() + loss.item()")
+                        if packed_ok else "FusedStep.load(4 pinned host tensors) + run() + loss.item()")
+                       + ": the engine call Mapper.optimize_map makes per iteration (2 C-ABI calls: "
                          "nsb_render_forward, nsb_render_backward with the fused mapping loss), loss read back every step",
                 "ms_per_step_from_4_host_tensors": ms_eng4},
         "e2e_autograd": {"value": world * n_rays / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e,

@@ -180,6 +180,9 @@ class FusedStep:
         self.graph = None
         self._side = None
         self._packed_dev = None
+        self.graph_host = None           # capture_host(): H2D of the staged batch + iteration + D2H of the loss
+        self._host_stage = self._host_keep = self._loss_host = self._keep_dev = None
+        self._host_n = -1
         self._peer_max = bool(self.with_gt_depth and self._sharded() and peers is not None and self.bucket is not None)
 
     # -- plumbing -----------------------------------------------------------------------
@@ -341,6 +344,53 @@ class FusedStep:
         with torch.cuda.graph(g):
             self._launch()
         self.graph = g
+
+    def capture_host(self):
+        """Record a whole host-to-host step into ONE graph: copy of the staged batch (pinned host memory) to the
+        device, ``nsb_load_batch_packed``, the iteration, copy of the loss back to pinned host memory.  Call after
+        a warm-up ``run``; then ``step_from_host`` costs the host one memcpy into the staging buffer, one graph
+        launch and one stream synchronisation per iteration."""
+        if self._sharded() and (self.bucket is None or self.bucket.peers is None or not self._peer_max):
+            raise NotImplementedError("capture_host on a sharded step needs the peer-memory exchange")
+        if self._host_stage is None:
+            self._host_stage = torch.zeros(self.N, 10, dtype=torch.float32).pin_memory()
+            self._host_keep = torch.zeros(self.N, dtype=torch.uint8).pin_memory()
+            self._loss_host = torch.zeros(1, dtype=torch.float64).pin_memory()
+            self._keep_dev = torch.zeros(self.N, dtype=torch.uint8, device=self.dev)
+            if self._packed_dev is None:
+                self._packed_dev = torch.empty(self.N, 10, device=self.dev)
+        g = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g):
+            self._packed_dev.copy_(self._host_stage, non_blocking=True)
+            self._keep_dev.copy_(self._host_keep, non_blocking=True)
+            check(lib().nsb_load_batch_packed(_ptr(self._packed_dev), _ptr(self._keep_dev), self.N, self.N,
+                                              _ptr(self.rays_o), _ptr(self.rays_d), _ptr(self.gt_depth),
+                                              _ptr(self.gt_color), _ptr(self.keep), _stream()), "load_batch_packed")
+            self._launch()
+            self._loss_host.copy_(self.loss, non_blocking=True)
+        self.graph_host = g
+
+    def step_from_host(self, packed, keep=None):
+        """One iteration on a packed [n,10] float32 HOST batch (``pack_batch``), loss returned as a Python float;
+        gradients are in ``self.bucket``.  Needs ``capture_host``."""
+        if self.graph_host is None:
+            raise RuntimeError("step_from_host needs capture_host() first")
+        n = packed.shape[0]
+        if n > self.N or packed.shape[1] != 10 or packed.dtype != torch.float32 or packed.is_cuda:
+            raise ValueError("step_from_host wants a float32 [n<=N, 10] host tensor")
+        self._host_stage[:n].copy_(packed)
+        if keep is not None:
+            self._host_keep[:n].copy_(keep.to(torch.uint8))
+            self._host_keep[n:] = 0
+            self._host_n = -1
+        elif n != self._host_n:
+            self._host_keep[:n] = 1
+            self._host_keep[n:] = 0
+            self._host_n = n
+        self.graph_host.replay()
+        torch.cuda.current_stream().synchronize()
+        return float(self._loss_host[0])
 
     def run(self, all_reduce=True):
         """One iteration on the loaded batch.  Returns the loss as a [1] fp64 device tensor (this

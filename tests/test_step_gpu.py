@@ -189,3 +189,23 @@ def test_render_img_vs_oracle(scene):
     assert_close(d.cpu().reshape(-1), d0, 1e-4, "depth")
     assert_close(v.cpu().reshape(-1), v0, 1e-4, "var")
     assert_close(col.cpu().reshape(-1, 3), c0, 1e-4, "color")
+
+
+def test_step_from_host_matches_load_and_run(scene):
+    """capture_host / step_from_host: the whole host-to-host step as one graph gives the loss and the gradients of
+    load() + run(), also after a batch with fewer rays (the tail is masked off by the staged keep bytes)."""
+    from nice_slam_annotation_b200.step import FusedStep
+    ns = scene
+    kw = dict(loss="mapping", w_color=0.2, grid_grads=("grid_middle", "grid_fine", "grid_color"),
+              decoder_grads=("color_decoder",))
+    a = FusedStep(ns.renderer, ns.shared_decoders, ns.shared_c, "color", 160, **kw)
+    b = FusedStep(ns.renderer, ns.shared_decoders, ns.shared_c, "color", 160, **kw)
+    big, small = _batch(ns, 160, seed=5), _batch(ns, 96, seed=6)
+    b.load(*big[:4]); b.run(); b.capture_host()
+    for batch in (big, small, big):
+        a.load(*batch[:4])
+        l0 = float(a.run().item())
+        g0 = a.bucket.flat.clone()
+        l1 = b.step_from_host(FusedStep.pack_batch(*batch[:4]))
+        assert abs(l1 - l0) <= 1e-9 * abs(l0)
+        assert_close(b.bucket.flat.cpu(), g0.cpu(), 1e-5, "bucket")
