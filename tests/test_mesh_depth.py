@@ -173,3 +173,13 @@ def test_mesh_depth_edge_cases():
         render_mesh_depth(v, np.array([[0, 1, 3]]), eye, H, W, FOCAL, FOCAL, CX, CY)
     with pytest.raises(RuntimeError):
         render_mesh_depth(v, t, eye, H, W, FOCAL, FOCAL, CX, CY, z_near=0.0)
+
+
+def test_product_path_needs_cuda():
+    """no CPU fallback: without a CUDA device the product call raises instead of routing through the oracle"""
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    from nice_slam_annotation_b200.tools.eval_recon import render_mesh_depth
+    v, t = quad(2.0)
+    with pytest.raises(RuntimeError):
+        render_mesh_depth(v, t, np.eye(4), H, W, FOCAL, FOCAL, CX, CY)
