@@ -597,6 +597,13 @@ def run_reference(args):
     if int(os.environ.get("RANK", 0)) != 0:
         return
     from nice_slam_annotation_b200.scene import build_scene
+    if "OMP_NUM_THREADS" in os.environ and int(os.environ.get("WORLD_SIZE", 1)) > 1:
+        # torchrun pins OMP_NUM_THREADS=1 for its workers; this arm runs on rank 0 alone and may use the host:
+        # the CPUs it is allowed on, which is what torch picks by itself at N=1
+        try:
+            torch.set_num_threads(max(1, min(len(os.sched_getaffinity(0)), 64)))
+        except (AttributeError, OSError):
+            pass
     ns = build_scene(SHAPE, "cpu", seed=0, n_frames=FRAMES)        # host only: no kernel of ours on this arm
     batches = make_batches_cpu(ns, args.rays, 4, seed=100)
     step = oracle_step_fn(ns, batches)
