@@ -314,6 +314,12 @@ int nsb_load_batch_packed(const float* packed, const uint8_t* keep, int64_t n, i
 int64_t nsb_render_workspace_bytes(int64_t N, int S);
 int nsb_render_forward(const NsbRenderCall* call, void* stream);
 int nsb_render_backward(const NsbRenderCall* call, void* stream);
+/* Diagnostic for benchmarks (no reference counterpart): after nsb_render_backward of `call`, count the
+ * tiles of `tile_points` consecutive points whose incoming gradient d(raw) is not exactly zero -- the
+ * decoder backward skips the others, so this is the share of the backward's work a fixture really asks
+ * for.  counts (device, int64 [3], zeroed by the callee): tiles, tiles with d(occupancy) != 0, tiles with
+ * d(rgb) != 0. */
+int nsb_render_live_tiles(const NsbRenderCall* call, int tile_points, int64_t* counts, void* stream);
 
 /* ---- losses of the two SLAM steps, value and gradient in one kernel --------------------------
  * mapping (src/Mapper.py:604-612): loss = sum_{gt>0} |gt - depth| + w_color sum |gt_c - color|

@@ -69,6 +69,9 @@ class Mapper(object):
         # whenever its preconditions hold; False: the autograd path below (same values)
         self.fused_loop = True
         self._loops = {}
+        # shared.prepare_shared(slam) ran before the objects were shared with the other processes: the loop
+        # must then never re-allocate a grid or a decoder parameter (the tracker would keep reading the old storage)
+        self.shared_prepared = bool(getattr(slam, 'shared_layout_prepared', False))
         # ray-sharded mapping over the GPUs of one box: see enable_sharding
         self.shard_group, self.shard_peers, self.shard_world, self.shard_rank = None, None, 1, 0
         self.H, self.W, self.fx, self.fy, self.cx, self.cy = slam.H, slam.W, slam.fx, slam.fy, slam.cx, slam.cy
@@ -443,12 +446,16 @@ class Mapper(object):
             if self.stage != prev:
                 loop.set_lr(self.stage, lr_factor)
                 prev = self.stage
+            loop.draw = self.index_source is None            # set on EVERY call: the loops (and their graphs) are cached
             if self.index_source is not None:
-                loop.draw = False
                 for i in range(loop.K):
                     loop.indices[i * loop.pix:(i + 1) * loop.pix].copy_(next(self.index_source))
             loop.iterate(self.stage)
         loop.finish()
+        if self.shard_peers is not None:
+            # a rank that missed a peer barrier leaves partial sums behind and the replicas diverge: one host
+            # read per optimize_map call, and raise
+            self.shard_peers.check_error()
         if self.BA:                                           # Mapper.py:644-667
             for i, frame in enumerate(optimize_frame):
                 if not ba_slots[i]:

@@ -117,6 +117,7 @@ _SIGS = {
     "nsb_render_workspace_bytes": (C.c_int64, [C.c_int64, C.c_int]),
     "nsb_render_forward": (C.c_int, [C.POINTER(NsbRenderCall), c_ptr]),
     "nsb_render_backward": (C.c_int, [C.POINTER(NsbRenderCall), c_ptr]),
+    "nsb_render_live_tiles": (C.c_int, [C.POINTER(NsbRenderCall), C.c_int, c_ptr, c_ptr]),
     "nsb_mapping_loss": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_float, C.c_int, c_ptr,
                                    c_ptr, c_ptr, c_ptr]),
     "nsb_composite_mapping_partials": (C.c_int64, [C.c_int64]),

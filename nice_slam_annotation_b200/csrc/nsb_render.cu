@@ -317,6 +317,34 @@ extern "C" int nsb_render_backward(const NsbRenderCall* r, void* stream) {
     return 0;
 }
 
+__global__ void k_live_tiles(const float* __restrict__ d_raw, long long P, int tile, long long* counts) {
+    const long long nt = (P + tile - 1) / tile;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < nt; t += (long long)gridDim.x * blockDim.x) {
+        bool occ = false, rgb = false;
+        const long long hi = (t + 1) * tile < P ? (t + 1) * tile : P;
+        for (long long i = t * tile; i < hi; ++i) {
+            const float4 v = reinterpret_cast<const float4*>(d_raw)[i];
+            occ |= v.w != 0.f;
+            rgb |= v.x != 0.f || v.y != 0.f || v.z != 0.f;
+        }
+        if (occ) atomicAdd((unsigned long long*)(counts + 1), 1ull);
+        if (rgb) atomicAdd((unsigned long long*)(counts + 2), 1ull);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) counts[0] = nt;
+}
+
+extern "C" int nsb_render_live_tiles(const NsbRenderCall* r, int tile_points, int64_t* counts, void* stream) {
+    if (!r || !r->workspace || !counts || tile_points <= 0) return set_error(NSB_EINVAL, "bad argument");
+    const int S = r->N_samples + (r->gt_depth ? r->N_surface : 0);
+    if (r->N <= 0) return 0;
+    Ws w = carve_ws(r->workspace, r->N, S);
+    cudaMemsetAsync(counts, 0, 3 * sizeof(int64_t), (cudaStream_t)stream);
+    const long long P = (long long)r->N * S, nt = (P + tile_points - 1) / tile_points;
+    k_live_tiles<<<(unsigned)((nt + 255) / 256 > 1184 ? 1184 : (nt + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        w.d_raw, P, tile_points, (long long*)counts);
+    return check_launch("k_live_tiles");
+}
+
 extern "C" int nsb_mapping_loss(const double* depth, const float* color, const float* gt_depth,
                                 const float* gt_color, const uint8_t* keep, int64_t N, float w_color,
                                 int use_color, double* loss, double* g_depth, float* g_color, void* stream) {

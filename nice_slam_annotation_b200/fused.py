@@ -97,14 +97,40 @@ def packed_decoder(dec, kind):
 # ---------------------------------------------------------------------------------------
 # structs
 # ---------------------------------------------------------------------------------------
+_layout_cache = {}        # (data_ptr, version, shape, device) -> channels-last copy; small LRU
+_LAYOUT_CACHE_MAX = 8
+
+
 def grid_to_kernel_layout(g):
-    """[1,32,Z,Y,X] fp32 -> same logical tensor, channels-last in memory (no copy if it is)."""
+    """[1,32,Z,Y,X] fp32 -> same logical tensor, channels-last in memory.
+
+    No copy when the grid already has the kernels' layout (scene.grid_init, shared.prepare_shared, the
+    package's Mapper).  A channels-FIRST grid -- what the reference's own ``NICE_SLAM.grid_init`` and its
+    ``val[mask] = val_grad`` non-leaf produce (NICE_SLAM.py:243-320, Mapper.py:499) -- has to be re-laid out:
+    * without autograd history (the tracker's detached copies, forward-only callers) the converted copy is
+      cached by (storage address, version counter), so the copy is paid once per ``update_para_from_mapping``
+      and not once per render call;
+    * with autograd history (the reference's mapper driving this Renderer) the conversion must stay a
+      differentiable op: one layout copy per call forward and one for its gradient (0.1 ms per 48 MB grid on
+      B200) -- use ``shared.prepare_shared`` / this package's Mapper to avoid it."""
     if g.dim() != 5 or g.shape[0] != 1 or g.shape[1] != 32:
         raise RuntimeError(f"feature grid must be [1,32,Z,Y,X], got {tuple(g.shape)}")
     if g.dtype != torch.float32:
         raise RuntimeError("feature grid must be float32")
     _require_cuda(g, "feature grid")
-    return g.contiguous(memory_format=torch.channels_last_3d)
+    if g.is_contiguous(memory_format=torch.channels_last_3d):
+        return g
+    if g.requires_grad and torch.is_grad_enabled():
+        return g.contiguous(memory_format=torch.channels_last_3d)
+    key = (g.data_ptr(), g._version, tuple(g.shape), tuple(g.stride()), str(g.device))
+    hit = _layout_cache.get(key)
+    if hit is not None:
+        return hit
+    out = g.detach().contiguous(memory_format=torch.channels_last_3d)
+    if len(_layout_cache) >= _LAYOUT_CACHE_MAX:
+        _layout_cache.pop(next(iter(_layout_cache)))
+    _layout_cache[key] = out
+    return out
 
 
 def _bound6(bound):

@@ -27,10 +27,16 @@ BETAS, EPS = (0.9, 0.999), 1e-8          # torch.optim.Adam defaults (the refere
 GROUP_LR = {"grid_coarse": "coarse_lr", "grid_middle": "middle_lr", "grid_fine": "fine_lr", "grid_color": "color_lr"}
 
 
-def flatten_decoder(dec, kind):
+def flatten_decoder(dec, kind, originals=None):
     """Re-point the parameters of one decoder at views of ONE flat buffer in canonical order (the
     order of its flat gradient), so that its Adam step is a single kernel.  Parameter objects,
-    names and values are unchanged (state_dict / load_state_dict / deepcopy keep working)."""
+    names and values are unchanged (state_dict / load_state_dict / deepcopy keep working).
+
+    The storages the parameters had before are NOT the ones trained afterwards.  When they are shared with
+    another process (the reference passes ``shared_decoders`` to the tracker through CUDA IPC at spawn,
+    NICE_SLAM.py:134,357-376) flatten BEFORE sharing (``shared.prepare_shared``); a caller that flattens later
+    passes ``originals`` (a list) to receive (old storage, new view) pairs and copies the trained values back
+    (``MappingLoop.finish``)."""
     params = canonical_params(dec, kind)
     flat = getattr(dec, "_nsb_flat", None)
     n = sum(p.numel() for p in params)
@@ -41,6 +47,8 @@ def flatten_decoder(dec, kind):
     for p, o in zip(params, _offsets(params)):
         seg = flat[o:o + p.numel()].view(p.shape)
         seg.copy_(p.data)
+        if originals is not None:
+            originals.append((p.data, seg))
         p.data = seg
     dec._nsb_flat = flat
     return flat
@@ -118,11 +126,21 @@ class MappingLoop:
         self.draw = True
         self.bound6 = fused._bound6(mp.bound)
         self.intr = tuple(float(x) for x in (mp.fx, mp.fy, mp.cx, mp.cy))
-        # grids: optimised in place, in the kernels' layout
+        # grids: optimised in place, in the kernels' layout.  A grid that is not in that layout yet is re-allocated;
+        # its old storage may be the one another process reads (shared_c travels to the tracker by CUDA IPC), so it
+        # is kept and refreshed by finish() -- unless the caller promised prepared shared objects, then it is an error
+        self._write_back = []
+        strict = bool(getattr(mp, "shared_prepared", False))
         for key in list(mp.c.keys()):
             g = mp.c[key]
             if not (g.is_cuda and g.is_contiguous(memory_format=torch.channels_last_3d)):
-                mp.c[key] = g.detach().to(dev).contiguous(memory_format=torch.channels_last_3d)
+                if strict:
+                    raise RuntimeError(f"{key} is not channels_last_3d on the device although shared.prepare_shared ran: "
+                                       "re-allocating it here would detach it from the other processes")
+                new = g.detach().to(dev).contiguous(memory_format=torch.channels_last_3d)
+                if g.is_cuda:
+                    self._write_back.append((g.detach(), new))
+                mp.c[key] = new
             elif g.requires_grad:
                 mp.c[key] = g.detach()
         self.grid_keys = ["grid_coarse"] if mp.coarse_mapper else ["grid_middle", "grid_fine", "grid_color"]
@@ -139,7 +157,11 @@ class MappingLoop:
                 self.train_dec.append("color_decoder")
         self.dec_kind = {name: k for k, name in enumerate(DEC_NAMES)}
         for name in self.train_dec:
-            self.opt[name] = _Opt(flatten_decoder(getattr(mp.decoders, name), self.dec_kind[name]))
+            n_before = len(self._write_back)
+            self.opt[name] = _Opt(flatten_decoder(getattr(mp.decoders, name), self.dec_kind[name], self._write_back))
+            if strict and len(self._write_back) != n_before:
+                raise RuntimeError(f"{name} had to be re-flattened although shared.prepare_shared ran: its old "
+                                   "storages are the ones the other processes read")
         want = {id(p) for name in self.train_dec for p in getattr(mp.decoders, name).parameters()}
         for p in mp.decoders.parameters():
             p.requires_grad_(id(p) in want)
@@ -258,16 +280,23 @@ class MappingLoop:
         if not graph or (st._sharded() and st.bucket.peers is None):    # NCCL calls are not captured
             self._launch(stage)
             return
-        g = self.graphs.get(stage)
+        key = (stage, bool(self.draw))           # the pixel draw is a node of the graph: one graph per draw flag
+        g = self.graphs.get(key)
         if g is None:
-            # warm-up outside the capture must not advance the optimiser: run render only
+            # warm-up outside the capture must not advance the optimiser (render only) nor the RNG stream
+            # (a seeded run must see the same draws with and without graphs)
+            rng = torch.cuda.get_rng_state(self.dev) if self.draw else None
+            keep_idx = self.indices.clone()
             self._sample(st)
             st._launch(exchange=False)
+            if rng is not None:
+                torch.cuda.set_rng_state(rng, self.dev)
+            self.indices.copy_(keep_idx)
             g = torch.cuda.CUDAGraph()
             torch.cuda.synchronize()
             with torch.cuda.graph(g):
                 self._launch(stage)
-            self.graphs[stage] = g
+            self.graphs[key] = g
         g.replay()
 
     def finish(self):
@@ -276,6 +305,8 @@ class MappingLoop:
         for name in self.train_dec:
             for p in getattr(self.mp.decoders, name).parameters():
                 torch.autograd.graph.increment_version(p)
+        for old, new in self._write_back:        # storages this loop replaced (see __init__): keep them current
+            old.copy_(new)
 
     def camera(self, slot):
         return self.cam[slot].clone()

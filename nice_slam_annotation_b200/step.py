@@ -403,6 +403,14 @@ class FusedStep:
             self.bucket.all_reduce(self.group)         # NCCL; the peer-memory exchange is part of _launch
         return self.loss
 
+    def live_tiles(self, tile_points=16):
+        """Diagnostic (after ``run``): share of the ``tile_points``-point tiles whose incoming gradient is not exactly
+        zero, as {'occupancy': f, 'rgb': f}: what the decoder backward cannot skip on this batch / fixture."""
+        counts = torch.zeros(3, dtype=torch.int64, device=self.dev)
+        check(lib().nsb_render_live_tiles(C.byref(self._call), int(tile_points), _ptr(counts), _stream()), "live_tiles")
+        n, occ, rgb = (int(x) for x in counts.tolist())
+        return {"tile_points": int(tile_points), "occupancy": occ / max(n, 1), "rgb": rgb / max(n, 1)}
+
     def decoder_grads(self, kind):
         """Per-parameter gradient views of a trainable decoder, in state_dict order of
         ``canonical_params``."""

@@ -329,7 +329,7 @@ def sample_pdf(bins, weights, N_samples, u=None):
     cdf = torch.cumsum(pdf, -1)
     cdf = torch.cat([torch.zeros_like(cdf[..., :1]), cdf], -1)
     if u is None:
-        u = torch.linspace(0., 1., steps=N_samples).expand(list(cdf.shape[:-1]) + [N_samples])
+        u = torch.linspace(0., 1., steps=N_samples).to(cdf.device).expand(list(cdf.shape[:-1]) + [N_samples])
     u = u.contiguous()
     inds = torch.searchsorted(cdf, u, right=True)
     below = torch.clamp(inds - 1, min=0)
@@ -375,7 +375,7 @@ def regulation(prm, grids, rays_d, rays_o, gt_depth, stage, bound, u, N_samples=
     """iMAP free-space regulariser: densities at jittered samples in [0, 0.85 d].
     src/utils/Renderer.py:343-409.  u: [N,N_samples] uniforms (always jittered there)."""
     g = gt_depth.reshape(-1, 1).repeat(1, N_samples)
-    t = torch.linspace(0., 1., steps=N_samples)
+    t = torch.linspace(0., 1., steps=N_samples).to(g.device)
     z = 0.0 * (1. - t) + g * 0.85 * t
     mids = .5 * (z[..., 1:] + z[..., :-1])
     upper = torch.cat([mids, z[..., -1:]], -1)

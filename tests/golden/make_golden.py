@@ -59,6 +59,23 @@ _stub("matplotlib", pyplot=_plt)
 for _n in ("open3d", "trimesh", "skimage", "mathutils"):
     _stub(_n)
 
+
+class _Matrix:
+    """Stand-in for ``mathutils.Matrix`` (not installed): the one method ``get_tensor_from_camera`` uses
+    (common.py:199-202), rotation matrix -> quaternion (w, x, y, z), through scipy.  Only the BA golden
+    (``mapper_variants``) reaches it; q and -q describe the same rotation, so the sign convention is immaterial."""
+
+    def __init__(self, R):
+        self.R = np.asarray(R, dtype=np.float64)
+
+    def to_quaternion(self):
+        from scipy.spatial.transform import Rotation
+        x, y, z, w = Rotation.from_matrix(self.R).as_quat()
+        return np.array([w, x, y, z])
+
+
+sys.modules["mathutils"].__dict__.setdefault("Matrix", _Matrix)
+
 from src import config as ref_config                      # noqa: E402
 from src.common import (get_camera_from_tensor, get_rays, get_samples,   # noqa: E402
                         raw2outputs_nerf_color, sample_pdf)
@@ -487,8 +504,64 @@ def gen_frustum():
     np.savez_compressed(os.path.join(HERE, "frustum.npz"), **out)
 
 
+def gen_mapper_variants():
+    """f1 pinned to the reference: Mapper.optimize_map from the trained state (trained_nice.npz) with
+    ``frustum_feature_selection=True`` (compact val[mask] Adam + write-back, Mapper.py:393-404,491-500,633-642) and
+    with local BA (camera tensors in the optimiser, Mapper.py:430-458,644-667), two keyframes + the current frame,
+    10 iterations (middle x5, fine x2, color x3).  Stores the pixel draws, the updated grids / decoders and poses."""
+    d = dict(np.load(os.path.join(HERE, "trained_nice.npz")))
+    cam = tuple(float(v) for v in d["cam"])
+    cam = (int(cam[0]), int(cam[1])) + cam[2:]
+    bound = [[-1.4, 1.6], [-1.1, 1.3], [-1.0, 1.1]]
+    depth, color = torch.from_numpy(d["depth_img"]), torch.from_numpy(d["color_img"])
+    c2w = torch.from_numpy(d["c2w"]).float()
+    if c2w.shape[0] == 3:
+        c2w = torch.cat([c2w, torch.tensor([[0, 0, 0, 1.]])], 0)
+    iters, pix = 10, 399
+    out = {"iters": np.array(iters), "pixels": np.array(pix)}
+    for name, frustum, ba in (("frustum", True, False), ("ba", False, True), ("frustum_ba", True, True)):
+        cfg = load_cfg(True)
+        cfg["grid_len"].update({"coarse": 1.0})
+        cfg["mapping"].update({"pixels": pix})
+        slam = build_scene(cfg, cam, bound, seed=0)
+        assert np.allclose(slam.bound.numpy(), d["bound"])
+        slam.shared_c = {k[2:]: torch.from_numpy(v.copy()) for k, v in d.items() if k.startswith("c.")}
+        slam.shared_decoders.load_state_dict({k[4:]: torch.from_numpy(v.copy()) for k, v in d.items() if k.startswith("dec.")})
+        mapper = make_mapper(slam, cfg, frustum=frustum)
+        mapper.BA = ba
+        mapper.keyframe_selection_method = "global"
+        kf = []
+        for i in range(2):
+            pose = c2w.clone()
+            pose[:3, 3] += 0.02 * (i + 1)
+            kf.append({"gt_c2w": pose.clone(), "idx": i, "color": color, "depth": depth, "est_c2w": pose.clone()})
+        mapper.keyframe_dict = kf
+        np.random.seed(0)
+        torch.manual_seed(61)
+        draws = np.stack([torch.randint(cam[0] * cam[1], (pix // 3,)).numpy() for _ in range(3 * iters)])
+        torch.manual_seed(61)
+        ret = mapper.optimize_map(iters, 1.0, 7, color, depth, c2w, kf, [0, 1], c2w.clone())
+        out[f"{name}.indices"] = draws
+        for k, v in slam.shared_c.items():
+            if k != "grid_coarse":
+                out[f"{name}.c_after.{k}"] = v.detach().numpy().copy()
+        for k, v in slam.shared_decoders.state_dict().items():
+            if k.startswith("color_decoder."):
+                out[f"{name}.dec_after.{k}"] = v.detach().numpy().copy()
+        out[f"{name}.kf_c2w"] = np.stack([np.asarray(k_["est_c2w"].detach().numpy()) for k_ in kf])
+        out[f"{name}.kf_c2w0"] = np.stack([np.asarray(k_["gt_c2w"].detach().numpy()) for k_ in kf])
+        if ba:
+            out[f"{name}.cur_c2w"] = ret.detach().numpy().copy()
+        else:
+            assert ret is None
+        moved = {k: float((v.detach() != torch.from_numpy(d["c." + k])).double().mean()) for k, v in slam.shared_c.items()}
+        print("mapper_variants", name, "moved fraction", moved,
+              "pose delta", float(np.abs(out[f"{name}.kf_c2w"] - out[f"{name}.kf_c2w0"]).max()))
+    np.savez_compressed(os.path.join(HERE, "mapper_variants.npz"), **out)
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["small", "variants", "units", "imap", "imap256", "trained", "frustum"]
+    which = sys.argv[1:] or ["small", "variants", "units", "imap", "imap256", "trained", "frustum", "mapper_variants"]
     torch.set_num_threads(1)
     if "small" in which:
         gen_small_nice()
@@ -504,6 +577,8 @@ if __name__ == "__main__":
         gen_trained()
     if "frustum" in which:
         gen_frustum()
+    if "mapper_variants" in which:
+        gen_mapper_variants()
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)) // 1024, "KiB")

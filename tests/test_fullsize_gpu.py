@@ -195,3 +195,114 @@ def test_sample_depths_adversarial_rays_bit_exact(replica):
     z = fused.sample_z(ro[ok].to(DEV), rd[ok].to(DEV), gd[ok].to(DEV), ns.bound, 32, 16, lindisp=True, u=u[ok].to(DEV)).cpu()
     same = (z == z_ref) | (z.isnan() & z_ref.isnan())
     assert bool(same.all()), int((~same).sum())
+
+
+# ---- configs[3] / configs[4] at full size -------------------------------------------------------------------------
+def _engine_vs_oracle(ns, per_frame, seed, tol_g=1e-3):
+    """Engine step (FusedStep, fused mapping loss) against the oracle on the GPU: depth, colour, loss, the three grid
+    gradients and the colour-decoder gradients."""
+    from nice_slam_annotation_b200.fused import canonical_params
+    from nice_slam_annotation_b200.step import FusedStep
+    ro, rd, gd, gc, keep = _batch(ns, per_frame, seed=seed)
+    sel = keep.bool()
+    n = ro.shape[0]
+    step = FusedStep(ns.renderer, ns.shared_decoders, ns.shared_c, "color", n, loss="mapping", w_color=0.2,
+                     use_color=True, grid_grads=("grid_middle", "grid_fine", "grid_color"),
+                     decoder_grads=("color_decoder",))
+    step.load(ro, rd, gd, gc, keep=keep)
+    loss = step.run().clone()
+    torch.cuda.synchronize()
+    prm, grids = _oracle_state(ns, "color_decoder.")
+    d0, _, c0 = O.render_batch_ray(prm, grids, rd[sel], ro[sel], "color", gd[sel], ns.bound.to(DEV))
+    l0 = O.mapping_loss(d0, c0, gd[sel], gc[sel])
+    l0.backward()
+    assert_close(step.depth[sel], d0.detach(), 1e-4, "depth")
+    assert_close(step.color[sel], c0.detach(), 1e-4, "color")
+    assert abs(float(loss) - float(l0)) <= 1e-4 * abs(float(l0))
+    for k, key in ((1, "grid_middle"), (2, "grid_fine"), (3, "grid_color")):
+        assert float(grids[key].grad.abs().max()) > 0
+        assert_close(step.bucket.view_of(step.grids[k]), grids[key].grad, tol_g, "d " + key)
+    by_ptr = {p.data_ptr(): nme for nme, p in ns.shared_decoders.color_decoder.named_parameters()}
+    for p, g in zip(canonical_params(ns.shared_decoders.color_decoder, 3), step.decoder_grads(3)):
+        assert_close(g, prm["color_decoder." + by_ptr[p.data_ptr()]].grad, tol_g, "d color_decoder." + by_ptr[p.data_ptr()])
+    return int(sel.sum())
+
+
+def test_apartment_5000_ray_mapping_step_vs_oracle():
+    """configs[3]: Apartment bound (124.9 MB of grids), 5000 rays per iteration (configs/Apartment/apartment.yaml:21-24)."""
+    ns = _scene("apartment", 5)
+    assert sum(v.numel() * 4 for v in ns.shared_c.values()) > 120e6
+    kept = _engine_vs_oracle(ns, 1000, seed=31)
+    assert kept > 4500
+
+
+def test_tum_scale_grid_mapping_step_vs_oracle():
+    """TUM fr3_office grid lengths (0.16 / 0.08 / 0.08 m): 127^3-class fine / colour grids, 556 MB, far beyond L2 and
+    beyond 2^31 bytes of voxel offsets x channel (the kernels index voxels with 32-bit, bytes with 64-bit arithmetic)."""
+    ns = _scene("tum_fr3_office", 5)
+    assert sum(v.numel() * 4 for v in ns.shared_c.values()) > 500e6
+    _engine_vs_oracle(ns, 200, seed=32)
+
+
+def test_replica_coarse_stage_vs_oracle(replica):
+    """stage 'coarse' (MLP_no_xyz on the enlarged coarse grid, 32 samples, no sensor depth in the sampler) at the full
+    Replica batch through Renderer.render_batch_ray + autograd."""
+    from nice_slam_annotation_b200 import fused
+    ns = replica
+    ro, rd, gd, gc, keep = _batch(ns, 200, seed=33)
+    sel = keep.bool()
+    dec = ns.shared_decoders
+    for p in dec.parameters():
+        p.requires_grad_(False)
+    grid = ns.shared_c["grid_coarse"].detach().clone().requires_grad_(True)
+    c = dict(ns.shared_c, grid_coarse=grid)
+    depth, var, color = ns.renderer.render_batch_ray(c, dec, rd[sel], ro[sel], DEV, "coarse", gt_depth=gd[sel])
+    loss = fused.mapping_loss(depth, color, gd[sel], gc[sel], 0.2, use_color=False)
+    loss.backward()
+    prm, grids = _oracle_state(ns, "none")
+    grids["grid_coarse"].requires_grad_(True)
+    d0, v0, c0 = O.render_batch_ray(prm, grids, rd[sel], ro[sel], "coarse", gd[sel], ns.bound.to(DEV))
+    l0 = O.mapping_loss(d0, c0, gd[sel], gc[sel], with_color=False)
+    l0.backward()
+    assert_close(depth, d0.detach(), 1e-4, "depth")
+    assert_close(var, v0.detach(), 1e-4, "var")
+    assert abs(float(loss) - float(l0)) <= 1e-4 * abs(float(l0))
+    assert float(grids["grid_coarse"].grad.abs().max()) > 0
+    assert_close(grid.grad, grids["grid_coarse"].grad, 1e-3, "d grid_coarse")
+
+
+def test_imap_5000_ray_mapping_step_vs_oracle():
+    """configs[4], the iMAP* stress case at its configured size (configs/imap.yaml: 5000 pixels, 32 + 12 samples, density
+    compositing, regulariser): render forward + mapping loss + 5e-4 x regulation + backward to all 11 parameter tensors
+    of the 4 x 256 MLP against the oracle on the GPU (fp32 torch ops)."""
+    import bench
+    from nice_slam_annotation_b200 import fused
+    from nice_slam_annotation_b200.common import get_samples
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    sc = bench.imap_scene(DEV)
+    n = 5000
+    idx = torch.randint(sc.H * sc.W, (n,), generator=torch.Generator().manual_seed(3))
+    ro, rd, gd, gc = get_samples(0, sc.H, 0, sc.W, n, sc.H, sc.W, sc.fx, sc.fy, sc.cx, sc.cy, sc.c2w, sc.depth, sc.color,
+                                 DEV, indices=idx)
+    ro, rd = ro.contiguous(), rd.contiguous()
+    bound = sc.r.bound
+    torch.manual_seed(7)
+    u = torch.rand(n, 32)                                     # the draw Renderer.regulation makes (CPU generator)
+    torch.manual_seed(7)
+    depth, _, color = sc.r.render_batch_ray({}, sc.dec, rd, ro, DEV, "color", gt_depth=gd)
+    sigma = sc.r.regulation({}, sc.dec, rd, ro, gd, DEV, "color")
+    loss = fused.mapping_loss(depth, color, gd, gc, 0.05, use_color=True) + 0.0005 * sigma.abs().sum()
+    loss.backward()
+    prm = {k: v.detach().clone().requires_grad_(True) for k, v in sc.dec.state_dict().items()}
+    d0, _, c0 = O.render_batch_ray(prm, {}, rd, ro, "color", gd, bound.to(DEV), N_samples=32, N_surface=0, N_importance=12,
+                                   occupancy=False, nice=False)
+    s0 = O.regulation(prm, {}, rd, ro, gd, "color", bound.to(DEV), u.to(DEV), N_samples=32, nice=False)
+    l0 = O.mapping_loss(d0, c0, gd, gc, w_color=0.05) + 0.0005 * s0.abs().sum()
+    l0.backward()
+    assert_close(depth, d0.detach(), 1e-4, "depth")
+    assert_close(color, c0.detach(), 1e-4, "color")
+    assert_close(sigma, s0.detach(), 1e-4, "regulation sigma")
+    assert abs(float(loss) - float(l0)) <= 1e-4 * abs(float(l0))
+    for k, p in sc.dec.named_parameters():
+        assert_close(p.grad, prm[k].grad, 1e-3, "d " + k)

@@ -381,3 +381,64 @@ def test_fused_mapping_loop_vs_autograd_loop(gpu, golden, frustum, ba):
             assert torch.allclose(a["est_c2w"], b["est_c2w"], atol=1e-4), "BA: keyframe pose"
     else:
         assert out is None and ref_out is None
+
+
+@pytest.mark.parametrize("fused_loop", [True, False])
+@pytest.mark.parametrize("name,frustum,ba", [("frustum", True, False), ("ba", False, True), ("frustum_ba", True, True)])
+def test_mapping_loop_vs_reference_frustum_and_ba(gpu, golden, name, frustum, ba, fused_loop):
+    """f1 pinned to the reference itself: Mapper.optimize_map with frustum feature selection (the reference's compact
+    val[mask] Adam + write-back, Mapper.py:393-404,491-500,633-642) and with local BA (Mapper.py:430-458,644-667),
+    10 iterations from the trained state on the reference's recorded pixel draws, against the grids / colour decoder
+    / poses the reference's own Mapper produced (tests/golden/mapper_variants.npz)."""
+    import numpy as np
+    from nice_slam_annotation_b200.Mapper import Mapper
+    d, v = golden("trained_nice"), golden("mapper_variants")
+    iters, pix = int(v["iters"]), int(v["pixels"])
+    depth = torch.as_tensor(d["depth_img"]).to(gpu.DEV)
+    color = torch.as_tensor(d["color_img"]).to(gpu.DEV)
+    c2w = torch.as_tensor(d["c2w"]).to(gpu.DEV).float()
+    if c2w.shape[0] == 3:
+        c2w = torch.cat([c2w, torch.tensor([[0, 0, 0, 1.]], device=gpu.DEV)], 0)
+    cfg, ns = _slam_ns(gpu, d, {"mapping": {"frustum_feature_selection": frustum, "keyframe_selection_method": "global",
+                                            "pixels": pix}})
+    ns.shared_decoders = gpu.nice_from_state(sub(d, "dec."), d["bound"])
+    ns.shared_c = gpu.grids_from(d)
+    mp = Mapper(cfg, None, ns)
+    mp.fused_loop, mp.BA = fused_loop, ba
+    kf = []
+    for i in range(2):
+        pose = c2w.clone()
+        pose[:3, 3] += 0.02 * (i + 1)
+        kf.append({"gt_c2w": pose.clone(), "idx": i, "color": color, "depth": depth, "est_c2w": pose.clone()})
+    mp.keyframe_dict = kf
+    mp.index_source = iter([torch.as_tensor(x).to(gpu.DEV) for x in v[name + ".indices"]])
+    np.random.seed(0)
+    out = mp.optimize_map(iters, 1.0, 7, color, depth, c2w, kf, [0, 1], c2w.clone())
+
+    def mostly_close(a, b, what, tol=2e-3, frac=0.999):
+        b = torch.as_tensor(b).double()
+        err = (a.double().cpu() - b).abs()
+        ok = (err <= tol * b.abs().max().clamp_min(1e-30)).double().mean().item()
+        assert ok >= frac, f"{what}: only {ok:.5f} of the elements within {tol:g}"
+    for k in ("grid_middle", "grid_fine", "grid_color"):
+        ref = torch.as_tensor(v[f"{name}.c_after.{k}"])
+        start = torch.as_tensor(d["c." + k])
+        moved_ref, moved = ref != start, mp.c[k].detach().cpu() != start
+        assert moved_ref.any()
+        assert (moved_ref != moved).double().mean().item() < 1e-3, "optimised voxel sets differ: " + k
+        mostly_close(mp.c[k].detach(), ref, "grid " + k)
+    sd = mp.decoders.state_dict()
+    for k, ref in sub(v, name + ".dec_after.").items():
+        mostly_close(sd[k], ref, "decoder " + k, frac=0.99)
+    kf_ref, kf0 = torch.as_tensor(v[name + ".kf_c2w"]), torch.as_tensor(v[name + ".kf_c2w0"])
+    if ba:
+        ref_cur = torch.as_tensor(v[name + ".cur_c2w"])
+        assert float((ref_cur - c2w.cpu()).abs().max()) > 0
+        assert_close(out.cpu() - c2w.cpu(), ref_cur - c2w.cpu(), 5e-2, "BA: current pose update")
+        for i, k_ in enumerate(kf):
+            assert torch.allclose(k_["est_c2w"].cpu(), kf_ref[i], atol=2e-4), "BA: keyframe pose"
+        assert float((kf_ref[1] - kf0[1]).abs().max()) > 0      # the reference did move the newer keyframe
+    else:
+        assert out is None
+        for i, k_ in enumerate(kf):
+            assert torch.equal(k_["est_c2w"].cpu(), kf0[i])
