@@ -341,6 +341,22 @@ int nsb_composite_mapping(const NsbPoints* rays, const double* bound6_host, int 
                           const float* gt_depth, const float* gt_color, const uint8_t* keep, float w_color,
                           int use_color, double* depth, double* var, float* rgb, float* d_raw,
                           double* partials, uint32_t* ticket, double* loss, void* stream);
+/* nsb_composite_mapping without caller scratch and without ANY allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same kernel, inputs, outputs and results as nsb_composite_mapping; the
+ * per-block loss partials and the ticket live in one file-scope `static __device__` array of the library (128.25 KiB,
+ * held by every GPU that loads the library until exit), whose device address is taken with cudaGetSymbolAddress once
+ * per device on the first call made with that device current (make that first call outside a stream capture).
+ * Limit: N <= NSB_STATIC_MAX_RAYS rays per call; a larger batch is rejected with NSB_EINVAL and a message naming the
+ * limit.  The callee clears the ticket on `stream` before every launch (the array keeps the last call's contents).
+ * Every call on a device shares the array: calls that OVERLAP on the GPU (two streams, two host threads) race --
+ * serialise them on one stream.  Calls no cudaMalloc / cudaFree / allocating library routine. */
+#define NSB_STATIC_MAX_RAYS 65536
+int nsb_composite_mapping_static(const NsbPoints* rays, const double* bound6_host, int stage, int occupancy,
+                                 const float* out_occ0, const float* out_occ1, const float* out_rgb,
+                                 const float* gt_depth, const float* gt_color, const uint8_t* keep, float w_color,
+                                 int use_color, double* depth, double* var, float* rgb, float* d_raw, double* loss,
+                                 void* stream);
 int nsb_tracking_loss(const double* depth, const double* var, const float* color,
                       const float* gt_depth, const float* gt_color, const uint8_t* keep, int64_t N,
                       float w_color, int use_color, int handle_dynamic, double* loss,

@@ -124,6 +124,9 @@ _SIGS = {
     "nsb_composite_mapping": (C.c_int, [C.POINTER(NsbPoints), c_ptr, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                                         c_ptr, C.c_float, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                                         c_ptr]),
+    "nsb_composite_mapping_static": (C.c_int, [C.POINTER(NsbPoints), c_ptr, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr,
+                                               c_ptr, c_ptr, C.c_float, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                                               c_ptr]),
     "nsb_tracking_loss": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_float, C.c_int,
                                     C.c_int, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_adam": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, c_ptr, c_ptr, c_ptr, C.c_float, C.c_float, C.c_float,

@@ -593,3 +593,71 @@ extern "C" int nsb_composite_mapping(const NsbPoints* rays, const double* bound6
         c, gt_depth, gt_color, keep, w_color, use_color, depth, var, rgb, d_raw, partials, ticket, loss);
     return check_launch("k_composite_map");
 }
+
+// ---- allocation-free variant of nsb_composite_mapping ------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernel, same
+// inputs and outputs; its scratch (per-block loss partials + the arrival ticket) lives in ONE file-scope device
+// array of a fixed, modest size that every GPU loading the library holds until exit:
+//     [0, 256)                      the 32-bit ticket (rest of the 256-byte slot unused)
+//     [256, 256 + 8 * MAX_PARTIALS) one fp64 partial sum per 128-thread block (4 rays per block)
+// = 128.25 KiB for NSB_STATIC_MAX_RAYS = 65536 rays per call.
+// In HOST code `g_cm_static_scratch` is only a stand-in for the symbol, not a device address: the address is taken
+// with cudaGetSymbolAddress, once per device, with that device current, and that pointer is what the kernel gets.
+// The array is shared by every call and keeps the last call's contents: the ticket must start at zero, so it is
+// cleared on the caller's stream before every launch (the partials need no clearing: every block writes its slot
+// before the last block reads them).  Calls that overlap on the GPU (two streams, two host threads) RACE on it.
+constexpr long long CM_STATIC_MAX_RAYS = NSB_STATIC_MAX_RAYS;
+constexpr long long CM_STATIC_MAX_PARTIALS = (CM_STATIC_MAX_RAYS * 32 + 127) / 128;
+constexpr size_t CM_STATIC_BYTES = 256 + 8 * (size_t)CM_STATIC_MAX_PARTIALS;
+static __device__ __align__(256) unsigned char g_cm_static_scratch[CM_STATIC_BYTES];
+
+constexpr int CM_STATIC_MAX_DEVICES = 64;
+static unsigned char* g_cm_static_ptr[CM_STATIC_MAX_DEVICES] = {};      // device address of the array, per device ordinal
+
+// device address of the static scratch on the CURRENT device (set-up once per device; no allocation)
+static int cm_static_scratch(unsigned char** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return set_error((int)e, "cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= CM_STATIC_MAX_DEVICES)
+        return set_error(NSB_EINVAL, "nsb_composite_mapping_static: device ordinal %d out of range (max %d)", dev,
+                         CM_STATIC_MAX_DEVICES - 1);
+    if (!g_cm_static_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_cm_static_scratch);
+        if (e != cudaSuccess || !p)
+            return set_error(e != cudaSuccess ? (int)e : NSB_EINVAL, "cudaGetSymbolAddress(static scratch) on device %d: %s",
+                             dev, cudaGetErrorString(e));
+        g_cm_static_ptr[dev] = (unsigned char*)p;
+    }
+    *out = g_cm_static_ptr[dev];
+    return 0;
+}
+
+extern "C" int nsb_composite_mapping_static(const NsbPoints* rays, const double* bound6_host, int stage, int occupancy,
+                                            const float* out_occ0, const float* out_occ1, const float* out_rgb,
+                                            const float* gt_depth, const float* gt_color, const uint8_t* keep,
+                                            float w_color, int use_color, double* depth, double* var, float* rgb,
+                                            float* d_raw, double* loss, void* stream) {
+    CompParams c;
+    if (int rc = comp_params(rays, bound6_host, stage, occupancy, out_occ0, out_occ1, out_rgb, true, c)) return rc;
+    if (!gt_depth || !gt_color || !depth || !var || !rgb || !d_raw || !loss) return set_error(NSB_EINVAL, "null argument");
+    if (c.q.N > CM_STATIC_MAX_RAYS)
+        return set_error(NSB_EINVAL,
+                         "nsb_composite_mapping_static: N = %lld rays exceeds the static scratch limit of %lld rays per call "
+                         "(NSB_STATIC_MAX_RAYS); use nsb_composite_mapping with caller-provided scratch",
+                         (long long)c.q.N, CM_STATIC_MAX_RAYS);
+    if (c.q.N <= 0) return 0;
+    unsigned char* base = nullptr;
+    if (int rc = cm_static_scratch(&base)) return rc;
+    unsigned* ticket = reinterpret_cast<unsigned*>(base);
+    double* partials = reinterpret_cast<double*>(base + 256);
+    cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned), (cudaStream_t)stream);      // must start at zero
+    if (e != cudaSuccess) return set_error((int)e, "cudaMemsetAsync(ticket): %s", cudaGetErrorString(e));
+    const int bs = 128;
+    // an ordinary launch: the kernel's griddepcontrol instructions are no-ops without the programmatic attribute
+    k_composite_map<<<(unsigned)((c.q.N * 32 + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(
+        c, gt_depth, gt_color, keep, w_color, use_color, depth, var, rgb, d_raw, partials, ticket, loss);
+    return check_launch("k_composite_map (static scratch)");
+}
