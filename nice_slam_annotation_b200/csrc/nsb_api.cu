@@ -136,6 +136,48 @@ static void build_tc_table(int32_t* tab) {
                     tab[offW[i] + tc_kmajor_index(n, k, HID)] = enc(C::P_W + i, n * C::in_dim(i) + (i == 3 ? EMB : 0) + k);
         for (int n = 0; n < C::NOUT; ++n)
             for (int k = 0; k < HID; ++k) tab[T::T_WO + tc_kmajor_index(n, k, T::NO)] = enc(C::P_WO, n * HID + k);
+        // backward blocks: rows 0..31 = W_i^T (element (n = input feature, k = output feature) = W_i[k][n]); rows
+        // 32..63 are products of two parameters, written by k_pack_products after this gather
+        const int offG[5] = {-1, T::T_BG1, T::T_BG2, T::T_BG3, T::T_BG4};
+        for (int i = 1; i < 5; ++i)
+            for (int n = 0; n < HID; ++n)
+                for (int k = 0; k < HID; ++k)
+                    tab[offG[i] + tc_kmajor_index(n, k, 64)] = enc(C::P_W + i, k * C::in_dim(i) + (i == 3 ? EMB : 0) + n);
+        for (int n = 0; n < HID; ++n)
+            for (int k = 0; k < C::NOUT; ++k) tab[T::T_BG5 + tc_kmajor_index(n, k, 64)] = enc(C::P_WO, k * HID + n);
+        for (int f = 0; f < EMB; ++f)
+            for (int k = 0; k < HID; ++k) {
+                tab[T::T_BE0 + tc_kmajor_index(f, k, EMB_PAD)] = enc(C::P_W + 0, k * C::in_dim(0) + f);
+                tab[T::T_BE3 + tc_kmajor_index(f, k, EMB_PAD)] = enc(C::P_W + 3, k * C::in_dim(3) + f);
+            }
+    }
+}
+
+// rows 32..63 of the backward blocks: (W_i[:, hidden] Wc_{i-1})^T for i = 1..4 and (Wo Wc_4)^T, own-grid channels
+// (the first 32 columns of Wc; the fine decoder's other 32 are the middle feature, which carries no gradient).
+// One block per product, one thread per element; fp32 FMA in a fixed order.
+template <int KIND>
+__global__ void k_pack_products(const float* const* __restrict__ ptrs, float* __restrict__ blob) {
+    using C = DecCfg<KIND>;
+    using T = TcCfg<KIND>;
+    pdl_launch_dependents();
+    pdl_wait();
+    const int i = blockIdx.x + 1;                              // 1..5
+    const int k = threadIdx.x >> 5, c = threadIdx.x & 31;      // k: output feature of layer i (row of W_i), c: grid channel
+    const float* Wc = ptrs[C::P_WC + i - 1];                   // [32, C_IN]
+    float acc = 0.f;
+    if (i < 5) {
+        const float* W = ptrs[C::P_W + i] + (i == 3 ? EMB : 0);
+        const int ld = C::in_dim(i);
+        for (int j = 0; j < HID; ++j) acc = fmaf(W[k * ld + j], Wc[j * C::C_IN + c], acc);
+        const int off = i == 1 ? T::T_BG1 : (i == 2 ? T::T_BG2 : (i == 3 ? T::T_BG3 : T::T_BG4));
+        blob[C::TOTAL + off + tc_kmajor_index(32 + c, k, 64)] = acc;
+    } else if (k < 8) {
+        if (k < C::NOUT) {
+            const float* Wo = ptrs[C::P_WO];                   // [NOUT, 32]
+            for (int j = 0; j < HID; ++j) acc = fmaf(Wo[k * HID + j], Wc[j * C::C_IN + c], acc);
+        }
+        blob[C::TOTAL + T::T_BG5 + tc_kmajor_index(32 + c, k, 64)] = acc;
     }
 }
 
@@ -347,5 +389,12 @@ extern "C" int nsb_pack_weights(int kind, const float* const* param_ptrs, const 
     int64_t n = nsb_packed_numel(kind);
     if (n < 0) return (int)n;
     launch_pdl(k_pack, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, (cudaStream_t)stream, param_ptrs, table, packed, (int)n);
-    return check_launch("k_pack");
+    if (int rc = check_launch("k_pack")) return rc;
+    switch (kind) {            // the tcgen05 backward blocks hold products of parameters (TcCfg::T_BG*)
+        case KIND_MIDDLE: launch_pdl(k_pack_products<KIND_MIDDLE>, dim3(5), dim3(1024), 0, (cudaStream_t)stream, param_ptrs, packed); break;
+        case KIND_FINE: launch_pdl(k_pack_products<KIND_FINE>, dim3(5), dim3(1024), 0, (cudaStream_t)stream, param_ptrs, packed); break;
+        case KIND_COLOR: launch_pdl(k_pack_products<KIND_COLOR>, dim3(5), dim3(1024), 0, (cudaStream_t)stream, param_ptrs, packed); break;
+        default: return 0;     // coarse: no tcgen05 section
+    }
+    return check_launch("k_pack_products");
 }

@@ -404,6 +404,14 @@ __device__ __forceinline__ void stage_weights(float* sm, const float* __restrict
     __syncthreads();
 }
 
+// floats [begin, end) of the blob to the same offsets of shared memory (both multiples of 4); no barrier
+__device__ __forceinline__ void stage_range(float* sm, const float* __restrict__ packed, int begin, int end) {
+    const float4* src = reinterpret_cast<const float4*>(packed);
+    float4* dst = reinterpret_cast<float4*>(sm);
+    for (int i = begin / 4 + threadIdx.x; i < end / 4; i += blockDim.x) dst[i] = __ldg(src + i);
+}
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 // inputs of a tile: rows, embedding (to shared), features (to registers)
 template <int KIND>
 __device__ __forceinline__ void tile_inputs(const PointsDev& q, const DecTask& T, const float* sm,
@@ -553,7 +561,15 @@ template <int KIND>
 __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, int task, float* sm) {
     using C = DecCfg<KIND>;
     using O = Off<KIND>;
-    stage_weights(sm, T.packed, C::TOTAL);
+    // a decoder that never recomputes its forward here (ReLU signs saved, layer inputs deposited) needs the
+    // constants and the transposed (backward) operand blocks only: 62 of the 131 KB
+    if (T.relu && (!T.dw_scratch || T.x_saved)) {
+        stage_range(sm, T.packed, 0, C::OFF_FWD);
+        stage_range(sm, T.packed, C::OFF_BWD, C::TOTAL);
+        __syncthreads();
+    } else {
+        stage_weights(sm, T.packed, C::TOTAL);
+    }
     pdl_wait();                 // everything below reads what the kernel before this one wrote
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, t = lane & 3;
     float* es = sm + C::TOTAL + warp * E_BUF;
@@ -563,8 +579,27 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, int
     using RC = RecCfg<KIND>;
     (void)ntiles;
     unsigned* ctr = P.ctr + task;
-    for (long long tile = P.tile_begin + next_tile(ctr, lane), nxt; tile < P.tile_end; tile = nxt) {
-        nxt = P.tile_begin + next_tile(ctr, lane);
+    // Tile queue, fetched TWO tiles ahead: the counter's answer (an L2 atomic round trip) is consumed one whole
+    // tile after it was asked for, instead of right away.  Warps over-fetch up to two tickets past the end.
+    long long tile = P.tile_begin + next_tile(ctr, lane);
+    unsigned ticket_next = 0, ticket_after = 0;
+    if (lane == 0) ticket_next = atomicAdd(ctr, 1u);
+    for (long long nxt; tile < P.tile_end; tile = nxt) {
+        if (lane == 0) ticket_after = atomicAdd(ctr, 1u);
+        nxt = P.tile_begin + (long long)__shfl_sync(FULL, ticket_next, 0);
+        ticket_next = ticket_after;
+        // the next tile's first reads (incoming gradient, ReLU signs) and this tile's LAST reads (sample depths of
+        // its rays: the point evaluation is scheduled at its first use, the scatter at the end of the tile) go to L1
+        // now, so that neither waits for L2 when its turn comes
+        if (lane < 8) {
+            const void* a = nullptr;
+            const long long last = P.pts.P - 1;                       // every address is that of a valid point
+            auto pt = [&](long long i) { return i < last ? i : last; };
+            if (lane < 2) a = P.d_raw + 4 * pt(nxt * 16 + 8 * lane);                       // 16 B per point
+            else if (lane < 6) a = T.relu ? T.relu + 8 * pt(nxt * 16 + 4 * (lane - 2)) : nullptr;   // 32 B per point
+            else if (P.pts.z) a = P.pts.z + pt(lane == 6 ? tile * 16 : nxt * 16);          // 8 B per point
+            if (a) prefetch_l1(a);
+        }
         float* rec = T.dw_scratch ? T.dw_scratch + (size_t)(tile - P.tile_begin) * RC::REC : nullptr;
         // incoming gradient first: most tiles behind the surface carry exact zeros
         float dA[1][4];
@@ -1045,14 +1080,17 @@ static void build_dw_tables(DwTables& T) {
 
 }  // namespace nsb
 #include "nsb_decoder_tc.cuh"
+#include "nsb_decoder_bwd_tc.cuh"
 namespace nsb {
 
 // ---- host side -------------------------------------------------------------------------------
 static int g_num_sms = 0;
 static int g_use_tc = 1;         // NSB_TC=0 selects the mma.sync kernels (A/B comparisons)
+static int g_use_tc_bwd = 1;     // NSB_TC_BWD=0 keeps the mma.sync backward under a tcgen05 forward
 static float g_xsaved_cost = 0.62f;  // backward cost of a decoder whose records' X sections the forward deposited: no
                                      // recomputation, but the G sections are still written (NSB_XSAVED_COST)
 static float g_xfwd_cost = 1.4f;     // forward cost of depositing them (NSB_XFWD_COST)
+static float g_tcb_dw_cost = 16.f;   // tcgen05 backward: cost of a decoder that writes records / d(e), others 10 (NSB_TCB_DW_COST)
 static float g_saved_cost = 0.3f; // backward cost of a decoder that skips the recomputation, relative (NSB_SAVED_COST; swept on B200, r01)
 static bool g_attr_done = false;
 constexpr int CTR_SLOTS = 256;                   // launches in flight before a counter slot is reused
@@ -1090,11 +1128,16 @@ static int init_device() {
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(k_decoders_forward_tc, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  TcSmem<KIND_FINE>::S_END * 4);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_decoders_backward_tc, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 TbSmem<KIND_FINE>::S_END * 4);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     if (const char* v = getenv("NSB_TC")) g_use_tc = atoi(v);
+    if (const char* v = getenv("NSB_TC_BWD")) g_use_tc_bwd = atoi(v);
     if (const char* v = getenv("NSB_SAVED_COST")) g_saved_cost = (float)atof(v);
     if (const char* v = getenv("NSB_XSAVED_COST")) g_xsaved_cost = (float)atof(v);
     if (const char* v = getenv("NSB_XFWD_COST")) g_xfwd_cost = (float)atof(v);
+    if (const char* v = getenv("NSB_TCB_DW_COST")) g_tcb_dw_cost = (float)atof(v);
     build_dw_tables<KIND_COARSE>(g_dw_host[0]);
     build_dw_tables<KIND_MIDDLE>(g_dw_host[1]);
     build_dw_tables<KIND_FINE>(g_dw_host[2]);
@@ -1113,7 +1156,7 @@ static int init_device() {
 // decoders of a stage (decoder.py:336-370) and their relative cost per point
 static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp, float* out_occ0,
                        float* out_occ1, float* out_rgb, float* d_point, long long P, unsigned dw_mask = 0,
-                       unsigned x_mask = 0) {
+                       unsigned x_mask = 0, bool tc_bwd = false) {
     int kinds[3], n = 0;
     float cost[3];
     switch (stage) {
@@ -1147,7 +1190,9 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
     // weight-gradient records costs a decoder another 1.35x
     // a decoder without a weight gradient whose forward saved its ReLU signs skips the recomputation
     const bool saved = sp.pts.relu != nullptr && g_use_tc;
-    if (bwd)
+    if (bwd && tc_bwd)      // tcgen05 backward: one chain per decoder; records + d(e) make a trained decoder dearer
+        for (int i = 0; i < n; ++i) cost[i] = (dw_mask & (1u << kinds[i])) ? g_tcb_dw_cost : 10.f;
+    else if (bwd)
         for (int i = 0; i < n; ++i) {
             if (kinds[i] == KIND_FINE) cost[i] = 35.f;
             if (dw_mask & (1u << kinds[i])) cost[i] *= (saved && (x_mask & (1u << kinds[i]))) ? g_xsaved_cost * g_saved_cost / 0.3f : 1.35f;
@@ -1176,7 +1221,7 @@ static int stage_tasks(const NsbScene& sc, int stage, bool bwd, StageParams& sp,
     // tcgen05 forward: a CTA runs whole 128-point tiles, and at 1000 rays a decoder has only 375 of them, 6-11 per
     // CTA -- the kernel lasts max_i ceil(tiles / share_i) * cost_i, which the proportional split misses by up
     // to a tile (measured: 35/55/58 CTAs 115 us, 38/54/56 CTAs 109 us).  Exact search over the splits, cached.
-    if (!bwd && g_use_tc && n >= 2 && !getenv("NSB_FWD_SHARES")) {
+    if ((!bwd || tc_bwd) && g_use_tc && n >= 2 && !getenv(bwd ? "NSB_BWD_SHARES" : "NSB_FWD_SHARES")) {
         struct Key { long long tiles; int n, sms; float c[3]; int share[3]; };
         static thread_local Key cache[8];
         static thread_local int cache_next = 0;
@@ -1387,10 +1432,22 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
                            (flags & NSB_GRAD_POINT) ? d_point : nullptr, sp.pts.P, dwm);
     if (ctas < 0) return ctas;
     // did the forward of these points deposit the X sections of the records into THIS scratch?
+    bool x_dep = false;
     if (dwm && pts->x_scratch == scratch && pts->x_scratch_bytes == scratch_bytes && pts->x_mask == dwm &&
         x_deposit_ok(*pts, sp, (sp.pts.P + 15) / 16)) {
+        x_dep = true;
         ctas = stage_tasks(*scene, stage, true, sp, nullptr, nullptr, nullptr,
                            (flags & NSB_GRAD_POINT) ? d_point : nullptr, sp.pts.P, dwm, dwm);
+        if (ctas < 0) return ctas;
+    }
+    // tcgen05 backward: every decoder of the launch has its ReLU signs from the forward, and the ones whose weights
+    // train found their layer inputs deposited (nothing to recompute); otherwise the mma.sync kernel
+    bool tc_bwd = g_use_tc && g_use_tc_bwd && sp.pts.relu != nullptr && (dwm == 0 || x_dep);
+    for (int i = 0; i < sp.ntask; ++i)
+        if (sp.task[i].kind == KIND_COARSE || !sp.task[i].relu) tc_bwd = false;
+    if (tc_bwd) {
+        ctas = stage_tasks(*scene, stage, true, sp, nullptr, nullptr, nullptr,
+                           (flags & NSB_GRAD_POINT) ? d_point : nullptr, sp.pts.P, dwm, x_dep ? dwm : 0u, true);
         if (ctas < 0) return ctas;
     }
     sp.d_raw = d_raw;
@@ -1438,16 +1495,18 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
         timing_mark(1, 0, (cudaStream_t)stream);
         {
             cudaLaunchConfig_t cfg = {};
-            cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(THREADS);
-            cfg.dynamicSmemBytes = (size_t)smem; cfg.stream = (cudaStream_t)stream;
+            cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(tc_bwd ? TC_THREADS : THREADS);
+            cfg.dynamicSmemBytes = tc_bwd ? (size_t)TbSmem<KIND_FINE>::S_END * 4 : (size_t)smem;
+            cfg.stream = (cudaStream_t)stream;
             cudaLaunchAttribute at[1];
             at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
             at[0].val.programmaticStreamSerializationAllowed = 1;
             cfg.attrs = at; cfg.numAttrs = (pdl && t0 == 0) ? 1 : 0;
-            cudaLaunchKernelEx(&cfg, k_decoders_backward, sp);
+            if (tc_bwd) cudaLaunchKernelEx(&cfg, k_decoders_backward_tc, sp);
+            else cudaLaunchKernelEx(&cfg, k_decoders_backward, sp);
         }
         timing_mark(1, 1, (cudaStream_t)stream);
-        if (int rc = check_launch("k_decoders_backward")) return rc;
+        if (int rc = check_launch(tc_bwd ? "k_decoders_backward_tc" : "k_decoders_backward")) return rc;
 #ifdef NSB_TC_PROFILE
         if (getenv("NSB_TC_PROFILE_PRINT")) {
             long long h[72];

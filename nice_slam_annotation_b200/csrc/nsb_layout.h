@@ -146,7 +146,23 @@ struct TcCfg {
     static constexpr int T_WO = T_W4 + HID * HID;              // R 16 (rows >= NOUT zero), K 32
     static constexpr int T_FWD_END = T_WO + NO * HID;
     static constexpr int W_FWD = T_FWD_END - T_CONST_END;      // forward weight floats
-    static constexpr int TOTAL = ENABLED ? T_FWD_END : 0;
+    // backward operands (k_decoders_backward_tc, nsb_decoder_bwd_tc.cuh).  With da_i = d(a_i) (gradient of the
+    // pre-activation of layer i, da_5 := d(out)) the adjoint chain is  dh_{i-1}' = da_i W_i[:, hidden part]  and the
+    // feature gradient  dc = sum_i dh_i' Wc_{i-1} = sum_i da_i (W_i[:, hidden] Wc_{i-1}):  ONE operand block per
+    // layer, R = 64 rows = [W_i^T (32 input features) ; (W_i Wc_{i-1})^T (32 own-grid channels)], K = 32 (layer
+    // outputs; block 5: K = 8 padded outputs of the head), so a layer is one N = 64 MMA group with A = da_i.  The
+    // product rows are filled by k_pack_products after the gather.  T_BE0 / T_BE3: W_0[:, :93]^T, W_3[:, :93]^T
+    // (R = 96) for d(e) -> d(point), d(B).
+    static constexpr int T_BG1 = T_FWD_END;                    // R 64, K 32: [W_1^T ; (W_1 Wc_0)^T]
+    static constexpr int T_BG2 = T_BG1 + 64 * HID;
+    static constexpr int T_BG3 = T_BG2 + 64 * HID;             // W_3[:, 93:]
+    static constexpr int T_BG4 = T_BG3 + 64 * HID;
+    static constexpr int T_BG5 = T_BG4 + 64 * HID;             // R 64, K 8: [Wo^T ; (Wo Wc_4)^T], outputs >= NOUT zero
+    static constexpr int T_BE0 = T_BG5 + 64 * 8;               // R 96, K 32
+    static constexpr int T_BE3 = T_BE0 + EMB_PAD * HID;
+    static constexpr int T_BWD_END = T_BE3 + EMB_PAD * HID;
+    static constexpr int W_BWD = T_BWD_END - T_FWD_END;        // backward weight floats (14848)
+    static constexpr int TOTAL = ENABLED ? T_BWD_END : 0;
 };
 template <int KIND>
 struct BlobCfg { static constexpr int TOTAL = DecCfg<KIND>::TOTAL + TcCfg<KIND>::TOTAL; };
