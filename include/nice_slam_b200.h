@@ -88,6 +88,10 @@ typedef struct NsbPoints {
     void* x_scratch;
     int64_t x_scratch_bytes;
     uint32_t x_mask;
+    /* optional [P][8] floats (opaque): nsb_decoders_forward leaves every point's fp32 position and normalised
+     * grid coordinate there (it evaluates them in fp64 from rays / depths), nsb_decoders_backward of the SAME
+     * points reads them instead of evaluating them again.  NULL: evaluate. */
+    float* point_cache;
 } NsbPoints;
 
 /* Scene of one call: bound (src/NICE_SLAM.py:188-208), grids, packed decoders. */

@@ -28,7 +28,7 @@ class NsbPoints(C.Structure):
     _fields_ = [("rays_o", c_ptr), ("rays_d", c_ptr), ("rays_o_stride", C.c_int64),
                 ("rays_d_stride", C.c_int64), ("z", c_ptr), ("N", C.c_int64), ("S", C.c_int32),
                 ("p64", c_ptr), ("p32", c_ptr), ("P", C.c_int64), ("relu_masks", c_ptr),
-                ("x_scratch", c_ptr), ("x_scratch_bytes", C.c_int64), ("x_mask", C.c_uint32)]
+                ("x_scratch", c_ptr), ("x_scratch_bytes", C.c_int64), ("x_mask", C.c_uint32), ("point_cache", c_ptr)]
 
 
 class NsbScene(C.Structure):

@@ -56,6 +56,7 @@ struct PointsDev {
     const float* p32;
     long long P;
     unsigned* relu;      // NsbPoints::relu_masks
+    float* pu;           // NsbPoints::point_cache: [P][8] = (p32 xyz, 0, u xyz, 0)
 };
 
 inline PointsDev to_dev(const NsbPoints& p) {
@@ -64,6 +65,7 @@ inline PointsDev to_dev(const NsbPoints& p) {
     d.z = p.z; d.N = p.N; d.S = p.S; d.p64 = p.p64; d.p32 = p.p32;
     d.P = p.rays_o ? p.N * (long long)p.S : p.P;
     d.relu = p.relu_masks;
+    d.pu = p.point_cache;
     return d;
 }
 

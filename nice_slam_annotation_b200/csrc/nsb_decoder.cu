@@ -1090,7 +1090,7 @@ static int g_use_tc_bwd = 1;     // NSB_TC_BWD=0 keeps the mma.sync backward und
 static float g_xsaved_cost = 0.62f;  // backward cost of a decoder whose records' X sections the forward deposited: no
                                      // recomputation, but the G sections are still written (NSB_XSAVED_COST)
 static float g_xfwd_cost = 1.4f;     // forward cost of depositing them (NSB_XFWD_COST)
-static float g_tcb_dw_cost = 16.f;   // tcgen05 backward: cost of a decoder that writes records / d(e), others 10 (NSB_TCB_DW_COST)
+static float g_tcb_dw_cost = 22.f;   // tcgen05 backward: cost of a decoder that writes records / d(e), others 10 (NSB_TCB_DW_COST)
 static float g_saved_cost = 0.3f; // backward cost of a decoder that skips the recomputation, relative (NSB_SAVED_COST; swept on B200, r01)
 static bool g_attr_done = false;
 constexpr int CTR_SLOTS = 256;                   // launches in flight before a counter slot is reused
@@ -1452,6 +1452,7 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
     }
     sp.d_raw = d_raw;
     sp.flags = flags;
+    if (tc_bwd && getenv("NSB_DEBUG_NO_SCATTER")) sp.flags |= 0x80000000u;      // timing experiments: wrong gradients
     const long long ntiles = (sp.pts.P + 15) / 16;
     // decoders whose parameters want a gradient
     int ndw = 0;
@@ -1495,7 +1496,7 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
         timing_mark(1, 0, (cudaStream_t)stream);
         {
             cudaLaunchConfig_t cfg = {};
-            cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(tc_bwd ? TC_THREADS : THREADS);
+            cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(tc_bwd ? TCB_THREADS : THREADS);
             cfg.dynamicSmemBytes = tc_bwd ? (size_t)TbSmem<KIND_FINE>::S_END * 4 : (size_t)smem;
             cfg.stream = (cudaStream_t)stream;
             cudaLaunchAttribute at[1];
@@ -1511,7 +1512,15 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
         if (getenv("NSB_TC_PROFILE_PRINT")) {
             long long h[72];
             cudaMemcpy(h, bprof_dev, sizeof(h), cudaMemcpyDeviceToHost);
-            for (int t = 0; t < sp.ntask; ++t)
+            const char* nm[12] = {"setup", "top", "prologue", "prol barrier", "issue", "wait mma", "epilogue", "barrier",
+                                  "wait de", "dc+coord", "scatter", "de+dp"};
+            for (int t = 0; t < sp.ntask && tc_bwd; ++t)
+                for (int w = 0; w < 2; ++w) {
+                    fprintf(stderr, "[tcbprof] task %d kind %d ctas %d %s:", t, sp.task[t].kind, sp.task[t].cta_count, w ? "thread200" : "thread0");
+                    for (int k = 0; k < 12; ++k) fprintf(stderr, " %s=%lld", nm[k], h[(t * 2 + w) * 12 + k]);
+                    fprintf(stderr, "\n");
+                }
+            for (int t = 0; t < sp.ntask && !tc_bwd; ++t)
                 fprintf(stderr, "[bwdprof] task %d kind %d ctas %d: slowest warp %lld cycles, mean %lld, warps %lld\n", t,
                         sp.task[t].kind, sp.task[t].cta_count, h[36 + 3 * t], h[36 + 3 * t + 1] / (h[36 + 3 * t + 2] ? h[36 + 3 * t + 2] : 1),
                         h[36 + 3 * t + 2]);

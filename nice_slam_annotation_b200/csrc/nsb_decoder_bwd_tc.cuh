@@ -14,7 +14,11 @@
 //    are summed in the epilogue;
 //  * d(e) = da_0 W_0[:, :93] + da_3 W_3[:, :93] (N = 96) only when somebody needs it: d(point) (tracking, BA) or
 //    d(B) of a decoder that trains;
-//  * scatter: a thread adds its 8 channels of dc to the 8 corners with two red.global.add.v4.f32 each;
+//  * scatter: FOUR EXTRA WARPS do nothing else.  The chain threads leave d(c) of a tile and its voxel addressing in a
+//    double-buffered shared-memory image and go on to the next tile; the scatter warps add it to the grid gradient
+//    with red.global.add.v4.f32, 8 lanes x 16 B per 128-byte voxel line (whole lines and sectors, 4 608 000 sectors
+//    per 48 000-point step = the algorithmic count).  The scatter is bound by the SM's write path to L2 (~131 KB per
+//    tile), the chain by tensor-core round trips: they overlap instead of alternating (named barriers 2..5);
 //  * weight gradients: the G sections of the records (d(a_i), d(h_i), d(out), d(e) cos, p) are written from the
 //    epilogue registers in the layout k_dweight reads; 16-point sub-tiles whose incoming gradient is zero are
 //    flagged dead and skipped, whole tiles of zeros are skipped altogether.
@@ -27,6 +31,25 @@
 namespace nsb {
 
 constexpr int TB_DAHI = 0, TB_DALO = 32, TB_GRP = 64, TB_DE = 384;
+constexpr int TCB_SCATTER_WARPS = 4;
+constexpr int TCB_THREADS = TC_THREADS + 32 * TCB_SCATTER_WARPS;     // 512 chain threads + the scatter warps
+constexpr int BAR_CHAIN = 1, BAR_FULL = 2, BAR_EMPTY = 4;            // named barriers (+ buffer index for FULL / EMPTY)
+__device__ __forceinline__ void nbar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void nbar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ int nbar_or(int id, int n, int pred) {
+    int r;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %3, 0;\n\t"
+        "bar.red.or.pred q, %1, %2, p;\n\t"
+        "selp.b32 %0, 1, 0, q;\n\t"
+        "}\n"
+        : "=r"(r)
+        : "r"(id), "r"(n), "r"(pred)
+        : "memory");
+    return r;
+}
 __device__ __forceinline__ constexpr int tb_group(int i) { return TB_GRP + 64 * (5 - i); }     // i = 5..1
 
 template <int KIND>
@@ -35,11 +58,11 @@ struct TbSmem {      // float offsets in dynamic shared memory
     static constexpr int S_BV = 0;                             // embedding matrix as [96] x float4
     static constexpr int S_WHI = 384;                          // 128-byte aligned
     static constexpr int S_WLO = S_WHI + T::W_BWD;
-    static constexpr int S_TRI = S_WLO + T::W_BWD;             // per point: voxel base / steps / coordinates / border bits
-    static constexpr int S_PT = S_TRI + 128 * TRI_WORDS;       // per point: p (fp32), valid
-    static constexpr int S_DP = S_PT + 128 * 4;                // per part and point: partial d(point) [4][128][4]
-    static constexpr int S_DC = S_DP + 4 * 128 * 4;            // d(c) of the tile [128][32], 16-byte chunks XOR-swizzled by row
-    static constexpr int S_END = S_DC + 128 * CDIM;
+    static constexpr int S_TRI = S_WLO + T::W_BWD;             // x2: per point: clipped coordinate / floor / border flags
+    static constexpr int S_PT = S_TRI + 2 * 128 * TRI_WORDS;   // x2: per point: p (fp32), valid
+    static constexpr int S_DP = S_PT + 2 * 128 * 4;            // per part and point: partial d(point) [4][128][4]
+    static constexpr int S_DC = S_DP + 4 * 128 * 4;            // x2: d(c) of the tile [128][32], 16-byte chunks XOR-swizzled by row
+    static constexpr int S_END = S_DC + 2 * 128 * CDIM;
 };
 
 // one axis of a point: fp32 position (embedding input) and normalised grid coordinate, as tc_load_point evaluates them
@@ -89,6 +112,7 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint32_t tmem_slot;
     __shared__ long long s_tile[2];
+    __shared__ long long s_cmd[2];                             // tile whose image is in buffer b, or -1: no more tiles
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int quad = warp & 3, part = warp >> 2;
     const int row = 32 * quad + lane;
@@ -111,7 +135,7 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
     // the d(e) blocks are the last 2 x 3072 floats: skipped when nobody needs d(e)
     const int w_floats = need_de ? TT::W_BWD : TT::T_BE0 - TT::T_FWD_END;
 #pragma unroll 4
-    for (int i = tid; i < w_floats / 4; i += TC_THREADS) {
+    for (int i = tid; i < w_floats / 4; i += TCB_THREADS) {
         const float4 w = __ldg(reinterpret_cast<const float4*>(blob + TT::T_FWD_END) + i);
         uint32_t h[4], l[4];
         split_tf32(w.x, h[0], l[0]); split_tf32(w.y, h[1], l[1]);
@@ -127,10 +151,44 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
     const uint32_t tbase = tmem_slot;
     const uint32_t lane_base = tc::tmem_addr(tbase, 32 * quad, 0);
     const float4* Bv = reinterpret_cast<const float4*>(sm + S::S_BV);
-    float4* s_pt = reinterpret_cast<float4*>(sm + S::S_PT);
-    float* s_tri = sm + S::S_TRI;
+    float4* const s_pt0 = reinterpret_cast<float4*>(sm + S::S_PT);
+    float* const s_tri0 = sm + S::S_TRI;
     float4* s_dp = reinterpret_cast<float4*>(sm + S::S_DP);
-    float4* s_dc = reinterpret_cast<float4*>(sm + S::S_DC);
+    float4* const s_dc0 = reinterpret_cast<float4*>(sm + S::S_DC);
+    // ---- the scatter warps -------------------------------------------------------------------------------------
+    if (warp >= TC_THREADS / 32) {
+        if (want_grid) {
+            const int sub = lane & 7, sw = warp - TC_THREADS / 32;
+            for (int b = 0;; b ^= 1) {
+                nbar_sync(BAR_FULL + b, TCB_THREADS);              // image b is complete
+                if (s_cmd[b] < 0) break;
+                const float4* s_pt = s_pt0 + b * 128;
+                const float* s_tri = s_tri0 + b * 128 * TRI_WORDS;
+                const float4* s_dc = s_dc0 + b * 128 * 8;
+#pragma unroll 1
+                for (int r = 0; r < 128 / (4 * TCB_SCATTER_WARPS); ++r) {
+                    const int q = (r * TCB_SCATTER_WARPS + sw) * 4 + (lane >> 3);
+                    if (s_pt[q].w == 0.f) continue;                     // beyond the batch
+                    int mb;
+                    const Tri t = tb_read_tri(s_tri + q * TRI_WORDS, T.own, mb);
+                    const float4 v = s_dc[q * 8 + (sub ^ (q & 7))];
+                    float* g0 = T.own.grad + 4 * sub;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const float w = tri_weight(t, k);
+                        if (!(P.flags & 0x80000000u))      // NSB_DEBUG_NO_SCATTER (timing experiments only)
+                            red_add_v4(g0 + (size_t)tri_offset(t, k) * CDIM, w * v.x, w * v.y, w * v.z, w * v.w);
+                    }
+                }
+                nbar_arrive(BAR_EMPTY + b, TCB_THREADS);           // image b may be overwritten
+            }
+        }
+        tc::fence_before_sync();
+        __syncthreads();
+        return;
+    }
+    // ---- the chain threads -------------------------------------------------------------------------------------
+    int nlive = 0;                                                 // live tiles so far: image buffer = nlive & 1
     const uint32_t whi = tc::smem_u32(sm + S::S_WHI), wlo = tc::smem_u32(sm + S::S_WLO);
     auto wdesc = [&](uint32_t base, int off_floats, int R) {
         return tc::kmajor_desc(base + 4u * (uint32_t)(off_floats - TT::T_FWD_END), R, 0);
@@ -142,6 +200,13 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
     const long long ntiles = (P.pts.P + 127) / 128;
     long long tile = s_tile[0];
     int slot = 0;
+#ifdef NSB_TC_PROFILE
+    long long tq[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
+#define TQB(k) { const long long tn_ = clock64(); tq[k] += tn_ - tlast; tlast = tn_; }
+#else
+#define TQB(k)
+#endif
+    TQB(0)     // set-up
     // incoming gradient d(out) of my point (every part reads it: 16 B, L1 serves three of four), fetched one tile ahead
     float4 dv_next = make_float4(0.f, 0.f, 0.f, 0.f);
     if (tile * 128 + row < P.pts.P) dv_next = __ldg(reinterpret_cast<const float4*>(P.d_raw) + tile * 128 + row);
@@ -158,7 +223,8 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
         const bool live_pt = dout[0] != 0.f || dout[1] != 0.f || dout[2] != 0.f;
         const unsigned live_bits = __ballot_sync(FULL, live_pt);      // lanes 0..15: sub-tile 2 quad, 16..31: 2 quad + 1
         const bool sub_live = ((lane < 16 ? live_bits & 0xffffu : live_bits >> 16) != 0u);
-        const int tile_live = __syncthreads_or(live_bits != 0u);      // also: every thread is done with the previous tile
+        const int tile_live = nbar_or(BAR_CHAIN, TC_THREADS, live_bits != 0u);      // also: every chain thread is done with the previous tile
+        TQB(1) // tile top: d(out), liveness vote
         if (tid == 0) s_tile[slot] = (long long)atomicAdd(P.ctr + task, 1u);     // the tile after next
         float* rec = nullptr;                                          // my 16-point record (live sub-tiles only)
         if (rec_base && part == 0 && (lane & 15) == 0 && i < (P.pts.P + 15) / 16 * 16)
@@ -168,18 +234,25 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
             if (want_point && part == 0 && ok) {
                 T.d_point[3 * i] = 0.f; T.d_point[3 * i + 1] = 0.f; T.d_point[3 * i + 2] = 0.f;
             }
-            __syncthreads();           // thread 0's refill of s_tile[slot] is read at the top of the next iteration
+            nbar_sync(BAR_CHAIN, TC_THREADS);      // thread 0's refill of s_tile[slot] is read at the top of the next iteration
             tile = nxt;
             slot ^= 1;
             continue;
         }
         // ---- prologue: d(out) as the first A operand, the point and its voxel addressing -----------------------
         const int r16 = row & 15;
+        const int buf = nlive & 1;
+        float4* s_pt = s_pt0 + buf * 128;
+        float* s_tri = s_tri0 + buf * 128 * TRI_WORDS;
+        float4* s_dc = s_dc0 + buf * 128 * 8;
+        if (want_grid && nlive >= 2) nbar_sync(BAR_EMPTY + buf, TCB_THREADS);      // the scatter warps are done with this image
+        ++nlive;
         if (part == 0) st_split8(lane_base, TB_DAHI, TB_DALO, dout);
         if (part < 3) {          // parts 0..2: one axis of the point each (the fp64 evaluation is the slow part)
             const long long ii = ok ? i : P.pts.P - 1;
             float p32a, ua, ic, f0, mult;
-            tb_point_axis<KIND>(P.pts, T, ii, part, p32a, ua);
+            if (P.pts.pu) { p32a = P.pts.pu[8 * ii + part]; ua = P.pts.pu[8 * ii + 4 + part]; }      // left by the forward
+            else tb_point_axis<KIND>(P.pts, T, ii, part, p32a, ua);
             tri_axis(ua, part == 0 ? T.own.X : (part == 1 ? T.own.Y : T.own.Z), ic, f0, mult);
             float* e = s_tri + row * TRI_WORDS;
             e[part] = ic; e[3 + part] = f0; e[6 + part] = mult;
@@ -198,7 +271,9 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
         if (ok) rb = __ldg(reinterpret_cast<const uint2*>(T.relu) + i * 4 + part);
         tc::tmem_st_wait();
         tc::fence_before_sync();
-        __syncthreads();
+        TQB(2) // prologue: first operand, point axis
+        nbar_sync(BAR_CHAIN, TC_THREADS);
+        TQB(3) // prologue barrier
         if (rec && part == 1) {      // record section p [16][8]
             const float4 pp = s_pt[row];
             const float pr[8] = {pp.x, pp.y, pp.z, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -213,9 +288,11 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
         // ---- the chain: round i applies the ReLU of layer i to d(h_{i+1}) = first half of group i + 1 ---------------
 #pragma unroll 1
         for (int i = 4; i >= 0; --i) {
+            TQB(4) // issue (warp 0) / nothing
             tc::mbar_wait(&bar, par);
             par ^= 1;
             tc::fence_after_sync();
+            TQB(5) // wait for the layer's MMA group
             float a[8];
             tc::tmem_ld8(lane_base + tb_group(i + 1) + hc, a);
             tc::tmem_ld_wait();
@@ -229,7 +306,9 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
             if (issue) st_split8(lane_base, TB_DAHI + hc, TB_DALO + hc, a);
             tc::tmem_st_wait();
             tc::fence_before_sync();
-            __syncthreads();
+            TQB(6) // layer epilogue: ld, mask, records, st
+            nbar_sync(BAR_CHAIN, TC_THREADS);
+            TQB(7) // layer barrier
             if (issue && warp == 0 && tc::elect_one()) {
                 tc::fence_after_sync();
                 if (i >= 1) {
@@ -250,6 +329,7 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
             par ^= 1;
             tc::fence_after_sync();
         }
+        TQB(8) // last issue + wait for d(e)
         // ---- d(c): the five parts, my 8 channels -------------------------------------------------------------
         float dc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -291,26 +371,14 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
             dp[1] = gy * ((mbits & 2) ? (float)(T.own.Y - 1) / 2 : 0.f) * (float)(2.0 / T.ext[1]);
             dp[2] = gz * ((mbits & 4) ? (float)(T.own.Z - 1) / 2 : 0.f) * (float)(2.0 / T.ext[2]);
         }
-        // ---- scatter (adjoint of the trilinear gather): 8 lanes x 16 B cover one 128-byte voxel line per request, four
-        //      points per warp per round -- whole lines and whole sectors, like the forward's gather
+        TQB(9) // d(c) sum, shared-memory image, coordinate gradient
+        // ---- hand the image (d(c), voxel addressing, validity) of this tile to the scatter warps -----------------------
         if (want_grid) {
-            __syncthreads();
-            const int sub = lane & 7;
-#pragma unroll 1
-            for (int r = 0; r < 128 / (4 * (TC_THREADS / 32)); ++r) {
-                const int q = (r * (TC_THREADS / 32) + warp) * 4 + (lane >> 3);
-                if (s_pt[q].w == 0.f) continue;                         // beyond the batch
-                int mb;
-                const Tri t = tb_read_tri(s_tri + q * TRI_WORDS, T.own, mb);
-                const float4 v = s_dc[q * 8 + (sub ^ (q & 7))];
-                float* g0 = T.own.grad + 4 * sub;
-#pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    const float w = tri_weight(t, k);
-                    red_add_v4(g0 + (size_t)tri_offset(t, k) * CDIM, w * v.x, w * v.y, w * v.z, w * v.w);
-                }
-            }
+            if (tid == 0) s_cmd[buf] = tile;
+            __threadfence_block();
+            nbar_arrive(BAR_FULL + buf, TCB_THREADS);
         }
+        TQB(10) // hand-over to the scatter warps
         // ---- d(e) cos(p B): -> d(point) through B, and the record section d(B) is computed from -----------------
         if (need_de) {
             const float4 pp = s_pt[row];
@@ -334,7 +402,7 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
         }
         if (want_point) {              // the four parts of a point add up through shared memory
             s_dp[part * 128 + row] = make_float4(dp[0], dp[1], dp[2], 0.f);
-            __syncthreads();
+            nbar_sync(BAR_CHAIN, TC_THREADS);
             if (part == 0 && ok) {
                 const float4 a0 = s_dp[row], a1 = s_dp[128 + row], a2 = s_dp[256 + row], a3 = s_dp[384 + row];
                 T.d_point[3 * i] = (a0.x + a1.x) + (a2.x + a3.x);
@@ -343,15 +411,27 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
             }
         }
         tc::fence_before_sync();       // my tensor-memory reads are complete before the next tile's MMAs (after its barrier)
+        TQB(11) // d(e) epilogue, d(point)
         tile = nxt;
         slot ^= 1;
     }
+    if (want_grid) {               // no more tiles: release the scatter warps (they wait on the next image)
+        const int buf = nlive & 1;
+        if (nlive >= 2) nbar_sync(BAR_EMPTY + buf, TCB_THREADS);
+        if (tid == 0) s_cmd[buf] = -1;
+        __threadfence_block();
+        nbar_arrive(BAR_FULL + buf, TCB_THREADS);
+    }
+#ifdef NSB_TC_PROFILE
+    if ((tid == 0 || tid == 200) && (int)blockIdx.x == T.cta_begin && P.prof)
+        for (int k = 0; k < 12; ++k) P.prof[(task * 2 + (tid != 0)) * 12 + k] = tq[k];
+#endif
     tc::fence_before_sync();
     __syncthreads();
     if (warp == 0) tc::tmem_dealloc<512>(tbase);
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(TCB_THREADS, 1)
 k_decoders_backward_tc(const __grid_constant__ StageParams P) {
     extern __shared__ __align__(16) float sm[];
     pdl_launch_dependents();     // k_dweight / k_ray_grad_reduce may be scheduled as CTAs of this kernel retire

@@ -294,6 +294,11 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             long long i_;
             tc_load_point<KIND>(P.pts, T, t, row, p32, u, ok_, i_);
             s_pt[row] = make_float4(p32[0], p32[1], p32[2], 0.f);
+            if (task == 0 && P.pts.pu && ok_) {      // the stage's first decoder leaves them for the backward (all share the bound)
+                float4* c4 = reinterpret_cast<float4*>(P.pts.pu + 8 * i_);
+                c4[0] = make_float4(p32[0], p32[1], p32[2], 0.f);
+                c4[1] = make_float4(u[0], u[1], u[2], 0.f);
+            }
             tc_publish_tri(T.own, u, s_tri, row);
             if constexpr (KIND == KIND_FINE) tc_publish_tri(T.aux, u, s_tri + 128 * TRI_WORDS, row);
         }

@@ -23,6 +23,7 @@ struct Ws {
     double* z;
     float *occ0, *occ1, *rgb, *d_raw, *d_point, *d_dnorm;
     uint32_t* relu;     // [3][P][8] ReLU sign words, forward -> backward
+    float* pu;          // [P][8] point cache (fp32 position, normalised coordinate), forward -> backward
     uint32_t* ticket;   // fused mapping loss: arrival counter (zeroed by k_sample_z) ...
     double* partials;   // ... and per-block partial sums
 };
@@ -44,6 +45,7 @@ static Ws carve_ws(void* base, int64_t N, int S) {
     w.d_point = c.take<float>(9 * P);
     w.d_dnorm = c.take<float>(3 * N);
     w.relu = c.take<uint32_t>(24 * P);
+    w.pu = c.take<float>(8 * P);
     w.ticket = c.take<uint32_t>(64);
     w.partials = c.take<double>(N / 4 + 1);
     return w;
@@ -250,7 +252,7 @@ extern "C" int64_t nsb_render_workspace_bytes(int64_t N, int S) {
     const int64_t P = N * S;
     // depth_max, z, occ0, occ1, rgb, d_raw, d_point (3 planes), d_dnorm, each rounded to 256 B
     // ... relu sign words, ticket, loss partials
-    return 256 * 13 + 256 + P * 8 + P * 4 * 2 + P * 16 * 2 + P * 36 + N * 12 + P * 96 + 256 + (N / 4 + 1) * 8;
+    return 256 * 14 + 256 + P * 8 + P * 4 * 2 + P * 16 * 2 + P * 36 + N * 12 + P * 96 + P * 32 + 256 + (N / 4 + 1) * 8;
 }
 
 extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
@@ -274,6 +276,7 @@ extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
                                r->u, dmax, w.z, fused_loss ? w.ticket : nullptr, r->keep, stream)) return rc;
     NsbPoints pts = ray_pts(r, w.z, S);
     pts.relu_masks = w.relu;
+    pts.point_cache = w.pu;
     float *o0, *o1, *rgb;
     stage_planes(r->stage, w, o0, o1, rgb);
     pdl_allow_next(true);         // the decoder kernel's prologue may overlap k_sample_z
@@ -292,6 +295,7 @@ extern "C" int nsb_render_backward(const NsbRenderCall* r, void* stream) {
     const double* b6 = &r->scene.bound[0][0];
     NsbPoints pts = ray_pts(r, w.z, S);
     pts.relu_masks = w.relu;             // written by nsb_render_forward of this call
+    pts.point_cache = w.pu;
     float *o0, *o1, *rgb;
     stage_planes(r->stage, w, o0, o1, rgb);
     const bool want_rays = (r->flags & NSB_GRAD_POINT) != 0;
