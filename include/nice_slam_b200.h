@@ -88,9 +88,10 @@ typedef struct NsbPoints {
     void* x_scratch;
     int64_t x_scratch_bytes;
     uint32_t x_mask;
-    /* optional [P][8] floats (opaque): nsb_decoders_forward leaves every point's fp32 position and normalised
-     * grid coordinate there (it evaluates them in fp64 from rays / depths), nsb_decoders_backward of the SAME
-     * points reads them instead of evaluating them again.  NULL: evaluate. */
+    /* optional [P][8] floats (opaque): every point's fp32 position and normalised grid coordinate, evaluated in
+     * fp64 from rays and depths.  As the rays argument of nsb_sample_z's render-call variant (nsb_render_forward) the
+     * sampler fills it for the depths it writes; nsb_decoders_forward / nsb_decoders_backward of those points then
+     * read it instead of evaluating the points per decoder.  Scene bound only (not the coarse decoder's).  NULL: evaluate. */
     float* point_cache;
 } NsbPoints;
 

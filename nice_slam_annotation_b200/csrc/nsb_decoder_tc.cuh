@@ -144,7 +144,11 @@ __device__ __forceinline__ void tc_load_point(const PointsDev& q, const DecTask&
     i = tile * 128 + row;
     ok = i < q.P;
     const long long ii = ok ? i : q.P - 1;
-    if (q.ro == nullptr && q.p32 != nullptr) {
+    if (q.pu) {                 // evaluated once per point by k_sample_z (NsbPoints::point_cache)
+        const float4 a4 = __ldg(reinterpret_cast<const float4*>(q.pu + 8 * ii)), b4 = __ldg(reinterpret_cast<const float4*>(q.pu + 8 * ii) + 1);
+        p32[0] = a4.x; p32[1] = a4.y; p32[2] = a4.z;
+        u[0] = b4.x; u[1] = b4.y; u[2] = b4.z;
+    } else if (q.ro == nullptr && q.p32 != nullptr) {
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
             p32[a] = q.p32[3 * ii + a];
@@ -294,11 +298,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             long long i_;
             tc_load_point<KIND>(P.pts, T, t, row, p32, u, ok_, i_);
             s_pt[row] = make_float4(p32[0], p32[1], p32[2], 0.f);
-            if (task == 0 && P.pts.pu && ok_) {      // the stage's first decoder leaves them for the backward (all share the bound)
-                float4* c4 = reinterpret_cast<float4*>(P.pts.pu + 8 * i_);
-                c4[0] = make_float4(p32[0], p32[1], p32[2], 0.f);
-                c4[1] = make_float4(u[0], u[1], u[2], 0.f);
-            }
+
             tc_publish_tri(T.own, u, s_tri, row);
             if constexpr (KIND == KIND_FINE) tc_publish_tri(T.aux, u, s_tri + 128 * TRI_WORDS, row);
         }

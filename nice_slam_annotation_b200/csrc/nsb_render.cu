@@ -270,13 +270,14 @@ extern "C" int nsb_render_forward(const NsbRenderCall* r, void* stream) {
         dmax = w.depth_max;
     }
     NsbPoints rays = ray_pts(r, nullptr, 0);
+    rays.point_cache = r->stage == NSB_STAGE_COARSE ? nullptr : w.pu;      // the coarse decoder has its own (enlarged) bound
     const bool fused_loss = r->loss != nullptr;
     if (fused_loss && (!r->gt_depth || !r->gt_color)) return set_error(NSB_EINVAL, "fused mapping loss needs gt_depth and gt_color");
     if (int rc = sample_z_impl(&rays, r->gt_depth, b6, r->N_samples, Nf, r->lindisp, r->t_uniform, r->t_surface,
                                r->u, dmax, w.z, fused_loss ? w.ticket : nullptr, r->keep, stream)) return rc;
     NsbPoints pts = ray_pts(r, w.z, S);
     pts.relu_masks = w.relu;
-    pts.point_cache = w.pu;
+    pts.point_cache = rays.point_cache;
     float *o0, *o1, *rgb;
     stage_planes(r->stage, w, o0, o1, rgb);
     pdl_allow_next(true);         // the decoder kernel's prologue may overlap k_sample_z
@@ -295,7 +296,7 @@ extern "C" int nsb_render_backward(const NsbRenderCall* r, void* stream) {
     const double* b6 = &r->scene.bound[0][0];
     NsbPoints pts = ray_pts(r, w.z, S);
     pts.relu_masks = w.relu;             // written by nsb_render_forward of this call
-    pts.point_cache = w.pu;
+    pts.point_cache = r->stage == NSB_STAGE_COARSE ? nullptr : w.pu;
     float *o0, *o1, *rgb;
     stage_planes(r->stage, w, o0, o1, rgb);
     const bool want_rays = (r->flags & NSB_GRAD_POINT) != 0;

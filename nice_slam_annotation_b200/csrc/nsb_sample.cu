@@ -270,6 +270,22 @@ __global__ void __launch_bounds__(256) k_sample_z(PointsDev q, const float* __re
         }
     }
     z_out[r * (long long)S + rank] = v;
+    if (q.pu) {
+        // point cache for the decoder kernels (NsbPoints::point_cache): p = o + d z in fp64, un-fused, as torch evaluates
+        // Renderer.py:227-228, its fp32 value (the embedding input, decoder.py:204) and the normalised grid coordinate
+        // (common.py:280-295) -- the expressions of ray_point / tc_load_point, evaluated once per point here instead of
+        // once per point and decoder there
+        float* c = q.pu + 8 * (r * (long long)S + rank);
+        float p32[3], un[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const double p = __dadd_rn((double)q.ro[r * q.so + a], __dmul_rn((double)q.rd[r * q.sd + a], v));
+            p32[a] = (float)p;
+            un[a] = (float)__dsub_rn(__dmul_rn(__ddiv_rn(__dsub_rn(p, bound.lo[a]), __dsub_rn(bound.hi[a], bound.lo[a])), 2.0), 1.0);
+        }
+        reinterpret_cast<float4*>(c)[0] = make_float4(p32[0], p32[1], p32[2], 0.f);
+        reinterpret_cast<float4*>(c)[1] = make_float4(un[0], un[1], un[2], 0.f);
+    }
 }
 
 // sample_pdf (common.py:19-63) on bins = mid(z), weights = w[1:-1]; then the sort-merge of
