@@ -93,6 +93,14 @@ typedef struct NsbPoints {
      * sampler fills it for the depths it writes; nsb_decoders_forward / nsb_decoders_backward of those points then
      * read it instead of evaluating the points per decoder.  Scene bound only (not the coarse decoder's).  NULL: evaluate. */
     float* point_cache;
+    /* optional (ray-sharded mapping): one BYTE per 128-byte line of the flat gradient bucket that starts at
+     * line_marks_base, at byte 128 + (byte offset >> 7) of line_marks; its first word = "marks are valid".
+     * The tcgen05 backward writes 1 for the voxel lines it scatters into (plain stores) and sets the first word;
+     * any other backward path clears the first word.  nsb_bucket_allreduce_sparse (NsbPeers.line_marks) then reads
+     * 32 bytes per 4 KB unit instead of scanning the unit, and clears them.  Local device memory of
+     * 128 + bucket bytes / 128 bytes, zero-initialised by the caller once. */
+    uint32_t* line_marks;
+    const float* line_marks_base;
 } NsbPoints;
 
 /* Scene of one call: bound (src/NICE_SLAM.py:188-208), grids, packed decoders. */
@@ -302,6 +310,15 @@ typedef struct NsbRenderCall {
      * dweight_mask, scratch and this field must then be the same in the forward and the backward call of
      * a step (they are when one struct serves both), and scratch must hold the whole batch. */
     int32_t deposit_dweight_inputs;
+    /* optional, ray-sharded mapping: see NsbPoints.line_marks / line_marks_base */
+    uint32_t* line_marks;
+    const float* line_marks_base;
+    /* nsb_render_backward in two calls, so that a caller can start the exchange of the grid gradients between them
+     * (they are complete after phase 1): 0 = everything (default), 1 = compositing adjoint + decoder backward only,
+     * 2 = only the weight-gradient kernels of a phase-1 call with the same struct (needs deposit_dweight_inputs).
+     * dweight_max_ctas > 0 caps their grid (leaves SMs to a concurrent exchange kernel). */
+    int32_t dweight_phase;
+    int32_t dweight_max_ctas;
 } NsbRenderCall;
 
 /* One ray batch (contiguous [n,3] / [n] device tensors, n <= N) into the fixed-shape input buffers of a
@@ -447,6 +464,9 @@ typedef struct NsbPeers {
     float* scalar[NSB_MAX_PEERS];     /* nsb_depth_max_peers only: a symmetric, zero-initialised pad of 64 words per rank */
     uint32_t* touched[NSB_MAX_PEERS]; /* nsb_bucket_allreduce_sparse only: per-rank symmetric scratch of
                                        * nsb_exchange_touched_words(bucket floats) words, mapped like bucket */
+    uint32_t* line_marks;             /* optional, LOCAL: NsbPoints.line_marks of the backward that filled bucket[rank] */
+    int64_t line_marks_floats;        /* leading floats of the bucket the marks cover (the grid segments); the rest
+                                       * (decoder weight gradients) is scanned */
 } NsbPeers;
 int64_t nsb_exchange_signal_words(void);
 
@@ -467,6 +487,9 @@ int64_t nsb_exchange_touched_words(int64_t n);
 int nsb_depth_max_peers(const NsbPeers* peers, const float* gt_depth, const uint8_t* keep, int64_t N,
                         float* out, void* stream);
 int nsb_bucket_allreduce_sparse(const NsbPeers* peers, int64_t offset, int64_t n, void* stream);
+/* The same with at most max_ctas CTAs (0: the default of nsb_bucket_allreduce_sparse): an exchange that runs beside
+ * another kernel and should leave it most of the SMs.  Every rank must pass the same value. */
+int nsb_bucket_allreduce_sparse_ctas(const NsbPeers* peers, int64_t offset, int64_t n, int max_ctas, void* stream);
 
 /* The same reduction fused with the mapper's Adam step (src/Mapper.py:462-482, 633-642; semantics of
  * nsb_adam): rank r sums the r-th slice of bucket[offset, offset + n), updates

@@ -28,7 +28,8 @@ class NsbPoints(C.Structure):
     _fields_ = [("rays_o", c_ptr), ("rays_d", c_ptr), ("rays_o_stride", C.c_int64),
                 ("rays_d_stride", C.c_int64), ("z", c_ptr), ("N", C.c_int64), ("S", C.c_int32),
                 ("p64", c_ptr), ("p32", c_ptr), ("P", C.c_int64), ("relu_masks", c_ptr),
-                ("x_scratch", c_ptr), ("x_scratch_bytes", C.c_int64), ("x_mask", C.c_uint32), ("point_cache", c_ptr)]
+                ("x_scratch", c_ptr), ("x_scratch_bytes", C.c_int64), ("x_mask", C.c_uint32), ("point_cache", c_ptr),
+                ("line_marks", c_ptr), ("line_marks_base", c_ptr)]
 
 
 class NsbScene(C.Structure):
@@ -48,7 +49,8 @@ class NsbRenderCall(C.Structure):
                 ("flags", C.c_uint32), ("dweight_mask", C.c_uint32), ("d_weight", c_ptr * 4),
                 ("scratch", c_ptr), ("scratch_bytes", C.c_int64), ("g_rays_o", c_ptr), ("g_rays_d", c_ptr),
                 ("gt_color", c_ptr), ("w_color", C.c_float), ("use_color", C.c_int32), ("loss", c_ptr),
-                ("deposit_dweight_inputs", C.c_int32)]
+                ("deposit_dweight_inputs", C.c_int32), ("line_marks", c_ptr), ("line_marks_base", c_ptr),
+                ("dweight_phase", C.c_int32), ("dweight_max_ctas", C.c_int32)]
 
 
 class NsbImapDecoder(C.Structure):
@@ -67,7 +69,7 @@ class NsbPeers(C.Structure):
     _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("bucket", c_ptr * NSB_MAX_PEERS),
                 ("bucket_multicast", c_ptr), ("param", c_ptr * NSB_MAX_PEERS), ("param_multicast", c_ptr),
                 ("signal", c_ptr * NSB_MAX_PEERS), ("error", c_ptr), ("scalar", c_ptr * NSB_MAX_PEERS),
-                ("touched", c_ptr * NSB_MAX_PEERS)]
+                ("touched", c_ptr * NSB_MAX_PEERS), ("line_marks", c_ptr), ("line_marks_floats", C.c_int64)]
 
 
 _SIGS = {
@@ -144,6 +146,7 @@ _SIGS = {
     "nsb_exchange_touched_words": (C.c_int64, [C.c_int64]),
     "nsb_depth_max_peers": (C.c_int, [C.POINTER(NsbPeers), c_ptr, c_ptr, C.c_int64, c_ptr, c_ptr]),
     "nsb_bucket_allreduce_sparse": (C.c_int, [C.POINTER(NsbPeers), C.c_int64, C.c_int64, c_ptr]),
+    "nsb_bucket_allreduce_sparse_ctas": (C.c_int, [C.POINTER(NsbPeers), C.c_int64, C.c_int64, C.c_int, c_ptr]),
     "nsb_bucket_reduce_adam": (C.c_int, [C.POINTER(NsbPeers), C.c_int64, C.c_int64, C.c_int64, c_ptr, c_ptr, c_ptr,
                                          c_ptr, c_ptr, C.c_float, C.c_float, C.c_float, c_ptr]),
     "nsb_imap_workspace_floats": (C.c_int64, [C.c_int64, C.c_int, C.c_int]),

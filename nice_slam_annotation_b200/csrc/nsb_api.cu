@@ -26,6 +26,9 @@ int check_launch(const char* what) {
     return 0;
 }
 
+static thread_local int g_dw_cap = 0;
+void dweight_grid_cap(int ctas) { g_dw_cap = ctas; }
+int dweight_grid_cap_take() { const int v = g_dw_cap; g_dw_cap = 0; return v; }
 static thread_local bool g_pdl_next = false;
 static int g_pdl_enabled = -1;
 bool pdl_enabled() {

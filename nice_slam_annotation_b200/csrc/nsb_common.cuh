@@ -19,6 +19,10 @@ int check_launch(const char* what);
 // decoder kernel (k_sample_z, k_composite_*) does not produce what the decoder kernel's prologue reads (packed
 // weights, tile counters), so they allow the next decoder launch to start while that kernel drains; the
 // decoder kernels call pdl_wait() before they touch anything else.  Other callers get ordinary launches.
+// nsb_render_backward in two calls (NsbRenderCall::dweight_phase): internal bits of nsb_decoders_backward's flags
+constexpr unsigned NSB_FLAG_DEFER_DWEIGHT = 0x40000000u;     // decoder backward only
+constexpr unsigned NSB_FLAG_ONLY_DWEIGHT = 0x20000000u;      // weight-gradient kernels only
+void dweight_grid_cap(int ctas);     // 0: no cap; read (and reset) by the next nsb_decoders_backward of this thread
 void pdl_allow_next(bool on);
 bool pdl_take();
 bool pdl_enabled();              // NSB_PDL=0 turns every programmatic launch into an ordinary one
@@ -57,6 +61,8 @@ struct PointsDev {
     long long P;
     unsigned* relu;      // NsbPoints::relu_masks
     float* pu;           // NsbPoints::point_cache: [P][8] = (p32 xyz, 0, u xyz, 0)
+    unsigned* marks;     // NsbPoints::line_marks (word 0: valid flag), or NULL
+    const float* marks_base;
 };
 
 inline PointsDev to_dev(const NsbPoints& p) {
@@ -66,6 +72,7 @@ inline PointsDev to_dev(const NsbPoints& p) {
     d.P = p.rays_o ? p.N * (long long)p.S : p.P;
     d.relu = p.relu_masks;
     d.pu = p.point_cache;
+    d.marks = p.line_marks; d.marks_base = p.line_marks_base;
     return d;
 }
 

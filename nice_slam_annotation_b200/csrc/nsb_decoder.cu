@@ -1084,6 +1084,7 @@ static void build_dw_tables(DwTables& T) {
 namespace nsb {
 
 // ---- host side -------------------------------------------------------------------------------
+int dweight_grid_cap_take();
 static int g_num_sms = 0;
 static int g_use_tc = 1;         // NSB_TC=0 selects the mma.sync kernels (A/B comparisons)
 static int g_use_tc_bwd = 1;     // NSB_TC_BWD=0 keeps the mma.sync backward under a tcgen05 forward
@@ -1423,6 +1424,9 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
                                      int64_t scratch_bytes, void* stream) {
     if (!pts || !scene || !d_raw) return set_error(NSB_EINVAL, "null argument");
     if (int rc = init_device()) return rc;
+    const bool defer_dw = (flags & NSB_FLAG_DEFER_DWEIGHT) != 0, only_dw = (flags & NSB_FLAG_ONLY_DWEIGHT) != 0;
+    flags &= ~(NSB_FLAG_DEFER_DWEIGHT | NSB_FLAG_ONLY_DWEIGHT);
+    const int dw_cap = dweight_grid_cap_take();
     StageParams sp{};
     sp.pts = to_dev(*pts);
     if (sp.pts.P <= 0) return 0;
@@ -1453,6 +1457,8 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
     sp.d_raw = d_raw;
     sp.flags = flags;
     if (tc_bwd && getenv("NSB_DEBUG_NO_SCATTER")) sp.flags |= 0x80000000u;      // timing experiments: wrong gradients
+    if (sp.pts.marks && !tc_bwd)      // this path does not mark the lines it scatters into: the exchange has to scan
+        cudaMemsetAsync(sp.pts.marks, 0, sizeof(unsigned), (cudaStream_t)stream);
     const long long ntiles = (sp.pts.P + 15) / 16;
     // decoders whose parameters want a gradient
     int ndw = 0;
@@ -1489,12 +1495,14 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
     sp.prof = bprof_dev;
 #endif
     const bool pdl = pdl_take();
+    if ((defer_dw || only_dw) && ndw && chunk != ntiles)
+        return set_error(NSB_EINVAL, "two-phase backward needs a scratch that holds the whole batch");
     for (long long t0 = 0; t0 < ntiles; t0 += chunk) {
         sp.tile_begin = t0;
         sp.tile_end = t0 + chunk < ntiles ? t0 + chunk : ntiles;
         sp.ctr = next_counters();
-        timing_mark(1, 0, (cudaStream_t)stream);
-        {
+        if (!only_dw) timing_mark(1, 0, (cudaStream_t)stream);
+        if (!only_dw) {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(tc_bwd ? TCB_THREADS : THREADS);
             cfg.dynamicSmemBytes = tc_bwd ? (size_t)TbSmem<KIND_FINE>::S_END * 4 : (size_t)smem;
@@ -1506,8 +1514,10 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
             if (tc_bwd) cudaLaunchKernelEx(&cfg, k_decoders_backward_tc, sp);
             else cudaLaunchKernelEx(&cfg, k_decoders_backward, sp);
         }
-        timing_mark(1, 1, (cudaStream_t)stream);
-        if (int rc = check_launch(tc_bwd ? "k_decoders_backward_tc" : "k_decoders_backward")) return rc;
+        if (!only_dw) {
+            timing_mark(1, 1, (cudaStream_t)stream);
+            if (int rc = check_launch(tc_bwd ? "k_decoders_backward_tc" : "k_decoders_backward")) return rc;
+        }
 #ifdef NSB_TC_PROFILE
         if (getenv("NSB_TC_PROFILE_PRINT")) {
             long long h[72];
@@ -1526,7 +1536,7 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
                         h[36 + 3 * t + 2]);
         }
 #endif
-        for (int i = 0; i < sp.ntask && ndw; ++i) {
+        for (int i = 0; i < sp.ntask && ndw && !defer_dw; ++i) {
             const DecTask& T = sp.task[i];
             if (!T.dw_scratch) continue;
             DwParams dp;
@@ -1539,6 +1549,7 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
             long long grid = dp.ntiles < g_num_sms ? dp.ntiles : g_num_sms;
             const long long need = (dp.ntiles + DW_LIVE_MAX - 2) / (DW_LIVE_MAX - 1);
             if (grid < need) grid = need;
+            if (dw_cap > 0 && grid > dw_cap && dw_cap >= need) grid = dw_cap;
             timing_mark(2, 0, (cudaStream_t)stream);
             launch_pdl(k_dweight, dim3((unsigned)grid), dim3(THREADS), (size_t)(DW_HEAD_FLOATS + 2 * g_dw_host[T.kind].rec) * 4, (cudaStream_t)stream, dp);
             timing_mark(2, 1, (cudaStream_t)stream);

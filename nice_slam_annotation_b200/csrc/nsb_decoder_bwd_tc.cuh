@@ -172,12 +172,23 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
                     int mb;
                     const Tri t = tb_read_tri(s_tri + q * TRI_WORDS, T.own, mb);
                     const float4 v = s_dc[q * 8 + (sub ^ (q & 7))];
+                    // a point whose d(c) is exactly zero (behind the surface the transmittance underflows) adds nothing:
+                    // no reductions, and its lines do not travel in the exchange.  Vote of the point's 8 lanes.
+                    const bool nz = v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f;
+                    if (!__any_sync(0xffu << (lane & 24), nz)) continue;
                     float* g0 = T.own.grad + 4 * sub;
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
                         const float w = tri_weight(t, k);
+                        float* line = g0 + (size_t)tri_offset(t, k) * CDIM;
                         if (!(P.flags & 0x80000000u))      // NSB_DEBUG_NO_SCATTER (timing experiments only)
-                            red_add_v4(g0 + (size_t)tri_offset(t, k) * CDIM, w * v.x, w * v.y, w * v.z, w * v.w);
+                            red_add_v4(line, w * v.x, w * v.y, w * v.z, w * v.w);
+                    }
+                    if (P.pts.marks) {      // ray-sharded mapping: these 8 lines travel in the exchange.  Lane sub marks corner
+                                            // sub with a plain one-byte store (idempotent: no atomics, nothing waits for memory)
+                        const size_t d = (size_t)(reinterpret_cast<const char*>(T.own.grad + (size_t)tri_offset(t, sub) * CDIM) -
+                                                  reinterpret_cast<const char*>(P.pts.marks_base));
+                        reinterpret_cast<unsigned char*>(P.pts.marks)[128 + (d >> 7)] = 1;
                     }
                 }
                 nbar_arrive(BAR_EMPTY + b, TCB_THREADS);           // image b may be overwritten
@@ -438,6 +449,7 @@ k_decoders_backward_tc(const __grid_constant__ StageParams P) {
     int k = 0;
     while (k + 1 < P.ntask && (int)blockIdx.x >= P.task[k + 1].cta_begin) ++k;
     const DecTask& T = P.task[k];
+    if (blockIdx.x == 0 && threadIdx.x == 0 && P.pts.marks) P.pts.marks[0] = 1u;      // this launch marks what it scatters
     switch (T.kind) {
         case KIND_MIDDLE: tc_backward_cta<KIND_MIDDLE>(P, T, k, sm); break;
         case KIND_FINE: tc_backward_cta<KIND_FINE>(P, T, k, sm); break;

@@ -22,6 +22,8 @@
 // ends and the launch can be replayed inside a CUDA graph.  A wait that lasts longer than
 // ~20 s sets *error and gives up, so a lost peer cannot hang the GPU.
 #include <stdlib.h>
+#include <cstdio>
+#include <cstdlib>
 #include "nsb_common.cuh"
 
 namespace nsb {
@@ -40,6 +42,8 @@ struct PeersDev {
     unsigned* touched[NSB_MAX_PEERS];
     float* scalar[NSB_MAX_PEERS];
     int* error;
+    unsigned* marks;          // NsbPeers::line_marks (local): word 0 valid flag, byte 128 + l = line l was touched
+    long long marks_units;    // leading units the marks cover
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -201,19 +205,43 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange(const __grid_constant__ 
 // Untouched lines are zero in every copy and stay so.  CTA b meets CTA b of the peers only, so the
 // units CTA b scans in A (for every owner) are exactly the units CTA b of that owner handles in C.
 constexpr int X_WARPS = X_THREADS / 32;
+__device__ unsigned long long g_xprof[8];      // NSB_X_PROFILE_PRINT: globaltimer stamps of CTA 0 (start, A, barrier, C, barrier)
+#define XSTAMP(k) if (blockIdx.x == 0 && threadIdx.x == 0) g_xprof[k] = globaltimer_ns();
 __device__ __forceinline__ bool line_on(unsigned word, int j, int lane) { return (word >> (4 * j + (lane >> 3))) & 1u; }
 
 __global__ void __launch_bounds__(X_THREADS) k_exchange_sparse(const __grid_constant__ PeersDev g, long long off,
                                                                 long long n4, long long n_units, long long per_u) {
     const int lane = threadIdx.x & 31;
     const long long gw = (long long)blockIdx.x * X_WARPS + (threadIdx.x >> 5), nw = (long long)gridDim.x * X_WARPS;
+    XSTAMP(0)
     // ---- A: touched bits of the local copy, pushed to the owner of each unit (posted peer stores: the
     //         owner later reads every rank's word from its OWN memory, no NVLink round trip)
     const float4* mine = reinterpret_cast<const float4*>(g.bucket[g.rank] + off);
+    // the backward that filled the local copy marked the lines it touched (NsbPoints::line_marks): read ~4 bytes per
+    // 4 KB unit instead of the unit, and clear the word for the next step.  Units the marks do not cover (the decoder
+    // weight gradients) and backward paths that do not mark (flag word 0) are scanned.
+    const bool marked = g.marks != nullptr && off == 0 && __ldcg(g.marks) != 0u;
+    const long long covered = marked ? g.marks_units : 0;
+    if (marked) {                          // 32 bytes per unit (lane = line) instead of the unit's 4 KB
+        unsigned char* mb = reinterpret_cast<unsigned char*>(g.marks) + 128;
+        for (int o = 0; o < g.world; ++o)
+            for (long long v = gw; v < per_u; v += nw) {
+                const long long u = o * per_u + v;
+                if (u >= n_units || u >= covered) break;
+                const unsigned char m = __ldcg(mb + u * 32 + lane);
+                const unsigned word = __ballot_sync(FULL, m != 0);
+                if (m) mb[u * 32 + lane] = 0;           // clean for the next step
+                if (lane == 0) {
+                    unsigned* dst = g.touched[o] + g.rank * per_u + v;
+                    asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(dst), "r"(word) : "memory");
+                }
+            }
+    }
     for (int o = 0; o < g.world; ++o)
         for (long long v = gw; v < per_u; v += nw) {
             const long long u = o * per_u + v;
             if (u >= n_units) break;
+            if (u < covered) continue;
             unsigned word = 0u;
             float4 x[8];
 #pragma unroll
@@ -233,7 +261,10 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange_sparse(const __grid_cons
                 asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(dst), "r"(word) : "memory");
             }
         }
+    __syncthreads();
+    XSTAMP(1)
     peer_barrier(g, (0 * X_MAX_BLOCKS + blockIdx.x) * NSB_MAX_PEERS);
+    XSTAMP(2)
     // ---- C: reduce the lines of my units that some rank touched, two units per pass (16 requests in
     //         flight per lane)
     const unsigned* words = g.touched[g.rank];
@@ -275,7 +306,10 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange_sparse(const __grid_cons
             }
         }
     }
+    __syncthreads();
+    XSTAMP(3)
     peer_barrier(g, (1 * X_MAX_BLOCKS + blockIdx.x) * NSB_MAX_PEERS);
+    XSTAMP(4)
 }
 
 // CTAs of one exchange: NVLink round trips are several microseconds, so the wire is only full with
@@ -357,6 +391,8 @@ static int to_dev(const NsbPeers* p, PeersDev& g, bool need_param) {
     g.bucket_mc = p->bucket_multicast;
     g.param_mc = p->param_multicast;
     g.error = p->error;
+    g.marks = p->line_marks;
+    g.marks_units = p->line_marks ? p->line_marks_floats / 1024 : 0;     // whole 4 KB units only
     return 0;
 }
 
@@ -415,6 +451,10 @@ extern "C" int nsb_bucket_reduce_adam(const NsbPeers* peers, int64_t offset, int
 extern "C" int64_t nsb_exchange_touched_words(int64_t n) { return n <= 0 ? 0 : (n + 1023) / 1024 + NSB_MAX_PEERS; }
 
 extern "C" int nsb_bucket_allreduce_sparse(const NsbPeers* peers, int64_t offset, int64_t n, void* stream) {
+    return nsb_bucket_allreduce_sparse_ctas(peers, offset, n, 0, stream);
+}
+
+extern "C" int nsb_bucket_allreduce_sparse_ctas(const NsbPeers* peers, int64_t offset, int64_t n, int max_ctas, void* stream) {
     PeersDev g;
     if (int e = to_dev(peers, g, false)) return e;
     if (n <= 0) return 0;
@@ -427,10 +467,22 @@ extern "C" int nsb_bucket_allreduce_sparse(const NsbPeers* peers, int64_t offset
     // one warp per unit and pass; the scan covers world x per_u units
     long long b = (per_u + X_WARPS - 1) / X_WARPS;
     const int cap = blocks_for(1ll << 40);
-    const int nb = (int)(b < 1 ? 1 : (b > cap ? cap : b));
+    int nb = (int)(b < 1 ? 1 : (b > cap ? cap : b));
+    if (max_ctas > 0 && nb > max_ctas) nb = max_ctas;
     timing_mark(3, 0, (cudaStream_t)stream);
     k_exchange_sparse<<<nb, X_THREADS, 0, (cudaStream_t)stream>>>(g, (long long)offset, n4, n_units, per_u);
     timing_mark(3, 1, (cudaStream_t)stream);
+    if (getenv("NSB_X_PROFILE_PRINT")) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        cudaStreamIsCapturing((cudaStream_t)stream, &cs);
+        if (cs == cudaStreamCaptureStatusNone) {
+            cudaStreamSynchronize((cudaStream_t)stream);
+            unsigned long long h[8];
+            cudaMemcpyFromSymbol(h, g_xprof, sizeof(h));
+            fprintf(stderr, "[xprof] rank %d ctas %d: scan/marks %.1f us, barrier %.1f us, reduce+store %.1f us, barrier %.1f us\n", g.rank, nb,
+                    (h[1] - h[0]) * 1e-3, (h[2] - h[1]) * 1e-3, (h[3] - h[2]) * 1e-3, (h[4] - h[3]) * 1e-3);
+        }
+    }
     return check_launch("k_exchange_sparse");
 }
 

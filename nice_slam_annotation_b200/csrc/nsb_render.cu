@@ -297,10 +297,20 @@ extern "C" int nsb_render_backward(const NsbRenderCall* r, void* stream) {
     NsbPoints pts = ray_pts(r, w.z, S);
     pts.relu_masks = w.relu;             // written by nsb_render_forward of this call
     pts.point_cache = r->stage == NSB_STAGE_COARSE ? nullptr : w.pu;
+    pts.line_marks = r->line_marks; pts.line_marks_base = r->line_marks_base;
     float *o0, *o1, *rgb;
     stage_planes(r->stage, w, o0, o1, rgb);
     const bool want_rays = (r->flags & NSB_GRAD_POINT) != 0;
     float* dn = (!r->occupancy && want_rays) ? w.d_dnorm : nullptr;
+    if (r->dweight_phase < 0 || r->dweight_phase > 2) return set_error(NSB_EINVAL, "dweight_phase %d", r->dweight_phase);
+    if (r->dweight_phase == 2) {      // second call: only the weight-gradient kernels of the phase-1 call
+        if (!(r->flags & NSB_GRAD_WEIGHT) || !r->dweight_mask) return 0;
+        dweight_grid_cap(r->dweight_max_ctas);
+        return nsb_decoders_backward(&pts, &r->scene, r->stage, w.d_raw, r->flags | NSB_FLAG_ONLY_DWEIGHT, r->dweight_mask,
+                                     r->d_weight, w.d_point, r->scratch, r->scratch_bytes, stream);
+    }
+    const unsigned phase_bit = r->dweight_phase == 1 ? NSB_FLAG_DEFER_DWEIGHT : 0u;
+    if (r->dweight_phase == 0) dweight_grid_cap(r->dweight_max_ctas);
     if (r->loss) {
         if (dn) return set_error(NSB_EINVAL, "fused mapping loss: density-mode ray gradients are not supported");
         if (!r->var || !r->color) return set_error(NSB_EINVAL, "null argument");
@@ -311,7 +321,7 @@ extern "C" int nsb_render_backward(const NsbRenderCall* r, void* stream) {
                                                r->g_var, r->g_color, w.d_raw, dn, stream)) return rc;
     pdl_allow_next(true);         // ... and the backward kernel's weight staging the compositing kernel
     if (r->flags)
-        if (int rc = nsb_decoders_backward(&pts, &r->scene, r->stage, w.d_raw, r->flags, r->dweight_mask,
+        if (int rc = nsb_decoders_backward(&pts, &r->scene, r->stage, w.d_raw, r->flags | phase_bit, r->dweight_mask,
                                            r->d_weight, w.d_point, r->scratch, r->scratch_bytes, stream)) return rc;
     pdl_allow_next(false);
     if (want_rays) {

@@ -49,8 +49,25 @@ class GradBucket:
             self.sparse = os.environ.get("NSB_X_DENSE", "0") != "1"
             self.touched = peers.alloc_touched(n) if self.sparse else None
             self._px = peers.struct(self.flat, touched=self.touched)
+            # touched-line marks (local): the tcgen05 backward writes one byte per 128-byte line it scatters into, the
+            # sparse exchange reads them instead of scanning the bucket (first word: "marks are valid"); they cover the
+            # leading 5-d leaves (the grids), the decoder segments behind them are scanned
+            self.marks = None
+            n_grid = 0
+            for p_, o_ in zip(self.leaves, self.offsets):
+                if p_.dim() != 5:
+                    break
+                n_grid = o_ + (p_.numel() + 63) // 64 * 64
+            self.n_grid = n_grid                     # floats of the leading grid segments
+            if self.sparse and os.environ.get("NSB_X_MARKS", "1") != "0":
+                self.marks = torch.zeros(128 + (n + 31) // 32, dtype=torch.uint8, device=self.flat.device)
+                self._px.line_marks = self.marks.data_ptr()
+                self._px.line_marks_floats = n_grid
         else:
             self.flat = torch.zeros(n, dtype=torch.float32, device=device)
+            self.marks = None
+            if os.environ.get("NSB_FORCE_MARKS") == "1":          # timing experiments: mark without an exchange
+                self.marks = torch.zeros(128 + (n + 31) // 32, dtype=torch.uint8, device=device)
         self.views = [self._view(p, o) for p, o in zip(self.leaves, self.offsets)]
 
     def _view(self, p, off):
@@ -80,6 +97,14 @@ class GradBucket:
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+
+    def all_reduce_range(self, offset, n, max_ctas=0):
+        """Peer-memory SUM of flat[offset, offset + n) (sparse exchange), optionally with few CTAs so that it can run
+        beside another kernel.  Every rank must make the same sequence of calls."""
+        if n <= 0:
+            return
+        check(lib().nsb_bucket_allreduce_sparse_ctas(C.byref(self._px), int(offset), int(n), int(max_ctas), _stream()),
+              "bucket_allreduce_sparse")
 
     def assign(self):
         """leaf.grad = its view (what optimizer.step() reads)."""
@@ -179,6 +204,7 @@ class FusedStep:
         self._call = self._build_call()
         self.graph = None
         self._side = None
+        self._xside = None
         self._packed_dev = None
         self.graph_host = None           # capture_host(): H2D of the staged batch + iteration + D2H of the loss
         self._host_stage = self._host_keep = self._loss_host = self._keep_dev = None
@@ -227,6 +253,8 @@ class FusedStep:
             flags |= GRAD_POINT
             call.g_rays_o, call.g_rays_d = self.g_rays_o.data_ptr(), self.g_rays_d.data_ptr()
         call.flags, call.dweight_mask = flags, mask
+        if self.bucket is not None and getattr(self.bucket, "marks", None) is not None:
+            call.line_marks, call.line_marks_base = self.bucket.marks.data_ptr(), self.bucket.flat.data_ptr()
         # one struct serves the forward and the backward call: the forward may deposit the trained decoders'
         # layer inputs into the weight-gradient records (the backward then skips their recomputation)
         call.deposit_dweight_inputs = 1 if (mask and os.environ.get("NSB_DEPOSIT", "1") != "0") else 0
@@ -333,9 +361,34 @@ class FusedStep:
                                           _ptr(self.keep), self.N, float(self.w_color), int(self.use_color),
                                           int(self.handle_dynamic), _ptr(self.loss), _ptr(self.g_depth),
                                           _ptr(self.g_color), s), "tracking_loss")
+        # Sharded with weight gradients: the grid gradients are complete when the decoder backward retires, the
+        # weight-gradient kernels (SM-bound) follow.  The exchange is bound by NVLink round trips, not by SMs: its grid
+        # segment starts right away on a side stream with a few CTAs, beside the weight-gradient kernels on the other
+        # SMs; only the small decoder segment is exchanged after the join.
+        overlap = (exchange and self.bucket is not None and self.bucket.peers is not None and self.bucket.sparse
+                   and bool(self.dec_grad_kinds) and call.deposit_dweight_inputs and self.bucket.n_grid > 0
+                   and os.environ.get("NSB_X_OVERLAP", "0") == "1")
+        if not overlap:
+            check(lib().nsb_render_backward(C.byref(call), s), "render_backward")
+            if exchange and self.bucket is not None and self.bucket.peers is not None:
+                self.bucket.all_reduce()
+            return
+        side_ctas = int(os.environ.get("NSB_X_SIDE_CTAS", "20"))
+        sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
+        main = torch.cuda.current_stream()
+        if self._xside is None:
+            self._xside = torch.cuda.Stream()
+        call.dweight_phase = 1
         check(lib().nsb_render_backward(C.byref(call), s), "render_backward")
-        if exchange and self.bucket is not None and self.bucket.peers is not None:
-            self.bucket.all_reduce()
+        self._xside.wait_stream(main)
+        with torch.cuda.stream(self._xside):
+            self.bucket.all_reduce_range(0, self.bucket.n_grid, side_ctas)
+        call.dweight_phase, call.dweight_max_ctas = 2, max(sms - side_ctas, 1)
+        check(lib().nsb_render_backward(C.byref(call), s), "render_backward (weight gradients)")
+        call.dweight_phase, call.dweight_max_ctas = 0, 0
+        main.wait_stream(self._xside)
+        n = self.bucket.flat.numel()
+        self.bucket.all_reduce_range(self.bucket.n_grid, n - self.bucket.n_grid)
 
     def capture(self):
         """Record the iteration into a CUDA graph (call once after a warm-up ``run``)."""
@@ -399,7 +452,7 @@ class FusedStep:
             self.graph.replay()
         else:
             self._launch()
-        if all_reduce and self.bucket is not None and self.bucket.peers is None:
+        if all_reduce and self.bucket is not None and self.bucket.peers is None and self._sharded():
             self.bucket.all_reduce(self.group)         # NCCL; the peer-memory exchange is part of _launch
         return self.loss
 
