@@ -89,6 +89,8 @@ class Tracker(object):
         self.c = {}
         self.decoders = None
         self._fused_loop = None
+        self._api_step = None            # engine behind optimize_cam_in_batch (graph without the camera optimiser)
+        self._api_frame = None           # (storage, version) of the frame loaded into it
         self.H, self.W, self.fx, self.fy, self.cx, self.cy = slam.H, slam.W, slam.fx, slam.fy, slam.cx, slam.cy
 
     def optimize_cam_in_batch(self, camera_tensor, gt_color, gt_depth, batch_size, optimizer, indices=None):
@@ -99,6 +101,8 @@ class Tracker(object):
         device = self.device
         H, W, fx, fy, cx, cy = self.H, self.W, self.fx, self.fy, self.cx, self.cy
         optimizer.zero_grad()
+        if self.nice and self.renderer.fixed_shape_ok() and camera_tensor.is_cuda and camera_tensor.requires_grad:
+            return self._optimize_cam_in_batch_graph(camera_tensor, gt_color, gt_depth, batch_size, optimizer, indices)
         Wedge, Hedge = self.ignore_edge_W, self.ignore_edge_H
         H0, H1, W0, W1 = Hedge, H - Hedge, Wedge, W - Wedge
         gt_depth = gt_depth.to(device)
@@ -134,6 +138,34 @@ class Tracker(object):
         optimizer.zero_grad()
         return loss.item()
 
+    def _optimize_cam_in_batch_graph(self, camera_tensor, gt_color, gt_depth, batch_size, optimizer, indices):
+        """optimize_cam_in_batch on the engine: the iteration up to d(loss)/d(camera tensor) -- pixel draw, camera
+        tensor to rays + box pre-filter, render, tracking loss, backward to the rays, pose gradient -- is ONE replayed
+        CUDA graph (step.TrackingStep without its own Adam).  What stays on the host is what the reference's caller
+        owns: the hand-over of the gradient to autograd (``camera_tensor`` may be ``cat([quad, T])`` of two leaves,
+        Tracker.py:226-231), ``optimizer.step()`` and the ``loss.item()`` read.  Same values as the autograd path."""
+        from .step import TrackingStep
+        ts = self._api_step
+        if ts is None or ts.N != batch_size:
+            ts = self._api_step = TrackingStep(self, batch_size, adam=False)
+            self._api_frame = None
+        # the reference passes the same frame for all its iterations (Tracker.py:244-258): load it once.  The key holds
+        # the tensors themselves, so their storage cannot be recycled for another frame while the key is compared.
+        frame = (gt_color.data_ptr(), gt_color._version, gt_depth.data_ptr(), gt_depth._version,
+                 tuple(gt_color.shape), tuple(gt_depth.shape))
+        if self._api_frame is None or frame != self._api_frame[0]:
+            ts.load_frame(gt_color.to(self.device), gt_depth.to(self.device))
+            self._api_frame = (frame, gt_color, gt_depth)
+        ts.cam.copy_(camera_tensor.detach().reshape(7), non_blocking=True)
+        draw = indices is None
+        if not draw:
+            ts.indices.copy_(indices.reshape(-1), non_blocking=True)
+        ts.iterate_api(draw)
+        camera_tensor.backward(ts.d_cam)                # autograd carries it to the leaves the optimiser owns
+        optimizer.step()
+        optimizer.zero_grad()
+        return ts.step.loss.item()
+
     def optimize_cam_fused(self, camera_tensor, gt_color, gt_depth, batch_size, num_iters=None, graph=True):
         """All camera iterations of one frame (the loop of Tracker.py:244-275 around
         optimize_cam_in_batch) without a host round trip per iteration: pixel draw, render,
@@ -162,6 +194,7 @@ class Tracker(object):
         if self.mapping_idx is None or self.mapping_idx[0] != self.prev_mapping_idx:
             self.decoders = copy.deepcopy(self.shared_decoders).to(self.device)
             self._fused_loop = None             # its packed weights / grid pointers are stale
+            self._api_step, self._api_frame = None, None
             for p in self.decoders.parameters():
                 p.requires_grad_(False)
             for key, val in self.shared_c.items():

@@ -500,9 +500,11 @@ class TrackingStep:
     n_rays  : tracking pixels per iteration (cfg['tracking']['pixels'])
     """
 
-    def __init__(self, tracker, n_rays, lr=None, separate_lr=None, betas=(0.9, 0.999), eps=1e-8):
+    def __init__(self, tracker, n_rays, lr=None, separate_lr=None, betas=(0.9, 0.999), eps=1e-8, adam=True):
         t = tracker
         self.t, self.N = t, int(n_rays)
+        self.adam = bool(adam)          # False: stop at d(camera tensor); the caller's optimiser takes the step
+        self._api_graphs = {}
         dev = next(t.decoders.parameters()).device
         self.dev = dev
         self.step = FusedStep(t.renderer, t.decoders, t.c, "color", n_rays, loss="tracking",
@@ -557,9 +559,10 @@ class TrackingStep:
         st._launch()
         check(L.nsb_pose_grad(_ptr(st.g_rays_o), _ptr(st.g_rays_d), _ptr(self.indices), _ptr(st.keep), self.N, H0, W0, W1 - W0,
                               fx, fy, cx, cy, _ptr(self.cam), _ptr(self.d_cam), s), "pose_grad")
-        check(L.nsb_cam_adam(_ptr(self.cam), _ptr(self.d_cam), _ptr(self.m), _ptr(self.v), _ptr(self.count),
-                             self.lr_q, self.lr_t, self.betas[0], self.betas[1], self.eps, _ptr(st.loss),
-                             _ptr(self.best_loss), _ptr(self.best_cam), s), "cam_adam")
+        if self.adam:
+            check(L.nsb_cam_adam(_ptr(self.cam), _ptr(self.d_cam), _ptr(self.m), _ptr(self.v), _ptr(self.count),
+                                 self.lr_q, self.lr_t, self.betas[0], self.betas[1], self.eps, _ptr(st.loss),
+                                 _ptr(self.best_loss), _ptr(self.best_cam), s), "cam_adam")
 
     def capture(self):
         g = torch.cuda.CUDAGraph()
@@ -574,6 +577,25 @@ class TrackingStep:
                 self.graph.replay()
             else:
                 self._launch()
+
+    def iterate_api(self, draw):
+        """One iteration up to ``d_cam`` for Tracker.optimize_cam_in_batch: a graph per draw flag (the pixel draw is a
+        node of the graph), captured on first use after one plain launch."""
+        g = self._api_graphs.get(bool(draw))
+        self.draw = bool(draw)
+        if g is None:
+            keep = self.indices.clone()
+            rng = torch.cuda.get_rng_state(self.dev) if draw else None
+            self._launch()                              # warm-up outside the capture, RNG- and index-neutral
+            if rng is not None:
+                torch.cuda.set_rng_state(rng, self.dev)
+            self.indices.copy_(keep)
+            g = torch.cuda.CUDAGraph()
+            torch.cuda.synchronize()
+            with torch.cuda.graph(g):
+                self._launch()
+            self._api_graphs[bool(draw)] = g
+        g.replay()
 
     def result(self):
         """(candidate camera tensor [7], its loss) -- the one host read of the frame."""
