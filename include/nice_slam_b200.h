@@ -177,6 +177,25 @@ int nsb_sample_z(const NsbPoints* rays, const float* gt_depth, const double* bou
                  const double* t_surface, const float* u, const float* depth_max,
                  double* z_out, void* stream);
 
+/* box pre-filter of explicit rays (src/Tracker.py:100-107, src/Mapper.py:587-594): keep[r] = 1 when ray r leaves
+ * the scene box (bound6_host: x0,x1,y0,y1,z0,z1, fp64) at or beyond its sensor depth.  The reference compacts the
+ * batch with this mask; the render entry points take it as NsbRenderCall.keep instead. */
+int nsb_box_prefilter(const float* rays_o, const float* rays_d, const float* gt_depth, int64_t n,
+                      const double* bound6_host, uint8_t* keep, void* stream);
+
+/* iMAP free-space regulariser points (src/utils/Renderer.py:360-394): N_samples stratified, always-jittered fp32
+ * depths in [0, 0.85 gt_depth] per ray and pts [N*N_samples,3] = o + d z; the densities are then one
+ * nsb_imap_* / eval_points call on pts (Renderer.py:395-409).  t_uniform [N_samples] = torch.linspace(0,1,.),
+ * u [N,N_samples] fp32 uniforms (the reference draws them from the CPU generator, Renderer.py:385).
+ * z_out (optional) [N,N_samples] keeps the depths for the backward. */
+int nsb_regulation_points(const float* rays_o, const float* rays_d, const float* gt_depth, int64_t N,
+                          int N_samples, const float* t_uniform, const float* u, float* pts, float* z_out,
+                          void* stream);
+/* adjoint of the above towards the rays (bundle adjustment, Mapper.py:571-584 makes them depend on the camera
+ * tensors): d_rays_o = sum_s d_pts, d_rays_d = sum_s z d_pts.  Either output may be NULL. */
+int nsb_regulation_points_backward(const float* d_pts, const float* z, int64_t N, int N_samples,
+                                   float* d_rays_o, float* d_rays_d, void* stream);
+
 /* importance resampling: sample_pdf (src/common.py:19-63) + sort-merge with the old depths
  * (Renderer.py:244-249).  weights [N,S] fp32 of the first pass, u [N,N_imp] fp32
  * (torch.linspace for the deterministic case, uniforms otherwise). */

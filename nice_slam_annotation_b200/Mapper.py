@@ -345,11 +345,7 @@ class Mapper(object):
             if self.nice:                                     # Mapper.py:580-596
                 # the reference compacts the batch with boolean indexing (a host sync per
                 # iteration); the fused path keeps the shape and passes the mask to the kernels
-                with torch.no_grad():
-                    b = torch.as_tensor(self.bound, dtype=torch.float64).to(device)
-                    t = (b.unsqueeze(0) - batch_rays_o.detach().unsqueeze(-1)) / batch_rays_d.detach().unsqueeze(-1)
-                    t, _ = torch.min(torch.max(t, dim=2)[0], dim=1)
-                    keep = (t >= batch_gt_depth).to(torch.uint8)
+                keep = fused.box_prefilter(batch_rays_o, batch_rays_d, batch_gt_depth, self.bound)
             if keep is not None and not self.renderer.fixed_shape_ok():
                 m = keep.bool()
                 batch_rays_d, batch_rays_o = batch_rays_d[m], batch_rays_o[m]

@@ -96,6 +96,9 @@ _SIGS = {
                                c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_importance_z": (C.c_int, [c_ptr, c_ptr, C.c_int64, C.c_int, C.c_int, c_ptr, C.c_int64, c_ptr,
                                    c_ptr, c_ptr]),
+    "nsb_box_prefilter": (C.c_int, [c_ptr, c_ptr, c_ptr, C.c_int64, c_ptr, c_ptr, c_ptr]),
+    "nsb_regulation_points": (C.c_int, [c_ptr, c_ptr, c_ptr, C.c_int64, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "nsb_regulation_points_backward": (C.c_int, [c_ptr, c_ptr, C.c_int64, C.c_int, c_ptr, c_ptr, c_ptr]),
     "nsb_sample_pdf": (C.c_int, [c_ptr, c_ptr, C.c_int64, C.c_int, C.c_int, c_ptr, C.c_int64, c_ptr, c_ptr]),
     "nsb_decoders_forward": (C.c_int, [C.POINTER(NsbPoints), C.POINTER(NsbScene), C.c_int, c_ptr, c_ptr,
                                        c_ptr, c_ptr]),

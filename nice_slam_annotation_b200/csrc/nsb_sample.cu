@@ -399,6 +399,28 @@ extern "C" int nsb_sample_rays(const int64_t* indices, int64_t n, int H0, int H1
     return check_launch("k_sample_rays");
 }
 
+// Box pre-filter of explicit rays (Tracker.py:100-107, Mapper.py:587-594): keep[r] = (exit depth of ray r from
+// the scene box, fp64 like the reference's .to(float64) bound) >= gt_depth[r].  Same box_exit as k_sample_rays.
+__global__ void k_box_prefilter(const float* __restrict__ ro, const float* __restrict__ rd,
+                                const float* __restrict__ gt_depth, long long n, BoundDev bound,
+                                uint8_t* __restrict__ keep) {
+    const long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    float o[3], d[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { o[a] = ro[3 * r + a]; d[a] = rd[3 * r + a]; }
+    keep[r] = box_exit(o, d, bound) >= (double)gt_depth[r] ? 1 : 0;
+}
+
+extern "C" int nsb_box_prefilter(const float* rays_o, const float* rays_d, const float* gt_depth, int64_t n,
+                                 const double* bound6_host, uint8_t* keep, void* stream) {
+    if (n <= 0) return 0;
+    if (!rays_o || !rays_d || !gt_depth || !bound6_host || !keep) return set_error(NSB_EINVAL, "null argument");
+    k_box_prefilter<<<(unsigned)blocks_for(n, 128), 128, 0, (cudaStream_t)stream>>>(rays_o, rays_d, gt_depth, n,
+                                                                                    to_bound(bound6_host), keep);
+    return check_launch("k_box_prefilter");
+}
+
 extern "C" int nsb_all_rays(int H, int W, float fx, float fy, float cx, float cy, const float* c2w,
                             float* rays_o, float* rays_d, void* stream) {
     if (!c2w || !rays_o || !rays_d) return set_error(NSB_EINVAL, "null argument");
@@ -497,6 +519,91 @@ extern "C" int nsb_sample_z(const NsbPoints* rays, const float* gt_depth, const 
     if (gt_depth && !depth_max) return set_error(NSB_EINVAL, "depth_max is required with gt_depth");
     return sample_z_impl(rays, gt_depth, bound6_host, N_samples, N_surface, lindisp, t_uniform, t_surface, u,
                          depth_max, z_out, nullptr, nullptr, stream);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// iMAP free-space regulariser points (Renderer.py:343-409): S stratified, always-jittered fp32 depths in
+// [0, 0.85 d] of each ray and the points o + d z they name, one thread per (ray, sample).  Each thread evaluates
+// its own depth and its two neighbours' (three products, no shared memory); every product and sum is the un-fused
+// fp32 operation torch evaluates, so points and depths equal the eager expressions bit for bit.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_regulation_points(const float* __restrict__ ro, const float* __restrict__ rd,
+                                                           const float* __restrict__ gt_depth, long long N, int S,
+                                                           const float* __restrict__ t_uniform,
+                                                           const float* __restrict__ u, float* __restrict__ pts,
+                                                           float* __restrict__ z_out) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= N * S) return;
+    const long long r = i / S;
+    const int k = (int)(i - r * S);
+    const float far = __fmul_rn(gt_depth[r], 0.85f);
+    auto zk = [&](int kk) -> float {                       // near * (1 - t) + far * t with near = 0
+        const float t = t_uniform[kk];
+        return __fadd_rn(__fmul_rn(0.f, __fsub_rn(1.f, t)), __fmul_rn(far, t));
+    };
+    const float zc = zk(k);
+    const float lower = k > 0 ? __fmul_rn(0.5f, __fadd_rn(zc, zk(k - 1))) : zc;
+    const float upper = k + 1 < S ? __fmul_rn(0.5f, __fadd_rn(zk(k + 1), zc)) : zc;
+    const float z = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), u[i]));
+    if (z_out) z_out[i] = z;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) pts[i * 3 + a] = __fadd_rn(ro[r * 3 + a], __fmul_rn(rd[r * 3 + a], z));
+}
+
+// adjoint of p = o + d z (z carries no gradient: the sensor depth is data): d(o) = sum_s d(p), d(d) = sum_s z d(p);
+// one warp per ray, lanes stride the samples, fixed-order butterfly sum.
+__global__ void __launch_bounds__(256) k_regulation_points_bwd(const float* __restrict__ d_pts,
+                                                               const float* __restrict__ z, long long N, int S,
+                                                               float* __restrict__ d_ro, float* __restrict__ d_rd) {
+    const long long r = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (r >= N) return;
+    float go[3] = {0.f, 0.f, 0.f}, gd[3] = {0.f, 0.f, 0.f};
+    for (int k = lane; k < S; k += 32) {
+        const float zz = z[r * S + k];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float g = d_pts[(r * S + k) * 3 + a];
+            go[a] += g;
+            gd[a] = fmaf(g, zz, gd[a]);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+        for (int sft = 16; sft > 0; sft >>= 1) {
+            go[a] += __shfl_xor_sync(FULL, go[a], sft);
+            gd[a] += __shfl_xor_sync(FULL, gd[a], sft);
+        }
+    if (lane == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            if (d_ro) d_ro[r * 3 + a] = go[a];
+            if (d_rd) d_rd[r * 3 + a] = gd[a];
+        }
+    }
+}
+
+extern "C" int nsb_regulation_points(const float* rays_o, const float* rays_d, const float* gt_depth, int64_t N,
+                                     int N_samples, const float* t_uniform, const float* u, float* pts,
+                                     float* z_out, void* stream) {
+    if (N < 0 || N_samples < 1) return set_error(NSB_EINVAL, "regulation_points: N >= 0 and N_samples >= 1");
+    if (N == 0) return 0;
+    if (!rays_o || !rays_d || !gt_depth || !t_uniform || !u || !pts)
+        return set_error(NSB_EINVAL, "regulation_points: null pointer");
+    const long long total = (long long)N * N_samples;
+    k_regulation_points<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        rays_o, rays_d, gt_depth, N, N_samples, t_uniform, u, pts, z_out);
+    return check_launch("k_regulation_points");
+}
+
+extern "C" int nsb_regulation_points_backward(const float* d_pts, const float* z, int64_t N, int N_samples,
+                                              float* d_rays_o, float* d_rays_d, void* stream) {
+    if (N < 0 || N_samples < 1) return set_error(NSB_EINVAL, "regulation_points_backward: N >= 0 and N_samples >= 1");
+    if (N == 0) return 0;
+    if (!d_pts || !z) return set_error(NSB_EINVAL, "regulation_points_backward: null pointer");
+    k_regulation_points_bwd<<<(unsigned)((N * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        d_pts, z, N, N_samples, d_rays_o, d_rays_d);
+    return check_launch("k_regulation_points_bwd");
 }
 
 extern "C" int nsb_importance_z(const double* z, const float* weights, int64_t N, int S, int N_imp,

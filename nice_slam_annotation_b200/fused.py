@@ -235,6 +235,57 @@ def sample_z(rays_o, rays_d, gt_depth, bound, N_samples, N_surface, lindisp=Fals
     return z
 
 
+def box_prefilter(rays_o, rays_d, gt_depth, bound):
+    """[N] uint8: 1 for the rays the reference keeps (src/Tracker.py:100-107, src/Mapper.py:587-594)."""
+    _require_cuda(rays_o, "rays_o")
+    N = rays_o.shape[0]
+    keep = torch.empty(N, dtype=torch.uint8, device=rays_o.device)
+    check(lib().nsb_box_prefilter(_ptr(rays_o.detach().float().contiguous()), _ptr(rays_d.detach().float().contiguous()),
+                                  _ptr(gt_depth.detach().reshape(-1).float().contiguous()), N, _bound6(bound),
+                                  _ptr(keep), _stream()), "box_prefilter")
+    return keep
+
+
+class _RegulationPointsFn(torch.autograd.Function):
+    """Renderer.py:360-394 as one kernel; backward carries d(points) to the rays (bundle adjustment)."""
+
+    @staticmethod
+    def forward(ctx, rays_o, rays_d, gt_depth, N_samples, u):
+        dev = rays_o.device
+        N = rays_o.shape[0]
+        ro, rd = rays_o.detach().float().contiguous(), rays_d.detach().float().contiguous()
+        gd = gt_depth.detach().reshape(-1).float().contiguous()
+        u = u.to(device=dev, dtype=torch.float32).contiguous()
+        pts = torch.empty(N * N_samples, 3, dtype=torch.float32, device=dev)
+        z = torch.empty(N, N_samples, dtype=torch.float32, device=dev)
+        check(lib().nsb_regulation_points(_ptr(ro), _ptr(rd), _ptr(gd), N, N_samples,
+                                          _ptr(_linspace(N_samples, torch.float32, dev)), _ptr(u), _ptr(pts), _ptr(z),
+                                          _stream()), "regulation_points")
+        ctx.save_for_backward(z)
+        ctx.mark_non_differentiable(z)
+        return pts, z
+
+    @staticmethod
+    def backward(ctx, g_pts, _gz):
+        (z,) = ctx.saved_tensors
+        N, S = z.shape
+        g = g_pts.float().contiguous()
+        d_o = torch.empty(N, 3, dtype=torch.float32, device=z.device) if ctx.needs_input_grad[0] else None
+        d_d = torch.empty(N, 3, dtype=torch.float32, device=z.device) if ctx.needs_input_grad[1] else None
+        if N and (d_o is not None or d_d is not None):
+            check(lib().nsb_regulation_points_backward(_ptr(g), _ptr(z), N, S, _ptr(d_o), _ptr(d_d), _stream()),
+                  "regulation_points_backward")
+        return d_o, d_d, None, None, None
+
+
+def regulation_points(rays_o, rays_d, gt_depth, N_samples, u, return_z=False):
+    """Points [N*N_samples,3] of the iMAP free-space regulariser (src/utils/Renderer.py:360-394): jittered depths in
+    [0, 0.85 gt_depth]; u [N,N_samples] uniforms.  Differentiable towards rays_o / rays_d."""
+    _require_cuda(rays_o, "rays_o")
+    pts, z = _RegulationPointsFn.apply(rays_o, rays_d, gt_depth, int(N_samples), u)
+    return (pts, z) if return_z else pts
+
+
 class _Planes:
     """Raw decoder outputs of one stage."""
 

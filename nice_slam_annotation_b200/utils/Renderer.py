@@ -102,21 +102,12 @@ class Renderer(object):
             return depth, uncertainty, color
 
     def regulation(self, c, decoders, rays_d, rays_o, gt_depth, device, stage='color'):
-        """iMAP free-space regulariser (Renderer.py:343-409): densities at 32 jittered samples in
-        [0, 0.85 d] of every ray -> [N * N_samples]."""
-        gt_depth = gt_depth.reshape(-1, 1)
-        N_samples = self.N_samples
-        gt_depth = gt_depth.repeat(1, N_samples)
-        t_vals = torch.linspace(0., 1., steps=N_samples).to(device)
-        near, far = 0.0, gt_depth * 0.85
-        z_vals = near * (1. - t_vals) + far * (t_vals)
-        if True:                                               # the reference always jitters here
-            mids = .5 * (z_vals[..., 1:] + z_vals[..., :-1])
-            upper = torch.cat([mids, z_vals[..., -1:]], -1)
-            lower = torch.cat([z_vals[..., :1], mids], -1)
-            t_rand = torch.rand(z_vals.shape).to(device)
-            z_vals = lower + (upper - lower) * t_rand
-        pts = rays_o[..., None, :] + rays_d[..., None, :] * z_vals[..., :, None]
-        pointsf = pts.reshape(-1, 3)
-        raw = self.eval_points(pointsf, decoders, c, stage, device)
-        return raw[:, -1]
+        """iMAP free-space regulariser (Renderer.py:343-409): densities at N_samples jittered samples in
+        [0, 0.85 d] of every ray -> [N * N_samples].  Depths and points come from one kernel
+        (csrc/nsb_sample.cu:k_regulation_points); the uniforms are drawn where the reference draws them
+        (CPU generator, Renderer.py:385), so a seeded run sees the same samples."""
+        n = rays_o.shape[0]
+        u = torch.rand(n, self.N_samples).to(device, non_blocking=True)
+        pts = fused.regulation_points(rays_o.to(device), rays_d.to(device), gt_depth.to(device).reshape(-1),
+                                      self.N_samples, u)
+        return self.eval_points(pts, decoders, c, stage, device)[:, -1]

@@ -371,9 +371,9 @@ def render_batch_ray(prm, grids, rays_d, rays_o, stage, gt_depth, bound, *, N_sa
     return depth, var, rgb
 
 
-def regulation(prm, grids, rays_d, rays_o, gt_depth, stage, bound, u, N_samples=32, nice=False):
-    """iMAP free-space regulariser: densities at jittered samples in [0, 0.85 d].
-    src/utils/Renderer.py:343-409.  u: [N,N_samples] uniforms (always jittered there)."""
+def regulation_points(rays_d, rays_o, gt_depth, u, N_samples=32):
+    """Jittered depths z [N,N_samples] in [0, 0.85 d] and the points o + d z [N*N_samples,3].
+    src/utils/Renderer.py:360-394.  u: [N,N_samples] uniforms (always jittered there)."""
     g = gt_depth.reshape(-1, 1).repeat(1, N_samples)
     t = torch.linspace(0., 1., steps=N_samples).to(g.device)
     z = 0.0 * (1. - t) + g * 0.85 * t
@@ -382,7 +382,13 @@ def regulation(prm, grids, rays_d, rays_o, gt_depth, stage, bound, u, N_samples=
     lower = torch.cat([z[..., :1], mids], -1)
     z = lower + (upper - lower) * u
     pts = rays_o[..., None, :] + rays_d[..., None, :] * z[..., :, None]
-    return eval_points(pts.reshape(-1, 3), prm, grids, stage, bound, nice)[:, -1]
+    return pts.reshape(-1, 3), z
+
+
+def regulation(prm, grids, rays_d, rays_o, gt_depth, stage, bound, u, N_samples=32, nice=False):
+    """iMAP free-space regulariser: densities at the points above.  src/utils/Renderer.py:343-409."""
+    pts, _ = regulation_points(rays_d, rays_o, gt_depth, u, N_samples)
+    return eval_points(pts, prm, grids, stage, bound, nice)[:, -1]
 
 
 # --------------------------------------------------------------------------------------

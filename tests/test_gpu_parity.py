@@ -227,6 +227,47 @@ def test_tracker_iteration_vs_reference(gpu, golden):
     assert_close((cam.detach().cpu() - torch.as_tensor(d["t.cam0"])), d["t.cam1"] - d["t.cam0"], 1e-2, "Adam step")
 
 
+def test_tracker_api_follows_frame_changes(gpu, golden):
+    """The engine behind optimize_cam_in_batch caches the loaded frame: a new frame tensor, and an in-place edit of
+    the same tensor, must both be picked up (checked against a fresh Tracker on each frame), and the random pixel
+    draw inside the graph must follow torch's CUDA generator like common.py:99."""
+    from nice_slam_annotation_b200.Tracker import Tracker
+    d = golden("trained_nice")
+    cfg, ns = _slam_ns(gpu, d)
+    ns.shared_decoders = gpu.nice_from_state(sub(d, "dec."), d["bound"])
+    ns.shared_c = gpu.grids_from(d)
+    depth = torch.as_tensor(d["depth_img"]).to(gpu.DEV)
+    color = torch.as_tensor(d["color_img"]).to(gpu.DEV)
+    idx = torch.as_tensor(d["t.indices"])
+
+    def one(tr, col, dep, indices=idx):
+        cam = torch.as_tensor(d["t.cam0"]).to(gpu.DEV).requires_grad_(True)
+        return tr.optimize_cam_in_batch(cam, col, dep, 150, torch.optim.SGD([cam], lr=0.0), indices=indices)
+
+    def fresh():
+        tr = Tracker(cfg, None, ns)
+        tr.update_para_from_mapping()
+        return tr
+    tr = fresh()
+    l0 = one(tr, color, depth)
+    depth2, color2 = (depth * 1.07).contiguous(), (color * 0.9).contiguous()
+    l1 = one(tr, color2, depth2)                         # another tensor
+    depth2.mul_(0.95)
+    l2 = one(tr, color2, depth2)                         # the same tensor, edited in place
+    assert l1 != l0 and l2 != l1
+    assert l1 == one(fresh(), color2, depth2 / 0.95) or abs(l1 - one(fresh(), color2, depth2 / 0.95)) <= 1e-5 * abs(l1)
+    ref2 = one(fresh(), color2, depth2)
+    assert abs(l2 - ref2) <= 1e-6 * abs(ref2), (l2, ref2)
+    assert abs(one(tr, color, depth) - l0) <= 1e-6 * abs(l0)
+    # random draw: same generator state -> same loss; advancing state -> another draw
+    torch.manual_seed(11)
+    a = one(tr, color, depth, indices=None)
+    b = one(tr, color, depth, indices=None)
+    torch.manual_seed(11)
+    a2 = one(tr, color, depth, indices=None)
+    assert a == a2 and a != b, (a, a2, b)
+
+
 def test_fused_tracking_loop_vs_api_loop(gpu, golden):
     """Tracker.optimize_cam_fused (pixel -> rays -> render -> loss -> pose gradient -> Adam ->
     candidate rule as one replayed CUDA graph) follows the same trajectory as the reference-shaped

@@ -92,6 +92,60 @@ def test_render_perturbed_and_regulation(gpu, golden, name):
     assert_close(sig.cpu(), d["reg.sigma"], TOL_OUT, "regulation sigma")
 
 
+@pytest.mark.parametrize("n,S", [(0, 32), (1, 32), (333, 32), (5000, 32), (77, 1), (64, 48)])
+def test_regulation_points_bit_exact_and_adjoint(gpu, n, S):
+    """k_regulation_points: depths and points equal the eager expressions of Renderer.py:381-394 (oracle
+    regulation_points) bit for bit -- fp32 throughout, including rays without sensor depth (d = 0) and a NaN
+    depth; the adjoint towards the rays equals autograd through the oracle."""
+    from nice_slam_annotation_b200 import fused
+    g = torch.Generator().manual_seed(n * 131 + S)
+    ro = (torch.randn(n, 3, generator=g) * 2).to(DEV)
+    rd = torch.randn(n, 3, generator=g).to(DEV)
+    gd = (torch.rand(n, generator=g) * 6).to(DEV)
+    if n > 10:
+        gd[3] = 0.0
+        gd[5] = float("nan")
+    u = torch.rand(n, S, generator=g).to(DEV)
+    ro_a, rd_a = ro.clone().requires_grad_(True), rd.clone().requires_grad_(True)
+    pts, z = fused.regulation_points(ro_a, rd_a, gd, S, u, return_z=True)
+    ro_b, rd_b = ro.clone().requires_grad_(True), rd.clone().requires_grad_(True)
+    pts0, z0 = O.regulation_points(rd_b, ro_b, gd, u, S)
+    assert pts.shape == (n * S, 3) and z.shape == (n, S)
+    assert torch.equal(torch.nan_to_num(z, nan=-7.0), torch.nan_to_num(z0, nan=-7.0))
+    assert torch.equal(torch.nan_to_num(pts, nan=-7.0), torch.nan_to_num(pts0, nan=-7.0))
+    if n == 0:
+        return
+    w = torch.randn(n * S, 3, generator=g).to(DEV)
+    finite = torch.isfinite(pts0).all(dim=1, keepdim=True)
+    (pts * w).masked_fill(~finite, 0).sum().backward()
+    (pts0 * w).masked_fill(~finite, 0).sum().backward()
+    ok = torch.isfinite(gd)
+    assert_close(ro_a.grad[ok].cpu(), ro_b.grad[ok].cpu(), 1e-5, "d rays_o")
+    assert_close(rd_a.grad[ok].cpu(), rd_b.grad[ok].cpu(), 1e-5, "d rays_d")
+
+
+def test_box_prefilter_vs_reference_expression(gpu):
+    """k_box_prefilter against the fp64 expression of Tracker.py:100-107 / Mapper.py:587-594, including rays
+    parallel to an axis (division by zero) and depth exactly on the exit."""
+    from nice_slam_annotation_b200 import fused
+    g = torch.Generator().manual_seed(3)
+    n = 4096
+    bound = torch.tensor([[-2.9, 8.9], [-3.2, 5.5], [-3.5, 3.3]])
+    ro = (torch.rand(n, 3, generator=g) * 4 - 1).to(DEV)
+    rd = torch.randn(n, 3, generator=g).to(DEV)
+    rd[::17, 0] = 0.0
+    rd[::29, 2] = 0.0
+    gd = (torch.rand(n, generator=g) * 8).to(DEV)
+    b = bound.to(torch.float64).to(DEV)
+    t = (b.unsqueeze(0) - ro.unsqueeze(-1)) / rd.unsqueeze(-1)
+    t, _ = torch.min(torch.max(t, dim=2)[0], dim=1)
+    gd[::13] = t[::13].float()                                  # ties at fp32 resolution
+    want = (t >= gd).to(torch.uint8)
+    got = fused.box_prefilter(ro, rd, gd, bound)
+    assert torch.equal(got, want), int((got != want).sum())
+    assert 0 < int(want.sum()) < n
+
+
 @pytest.mark.parametrize("P", [1, 127, 5000, 300000])
 def test_mlp_forward_backward_vs_oracle(gpu, golden, P):
     """MLP.forward on explicit points (ragged tile counts, a forward-only call larger than one
