@@ -482,7 +482,7 @@ def roofline_block(ctx, pts, fwd_ms, bwd_ms, dw_ms, step_ms):
                  "frac_of_tf32_peak": step_tf / peak_tc, "frac_of_bf16_sustained": step_tf / bf16},
         "hbm": {"peak_gbs": hbm,
                 "k_decoders_forward_tc": hbm_view(BYTES_PER_POINT_FWD * pts, fwd_ms, "k_decoders_forward_tc"),
-                "k_decoders_backward": hbm_view(BYTES_PER_POINT_BWD * pts, bwd_ms, "k_decoders_backward"),
+                "k_decoders_backward_tc": hbm_view(BYTES_PER_POINT_BWD * pts, bwd_ms, "k_decoders_backward_tc"),
                 "k_dweight": {"kernel_ms": dw_ms, "algorithmic_bytes_per_launch": 0,
                               "dram_bytes_per_launch_ncu": dram("k_dweight")},
                 "step": hbm_view((BYTES_PER_POINT_FWD + BYTES_PER_POINT_BWD) * pts, step_ms, None),

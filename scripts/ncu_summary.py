@@ -47,5 +47,36 @@ def main(path):
                 print(f"  {k:90s} {r[i]:>16s} {units[i]}")
 
 
+def traffic_json(path, source):
+    """profiles/ncu_traffic.json (read by bench.py's roofline block): per kernel, DRAM bytes and pipe utilisation of
+    its last profiled launch."""
+    import json
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units = rows[0], rows[1]
+
+    def val(r, k, scale_bytes=False):
+        i = hdr.index(k)
+        v = float(r[i].replace(",", ""))
+        if scale_bytes:
+            v *= {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[units[i]]
+        return v
+    res = {"source": source}
+    for r in rows[2:]:
+        name = r[hdr.index("Kernel Name")].split("(")[0].split("<")[0]
+        t = val(r, "gpu__time_duration.sum")
+        t *= {"ns": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3, "nsecond": 1e-3}.get(units[hdr.index("gpu__time_duration.sum")], 1.0)
+        res[name] = {"dram_bytes_read": int(val(r, "dram__bytes_read.sum", True)),
+                     "dram_bytes_write": int(val(r, "dram__bytes_write.sum", True)),
+                     "sm__pipe_tensor_cycles_active_pct": val(r, "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active"),
+                     "issue_active_pct": val(r, "smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                     "lts_hit_rate_pct": val(r, "lts__t_sector_hit_rate.pct"),
+                     "gpu_time_us": t}
+    print(json.dumps(res, indent=1))
+
+
 if __name__ == "__main__":
-    main(sys.argv[1])
+    if len(sys.argv) > 2 and sys.argv[2] == "--traffic-json":
+        traffic_json(sys.argv[1], sys.argv[3] if len(sys.argv) > 3 else sys.argv[1])
+    else:
+        main(sys.argv[1])
