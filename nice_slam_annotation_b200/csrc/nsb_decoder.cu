@@ -513,7 +513,7 @@ __device__ __forceinline__ void embed_grad(const float (&a)[4][4], const float* 
                 const float d = nn ? d1[q] : d0[q];
                 if (!last) { *slot = d; continue; }
                 const float v = (d + *slot) * cos_cw(phase(R.p[r], Bs, f));
-                if (des) des[(g + 8 * r) * EMB_PAD + rec_sw(g, f)] = v;   // d(B)[a][f] = sum_points p_a v
+                if (des) des[rec_e(g + 8 * r, f)] = v;   // d(B)[a][f] = sum_points p_a v
                 dp[r][0] = fmaf(v, Bs[f], dp[r][0]);
                 dp[r][1] = fmaf(v, Bs[EMB_PAD + f], dp[r][1]);
                 dp[r][2] = fmaf(v, Bs[2 * EMB_PAD + f], dp[r][2]);
@@ -667,10 +667,10 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, int
 #pragma unroll 1
                     for (int j = 0; j < E_SLABS; ++j) {
                         const int f0 = 8 * j + t, f1 = f0 + 4;
-                        rec[RC::R_E + g * EMB_PAD + rec_sw(g, f0)] = es[esw(g, f0)];
-                        rec[RC::R_E + (g + 8) * EMB_PAD + rec_sw(g, f0)] = es[esw(g + 8, f0)];
-                        rec[RC::R_E + g * EMB_PAD + rec_sw(g, f1)] = es[esw(g, f1)];
-                        rec[RC::R_E + (g + 8) * EMB_PAD + rec_sw(g, f1)] = es[esw(g + 8, f1)];
+                        rec[RC::R_E + rec_e(g, f0)] = es[esw(g, f0)];
+                        rec[RC::R_E + rec_e(g + 8, f0)] = es[esw(g + 8, f0)];
+                        rec[RC::R_E + rec_e(g, f1)] = es[esw(g, f1)];
+                        rec[RC::R_E + rec_e(g + 8, f1)] = es[esw(g + 8, f1)];
                     }
                 }
 #pragma unroll
@@ -728,7 +728,7 @@ __device__ void decoder_backward_cta(const StageParams& P, const DecTask& T, int
                 if (rec) store_c32(rec + RC::R_DH + i * 16 * HID, dh, lane);
             }
             mask_(dh, mk.get(i));                                      // through the ReLU
-            if (rec) store_c32(rec + RC::R_DA + i * 16 * HID, dh, lane);
+            if (rec) store_c32(rec + RC::da(i), dh, lane);
             chain<4>(a, dh);
             if (i == 3 || i == 0) {                                    // input-side part of the layer
                 if constexpr (C::EMBED) {
@@ -998,14 +998,11 @@ __global__ void __launch_bounds__(THREADS, 1) k_dweight(const DwParams P) {
     if ((int)threadIdx.x < nbias && bias_acc != 0.f) atomicAdd(P.dflat + mybias.out_idx, bias_acc);
 }
 
-// host: tables of one decoder kind
+// host: flat offsets of the canonical parameters of one decoder kind
 template <int KIND>
-static void build_dw_tables(DwTables& T) {
+static void canonical_offsets(int (&off)[32]) {
     using C = DecCfg<KIND>;
-    using RC = RecCfg<KIND>;
-    memset(&T, 0, sizeof(T));
-    // flat offsets of the canonical parameters
-    int off[32], acc_off = 0;
+    int acc_off = 0;
     for (int i = 0; i < C::N_PARAM; ++i) {
         off[i] = acc_off;
         int numel;
@@ -1015,21 +1012,31 @@ static void build_dw_tables(DwTables& T) {
         else numel = i == 10 ? HID : 1;
         acc_off += numel;
     }
+}
+
+// host: tables of one decoder kind
+template <int KIND>
+static void build_dw_tables(DwTables& T) {
+    using C = DecCfg<KIND>;
+    using RC = RecCfg<KIND>;
+    memset(&T, 0, sizeof(T));
+    int off[32];
+    canonical_offsets<KIND>(off);
     // sections of the record (the shared-memory copy is a verbatim image of it)
     auto add_sec = [&](int g_off, int width) {
         DwSec& s = T.sec[T.nsec++];
         s.g_off = g_off; s.width = width;
         return g_off;
     };
-    int sE = -1, sH[5], sC, sP = -1, sDA[5], sDH[5], sDO, sDE = -1;
-    if (C::EMBED) sE = add_sec(RC::R_E, EMB_PAD);
+    int sE[3] = {-1, -1, -1}, sH[5], sC, sP = -1, sDA[5], sDH[5], sDO, sDE[3] = {-1, -1, -1};
+    if (C::EMBED) for (int j = 0; j < 3; ++j) sE[j] = add_sec(RC::R_E + j * RC::ATOM, HID);
     for (int i = 0; i < 5; ++i) sH[i] = add_sec(RC::R_H + i * 16 * HID, HID);
     sC = add_sec(RC::R_C, C::C_IN);
     if (C::EMBED) sP = add_sec(RC::R_P, 8);
-    for (int i = 0; i < 5; ++i) sDA[i] = add_sec(RC::R_DA + i * 16 * HID, HID);
+    for (int i = 0; i < 5; ++i) sDA[i] = add_sec(RC::da(i), HID);
     if (C::EMBED) for (int i = 0; i < 5; ++i) sDH[i] = add_sec(RC::R_DH + i * 16 * HID, HID);
     sDO = add_sec(RC::R_DO, HID);
-    if (C::EMBED) sDE = add_sec(RC::R_DE, EMB_PAD);
+    if (C::EMBED) for (int j = 0; j < 3; ++j) sDE[j] = add_sec(RC::R_DE + j * RC::ATOM, HID);
     T.rec = RC::REC;
     auto add_unit = [&](int a_off, int a_width, int a_col0, int b_off, int b_width, int b_col0, int out_off,
                         int ld_row, int ld_col, int rows_valid, int cols_valid) {
@@ -1050,8 +1057,11 @@ static void build_dw_tables(DwTables& T) {
             }
         };
         if (C::EMBED) {
-            if (i == 0) part(sE, EMB_PAD, EMB, 0);
-            else if (i == 3) { part(sE, EMB_PAD, EMB, 0); part(sH[2], HID, HID, EMB); }
+            auto e_parts = [&]() {
+                for (int j = 0; j < 3; ++j) part(sE[j], HID, EMB - 32 * j < 32 ? EMB - 32 * j : 32, 32 * j);
+            };
+            if (i == 0) e_parts();
+            else if (i == 3) { e_parts(); part(sH[2], HID, HID, EMB); }
             else part(sH[i - 1], HID, HID, 0);
             for (int n = 0; n * 8 < C::C_IN; ++n)
                 add_unit(sDH[i], HID, 0, sC, C::C_IN, 8 * n, off[C::P_WC + i] + 8 * n, C::C_IN, 1, HID, 8);
@@ -1065,7 +1075,7 @@ static void build_dw_tables(DwTables& T) {
         add_unit(sDO, HID, 0, sH[4], HID, 8 * n, off[C::P_WO] + 8 * n, HID, 1, C::NOUT, 8);
     if (C::EMBED)
         for (int m0 = 0; m0 < EMB_PAD; m0 += 32)   // d(B)[a][f]: rows = features f, cols = axes a
-            add_unit(sDE, EMB_PAD, m0, sP, 8, 0, off[C::P_EMB] + m0, 1, EMB, (EMB - m0 < 32 ? EMB - m0 : 32), 3);
+            add_unit(sDE[m0 / 32], HID, 0, sP, 8, 0, off[C::P_EMB] + m0, 1, EMB, (EMB - m0 < 32 ? EMB - m0 : 32), 3);
     auto add_bias = [&](int sec, int width, int col, int out_idx) {
         DwBias& b = T.bias[T.nbias++];
         b.s_off = sec; b.s_w = width; b.col = col; b.out_idx = out_idx;
@@ -1081,13 +1091,28 @@ static void build_dw_tables(DwTables& T) {
 }  // namespace nsb
 #include "nsb_decoder_tc.cuh"
 #include "nsb_decoder_bwd_tc.cuh"
+#include "nsb_dweight_tc.cuh"
 namespace nsb {
+
+template <int KIND>
+static DwTcOffs dw_tc_offsets() {
+    using C = DecCfg<KIND>;
+    int off[32];
+    canonical_offsets<KIND>(off);
+    DwTcOffs o{};
+    for (int i = 0; i < 5; ++i) {
+        o.w[i] = off[C::P_W + i]; o.b[i] = off[C::P_B + i]; o.wc[i] = off[C::P_WC + i]; o.bc[i] = off[C::P_BC + i];
+    }
+    o.wo = off[C::P_WO]; o.bo = off[C::P_BO]; o.emb = off[C::P_EMB];
+    return o;
+}
 
 // ---- host side -------------------------------------------------------------------------------
 int dweight_grid_cap_take();
 static int g_num_sms = 0;
 static int g_use_tc = 1;         // NSB_TC=0 selects the mma.sync kernels (A/B comparisons)
 static int g_use_tc_bwd = 1;     // NSB_TC_BWD=0 keeps the mma.sync backward under a tcgen05 forward
+static int g_use_dw_tc = 1;      // NSB_DW_TC=0 keeps the mma.sync weight-gradient kernel (middle / colour decoders)
 static float g_xsaved_cost = 0.62f;  // backward cost of a decoder whose records' X sections the forward deposited: no
                                      // recomputation, but the G sections are still written (NSB_XSAVED_COST)
 static float g_xfwd_cost = 1.4f;     // forward cost of depositing them (NSB_XFWD_COST)
@@ -1132,8 +1157,12 @@ static int init_device() {
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(k_decoders_backward_tc, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  TbSmem<KIND_FINE>::S_END * 4);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_dweight_tc, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 DwTcSmem<KIND_COLOR>::S_END * 4 + 1024);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     if (const char* v = getenv("NSB_TC")) g_use_tc = atoi(v);
+    if (const char* v = getenv("NSB_DW_TC")) g_use_dw_tc = atoi(v);
     if (const char* v = getenv("NSB_TC_BWD")) g_use_tc_bwd = atoi(v);
     if (const char* v = getenv("NSB_SAVED_COST")) g_saved_cost = (float)atof(v);
     if (const char* v = getenv("NSB_XSAVED_COST")) g_xsaved_cost = (float)atof(v);
@@ -1551,9 +1580,19 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
             if (grid < need) grid = need;
             if (dw_cap > 0 && grid > dw_cap && dw_cap >= need) grid = dw_cap;
             timing_mark(2, 0, (cudaStream_t)stream);
-            launch_pdl(k_dweight, dim3((unsigned)grid), dim3(THREADS), (size_t)(DW_HEAD_FLOATS + 2 * g_dw_host[T.kind].rec) * 4, (cudaStream_t)stream, dp);
+            const bool dw_tc = g_use_tc && g_use_dw_tc && (T.kind == KIND_COLOR || T.kind == KIND_MIDDLE);
+            if (dw_tc) {
+                DwTcParams tp;
+                tp.p = dp;
+                tp.kind = T.kind;
+                tp.off = T.kind == KIND_COLOR ? dw_tc_offsets<KIND_COLOR>() : dw_tc_offsets<KIND_MIDDLE>();
+                launch_pdl(k_dweight_tc, dim3((unsigned)grid), dim3(DWT_THREADS),
+                           (size_t)DwTcSmem<KIND_COLOR>::S_END * 4 + 1024, (cudaStream_t)stream, tp);
+            } else {
+                launch_pdl(k_dweight, dim3((unsigned)grid), dim3(THREADS), (size_t)(DW_HEAD_FLOATS + 2 * g_dw_host[T.kind].rec) * 4, (cudaStream_t)stream, dp);
+            }
             timing_mark(2, 1, (cudaStream_t)stream);
-            if (int rc = check_launch("k_dweight")) return rc;
+            if (int rc = check_launch(dw_tc ? "k_dweight_tc" : "k_dweight")) return rc;
         }
     }
     return 0;

@@ -312,7 +312,7 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
 #pragma unroll
             for (int j = 0; j < 8; ++j)
                 if (!((bits >> j) & 1u)) a[j] = 0.f;
-            if (rec) st_global_v8(rec + RC::R_DA + i * 16 * HID + r16 * HID + rec_sw(r16, hc), a);      // d(a_i)
+            if (rec) st_global_v8(rec + RC::da(i) + r16 * HID + rec_sw(r16, hc), a);      // d(a_i)
             const bool issue = i >= 1 || need_de;                      // uniform over the CTA
             if (issue) st_split8(lane_base, TB_DAHI + hc, TB_DALO + hc, a);
             tc::tmem_st_wait();
@@ -408,7 +408,7 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
                     dp[1] = fmaf(v, b.y, dp[1]);
                     dp[2] = fmaf(v, b.z, dp[2]);
                 }
-                if (rec) st_global_v8(rec + RC::R_DE + r16 * EMB_PAD + rec_sw(r16, c0), d8);
+                if (rec) st_global_v8(rec + RC::R_DE + rec_e(r16, c0), d8);
             }
         }
         if (want_point) {              // the four parts of a point add up through shared memory

@@ -176,7 +176,7 @@ __device__ __forceinline__ void st_global_v8(float* d, const float (&v)[8]) {
 
 // 8 embedding features [c0, c0 + 8) of this thread's point -> tensor memory (hi / lo)
 // (Bv: [feature] -> (B[0][f], B[1][f], B[2][f], 0); same operation order as phase())
-// erow (optional): this point's row of the record's e section ([16][96], rec_sw columns), r its row index
+// erow (optional): the e section (3 atoms, rec_e) of this point's record, r its row index there
 __device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float4* Bv, uint32_t lane_base, int c0,
                                           float* erow = nullptr, int r = 0) {
     float e[8];
@@ -187,7 +187,7 @@ __device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float4* B
     }
     st_split8(lane_base, TM_EHI + c0, TM_ELO + c0, e);
     if (erow) {
-        st_global_v8(erow + rec_sw(r, c0), e);
+        st_global_v8(erow + rec_e(r, c0), e);
     }
 }
 
@@ -311,7 +311,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         {
             const float4 pp = s_pt[row];
             const float p32[3] = {pp.x, pp.y, pp.z};
-            float* er = rec_row(tile, RC::R_E, EMB_PAD);
+            float* er = rec_row(tile, RC::R_E, 0);
 #pragma unroll
             for (int j = 0; j < 3; ++j) tc_embed8(p32, Bv, lane_base, EPP * part + 8 * j, er, row & 15);
         }
@@ -406,7 +406,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
                 else if (L <= 3) {
                     const float4 pp = s_pt[row];
                     const float p32n[3] = {pp.x, pp.y, pp.z};
-                    tc_embed8(p32n, Bv, lane_base, EPP * part + 8 * (L - 1), rec_row(nxt, RC::R_E, EMB_PAD), row & 15);
+                    tc_embed8(p32n, Bv, lane_base, EPP * part + 8 * (L - 1), rec_row(nxt, RC::R_E, 0), row & 15);
                 }
             }
             TQ(7)  // next tile's slice

@@ -169,28 +169,39 @@ struct BlobCfg { static constexpr int TOTAL = DecCfg<KIND>::TOTAL + TcCfg<KIND>:
 }  // namespace nsb
 
 // ---- weight-gradient scratch record ---------------------------------------------------------
-// One record per 16-point tile, written by the backward kernel and consumed by k_dweight:
-// the layer inputs X and the output-side gradients G of every linear layer, each a dense
-// [16 points][width] fp32 matrix.  d(W) of a layer is G^T X summed over points.
+// One record per 16-point tile, written by the forward (layer inputs X) and the backward kernel (output-side
+// gradients G) and consumed by k_dweight / k_dweight_tc: d(W) of a layer is G^T X summed over points.
+// Every 32-channel block of a section is an "atom": a dense [16 points][32 channels] fp32 matrix (128 bytes per
+// point) whose 32-byte chunks are XOR-swizzled with (point & 3) (rec_sw).  That is at once bank-conflict free for
+// k_dweight's transposed mma.sync fragment reads and the ONLY shared-memory layout tcgen05 accepts for MN-major
+// tf32 operands (SWIZZLE_128B_BASE32B: 4-point x 128-byte swizzle atoms, next 4 points 512 B further = SBO, next
+// 32 channels 2048 B further = LBO; scripts/probe_mn_decode.cu), so a record copied verbatim into shared memory is
+// the operand image of k_dweight_tc.  Atoms that one MMA stacks along M or N are adjacent:
+//   [c | e0 e1 e2]           X stack of W0 / W3 (embedding part) / Wc_i
+//   [h1 h2 h3 h4] h5         X stack of W1..W4; h5 feeds the output layer
+//   [da1 da2 da4 da3] da0    G of [h1 h2 h4 h3]; the last two ...
+//   ... [da3 da0 dh0..dh4]   are the first two of the G stack of [c | e]
 namespace nsb {
+NSB_HD inline int rec_da_slot(int i) { return i == 0 ? 4 : (i == 3 ? 3 : (i == 4 ? 2 : i - 1)); }
 template <int KIND>
 struct RecCfg {
     using C = DecCfg<KIND>;
+    static constexpr int ATOM = 16 * HID;                      // floats of one atom (2048 B)
     static constexpr int W_E = C::EMBED ? EMB_PAD : 0;
-    static constexpr int R_E = 0;                              // e = sin(pB)          [16][96]
-    static constexpr int R_H = R_E + 16 * W_E;                 // h1..h5               5 x [16][32]
-    static constexpr int R_C = R_H + 5 * 16 * HID;             // c                    [16][C_IN]
-    static constexpr int R_P = R_C + 16 * C::C_IN;             // p (cols 0..2)        [16][8]
-    static constexpr int R_DA = R_P + 16 * 8;                  // d(a1)..d(a5)         5 x [16][32]
-    static constexpr int R_DH = R_DA + 5 * 16 * HID;           // d(h1)..d(h5)         5 x [16][32]
-    static constexpr int R_DO = R_DH + 5 * 16 * HID;           // d(out) (cols < NOUT) [16][32]
-    static constexpr int R_DE = R_DO + 16 * HID;               // d(e) * cos(pB)       [16][96]
+    static constexpr int R_C = 0;                              // c                    [16][C_IN]
+    static constexpr int R_E = R_C + 16 * C::C_IN;             // e = sin(pB)          3 atoms (features 32j..32j+31)
+    static constexpr int R_H = R_E + 16 * W_E;                 // h1..h5               5 atoms
+    static constexpr int R_P = R_H + 5 * ATOM;                 // p (cols 0..2)        [16][8]
+    static constexpr int R_DA = R_P + 16 * 8;                  // d(a_i) at slot rec_da_slot(i)   5 atoms
+    static constexpr int R_DH = R_DA + 5 * ATOM;               // d(h1)..d(h5)         5 atoms
+    static constexpr int R_DO = R_DH + 5 * ATOM;               // d(out) (cols < NOUT) 1 atom
+    static constexpr int R_DE = R_DO + ATOM;                   // d(e) * cos(pB)       3 atoms
     static constexpr int REC = R_DE + 16 * W_E;
+    NSB_HD static int da(int i) { return R_DA + rec_da_slot(i) * ATOM; }
 };
 constexpr int REC_MAX = RecCfg<KIND_FINE>::REC;
-// Within a section of width >= 32 the element (row, col) is stored at column
-// col ^ ((row & 3) << 3): k_dweight copies a record to shared memory verbatim (one linear
-// async copy) and its transposed fragment reads (4 rows x 8 columns per request) are then
-// bank-conflict free without padding.
+// column of element (row, col) inside a row of a section of width >= 32 (see above)
 NSB_HD inline int rec_sw(int row, int col) { return col ^ ((row & 3) << 3); }
+// float offset of feature f of point `row` inside an e / d(e) section (3 atoms)
+NSB_HD inline int rec_e(int row, int f) { return (f >> 5) * (16 * HID) + row * HID + rec_sw(row, f & 31); }
 }  // namespace nsb
