@@ -17,7 +17,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libnsb200.so")
 SOURCES = ["nsb_api.cu", "nsb_sample.cu", "nsb_decoder.cu", "nsb_composite.cu", "nsb_render.cu", "nsb_tc_selftest.cu", "nsb_gemm.cu",
            "nsb_imap.cu", "nsb_exchange.cu", "nsb_frustum.cu", "nsb_mesh.cu"]
-HEADERS = ["nsb_common.cuh", "nsb_layout.h", "nsb_tc.cuh", "nsb_decoder_tc.cuh", "nsb_decoder_bwd_tc.cuh", "nsb_gemm.cuh", os.path.join("..", "..", "include", "nice_slam_b200.h")]
+HEADERS = ["nsb_common.cuh", "nsb_layout.h", "nsb_tc.cuh", "nsb_decoder_tc.cuh", "nsb_decoder_bwd_tc.cuh", "nsb_dweight_tc.cuh", "nsb_gemm.cuh", os.path.join("..", "..", "include", "nice_slam_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "--extended-lambda"]
 

@@ -1104,6 +1104,7 @@ static DwTcOffs dw_tc_offsets() {
         o.w[i] = off[C::P_W + i]; o.b[i] = off[C::P_B + i]; o.wc[i] = off[C::P_WC + i]; o.bc[i] = off[C::P_BC + i];
     }
     o.wo = off[C::P_WO]; o.bo = off[C::P_BO]; o.emb = off[C::P_EMB];
+    o.total = off[C::P_EMB] + 3 * EMB;
     return o;
 }
 
@@ -1585,9 +1586,22 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
                 DwTcParams tp;
                 tp.p = dp;
                 tp.kind = T.kind;
+                static const int dbg = getenv("NSB_DWT_DEBUG") ? atoi(getenv("NSB_DWT_DEBUG")) : 0;
+                tp.debug = dbg;
                 tp.off = T.kind == KIND_COLOR ? dw_tc_offsets<KIND_COLOR>() : dw_tc_offsets<KIND_MIDDLE>();
-                launch_pdl(k_dweight_tc, dim3((unsigned)grid), dim3(DWT_THREADS),
-                           (size_t)DwTcSmem<KIND_COLOR>::S_END * 4 + 1024, (cudaStream_t)stream, tp);
+                cudaLaunchConfig_t cfg = {};
+                cfg.gridDim = dim3((unsigned)((grid + DWT_CLUSTER - 1) / DWT_CLUSTER * DWT_CLUSTER));   // idle CTAs add zeros
+                cfg.blockDim = dim3(DWT_THREADS);
+                cfg.dynamicSmemBytes = (size_t)DwTcSmem<KIND_COLOR>::S_END * 4 + 1024;
+                cfg.stream = (cudaStream_t)stream;
+                cudaLaunchAttribute at[2];
+                at[0].id = cudaLaunchAttributeClusterDimension;
+                at[0].val.clusterDim.x = DWT_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+                at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+                at[1].val.programmaticStreamSerializationAllowed = 1;
+                cfg.attrs = DWT_CLUSTER > 1 ? at : at + 1;
+                cfg.numAttrs = (DWT_CLUSTER > 1 ? 1 : 0) + (pdl_enabled() ? 1 : 0);
+                cudaLaunchKernelEx(&cfg, k_dweight_tc, tp);
             } else {
                 launch_pdl(k_dweight, dim3((unsigned)grid), dim3(THREADS), (size_t)(DW_HEAD_FLOATS + 2 * g_dw_host[T.kind].rec) * 4, (cudaStream_t)stream, dp);
             }
