@@ -914,7 +914,7 @@ def sweep_bench(ctx, ns):
             irows.append({"rays": n, "unavailable": f"{type(e).__name__}: {e}"[:200]})
         torch.cuda.empty_cache()
     return {"what": f"engine step vs ray count on {ctx.world} GPU(s), rays split over the ranks (strong scaling), graph "
-                    f"replay, L2 flushed between steps; kernel times are per step on rank 0; above 65 536 points per call "
+                    f"replay, L2 flushed between steps; kernel times are per step on rank 0; above 4 194 304 points per call "
                     f"the backward runs in chunks (weight-gradient scratch)", "nice_stage_color": rows, "imap": irows}
 
 

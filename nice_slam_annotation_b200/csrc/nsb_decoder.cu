@@ -815,7 +815,7 @@ constexpr int DW_UPW = 8;          // max units per warp
 constexpr int DW_MAX_UNITS = DW_UPW * WARPS;
 constexpr int DW_MAX_SEC = 26;
 constexpr int DW_MAX_BIAS = THREADS;
-constexpr int DW_LIVE_MAX = 64;    // tiles per CTA range
+constexpr int DW_LIVE_MAX = 256;   // tiles per CTA range
 
 struct DwUnit {       // all offsets in floats of the record
     int a_off, a_w, a_col0;      // G section, row stride, first row (f') of the 32-row block
@@ -1347,7 +1347,11 @@ using namespace nsb;
 
 // bytes of one tile's record + flag, sized for the largest decoder
 static const int64_t kDwTileBytes = (int64_t)REC_MAX * 4 + 1;
-static const int64_t kDwMaxTiles = 4096;     // 64 Ki points per chunk
+// Records of a whole batch are kept when it has at most kDwMaxTiles tiles (4 Mi points, 12.5 GB per trained decoder):
+// the forward can then deposit the layer inputs and the tcgen05 backward runs.  Larger batches go through in chunks of
+// kDwChunkTiles (512 Ki points, 1.56 GB; measured faster than larger chunks: 49.9 vs 58.4 ms per step at 256 k rays).
+static const int64_t kDwMaxTiles = 262144;
+static const int64_t kDwChunkTiles = 32768;
 
 // Weight-gradient scratch layout: [records of trained decoder 0 | 1 | ... | flags ...], `chunk` tiles per
 // decoder (the backward runs in chunks when the scratch is smaller than the batch).  Returns chunk (0:
@@ -1443,7 +1447,7 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
 extern "C" int64_t nsb_dweight_scratch_bytes(int kind, int64_t P) {
     (void)kind;
     int64_t tiles = (P + 15) / 16;
-    if (tiles > kDwMaxTiles) tiles = kDwMaxTiles;
+    if (tiles > kDwMaxTiles) tiles = kDwChunkTiles;
     if (tiles < 1) tiles = 1;
     return tiles * kDwTileBytes + 256;
 }
@@ -1506,7 +1510,8 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
         chunk = share / kDwTileBytes;
         if (chunk < 1) return set_error(NSB_EINVAL, "scratch too small: %lld bytes for %d decoders",
                                         (long long)scratch_bytes, ndw);
-        if (chunk > ntiles) chunk = ntiles;
+        if (chunk >= ntiles) chunk = ntiles;
+        else if (chunk > kDwChunkTiles) chunk = kDwChunkTiles;
         // carve: [records of decoder 0 | records of decoder 1 | ... | flags ...]
         char* base = (char*)(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
         int k = 0;
