@@ -183,7 +183,7 @@ __device__ __forceinline__ void tc_embed8(const float (&p32)[3], const float4* B
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const float4 b = Bv[c0 + j];
-        e[j] = sin_cw(fmaf(p32[2], b.z, fmaf(p32[1], b.y, p32[0] * b.x)));
+        e[j] = sin_embed(fmaf(p32[2], b.z, fmaf(p32[1], b.y, p32[0] * b.x)));
     }
     st_split8(lane_base, TM_EHI + c0, TM_ELO + c0, e);
     if (erow) {
