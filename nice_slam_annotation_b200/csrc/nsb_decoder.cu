@@ -1397,6 +1397,10 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
     }
     sp.d_raw = nullptr;
     sp.flags = 0;
+    {
+        static const int dbg = getenv("NSB_DEBUG_FWD") ? atoi(getenv("NSB_DEBUG_FWD")) : 0;   // timing experiments only
+        sp.flags |= (unsigned)(dbg & 3) << 28;
+    }
     sp.tile_begin = 0;
     sp.tile_end = (sp.pts.P + 15) / 16;
     sp.ctr = next_counters();

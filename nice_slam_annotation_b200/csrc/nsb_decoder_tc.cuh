@@ -401,9 +401,11 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             TQ(6)  // MMA issue (warp 0)
             // ---- a slice of the next tile's inputs while the tensor core works ------------------------
             if (has_next) {
-                if (L == 0) tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane, rec_tile(nxt, RC::R_C),
-                                            RC::REC, C::C_IN, rows_ok(nxt));
-                else if (L <= 3) {
+                if (L == 0) {
+                    if (!(P.flags & 0x20000000u))      // NSB_DEBUG_FWD=2: timing experiment, wrong results
+                        tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane, rec_tile(nxt, RC::R_C),
+                                        RC::REC, C::C_IN, rows_ok(nxt));
+                } else if (L <= 3 && !(P.flags & 0x10000000u)) {      // NSB_DEBUG_FWD=1: no embedding
                     const float4 pp = s_pt[row];
                     const float p32n[3] = {pp.x, pp.y, pp.z};
                     tc_embed8(p32n, Bv, lane_base, EPP * part + 8 * (L - 1), rec_row(nxt, RC::R_E, 0), row & 15);
