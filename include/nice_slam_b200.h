@@ -230,7 +230,9 @@ int nsb_assemble_raw(const NsbPoints* pts, const double* bound6_host, int stage,
  *   NSB_GRAD_GRID   -> scene->grid[k].grad accumulated (levels with gradient at this stage)
  *   NSB_GRAD_POINT  -> d_point [ndec, P, 3] fp32, one plane per decoder that ran
  *   NSB_GRAD_WEIGHT -> d_weight[k] (flat canonical order, accumulated) for k in dweight_mask;
- *                      scratch must hold nsb_dweight_scratch_bytes(P) bytes
+ *                      scratch must hold nsb_dweight_scratch_bytes(P) bytes per trained decoder: the records of
+ *                      the whole batch up to 4 Mi points (47.6 KB per 16 points), above that one 512 Ki-point
+ *                      chunk (the backward then runs in chunks and the forward cannot deposit, see x_scratch)
  * Points whose incoming gradient is exactly zero are skipped. */
 int64_t nsb_dweight_scratch_bytes(int kind, int64_t P);
 int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene, int stage,

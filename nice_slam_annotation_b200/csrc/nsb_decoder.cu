@@ -1421,7 +1421,7 @@ extern "C" int nsb_decoders_forward(const NsbPoints* pts, const NsbScene* scene,
     const bool pdl = pdl_take();
     if (tc) {
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(TC_THREADS);
+        cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(TCF_THREADS);
         cfg.dynamicSmemBytes = (size_t)tc_smem * 4; cfg.stream = (cudaStream_t)stream;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;

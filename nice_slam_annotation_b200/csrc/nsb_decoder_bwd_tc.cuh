@@ -34,8 +34,6 @@ constexpr int TB_DAHI = 0, TB_DALO = 32, TB_GRP = 64, TB_DE = 384;
 constexpr int TCB_SCATTER_WARPS = 4;
 constexpr int TCB_THREADS = TC_THREADS + 32 * TCB_SCATTER_WARPS;     // 512 chain threads + the scatter warps
 constexpr int BAR_CHAIN = 1, BAR_FULL = 2, BAR_EMPTY = 4;            // named barriers (+ buffer index for FULL / EMPTY)
-__device__ __forceinline__ void nbar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-__device__ __forceinline__ void nbar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ int nbar_or(int id, int n, int pred) {
     int r;
     asm volatile(

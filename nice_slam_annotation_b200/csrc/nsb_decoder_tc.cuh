@@ -12,9 +12,11 @@
 //    sixteen warps per SM instead of four is what hides the sinf / gather / TMEM latencies;
 //  * the grid features are gathered cooperatively (8 lanes x 16 B per 128-byte voxel line, so
 //    every request is a fully used line) into a shared-memory operand tile (SS form);
-//  * one elected thread issues the MMAs: the embedding GEMM for layers 0 and 3 (N = 64) and the
+//  * a seventeenth warp issues the MMAs: the embedding GEMM for layers 0 and 3 (N = 64) and the
 //    feature GEMM for all five layers (N = 160) up front, then the serial chain of 32 x 32
-//    layers; completion comes back through an mbarrier (tcgen05.commit);
+//    layers.  The workers arrive at a named barrier when a group's operands are in place
+//    (bar.arrive: they do not wait) and the issuing warp, waiting there, issues the group and commits
+//    it to an mbarrier on which the workers wait before they read the accumulator;
 //  * accumulators live in tensor memory and are read back with tcgen05.ld for the bias / ReLU /
 //    feature-add epilogue of each layer.
 //
@@ -26,8 +28,15 @@
 
 namespace nsb {
 
-constexpr int TC_THREADS = 512;
+constexpr int TC_THREADS = 512;                 // worker threads (the backward's chain threads use the same constant)
 constexpr int TC_PARTS = TC_THREADS / 128;      // threads per point
+constexpr int TCF_THREADS = TC_THREADS + 32;    // forward CTA: workers + one MMA-issuing warp
+// named barriers of the forward (0 is __syncthreads)
+constexpr int FB_WORK = 1;                      // the 512 workers among themselves
+constexpr int FB_LAYER = 2;                     // workers arrive (operands of the next MMA group are in place), the issuer waits
+constexpr int FB_INPUT = 3;                     // workers arrive (next tile's inputs in place, accumulators read), the issuer waits
+__device__ __forceinline__ void nbar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void nbar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 constexpr int TM_EHI = 0, TM_ELO = 96, TM_ACCE = 192, TM_ACCC = 256, TM_ACCH = 416, TM_ACCO = 416;
 constexpr int TM_HHI = 448, TM_HLO = 480;
 constexpr int TRI_WORDS = 12;
@@ -215,13 +224,14 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         s_tile[0] = (long long)atomicAdd(P.ctr + task, 1u);
         s_tile[1] = (long long)atomicAdd(P.ctr + task, 1u);
     }
-    for (int i = tid; i < TT::T_CONST_END; i += TC_THREADS) sm[S::S_CONST + i] = __ldg(blob + i);
+    const bool worker = tid < TC_THREADS;       // warp 16 only issues MMAs
+    for (int i = tid; worker && i < TT::T_CONST_END; i += TC_THREADS) sm[S::S_CONST + i] = __ldg(blob + i);
     if (tid < EMB_PAD)
         reinterpret_cast<float4*>(sm + S::S_BV)[tid] =
             make_float4(__ldg(blob + TT::T_B + tid), __ldg(blob + TT::T_B + EMB_PAD + tid),
                         __ldg(blob + TT::T_B + 2 * EMB_PAD + tid), 0.f);
 #pragma unroll 4
-    for (int i = tid; i < TT::W_FWD / 4; i += TC_THREADS) {
+    for (int i = tid; worker && i < TT::W_FWD / 4; i += TC_THREADS) {
         const float4 w = __ldg(reinterpret_cast<const float4*>(blob + TT::T_CONST_END) + i);
         uint32_t h[4], l[4];
         split_tf32(w.x, h[0], l[0]); split_tf32(w.y, h[1], l[1]);
@@ -287,9 +297,60 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         tc::mma_commit(&bar);
     };
 
-    // ---- prologue: inputs and up-front GEMMs of the first tile ------------------------------------------
     long long tile = s_tile[0];
     int slot = 0;                      // s_tile[slot] is the current tile, s_tile[slot ^ 1] the next
+    if (!worker) {
+        // ---- the issuing warp: waits for the workers' arrival at a named barrier, issues the MMA group they prepared
+        // and commits it to `bar`.  It follows the same tile sequence as the workers (s_tile), one group behind them;
+        // the workers never wait at a CTA barrier for the issue and none of them pays its instruction time.
+        auto issue = [&](auto&& f) {
+            if (tc::elect_one()) {
+                tc::fence_after_sync();
+                f();
+            }
+            __syncwarp();
+        };
+        if (tile < ntiles) {
+            nbar_sync(FB_INPUT, TCF_THREADS);
+            issue(issue_input_gemms);
+        }
+        while (tile < ntiles) {
+            if constexpr (KIND == KIND_FINE) {
+                nbar_sync(FB_LAYER, TCF_THREADS);
+                issue([&]() {
+                    const uint64_t koff = (uint64_t)(4 * 2 * 160);     // K columns 32..63: 4 K steps further
+                    mma3_ss(tbase + TM_ACCC, d_chi, d_clo, wdesc(whi, TT::T_WC, 160) + koff, wdesc(wlo, TT::T_WC, 160) + koff,
+                            160, CDIM / 8, ID160, true);
+                    tc::mma_commit(&bar);
+                });
+            }
+#pragma unroll 1
+            for (int L = 0; L < 5; ++L) {
+                nbar_sync(FB_LAYER, TCF_THREADS);
+                issue([&]() {
+                    if (L < 4) {
+                        const int off = L == 0 ? TT::T_W1 : (L == 1 ? TT::T_W2 : (L == 2 ? TT::T_W3H : TT::T_W4));
+                        // layer 3 accumulates on top of its embedding part (the skip connection [e, h])
+                        mma3_ts(tbase + (L == 2 ? TM_ACCE + 32 : TM_ACCH), tbase + TM_HHI, tbase + TM_HLO, wdesc(whi, off, 32),
+                                wdesc(wlo, off, 32), 32, HID / 8, ID32, L == 2);
+                    } else {
+                        mma3_ts(tbase + TM_ACCO, tbase + TM_HHI, tbase + TM_HLO, wdesc(whi, TT::T_WO, TT::NO),
+                                wdesc(wlo, TT::T_WO, TT::NO), TT::NO, HID / 8, ID16, false);
+                    }
+                    tc::mma_commit(&bar);
+                });
+            }
+            nbar_sync(FB_INPUT, TCF_THREADS);          // the workers published s_tile[slot] (tile after next) before it
+            const long long nxt = s_tile[slot ^ 1];
+            if (nxt < ntiles) issue(issue_input_gemms);
+            tile = nxt;
+            slot ^= 1;
+        }
+        tc::fence_before_sync();
+        __syncthreads();
+        return;
+    }
+    // ---- prologue: inputs and up-front GEMMs of the first tile ------------------------------------------
     // one thread per point (part 0) evaluates the fp64 point and publishes it for the other three
     auto publish_point = [&](long long t) {
         if (part == 0) {
@@ -305,7 +366,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     };
     if (tile < ntiles) {
         publish_point(tile);
-        __syncthreads();
+        nbar_sync(FB_WORK, TC_THREADS);
         tc_gather_level(T.own, s_tri, sm + S::S_CHI, sm + S::S_CLO, warp, lane, rec_tile(tile, RC::R_C), RC::REC, C::C_IN,
                         rows_ok(tile));
         {
@@ -318,11 +379,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         tc::tmem_st_wait();
         tc::fence_async_smem();
         tc::fence_before_sync();
-        __syncthreads();
-        if (warp == 0 && tc::elect_one()) {
-            tc::fence_after_sync();
-            issue_input_gemms();
-        }
+        nbar_arrive(FB_INPUT, TCF_THREADS);
     }
     TQ(0)      // set-up + prologue
     while (tile < ntiles) {
@@ -336,14 +393,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
                             xrec ? rec_tile(tile, RC::R_C) + 32 : nullptr, RC::REC, C::C_IN, rows_ok(tile));
             tc::fence_async_smem();
             tc::fence_before_sync();
-            __syncthreads();
-            if (warp == 0 && tc::elect_one()) {
-                tc::fence_after_sync();
-                const uint64_t koff = (uint64_t)(4 * 2 * 160);     // K columns 32..63: 4 K steps further
-                mma3_ss(tbase + TM_ACCC, d_chi, d_clo, wdesc(whi, TT::T_WC, 160) + koff, wdesc(wlo, TT::T_WC, 160) + koff,
-                        160, CDIM / 8, ID160, true);
-                tc::mma_commit(&bar);
-            }
+            nbar_arrive(FB_LAYER, TCF_THREADS);
             tc::mbar_wait(&bar, par);
             par ^= 1;
             tc::fence_after_sync();
@@ -352,6 +402,8 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         // ---- next tile: point and voxel addressing (published before the chain's first barrier) ----
         const long long nxt = s_tile[slot ^ 1];
         const bool has_next = nxt < ntiles;
+        unsigned after_next = 0u;                   // the tile after next, fetched now, published in the L = 0 slot
+        if (tid == 0) after_next = atomicAdd(P.ctr + task, 1u);
         if (has_next) publish_point(nxt);
         TQ(3)  // next tile's point + publish
         // ---- the layer chain: every thread finishes 8 columns of its row ------------------------------
@@ -380,23 +432,13 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
             tc::tmem_st_wait();
             tc::fence_before_sync();
             TQ(4)  // layer epilogue (ld, alu, st)
-            __syncthreads();
-            TQ(5)  // barrier
-            if (warp == 0 && tc::elect_one()) {
-                tc::fence_after_sync();
-                // the tile after next: its slot holds the current tile index, which everyone has
-                // in a register by now, and several barriers separate this store from its readers
-                if (L == 0) s_tile[slot] = (long long)atomicAdd(P.ctr + task, 1u);
-                if (L < 4) {
-                    const int off = L == 0 ? TT::T_W1 : (L == 1 ? TT::T_W2 : (L == 2 ? TT::T_W3H : TT::T_W4));
-                    // layer 3 accumulates on top of its embedding part (the skip connection [e, h])
-                    mma3_ts(tbase + (L == 2 ? TM_ACCE + 32 : TM_ACCH), tbase + TM_HHI, tbase + TM_HLO, wdesc(whi, off, 32),
-                            wdesc(wlo, off, 32), 32, HID / 8, ID32, L == 2);
-                } else {
-                    mma3_ts(tbase + TM_ACCO, tbase + TM_HHI, tbase + TM_HLO, wdesc(whi, TT::T_WO, TT::NO),
-                            wdesc(wlo, TT::T_WO, TT::NO), TT::NO, HID / 8, ID16, false);
-                }
-                tc::mma_commit(&bar);
+            nbar_arrive(FB_LAYER, TCF_THREADS);         // my columns of h are in place: the issuing warp takes it from here
+            TQ(5)  // arrive
+            if (L == 0) {
+                // the tile after next: its slot holds the current tile index, which everyone (the issuing warp too)
+                // has in a register by now; readers are ordered behind this store by the barriers that follow
+                if (tid == 0) s_tile[slot] = (long long)after_next;
+                nbar_sync(FB_WORK, TC_THREADS);         // next tile's points / voxel addressing are published
             }
             TQ(6)  // MMA issue (warp 0)
             // ---- a slice of the next tile's inputs while the tensor core works ------------------------
@@ -438,13 +480,8 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
         tc::fence_async_smem();
         tc::fence_before_sync();
         TQ(9)  // output
-        __syncthreads();
-        if (has_next && warp == 0 && tc::elect_one()) {
-            tc::fence_after_sync();
-            issue_input_gemms();
-        }
-        tc::fence_after_sync();
-        TQ(10) // end-of-tile barrier + up-front GEMM issue
+        nbar_arrive(FB_INPUT, TCF_THREADS);
+        TQ(10) // end of tile
         tile = nxt;
         slot ^= 1;
     }
@@ -457,7 +494,7 @@ __device__ void tc_forward_cta(const StageParams& P, const DecTask& T, int task,
     if (warp == 0) tc::tmem_dealloc<512>(tbase);
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(TCF_THREADS, 1)
 k_decoders_forward_tc(const __grid_constant__ StageParams P) {
     extern __shared__ __align__(16) float sm[];
     pdl_launch_dependents();     // the compositing kernel may be scheduled as CTAs of this kernel retire
