@@ -1592,6 +1592,9 @@ extern "C" int nsb_decoders_backward(const NsbPoints* pts, const NsbScene* scene
             timing_mark(2, 0, (cudaStream_t)stream);
             const bool dw_tc = g_use_tc && g_use_dw_tc && (T.kind == KIND_COLOR || T.kind == KIND_MIDDLE);
             if (dw_tc) {
+                // one wave whatever the batch: a CTA walks its strided share of the records, accumulators stay in TMEM
+                grid = dp.ntiles < g_num_sms ? dp.ntiles : g_num_sms;
+                if (dw_cap > 0 && grid > dw_cap) grid = dw_cap;
                 DwTcParams tp;
                 tp.p = dp;
                 tp.kind = T.kind;

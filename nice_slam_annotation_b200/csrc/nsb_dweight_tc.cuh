@@ -66,7 +66,7 @@ struct DwTcSmem {          // float offsets in dynamic shared memory (base align
     static constexpr int S_RAW = 0;
     static constexpr int S_LO = S_RAW + DWT_RING * RC::REC;
     static constexpr int S_LIVE = S_LO + DWT_LO * (X_LO + G_LO);
-    static constexpr int S_BAR = S_LIVE + DW_LIVE_MAX;         // mbarriers (8 B each)
+    static constexpr int S_BAR = S_LIVE + 16;                  // mbarriers (8 B each)
     static constexpr int S_END = S_BAR + 2 * (2 * DWT_RING + DWT_LO) + 2;
     static_assert(RC::REC % 128 == 0, "records keep the 512-byte atom alignment");
     static_assert(RC::R_H == RC::R_C + 4 * RC::ATOM && RC::R_DH == RC::R_DA + 5 * RC::ATOM, "operand stacks are adjacent");
@@ -99,7 +99,6 @@ __device__ void dweight_tc_body(const DwParams& P, const DwTcOffs& O, float* sm,
     __shared__ uint32_t s_tmem;
     __shared__ int s_nlive;
     __shared__ int s_warp_cnt[DWT_THREADS / 32];
-    int* s_live = reinterpret_cast<int*>(sm + S::S_LIVE);
     uint64_t* bars = reinterpret_cast<uint64_t*>(sm + S::S_BAR);
     uint64_t* full = bars;                   // [RING] record landed
     uint64_t* done = bars + DWT_RING;        // [RING] the MMAs that read the record (and its lo image) have completed
@@ -111,48 +110,28 @@ __device__ void dweight_tc_body(const DwParams& P, const DwTcOffs& O, float* sm,
         tc::mbar_init_fence();
     }
     pdl_wait();                              // flags and records come from the kernels before
-    // balanced shares of the live records, as in k_dweight
+    // CTA b takes the records T - 1 - (b + k G), k = 0, 1, ..., that are live: strided, so that all CTAs work on the same
+    // age band at any time (and get statistically equal shares), and newest first -- the backward wrote its sections
+    // in tile order, the last ones are the likeliest to be still in L2.  Only the count is needed up front; the
+    // producer warp finds the live ones as it goes (32 flags per ballot).
     const long long T_ = P.ntiles;
-    const int per_thread = (int)((T_ + DWT_THREADS - 1) / DWT_THREADS);
-    const long long my0 = (long long)threadIdx.x * per_thread;
-    int mine = 0;
-    for (int j = 0; j < per_thread; ++j) {
-        const long long i = my0 + j;
-        if (i < T_ && P.flags[i] != 0) ++mine;
-    }
-    int incl = mine;
+    const int G_ = (int)gridDim.x, b_ = (int)blockIdx.x;
+    const int cand = T_ > b_ ? (int)((T_ - 1 - b_) / G_) + 1 : 0;
+    {
+        int mine = 0;
+        for (int k = threadIdx.x; k < cand; k += DWT_THREADS)
+            if (P.flags[T_ - 1 - (b_ + (long long)k * G_)] != 0) ++mine;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const int o = __shfl_up_sync(FULL, incl, d);
-        if (lane >= d) incl += o;
+        for (int d = 16; d > 0; d >>= 1) mine += __shfl_xor_sync(FULL, mine, d);
+        if (lane == 0) s_warp_cnt[warp] = mine;
     }
-    if (lane == 31) s_warp_cnt[warp] = incl;
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
-    int before = incl - mine, total = 0;
-    for (int w = 0; w < DWT_THREADS / 32; ++w) {
-        const int c = s_warp_cnt[w];
-        if (w < warp) before += c;
-        total += c;
-    }
-    // CTA b takes the live records of rank total - 1 - (b + k G), k = 0, 1, ..: strided, so that all CTAs work on the
-    // same age band at any time, and newest first -- the backward wrote its sections in tile order, the last ones are
-    // the likeliest to be still in L2
-    {
-        int rank = before;
-        for (int j = 0; j < per_thread; ++j) {
-            const long long i = my0 + j;
-            if (i < T_ && P.flags[i] != 0) {
-                const int rr = total - 1 - rank;
-                if (rr % (int)gridDim.x == (int)blockIdx.x && rr / (int)gridDim.x < DW_LIVE_MAX) s_live[rr / (int)gridDim.x] = (int)i;
-                ++rank;
-            }
-        }
-    }
     if (threadIdx.x == 0) {
-        const int cnt = total > (int)blockIdx.x ? (total - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
-        s_nlive = cnt < DW_LIVE_MAX ? cnt : DW_LIVE_MAX;
+        int total = 0;
+        for (int w = 0; w < DWT_THREADS / 32; ++w) total += s_warp_cnt[w];
+        s_nlive = total;
     }
     __syncthreads();
     const int nlive = s_nlive;
@@ -174,19 +153,33 @@ __device__ void dweight_tc_body(const DwParams& P, const DwTcOffs& O, float* sm,
         __syncthreads();
     };
     if (warp == 0) {
-        // ---- producer ------------------------------------------------------------------------------------------
-        if (lane == 0) {
-            for (int i = 0; i < nlive; ++i) {
+        // ---- producer (whole warp: 32 candidate flags per ballot, lane 0 issues the copies) --------------------------
+        int k0 = 0;                                  // first candidate of the current 32-candidate window
+        unsigned live_bits = 0u;                     // live candidates of the window not yet taken
+        bool have_window = false;
+        for (int i = 0; i < nlive; ++i) {
+            while (live_bits == 0u) {
+                if (have_window) k0 += 32;
+                have_window = true;
+                const int k = k0 + lane;
+                const bool lv = k < cand && P.flags[T_ - 1 - (b_ + (long long)k * G_)] != 0;
+                live_bits = __ballot_sync(FULL, lv);
+            }
+            const int bit = __ffs(live_bits) - 1;
+            live_bits &= live_bits - 1u;
+            const long long rec_index = T_ - 1 - (b_ + (long long)(k0 + bit) * G_);
+            if (lane == 0) {
                 const int s = i % DWT_RING;
                 if (i >= DWT_RING) tc::mbar_wait(done + s, (uint32_t)((i / DWT_RING - 1) & 1));
                 mbar_expect_tx(full + s, REC_BYTES);
-                const char* src = reinterpret_cast<const char*>(P.scratch + (size_t)s_live[i] * RC::REC);
+                const char* src = reinterpret_cast<const char*>(P.scratch + (size_t)rec_index * RC::REC);
                 char* dst = reinterpret_cast<char*>(raw + s * RC::REC);
                 constexpr uint32_t PART = REC_BYTES / 3;
                 static_assert(PART % 16 == 0 && PART * 3 == REC_BYTES, "bulk copy granularity");
 #pragma unroll
                 for (int c = 0; c < 3; ++c) bulk_g2s(dst + c * PART, src + c * PART, PART, full + s);
             }
+            __syncwarp();
         }
         __syncwarp();
         finish_loops();
