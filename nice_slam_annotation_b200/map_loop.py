@@ -21,7 +21,7 @@ import torch
 from . import fused
 from ._lib import check, lib
 from .fused import DEC_NAMES, GRID_KEYS, STAGE_DECODERS, _ptr, _stream, canonical_params
-from .step import FusedStep
+from .step import FusedStep, graph_capture
 
 BETAS, EPS = (0.9, 0.999), 1e-8          # torch.optim.Adam defaults (the reference passes none)
 GROUP_LR = {"grid_coarse": "coarse_lr", "grid_middle": "middle_lr", "grid_fine": "fine_lr", "grid_color": "color_lr"}
@@ -294,7 +294,7 @@ class MappingLoop:
             self.indices.copy_(keep_idx)
             g = torch.cuda.CUDAGraph()
             torch.cuda.synchronize()
-            with torch.cuda.graph(g):
+            with graph_capture(g):
                 self._launch(stage)
             self.graphs[key] = g
         g.replay()

@@ -13,6 +13,8 @@ step.  The batch-global scalar ``max(gt_depth)`` (src/utils/Renderer.py:157,194)
 so the sharded render equals the unsharded one.
 """
 import ctypes as C
+import contextlib
+import gc
 import os
 
 import torch
@@ -25,6 +27,25 @@ from .fused import DEC_NAMES, GRID_KEYS, STAGE_DECODERS, _linspace, _ptr, _strea
 # ---------------------------------------------------------------------------------------
 # gradient bucket (pure torch: also exercised on CPU / gloo by the tests)
 # ---------------------------------------------------------------------------------------
+@contextlib.contextmanager
+def graph_capture(g):
+    """``torch.cuda.graph(g)`` with Python's cyclic garbage collector off for the duration of the capture.  A collection
+    that happens to run while a stream is capturing can free CUDA objects of unrelated, already dead owners (steps,
+    graphs, side streams of earlier work) and the allocator's bookkeeping for them invalidates the capture
+    (cudaErrorStreamCaptureInvalidated at the next launch) -- seen when merely the number of collected test items moved
+    the collector's trigger into a capture.  torch collects once before the capture starts; nothing needs collecting
+    during it."""
+    was = gc.isenabled()
+    gc.collect()
+    gc.disable()
+    try:
+        with torch.cuda.graph(g):
+            yield
+    finally:
+        if was:
+            gc.enable()
+
+
 class GradBucket:
     """Gradients of a list of leaves as views of one flat fp32 buffer.
 
@@ -180,7 +201,14 @@ class FusedStep:
         self.g_color = torch.zeros(N, 3, device=dev)
         self.g_rays_o = torch.zeros(N, 3, device=dev) if ray_grads else None
         self.g_rays_d = torch.zeros(N, 3, device=dev) if ray_grads else None
-        self.ws = torch.empty(max(lib().nsb_render_workspace_bytes(N, self.S), 1), dtype=torch.uint8, device=dev)
+        # Large mapping batches run as ray chunks (forward + loss + backward per chunk, gradients accumulate in the bucket):
+        # rays are independent once the batch depth max is known, so the result is the same, the per-call buffers stay
+        # small and every chunk keeps the deposit + tcgen05 backward path (whole-batch records, nsb_layout.h).
+        chunk = int(os.environ.get("NSB_STEP_CHUNK_RAYS", "16384"))
+        can_chunk = (loss == "mapping" and self.with_gt_depth and bool(renderer.occupancy))      # = fused_loss below
+        self.chunk = min(N, max(chunk, 1)) if can_chunk else N
+        self.nchunk = (N + self.chunk - 1) // self.chunk
+        self.ws = torch.empty(max(lib().nsb_render_workspace_bytes(self.chunk, self.S), 1), dtype=torch.uint8, device=dev)
         # gradient bucket: grids first, then one flat canonical segment per trainable decoder
         self.grid_grad_kinds = [k for k in self.kinds if GRID_KEYS[k] in grid_grads]
         self.dec_grad_kinds = [k for k in self.kinds if DEC_NAMES[k] in decoder_grads]
@@ -189,7 +217,7 @@ class FusedStep:
         self.bucket = GradBucket(leaves + self.dw_holders, dev, peers) if (leaves or self.dw_holders) else None
         self.scratch = None
         if self.dec_grad_kinds:
-            nbytes = len(self.dec_grad_kinds) * lib().nsb_dweight_scratch_bytes(self.dec_grad_kinds[0], N * self.S)
+            nbytes = len(self.dec_grad_kinds) * lib().nsb_dweight_scratch_bytes(self.dec_grad_kinds[0], self.chunk * self.S)
             self.scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         # static packed decoder blobs, re-packed in place from the live parameters
         self.packed, self._pack_args = {}, {}
@@ -201,7 +229,9 @@ class FusedStep:
             self.packed[k] = torch.empty(lib().nsb_packed_numel(k), device=dev)
             self._pack_args[k] = (ptrs, params, pack_table(k, dev))
             self._pack(k)
-        self._call = self._build_call()
+        self.loss_parts = torch.zeros(self.nchunk, dtype=torch.float64, device=dev) if self.nchunk > 1 else None
+        self._calls = [self._build_call(i * self.chunk, min(self.chunk, N - i * self.chunk), i) for i in range(self.nchunk)]
+        self._call = self._calls[0]
         self.graph = None
         self._side = None
         self._xside = None
@@ -222,17 +252,19 @@ class FusedStep:
         ptrs, _, table = self._pack_args[k]
         check(lib().nsb_pack_weights(k, _ptr(ptrs), _ptr(table), _ptr(self.packed[k]), _stream()), "pack_weights")
 
-    def _build_call(self):
+    def _build_call(self, off=0, n=None, part=0):
+        """The render call of rays [off, off + n) (one chunk; the whole batch by default)."""
         r, dev = self.r, self.dev
+        n = self.N if n is None else n
         call = NsbRenderCall()
-        call.rays_o, call.rays_d = self.rays_o.data_ptr(), self.rays_d.data_ptr()
+        call.rays_o, call.rays_d = self.rays_o[off:].data_ptr(), self.rays_d[off:].data_ptr()
         call.rays_o_stride = call.rays_d_stride = 3
-        call.N = self.N
-        call.gt_depth = self.gt_depth.data_ptr() if self.with_gt_depth else 0
-        call.keep = self.keep.data_ptr()
-        # sharded: the batch depth max is MAX-reduced over ranks by load(); one rank: the render
-        # call computes it itself (inside the captured graph)
-        call.depth_max = self.depth_max.data_ptr() if (self.with_gt_depth and self._sharded()) else 0
+        call.N = n
+        call.gt_depth = self.gt_depth[off:].data_ptr() if self.with_gt_depth else 0
+        call.keep = self.keep[off:].data_ptr()
+        # sharded: the batch depth max is MAX-reduced over ranks by load(); chunked: _launch computes it over the whole
+        # batch first; otherwise the render call computes it itself (inside the captured graph)
+        call.depth_max = self.depth_max.data_ptr() if (self.with_gt_depth and (self._sharded() or self.nchunk > 1)) else 0
         call.N_samples, call.N_surface = r.N_samples, r.N_surface
         call.lindisp, call.stage, call.occupancy = int(r.lindisp), STAGES[self.stage], int(r.occupancy)
         call.t_uniform = _linspace(r.N_samples, torch.float32, dev).data_ptr()
@@ -240,8 +272,8 @@ class FusedStep:
         grads = {k: self.bucket.view_of(self.grids[k]) for k in self.grid_grad_kinds}
         call.scene = fused.make_scene(r.bound, self.grids, self.packed, grads, r.coarse_bound_enlarge)
         call.workspace, call.workspace_bytes = self.ws.data_ptr(), self.ws.numel()
-        call.depth, call.var, call.color = self.depth.data_ptr(), self.var.data_ptr(), self.color.data_ptr()
-        call.g_depth, call.g_color = self.g_depth.data_ptr(), self.g_color.data_ptr()
+        call.depth, call.var, call.color = self.depth[off:].data_ptr(), self.var[off:].data_ptr(), self.color[off:].data_ptr()
+        call.g_depth, call.g_color = self.g_depth[off:].data_ptr(), self.g_color[off:].data_ptr()
         flags, mask = (GRAD_GRID if self.grid_grad_kinds else 0), 0
         for k, h in zip(self.dec_grad_kinds, self.dw_holders):
             call.d_weight[k] = self.bucket.view_of(h).data_ptr()
@@ -251,7 +283,7 @@ class FusedStep:
             call.scratch, call.scratch_bytes = self.scratch.data_ptr(), self.scratch.numel()
         if self.ray_grads:
             flags |= GRAD_POINT
-            call.g_rays_o, call.g_rays_d = self.g_rays_o.data_ptr(), self.g_rays_d.data_ptr()
+            call.g_rays_o, call.g_rays_d = self.g_rays_o[off:].data_ptr(), self.g_rays_d[off:].data_ptr()
         call.flags, call.dweight_mask = flags, mask
         if self.bucket is not None and getattr(self.bucket, "marks", None) is not None:
             call.line_marks, call.line_marks_base = self.bucket.marks.data_ptr(), self.bucket.flat.data_ptr()
@@ -261,7 +293,8 @@ class FusedStep:
         # mapping: compositing + loss + their adjoint run as one kernel inside nsb_render_backward
         self.fused_loss = self.loss_kind == "mapping" and self.with_gt_depth and bool(r.occupancy)
         if self.fused_loss:
-            call.gt_color, call.loss = self.gt_color.data_ptr(), self.loss.data_ptr()
+            call.gt_color = self.gt_color[off:].data_ptr()
+            call.loss = self.loss.data_ptr() if self.nchunk == 1 else self.loss_parts[part:].data_ptr()
             call.w_color, call.use_color = float(self.w_color), int(self.use_color)
         return call
 
@@ -346,6 +379,18 @@ class FusedStep:
         if self._peer_max:                       # batch depth max over all ranks, through peer memory
             check(lib().nsb_depth_max_peers(C.byref(self.bucket._px), _ptr(self.gt_depth), _ptr(self.keep), self.N,
                                             _ptr(self.depth_max), s), "depth_max_peers")
+        if self.nchunk > 1:
+            if not self._sharded():              # the batch-global depth max, once for all chunks
+                check(lib().nsb_depth_max(_ptr(self.gt_depth), _ptr(self.keep), self.N, _ptr(self.depth_max), s), "depth_max")
+            for i, c in enumerate(self._calls):
+                check(lib().nsb_render_forward(C.byref(c), s), "render_forward")
+                if i == 0 and joined is not None:
+                    torch.cuda.current_stream().wait_stream(joined)
+                check(lib().nsb_render_backward(C.byref(c), s), "render_backward")
+            torch.sum(self.loss_parts, dim=0, keepdim=True, out=self.loss)
+            if exchange and self.bucket is not None and self.bucket.peers is not None:
+                self.bucket.all_reduce()
+            return
         check(lib().nsb_render_forward(C.byref(call), s), "render_forward")
         if joined is not None:
             torch.cuda.current_stream().wait_stream(joined)
@@ -394,7 +439,7 @@ class FusedStep:
         """Record the iteration into a CUDA graph (call once after a warm-up ``run``)."""
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize()
-        with torch.cuda.graph(g):
+        with graph_capture(g):
             self._launch()
         self.graph = g
 
@@ -414,7 +459,7 @@ class FusedStep:
                 self._packed_dev = torch.empty(self.N, 10, device=self.dev)
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize()
-        with torch.cuda.graph(g):
+        with graph_capture(g):
             self._packed_dev.copy_(self._host_stage, non_blocking=True)
             self._keep_dev.copy_(self._host_keep, non_blocking=True)
             check(lib().nsb_load_batch_packed(_ptr(self._packed_dev), _ptr(self._keep_dev), self.N, self.N,
@@ -567,7 +612,7 @@ class TrackingStep:
     def capture(self):
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize()
-        with torch.cuda.graph(g):
+        with graph_capture(g):
             self._launch()
         self.graph = g
 
@@ -592,7 +637,7 @@ class TrackingStep:
             self.indices.copy_(keep)
             g = torch.cuda.CUDAGraph()
             torch.cuda.synchronize()
-            with torch.cuda.graph(g):
+            with graph_capture(g):
                 self._launch()
             self._api_graphs[bool(draw)] = g
         g.replay()

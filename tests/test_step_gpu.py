@@ -209,3 +209,32 @@ def test_step_from_host_matches_load_and_run(scene):
         l1 = b.step_from_host(FusedStep.pack_batch(*batch[:4]))
         assert abs(l1 - l0) <= 1e-9 * abs(l0)
         assert_close(b.bucket.flat.cpu(), g0.cpu(), 1e-5, "bucket")
+
+
+@pytest.mark.parametrize("chunk", [96, 250])
+def test_chunked_step_equals_whole_batch(scene, chunk, monkeypatch):
+    """A large mapping batch runs as ray chunks (forward + loss + backward per chunk, step.FusedStep.chunk); with the
+    batch depth max computed once over the whole batch every value must equal the single-call step: outputs bit for
+    bit, loss to rounding, gradients to atomic-order noise.  Ragged last chunk, dropped rays, graph replay."""
+    from nice_slam_annotation_b200.step import FusedStep
+    ns = scene
+    n = 600
+    ro, rd, gd, gc, keep = _batch(ns, n, seed=13)
+    kw = dict(loss="mapping", w_color=0.2, use_color=True, grid_grads=("grid_middle", "grid_fine", "grid_color"),
+              decoder_grads=("color_decoder",), ray_grads=True)
+    whole = FusedStep(ns.renderer, ns.shared_decoders, ns.shared_c, "color", n, **kw)
+    assert whole.nchunk == 1
+    monkeypatch.setenv("NSB_STEP_CHUNK_RAYS", str(chunk))
+    parts = FusedStep(ns.renderer, ns.shared_decoders, ns.shared_c, "color", n, **kw)
+    assert parts.nchunk == (n + chunk - 1) // chunk and parts.chunk == chunk
+    for st in (whole, parts):
+        st.load(ro, rd, gd, gc, keep=keep)
+        st.run()
+    parts.capture()
+    parts.run()
+    torch.cuda.synchronize()
+    for name in ("depth", "var", "color", "g_rays_o", "g_rays_d"):
+        assert torch.equal(getattr(parts, name), getattr(whole, name)), name
+    assert abs(float(parts.loss) - float(whole.loss)) <= 1e-12 * abs(float(whole.loss))
+    assert float(whole.bucket.flat.abs().max()) > 0
+    assert_close(parts.bucket.flat, whole.bucket.flat, 1e-5, "gradient bucket")
