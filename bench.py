@@ -418,8 +418,7 @@ def headline(ctx, ns):
                    "engine": "FusedStep: render forward + fused mapping loss + render backward as 2 library calls"
                              + ("" if args.no_graph else ", replayed as one CUDA graph"),
                    "arithmetic": "3xTF32 tensor-core products with fp32 accumulation (fp32-class accuracy), fp32 Fourier "
-                                 "embedding (Cody-Waite reduction + MUFU.SIN, 5e-7 absolute), fp64 sample depths / depth / "
-                                 "variance like the reference; outputs within 1e-5 of the reference (bar 1e-4)",
+                                 "embedding, fp64 sample depths / depth / variance like the reference",
                    "parallelism": f"rays sharded over {world} GPU(s), grids+decoders replicated"
                                   + ("; gradient exchange: " + exchange if world > 1 else ""),
                    "exchange": exchange, "exchange_kernel_ms": x_kernel_ms, "depth_max_peers_kernel_ms": dmax_kernel_ms,

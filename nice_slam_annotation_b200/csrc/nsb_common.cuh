@@ -229,11 +229,12 @@ __device__ __forceinline__ float sin_cw(float x) {
     const float v = fmaf(r * r2, q, r);
     return __uint_as_float(__float_as_uint(v) ^ ((uint32_t)(int)k << 31));
 }
-// Embedding sine of the tcgen05 forward: x = 2 pi k + r by a two-term Cody-Waite reduction (exact to ~1e-7 for
-// |x| < 1e5, the FMA rounds once), then the special-function unit (MUFU.SIN: 2^-21.4 absolute error on [-pi, pi]).
-// 9 instructions instead of sin_cw's 17: the forward evaluates 13.4 M of these per 1000-ray step, its largest block
-// of issue slots.  Absolute error ~5e-7 on values in [-1, 1] -- 200 x below the 1e-4 parity bar (outputs stay at
-// ~2e-6 of the reference, tests/test_gpu_parity.py); NSB_NVCC_EXTRA=-DNSB_EXACT_SIN restores sin_cw.
+// Embedding sine of the tcgen05 forward: x = 2 pi k + r by a two-term Cody-Waite reduction (the FMA rounds once; exact to
+// ~1e-7 for |x| < 1e5), then the special-function unit (MUFU.SIN: 2^-21.4 absolute error on [-pi, pi]).  9 instructions
+// instead of sin_cw's 17 for the 13.4 M evaluations of a 1000-ray step: forward 104.6 -> 100.3 us.  Parity is unchanged
+// within noise -- outputs against the fp32 torch oracle at the bench workload (scripts/accuracy_probe.py): depth / variance /
+// colour 2.7e-6 / 7.6e-6 / 6.1e-6 with it, 2.9e-6 / 5.6e-6 / 7.7e-6 with sin_cw (bar 1e-4): the difference to torch is the
+// summation order of the layers, not the sine.  -DNSB_EXACT_SIN (NSB_NVCC_EXTRA) restores sin_cw.
 __device__ __forceinline__ float sin_embed(float x) {
 #ifdef NSB_EXACT_SIN
     return sin_cw(x);
