@@ -483,8 +483,10 @@ def roofline_block(ctx, pts, fwd_ms, bwd_ms, dw_ms, step_ms):
         "hbm": {"peak_gbs": hbm,
                 "k_decoders_forward_tc": hbm_view(BYTES_PER_POINT_FWD * pts, fwd_ms, "k_decoders_forward_tc"),
                 "k_decoders_backward_tc": hbm_view(BYTES_PER_POINT_BWD * pts, bwd_ms, "k_decoders_backward_tc"),
-                "k_dweight": {"kernel_ms": dw_ms, "algorithmic_bytes_per_launch": 0,
-                              "dram_bytes_per_launch_ncu": dram("k_dweight")},
+                "k_dweight_tc": {"kernel_ms": dw_ms, "algorithmic_bytes_per_launch": 0,
+                                 "dram_bytes_per_launch_ncu": dram("k_dweight_tc") or dram("k_dweight"),
+                                 "note": "SURVEY.md 8d assigns the weight gradient no bytes; what it streams is the "
+                                         "16-point records (47.6 KB each, live ones only)"},
                 "step": hbm_view((BYTES_PER_POINT_FWD + BYTES_PER_POINT_BWD) * pts, step_ms, None),
                 "note": "request level = 8 corners x 128 B per level per point, no cache credit (SURVEY.md 8d): forward "
                         "3072 B/pt (gather), mapping backward 6144 B/pt (scatter RMW; it does not re-gather); the grids "
