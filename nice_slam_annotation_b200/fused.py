@@ -6,6 +6,7 @@ autograd node ``_RenderFn`` replaces the ~620 ATen kernels the reference launche
 ``Renderer.render_batch_ray`` forward + backward.
 """
 import ctypes as C
+import os
 import weakref
 
 import numpy as np
@@ -365,8 +366,27 @@ class _RenderFn(torch.autograd.Function):
             ws = torch.empty(max(lib().nsb_render_workspace_bytes(N, S), 1), dtype=torch.uint8, device=dev)
             if meta.get("u") is not None:
                 meta["u"] = meta["u"].to(device=dev, dtype=torch.float32).contiguous()
+            # decoders whose parameters want a gradient: the forward deposits their layer inputs into the weight-gradient
+            # records (NsbRenderCall.deposit_dweight_inputs), the backward then runs the tcgen05 adjoint without
+            # recomputation; the scratch lives from here to the backward
+            ctx.dw_scratch, ctx.dw_mask = None, 0
             if N > 0:
                 call = _render_call(meta, rays_o, rays_d, grids, None, ws, depth, var, color)
+                need_param = ctx.needs_input_grad[3 + n_grid:]
+                if torch.is_grad_enabled() and any(need_param) and os.environ.get("NSB_DEPOSIT", "1") != "0":
+                    pi, mask = 0, 0
+                    for k in kinds:
+                        n = lib().nsb_param_count(k)
+                        if any(need_param[pi:pi + n]):
+                            mask |= 1 << k
+                        pi += n
+                    if mask:
+                        ndw = bin(mask).count("1")
+                        nbytes = ndw * max(lib().nsb_dweight_scratch_bytes(k, N * S) for k in kinds if mask & (1 << k))
+                        ctx.dw_scratch, ctx.dw_mask = torch.empty(nbytes, dtype=torch.uint8, device=dev), mask
+                        call.scratch, call.scratch_bytes = ctx.dw_scratch.data_ptr(), nbytes
+                        call.flags, call.dweight_mask = GRAD_WEIGHT, mask
+                        call.deposit_dweight_inputs = 1
                 check(lib().nsb_render_forward(C.byref(call), _stream()), "render_forward")
             ctx.meta, ctx.kinds, ctx.n_grid, ctx.fused_ws, ctx.S = meta, kinds, n_grid, ws, S
             ctx.param_shapes = [p.shape for p in flat_params]
@@ -454,9 +474,13 @@ class _RenderFn(torch.autograd.Function):
             pi += n
         if dw_mask:
             flags |= GRAD_WEIGHT
-            nbytes = len(dw) * max(lib().nsb_dweight_scratch_bytes(k, P) for k in dw)
-            hold.append(torch.empty(nbytes, dtype=torch.uint8, device=dev))
-            call.scratch, call.scratch_bytes = hold[-1].data_ptr(), nbytes
+            if ctx.dw_scratch is not None and ctx.dw_mask == dw_mask:      # the forward deposited into it
+                call.scratch, call.scratch_bytes = ctx.dw_scratch.data_ptr(), ctx.dw_scratch.numel()
+                call.deposit_dweight_inputs = 1
+            else:
+                nbytes = len(dw) * max(lib().nsb_dweight_scratch_bytes(k, P) for k in dw)
+                hold.append(torch.empty(nbytes, dtype=torch.uint8, device=dev))
+                call.scratch, call.scratch_bytes = hold[-1].data_ptr(), nbytes
         if need_rays:
             flags |= GRAD_POINT
             g_o = torch.empty(N, 3, dtype=torch.float32, device=dev)
