@@ -236,6 +236,14 @@ def test_apartment_5000_ray_mapping_step_vs_oracle():
     assert kept > 4500
 
 
+def test_demo_config_step_vs_oracle():
+    """configs[0]: the reference's CPU-runnable case -- Demo config (configs/Demo/demo.yaml: ScanNet frames cropped to
+    460x620, bound [[0,6.5],[0,4],[0,3.5]], 5.8 MB of grids), 1000 rays, stage color, forward + backward."""
+    ns = _scene("demo", 5)
+    kept = _engine_vs_oracle(ns, 200, seed=30)
+    assert kept > 800
+
+
 def test_tum_scale_grid_mapping_step_vs_oracle():
     """TUM fr3_office grid lengths (0.16 / 0.08 / 0.08 m): 127^3-class fine / colour grids, 556 MB, far beyond L2 and
     beyond 2^31 bytes of voxel offsets x channel (the kernels index voxels with 32-bit, bytes with 64-bit arithmetic)."""
