@@ -197,7 +197,9 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange(const __grid_constant__ 
 
 // Sparse two-shot all-reduce.  One mapping step touches 16 % (1000 rays) to 39 % (8000 rays) of the
 // 128-byte voxel lines of the Replica bucket (scripts/bucket_sparsity.py), so most of a dense
-// exchange moves zeros.  Unit = 32 lines (4 KB); rank o owns units [o * per_u, (o + 1) * per_u).
+// exchange moves zeros.  Unit = 32 lines (4 KB); rank o owns the units u = v * world + o (v < per_u): interleaved, because
+// the touched lines of a step are a spatial subset of the grids (the camera frusta) and contiguous slices left some
+// owners with most of the work while the others waited at the closing barrier.
 //   A  every rank scans its local copy and publishes one bit per line (word per unit) in symmetric memory
 //   -- barrier --
 //   C  the owner ORs the words of all ranks and reduces / stores only lines some rank touched
@@ -226,7 +228,7 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange_sparse(const __grid_cons
         unsigned char* mb = reinterpret_cast<unsigned char*>(g.marks) + 128;
         for (int o = 0; o < g.world; ++o)
             for (long long v = gw; v < per_u; v += nw) {
-                const long long u = o * per_u + v;
+                const long long u = v * g.world + o;
                 if (u >= n_units || u >= covered) break;
                 const unsigned char m = __ldcg(mb + u * 32 + lane);
                 const unsigned word = __ballot_sync(FULL, m != 0);
@@ -239,7 +241,7 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange_sparse(const __grid_cons
     }
     for (int o = 0; o < g.world; ++o)
         for (long long v = gw; v < per_u; v += nw) {
-            const long long u = o * per_u + v;
+            const long long u = v * g.world + o;
             if (u >= n_units) break;
             if (u < covered) continue;
             unsigned word = 0u;
@@ -275,7 +277,7 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange_sparse(const __grid_cons
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
             unsigned w = 0u;
-            const bool live = v[k] < per_u && g.rank * per_u + v[k] < n_units;
+            const bool live = v[k] < per_u && v[k] * g.world + g.rank < n_units;
             if (live && lane < g.world) {
                 const unsigned* p = words + lane * per_u + v[k];
                 asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(w) : "l"(p) : "memory");
@@ -285,7 +287,7 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange_sparse(const __grid_cons
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
             if (!word[k]) continue;
-            const long long u = g.rank * per_u + v[k];
+            const long long u = v[k] * g.world + g.rank;
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const long long i4 = u * 256 + j * 32 + lane;
@@ -295,7 +297,7 @@ __global__ void __launch_bounds__(X_THREADS) k_exchange_sparse(const __grid_cons
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
             if (!word[k]) continue;
-            const long long u = g.rank * per_u + v[k];
+            const long long u = v[k] * g.world + g.rank;
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const long long i4 = u * 256 + j * 32 + lane;
