@@ -270,6 +270,13 @@ int nsb_ray_grad_reduce(const NsbPoints* rays, const float* d_point, int ndec,
 int nsb_pose_grad(const float* g_rays_o, const float* g_rays_d, const int64_t* indices,
                   const uint8_t* keep, int64_t n, int H0, int W0, int Wc, float fx, float fy,
                   float cx, float cy, const float* cam7, float* d_cam7, void* stream);
+/* the same followed, in the same launch, by the camera optimiser's step of nsb_cam_adam (src/Tracker.py:232-242,
+ * 262-275): cam7 is read for the gradient and then updated in place. */
+int nsb_pose_grad_adam(const float* g_rays_o, const float* g_rays_d, const int64_t* indices,
+                       const uint8_t* keep, int64_t n, int H0, int W0, int Wc, float fx, float fy,
+                       float cx, float cy, float* cam7, float* d_cam7, float* m, float* v, int32_t* step,
+                       float lr_q, float lr_t, float beta1, float beta2, float eps, const double* loss,
+                       double* best_loss, float* best_cam, void* stream);
 
 /* test hook: D[128,N] = A[128,K] W[N,K]^T on the tcgen05 tensor cores (kind::tf32).  mode bit 0:
  * A operand from tensor memory instead of shared memory; bit 1: 3xTF32 error compensation. */

@@ -159,6 +159,9 @@ _SIGS = {
                                     C.POINTER(NsbImapGrads), c_ptr, c_ptr, c_ptr]),
     "nsb_gemm3x": (C.c_int, [c_ptr, C.c_int64, C.c_int, c_ptr, C.c_int64, C.c_int, c_ptr, C.c_int64, C.c_int64,
                              C.c_int, C.c_int64, C.c_int, c_ptr, c_ptr, C.c_int64, c_ptr, C.c_int, c_ptr]),
+    "nsb_pose_grad_adam": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_int, C.c_int, C.c_int,
+                                     C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                                     C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, c_ptr, c_ptr, c_ptr]),
     "nsb_cam_adam": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_float, C.c_float, C.c_float, C.c_float,
                                C.c_float, c_ptr, c_ptr, c_ptr, c_ptr]),
 }

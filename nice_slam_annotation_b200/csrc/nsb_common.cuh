@@ -258,6 +258,47 @@ __device__ __forceinline__ float cos_cw(float x) {
     return __uint_as_float(__float_as_uint(v) ^ ((uint32_t)(int)k << 31));
 }
 
+// Adam on the 7 camera parameters + the tracker's best-candidate rule (Tracker.py:232-242,262-275), executed by one warp
+// (lane i < 7 owns parameter i, g = its gradient); bias corrections in fp64 like torch's Python scalars.
+__device__ __forceinline__ void cam_adam_warp(int i, float g, float* cam, float* m, float* v, int* step, float lr_q, float lr_t,
+                                              float beta1, float beta2, float eps, const double* loss, double* best_loss,
+                                              float* best_cam) {
+    const int t = step[0] + 1;
+    __syncwarp();
+    if (i == 0) step[0] = t;
+    float p = 0.f;
+    if (i < 7) {
+        const float mi = m[i] + (g - m[i]) * (1.f - beta1);              // exp_avg.lerp_(grad, 1 - beta1)
+        const float vi = v[i] * beta2 + (1.f - beta2) * g * g;
+        m[i] = mi;
+        v[i] = vi;
+        const double bc1 = 1.0 - pow((double)beta1, (double)t), bc2 = 1.0 - pow((double)beta2, (double)t);
+        const float step_size = (float)((double)(i < 4 ? lr_q : lr_t) / bc1);
+        const float denom = sqrtf(vi) / (float)sqrt(bc2) + eps;
+        p = cam[i] - step_size * (mi / denom);
+        cam[i] = p;
+    }
+    if (best_loss && loss[0] < best_loss[0]) {                            // uniform over the warp
+        __syncwarp();
+        if (i < 7) best_cam[i] = p;
+        if (i == 0) best_loss[0] = loss[0];
+    }
+}
+
+// cos(x) of the tcgen05 backward's embedding gradient d(e) cos(pB): sin_embed's reduction + MUFU.COS (gradients are
+// compared at 1e-3; -DNSB_EXACT_SIN restores cos_cw as well).
+__device__ __forceinline__ float cos_embed(float x) {
+#ifdef NSB_EXACT_SIN
+    return cos_cw(x);
+#else
+    if (fabsf(x) > 1.0e5f) return cos_slow(x);
+    const float k = rintf(x * 0.15915494309f);
+    float r = fmaf(k, -6.2831855f, x);
+    r = fmaf(k, 1.7484555e-07f, r);
+    return __cosf(r);
+#endif
+}
+
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};\n" ::"l"(addr), "f"(a), "f"(b),
                  "f"(c), "f"(d)

@@ -431,14 +431,21 @@ __global__ void k_ray_grad_reduce(PointsDev q, const float* __restrict__ d_point
     }
 }
 
+struct CamAdam {        // optional Adam step on the camera tensor at the end of k_pose_grad (cam == NULL: none)
+    float* cam; float* m; float* v; int* step;
+    float lr_q, lr_t, beta1, beta2, eps;
+    const double* loss; double* best_loss; float* best_cam;
+};
+
 // d(camera_tensor): dt = sum g_o ; dR = sum g_d (x) dirs ; dq = J(quad2rotation)^T dR
 __global__ void k_pose_grad(const float* __restrict__ g_o, const float* __restrict__ g_d,
                             const int64_t* __restrict__ indices, const uint8_t* __restrict__ keep,
                             long long n, int H0, int W0, int wc, float fx, float fy, float cx,
-                            float cy, const float* __restrict__ cam7, float* __restrict__ d_cam7) {
+                            float cy, const float* __restrict__ cam7, float* __restrict__ d_cam7, CamAdam A) {
     pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
     pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     __shared__ double red[12][32];
+    __shared__ float s_dc[8];
     double acc[12];
     for (int k = 0; k < 12; ++k) acc[k] = 0.0;
     for (long long r = threadIdx.x; r < n; r += blockDim.x) {
@@ -485,14 +492,20 @@ __global__ void k_pose_grad(const float* __restrict__ g_o, const float* __restri
         const double gqk = dR[0][0] * (-2 * qk) + dR[0][1] * (-qr) + dR[0][2] * qi + dR[1][0] * qr +
                            dR[1][1] * (-2 * qk) + dR[1][2] * qj + dR[2][0] * qi + dR[2][1] * qj;
         // s = 2/n, n = |q|^2: d(s)/d(q_m) = -2/n^2 * 2 q_m = -(s*s) q_m
-        d_cam7[0] = (float)(s * gqr - s * s * qr * dP);
-        d_cam7[1] = (float)(s * gqi - s * s * qi * dP);
-        d_cam7[2] = (float)(s * gqj - s * s * qj * dP);
-        d_cam7[3] = (float)(s * gqk - s * s * qk * dP);
-        d_cam7[4] = (float)dt[0];
-        d_cam7[5] = (float)dt[1];
-        d_cam7[6] = (float)dt[2];
+        s_dc[0] = (float)(s * gqr - s * s * qr * dP);
+        s_dc[1] = (float)(s * gqi - s * s * qi * dP);
+        s_dc[2] = (float)(s * gqj - s * s * qj * dP);
+        s_dc[3] = (float)(s * gqk - s * s * qk * dP);
+        s_dc[4] = (float)dt[0];
+        s_dc[5] = (float)dt[1];
+        s_dc[6] = (float)dt[2];
     }
+    __syncwarp();
+    const float g = lane < 7 ? s_dc[lane] : 0.f;
+    if (lane < 7) d_cam7[lane] = g;
+    // the camera optimiser's step in the same launch (nsb_pose_grad_adam): cam7 == A.cam is read above, written here
+    if (A.cam)
+        cam_adam_warp(lane, g, A.cam, A.m, A.v, A.step, A.lr_q, A.lr_t, A.beta1, A.beta2, A.eps, A.loss, A.best_loss, A.best_cam);
 }
 
 static int comp_params(const NsbPoints* rays, const double* b6, int stage, int occupancy,
@@ -572,7 +585,21 @@ extern "C" int nsb_pose_grad(const float* g_rays_o, const float* g_rays_d, const
                              float cx, float cy, const float* cam7, float* d_cam7, void* stream) {
     if (!g_rays_o || !g_rays_d || !indices || !cam7 || !d_cam7) return set_error(NSB_EINVAL, "null argument");
     launch_pdl(k_pose_grad, dim3(1), dim3(1024), 0, (cudaStream_t)stream, g_rays_o, g_rays_d, indices, keep, n, H0, W0, Wc, fx, fy,
-                                                     cx, cy, cam7, d_cam7);
+                                                     cx, cy, cam7, d_cam7, CamAdam{});
+    return check_launch("k_pose_grad");
+}
+
+extern "C" int nsb_pose_grad_adam(const float* g_rays_o, const float* g_rays_d, const int64_t* indices,
+                                  const uint8_t* keep, int64_t n, int H0, int W0, int Wc, float fx, float fy,
+                                  float cx, float cy, float* cam7, float* d_cam7, float* m, float* v, int32_t* step,
+                                  float lr_q, float lr_t, float beta1, float beta2, float eps, const double* loss,
+                                  double* best_loss, float* best_cam, void* stream) {
+    if (!g_rays_o || !g_rays_d || !indices || !cam7 || !d_cam7 || !m || !v || !step)
+        return set_error(NSB_EINVAL, "null argument");
+    if (best_loss && (!loss || !best_cam)) return set_error(NSB_EINVAL, "best_loss needs loss and best_cam");
+    CamAdam A{cam7, m, v, step, lr_q, lr_t, beta1, beta2, eps, loss, best_loss, best_cam};
+    launch_pdl(k_pose_grad, dim3(1), dim3(1024), 0, (cudaStream_t)stream, g_rays_o, g_rays_d, indices, keep, n, H0, W0, Wc, fx, fy,
+                                                     cx, cy, (const float*)cam7, d_cam7, A);
     return check_launch("k_pose_grad");
 }
 

@@ -400,7 +400,7 @@ __device__ void tc_backward_cta(const StageParams& P, const DecTask& T, int task
 #pragma unroll
                 for (int q = 0; q < 8; ++q) {
                     const float4 b = Bv[c0 + q];
-                    const float v = d8[q] * cos_cw(fmaf(pp.z, b.z, fmaf(pp.y, b.y, pp.x * b.x)));
+                    const float v = d8[q] * cos_embed(fmaf(pp.z, b.z, fmaf(pp.y, b.y, pp.x * b.x)));
                     d8[q] = v;
                     dp[0] = fmaf(v, b.x, dp[0]);
                     dp[1] = fmaf(v, b.y, dp[1]);

@@ -378,27 +378,7 @@ __global__ void k_cam_adam(float* cam, const float* d_cam, float* m, float* v, i
     pdl_launch_dependents();     // the next kernel of the stream may be scheduled; it waits for this one below
     pdl_wait();                  // (programmatic launch) everything read below is complete and visible
     const int i = threadIdx.x;
-    const int t = step[0] + 1;
-    __syncwarp();
-    if (i == 0) step[0] = t;
-    float p = 0.f;
-    if (i < 7) {
-        const float g = d_cam[i];
-        const float mi = m[i] + (g - m[i]) * (1.f - beta1);              // exp_avg.lerp_(grad, 1 - beta1)
-        const float vi = v[i] * beta2 + (1.f - beta2) * g * g;
-        m[i] = mi;
-        v[i] = vi;
-        const double bc1 = 1.0 - pow((double)beta1, (double)t), bc2 = 1.0 - pow((double)beta2, (double)t);
-        const float step_size = (float)((double)(i < 4 ? lr_q : lr_t) / bc1);
-        const float denom = sqrtf(vi) / (float)sqrt(bc2) + eps;
-        p = cam[i] - step_size * (mi / denom);
-        cam[i] = p;
-    }
-    if (best_loss && loss[0] < best_loss[0]) {                            // uniform over the warp
-        __syncwarp();
-        if (i < 7) best_cam[i] = p;
-        if (i == 0) best_loss[0] = loss[0];
-    }
+    cam_adam_warp(i, i < 7 ? d_cam[i] : 0.f, cam, m, v, step, lr_q, lr_t, beta1, beta2, eps, loss, best_loss, best_cam);
 }
 
 extern "C" int nsb_cam_adam(float* cam, const float* d_cam, float* m, float* v, int32_t* step, float lr_q, float lr_t,

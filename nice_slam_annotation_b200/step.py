@@ -602,12 +602,14 @@ class TrackingStep:
                                 _ptr(st.rays_o), _ptr(st.rays_d), _ptr(st.gt_depth), _ptr(st.gt_color),
                                 _ptr(st.keep), s), "sample_rays")
         st._launch()
-        check(L.nsb_pose_grad(_ptr(st.g_rays_o), _ptr(st.g_rays_d), _ptr(self.indices), _ptr(st.keep), self.N, H0, W0, W1 - W0,
-                              fx, fy, cx, cy, _ptr(self.cam), _ptr(self.d_cam), s), "pose_grad")
-        if self.adam:
-            check(L.nsb_cam_adam(_ptr(self.cam), _ptr(self.d_cam), _ptr(self.m), _ptr(self.v), _ptr(self.count),
-                                 self.lr_q, self.lr_t, self.betas[0], self.betas[1], self.eps, _ptr(st.loss),
-                                 _ptr(self.best_loss), _ptr(self.best_cam), s), "cam_adam")
+        if self.adam:       # pose gradient + Adam on the camera tensor + best-candidate rule: one launch
+            check(L.nsb_pose_grad_adam(_ptr(st.g_rays_o), _ptr(st.g_rays_d), _ptr(self.indices), _ptr(st.keep), self.N, H0, W0,
+                                       W1 - W0, fx, fy, cx, cy, _ptr(self.cam), _ptr(self.d_cam), _ptr(self.m), _ptr(self.v),
+                                       _ptr(self.count), self.lr_q, self.lr_t, self.betas[0], self.betas[1], self.eps,
+                                       _ptr(st.loss), _ptr(self.best_loss), _ptr(self.best_cam), s), "pose_grad_adam")
+        else:
+            check(L.nsb_pose_grad(_ptr(st.g_rays_o), _ptr(st.g_rays_d), _ptr(self.indices), _ptr(st.keep), self.N, H0, W0,
+                                  W1 - W0, fx, fy, cx, cy, _ptr(self.cam), _ptr(self.d_cam), s), "pose_grad")
 
     def capture(self):
         g = torch.cuda.CUDAGraph()
