@@ -573,10 +573,14 @@ int nsb_imap_backward(const NsbPoints* pts, const NsbImapDecoder* dec, const flo
  * C[m, n] = epi(sum_k A(m, k) B(n, k)), m < M, n < N_valid <= 256.  a_rc / b_rc = 0: element (r, k)
  * at p[r * ld + k]; 1: at p[k * ld + r].  epi: 0 store, 1 +bias & ReLU, 2 +bias, 3 zero where
  * mask[m, n] <= 0, 4 atomic accumulate (required for n_split > 1).  colsum (optional, a_rc = 1):
- * colsum[m] += sum_k A(m, k). */
+ * colsum[m] += sum_k A(m, k).  b_scratch (optional, nsb_gemm3x_pack_floats(N_valid, K) floats, 16-byte
+ * aligned): B is split once into its operand images there and fetched by bulk copies -- the route the
+ * iMAP* chains take for their weight matrices. */
+int64_t nsb_gemm3x_pack_floats(int N_valid, int64_t K);
 int nsb_gemm3x(const float* A, int64_t lda, int a_rc, const float* B, int64_t ldb, int b_rc, float* C,
                int64_t ldc, int64_t M, int N_valid, int64_t K, int epi, const float* bias,
-               const float* mask, int64_t ldmask, float* colsum, int n_split, void* stream);
+               const float* mask, int64_t ldmask, float* colsum, int n_split, float* b_scratch,
+               void* stream);
 
 #ifdef __cplusplus
 }

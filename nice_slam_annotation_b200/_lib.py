@@ -158,7 +158,8 @@ _SIGS = {
     "nsb_imap_backward": (C.c_int, [C.POINTER(NsbPoints), C.POINTER(NsbImapDecoder), c_ptr, c_ptr, C.c_uint,
                                     C.POINTER(NsbImapGrads), c_ptr, c_ptr, c_ptr]),
     "nsb_gemm3x": (C.c_int, [c_ptr, C.c_int64, C.c_int, c_ptr, C.c_int64, C.c_int, c_ptr, C.c_int64, C.c_int64,
-                             C.c_int, C.c_int64, C.c_int, c_ptr, c_ptr, C.c_int64, c_ptr, C.c_int, c_ptr]),
+                             C.c_int, C.c_int64, C.c_int, c_ptr, c_ptr, C.c_int64, c_ptr, C.c_int, c_ptr, c_ptr]),
+    "nsb_gemm3x_pack_floats": (C.c_int64, [C.c_int, C.c_int64]),
     "nsb_pose_grad_adam": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_int, C.c_int, C.c_int,
                                      C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                                      C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, c_ptr, c_ptr, c_ptr]),

@@ -77,18 +77,9 @@ __device__ __forceinline__ uint64_t dwt_desc(uint32_t saddr) {        // MN-majo
 }
 __host__ __device__ constexpr uint32_t dwt_idesc(int N) { return tc::idesc_tf32(128, N) | (1u << 15) | (1u << 16); }
 
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(tc::smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(tc::smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
-                     tc::smem_u32(smem_dst)),
-                 "l"(gmem_src), "r"(bytes), "r"(tc::smem_u32(bar))
-                 : "memory");
-}
+using tc::bulk_g2s;
+using tc::mbar_arrive;
+using tc::mbar_expect_tx;
 
 template <int KIND>
 __device__ void dweight_tc_body(const DwParams& P, const DwTcOffs& O, float* sm, int debug) {

@@ -1,9 +1,10 @@
 // k_gemm3x: chained / batched 3xTF32 GEMM on tcgen05 (see nsb_gemm.cuh for the contract).
 //
-// CTA = 13 warps: warps 0-3 epilogue (TMEM lane quadrant = warp), warp 4 MMA issue (one thread),
-// warps 5-12 producers.  Shared memory: 4 stages x { A hi, A lo (128 x 16), B hi, B lo (256 x 16) }
-// = 4 x 48 KB of K-major core-matrix images.  Tensor memory: two 256-column accumulators, so the
-// epilogue of one item overlaps the MMAs of the next.
+// CTA = 17 warps: warps 0-7 epilogue (TMEM lane quadrant = warp & 3, two warps share a quadrant and take
+// alternate 16-column groups), warp 8 MMA issue (one thread), warps 9-16 producers (a packed B image is
+// fetched by one bulk asynchronous copy issued by the first thread of the stage's producer group).  Shared memory: 4 stages x { A hi, A lo
+// (128 x 16), B hi, B lo (256 x 16) } = 4 x 48 KB of operand images.  Tensor memory: two 256-column
+// accumulators, so the epilogue of one item overlaps the MMAs of the next.
 #include "nsb_gemm.cuh"
 
 #include "nsb_common.cuh"
@@ -17,9 +18,16 @@ constexpr int G_KC = 16;                                          // k per stage
 constexpr int G_A_FLOATS = 128 * G_KC;                            // one image (hi or lo) of A
 constexpr int G_B_FLOATS = 256 * G_KC;
 constexpr int G_STAGE_FLOATS = 2 * G_A_FLOATS + 2 * G_B_FLOATS;   // 48 KB
-constexpr int G_EPI_WARPS = 4, G_PROD_WARPS = 8;
-constexpr int G_THREADS = (G_EPI_WARPS + 1 + G_PROD_WARPS) * 32;  // 416
+constexpr int G_EPI_WARPS = 8, G_PROD_WARPS = 8;
+constexpr int G_MMA_WARP = G_EPI_WARPS, G_PROD_WARP0 = G_EPI_WARPS + 1;
+constexpr int G_THREADS = (G_EPI_WARPS + 1 + G_PROD_WARPS) * 32;  // 544
 constexpr int G_SMEM = G_STAGES * G_STAGE_FLOATS * 4 + 1024;
+
+// how the operands of a layer reach shared memory
+enum : int { G_MODE_KMAJOR = 0, G_MODE_MN = 1 };
+__host__ __device__ inline int layer_mode(const GemmLayer& L, bool packed) {
+    return (!packed && L.a_rc && L.b_rc && (L.N & 31) == 0) ? G_MODE_MN : G_MODE_KMAJOR;
+}
 
 struct Item {
     int layer;
@@ -77,9 +85,7 @@ struct ItemIter {
     }
 };
 
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(tc::smem_u32(bar)) : "memory");
-}
+using tc::mbar_arrive;
 // plain (coherent) global loads: in a chain the A operand was written by this CTA moments ago
 __device__ __forceinline__ float ld_f32(const float* p) {
     float v;
@@ -123,21 +129,68 @@ __device__ __forceinline__ void split_store(float* hi_img, float* lo_img, int id
 
 __device__ __forceinline__ bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// row-contiguous operand: four consecutive rows r .. r + 3 at reduction index k (zeros outside)
+__device__ __forceinline__ float4 load_rquad(const float* base, long long ld, bool vec_ok, long long r, long long rows_valid,
+                                             long long k, long long k_end) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r >= rows_valid || k >= k_end) return v;
+    const float* p = base + k * ld + r;
+    if (vec_ok && r + 3 < rows_valid) return ld_v4(p);
+    v.x = ld_f32(p);
+    if (r + 1 < rows_valid) v.y = ld_f32(p + 1);
+    if (r + 2 < rows_valid) v.z = ld_f32(p + 2);
+    if (r + 3 < rows_valid) v.w = ld_f32(p + 3);
+    return v;
+}
+
+// B operand images of every layer, chunk by chunk: [chunk][hi N x 16 | lo N x 16], K-major core matrices,
+// zero outside N_valid x K -- what the GEMM's bulk copies land in a stage as is
+__global__ void __launch_bounds__(256) k_gemm_pack_b(const __grid_constant__ GemmBatch gb) {
+    const GemmLayer& L = gb.L[blockIdx.y];
+    const int N = L.N, per = N * G_KC;
+    const long long chunks = (L.K + G_KC - 1) / G_KC;
+    for (long long c = blockIdx.x; c < chunks; c += gridDim.x) {
+        float* dst = L.b_packed + c * (2LL * per);
+        for (int e = threadIdx.x; e < per; e += blockDim.x) {
+            int n, kk;
+            if (L.b_rc) { kk = e / N; n = e - kk * N; } else { n = e >> 4; kk = e & 15; }
+            const long long k = c * G_KC + kk;
+            float v = 0.f;
+            if (n < L.N_valid && k < L.K) v = L.b_rc ? L.B[k * L.ldb + n] : L.B[(long long)n * L.ldb + k];
+            uint32_t hi, lo;
+            split_tf32(v, hi, lo);
+            const int idx = tc::kmajor_index(n, kk, N);
+            dst[idx] = __uint_as_float(hi);
+            dst[per + idx] = __uint_as_float(lo);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__ GemmBatch gb) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* stages = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) uint64_t bar_full[G_STAGES], bar_empty[G_STAGES], bar_acc_full[2], bar_acc_empty[2];
+    __shared__ __align__(8) uint64_t bar_epi_done[2];     // chain: the epilogue of an item has stored its rows
     __shared__ uint32_t tmem_slot;
-    __shared__ unsigned epi_count;       // epilogue threads that have finished an item (128 per item)
+    __shared__ __align__(16) float s_bias[GEMM_MAX_LAYERS][256];
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
-        epi_count = 0;
-        for (int s = 0; s < G_STAGES; ++s) { tc::mbar_init(&bar_full[s], 64); tc::mbar_init(&bar_empty[s], 1); }
-        for (int a = 0; a < 2; ++a) { tc::mbar_init(&bar_acc_full[a], 1); tc::mbar_init(&bar_acc_empty[a], G_EPI_WARPS * 32); }
+        // a stage is full when its two producer warps have arrived (+ the bulk copy's expect_tx arrival)
+        for (int s = 0; s < G_STAGES; ++s) { tc::mbar_init(&bar_full[s], 64 + (gb.packed ? 1 : 0)); tc::mbar_init(&bar_empty[s], 1); }
+        for (int a = 0; a < 2; ++a) {
+            tc::mbar_init(&bar_acc_full[a], 1);
+            tc::mbar_init(&bar_acc_empty[a], G_EPI_WARPS * 32);
+            tc::mbar_init(&bar_epi_done[a], G_EPI_WARPS * 32);
+        }
         tc::mbar_init_fence();
     }
-    if (warp == G_EPI_WARPS) tc::tmem_alloc<512>(&tmem_slot);
+    for (int i = tid; i < gb.n_layers * 256; i += G_THREADS) {
+        const GemmLayer& L = gb.L[i >> 8];
+        const int n = i & 255;
+        s_bias[i >> 8][n] = (L.bias && n < L.N_valid) ? __ldg(L.bias + n) : 0.f;
+    }
+    if (warp == G_MMA_WARP) tc::tmem_alloc<512>(&tmem_slot);
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
@@ -149,9 +202,11 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
 
     if (warp < G_EPI_WARPS) {
         // ------------------------------------------------ epilogue: TMEM -> registers -> global
-        const int row = 32 * warp + lane;
+        const int quad = warp & 3, half = warp >> 2;
+        const int row = 32 * quad + lane;
         for (int i = 0; iter.next(gb, it); ++i) {
             const GemmLayer& L = gb.L[it.layer];
+            const float* bias = s_bias[it.layer];
             const int acc = i & 1;
             tc::mbar_wait(&bar_acc_full[acc], (uint32_t)((i >> 1) & 1));
             tc::fence_after_sync();
@@ -162,12 +217,16 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
             const float* mrow = L.mask ? L.mask + m * L.ldmask : nullptr;
             const bool cvec = (L.ldc & 3) == 0 && aligned16(L.C);
             const bool mvec = mrow && (L.ldmask & 3) == 0 && aligned16(L.mask);
-            const uint32_t tacc = tc::tmem_addr(tbase, 32 * warp, acc * 256);
-            for (int n0 = 0; n0 < L.N; n0 += 16) {
+            const uint32_t tacc = tc::tmem_addr(tbase, 32 * quad, acc * 256);
+            if (16 * half >= L.N) {                         // no column group for this warp (N = 16)
+                tc::fence_before_sync();
+                mbar_arrive(&bar_acc_empty[acc]);
+            }
+            for (int n0 = 16 * half; n0 < L.N; n0 += 32) {
                 float v[16];
                 tc::tmem_ld16(tacc + n0, v);
                 tc::tmem_ld_wait();
-                if (n0 + 16 >= L.N) {                       // accumulator drained: hand it back to the MMA warp
+                if (n0 + 32 >= L.N) {                       // my share of the accumulator is drained: hand it back
                     tc::fence_before_sync();
                     mbar_arrive(&bar_acc_empty[acc]);
                 }
@@ -179,12 +238,12 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
                     float o[4] = {v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]};
                     const bool full4 = n + 3 < L.N_valid;
                     if (L.epi == GEMM_EPI_BIAS_RELU || L.epi == GEMM_EPI_BIAS) {
+                        const float4 b4 = *reinterpret_cast<const float4*>(bias + n);      // zeros beyond N_valid
+                        o[0] += b4.x; o[1] += b4.y; o[2] += b4.z; o[3] += b4.w;
+                        if (L.epi == GEMM_EPI_BIAS_RELU) {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (n + j < L.N_valid) {
-                                o[j] += __ldg(L.bias + n + j);
-                                if (L.epi == GEMM_EPI_BIAS_RELU) o[j] = fmaxf(o[j], 0.f);
-                            }
+                            for (int j = 0; j < 4; ++j) o[j] = fmaxf(o[j], 0.f);
+                        }
                     } else if (L.epi == GEMM_EPI_MASK) {
                         if (mvec && full4) {
                             const float4 mk = ld_v4(mrow + n);
@@ -209,10 +268,9 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
                     }
                 }
             }
-            __threadfence_block();                 // release: this item's C rows are visible to the producers
-            atomicAdd(&epi_count, 1u);
+            mbar_arrive(&bar_epi_done[acc]);       // release: this item's C rows are visible to the producers
         }
-    } else if (warp == G_EPI_WARPS) {
+    } else if (warp == G_MMA_WARP) {
         // ------------------------------------------------ MMA issue (one thread)
         if (lane == 0) {
             uint32_t itc = 0;
@@ -221,7 +279,8 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
                 const int acc = i & 1;
                 tc::mbar_wait(&bar_acc_empty[acc], (uint32_t)(((i >> 1) & 1) ^ 1));
                 tc::fence_after_sync();
-                const uint32_t idesc = tc::idesc_tf32(128, L.N);
+                const bool mn = layer_mode(L, gb.packed) == G_MODE_MN;
+                const uint32_t idesc = tc::idesc_tf32(128, L.N) | (mn ? (tc::IDESC_A_MN | tc::IDESC_B_MN) : 0u);
                 const uint32_t dacc = tbase + (uint32_t)(acc * 256);
                 const int ns = (int)((it.k1 - it.k0 + G_KC - 1) / G_KC);
                 bool accum = false;
@@ -231,13 +290,20 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
                     tc::fence_after_sync();
                     const uint32_t sa = tc::smem_u32(stages + (size_t)st * G_STAGE_FLOATS);
                     const uint32_t a_hi = sa, a_lo = sa + G_A_FLOATS * 4, b_hi = sa + 2 * G_A_FLOATS * 4,
-                                   b_lo = b_hi + G_B_FLOATS * 4;
+                                   b_lo = b_hi + (uint32_t)L.N * G_KC * 4;
                     const long long kb = it.k0 + (long long)s * G_KC;
 #pragma unroll
                     for (int k8 = 0; k8 < G_KC; k8 += 8) {
                         if (kb + k8 >= it.k1) break;
-                        const uint64_t dah = tc::kmajor_desc(a_hi, 128, k8), dal = tc::kmajor_desc(a_lo, 128, k8);
-                        const uint64_t dbh = tc::kmajor_desc(b_hi, L.N, k8), dbl = tc::kmajor_desc(b_lo, L.N, k8);
+                        uint64_t dah, dal, dbh, dbl;
+                        if (mn) {
+                            const uint32_t o = (uint32_t)k8 * 128u;       // 8 k further: 8 x 128 B inside every atom
+                            dah = tc::mnmajor_desc(a_hi + o); dal = tc::mnmajor_desc(a_lo + o);
+                            dbh = tc::mnmajor_desc(b_hi + o); dbl = tc::mnmajor_desc(b_lo + o);
+                        } else {
+                            dah = tc::kmajor_desc(a_hi, 128, k8); dal = tc::kmajor_desc(a_lo, 128, k8);
+                            dbh = tc::kmajor_desc(b_hi, L.N, k8); dbl = tc::kmajor_desc(b_lo, L.N, k8);
+                        }
                         tc::mma_ss(dacc, dal, dbh, idesc, accum);
                         tc::mma_ss(dacc, dah, dbl, idesc, true);
                         tc::mma_ss(dacc, dah, dbh, idesc, true);
@@ -253,30 +319,75 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
         // ------------------------------------------------ producers: global fp32 -> tf32 hi/lo images
         // Group g (two warps) owns shared-memory stage g: it stages every 4th K chunk, so four chunks
         // are in flight and a group has four MMA-stage times to cover its L2 round trips.
-        const int pw = warp - G_EPI_WARPS - 1;      // 0..7
+        const int pw = warp - G_PROD_WARP0;         // 0..7
         const int grp = pw >> 1, w2 = pw & 1;
         uint32_t itc_base = 0;                      // K chunks of all previous items
         for (int i = 0; iter.next(gb, it); ++i) {
             const GemmLayer& L = gb.L[it.layer];
-            if (i - it.dep >= 0) {                  // the rows this item reads were written by item i - dep
-                const unsigned target = (unsigned)(G_EPI_WARPS * 32) * (unsigned)(i - it.dep + 1);
-                while (*reinterpret_cast<volatile unsigned*>(&epi_count) < target) {}
-                __threadfence_block();
+            const int ns = (int)((it.k1 - it.k0 + G_KC - 1) / G_KC);
+            const int s0 = (grp - (int)(itc_base & 3) + 4) & 3;       // this group's first chunk of the item
+            if (gb.chain && it.layer > 0 && s0 < ns) {
+                // the rows this item reads were written by the epilogue of item i - dep (same CTA)
+                const int j = i - it.dep;
+                tc::mbar_wait(&bar_epi_done[j & 1], (uint32_t)((j >> 1) & 1));
             }
             const long long Mv = gb.chain ? gb.M : L.M;
             const bool avec = (L.lda & 3) == 0 && aligned16(L.A), bvec = (L.ldb & 3) == 0 && aligned16(L.B);
             const int N = L.N, n8 = N >> 3, n_rb = (N + 31) >> 5;
-            const int ns = (int)((it.k1 - it.k0 + G_KC - 1) / G_KC);
-            float csum[2] = {0.f, 0.f};
             float* a_hi = stages + (size_t)grp * G_STAGE_FLOATS;
             float* a_lo = a_hi + G_A_FLOATS;
             float* b_hi = a_lo + G_A_FLOATS;
-            float* b_lo = b_hi + G_B_FLOATS;
-            for (int s = (grp - (int)(itc_base & 3) + 4) & 3; s < ns; s += G_STAGES) {
+            float* b_lo = b_hi + N * G_KC;
+            if (layer_mode(L, gb.packed) == G_MODE_MN) {
+                // ---- both operands row-contiguous: MN-major images, one float4 along the rows per lane.
+                // Warp w2 of the group takes the k rows w2, w2 + 2, .. of the chunk, four at a time.
+                float csum[4] = {0.f, 0.f, 0.f, 0.f};
+                const long long am = it.m0 + 4 * lane;
+                const int a_idx = (lane >> 3) * 512 + ((lane & 7) >> 1) * 8 + (lane & 1) * 4;      // + k * 32, chunk ^ (k & 3)
+                const int nbq = (N + 127) >> 7;                         // float4 per lane and k row of B
+                for (int s = s0; s < ns; s += G_STAGES) {
+                    const uint32_t itc = itc_base + (uint32_t)s;
+                    const long long kb = it.k0 + (long long)s * G_KC;
+#pragma unroll
+                    for (int bt = 0; bt < 2; ++bt) {
+                        float4 va[4], vb[4][2];
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) {
+                            const int kk = w2 + 2 * (4 * bt + r);
+                            va[r] = load_rquad(L.A, L.lda, avec, am, Mv, kb + kk, it.k1);
+#pragma unroll
+                            for (int q = 0; q < 2; ++q)
+                                if (q < nbq) vb[r][q] = load_rquad(L.B, L.ldb, bvec, 128 * q + 4 * lane, 128 * q + 4 * lane < N ? L.N_valid : 0, kb + kk, it.k1);
+                        }
+                        if (bt == 0) tc::mbar_wait(&bar_empty[grp], ((itc / G_STAGES) & 1) ^ 1);
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) {
+                            const int kk = w2 + 2 * (4 * bt + r);
+                            const int idx = (a_idx ^ ((kk & 3) << 3)) + kk * 32;
+                            split_store(a_hi, a_lo, idx, va[r]);
+                            csum[0] += va[r].x; csum[1] += va[r].y; csum[2] += va[r].z; csum[3] += va[r].w;
+#pragma unroll
+                            for (int q = 0; q < 2; ++q)
+                                if (q < nbq && 128 * q + 4 * lane < N) split_store(b_hi, b_lo, idx + q * 2048, vb[r][q]);
+                        }
+                    }
+                    tc::fence_async_smem();
+                    mbar_arrive(&bar_full[grp]);
+                }
+                if (L.colsum && s0 < ns) {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c)
+                        if (am + c < Mv) atomicAdd(L.colsum + am + c, csum[c]);
+                }
+                itc_base += (uint32_t)ns;
+                continue;
+            }
+            float csum[2] = {0.f, 0.f};
+            for (int s = s0; s < ns; s += G_STAGES) {
                 const uint32_t itc = itc_base + (uint32_t)s;
                 const long long kb = it.k0 + (long long)s * G_KC;
-                float4 va[8], vb[8];
-                // A (8 quads per thread) and the first half of B in flight, then the second half of B
+                float4 va[8], vb[4];
+                // A (8 quads per thread) and the first quarter of B in flight, then the rest of B quarter by quarter
                 if (L.a_rc == 0) {
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
@@ -289,48 +400,61 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
                         csum[j & 1] += (va[j].x + va[j].y) + (va[j].z + va[j].w);
                     }
                 }
+                auto store_a = [&]() {
+                    if (L.a_rc == 0) {
 #pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    if (L.b_rc == 0) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int rg = w2 + 2 * (j + 8 * half);
-                            if (rg < n8) vb[j] = load_quad(L.B, L.ldb, 0, bvec, rg * 8 + (lane & 7), L.N_valid, kb + 4 * (lane >> 3), it.k1);
-                        }
+                        for (int j = 0; j < 8; ++j)
+                            split_store(a_hi, a_lo, ((lane >> 3) * 16 + (w2 + 2 * j)) * 32 + (lane & 7) * 4, va[j]);
                     } else {
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
-                            const int itx = w2 + 2 * (j + 8 * half);
-                            if (itx < 4 * n_rb) vb[j] = load_quad(L.B, L.ldb, 1, false, (itx % n_rb) * 32 + lane, L.N_valid, kb + 4 * (itx / n_rb), it.k1);
+                            const int itx = w2 + 2 * j, r = (itx & 3) * 32 + lane, kq = itx >> 2;
+                            split_store(a_hi, a_lo, (kq * 16 + (r >> 3)) * 32 + (r & 7) * 4, va[j]);
                         }
                     }
-                    if (half == 0) {
-                        tc::mbar_wait(&bar_empty[grp], ((itc / G_STAGES) & 1) ^ 1);
-                        if (L.a_rc == 0) {
+                };
+                if (gb.packed) {                    // B: one bulk copy of the chunk's pre-split images
+                    tc::mbar_wait(&bar_empty[grp], ((itc / G_STAGES) & 1) ^ 1);
+                    if (w2 == 0 && lane == 0) {
+                        const uint32_t bytes = (uint32_t)N * G_KC * 2 * 4;
+                        tc::mbar_expect_tx(&bar_full[grp], bytes);
+                        tc::bulk_g2s(b_hi, L.b_packed + (it.k0 / G_KC + s) * (2LL * N * G_KC), bytes, &bar_full[grp]);
+                    }
+                    store_a();
+                } else {
 #pragma unroll
-                            for (int j = 0; j < 8; ++j)
-                                split_store(a_hi, a_lo, ((lane >> 3) * 16 + (w2 + 2 * j)) * 32 + (lane & 7) * 4, va[j]);
+                    for (int part = 0; part < 4; ++part) {
+                        if (L.b_rc == 0) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const int rg = w2 + 2 * (j + 4 * part);
+                                if (rg < n8) vb[j] = load_quad(L.B, L.ldb, 0, bvec, rg * 8 + (lane & 7), L.N_valid, kb + 4 * (lane >> 3), it.k1);
+                            }
                         } else {
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                const int itx = w2 + 2 * j, r = (itx & 3) * 32 + lane, kq = itx >> 2;
-                                split_store(a_hi, a_lo, (kq * 16 + (r >> 3)) * 32 + (r & 7) * 4, va[j]);
+                            for (int j = 0; j < 4; ++j) {
+                                const int itx = w2 + 2 * (j + 4 * part);
+                                if (itx < 4 * n_rb) vb[j] = load_quad(L.B, L.ldb, 1, false, (itx % n_rb) * 32 + lane, L.N_valid, kb + 4 * (itx / n_rb), it.k1);
                             }
                         }
-                    }
-                    if (L.b_rc == 0) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int rg = w2 + 2 * (j + 8 * half);
-                            if (rg < n8) split_store(b_hi, b_lo, ((lane >> 3) * n8 + rg) * 32 + (lane & 7) * 4, vb[j]);
+                        if (part == 0) {
+                            tc::mbar_wait(&bar_empty[grp], ((itc / G_STAGES) & 1) ^ 1);
+                            store_a();
                         }
-                    } else {
+                        if (L.b_rc == 0) {
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int itx = w2 + 2 * (j + 8 * half);
-                            if (itx < 4 * n_rb) {
-                                const int r = (itx % n_rb) * 32 + lane, kq = itx / n_rb;
-                                if (r < N) split_store(b_hi, b_lo, (kq * n8 + (r >> 3)) * 32 + (r & 7) * 4, vb[j]);
+                            for (int j = 0; j < 4; ++j) {
+                                const int rg = w2 + 2 * (j + 4 * part);
+                                if (rg < n8) split_store(b_hi, b_lo, ((lane >> 3) * n8 + rg) * 32 + (lane & 7) * 4, vb[j]);
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const int itx = w2 + 2 * (j + 4 * part);
+                                if (itx < 4 * n_rb) {
+                                    const int r = (itx % n_rb) * 32 + lane, kq = itx / n_rb;
+                                    if (r < N) split_store(b_hi, b_lo, (kq * n8 + (r >> 3)) * 32 + (r & 7) * 4, vb[j]);
+                                }
                             }
                         }
                     }
@@ -350,7 +474,7 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
     }
     tc::fence_before_sync();
     __syncthreads();
-    if (warp == G_EPI_WARPS) tc::tmem_dealloc<512>(tbase);
+    if (warp == G_MMA_WARP) tc::tmem_dealloc<512>(tbase);
 }
 
 }  // namespace
@@ -395,6 +519,21 @@ int gemm3x_launch(GemmBatch& gb, cudaStream_t stream) {
         cudaError_t e = cudaFuncSetAttribute(k_gemm3x, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
         if (e != cudaSuccess) { g_gemm_sms = 0; return set_error((int)e, "cudaFuncSetAttribute(k_gemm3x): %s", cudaGetErrorString(e)); }
     }
+    int n_packed = 0;
+    long long max_chunks = 1;
+    for (int i = 0; i < gb.n_layers; ++i) {
+        const GemmLayer& L = gb.L[i];
+        if (!L.b_packed) continue;
+        if (reinterpret_cast<uintptr_t>(L.b_packed) & 15u) return set_error(NSB_EINVAL, "gemm layer %d: b_packed is not 16-byte aligned", i);
+        ++n_packed;
+        if ((L.K + G_KC - 1) / G_KC > max_chunks) max_chunks = (L.K + G_KC - 1) / G_KC;
+    }
+    if (n_packed && n_packed != gb.n_layers) return set_error(NSB_EINVAL, "gemm: b_packed on %d of %d layers", n_packed, gb.n_layers);
+    gb.packed = n_packed ? 1 : 0;
+    if (gb.packed) {
+        k_gemm_pack_b<<<dim3((unsigned)(max_chunks < 64 ? max_chunks : 64), (unsigned)gb.n_layers), 256, 0, stream>>>(gb);
+        if (int rc = check_launch("k_gemm_pack_b")) return rc;
+    }
     const int grid = (int)(items < g_gemm_sms ? items : g_gemm_sms);
     k_gemm3x<<<grid, G_THREADS, G_SMEM, stream>>>(gb);
     return check_launch("k_gemm3x");
@@ -405,15 +544,18 @@ int gemm3x_launch(GemmBatch& gb, cudaStream_t stream) {
 using namespace nsb;
 
 // test hook: one GEMM through the chained kernel (tests/test_gemm3x.py)
+extern "C" int64_t nsb_gemm3x_pack_floats(int N_valid, int64_t K) { return gemm3x_pack_floats((N_valid + 15) / 16 * 16, K); }
+
 extern "C" int nsb_gemm3x(const float* A, int64_t lda, int a_rc, const float* B, int64_t ldb, int b_rc, float* C,
                           int64_t ldc, int64_t M, int N_valid, int64_t K, int epi, const float* bias,
-                          const float* mask, int64_t ldmask, float* colsum, int n_split, void* stream) {
+                          const float* mask, int64_t ldmask, float* colsum, int n_split, float* b_scratch,
+                          void* stream) {
     GemmBatch gb{};
     gb.n_layers = 1;
     gb.chain = 0;
     GemmLayer& L = gb.L[0];
     L.A = A; L.lda = lda; L.a_rc = a_rc; L.B = B; L.ldb = ldb; L.b_rc = b_rc; L.C = C; L.ldc = ldc;
     L.M = M; L.N_valid = N_valid; L.N = (N_valid + 15) / 16 * 16; L.K = K; L.epi = epi; L.bias = bias;
-    L.mask = mask; L.ldmask = ldmask; L.colsum = colsum; L.n_split = n_split;
+    L.mask = mask; L.ldmask = ldmask; L.colsum = colsum; L.n_split = n_split; L.b_packed = b_scratch;
     return gemm3x_launch(gb, (cudaStream_t)stream);
 }

@@ -7,9 +7,15 @@
 // element (r, k) at p[r * ld + k]) or with the row index contiguous ("RC": p[k * ld + r]), so the
 // forward layers (X W^T), the input-gradient layers (G W) and the weight gradients (G^T X) all read
 // the live torch tensors without a packing pass.  Producer warps split every value into tf32 hi/lo
-// and write K-major core-matrix images to shared memory; one thread issues three MMAs per K step
-// (hi*hi + lo*hi + hi*lo, fp32 accumulate in tensor memory); four epilogue warps read the
+// and write operand images to shared memory; one thread issues three MMAs per K step
+// (hi*hi + lo*hi + hi*lo, fp32 accumulate in tensor memory); eight epilogue warps read the
 // accumulator back (tcgen05.ld) and apply bias / ReLU / ReLU-mask / atomic accumulation.
+// Two shortcuts keep the producers off the critical path:
+//  * a B operand that is a WEIGHT matrix (the same for every row tile) can be split once per launch into
+//    its per-chunk hi/lo images in global scratch (GemmLayer::b_packed, k_gemm_pack_b); the kernel then
+//    fetches a chunk with one bulk asynchronous copy (cp.async.bulk -> mbarrier) and no ALU work;
+//  * when BOTH operands are row-contiguous (the weight gradients G^T X: K = points) the images are
+//    MN-major (nsb_tc.cuh), so the producers move float4s along the rows instead of transposing scalars.
 //
 // A batch is either a CHAIN (all layers share the row dimension; a CTA carries a pair of 128-row
 // tiles through every layer, layer l+1 of a tile reading what layer l of the same CTA wrote, so the
@@ -41,6 +47,8 @@ struct GemmLayer {
     const float* mask;
     long long ldmask;
     float* colsum;      // optional (RC-addressed A only): colsum[m] += sum_k A(m, k)
+    float* b_packed;    // optional scratch of gemm3x_pack_floats(N, K) floats (16-byte aligned): B's operand images,
+                        // written by gemm3x_launch before the GEMM; all layers of a batch or none
     long long M;        // valid rows of A / C (independent mode; a chain uses GemmBatch::M)
     long long K;        // valid reduction length
     long long k_per_split;   // multiple of 16 (independent mode)
@@ -57,10 +65,14 @@ struct GemmBatch {
     int chain;
     long long M;        // chain: rows shared by all layers
     int m_tiles;        // chain: ceil(M / 128)
+    int packed;         // set by gemm3x_launch: every layer's B comes from its b_packed images
     GemmLayer L[GEMM_MAX_LAYERS];
 };
 
-// validates the batch, fills m_tiles, launches k_gemm3x on `stream`
+// floats of GemmLayer::b_packed for an operand of N (padded) rows and reduction length K
+inline long long gemm3x_pack_floats(int N, long long K) { return (K + 15) / 16 * (long long)N * 32; }
+
+// validates the batch, fills m_tiles, launches (k_gemm_pack_b and) k_gemm3x on `stream`
 int gemm3x_launch(GemmBatch& gb, cudaStream_t stream);
 
 }  // namespace nsb

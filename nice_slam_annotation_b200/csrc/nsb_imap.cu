@@ -100,6 +100,20 @@ __global__ void __launch_bounds__(384) k_imap_embed_bwd(PointsDev q, long long P
     }
 }
 
+// floats of the B operand images of one five-layer chain (k_gemm_pack_b): the forward chain (W0 .. W3, head) and
+// the input-gradient chain (Wo^T, W3^T .. W0^T) need the same amount
+long long pack_floats(int h) {
+    return gemm3x_pack_floats(h, IM_EMB) + 3 * gemm3x_pack_floats(h, h) + gemm3x_pack_floats(16, h) +
+           gemm3x_pack_floats(h, 4) + gemm3x_pack_floats(IM_EPAD, h);
+}
+// hands every layer of a chain its slice of `pack`
+void assign_pack(GemmBatch& gb, float* pack) {
+    for (int l = 0; l < gb.n_layers; ++l) {
+        gb.L[l].b_packed = pack;
+        pack += gemm3x_pack_floats(gb.L[l].N, gb.L[l].K);
+    }
+}
+
 int check_decoder(const NsbImapDecoder* d) {
     if (!d) return set_error(NSB_EINVAL, "imap: null decoder");
     if (d->hidden < 16 || d->hidden > 256 || (d->hidden & 15)) return set_error(NSB_EINVAL, "imap: hidden size %d (multiple of 16 up to 256)", d->hidden);
@@ -142,14 +156,14 @@ using namespace nsb;
 
 extern "C" int64_t nsb_imap_workspace_floats(int64_t P, int hidden, int save) {
     if (P < 1) P = 1;
-    if (save) return P * (IM_EPAD + 4LL * hidden);
+    if (save) return P * (IM_EPAD + 4LL * hidden) + pack_floats(hidden);
     const long long n = P < IM_CHUNK ? P : IM_CHUNK;
-    return n * (IM_EPAD + 2LL * hidden);
+    return n * (IM_EPAD + 2LL * hidden) + pack_floats(hidden);
 }
 
 extern "C" int64_t nsb_imap_backward_scratch_floats(int64_t P, int hidden) {
     if (P < 1) P = 1;
-    return P * (IM_EPAD + 4LL * hidden);
+    return P * (IM_EPAD + 4LL * hidden) + pack_floats(hidden);
 }
 
 extern "C" int nsb_imap_forward(const NsbPoints* pts, const NsbImapDecoder* dec, float* raw, float* workspace,
@@ -167,6 +181,7 @@ extern "C" int nsb_imap_forward(const NsbPoints* pts, const NsbImapDecoder* dec,
         for (int l = 0; l < 4; ++l) H[l] = workspace + q.P * IM_EPAD + (long long)l * q.P * h;
         if (int rc = embed_launch(q, 0, q.P, dec->B, E, s)) return rc;
         forward_chain(gb, *dec, q.P, E, H, raw);
+        assign_pack(gb, workspace + q.P * (IM_EPAD + 4LL * h));      // behind E and H[0..3] (all multiples of 16 floats)
         return gemm3x_launch(gb, s);
     }
     const long long ch = q.P < IM_CHUNK ? q.P : IM_CHUNK;
@@ -178,6 +193,7 @@ extern "C" int nsb_imap_forward(const NsbPoints* pts, const NsbImapDecoder* dec,
         const long long n = q.P - i0 < ch ? q.P - i0 : ch;
         if (int rc = embed_launch(q, i0, n, dec->B, E, s)) return rc;
         forward_chain(gb, *dec, n, E, H, raw + 4 * i0);
+        assign_pack(gb, bufB + ch * h);
         if (int rc = gemm3x_launch(gb, s)) return rc;
     }
     return 0;
@@ -232,6 +248,7 @@ extern "C" int nsb_imap_backward(const NsbPoints* pts, const NsbImapDecoder* dec
         L.C = dE; L.ldc = IM_EPAD; L.N = IM_EPAD; L.N_valid = IM_EMB;
         L.epi = GEMM_EPI_STORE;
     }
+    assign_pack(gb, scratch + P * (IM_EPAD + 4LL * h));
     if (int rc = gemm3x_launch(gb, s)) return rc;
 
     // ---- weight gradients: dW_l = g_l^T h_{l-1}, db_l = column sums of g_l

@@ -40,6 +40,16 @@ __device__ __forceinline__ uint64_t kmajor_desc(uint32_t saddr, int R, int k0) {
     return smem_desc(saddr + (uint32_t)(k0 >> 2) * lbo, lbo, 128u);
 }
 
+// MN-major operand (the M / N index is the contiguous one): the only layout tcgen05 takes for tf32 is
+// SWIZZLE_128B_BASE32B (measured, scripts/probe_mn_major.cu): per 32 rows an atom [K][32 rows] with 128 B per k
+// whose 32-byte chunks are XOR-ed with (k & 3); SBO = next 4 k = 512 B, LBO = next atom; one MMA (K = 8)
+// starts 1024 B after the previous one.  float index of element (r, k) of a 16-k chunk:
+__host__ __device__ __forceinline__ int mnmajor_index(int r, int k) {
+    return (r >> 5) * 512 + k * 32 + ((((r >> 3) & 3) ^ (k & 3)) << 3) + (r & 7);
+}
+__device__ __forceinline__ uint64_t mnmajor_desc(uint32_t saddr) { return smem_desc(saddr, 2048u, 512u) | (1ull << 61); }
+constexpr uint32_t IDESC_A_MN = 1u << 15, IDESC_B_MN = 1u << 16;
+
 // instruction descriptor (cute::UMMA::InstrDescriptor): tf32 x tf32 -> f32, K-major A and B
 __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
@@ -79,6 +89,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "DONE_%=:\n\t"
         "}\n" ::"r"(a), "r"(parity)
         : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(smem_u32(bar)) : "memory");
+}
+// one arrival + `bytes` expected from asynchronous copies that complete on `bar`
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// bulk asynchronous copy global -> shared (16-byte aligned, size a multiple of 16), completing on `bar`
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
 }
 // all MMAs issued so far by this thread -> one arrival on `bar` when they have completed
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {

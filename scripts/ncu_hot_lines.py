@@ -35,7 +35,7 @@ def main(path, kernel, top=40):
             pass
     tot = sum(x[0] for x in data) or 1
     print(f"# {kernel}: {tot} stall samples; top {top} source lines")
-    for s, f, ln, src, ie, st in sorted(data, reverse=True)[:top]:
+    for s, f, ln, src, ie, st in sorted(data, key=lambda x: x[:3], reverse=True)[:top]:
         top3 = ",".join(f"{k}:{v}" for k, v in sorted(st.items(), key=lambda kv: -kv[1])[:3])
         print(f"{100 * s / tot:5.1f}% {f}:{ln:<5d} inst={ie:<9d} [{top3}]  {src}")
 
