@@ -283,8 +283,10 @@ int nsb_pose_grad_adam(const float* g_rays_o, const float* g_rays_d, const int64
 int nsb_tc_selftest(const float* A, const float* W, float* D, int K, int N, int mode, void* stream);
 
 /* micro-benchmark: SM cycles for `count` tf32 MMAs (M 128, width N, K 8) issued back to back into
- * `nacc` accumulators in rotation; out2[0] = issue cycles, out2[1] = cycles until all completed. */
-int nsb_tc_mma_latency(long long* out2, int N, int count, int nacc, void* stream);
+ * `nacc` accumulators in rotation; out2[0] = issue cycles, out2[1] = cycles until all completed.
+ * mode 0: A in tensor memory, B K-major; 1: A and B K-major in shared memory; 2: both MN-major
+ * (N a multiple of 32); 3: A K-major, B MN-major; 4: A MN-major, B K-major. */
+int nsb_tc_mma_latency(long long* out2, int N, int count, int nacc, int mode, void* stream);
 
 /* ---- whole render call ---------------------------------------------------------------------
  * Renderer.render_batch_ray (src/utils/Renderer.py:95-262) without importance resampling, and

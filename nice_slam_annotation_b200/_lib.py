@@ -115,7 +115,7 @@ _SIGS = {
     "nsb_pose_grad": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_int, C.c_int, C.c_int,
                                 C.c_float, C.c_float, C.c_float, C.c_float, c_ptr, c_ptr, c_ptr]),
     "nsb_tc_selftest": (C.c_int, [c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, c_ptr]),
-    "nsb_tc_mma_latency": (C.c_int, [c_ptr, C.c_int, C.c_int, C.c_int, c_ptr]),
+    "nsb_tc_mma_latency": (C.c_int, [c_ptr, C.c_int, C.c_int, C.c_int, C.c_int, c_ptr]),
     "nsb_load_batch": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int64, C.c_int64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                                  c_ptr]),
     "nsb_load_batch_packed": (C.c_int, [c_ptr, c_ptr, C.c_int64, C.c_int64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),

@@ -1,11 +1,15 @@
 // k_gemm3x: chained / batched 3xTF32 GEMM on tcgen05 (see nsb_gemm.cuh for the contract).
 //
-// CTA = 17 warps: warps 0-7 epilogue (TMEM lane quadrant = warp & 3, two warps share a quadrant and take
-// alternate 16-column groups), warp 8 MMA issue (one thread), warps 9-16 producers (a packed B image is
-// fetched by one bulk asynchronous copy issued by the first thread of the stage's producer group).  Shared memory: 4 stages x { A hi, A lo
+// CTA (GemmCfg): epilogue warps (TMEM lane quadrant = warp & 3; with eight of them two share a quadrant and
+// take alternate 16-column groups), one MMA-issuing warp (one thread), in PACKED mode a warp that fetches the
+// packed B images with bulk asynchronous copies (one thread: it runs ahead of the chain dependency the
+// producers wait for, so the weights of the next item are in place when its rows become readable), and
+// eight producer warps.  Shared memory: 4 stages x { A hi, A lo
 // (128 x 16), B hi, B lo (256 x 16) } = 4 x 48 KB of operand images.  Tensor memory: two 256-column
 // accumulators, so the epilogue of one item overlaps the MMAs of the next.
 #include "nsb_gemm.cuh"
+
+#include <cstdlib>
 
 #include "nsb_common.cuh"
 #include "nsb_tc.cuh"
@@ -18,16 +22,25 @@ constexpr int G_KC = 16;                                          // k per stage
 constexpr int G_A_FLOATS = 128 * G_KC;                            // one image (hi or lo) of A
 constexpr int G_B_FLOATS = 256 * G_KC;
 constexpr int G_STAGE_FLOATS = 2 * G_A_FLOATS + 2 * G_B_FLOATS;   // 48 KB
-constexpr int G_EPI_WARPS = 8, G_PROD_WARPS = 8;
-constexpr int G_MMA_WARP = G_EPI_WARPS, G_PROD_WARP0 = G_EPI_WARPS + 1;
-constexpr int G_THREADS = (G_EPI_WARPS + 1 + G_PROD_WARPS) * 32;  // 544
+constexpr int G_PROD_WARPS = 8;
 constexpr int G_SMEM = G_STAGES * G_STAGE_FLOATS * 4 + 1024;
 
-// how the operands of a layer reach shared memory
-enum : int { G_MODE_KMAJOR = 0, G_MODE_MN = 1 };
-__host__ __device__ inline int layer_mode(const GemmLayer& L, bool packed) {
-    return (!packed && L.a_rc && L.b_rc && (L.N & 31) == 0) ? G_MODE_MN : G_MODE_KMAJOR;
-}
+// How the operands of a batch reach shared memory: one kernel instantiation each (all layers of a batch agree), so
+// that the register budget of one path is not set by the others.
+//   LEGACY  K-major images, both operands split by the producers through registers (any addressing)
+//   PACKED  K-major images, B's pre-split images fetched by bulk copies (a dedicated warp), A by the producers
+//   MN      both operands row-contiguous: MN-major images
+enum : int { G_MODE_LEGACY = 0, G_MODE_PACKED = 1, G_MODE_MN = 2 };
+template <int MODE>
+struct GemmCfg {
+    static constexpr int EPI_WARPS = MODE == G_MODE_MN ? 4 : 8;      // weight gradients: one epilogue per 64 chunks
+    static constexpr int MMA_WARP = EPI_WARPS;
+    static constexpr int BULK_WARP = MODE == G_MODE_PACKED ? EPI_WARPS + 1 : -1;
+    static constexpr int PROD_WARP0 = EPI_WARPS + (MODE == G_MODE_PACKED ? 2 : 1);
+    static constexpr int THREADS = (PROD_WARP0 + G_PROD_WARPS) * 32;
+    static constexpr int EPI_SPLIT = EPI_WARPS / 4;                  // warps sharing a TMEM lane quadrant
+};
+inline bool layer_mn_capable(const GemmLayer& L) { return L.a_rc && L.b_rc && (L.N & 31) == 0; }
 
 struct Item {
     int layer;
@@ -143,6 +156,23 @@ __device__ __forceinline__ float4 load_rquad(const float* base, long long ld, bo
     return v;
 }
 
+// 16-byte asynchronous copy global -> shared (LDGSTS), the last 16 - src_bytes bytes zero-filled
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gmem_src, int src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(tc::smem_u32(smem_dst)), "l"(gmem_src), "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
+}
+// lo image of four values already in the hi image (raw fp32 there: the tensor core truncates hi itself)
+__device__ __forceinline__ float4 lo_pass(const float* hi_img, float* lo_img, int idx) {
+    const float4 v = *reinterpret_cast<const float4*>(hi_img + idx);
+    uint32_t h, l0, l1, l2, l3;
+    split_tf32(v.x, h, l0); split_tf32(v.y, h, l1); split_tf32(v.z, h, l2); split_tf32(v.w, h, l3);
+    *reinterpret_cast<uint4*>(lo_img + idx) = make_uint4(l0, l1, l2, l3);
+    return v;
+}
+
 // B operand images of every layer, chunk by chunk: [chunk][hi N x 16 | lo N x 16], K-major core matrices,
 // zero outside N_valid x K -- what the GEMM's bulk copies land in a stage as is
 __global__ void __launch_bounds__(256) k_gemm_pack_b(const __grid_constant__ GemmBatch gb) {
@@ -166,7 +196,12 @@ __global__ void __launch_bounds__(256) k_gemm_pack_b(const __grid_constant__ Gem
     }
 }
 
-__global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__ GemmBatch gb) {
+template <int MODE>
+__global__ void __launch_bounds__(GemmCfg<MODE>::THREADS, 1) k_gemm3x(const __grid_constant__ GemmBatch gb) {
+    using Cfg = GemmCfg<MODE>;
+    constexpr int G_EPI_WARPS = Cfg::EPI_WARPS, G_MMA_WARP = Cfg::MMA_WARP, G_BULK_WARP = Cfg::BULK_WARP,
+                  G_PROD_WARP0 = Cfg::PROD_WARP0, G_THREADS = Cfg::THREADS, EPI_SPLIT = Cfg::EPI_SPLIT;
+    constexpr bool PACKED = MODE == G_MODE_PACKED, MN = MODE == G_MODE_MN;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* stages = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) uint64_t bar_full[G_STAGES], bar_empty[G_STAGES], bar_acc_full[2], bar_acc_empty[2];
@@ -177,7 +212,7 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         // a stage is full when its two producer warps have arrived (+ the bulk copy's expect_tx arrival)
-        for (int s = 0; s < G_STAGES; ++s) { tc::mbar_init(&bar_full[s], 64 + (gb.packed ? 1 : 0)); tc::mbar_init(&bar_empty[s], 1); }
+        for (int s = 0; s < G_STAGES; ++s) { tc::mbar_init(&bar_full[s], 64 + ((PACKED && !(gb.debug & 8)) ? 1 : 0)); tc::mbar_init(&bar_empty[s], 1); }
         for (int a = 0; a < 2; ++a) {
             tc::mbar_init(&bar_acc_full[a], 1);
             tc::mbar_init(&bar_acc_empty[a], G_EPI_WARPS * 32);
@@ -202,14 +237,12 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
 
     if (warp < G_EPI_WARPS) {
         // ------------------------------------------------ epilogue: TMEM -> registers -> global
-        const int quad = warp & 3, half = warp >> 2;
+        const int quad = warp & 3, half = warp >> 2;       // half < EPI_SPLIT
         const int row = 32 * quad + lane;
         for (int i = 0; iter.next(gb, it); ++i) {
             const GemmLayer& L = gb.L[it.layer];
             const float* bias = s_bias[it.layer];
             const int acc = i & 1;
-            tc::mbar_wait(&bar_acc_full[acc], (uint32_t)((i >> 1) & 1));
-            tc::fence_after_sync();
             const long long m = it.m0 + row;
             const long long Mv = gb.chain ? gb.M : L.M;
             const bool valid = m < Mv;
@@ -217,24 +250,41 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
             const float* mrow = L.mask ? L.mask + m * L.ldmask : nullptr;
             const bool cvec = (L.ldc & 3) == 0 && aligned16(L.C);
             const bool mvec = mrow && (L.ldmask & 3) == 0 && aligned16(L.mask);
+            // ReLU-adjoint mask of a 16-column group (the saved activations): fetched one group ahead of the
+            // accumulator, the first one before the MMAs of the item have even finished
+            const bool mpre = L.epi == GEMM_EPI_MASK && mvec && valid;
+            float4 mk[4], mkn[4];
+            auto load_mask = [&](int n0, float4 (&mm)[4]) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int n = n0 + 4 * q;
+                    mm[q] = (mpre && n0 < L.N && n + 3 < L.N_valid) ? ld_v4(mrow + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            };
+            load_mask(16 * half, mk);
+            tc::mbar_wait(&bar_acc_full[acc], (uint32_t)((i >> 1) & 1));
+            tc::fence_after_sync();
             const uint32_t tacc = tc::tmem_addr(tbase, 32 * quad, acc * 256);
             if (16 * half >= L.N) {                         // no column group for this warp (N = 16)
                 tc::fence_before_sync();
                 mbar_arrive(&bar_acc_empty[acc]);
             }
-            for (int n0 = 16 * half; n0 < L.N; n0 += 32) {
+            for (int n0 = 16 * half; n0 < L.N; n0 += 16 * EPI_SPLIT) {
                 float v[16];
+                load_mask(n0 + 16 * EPI_SPLIT, mkn);
                 tc::tmem_ld16(tacc + n0, v);
                 tc::tmem_ld_wait();
-                if (n0 + 32 >= L.N) {                       // my share of the accumulator is drained: hand it back
+                if (n0 + 16 * EPI_SPLIT >= L.N) {           // my share of the accumulator is drained: hand it back
                     tc::fence_before_sync();
                     mbar_arrive(&bar_acc_empty[acc]);
                 }
-                if (!valid) continue;
+                if (!valid || (gb.debug & 1)) continue;      // (debug 1: timing experiment without the epilogue's global traffic)
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int n = n0 + 4 * q;
-                    if (n >= L.N_valid) break;
+                    const float4 mk_q = mk[q];
+                    mk[q] = mkn[q];
+                    if (n >= L.N_valid) continue;
                     float o[4] = {v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]};
                     const bool full4 = n + 3 < L.N_valid;
                     if (L.epi == GEMM_EPI_BIAS_RELU || L.epi == GEMM_EPI_BIAS) {
@@ -246,9 +296,8 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
                         }
                     } else if (L.epi == GEMM_EPI_MASK) {
                         if (mvec && full4) {
-                            const float4 mk = ld_v4(mrow + n);
-                            o[0] = mk.x > 0.f ? o[0] : 0.f; o[1] = mk.y > 0.f ? o[1] : 0.f;
-                            o[2] = mk.z > 0.f ? o[2] : 0.f; o[3] = mk.w > 0.f ? o[3] : 0.f;
+                            o[0] = mk_q.x > 0.f ? o[0] : 0.f; o[1] = mk_q.y > 0.f ? o[1] : 0.f;
+                            o[2] = mk_q.z > 0.f ? o[2] : 0.f; o[3] = mk_q.w > 0.f ? o[3] : 0.f;
                         } else {
 #pragma unroll
                             for (int j = 0; j < 4; ++j)
@@ -279,39 +328,57 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
                 const int acc = i & 1;
                 tc::mbar_wait(&bar_acc_empty[acc], (uint32_t)(((i >> 1) & 1) ^ 1));
                 tc::fence_after_sync();
-                const bool mn = layer_mode(L, gb.packed) == G_MODE_MN;
+                constexpr bool mn = MN;
                 const uint32_t idesc = tc::idesc_tf32(128, L.N) | (mn ? (tc::IDESC_A_MN | tc::IDESC_B_MN) : 0u);
                 const uint32_t dacc = tbase + (uint32_t)(acc * 256);
                 const int ns = (int)((it.k1 - it.k0 + G_KC - 1) / G_KC);
+                // operand descriptors of stage 0 at k = 0; the address field counts 16-byte units, so a stage, the lo
+                // image and the second K step are plain additions (one thread issues everything: keep its loop short)
+                const uint32_t s0a = tc::smem_u32(stages);
+                const uint64_t dA = mn ? tc::mnmajor_desc(s0a) : tc::kmajor_desc(s0a, 128, 0);
+                const uint64_t dB = mn ? tc::mnmajor_desc(s0a + 2 * G_A_FLOATS * 4) : tc::kmajor_desc(s0a + 2 * G_A_FLOATS * 4, L.N, 0);
+                const uint64_t a_lo_off = (G_A_FLOATS * 4) >> 4, b_lo_off = (uint64_t)(L.N * G_KC * 4) >> 4;
+                const uint64_t a_k8 = mn ? (1024 >> 4) : (2 * 16 * 128) >> 4;              // 8 k further
+                const uint64_t b_k8 = mn ? (1024 >> 4) : (uint64_t)(2 * (L.N >> 3) * 128) >> 4;
+                const int k_last = (int)(it.k1 - it.k0 - (long long)(ns - 1) * G_KC);     // valid k of the last chunk
                 bool accum = false;
                 for (int s = 0; s < ns; ++s, ++itc) {
                     const int st = itc % G_STAGES;
                     tc::mbar_wait(&bar_full[st], (itc / G_STAGES) & 1);
                     tc::fence_after_sync();
-                    const uint32_t sa = tc::smem_u32(stages + (size_t)st * G_STAGE_FLOATS);
-                    const uint32_t a_hi = sa, a_lo = sa + G_A_FLOATS * 4, b_hi = sa + 2 * G_A_FLOATS * 4,
-                                   b_lo = b_hi + (uint32_t)L.N * G_KC * 4;
-                    const long long kb = it.k0 + (long long)s * G_KC;
-#pragma unroll
-                    for (int k8 = 0; k8 < G_KC; k8 += 8) {
-                        if (kb + k8 >= it.k1) break;
-                        uint64_t dah, dal, dbh, dbl;
-                        if (mn) {
-                            const uint32_t o = (uint32_t)k8 * 128u;       // 8 k further: 8 x 128 B inside every atom
-                            dah = tc::mnmajor_desc(a_hi + o); dal = tc::mnmajor_desc(a_lo + o);
-                            dbh = tc::mnmajor_desc(b_hi + o); dbl = tc::mnmajor_desc(b_lo + o);
-                        } else {
-                            dah = tc::kmajor_desc(a_hi, 128, k8); dal = tc::kmajor_desc(a_lo, 128, k8);
-                            dbh = tc::kmajor_desc(b_hi, L.N, k8); dbl = tc::kmajor_desc(b_lo, L.N, k8);
-                        }
-                        tc::mma_ss(dacc, dal, dbh, idesc, accum);
-                        tc::mma_ss(dacc, dah, dbl, idesc, true);
-                        tc::mma_ss(dacc, dah, dbh, idesc, true);
-                        accum = true;
+                    const uint64_t so = (uint64_t)st * ((G_STAGE_FLOATS * 4) >> 4);
+                    const uint64_t ah = dA + so, bh = dB + so, al = ah + a_lo_off, bl = bh + b_lo_off;
+                    tc::mma_ss(dacc, al, bh, idesc, accum);
+                    tc::mma_ss(dacc, ah, bl, idesc, true);
+                    tc::mma_ss(dacc, ah, bh, idesc, true);
+                    accum = true;
+                    if (s + 1 < ns || k_last > 8) {
+                        tc::mma_ss(dacc, al + a_k8, bh + b_k8, idesc, true);
+                        tc::mma_ss(dacc, ah + a_k8, bl + b_k8, idesc, true);
+                        tc::mma_ss(dacc, ah + a_k8, bh + b_k8, idesc, true);
                     }
                     tc::mma_commit(&bar_empty[st]);        // stage reusable once these MMAs have read it
                 }
                 tc::mma_commit(&bar_acc_full[acc]);
+            }
+        }
+        __syncwarp();
+    } else if (PACKED && warp == G_BULK_WARP) {
+        // ------------------------------------------------ packed B images: one bulk copy per stage (one thread)
+        if (lane == 0 && !(gb.debug & 8)) {
+            uint32_t itc = 0;
+            for (int i = 0; iter.next(gb, it); ++i) {
+                const GemmLayer& L = gb.L[it.layer];
+                const uint32_t bytes = (uint32_t)L.N * G_KC * 2 * 4;
+                const int ns = (int)((it.k1 - it.k0 + G_KC - 1) / G_KC);
+                const float* src = L.b_packed + (it.k0 / G_KC) * (2LL * L.N * G_KC);
+                float* dst = stages + 2 * G_A_FLOATS;
+                for (int s = 0; s < ns; ++s, ++itc) {
+                    const int st = itc % G_STAGES;
+                    tc::mbar_wait(&bar_empty[st], ((itc / G_STAGES) & 1) ^ 1);
+                    tc::mbar_expect_tx(&bar_full[st], bytes);
+                    tc::bulk_g2s(dst + (size_t)st * G_STAGE_FLOATS, src + (long long)s * (2LL * L.N * G_KC), bytes, &bar_full[st]);
+                }
             }
         }
         __syncwarp();
@@ -338,7 +405,7 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
             float* a_lo = a_hi + G_A_FLOATS;
             float* b_hi = a_lo + G_A_FLOATS;
             float* b_lo = b_hi + N * G_KC;
-            if (layer_mode(L, gb.packed) == G_MODE_MN) {
+            if constexpr (MN) {
                 // ---- both operands row-contiguous: MN-major images, one float4 along the rows per lane.
                 // Warp w2 of the group takes the k rows w2, w2 + 2, .. of the chunk, four at a time.
                 float csum[4] = {0.f, 0.f, 0.f, 0.f};
@@ -348,6 +415,43 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
                 for (int s = s0; s < ns; s += G_STAGES) {
                     const uint32_t itc = itc_base + (uint32_t)s;
                     const long long kb = it.k0 + (long long)s * G_KC;
+                    if (avec && bvec) {
+                        // 16-byte asynchronous copies straight into the hi images (raw fp32: the tensor core truncates),
+                        // all 24 of this thread in flight at once; then the lo images from shared memory
+                        tc::mbar_wait(&bar_empty[grp], ((itc / G_STAGES) & 1) ^ 1);
+                        const long long a_left = Mv - am;
+                        const int a_bytes = a_left >= 4 ? 16 : (a_left > 0 ? 4 * (int)a_left : 0);
+#pragma unroll
+                        for (int r = 0; r < 8; ++r) {
+                            const int kk = w2 + 2 * r;
+                            const int idx = (a_idx ^ ((kk & 3) << 3)) + kk * 32;
+                            const bool kv = kb + kk < it.k1;
+                            cp_async16(a_hi + idx, (kv && a_bytes) ? L.A + (kb + kk) * L.lda + am : L.A, kv ? a_bytes : 0);
+#pragma unroll
+                            for (int q = 0; q < 2; ++q) {
+                                const int n = 128 * q + 4 * lane;
+                                if (q < nbq && n < N) {
+                                    const int left = L.N_valid - n;
+                                    const int b_bytes = left >= 4 ? 16 : (left > 0 ? 4 * left : 0);
+                                    cp_async16(b_hi + idx + q * 2048, (kv && b_bytes) ? L.B + (kb + kk) * L.ldb + n : L.B, kv ? b_bytes : 0);
+                                }
+                            }
+                        }
+                        cp_async_wait_all();
+#pragma unroll
+                        for (int r = 0; r < 8; ++r) {
+                            const int kk = w2 + 2 * r;
+                            const int idx = (a_idx ^ ((kk & 3) << 3)) + kk * 32;
+                            const float4 v = lo_pass(a_hi, a_lo, idx);
+                            csum[0] += v.x; csum[1] += v.y; csum[2] += v.z; csum[3] += v.w;
+#pragma unroll
+                            for (int q = 0; q < 2; ++q)
+                                if (q < nbq && 128 * q + 4 * lane < N) lo_pass(b_hi, b_lo, idx + q * 2048);
+                        }
+                        tc::fence_async_smem();
+                        mbar_arrive(&bar_full[grp]);
+                        continue;
+                    }
 #pragma unroll
                     for (int bt = 0; bt < 2; ++bt) {
                         float4 va[4], vb[4][2];
@@ -380,15 +484,15 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
                         if (am + c < Mv) atomicAdd(L.colsum + am + c, csum[c]);
                 }
                 itc_base += (uint32_t)ns;
-                continue;
-            }
+            } else {
             float csum[2] = {0.f, 0.f};
             for (int s = s0; s < ns; s += G_STAGES) {
                 const uint32_t itc = itc_base + (uint32_t)s;
                 const long long kb = it.k0 + (long long)s * G_KC;
                 float4 va[8], vb[4];
                 // A (8 quads per thread) and the first quarter of B in flight, then the rest of B quarter by quarter
-                if (L.a_rc == 0) {
+                if (gb.debug & 2) {                 // timing experiment: no A production
+                } else if (L.a_rc == 0) {
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
                         va[j] = load_quad(L.A, L.lda, 0, avec, it.m0 + (w2 + 2 * j) * 8 + (lane & 7), Mv, kb + 4 * (lane >> 3), it.k1);
@@ -413,14 +517,9 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
                         }
                     }
                 };
-                if (gb.packed) {                    // B: one bulk copy of the chunk's pre-split images
+                if constexpr (PACKED) {             // B arrives by bulk copy (warp G_BULK_WARP)
                     tc::mbar_wait(&bar_empty[grp], ((itc / G_STAGES) & 1) ^ 1);
-                    if (w2 == 0 && lane == 0) {
-                        const uint32_t bytes = (uint32_t)N * G_KC * 2 * 4;
-                        tc::mbar_expect_tx(&bar_full[grp], bytes);
-                        tc::bulk_g2s(b_hi, L.b_packed + (it.k0 / G_KC + s) * (2LL * N * G_KC), bytes, &bar_full[grp]);
-                    }
-                    store_a();
+                    if (!(gb.debug & 2)) store_a();
                 } else {
 #pragma unroll
                     for (int part = 0; part < 4; ++part) {
@@ -470,6 +569,7 @@ __global__ void __launch_bounds__(G_THREADS, 1) k_gemm3x(const __grid_constant__
                     if (r < Mv) atomicAdd(L.colsum + r, csum[q]);
                 }
             }
+            }       // K-major modes
         }
     }
     tc::fence_before_sync();
@@ -516,7 +616,9 @@ int gemm3x_launch(GemmBatch& gb, cudaStream_t stream) {
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&g_gemm_sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaError_t e = cudaFuncSetAttribute(k_gemm3x, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
+        cudaError_t e = cudaFuncSetAttribute(k_gemm3x<G_MODE_LEGACY>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm3x<G_MODE_PACKED>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm3x<G_MODE_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
         if (e != cudaSuccess) { g_gemm_sms = 0; return set_error((int)e, "cudaFuncSetAttribute(k_gemm3x): %s", cudaGetErrorString(e)); }
     }
     int n_packed = 0;
@@ -530,12 +632,18 @@ int gemm3x_launch(GemmBatch& gb, cudaStream_t stream) {
     }
     if (n_packed && n_packed != gb.n_layers) return set_error(NSB_EINVAL, "gemm: b_packed on %d of %d layers", n_packed, gb.n_layers);
     gb.packed = n_packed ? 1 : 0;
+    static const int dbg = [] { const char* e = getenv("NSB_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
+    gb.debug = dbg;
     if (gb.packed) {
         k_gemm_pack_b<<<dim3((unsigned)(max_chunks < 64 ? max_chunks : 64), (unsigned)gb.n_layers), 256, 0, stream>>>(gb);
         if (int rc = check_launch("k_gemm_pack_b")) return rc;
     }
     const int grid = (int)(items < g_gemm_sms ? items : g_gemm_sms);
-    k_gemm3x<<<grid, G_THREADS, G_SMEM, stream>>>(gb);
+    bool all_mn = !gb.packed;
+    for (int i = 0; i < gb.n_layers; ++i) all_mn = all_mn && layer_mn_capable(gb.L[i]);
+    if (gb.packed) k_gemm3x<G_MODE_PACKED><<<grid, GemmCfg<G_MODE_PACKED>::THREADS, G_SMEM, stream>>>(gb);
+    else if (all_mn) k_gemm3x<G_MODE_MN><<<grid, GemmCfg<G_MODE_MN>::THREADS, G_SMEM, stream>>>(gb);
+    else k_gemm3x<G_MODE_LEGACY><<<grid, GemmCfg<G_MODE_LEGACY>::THREADS, G_SMEM, stream>>>(gb);
     return check_launch("k_gemm3x");
 }
 

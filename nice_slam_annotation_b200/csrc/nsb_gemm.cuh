@@ -66,6 +66,8 @@ struct GemmBatch {
     long long M;        // chain: rows shared by all layers
     int m_tiles;        // chain: ceil(M / 128)
     int packed;         // set by gemm3x_launch: every layer's B comes from its b_packed images
+    int debug;          // set by gemm3x_launch from NSB_GEMM_DEBUG (timing experiments, results are wrong):
+                        // 1 no epilogue stores, 2 no A production, 8 no bulk copies of B
     GemmLayer L[GEMM_MAX_LAYERS];
 };
 

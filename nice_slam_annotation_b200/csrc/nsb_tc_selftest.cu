@@ -102,14 +102,16 @@ k_tc_selftest(const float* __restrict__ A, const float* __restrict__ W, float* _
 // Micro-benchmark behind the kernel design: cycles for `count` tf32 MMAs of width N
 // (K = 8 each, A from tensor memory) issued back to back by one thread, accumulating into
 // `nacc` different accumulators in rotation (nacc = 1: one dependent chain).
-__global__ void __launch_bounds__(128, 1) k_tc_mma_latency(long long* out, int N, int count, int nacc) {
-    extern __shared__ __align__(128) float sm[];
+// mode 0: A from tensor memory, B K-major (the decoder kernels' layer chain); 1: A and B K-major in shared memory
+// (nsb_gemm.cu chains); 2: A and B MN-major (weight gradients); 3: A K-major, B MN-major; 4: A MN-major, B K-major.
+__global__ void __launch_bounds__(128, 1) k_tc_mma_latency(long long* out, int N, int count, int nacc, int mode) {
+    extern __shared__ __align__(1024) float sm[];
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint32_t tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5;
     if (warp == 0) tc::tmem_alloc<512>(&tmem_slot);
     if (tid == 0) { tc::mbar_init(&bar, 1); tc::mbar_init_fence(); }
-    for (int i = tid; i < 256 * 8; i += 128) sm[i] = 0.f;
+    for (int i = tid; i < 3 * 2048; i += 128) sm[i] = 0.f;       // A: 8 KB, B: 16 KB (MN-major atoms are 2 KB apart)
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
@@ -126,11 +128,19 @@ __global__ void __launch_bounds__(128, 1) k_tc_mma_latency(long long* out, int N
     __syncthreads();
     if (warp == 0 && tc::elect_one()) {
         tc::fence_after_sync();
-        const uint32_t idesc = tc::idesc_tf32(128, N);
-        const uint64_t b = tc::kmajor_desc(tc::smem_u32(sm), N, 0);
+        const bool a_mn = mode == 2 || mode == 4, b_mn = mode == 2 || mode == 3;
+        const uint32_t idesc = tc::idesc_tf32(128, N) | (a_mn ? tc::IDESC_A_MN : 0u) | (b_mn ? tc::IDESC_B_MN : 0u);
+        const uint32_t sa = tc::smem_u32(sm), sb = sa + 8192;
+        const uint64_t a = a_mn ? tc::mnmajor_desc(sa) : tc::kmajor_desc(sa, 128, 0);
+        const uint64_t b = b_mn ? tc::mnmajor_desc(sb) : tc::kmajor_desc(sb, N, 0);
         const long long t0 = clock64();
-        for (int i = 0; i < count; ++i)
-            tc::mma_ts(tbase + 16 + (uint32_t)((i % nacc) * N), tbase, b, idesc, i >= nacc);
+        if (mode == 0) {
+            for (int i = 0; i < count; ++i)
+                tc::mma_ts(tbase + 16 + (uint32_t)((i % nacc) * N), tbase, b, idesc, i >= nacc);
+        } else {
+            for (int i = 0; i < count; ++i)
+                tc::mma_ss(tbase + 16 + (uint32_t)((i % nacc) * N), a, b, idesc, i >= nacc);
+        }
         tc::mma_commit(&bar);
         const long long t1 = clock64();
         tc::mbar_wait(&bar, 0);
@@ -149,9 +159,11 @@ __global__ void __launch_bounds__(128, 1) k_tc_mma_latency(long long* out, int N
 
 using namespace nsb;
 
-extern "C" int nsb_tc_mma_latency(long long* out2, int N, int count, int nacc, void* stream) {
-    if (!out2 || N < 16 || N > 256 || N % 16 || nacc < 1 || 16 + nacc * N > 512) return set_error(NSB_EINVAL, "bad argument");
-    k_tc_mma_latency<<<1, 128, 256 * 8 * 4, (cudaStream_t)stream>>>(out2, N, count, nacc);
+extern "C" int nsb_tc_mma_latency(long long* out2, int N, int count, int nacc, int mode, void* stream) {
+    if (!out2 || N < 16 || N > 256 || N % 16 || nacc < 1 || 16 + nacc * N > 512 || mode < 0 || mode > 4 ||
+        (mode >= 2 && N % 32))
+        return set_error(NSB_EINVAL, "bad argument");
+    k_tc_mma_latency<<<1, 128, 3 * 2048 * 4, (cudaStream_t)stream>>>(out2, N, count, nacc, mode);
     return check_launch("k_tc_mma_latency");
 }
 

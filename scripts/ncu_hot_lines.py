@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Hot source lines of one kernel of an ncu report (needs -lineinfo + --import-source on).
 
-    python scripts/ncu_hot_lines.py gpurun_out/prof.ncu-rep k_decoders_backward [top]
+    python scripts/ncu_hot_lines.py gpurun_out/prof.ncu-rep k_decoders_backward [top] [launch index among the matches]
 """
 import csv
 import io
@@ -9,9 +9,10 @@ import subprocess
 import sys
 
 
-def main(path, kernel, top=40):
+def main(path, kernel, top=40, launch=None):
+    sel = [] if launch is None else ["--launch-skip", str(launch), "--launch-count", "1"]
     out = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv", "--print-source", "cuda,sass",
-                          "--kernel-name", kernel], capture_output=True, text=True).stdout
+                          "--kernel-name", kernel, *sel], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     fname, hdr, data, seen_fn = "?", None, [], 0
     for r in rows:
@@ -41,4 +42,4 @@ def main(path, kernel, top=40):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1], sys.argv[2], int(sys.argv[3]) if len(sys.argv) > 3 else 40)
+    main(sys.argv[1], sys.argv[2], int(sys.argv[3]) if len(sys.argv) > 3 else 40, int(sys.argv[4]) if len(sys.argv) > 4 else None)
