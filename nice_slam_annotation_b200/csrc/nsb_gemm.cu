@@ -208,6 +208,7 @@ __global__ void __launch_bounds__(GemmCfg<MODE>::THREADS, 1) k_gemm3x(const __gr
     __shared__ __align__(8) uint64_t bar_epi_done[2];     // chain: the epilogue of an item has stored its rows
     __shared__ uint32_t tmem_slot;
     __shared__ __align__(16) float s_bias[GEMM_MAX_LAYERS][256];
+    __shared__ __align__(16) float s_stage[G_EPI_WARPS][32 * 16];      // epilogue transposition tiles
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
@@ -236,29 +237,36 @@ __global__ void __launch_bounds__(GemmCfg<MODE>::THREADS, 1) k_gemm3x(const __gr
     Item it;
 
     if (warp < G_EPI_WARPS) {
-        // ------------------------------------------------ epilogue: TMEM -> registers -> global
+        // ------------------------------------------------ epilogue: TMEM -> registers -> shared (transpose) -> global
+        // tcgen05.ld hands a thread 16 columns of ITS row; stored like that, a warp's request touches 32 different
+        // 128-byte lines (16 bytes of each) and the load/store unit takes 32 passes per request -- measured as a third
+        // of the forward chain.  So a 16-column group goes through a 32 x 16 staging tile (16-byte chunks XOR-swizzled,
+        // conflict-free both ways) and leaves as 4 requests of 8 rows x 64 contiguous bytes; the ReLU-adjoint mask is
+        // read and the split-K sums are reduced (red.global.add.v4) in the same coalesced shape.
         const int quad = warp & 3, half = warp >> 2;       // half < EPI_SPLIT
-        const int row = 32 * quad + lane;
+        float* T = s_stage[warp];
+        const int t_st = lane * 16, t_sx = (lane >> 1) & 3;                 // writer: row = lane, chunk q -> q ^ t_sx
+        const int q_ld = lane & 3;                                          // reader: row 8 j + (lane >> 2), chunk q_ld
         for (int i = 0; iter.next(gb, it); ++i) {
             const GemmLayer& L = gb.L[it.layer];
             const float* bias = s_bias[it.layer];
             const int acc = i & 1;
-            const long long m = it.m0 + row;
             const long long Mv = gb.chain ? gb.M : L.M;
-            const bool valid = m < Mv;
-            float* crow = L.C + m * L.ldc;
-            const float* mrow = L.mask ? L.mask + m * L.ldmask : nullptr;
+            const long long m_base = it.m0 + 32 * quad + (lane >> 2);       // + 8 j: the rows this thread stores
             const bool cvec = (L.ldc & 3) == 0 && aligned16(L.C);
-            const bool mvec = mrow && (L.ldmask & 3) == 0 && aligned16(L.mask);
+            const bool mvec = L.mask && (L.ldmask & 3) == 0 && aligned16(L.mask);
+            const bool bias_epi = L.epi == GEMM_EPI_BIAS_RELU || L.epi == GEMM_EPI_BIAS;
             // ReLU-adjoint mask of a 16-column group (the saved activations): fetched one group ahead of the
             // accumulator, the first one before the MMAs of the item have even finished
-            const bool mpre = L.epi == GEMM_EPI_MASK && mvec && valid;
+            const bool mpre = L.epi == GEMM_EPI_MASK && mvec;
             float4 mk[4], mkn[4];
             auto load_mask = [&](int n0, float4 (&mm)[4]) {
+                const int n = n0 + 4 * q_ld;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int n = n0 + 4 * q;
-                    mm[q] = (mpre && n0 < L.N && n + 3 < L.N_valid) ? ld_v4(mrow + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int j = 0; j < 4; ++j) {
+                    const long long m = m_base + 8 * j;
+                    mm[j] = (mpre && n0 < L.N && n + 3 < L.N_valid && m < Mv) ? ld_v4(L.mask + m * L.ldmask + n)
+                                                                              : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             };
             load_mask(16 * half, mk);
@@ -278,42 +286,59 @@ __global__ void __launch_bounds__(GemmCfg<MODE>::THREADS, 1) k_gemm3x(const __gr
                     tc::fence_before_sync();
                     mbar_arrive(&bar_acc_empty[acc]);
                 }
-                if (!valid || (gb.debug & 1)) continue;      // (debug 1: timing experiment without the epilogue's global traffic)
+                if (bias_epi) {                             // per column: while the thread still holds a row
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int n = n0 + 4 * q;
-                    const float4 mk_q = mk[q];
-                    mk[q] = mkn[q];
-                    if (n >= L.N_valid) continue;
-                    float o[4] = {v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]};
-                    const bool full4 = n + 3 < L.N_valid;
-                    if (L.epi == GEMM_EPI_BIAS_RELU || L.epi == GEMM_EPI_BIAS) {
-                        const float4 b4 = *reinterpret_cast<const float4*>(bias + n);      // zeros beyond N_valid
-                        o[0] += b4.x; o[1] += b4.y; o[2] += b4.z; o[3] += b4.w;
-                        if (L.epi == GEMM_EPI_BIAS_RELU) {
+                    for (int q = 0; q < 4; ++q) {
+                        const float4 b4 = *reinterpret_cast<const float4*>(bias + n0 + 4 * q);     // zeros beyond N_valid
+                        v[4 * q] += b4.x; v[4 * q + 1] += b4.y; v[4 * q + 2] += b4.z; v[4 * q + 3] += b4.w;
+                    }
+                    if (L.epi == GEMM_EPI_BIAS_RELU) {
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) o[j] = fmaxf(o[j], 0.f);
-                        }
-                    } else if (L.epi == GEMM_EPI_MASK) {
+                        for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+                    }
+                }
+                __syncwarp();                               // the previous group has been read out of the tile
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    *reinterpret_cast<float4*>(T + t_st + 4 * (q ^ t_sx)) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                __syncwarp();
+                const int n = n0 + 4 * q_ld;
+                const bool full4 = n + 3 < L.N_valid;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int r = 8 * j + (lane >> 2);
+                    const float4 t4 = *reinterpret_cast<const float4*>(T + r * 16 + 4 * (q_ld ^ ((r >> 1) & 3)));
+                    const float4 mk_j = mk[j];
+                    mk[j] = mkn[j];
+                    const long long m = m_base + 8 * j;
+                    if (m >= Mv || n >= L.N_valid || (gb.debug & 1)) continue;     // (debug 1: timing experiment, no global traffic)
+                    float o[4] = {t4.x, t4.y, t4.z, t4.w};
+                    float* cp = L.C + m * L.ldc + n;
+                    if (L.epi == GEMM_EPI_MASK) {
                         if (mvec && full4) {
-                            o[0] = mk_q.x > 0.f ? o[0] : 0.f; o[1] = mk_q.y > 0.f ? o[1] : 0.f;
-                            o[2] = mk_q.z > 0.f ? o[2] : 0.f; o[3] = mk_q.w > 0.f ? o[3] : 0.f;
+                            o[0] = mk_j.x > 0.f ? o[0] : 0.f; o[1] = mk_j.y > 0.f ? o[1] : 0.f;
+                            o[2] = mk_j.z > 0.f ? o[2] : 0.f; o[3] = mk_j.w > 0.f ? o[3] : 0.f;
                         } else {
+                            const float* mp = L.mask + m * L.ldmask + n;
 #pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                if (n + j < L.N_valid) o[j] = ld_f32(mrow + n + j) > 0.f ? o[j] : 0.f;
+                            for (int e = 0; e < 4; ++e)
+                                if (n + e < L.N_valid) o[e] = ld_f32(mp + e) > 0.f ? o[e] : 0.f;
                         }
                     }
                     if (L.epi == GEMM_EPI_ATOMIC) {
+                        if (cvec && full4) {
+                            red_add_v4(cp, o[0], o[1], o[2], o[3]);
+                        } else {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (n + j < L.N_valid) atomicAdd(crow + n + j, o[j]);
+                            for (int e = 0; e < 4; ++e)
+                                if (n + e < L.N_valid) atomicAdd(cp + e, o[e]);
+                        }
                     } else if (cvec && full4) {
-                        *reinterpret_cast<float4*>(crow + n) = make_float4(o[0], o[1], o[2], o[3]);
+                        *reinterpret_cast<float4*>(cp) = make_float4(o[0], o[1], o[2], o[3]);
                     } else {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (n + j < L.N_valid) crow[n + j] = o[j];
+                        for (int e = 0; e < 4; ++e)
+                            if (n + e < L.N_valid) cp[e] = o[e];
                     }
                 }
             }
