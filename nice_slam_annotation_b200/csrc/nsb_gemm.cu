@@ -86,7 +86,9 @@ struct ItemIter {
             int li = 0;
             while (r >= (long long)gb.L[li].m_tiles * gb.L[li].n_split) { r -= (long long)gb.L[li].m_tiles * gb.L[li].n_split; ++li; }
             const GemmLayer& L = gb.L[li];
-            const long long mt = r / L.n_split, sp = r % L.n_split;
+            // the row tiles of one K split are neighbours in the item order: CTAs b and b + 1 read the same rows of B at
+            // the same time, so the second read is served by L2
+            const long long mt = r % L.m_tiles, sp = r / L.m_tiles;
             g += G;
             it.layer = li; it.dep = 2;
             it.m0 = mt * 128;
@@ -157,9 +159,8 @@ __device__ __forceinline__ float4 load_rquad(const float* base, long long ld, bo
 }
 
 // 16-byte asynchronous copy global -> shared (LDGSTS), the last 16 - src_bytes bytes zero-filled
-__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gmem_src, int src_bytes) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(tc::smem_u32(smem_dst)), "l"(gmem_src), "r"(src_bytes)
-                 : "memory");
+__device__ __forceinline__ void cp_async16(uint32_t smem_dst, const float* gmem_src, int src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(smem_dst), "l"(gmem_src), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() {
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
@@ -437,6 +438,11 @@ __global__ void __launch_bounds__(GemmCfg<MODE>::THREADS, 1) k_gemm3x(const __gr
                 const long long am = it.m0 + 4 * lane;
                 const int a_idx = (lane >> 3) * 512 + ((lane & 7) >> 1) * 8 + (lane & 1) * 4;      // + k * 32, chunk ^ (k & 3)
                 const int nbq = (N + 127) >> 7;                         // float4 per lane and k row of B
+                // bytes of this lane's 16-byte pieces that are inside the operands (-1: no such piece)
+                const long long a_left = Mv - am;
+                const int a_bytes = a_left >= 4 ? 16 : (a_left > 0 ? 4 * (int)a_left : 0);
+                auto piece_bytes = [&](int n) { const int left = L.N_valid - n; return n >= N ? -1 : (left >= 4 ? 16 : (left > 0 ? 4 * left : 0)); };
+                const int b_bytes0 = piece_bytes(4 * lane), b_bytes1 = nbq > 1 ? piece_bytes(128 + 4 * lane) : -1;
                 for (int s = s0; s < ns; s += G_STAGES) {
                     const uint32_t itc = itc_base + (uint32_t)s;
                     const long long kb = it.k0 + (long long)s * G_KC;
@@ -444,23 +450,21 @@ __global__ void __launch_bounds__(GemmCfg<MODE>::THREADS, 1) k_gemm3x(const __gr
                         // 16-byte asynchronous copies straight into the hi images (raw fp32: the tensor core truncates),
                         // all 24 of this thread in flight at once; then the lo images from shared memory
                         tc::mbar_wait(&bar_empty[grp], ((itc / G_STAGES) & 1) ^ 1);
-                        const long long a_left = Mv - am;
-                        const int a_bytes = a_left >= 4 ? 16 : (a_left > 0 ? 4 * (int)a_left : 0);
+                        // (everything that does not depend on the k row is hoisted: this loop is the producers' hot spot)
+                        const uint32_t sa = tc::smem_u32(a_hi), sb = tc::smem_u32(b_hi);
+                        const float* pa = L.A + (kb + w2) * L.lda + am;
+                        const float* pb = L.B + (kb + w2) * L.ldb + 4 * lane;
+                        const long long k_left = it.k1 - kb - w2;                  // rows w2, w2 + 2, .. below it are valid
 #pragma unroll
                         for (int r = 0; r < 8; ++r) {
                             const int kk = w2 + 2 * r;
-                            const int idx = (a_idx ^ ((kk & 3) << 3)) + kk * 32;
-                            const bool kv = kb + kk < it.k1;
-                            cp_async16(a_hi + idx, (kv && a_bytes) ? L.A + (kb + kk) * L.lda + am : L.A, kv ? a_bytes : 0);
-#pragma unroll
-                            for (int q = 0; q < 2; ++q) {
-                                const int n = 128 * q + 4 * lane;
-                                if (q < nbq && n < N) {
-                                    const int left = L.N_valid - n;
-                                    const int b_bytes = left >= 4 ? 16 : (left > 0 ? 4 * left : 0);
-                                    cp_async16(b_hi + idx + q * 2048, (kv && b_bytes) ? L.B + (kb + kk) * L.ldb + n : L.B, kv ? b_bytes : 0);
-                                }
-                            }
+                            const uint32_t o = 4u * (uint32_t)((a_idx ^ ((kk & 3) << 3)) + kk * 32);
+                            const bool kv = 2 * r < k_left;
+                            cp_async16(sa + o, (kv && a_bytes) ? pa : L.A, kv ? a_bytes : 0);
+                            if (b_bytes0 >= 0) cp_async16(sb + o, (kv && b_bytes0) ? pb : L.B, kv ? b_bytes0 : 0);
+                            if (b_bytes1 >= 0) cp_async16(sb + o + 4u * 2048u, (kv && b_bytes1) ? pb + 128 : L.B, kv ? b_bytes1 : 0);
+                            pa += 2 * L.lda;
+                            pb += 2 * L.ldb;
                         }
                         cp_async_wait_all();
 #pragma unroll
