@@ -24,6 +24,13 @@ constexpr int G_B_FLOATS = 256 * G_KC;
 constexpr int G_STAGE_FLOATS = 2 * G_A_FLOATS + 2 * G_B_FLOATS;   // 48 KB
 constexpr int G_PROD_WARPS = 8;
 constexpr int G_SMEM = G_STAGES * G_STAGE_FLOATS * 4 + 1024;
+// MN mode (weight gradients) cuts the same 192 KB into eight stages of K = 8, two per producer group, so that a group
+// has the copies of its next chunk in flight while it finishes the current one
+constexpr int MN_STAGES = 8, MN_KC = 8;
+constexpr int MN_A_FLOATS = 128 * MN_KC, MN_B_FLOATS = 256 * MN_KC;
+constexpr int MN_STAGE_FLOATS = 2 * MN_A_FLOATS + 2 * MN_B_FLOATS;   // 24 KB
+constexpr int G_MAX_STAGES = MN_STAGES;
+static_assert(MN_STAGES * MN_STAGE_FLOATS == G_STAGES * G_STAGE_FLOATS, "both rings fill the same shared memory");
 
 // How the operands of a batch reach shared memory: one kernel instantiation each (all layers of a batch agree), so
 // that the register budget of one path is not set by the others.
@@ -162,9 +169,6 @@ __device__ __forceinline__ float4 load_rquad(const float* base, long long ld, bo
 __device__ __forceinline__ void cp_async16(uint32_t smem_dst, const float* gmem_src, int src_bytes) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(smem_dst), "l"(gmem_src), "r"(src_bytes) : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() {
-    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
-}
 // lo image of four values already in the hi image (raw fp32 there: the tensor core truncates hi itself)
 __device__ __forceinline__ float4 lo_pass(const float* hi_img, float* lo_img, int idx) {
     const float4 v = *reinterpret_cast<const float4*>(hi_img + idx);
@@ -205,7 +209,7 @@ __global__ void __launch_bounds__(GemmCfg<MODE>::THREADS, 1) k_gemm3x(const __gr
     constexpr bool PACKED = MODE == G_MODE_PACKED, MN = MODE == G_MODE_MN;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* stages = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) uint64_t bar_full[G_STAGES], bar_empty[G_STAGES], bar_acc_full[2], bar_acc_empty[2];
+    __shared__ __align__(8) uint64_t bar_full[G_MAX_STAGES], bar_empty[G_MAX_STAGES], bar_acc_full[2], bar_acc_empty[2];
     __shared__ __align__(8) uint64_t bar_epi_done[2];     // chain: the epilogue of an item has stored its rows
     __shared__ uint32_t tmem_slot;
     __shared__ __align__(16) float s_bias[GEMM_MAX_LAYERS][256];
@@ -214,7 +218,7 @@ __global__ void __launch_bounds__(GemmCfg<MODE>::THREADS, 1) k_gemm3x(const __gr
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         // a stage is full when its two producer warps have arrived (+ the bulk copy's expect_tx arrival)
-        for (int s = 0; s < G_STAGES; ++s) { tc::mbar_init(&bar_full[s], 64 + ((PACKED && !(gb.debug & 8)) ? 1 : 0)); tc::mbar_init(&bar_empty[s], 1); }
+        for (int s = 0; s < G_MAX_STAGES; ++s) { tc::mbar_init(&bar_full[s], 64 + ((PACKED && !(gb.debug & 8)) ? 1 : 0)); tc::mbar_init(&bar_empty[s], 1); }
         for (int a = 0; a < 2; ++a) {
             tc::mbar_init(&bar_acc_full[a], 1);
             tc::mbar_init(&bar_acc_empty[a], G_EPI_WARPS * 32);
@@ -354,7 +358,29 @@ __global__ void __launch_bounds__(GemmCfg<MODE>::THREADS, 1) k_gemm3x(const __gr
                 const int acc = i & 1;
                 tc::mbar_wait(&bar_acc_empty[acc], (uint32_t)(((i >> 1) & 1) ^ 1));
                 tc::fence_after_sync();
-                constexpr bool mn = MN;
+                if constexpr (MN) {
+                    // ring of eight K = 8 stages: one K step (three MMAs) per stage; rows beyond the reduction are zero
+                    const uint32_t idesc = tc::idesc_tf32(128, L.N) | tc::IDESC_A_MN | tc::IDESC_B_MN;
+                    const uint32_t dacc = tbase + (uint32_t)(acc * 256);
+                    const int ns = (int)((it.k1 - it.k0 + MN_KC - 1) / MN_KC);
+                    const uint32_t s0a = tc::smem_u32(stages);
+                    const uint64_t dA = tc::mnmajor_desc(s0a, 1024u), dB = tc::mnmajor_desc(s0a + 2 * MN_A_FLOATS * 4, 1024u);
+                    const uint64_t a_lo_off = (MN_A_FLOATS * 4) >> 4, b_lo_off = (uint64_t)(L.N * MN_KC * 4) >> 4;
+                    for (int s = 0; s < ns; ++s, ++itc) {
+                        const int st = itc % MN_STAGES;
+                        tc::mbar_wait(&bar_full[st], (itc / MN_STAGES) & 1);
+                        tc::fence_after_sync();
+                        const uint64_t so = (uint64_t)st * ((MN_STAGE_FLOATS * 4) >> 4);
+                        const uint64_t ah = dA + so, bh = dB + so;
+                        tc::mma_ss(dacc, ah + a_lo_off, bh, idesc, s > 0);
+                        tc::mma_ss(dacc, ah, bh + b_lo_off, idesc, true);
+                        tc::mma_ss(dacc, ah, bh, idesc, true);
+                        tc::mma_commit(&bar_empty[st]);
+                    }
+                    tc::mma_commit(&bar_acc_full[acc]);
+                    continue;
+                }
+                constexpr bool mn = false;
                 const uint32_t idesc = tc::idesc_tf32(128, L.N) | (mn ? (tc::IDESC_A_MN | tc::IDESC_B_MN) : 0u);
                 const uint32_t dacc = tbase + (uint32_t)(acc * 256);
                 const int ns = (int)((it.k1 - it.k0 + G_KC - 1) / G_KC);
@@ -432,87 +458,112 @@ __global__ void __launch_bounds__(GemmCfg<MODE>::THREADS, 1) k_gemm3x(const __gr
             float* b_hi = a_lo + G_A_FLOATS;
             float* b_lo = b_hi + N * G_KC;
             if constexpr (MN) {
-                // ---- both operands row-contiguous: MN-major images, one float4 along the rows per lane.
-                // Warp w2 of the group takes the k rows w2, w2 + 2, .. of the chunk, four at a time.
+                // ---- both operands row-contiguous: MN-major images (atoms [8 k][32 rows]), one 16-byte piece along the rows
+                // per lane and k row.  Group g takes the chunks c = g (mod 4) of the global chunk sequence, i.e. ring
+                // stages g and g + 4 in turn; warp w2 of the group takes the k rows w2, w2 + 2, w2 + 4, w2 + 6 of a chunk.
+                const int nsm = (int)((it.k1 - it.k0 + MN_KC - 1) / MN_KC);
+                const int s0m = (grp - (int)(itc_base & 3) + 4) & 3;
                 float csum[4] = {0.f, 0.f, 0.f, 0.f};
                 const long long am = it.m0 + 4 * lane;
-                const int a_idx = (lane >> 3) * 512 + ((lane & 7) >> 1) * 8 + (lane & 1) * 4;      // + k * 32, chunk ^ (k & 3)
+                const int a_idx = (lane >> 3) * 256 + ((lane & 7) >> 1) * 8 + (lane & 1) * 4;      // + k * 32, chunk ^ (k & 3)
                 const int nbq = (N + 127) >> 7;                         // float4 per lane and k row of B
                 // bytes of this lane's 16-byte pieces that are inside the operands (-1: no such piece)
                 const long long a_left = Mv - am;
                 const int a_bytes = a_left >= 4 ? 16 : (a_left > 0 ? 4 * (int)a_left : 0);
                 auto piece_bytes = [&](int n) { const int left = L.N_valid - n; return n >= N ? -1 : (left >= 4 ? 16 : (left > 0 ? 4 * left : 0)); };
                 const int b_bytes0 = piece_bytes(4 * lane), b_bytes1 = nbq > 1 ? piece_bytes(128 + 4 * lane) : -1;
-                for (int s = s0; s < ns; s += G_STAGES) {
-                    const uint32_t itc = itc_base + (uint32_t)s;
-                    const long long kb = it.k0 + (long long)s * G_KC;
-                    if (avec && bvec) {
-                        // 16-byte asynchronous copies straight into the hi images (raw fp32: the tensor core truncates),
-                        // all 24 of this thread in flight at once; then the lo images from shared memory
-                        tc::mbar_wait(&bar_empty[grp], ((itc / G_STAGES) & 1) ^ 1);
-                        // (everything that does not depend on the k row is hoisted: this loop is the producers' hot spot)
-                        const uint32_t sa = tc::smem_u32(a_hi), sb = tc::smem_u32(b_hi);
+                auto stage_of = [&](int s) { return (int)((itc_base + (uint32_t)s) % MN_STAGES); };
+                auto wait_empty = [&](int s) {
+                    const uint32_t c = itc_base + (uint32_t)s;
+                    tc::mbar_wait(&bar_empty[c % MN_STAGES], ((c / MN_STAGES) & 1) ^ 1);
+                };
+                if (avec && bvec) {
+                    // 16-byte asynchronous copies (LDGSTS) straight into the hi images -- raw fp32, the tensor core truncates
+                    // -- then the lo images x - trunc(x) of the same pieces from shared memory.  Software pipeline: the
+                    // copies of the group's next chunk are issued before it waits for the current one.
+                    auto issue = [&](int s) {
+                        wait_empty(s);
+                        float* st_base = stages + (size_t)stage_of(s) * MN_STAGE_FLOATS;
+                        const uint32_t sa = tc::smem_u32(st_base), sb = sa + 2 * MN_A_FLOATS * 4;
+                        const long long kb = it.k0 + (long long)s * MN_KC;
                         const float* pa = L.A + (kb + w2) * L.lda + am;
                         const float* pb = L.B + (kb + w2) * L.ldb + 4 * lane;
                         const long long k_left = it.k1 - kb - w2;                  // rows w2, w2 + 2, .. below it are valid
 #pragma unroll
-                        for (int r = 0; r < 8; ++r) {
+                        for (int r = 0; r < 4; ++r) {
                             const int kk = w2 + 2 * r;
                             const uint32_t o = 4u * (uint32_t)((a_idx ^ ((kk & 3) << 3)) + kk * 32);
                             const bool kv = 2 * r < k_left;
                             cp_async16(sa + o, (kv && a_bytes) ? pa : L.A, kv ? a_bytes : 0);
                             if (b_bytes0 >= 0) cp_async16(sb + o, (kv && b_bytes0) ? pb : L.B, kv ? b_bytes0 : 0);
-                            if (b_bytes1 >= 0) cp_async16(sb + o + 4u * 2048u, (kv && b_bytes1) ? pb + 128 : L.B, kv ? b_bytes1 : 0);
+                            if (b_bytes1 >= 0) cp_async16(sb + o + 4u * 1024u, (kv && b_bytes1) ? pb + 128 : L.B, kv ? b_bytes1 : 0);
                             pa += 2 * L.lda;
                             pb += 2 * L.ldb;
                         }
-                        cp_async_wait_all();
+                        asm volatile("cp.async.commit_group;\n" ::: "memory");
+                    };
+                    if (s0m < nsm) issue(s0m);
+                    for (int s = s0m; s < nsm; s += 4) {
+                        if (s + 4 < nsm) {
+                            issue(s + 4);
+                            asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+                        } else {
+                            asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+                        }
+                        float* a_hi8 = stages + (size_t)stage_of(s) * MN_STAGE_FLOATS;
+                        float* a_lo8 = a_hi8 + MN_A_FLOATS;
+                        float* b_hi8 = a_lo8 + MN_A_FLOATS;
+                        float* b_lo8 = b_hi8 + N * MN_KC;
 #pragma unroll
-                        for (int r = 0; r < 8; ++r) {
+                        for (int r = 0; r < 4; ++r) {
                             const int kk = w2 + 2 * r;
                             const int idx = (a_idx ^ ((kk & 3) << 3)) + kk * 32;
-                            const float4 v = lo_pass(a_hi, a_lo, idx);
+                            const float4 v = lo_pass(a_hi8, a_lo8, idx);
                             csum[0] += v.x; csum[1] += v.y; csum[2] += v.z; csum[3] += v.w;
-#pragma unroll
-                            for (int q = 0; q < 2; ++q)
-                                if (q < nbq && 128 * q + 4 * lane < N) lo_pass(b_hi, b_lo, idx + q * 2048);
+                            if (b_bytes0 >= 0) lo_pass(b_hi8, b_lo8, idx);
+                            if (b_bytes1 >= 0) lo_pass(b_hi8, b_lo8, idx + 1024);
                         }
                         tc::fence_async_smem();
-                        mbar_arrive(&bar_full[grp]);
-                        continue;
+                        mbar_arrive(&bar_full[stage_of(s)]);
                     }
-#pragma unroll
-                    for (int bt = 0; bt < 2; ++bt) {
+                } else {
+                    // operands that are not 16-byte addressable: through registers, one chunk at a time
+                    for (int s = s0m; s < nsm; s += 4) {
+                        const long long kb = it.k0 + (long long)s * MN_KC;
                         float4 va[4], vb[4][2];
 #pragma unroll
                         for (int r = 0; r < 4; ++r) {
-                            const int kk = w2 + 2 * (4 * bt + r);
+                            const int kk = w2 + 2 * r;
                             va[r] = load_rquad(L.A, L.lda, avec, am, Mv, kb + kk, it.k1);
 #pragma unroll
                             for (int q = 0; q < 2; ++q)
                                 if (q < nbq) vb[r][q] = load_rquad(L.B, L.ldb, bvec, 128 * q + 4 * lane, 128 * q + 4 * lane < N ? L.N_valid : 0, kb + kk, it.k1);
                         }
-                        if (bt == 0) tc::mbar_wait(&bar_empty[grp], ((itc / G_STAGES) & 1) ^ 1);
+                        wait_empty(s);
+                        float* a_hi8 = stages + (size_t)stage_of(s) * MN_STAGE_FLOATS;
+                        float* a_lo8 = a_hi8 + MN_A_FLOATS;
+                        float* b_hi8 = a_lo8 + MN_A_FLOATS;
+                        float* b_lo8 = b_hi8 + N * MN_KC;
 #pragma unroll
                         for (int r = 0; r < 4; ++r) {
-                            const int kk = w2 + 2 * (4 * bt + r);
+                            const int kk = w2 + 2 * r;
                             const int idx = (a_idx ^ ((kk & 3) << 3)) + kk * 32;
-                            split_store(a_hi, a_lo, idx, va[r]);
+                            split_store(a_hi8, a_lo8, idx, va[r]);
                             csum[0] += va[r].x; csum[1] += va[r].y; csum[2] += va[r].z; csum[3] += va[r].w;
 #pragma unroll
                             for (int q = 0; q < 2; ++q)
-                                if (q < nbq && 128 * q + 4 * lane < N) split_store(b_hi, b_lo, idx + q * 2048, vb[r][q]);
+                                if (q < nbq && 128 * q + 4 * lane < N) split_store(b_hi8, b_lo8, idx + q * 1024, vb[r][q]);
                         }
+                        tc::fence_async_smem();
+                        mbar_arrive(&bar_full[stage_of(s)]);
                     }
-                    tc::fence_async_smem();
-                    mbar_arrive(&bar_full[grp]);
                 }
-                if (L.colsum && s0 < ns) {
+                if (L.colsum && s0m < nsm) {
 #pragma unroll
                     for (int c = 0; c < 4; ++c)
                         if (am + c < Mv) atomicAdd(L.colsum + am + c, csum[c]);
                 }
-                itc_base += (uint32_t)ns;
+                itc_base += (uint32_t)nsm;
             } else {
             float csum[2] = {0.f, 0.f};
             for (int s = s0; s < ns; s += G_STAGES) {

@@ -47,7 +47,10 @@ __device__ __forceinline__ uint64_t kmajor_desc(uint32_t saddr, int R, int k0) {
 __host__ __device__ __forceinline__ int mnmajor_index(int r, int k) {
     return (r >> 5) * 512 + k * 32 + ((((r >> 3) & 3) ^ (k & 3)) << 3) + (r & 7);
 }
-__device__ __forceinline__ uint64_t mnmajor_desc(uint32_t saddr) { return smem_desc(saddr, 2048u, 512u) | (1ull << 61); }
+// (lbo_bytes: distance of the atoms = 128 B x the k rows of a chunk; 2048 for 16-k chunks)
+__device__ __forceinline__ uint64_t mnmajor_desc(uint32_t saddr, uint32_t lbo_bytes = 2048u) {
+    return smem_desc(saddr, lbo_bytes, 512u) | (1ull << 61);
+}
 constexpr uint32_t IDESC_A_MN = 1u << 15, IDESC_B_MN = 1u << 16;
 
 // instruction descriptor (cute::UMMA::InstrDescriptor): tf32 x tf32 -> f32, K-major A and B
