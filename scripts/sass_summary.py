@@ -30,6 +30,7 @@ def main():
         m = re.search(r"Function : (\S+)", line)
         if m:
             name = subprocess.run(["c++filt", m.group(1)], capture_output=True, text=True).stdout.strip()
+            name = name.replace("(anonymous namespace)::", "")                 # k_gemm3x<mode> lives in one
             cur = per.setdefault(re.sub(r"\(.*", "", name), collections.Counter())
             continue
         if cur is None:
