@@ -4,9 +4,11 @@
 // take alternate 16-column groups), one MMA-issuing warp (one thread), in PACKED mode a warp that fetches the
 // packed B images with bulk asynchronous copies (one thread: it runs ahead of the chain dependency the
 // producers wait for, so the weights of the next item are in place when its rows become readable), and
-// eight producer warps.  Shared memory: 4 stages x { A hi, A lo
-// (128 x 16), B hi, B lo (256 x 16) } = 4 x 48 KB of operand images.  Tensor memory: two 256-column
-// accumulators, so the epilogue of one item overlaps the MMAs of the next.
+// eight producer warps in four groups.  Shared memory: a ring of 4 stages x { A hi, A lo (128 x 16), B hi, B lo
+// (256 x 16) } = 4 x 48 KB of operand images (MN mode: 8 stages of K = 8, two per producer group).  Tensor
+// memory: two 256-column accumulators, so the epilogue of one item overlaps the MMAs of the next.
+// What the structure answers to (profiles/r02zz_gemm3x_ablation.txt): the tensor pipe, L2 and DRAM were never
+// the limit of this kernel -- the instruction streams of the producer warps and the load/store unit were.
 #include "nsb_gemm.cuh"
 
 #include <cstdlib>
@@ -40,7 +42,7 @@ static_assert(MN_STAGES * MN_STAGE_FLOATS == G_STAGES * G_STAGE_FLOATS, "both ri
 enum : int { G_MODE_LEGACY = 0, G_MODE_PACKED = 1, G_MODE_MN = 2 };
 template <int MODE>
 struct GemmCfg {
-    static constexpr int EPI_WARPS = MODE == G_MODE_MN ? 4 : 8;      // weight gradients: one epilogue per 64 chunks
+    static constexpr int EPI_WARPS = MODE == G_MODE_MN ? 4 : 8;      // weight gradients: one epilogue per 128 chunks
     static constexpr int MMA_WARP = EPI_WARPS;
     static constexpr int BULK_WARP = MODE == G_MODE_PACKED ? EPI_WARPS + 1 : -1;
     static constexpr int PROD_WARP0 = EPI_WARPS + (MODE == G_MODE_PACKED ? 2 : 1);
