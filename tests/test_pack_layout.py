@@ -81,3 +81,25 @@ def test_fragment_emulation_matches_mlp(kind):
     if kind != 0:
         assert np.allclose(dE[:, :93], e.grad.numpy(), rtol=1e-9, atol=1e-10)
         assert np.allclose(dE[:, 93:], 0.0)
+
+
+def test_imap_workspace_sizes_hold_the_weight_images():
+    """Host-only size queries of the iMAP* path (no GPU work): the forward workspace and the backward scratch hold
+    the activations AND the per-launch operand images of the weight matrices (csrc/nsb_imap.cu: pack_floats), at
+    offsets that keep the 16-byte alignment the bulk copies need."""
+    L = _lib.lib()
+
+    def pack(N, K):                     # csrc/nsb_gemm.cuh: gemm3x_pack_floats (hi + lo image of every 16-k chunk)
+        return (K + 15) // 16 * N * 32
+
+    for hidden in (16, 64, 256):
+        need = pack(hidden, 93) + 3 * pack(hidden, hidden) + pack(16, hidden) + pack(hidden, 4) + pack(96, hidden)
+        for P in (1, 777, 220000, 300000):
+            acts = P * (96 + 4 * hidden)
+            assert L.nsb_imap_workspace_floats(P, hidden, 1) == acts + need
+            assert L.nsb_imap_backward_scratch_floats(P, hidden) == acts + need
+            chunk = min(P, 262144)
+            assert L.nsb_imap_workspace_floats(P, hidden, 0) == chunk * (96 + 2 * hidden) + need
+            assert acts % 4 == 0 and (chunk * (96 + 2 * hidden)) % 4 == 0      # the images start 16-byte aligned
+    assert L.nsb_gemm3x_pack_floats(93, 777) == pack(96, 777)                  # N padded to the MMA width
+    assert L.nsb_gemm3x_pack_floats(256, 16) == 256 * 32
